@@ -1,0 +1,224 @@
+"""ctypes bindings for the CPU checker -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+Loads oracle/liborb_oracle.so (our restatement, orb_oracle.cpp) and, when present,
+oracle/_ref/libreforb{,_mono}.so (the reference's own src/ORBextractor.cc compiled in place).
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+CAND_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+_u8p = C.POINTER(C.c_uint8)
+_vp = C.c_void_p
+
+
+def build(ref: str = "/root/reference") -> None:
+    """Compile the oracle (and oracle/_ref when the reference tree is present)."""
+    subprocess.run(["make", "-s", "-C", str(HERE), f"REF={ref}", "all"], check=True)
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(_u8p)
+
+
+class _Base:
+    """Common driver for the three libraries (same call shapes, different symbol prefix)."""
+
+    prefix = ""
+
+    def __init__(self, lib: C.CDLL, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.lib = lib
+        p = self.prefix
+        f = getattr(lib, p + "create")
+        f.restype = _vp
+        f.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        self.h = _vp(f(nfeatures, scale_factor, nlevels, ini_th, min_th))
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        ex = getattr(lib, p + "extract")
+        ex.restype = C.c_int
+        ex.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_size_t, _vp, _vp, C.c_int]
+        self._extract = ex
+        getattr(lib, p + "destroy").argtypes = [_vp]
+        for name in ("table",):
+            getattr(lib, p + name).argtypes = [_vp, C.c_int, _vp]
+        getattr(lib, p + "quotas").argtypes = [_vp, _vp]
+        getattr(lib, p + "umax").argtypes = [_vp, _vp]
+        getattr(lib, p + "pyramid_copy").argtypes = [_vp, C.c_int, C.c_int, _vp]
+
+    def close(self):
+        if self.h:
+            getattr(self.lib, self.prefix + "destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def extract(self, img: np.ndarray | None):
+        """-> (keypoints structured array, descriptors [n,32] u8) or an int status < 0."""
+        cap = self.nfeatures + 64 * self.nlevels + 4096
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        if img is None or img.size == 0:
+            n = self._extract(self.h, None, 0, 0, 0, kps.ctypes.data, desc.ctypes.data, cap)
+            return n
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        n = self._extract(self.h, img.ctypes.data, img.shape[1], img.shape[0], img.strides[0],
+                          kps.ctypes.data, desc.ctypes.data, cap)
+        if n < 0:
+            return n
+        assert n <= cap
+        return kps[:n].copy(), desc[:n].copy()
+
+    def table(self, which: int) -> np.ndarray:
+        out = np.zeros(self.nlevels, np.float32)
+        getattr(self.lib, self.prefix + "table")(self.h, which, out.ctypes.data)
+        return out
+
+    def quotas(self) -> np.ndarray:
+        out = np.zeros(self.nlevels, np.int32)
+        getattr(self.lib, self.prefix + "quotas")(self.h, out.ctypes.data)
+        return out
+
+    def umax(self) -> np.ndarray:
+        out = np.zeros(16, np.int32)
+        getattr(self.lib, self.prefix + "umax")(self.h, out.ctypes.data)
+        return out
+
+
+class Oracle(_Base):
+    """Our restatement (liborb_oracle.so, canonical quadtree tie-break)."""
+
+    prefix = "orbo_"
+    _lib = None
+
+    @classmethod
+    def load(cls) -> C.CDLL:
+        if cls._lib is None:
+            path = HERE / "liborb_oracle.so"
+            if not path.exists():
+                build()
+            lib = C.CDLL(str(path))
+            lib.orbo_level_size.argtypes = [_vp, C.c_int, _vp, _vp]
+            lib.orbo_blurred_copy.argtypes = [_vp, C.c_int, _vp]
+            lib.orbo_candidates.argtypes = [_vp, C.c_int, _vp, C.c_int]
+            lib.orbo_level_keypoints.argtypes = [_vp, C.c_int, _vp, C.c_int]
+            lib.orbo_distribute.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_int, _vp, C.c_int]
+            lib.orbo_describe.argtypes = [_vp, C.c_size_t, C.c_int, C.c_int, C.c_float, _vp]
+            lib.orbo_ic_angle.argtypes = [_vp, C.c_size_t, C.c_int, C.c_int]
+            lib.orbo_ic_angle.restype = C.c_float
+            lib.orbo_pattern.restype = _vp
+            cls._lib = lib
+        return cls._lib
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        super().__init__(self.load(), nfeatures, scale_factor, nlevels, ini_th, min_th)
+
+    def level_size(self, level: int):
+        c, r = C.c_int(), C.c_int()
+        assert self.lib.orbo_level_size(self.h, level, C.byref(c), C.byref(r)) == 0
+        return c.value, r.value
+
+    def pyramid(self, level: int, border: int = 19) -> np.ndarray:
+        c, r = self.level_size(level)
+        out = np.zeros((r + 2 * border, c + 2 * border), np.uint8)
+        assert self.lib.orbo_pyramid_copy(self.h, level, border, out.ctypes.data) == 0
+        return out
+
+    def blurred(self, level: int):
+        c, r = self.level_size(level)
+        out = np.zeros((r, c), np.uint8)
+        if self.lib.orbo_blurred_copy(self.h, level, out.ctypes.data) != 0:
+            return None
+        return out
+
+    def candidates(self, level: int) -> np.ndarray:
+        n = self.lib.orbo_candidates(self.h, level, None, 0)
+        out = np.zeros(max(n, 1), CAND_DTYPE)
+        self.lib.orbo_candidates(self.h, level, out.ctypes.data, n)
+        return out[:n]
+
+    def level_keypoints(self, level: int) -> np.ndarray:
+        n = self.lib.orbo_level_keypoints(self.h, level, None, 0)
+        out = np.zeros(max(n, 1), KP_DTYPE)
+        self.lib.orbo_level_keypoints(self.h, level, out.ctypes.data, n)
+        return out[:n]
+
+
+def distribute(xs, ys, resp, min_x, max_x, min_y, max_y, n_target):
+    """Stand-alone canonical quadtree distribution -> indices of survivors in output order."""
+    lib = Oracle.load()
+    xs = np.ascontiguousarray(xs, np.int32)
+    ys = np.ascontiguousarray(ys, np.int32)
+    resp = np.ascontiguousarray(resp, np.int32)
+    out = np.zeros(len(xs) + 8, np.int32)
+    n = lib.orbo_distribute(xs.ctypes.data, ys.ctypes.data, resp.ctypes.data, len(xs), min_x, max_x,
+                            min_y, max_y, n_target, out.ctypes.data, len(out))
+    if n < 0:
+        return n
+    return out[:n].copy()
+
+
+def describe(img: np.ndarray, x: int, y: int, angle_deg: float) -> np.ndarray:
+    out = np.zeros(32, np.uint8)
+    Oracle.load().orbo_describe(img.ctypes.data, img.strides[0], x, y, angle_deg, out.ctypes.data)
+    return out
+
+
+def ic_angle(img: np.ndarray, x: int, y: int) -> float:
+    return float(Oracle.load().orbo_ic_angle(img.ctypes.data, img.strides[0], x, y))
+
+
+def pattern() -> np.ndarray:
+    p = Oracle.load().orbo_pattern()
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_int8)), shape=(512, 2)).copy()
+
+
+class Reference(_Base):
+    """The reference's own ORBextractor.cc (oracle/_ref).  mono=True -> monotone-allocator build,
+    whose heap-address tie-break coincides with the canonical rule."""
+
+    prefix = "reforb_"
+    _libs: dict = {}
+
+    @classmethod
+    def available(cls, mono: bool = True) -> bool:
+        return (HERE / "_ref" / ("libreforb_mono.so" if mono else "libreforb.so")).exists()
+
+    @classmethod
+    def load(cls, mono: bool) -> C.CDLL:
+        if mono not in cls._libs:
+            path = HERE / "_ref" / ("libreforb_mono.so" if mono else "libreforb.so")
+            lib = C.CDLL(str(path))
+            lib.reforb_pyramid_info.argtypes = [_vp, C.c_int, _vp, _vp]
+            cls._libs[mono] = lib
+        return cls._libs[mono]
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, mono=True):
+        super().__init__(self.load(mono), nfeatures, scale_factor, nlevels, ini_th, min_th)
+
+    def level_size(self, level: int):
+        c, r = C.c_int(), C.c_int()
+        assert self.lib.reforb_pyramid_info(self.h, level, C.byref(c), C.byref(r)) == 0
+        return c.value, r.value
+
+    def pyramid(self, level: int, border: int = 19) -> np.ndarray:
+        c, r = self.level_size(level)
+        out = np.zeros((r + 2 * border, c + 2 * border), np.uint8)
+        assert self.lib.reforb_pyramid_copy(self.h, level, border, out.ctypes.data) == 0
+        return out
