@@ -1,0 +1,118 @@
+/*
+ * include/borb.h -- C ABI of the B200 ORB extraction library (liborb_b200.so).
+ *
+ * This is the boundary a maintainer of the reference binds instead of the CPU body of
+ * ORB_SLAM2::ORBextractor (reference: include/ORBextractor.h:46-144, src/ORBextractor.cc).
+ * Plain pointers and sizes only; no OpenCV, torch or CUDA types.  The C++ host shim
+ * (orb_slam2_test_b200/shim/ORBextractor.{h,cc}) keeps the reference's class interface on top
+ * of these calls; INTEGRATION.md shows the binding.
+ *
+ * All functions return BORB_OK (0) or a negative borb_status; borb_last_error() gives the
+ * message for the calling thread.  There is no CPU fallback: without a CUDA device every compute
+ * entry point fails with BORB_ERR_CUDA.
+ *
+ * Threading (reference: src/Frame.cc:110-113 runs the left and right extractor on two threads):
+ * one handle may be used by one thread at a time; different handles are fully independent (own
+ * stream, graph, device and pinned buffers).
+ */
+#ifndef BORB_H
+#define BORB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct borb_extractor borb_extractor;
+
+typedef enum borb_status {
+    BORB_OK = 0,
+    BORB_ERR_ARG = -1,      /* bad argument / unsupported parameter range               */
+    BORB_ERR_CUDA = -2,     /* CUDA runtime failure, or no device                        */
+    BORB_ERR_GEOMETRY = -3, /* image too small for the pyramid / aspect ratio < 0.5 (the
+                               reference divides by zero there, src/ORBextractor.cc:674-680) */
+    BORB_ERR_CAPACITY = -4, /* batch larger than max_batch, or internal buffer overflow   */
+    BORB_ERR_STATE = -5     /* result requested before any extraction                     */
+} borb_status;
+
+/* Binary image of cv::KeyPoint (7 x 4 bytes), the element type of the reference's output
+ * vector (src/ORBextractor.cc:1361-1395). */
+typedef struct borb_keypoint {
+    float x, y;     /* pt, original-image coordinates (level coords * mvScaleFactor[octave]) */
+    float size;     /* (float)(int)(31 * mvScaleFactor[octave])                              */
+    float angle;    /* degrees [0,360)                                                       */
+    float response; /* FAST score                                                            */
+    int32_t octave;
+    int32_t class_id; /* always -1 */
+} borb_keypoint;
+
+/* -- lifetime: replaces ORBextractor::ORBextractor (src/ORBextractor.cc:432-521) ------------- */
+
+/* device < 0 selects the current CUDA device.  max_batch >= 1 is the largest number of frames
+ * one borb_extract_* call may carry (frames of one call run through the kernels together). */
+int borb_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast,
+                int device, int max_batch, borb_extractor **out);
+void borb_destroy(borb_extractor *h);
+const char *borb_last_error(void);
+const char *borb_version(void);
+
+/* -- constructor-derived tables: replace the inline getters (include/ORBextractor.h:78-98) ---- */
+int borb_levels(const borb_extractor *h);
+float borb_scale_factor(const borb_extractor *h); /* GetScaleFactor(): the double member as float */
+/* which: 0 mvScaleFactor, 1 mvInvScaleFactor, 2 mvLevelSigma2, 3 mvInvLevelSigma2; out[nlevels] */
+int borb_table(const borb_extractor *h, int which, float *out);
+int borb_features_per_level(const borb_extractor *h, int32_t *out); /* mnFeaturesPerLevel */
+int borb_umax(const borb_extractor *h, int32_t *out);               /* 16 entries         */
+
+/* -- extraction: replaces ORBextractor::operator() (src/ORBextractor.cc:1330-1397) ------------ */
+
+/* flags */
+#define BORB_WANT_PYRAMID 1u /* also bring the padded pyramid back to pinned host memory
+                                (mvImagePyramid, include/ORBextractor.h:101)                  */
+
+/* n_frames 8-bit single-channel images in HOST memory: frame f starts at img + f*frame_stride,
+ * rows are `step` bytes apart.  Copies them to the device, runs the whole path, copies the
+ * results back and returns when they are readable through borb_result(). */
+int borb_extract_host(borb_extractor *h, const uint8_t *img, int n_frames, int cols, int rows,
+                      size_t step, size_t frame_stride, unsigned flags);
+
+/* Same, but the images already are in DEVICE memory and the results stay on the device until
+ * borb_fetch() is called (kernel-only timing, pipelines that keep descriptors on the GPU). */
+int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n_frames, int cols,
+                        int rows, size_t step, size_t frame_stride);
+int borb_fetch(borb_extractor *h, unsigned flags);
+/* blocks until everything enqueued on the handle's stream has finished */
+int borb_sync(borb_extractor *h);
+
+/* Results of the last call, frame f: pointers into the handle's pinned staging memory, valid
+ * until the next extract call on this handle.  *n may be 0 (desc/kps then still valid). */
+int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps,
+                const uint8_t **desc, int *n);
+/* Level `level` of frame f: *data points at pixel (0,0) of the level image inside its padded
+ * (19-pixel reflect-101 frame) parent, rows *step bytes apart -- the same view
+ * mvImagePyramid[level] is (src/ORBextractor.cc:1417).  Needs BORB_WANT_PYRAMID. */
+int borb_pyramid(const borb_extractor *h, int frame, int level, const uint8_t **data, int *cols,
+                 int *rows, size_t *step);
+/* geometry only (valid after any extract call) */
+int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows);
+
+/* number of kernel launches one extract call enqueues (for bench.py's gpu_launches) */
+int borb_launches_per_call(const borb_extractor *h);
+/* CUDA-event time of the last borb_extract_device call's kernels, milliseconds (<0: n/a) */
+float borb_last_device_ms(const borb_extractor *h);
+
+/* -- stage taps for parity tests (device -> caller buffers; not part of the hot path) -------- */
+/* FAST candidates of (frame, level) before distribution, coords relative to (16,16);
+ * unordered.  Returns count via *n (may exceed cap; only cap entries are written). */
+int borb_debug_candidates(borb_extractor *h, int frame, int level, int32_t *xs, int32_t *ys,
+                          int32_t *scores, int cap, int *n);
+int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out /* cols*rows */);
+/* host evaluation of the device sin/cos routine (same inline function, host build) */
+void borb_debug_sincos(float radians, float *s, float *c);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,710 @@
+/*
+ * borb_api.cu -- host side of liborb_b200.so: the C ABI declared in include/borb.h.
+ *
+ * Per handle: one CUDA stream, one device "plan" per image geometry (level sizes, resize tap
+ * tables, FAST cell list, blur tile list, quadtree parameters -- everything that the reference
+ * recomputes per call from (cols, rows) in ComputePyramid / ComputeKeyPointsOctTree,
+ * src/ORBextractor.cc:1400-1443, :966-996), device slabs for max_batch frames, pinned staging,
+ * and a cache of instantiated CUDA graphs (one per call shape) so a call is one graph launch.
+ *
+ * No CPU fallback: if the device work cannot run the call fails with BORB_ERR_CUDA.
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/borb.h"
+#include "borb_internal.h"
+#include "k_blur.cuh"
+#include "k_describe.cuh"
+#include "k_fast.cuh"
+#include "k_pyramid.cuh"
+#include "k_quadtree.cuh"
+
+static_assert(sizeof(borb_keypoint) == 28 && sizeof(BorbKpRec) == 28, "cv::KeyPoint layout");
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(BORB_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_),   \
+                        __FILE__, __LINE__);                                              \
+    } while (0)
+
+const signed char kPattern[1024] = {
+#include "orb_pattern.inc"
+};
+
+inline int round_half_even(float v) { return (int)lrintf(v); }
+inline int round_half_even_d(double v) { return (int)lrint(v); }
+inline int floor_f(float v)
+{
+    int i = (int)v;
+    return i - (v < (float)i);
+}
+inline short sat16(int v) { return (short)(v < -32768 ? -32768 : v > 32767 ? 32767 : v); }
+inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
+
+struct GraphKey {
+    int mode;            /* 0 host path, 1 device path */
+    const void *src;
+    int n;
+    size_t step, stride;
+    unsigned flags;
+    bool operator==(const GraphKey &o) const
+    {
+        return mode == o.mode && src == o.src && n == o.n && step == o.step && stride == o.stride &&
+               flags == o.flags;
+    }
+};
+struct GraphEntry {
+    GraphKey key;
+    cudaGraphExec_t exec;
+};
+
+} // namespace
+
+struct borb_extractor {
+    /* constructor state, reference src/ORBextractor.cc:432-521 */
+    int nfeatures, nlevels, ini_th, min_th;
+    double scale_factor;
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> quota;
+    int umax[16];
+
+    int device, max_batch;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool use_graph = true;
+
+    /* geometry-dependent state */
+    bool have_plan = false;
+    BorbPlan plan;
+    int qt_M = 0;
+    std::vector<BorbCell> cells;
+    std::vector<BorbTile> tiles;
+    BorbPlan *d_plan = nullptr;
+    BorbCell *d_cells = nullptr;
+    BorbTile *d_tiles = nullptr;
+    int *d_tab_i = nullptr;
+    short *d_tab_s = nullptr;
+    signed char *d_pattern = nullptr;
+    uint8_t *d_in = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
+    uint32_t *d_cand_xy = nullptr, *d_cand_score = nullptr, *d_cand_node = nullptr;
+    int *d_ncand = nullptr, *d_nlkp = nullptr, *d_nout = nullptr, *d_err = nullptr;
+    uint32_t *d_lkp_xy = nullptr, *d_lkp_score = nullptr;
+    BorbKpRec *d_out_kp = nullptr;
+    uint8_t *d_out_desc = nullptr;
+    /* pinned staging */
+    uint8_t *h_in = nullptr, *h_pyr = nullptr, *h_out_desc = nullptr;
+    BorbKpRec *h_out_kp = nullptr;
+    int *h_nout = nullptr, *h_err = nullptr;
+
+    std::vector<GraphEntry> graphs;
+    int last_n = 0;          /* frames of the last call */
+    bool results_on_host = false, pyramid_on_host = false;
+    float last_ms = -1.f;
+};
+
+namespace {
+
+/* ---- constructor tables: src/ORBextractor.cc:437-520, same float/double mix ---- */
+void build_tables(borb_extractor *h)
+{
+    const int nl = h->nlevels;
+    h->scale.assign(nl, 1.f);
+    h->sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        h->scale[i] = (float)(h->scale[i - 1] * h->scale_factor); /* member is a double */
+        h->sigma2[i] = h->scale[i] * h->scale[i];
+    }
+    h->inv_scale.resize(nl);
+    h->inv_sigma2.resize(nl);
+    for (int i = 0; i < nl; ++i) {
+        h->inv_scale[i] = 1.0f / h->scale[i];
+        h->inv_sigma2[i] = 1.0f / h->sigma2[i];
+    }
+    h->quota.assign(nl, 0);
+    const float factor = (float)(1.0f / h->scale_factor);
+    float want = h->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        h->quota[l] = round_half_even(want);
+        sum += h->quota[l];
+        want *= factor;
+    }
+    h->quota[nl - 1] = std::max(h->nfeatures - sum, 0);
+    /* half-widths of the rows of the 31-px orientation disc */
+    const int half = 15;
+    const int vmax = (int)std::floor((double)(half * std::sqrt(2.f) / 2 + 1));
+    const int vmin = (int)std::ceil((double)(half * std::sqrt(2.f) / 2));
+    const double hp2 = half * half;
+    for (int v = 0; v <= vmax; ++v) h->umax[v] = round_half_even_d(std::sqrt(hp2 - v * v));
+    for (int v = half, v0 = 0; v >= vmin; --v) {
+        while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+        h->umax[v] = v0;
+        ++v0;
+    }
+}
+
+/* taps of cv::resize INTER_LINEAR for one axis.  OpenCV clamps the horizontal
+ * taps in the table but clips the vertical ROW INDEX at run time; clamp_taps selects which. */
+void resize_axis(int sn, int dn, bool clamp_taps, int *ofs, short *coef)
+{
+    const double scale = 1.0 / ((double)dn / (double)sn);
+    for (int d = 0; d < dn; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = floor_f(f);
+        f -= (float)s;
+        if (clamp_taps) {
+            if (s < 0) { f = 0.f; s = 0; }
+            if (s >= sn - 1) { f = 0.f; s = sn - 1; }
+        }
+        ofs[d] = s;
+        coef[2 * d] = sat16(round_half_even((1.f - f) * 2048.f));
+        coef[2 * d + 1] = sat16(round_half_even(f * 2048.f));
+    }
+}
+
+void free_geometry(borb_extractor *h)
+{
+    for (GraphEntry &g : h->graphs) cudaGraphExecDestroy(g.exec);
+    h->graphs.clear();
+    void *dev[] = {h->d_plan, h->d_cells, h->d_tiles, h->d_tab_i, h->d_tab_s, h->d_in, h->d_pyr,
+                   h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
+                   h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc};
+    for (void *p : dev) if (p) cudaFree(p);
+    void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err};
+    for (void *p : host) if (p) cudaFreeHost(p);
+    h->d_plan = nullptr; h->d_cells = nullptr; h->d_tiles = nullptr; h->d_tab_i = nullptr;
+    h->d_tab_s = nullptr; h->d_in = h->d_pyr = h->d_blur = nullptr;
+    h->d_cand_xy = h->d_cand_score = h->d_cand_node = nullptr;
+    h->d_ncand = h->d_nlkp = h->d_nout = h->d_err = nullptr;
+    h->d_lkp_xy = h->d_lkp_score = nullptr; h->d_out_kp = nullptr; h->d_out_desc = nullptr;
+    h->h_in = h->h_pyr = h->h_out_desc = nullptr; h->h_out_kp = nullptr;
+    h->h_nout = h->h_err = nullptr;
+    h->have_plan = false;
+    h->results_on_host = h->pyramid_on_host = false;
+    h->last_n = 0;
+}
+
+/* everything that depends on (cols, rows) */
+int build_plan(borb_extractor *h, int cols, int rows)
+{
+    if (h->have_plan && h->plan.cols == cols && h->plan.rows == rows) return BORB_OK;
+    CU(cudaStreamSynchronize(h->stream));
+    free_geometry(h);
+
+    BorbPlan P;
+    std::memset(&P, 0, sizeof P);
+    P.nlevels = h->nlevels;
+    P.cols = cols; P.rows = rows;
+    P.ini_th = h->ini_th; P.min_th = h->min_th;
+    std::memcpy(P.umax, h->umax, sizeof P.umax);
+    std::vector<int> tab_i;
+    std::vector<short> tab_s;
+    std::vector<BorbCell> cells;
+    std::vector<BorbTile> tiles;
+    long long pyr_off = 0, cand_off = 0;
+    int kp_off = 0, M = 0;
+    for (int l = 0; l < h->nlevels; ++l) {
+        BorbLevel &L = P.lv[l];
+        /* level size from the ORIGINAL size, src/ORBextractor.cc:1404-1406 */
+        L.w = round_half_even((float)cols * h->inv_scale[l]);
+        L.h = round_half_even((float)rows * h->inv_scale[l]);
+        if (L.w > 32767 || L.h > 32767)
+            return fail(BORB_ERR_GEOMETRY, "level %d is %dx%d: coordinates are packed in 16 bits", l, L.w, L.h);
+        L.pitch = (int)align_up(BORB_XPAD + L.w + BORB_EDGE, 32);
+        L.prows = L.h + 2 * BORB_EDGE;
+        L.off = pyr_off;
+        pyr_off = align_up(pyr_off + (long long)L.pitch * L.prows, 256);
+        L.scale = h->scale[l];
+        L.patch_size = (float)(int)(31 * h->scale[l]);
+        L.quota = h->quota[l];
+        if (l > 0) {
+            const BorbLevel &S = P.lv[l - 1];
+            L.xofs_off = (int)tab_i.size(); tab_i.resize(tab_i.size() + L.w);
+            L.yofs_off = (int)tab_i.size(); tab_i.resize(tab_i.size() + L.h);
+            L.xa_off = (int)tab_s.size(); tab_s.resize(tab_s.size() + 2 * L.w);
+            L.yb_off = (int)tab_s.size(); tab_s.resize(tab_s.size() + 2 * L.h);
+            resize_axis(S.w, L.w, true, &tab_i[L.xofs_off], &tab_s[L.xa_off]);
+            resize_axis(S.h, L.h, false, &tab_i[L.yofs_off], &tab_s[L.yb_off]);
+        }
+        /* FAST cell grid, src/ORBextractor.cc:974-1064 (float arithmetic as written there) */
+        const int min_b = BORB_FAST_MARGIN;
+        L.max_bx = L.w - BORB_EDGE + 3;
+        L.max_by = L.h - BORB_EDGE + 3;
+        const float width = (float)(L.max_bx - min_b), height = (float)(L.max_by - min_b);
+        L.n_cols = (int)(width / 30.f);
+        L.n_rows = (int)(height / 30.f);
+        if (L.n_cols <= 0 || L.n_rows <= 0)
+            return fail(BORB_ERR_GEOMETRY, "level %d (%dx%d) is smaller than one 30-px FAST cell", l, L.w, L.h);
+        L.w_cell = (int)std::ceil(width / L.n_cols);
+        L.h_cell = (int)std::ceil(height / L.n_rows);
+        if (L.w_cell > BORB_MAXCELL || L.h_cell > BORB_MAXCELL || L.n_cols > 4095 || L.n_rows > 4095)
+            return fail(BORB_ERR_GEOMETRY, "cell grid out of range at level %d", l);
+        long long cap = 0;
+        for (int i = 0; i < L.n_rows; ++i) {
+            const float ini_y = (float)(min_b + i * L.h_cell);
+            float max_y = ini_y + L.h_cell + 6;
+            if (ini_y >= L.max_by - 3) continue;
+            if (max_y > L.max_by) max_y = (float)L.max_by;
+            for (int j = 0; j < L.n_cols; ++j) {
+                const float ini_x = (float)(min_b + j * L.w_cell);
+                float max_x = ini_x + L.w_cell + 6;
+                if (ini_x >= L.max_bx - 6) continue;
+                if (max_x > L.max_bx) max_x = (float)L.max_bx;
+                BorbCell c;
+                c.level = (short)l; c.pad = 0;
+                c.x0 = (short)(int)ini_x; c.y0 = (short)(int)ini_y;
+                c.ww = (short)((int)max_x - (int)ini_x);
+                c.wh = (short)((int)max_y - (int)ini_y);
+                c.sx = (short)(j * L.w_cell); c.sy = (short)(i * L.h_cell);
+                if (c.ww < 7 || c.wh < 7) continue; /* cv::FAST finds nothing in such a window */
+                cells.push_back(c);
+                cap += (long long)((c.ww - 6 + 1) / 2) * ((c.wh - 6 + 1) / 2);
+            }
+        }
+        L.cand_cap = (int)std::max<long long>(cap, 1);
+        L.cand_off = cand_off;
+        cand_off += align_up(L.cand_cap, 32);
+        /* quadtree roots, src/ORBextractor.cc:674-680 */
+        L.qt_w = L.max_bx - min_b;
+        L.qt_h = L.max_by - min_b;
+        L.n_ini = (int)std::round((float)L.qt_w / (float)L.qt_h);
+        if (L.n_ini <= 0)
+            return fail(BORB_ERR_GEOMETRY, "level %d: width/height rounds to 0 root nodes "
+                        "(the reference divides by zero here)", l);
+        L.hx = (float)L.qt_w / (float)L.n_ini;
+        L.kp_cap = std::max(L.quota, 4 * L.n_ini) + 4;
+        L.kp_off = kp_off;
+        kp_off += L.kp_cap;
+        M = std::max(M, L.kp_cap);
+        for (int y = 0; y < L.h; y += BORB_BLUR_TH)
+            for (int x = 0; x < L.w; x += BORB_BLUR_TW) {
+                BorbTile t;
+                t.level = (short)l; t.pad = 0; t.x0 = (short)x; t.y0 = (short)y;
+                tiles.push_back(t);
+            }
+    }
+    if (M > BORB_QT_MAXNODES)
+        return fail(BORB_ERR_CAPACITY, "%d features on one level exceed the shared-memory quadtree "
+                    "capacity (%d)", M, BORB_QT_MAXNODES);
+    P.pyr_bytes = pyr_off;
+    P.cand_total = cand_off;
+    P.kp_total = kp_off;
+    P.n_cells = (int)cells.size();
+    P.n_tiles = (int)tiles.size();
+
+    const size_t B = (size_t)h->max_batch;
+    CU(cudaMalloc(&h->d_plan, sizeof P));
+    CU(cudaMalloc(&h->d_cells, cells.size() * sizeof(BorbCell)));
+    CU(cudaMalloc(&h->d_tiles, tiles.size() * sizeof(BorbTile)));
+    CU(cudaMalloc(&h->d_tab_i, std::max<size_t>(tab_i.size(), 1) * sizeof(int)));
+    CU(cudaMalloc(&h->d_tab_s, std::max<size_t>(tab_s.size(), 1) * sizeof(short)));
+    CU(cudaMalloc(&h->d_in, B * (size_t)cols * rows));
+    CU(cudaMalloc(&h->d_pyr, B * (size_t)P.pyr_bytes));
+    CU(cudaMalloc(&h->d_blur, B * (size_t)P.pyr_bytes));
+    CU(cudaMalloc(&h->d_cand_xy, B * (size_t)P.cand_total * 4));
+    CU(cudaMalloc(&h->d_cand_score, B * (size_t)P.cand_total * 4));
+    CU(cudaMalloc(&h->d_cand_node, B * (size_t)P.cand_total * 4));
+    CU(cudaMalloc(&h->d_ncand, B * BORB_MAXL * 4));
+    CU(cudaMalloc(&h->d_nlkp, B * BORB_MAXL * 4));
+    CU(cudaMalloc(&h->d_nout, B * 4));
+    CU(cudaMalloc(&h->d_err, 4));
+    CU(cudaMalloc(&h->d_lkp_xy, B * (size_t)P.kp_total * 4));
+    CU(cudaMalloc(&h->d_lkp_score, B * (size_t)P.kp_total * 4));
+    CU(cudaMalloc(&h->d_out_kp, B * (size_t)P.kp_total * sizeof(BorbKpRec)));
+    CU(cudaMalloc(&h->d_out_desc, B * (size_t)P.kp_total * 32));
+    CU(cudaMallocHost(&h->h_in, B * (size_t)cols * rows));
+    CU(cudaMallocHost(&h->h_out_kp, B * (size_t)P.kp_total * sizeof(BorbKpRec)));
+    CU(cudaMallocHost(&h->h_out_desc, B * (size_t)P.kp_total * 32));
+    CU(cudaMallocHost(&h->h_nout, B * 4));
+    CU(cudaMallocHost(&h->h_err, 4));
+    CU(cudaMemcpy(h->d_plan, &P, sizeof P, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_cells, cells.data(), cells.size() * sizeof(BorbCell), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_tiles, tiles.data(), tiles.size() * sizeof(BorbTile), cudaMemcpyHostToDevice));
+    if (!tab_i.empty()) CU(cudaMemcpy(h->d_tab_i, tab_i.data(), tab_i.size() * sizeof(int), cudaMemcpyHostToDevice));
+    if (!tab_s.empty()) CU(cudaMemcpy(h->d_tab_s, tab_s.data(), tab_s.size() * sizeof(short), cudaMemcpyHostToDevice));
+    CU(cudaMemset(h->d_err, 0, 4));
+    /* the blurred slab's frame/padding is never written; keep it defined */
+    CU(cudaMemset(h->d_blur, 0, B * (size_t)P.pyr_bytes));
+    CU(cudaMemset(h->d_pyr, 0, B * (size_t)P.pyr_bytes));
+
+    h->qt_M = M;
+    const size_t qt_smem = qt_smem_bytes(M);
+    CU(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem));
+    h->plan = P;
+    h->cells.swap(cells);
+    h->tiles.swap(tiles);
+    h->have_plan = true;
+    return BORB_OK;
+}
+
+} // namespace
+
+namespace {
+
+/* Enqueue the whole per-call chain for n frames whose pixels are at dev_img on the device. */
+int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t step, size_t stride)
+{
+    const BorbPlan &P = h->plan;
+    cudaStream_t st = h->stream;
+    CU(cudaMemsetAsync(h->d_ncand, 0, (size_t)n * BORB_MAXL * 4, st));
+    {   /* K1 */
+        const BorbLevel &L0 = P.lv[0];
+        dim3 g((L0.pitch / 4 + 255) / 256, L0.prows, n);
+        k_pyr_level0<<<g, 256, 0, st>>>(h->d_plan, dev_img, step, stride, h->d_pyr);
+        for (int l = 1; l < P.nlevels; ++l) {
+            const BorbLevel &L = P.lv[l];
+            dim3 gl((L.pitch / 4 + 255) / 256, L.prows, n);
+            k_pyr_resize<<<gl, 256, 0, st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s, h->d_pyr);
+        }
+    }
+    k_fast_cells<<<dim3(P.n_cells, n), 128, 0, st>>>(h->d_plan, h->d_cells, h->d_pyr, h->d_cand_xy,
+                                                     h->d_cand_score, h->d_ncand);
+    k_quadtree<<<dim3(P.nlevels, n), QT_NT, qt_smem_bytes(h->qt_M), st>>>(
+        h->d_plan, h->qt_M, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_lkp_xy,
+        h->d_lkp_score, h->d_nlkp, h->d_err);
+    k_blur_tiles<<<dim3(P.n_tiles, n), 256, 0, st>>>(h->d_plan, h->d_tiles, h->d_pyr, h->d_blur);
+    k_orient_describe<<<dim3((P.kp_total + 7) / 8, n), 256, 0, st>>>(
+        h->d_plan, h->d_pattern, h->d_pyr, h->d_blur, h->d_lkp_xy, h->d_lkp_score, h->d_nlkp,
+        h->d_out_kp, h->d_out_desc, h->d_nout);
+    CU(cudaGetLastError());
+    return BORB_OK;
+}
+
+int enqueue_fetch(borb_extractor *h, int n, unsigned flags)
+{
+    const BorbPlan &P = h->plan;
+    cudaStream_t st = h->stream;
+    CU(cudaMemcpyAsync(h->h_nout, h->d_nout, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_out_kp, h->d_out_kp, (size_t)n * P.kp_total * sizeof(BorbKpRec),
+                       cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_out_desc, h->d_out_desc, (size_t)n * P.kp_total * 32,
+                       cudaMemcpyDeviceToHost, st));
+    if (flags & BORB_WANT_PYRAMID)
+        CU(cudaMemcpyAsync(h->h_pyr, h->d_pyr, (size_t)n * (size_t)P.pyr_bytes,
+                           cudaMemcpyDeviceToHost, st));
+    return BORB_OK;
+}
+
+/* body(h) enqueues work on h->stream; run it through a cached CUDA graph when enabled */
+template <typename F>
+int run_cached(borb_extractor *h, const GraphKey &key, F body)
+{
+    if (!h->use_graph) return body();
+    for (GraphEntry &g : h->graphs)
+        if (g.key == key) {
+            CU(cudaGraphLaunch(g.exec, h->stream));
+            return BORB_OK;
+        }
+    cudaGraph_t graph = nullptr;
+    CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = body();
+    cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+    if (rc != BORB_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (e != cudaSuccess) return fail(BORB_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+    GraphEntry ge;
+    ge.key = key;
+    e = cudaGraphInstantiate(&ge.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return fail(BORB_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
+    if (h->graphs.size() >= 16) {
+        cudaGraphExecDestroy(h->graphs.front().exec);
+        h->graphs.erase(h->graphs.begin());
+    }
+    h->graphs.push_back(ge);
+    CU(cudaGraphLaunch(ge.exec, h->stream));
+    return BORB_OK;
+}
+
+int check_device_err(borb_extractor *h)
+{
+    if (*h->h_err != 0) {
+        const int e = *h->h_err;
+        *h->h_err = 0;
+        cudaMemsetAsync(h->d_err, 0, 4, h->stream);
+        return fail(BORB_ERR_CAPACITY, "device buffer overflow (code %d)", e);
+    }
+    return BORB_OK;
+}
+
+int ensure_pyr_host(borb_extractor *h)
+{
+    if (!h->h_pyr)
+        CU(cudaMallocHost(&h->h_pyr, (size_t)h->max_batch * (size_t)h->plan.pyr_bytes));
+    return BORB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *borb_last_error(void) { return g_err.c_str(); }
+const char *borb_version(void) { return "orb_b200 0.1 (sm_100a)"; }
+
+int borb_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int device,
+                int max_batch, borb_extractor **out)
+{
+    if (!out) return fail(BORB_ERR_ARG, "out is null");
+    *out = nullptr;
+    if (nfeatures < 1 || nlevels < 1 || nlevels > BORB_MAXL || !(scale_factor > 1.0f) ||
+        ini_th < 1 || min_th < 1 || ini_th > 254 || min_th > 254 || max_batch < 1)
+        return fail(BORB_ERR_ARG, "unsupported parameters (nlevels 1..%d, scaleFactor > 1, "
+                    "FAST thresholds 1..254, max_batch >= 1)", BORB_MAXL);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(BORB_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    if (device < 0) CU(cudaGetDevice(&device));
+    if (device >= ndev) return fail(BORB_ERR_ARG, "device %d of %d", device, ndev);
+    CU(cudaSetDevice(device));
+    borb_extractor *h = new borb_extractor();
+    h->nfeatures = nfeatures; h->nlevels = nlevels; h->ini_th = ini_th; h->min_th = min_th;
+    h->scale_factor = scale_factor;
+    h->device = device; h->max_batch = max_batch;
+    build_tables(h);
+    const char *ng = getenv("BORB_NO_GRAPH");
+    h->use_graph = !(ng && ng[0] == '1');
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_pattern, sizeof kPattern);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_pattern, kPattern, sizeof kPattern, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        borb_destroy(h);
+        return fail(BORB_ERR_CUDA, "create: %s", cudaGetErrorString(e));
+    }
+    *out = h;
+    return BORB_OK;
+}
+
+void borb_destroy(borb_extractor *h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_geometry(h);
+    if (h->d_pattern) cudaFree(h->d_pattern);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int borb_levels(const borb_extractor *h) { return h ? h->nlevels : 0; }
+float borb_scale_factor(const borb_extractor *h) { return h ? (float)h->scale_factor : 0.f; }
+
+int borb_table(const borb_extractor *h, int which, float *out)
+{
+    if (!h || !out || which < 0 || which > 3) return fail(BORB_ERR_ARG, "borb_table arguments");
+    const std::vector<float> &v = which == 0 ? h->scale : which == 1 ? h->inv_scale
+                                : which == 2 ? h->sigma2 : h->inv_sigma2;
+    std::memcpy(out, v.data(), v.size() * sizeof(float));
+    return BORB_OK;
+}
+int borb_features_per_level(const borb_extractor *h, int32_t *out)
+{
+    if (!h || !out) return fail(BORB_ERR_ARG, "null");
+    std::memcpy(out, h->quota.data(), h->quota.size() * sizeof(int));
+    return BORB_OK;
+}
+int borb_umax(const borb_extractor *h, int32_t *out)
+{
+    if (!h || !out) return fail(BORB_ERR_ARG, "null");
+    std::memcpy(out, h->umax, sizeof h->umax);
+    return BORB_OK;
+}
+
+static int check_call(borb_extractor *h, const void *img, int n, int cols, int rows, size_t step,
+                      size_t stride)
+{
+    if (!h || !img) return fail(BORB_ERR_ARG, "null handle or image");
+    if (n < 1 || cols < 1 || rows < 1 || step < (size_t)cols || (n > 1 && stride < step * (size_t)(rows - 1) + cols))
+        return fail(BORB_ERR_ARG, "bad image geometry");
+    if (n > h->max_batch) return fail(BORB_ERR_CAPACITY, "%d frames > max_batch %d", n, h->max_batch);
+    CU(cudaSetDevice(h->device));
+    return build_plan(h, cols, rows);
+}
+
+int borb_extract_host(borb_extractor *h, const uint8_t *img, int n, int cols, int rows, size_t step,
+                      size_t stride, unsigned flags)
+{
+    int rc = check_call(h, img, n, cols, rows, step, stride);
+    if (rc != BORB_OK) return rc;
+    if ((flags & BORB_WANT_PYRAMID) && (rc = ensure_pyr_host(h)) != BORB_OK) return rc;
+    /* pageable caller memory -> pinned staging (strided rows packed), then one async H2D */
+    const size_t fsz = (size_t)cols * rows;
+    for (int f = 0; f < n; ++f) {
+        const uint8_t *s = img + (size_t)f * stride;
+        uint8_t *d = h->h_in + (size_t)f * fsz;
+        if (step == (size_t)cols) std::memcpy(d, s, fsz);
+        else for (int y = 0; y < rows; ++y) std::memcpy(d + (size_t)y * cols, s + (size_t)y * step, (size_t)cols);
+    }
+    GraphKey key = {0, nullptr, n, 0, 0, flags};
+    rc = run_cached(h, key, [&]() -> int {
+        CU(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)n * fsz, cudaMemcpyHostToDevice, h->stream));
+        int r = enqueue_kernels(h, h->d_in, n, (size_t)cols, fsz);
+        if (r != BORB_OK) return r;
+        return enqueue_fetch(h, n, flags);
+    });
+    if (rc != BORB_OK) return rc;
+    CU(cudaStreamSynchronize(h->stream));
+    h->last_n = n;
+    h->results_on_host = true;
+    h->pyramid_on_host = (flags & BORB_WANT_PYRAMID) != 0;
+    return check_device_err(h);
+}
+
+int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int cols, int rows,
+                        size_t step, size_t stride)
+{
+    int rc = check_call(h, dev_img, n, cols, rows, step, stride);
+    if (rc != BORB_OK) return rc;
+    GraphKey key = {1, dev_img, n, step, stride, 0};
+    CU(cudaEventRecord(h->ev0, h->stream));
+    rc = run_cached(h, key, [&]() -> int { return enqueue_kernels(h, dev_img, n, step, stride); });
+    if (rc != BORB_OK) return rc;
+    CU(cudaEventRecord(h->ev1, h->stream));
+    h->last_n = n;
+    h->results_on_host = false;
+    h->pyramid_on_host = false;
+    return BORB_OK;
+}
+
+int borb_fetch(borb_extractor *h, unsigned flags)
+{
+    if (!h || !h->have_plan || h->last_n < 1) return fail(BORB_ERR_STATE, "nothing to fetch");
+    CU(cudaSetDevice(h->device));
+    int rc;
+    if ((flags & BORB_WANT_PYRAMID) && (rc = ensure_pyr_host(h)) != BORB_OK) return rc;
+    rc = enqueue_fetch(h, h->last_n, flags);
+    if (rc != BORB_OK) return rc;
+    CU(cudaStreamSynchronize(h->stream));
+    h->results_on_host = true;
+    h->pyramid_on_host = (flags & BORB_WANT_PYRAMID) != 0;
+    return check_device_err(h);
+}
+
+int borb_sync(borb_extractor *h)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    return BORB_OK;
+}
+
+float borb_last_device_ms(const borb_extractor *h)
+{
+    float ms = -1.f;
+    if (!h || cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) {
+        cudaGetLastError();
+        return -1.f;
+    }
+    return ms;
+}
+
+int borb_launches_per_call(const borb_extractor *h) { return h ? h->nlevels + 4 : 0; }
+
+int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps, const uint8_t **desc, int *n)
+{
+    if (!h || !h->results_on_host) return fail(BORB_ERR_STATE, "no results on the host");
+    if (frame < 0 || frame >= h->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, h->last_n);
+    const size_t o = (size_t)frame * h->plan.kp_total;
+    if (kps) *kps = reinterpret_cast<const borb_keypoint *>(h->h_out_kp + o);
+    if (desc) *desc = h->h_out_desc + o * 32;
+    if (n) *n = h->h_nout[frame];
+    return BORB_OK;
+}
+
+int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows)
+{
+    if (!h || !h->have_plan) return fail(BORB_ERR_STATE, "no geometry yet");
+    if (level < 0 || level >= h->nlevels) return fail(BORB_ERR_ARG, "level");
+    if (cols) *cols = h->plan.lv[level].w;
+    if (rows) *rows = h->plan.lv[level].h;
+    return BORB_OK;
+}
+
+int borb_pyramid(const borb_extractor *h, int frame, int level, const uint8_t **data, int *cols,
+                 int *rows, size_t *step)
+{
+    if (!h || !h->pyramid_on_host) return fail(BORB_ERR_STATE, "pyramid was not requested");
+    if (frame < 0 || frame >= h->last_n || level < 0 || level >= h->nlevels) return fail(BORB_ERR_ARG, "frame/level");
+    const BorbLevel &L = h->plan.lv[level];
+    if (data) *data = h->h_pyr + (size_t)frame * (size_t)h->plan.pyr_bytes + L.off + (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
+    if (cols) *cols = L.w;
+    if (rows) *rows = L.h;
+    if (step) *step = (size_t)L.pitch;
+    return BORB_OK;
+}
+
+int borb_debug_candidates(borb_extractor *h, int frame, int level, int32_t *xs, int32_t *ys,
+                          int32_t *scores, int cap, int *n)
+{
+    if (!h || !h->have_plan || frame < 0 || frame >= h->last_n || level < 0 || level >= h->nlevels)
+        return fail(BORB_ERR_ARG, "debug_candidates arguments");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    int cnt = 0;
+    CU(cudaMemcpy(&cnt, h->d_ncand + frame * BORB_MAXL + level, 4, cudaMemcpyDeviceToHost));
+    const BorbLevel &L = h->plan.lv[level];
+    const int m = std::min(std::min(cnt, cap), L.cand_cap);
+    std::vector<uint32_t> xy((size_t)std::max(m, 1)), sc((size_t)std::max(m, 1));
+    const size_t o = (size_t)frame * (size_t)h->plan.cand_total + L.cand_off;
+    if (m > 0) {
+        CU(cudaMemcpy(xy.data(), h->d_cand_xy + o, (size_t)m * 4, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(sc.data(), h->d_cand_score + o, (size_t)m * 4, cudaMemcpyDeviceToHost));
+    }
+    for (int i = 0; i < m; ++i) {
+        xs[i] = (int)(xy[i] & 0xffff);
+        ys[i] = (int)(xy[i] >> 16);
+        scores[i] = (int)sc[i];
+    }
+    if (n) *n = cnt;
+    return BORB_OK;
+}
+
+int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out)
+{
+    if (!h || !h->have_plan || frame < 0 || frame >= h->last_n || level < 0 || level >= h->nlevels)
+        return fail(BORB_ERR_ARG, "debug_blurred arguments");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    const BorbLevel &L = h->plan.lv[level];
+    const uint8_t *src = h->d_blur + (size_t)frame * (size_t)h->plan.pyr_bytes + L.off + (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
+    CU(cudaMemcpy2D(out, (size_t)L.w, src, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
+    return BORB_OK;
+}
+
+void borb_debug_sincos(float radians, float *s, float *c) { orb_sincosf_exact(radians, s, c); }
+
+} // extern "C"

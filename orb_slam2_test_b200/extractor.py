@@ -1,0 +1,252 @@
+"""Python host mirror of the reference's ORBextractor interface over the C ABI (include/borb.h).
+
+The reference class (include/ORBextractor.h:46-144 of the reference tree) is C++; the C++ drop-in
+lives in orb_slam2_test_b200/shim/.  This module is the same surface for Python callers, tests and
+bench.py: same constructor arguments, same getter names, `__call__(image, mask)` in place of
+`operator()`, `mvImagePyramid` as a list of level views.  Everything runs in liborb_b200.so on the
+GPU -- there is no CPU path, and importing this on a machine without the built library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "liborb_b200.so"
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+BORB_WANT_PYRAMID = 1
+
+_vp = C.c_void_p
+_lib = None
+
+# every symbol include/borb.h declares (tests check the list against the header)
+SYMBOLS = [
+    "borb_create", "borb_destroy", "borb_last_error", "borb_version", "borb_levels",
+    "borb_scale_factor", "borb_table", "borb_features_per_level", "borb_umax",
+    "borb_extract_host", "borb_extract_device", "borb_fetch", "borb_sync", "borb_result",
+    "borb_pyramid", "borb_level_size", "borb_launches_per_call", "borb_last_device_ms",
+    "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos",
+]
+
+
+class BorbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"borb status {code}: {msg}")
+        self.code = code
+
+
+def load_library() -> C.CDLL:
+    """dlopen liborb_b200.so (in-tree build).  Raises if it has not been built: no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise FileNotFoundError(
+            f"{LIB_PATH} is missing: build it with `make -C {_HERE / 'csrc'}` "
+            "(or __graft_entry__.build()); this package has no CPU fallback")
+    lib = C.CDLL(str(LIB_PATH))
+    lib.borb_last_error.restype = C.c_char_p
+    lib.borb_version.restype = C.c_char_p
+    lib.borb_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                C.POINTER(_vp)]
+    lib.borb_destroy.argtypes = [_vp]
+    lib.borb_levels.argtypes = [_vp]
+    lib.borb_scale_factor.argtypes = [_vp]
+    lib.borb_scale_factor.restype = C.c_float
+    lib.borb_table.argtypes = [_vp, C.c_int, _vp]
+    lib.borb_features_per_level.argtypes = [_vp, _vp]
+    lib.borb_umax.argtypes = [_vp, _vp]
+    lib.borb_extract_host.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
+                                      C.c_uint]
+    lib.borb_extract_device.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t]
+    lib.borb_fetch.argtypes = [_vp, C.c_uint]
+    lib.borb_sync.argtypes = [_vp]
+    lib.borb_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int)]
+    lib.borb_pyramid.argtypes = [_vp, C.c_int, C.c_int, C.POINTER(_vp), C.POINTER(C.c_int),
+                                 C.POINTER(C.c_int), C.POINTER(C.c_size_t)]
+    lib.borb_level_size.argtypes = [_vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_launches_per_call.argtypes = [_vp]
+    lib.borb_last_device_ms.argtypes = [_vp]
+    lib.borb_last_device_ms.restype = C.c_float
+    lib.borb_debug_candidates.argtypes = [_vp, C.c_int, C.c_int, _vp, _vp, _vp, C.c_int,
+                                          C.POINTER(C.c_int)]
+    lib.borb_debug_blurred.argtypes = [_vp, C.c_int, C.c_int, _vp]
+    lib.borb_debug_sincos.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    _lib = lib
+    return lib
+
+
+def _check(lib, rc: int) -> None:
+    if rc != 0:
+        raise BorbError(rc, lib.borb_last_error().decode())
+
+
+def debug_sincos(radians: float):
+    lib = load_library()
+    s, c = C.c_float(), C.c_float()
+    lib.borb_debug_sincos(radians, C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+class ORBextractor:
+    """Same constructor arguments and accessor names as ORB_SLAM2::ORBextractor.
+
+    `extractor(image)` returns (keypoints, descriptors): a structured array with cv::KeyPoint's
+    fields and an [n, 32] uint8 array, in the reference's output order.  `max_batch` > 1 enables
+    `extract_batch` (frames of one call go through the kernels together).
+    """
+
+    HARRIS_SCORE, FAST_SCORE = 0, 1
+
+    def __init__(self, nfeatures: int, scaleFactor: float, nlevels: int, iniThFAST: int,
+                 minThFAST: int, device: int = -1, max_batch: int = 1, want_pyramid: bool = True):
+        self._lib = load_library()
+        self._h = _vp()
+        _check(self._lib, self._lib.borb_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST,
+                                                device, max_batch, C.byref(self._h)))
+        self.nlevels = nlevels
+        self.max_batch = max_batch
+        self.want_pyramid = want_pyramid
+        self.mvImagePyramid: list[np.ndarray] = []
+        self._n = 0
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.borb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- getters (include/ORBextractor.h:78-98) --
+    def GetLevels(self) -> int:
+        return self._lib.borb_levels(self._h)
+
+    def GetScaleFactor(self) -> float:
+        return self._lib.borb_scale_factor(self._h)
+
+    def _table(self, which: int) -> np.ndarray:
+        out = np.zeros(self.nlevels, np.float32)
+        _check(self._lib, self._lib.borb_table(self._h, which, out.ctypes.data))
+        return out
+
+    def GetScaleFactors(self):
+        return self._table(0)
+
+    def GetInverseScaleFactors(self):
+        return self._table(1)
+
+    def GetScaleSigmaSquares(self):
+        return self._table(2)
+
+    def GetInverseScaleSigmaSquares(self):
+        return self._table(3)
+
+    def features_per_level(self) -> np.ndarray:
+        out = np.zeros(self.nlevels, np.int32)
+        _check(self._lib, self._lib.borb_features_per_level(self._h, out.ctypes.data))
+        return out
+
+    def umax(self) -> np.ndarray:
+        out = np.zeros(16, np.int32)
+        _check(self._lib, self._lib.borb_umax(self._h, out.ctypes.data))
+        return out
+
+    # -- operator() (src/ORBextractor.cc:1330-1397) --
+    def __call__(self, image: np.ndarray, mask=None):
+        """mask is ignored, as in the reference (include/ORBextractor.h:72)."""
+        if image is None or image.size == 0:
+            return None  # the reference returns without touching its outputs (:1333-1334)
+        if image.dtype != np.uint8 or image.ndim != 2:
+            raise TypeError("image must be CV_8UC1 (2-D uint8)")  # reference: assert, :1337
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        rows, cols = image.shape
+        flags = BORB_WANT_PYRAMID if self.want_pyramid else 0
+        _check(self._lib, self._lib.borb_extract_host(self._h, image.ctypes.data, 1, cols, rows,
+                                                      image.strides[0], 0, flags))
+        self._n = 1
+        if self.want_pyramid:
+            self.mvImagePyramid = [self.pyramid_level(0, l) for l in range(self.nlevels)]
+        return self.result(0)
+
+    def extract_batch(self, images: np.ndarray, want_pyramid: bool = False):
+        """images: [n, rows, cols] uint8, C-contiguous.  Returns a list of (kps, desc)."""
+        assert images.dtype == np.uint8 and images.ndim == 3 and images.flags.c_contiguous
+        n, rows, cols = images.shape
+        _check(self._lib, self._lib.borb_extract_host(self._h, images.ctypes.data, n, cols, rows, cols,
+                                                      rows * cols, BORB_WANT_PYRAMID if want_pyramid else 0))
+        self._n = n
+        return [self.result(f) for f in range(n)]
+
+    def extract_device(self, dev_ptr: int, n: int, cols: int, rows: int, step: int | None = None,
+                       frame_stride: int | None = None) -> None:
+        """Frames already in device memory (e.g. tensor.data_ptr()); asynchronous."""
+        step = cols if step is None else step
+        frame_stride = rows * step if frame_stride is None else frame_stride
+        _check(self._lib, self._lib.borb_extract_device(self._h, dev_ptr, n, cols, rows, step, frame_stride))
+        self._n = n
+
+    def fetch(self, want_pyramid: bool = False):
+        _check(self._lib, self._lib.borb_fetch(self._h, BORB_WANT_PYRAMID if want_pyramid else 0))
+        return [self.result(f) for f in range(self._n)]
+
+    def sync(self) -> None:
+        _check(self._lib, self._lib.borb_sync(self._h))
+
+    def last_device_ms(self) -> float:
+        return self._lib.borb_last_device_ms(self._h)
+
+    def launches_per_call(self) -> int:
+        return self._lib.borb_launches_per_call(self._h)
+
+    def result(self, frame: int = 0, copy: bool = True):
+        kp, de, n = _vp(), _vp(), C.c_int()
+        _check(self._lib, self._lib.borb_result(self._h, frame, C.byref(kp), C.byref(de), C.byref(n)))
+        cnt = n.value
+        if cnt == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        kps = np.ctypeslib.as_array(C.cast(kp, C.POINTER(C.c_uint8)), shape=(cnt * 28,)).view(KP_DTYPE)
+        desc = np.ctypeslib.as_array(C.cast(de, C.POINTER(C.c_uint8)), shape=(cnt, 32))
+        return (kps.copy(), desc.copy()) if copy else (kps, desc)
+
+    def level_size(self, level: int):
+        c, r = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_level_size(self._h, level, C.byref(c), C.byref(r)))
+        return c.value, r.value
+
+    def pyramid_level(self, frame: int, level: int, border: int = 0) -> np.ndarray:
+        """Level image as a view with `border` (<= 19) pixels of its reflect-101 frame."""
+        data, c, r, st = _vp(), C.c_int(), C.c_int(), C.c_size_t()
+        _check(self._lib, self._lib.borb_pyramid(self._h, frame, level, C.byref(data), C.byref(c),
+                                                 C.byref(r), C.byref(st)))
+        step = st.value
+        base = data.value - border * step - border
+        H, W = r.value + 2 * border, c.value + 2 * border
+        buf = (C.c_uint8 * (H * step)).from_address(base)
+        return np.lib.stride_tricks.as_strided(np.frombuffer(buf, np.uint8), shape=(H, W), strides=(step, 1)).copy()
+
+    # -- stage taps for the parity tests --
+    def debug_candidates(self, frame: int, level: int):
+        cap = 1 << 20
+        xs = np.zeros(cap, np.int32); ys = np.zeros(cap, np.int32); sc = np.zeros(cap, np.int32)
+        n = C.c_int()
+        _check(self._lib, self._lib.borb_debug_candidates(self._h, frame, level, xs.ctypes.data, ys.ctypes.data,
+                                                          sc.ctypes.data, cap, C.byref(n)))
+        m = min(n.value, cap)
+        return xs[:m].copy(), ys[:m].copy(), sc[:m].copy()
+
+    def debug_blurred(self, frame: int, level: int) -> np.ndarray:
+        c, r = self.level_size(level)
+        out = np.zeros((r, c), np.uint8)
+        _check(self._lib, self._lib.borb_debug_blurred(self._h, frame, level, out.ctypes.data))
+        return out
