@@ -111,6 +111,9 @@ int borb_debug_candidates(borb_extractor *h, int frame, int level, int32_t *xs, 
 int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out /* cols*rows */);
 /* host evaluation of the device sin/cos routine (same inline function, host build) */
 void borb_debug_sincos(float radians, float *s, float *c);
+/* host evaluation of the per-pixel FAST score used by the cell kernel: 0 = not a FAST-9 corner at
+ * threshold t_lo, else the largest threshold at which p still is one */
+int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo);
 
 #ifdef __cplusplus
 }

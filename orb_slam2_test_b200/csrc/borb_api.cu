@@ -706,5 +706,6 @@ int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out)
 }
 
 void borb_debug_sincos(float radians, float *s, float *c) { orb_sincosf_exact(radians, s, c); }
+int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_score_px(p, pitch, t_lo); }
 
 } // extern "C"

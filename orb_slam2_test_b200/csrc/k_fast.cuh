@@ -23,8 +23,9 @@
 #define FAST_WPITCH 68 /* >= BORB_MAXCELL + 6, multiple of 4 */
 #define FAST_SPITCH 64 /* >= BORB_MAXCELL + 2 */
 
+
 /* 9 contiguous set bits in a 16-bit circular mask */
-__device__ __forceinline__ bool has_arc9(uint32_t m)
+__host__ __device__ __forceinline__ bool has_arc9(uint32_t m)
 {
     uint32_t x = m | (m << 16);
     x &= x >> 1;  /* runs of 2 */
@@ -34,25 +35,53 @@ __device__ __forceinline__ bool has_arc9(uint32_t m)
     return (x & 0xffffu) != 0;
 }
 
-/* max over the 16 arcs of 9 contiguous ring samples of min(d) -- "bright" when fed d,
- * "dark" when fed -d.  Mirrors OpenCV's cornerScore<16> pairing of arcs (k, k+1). */
-__device__ __forceinline__ int arc_maxmin(const int (&d)[16], int floor_v)
+/* FAST score of the pixel at p (row pitch `pitch`): 0 if it is not a FAST-9 corner at threshold
+ * t_lo, else the largest threshold at which it still is one (>= t_lo). */
+__host__ __device__ __forceinline__ int fast_score_px(const uint8_t *p, int pitch, int t_lo)
 {
-    int a0 = floor_v;
-#pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        int a = min(d[(k + 1) & 15], d[(k + 2) & 15]);
-        a = min(a, d[(k + 3) & 15]);
-        if (a <= a0) continue;
-        a = min(a, d[(k + 4) & 15]);
-        a = min(a, d[(k + 5) & 15]);
-        a = min(a, d[(k + 6) & 15]);
-        a = min(a, d[(k + 7) & 15]);
-        a = min(a, d[(k + 8) & 15]);
-        a0 = max(a0, min(a, d[k]));
-        a0 = max(a0, min(a, d[(k + 9) & 15]));
+    const int v = p[0];
+    int d[16];
+    d[0] = v - p[3 * pitch];       d[8] = v - p[-3 * pitch];
+    d[4] = v - p[3];               d[12] = v - p[-3];
+    /* a 9-arc contains at least two of the four compass points, on the same side */
+    {
+        const int nb = (d[0] > t_lo) + (d[4] > t_lo) + (d[8] > t_lo) + (d[12] > t_lo);
+        const int nd = (d[0] < -t_lo) + (d[4] < -t_lo) + (d[8] < -t_lo) + (d[12] < -t_lo);
+        if (nb < 2 && nd < 2) return 0;
     }
-    return a0;
+    d[1] = v - p[3 * pitch + 1];   d[2] = v - p[2 * pitch + 2];
+    d[3] = v - p[pitch + 3];       d[5] = v - p[-pitch + 3];
+    d[6] = v - p[-2 * pitch + 2];  d[7] = v - p[-3 * pitch + 1];
+    d[9] = v - p[-3 * pitch - 1];  d[10] = v - p[-2 * pitch - 2];
+    d[11] = v - p[-pitch - 3];     d[13] = v - p[pitch - 3];
+    d[14] = v - p[2 * pitch - 2];  d[15] = v - p[3 * pitch - 1];
+    uint32_t mb = 0, md = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        mb |= (uint32_t)(d[k] > t_lo) << k;
+        md |= (uint32_t)(d[k] < -t_lo) << k;
+    }
+    const bool bright = has_arc9(mb);
+    if (!bright && !has_arc9(md)) return 0;
+    /* OpenCV's cornerScore<16> equals max over the 16 arcs of min|d| minus 1, i.e. the largest
+     * threshold at which the pixel still passes the segment test.  A bright 9-arc and a dark
+     * 9-arc cannot coexist (18 > 16 samples), so only the side found above is searched.
+     * Bisection over the threshold with the same bit-mask test; NOTE: a min/max-chain
+     * formulation of this score is miscompiled by ptxas 12.9 -O1..-O3 for sm_100a (VIMNMX3
+     * fusion; tools/dbg_fast.cu reproduces it), do not reintroduce it without that check. */
+    int e[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) e[k] = bright ? d[k] : -d[k];
+    int lo = t_lo, hi = 254;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        uint32_t m = 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) m |= (uint32_t)(e[k] > mid) << k;
+        if (has_arc9(m)) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
 }
 
 __global__ void __launch_bounds__(128)
@@ -82,35 +111,8 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     const int t_lo = min(plan->ini_th, plan->min_th);
     for (int i = tid; i < dw * dh; i += blockDim.x) {
         const int y = i / dw, x = i - y * dw;
-        const uint8_t *p = win + (y + 3) * FAST_WPITCH + x + 3;
-        const int v = p[0];
-        int d[16];
-        d[0] = v - p[3 * FAST_WPITCH];       d[8] = v - p[-3 * FAST_WPITCH];
-        d[4] = v - p[3];                     d[12] = v - p[-3];
-        /* a 9-arc contains at least two of the four compass points on the same side */
-        {
-            const int nb = (d[0] > t_lo) + (d[4] > t_lo) + (d[8] > t_lo) + (d[12] > t_lo);
-            const int nd = (d[0] < -t_lo) + (d[4] < -t_lo) + (d[8] < -t_lo) + (d[12] < -t_lo);
-            if (nb < 2 && nd < 2) continue;
-        }
-        d[1] = v - p[3 * FAST_WPITCH + 1];   d[2] = v - p[2 * FAST_WPITCH + 2];
-        d[3] = v - p[FAST_WPITCH + 3];       d[5] = v - p[-FAST_WPITCH + 3];
-        d[6] = v - p[-2 * FAST_WPITCH + 2];  d[7] = v - p[-3 * FAST_WPITCH + 1];
-        d[9] = v - p[-3 * FAST_WPITCH - 1];  d[10] = v - p[-2 * FAST_WPITCH - 2];
-        d[11] = v - p[-FAST_WPITCH - 3];     d[13] = v - p[FAST_WPITCH - 3];
-        d[14] = v - p[2 * FAST_WPITCH - 2];  d[15] = v - p[3 * FAST_WPITCH - 1];
-        uint32_t mb = 0, md = 0;
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            mb |= (uint32_t)(d[k] > t_lo) << k;
-            md |= (uint32_t)(d[k] < -t_lo) << k;
-        }
-        if (!has_arc9(mb) && !has_arc9(md)) continue;
-        const int a = arc_maxmin(d, t_lo);
-        int nd_[16];
-#pragma unroll
-        for (int k = 0; k < 16; ++k) nd_[k] = -d[k];
-        const int s = arc_maxmin(nd_, a) - 1; /* = max(t_lo, A, B) - 1 */
+        const int s = fast_score_px(win + (y + 3) * FAST_WPITCH + x + 3, FAST_WPITCH, t_lo);
+        if (s == 0) continue;
         sc[(y + 1) * FAST_SPITCH + x + 1] = (uint8_t)s;
     }
     __syncthreads();

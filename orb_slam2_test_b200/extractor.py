@@ -31,7 +31,7 @@ SYMBOLS = [
     "borb_scale_factor", "borb_table", "borb_features_per_level", "borb_umax",
     "borb_extract_host", "borb_extract_device", "borb_fetch", "borb_sync", "borb_result",
     "borb_pyramid", "borb_level_size", "borb_launches_per_call", "borb_last_device_ms",
-    "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos",
+    "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score",
 ]
 
 
@@ -78,6 +78,7 @@ def load_library() -> C.CDLL:
                                           C.POINTER(C.c_int)]
     lib.borb_debug_blurred.argtypes = [_vp, C.c_int, C.c_int, _vp]
     lib.borb_debug_sincos.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.borb_debug_fast_score.argtypes = [_vp, C.c_int, C.c_int]
     _lib = lib
     return lib
 
