@@ -78,6 +78,18 @@ int borb_umax(const borb_extractor *h, int32_t *out);               /* 16 entrie
 int borb_extract_host(borb_extractor *h, const uint8_t *img, int n_frames, int cols, int rows,
                       size_t step, size_t frame_stride, unsigned flags);
 
+/* The two halves of borb_extract_host: submit enqueues copy-in, kernels and copy-out on the
+ * handle's stream and returns; wait blocks until the results are readable.  Several handles kept
+ * in flight this way overlap their transfers and kernels. */
+int borb_submit_host(borb_extractor *h, const uint8_t *img, int n_frames, int cols, int rows,
+                     size_t step, size_t frame_stride, unsigned flags);
+int borb_wait(borb_extractor *h);
+
+/* Page-locked host memory for image batches: borb_submit_host copies from such memory straight
+ * to the device (densely packed frames only) instead of staging through its own pinned buffer. */
+void *borb_host_alloc(size_t bytes);
+void borb_host_free(void *p);
+
 /* Same, but the images already are in DEVICE memory and the results stay on the device until
  * borb_fetch() is called (kernel-only timing, pipelines that keep descriptors on the GPU). */
 int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n_frames, int cols,
@@ -102,6 +114,16 @@ int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows);
 int borb_launches_per_call(const borb_extractor *h);
 /* CUDA-event time of the last borb_extract_device call's kernels, milliseconds (<0: n/a) */
 float borb_last_device_ms(const borb_extractor *h);
+
+/* CUDA-event stopwatch on the handle's stream (bench.py: the library does not run on torch's
+ * stream, so torch.cuda.Event cannot time it) */
+int borb_timer_start(borb_extractor *h);
+int borb_timer_stop(borb_extractor *h);
+float borb_timer_ms(borb_extractor *h);
+/* one un-graphed pass over n frames in device memory with an event between stages:
+ * ms[0..4] = pyramid, FAST, quadtree, blur, orientation+descriptor */
+int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n_frames, int cols, int rows,
+                     size_t step, size_t frame_stride, float *ms);
 
 /* -- stage taps for parity tests (device -> caller buffers; not part of the hot path) -------- */
 /* FAST candidates of (frame, level) before distribution, coords relative to (16,16);

@@ -96,7 +96,11 @@ struct borb_extractor {
 
     int device, max_batch;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;       /* around the last device call */
+    cudaEvent_t evt0 = nullptr, evt1 = nullptr;     /* user timer */
+    cudaEvent_t evs[8] = {};                        /* stage boundaries */
+    bool pending = false;                           /* submitted, not yet waited for */
+    unsigned pending_flags = 0;
     bool use_graph = true;
 
     /* geometry-dependent state */
@@ -368,11 +372,14 @@ int build_plan(borb_extractor *h, int cols, int rows)
 namespace {
 
 /* Enqueue the whole per-call chain for n frames whose pixels are at dev_img on the device. */
-int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t step, size_t stride)
+int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t step, size_t stride,
+                    bool stage_events = false)
 {
+#define STAGE(i) do { if (stage_events) CU(cudaEventRecord(h->evs[i], st)); } while (0)
     const BorbPlan &P = h->plan;
     cudaStream_t st = h->stream;
     CU(cudaMemsetAsync(h->d_ncand, 0, (size_t)n * BORB_MAXL * 4, st));
+    STAGE(0);
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         dim3 g((L0.pitch / 4 + 255) / 256, L0.prows, n);
@@ -383,15 +390,21 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             k_pyr_resize<<<gl, 256, 0, st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s, h->d_pyr);
         }
     }
+    STAGE(1);
     k_fast_cells<<<dim3(P.n_cells, n), 128, 0, st>>>(h->d_plan, h->d_cells, h->d_pyr, h->d_cand_xy,
                                                      h->d_cand_score, h->d_ncand);
+    STAGE(2);
     k_quadtree<<<dim3(P.nlevels, n), QT_NT, qt_smem_bytes(h->qt_M), st>>>(
         h->d_plan, h->qt_M, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_lkp_xy,
         h->d_lkp_score, h->d_nlkp, h->d_err);
+    STAGE(3);
     k_blur_tiles<<<dim3(P.n_tiles, n), 256, 0, st>>>(h->d_plan, h->d_tiles, h->d_pyr, h->d_blur);
+    STAGE(4);
     k_orient_describe<<<dim3((P.kp_total + 7) / 8, n), 256, 0, st>>>(
         h->d_plan, h->d_pattern, h->d_pyr, h->d_blur, h->d_lkp_xy, h->d_lkp_score, h->d_nlkp,
         h->d_out_kp, h->d_out_desc, h->d_nout);
+    STAGE(5);
+#undef STAGE
     CU(cudaGetLastError());
     return BORB_OK;
 }
@@ -497,6 +510,9 @@ int borb_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int 
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->evt0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->evt1);
+    for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->evs[i]);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_pattern, sizeof kPattern);
     if (e == cudaSuccess) e = cudaMemcpy(h->d_pattern, kPattern, sizeof kPattern, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
@@ -516,6 +532,9 @@ void borb_destroy(borb_extractor *h)
     if (h->d_pattern) cudaFree(h->d_pattern);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->evt0) cudaEventDestroy(h->evt0);
+    if (h->evt1) cudaEventDestroy(h->evt1);
+    for (int i = 0; i < 8; ++i) if (h->evs[i]) cudaEventDestroy(h->evs[i]);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -555,33 +574,123 @@ static int check_call(borb_extractor *h, const void *img, int n, int cols, int r
     return build_plan(h, cols, rows);
 }
 
-int borb_extract_host(borb_extractor *h, const uint8_t *img, int n, int cols, int rows, size_t step,
-                      size_t stride, unsigned flags)
+int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int rows, size_t step,
+                     size_t stride, unsigned flags)
 {
     int rc = check_call(h, img, n, cols, rows, step, stride);
     if (rc != BORB_OK) return rc;
+    if (h->pending) return fail(BORB_ERR_STATE, "previous submit has not been waited for");
     if ((flags & BORB_WANT_PYRAMID) && (rc = ensure_pyr_host(h)) != BORB_OK) return rc;
-    /* pageable caller memory -> pinned staging (strided rows packed), then one async H2D */
     const size_t fsz = (size_t)cols * rows;
-    for (int f = 0; f < n; ++f) {
-        const uint8_t *s = img + (size_t)f * stride;
-        uint8_t *d = h->h_in + (size_t)f * fsz;
-        if (step == (size_t)cols) std::memcpy(d, s, fsz);
-        else for (int y = 0; y < rows; ++y) std::memcpy(d + (size_t)y * cols, s + (size_t)y * step, (size_t)cols);
+    /* Caller memory that is already page-locked (borb_host_alloc / cudaHostRegister) and densely
+     * packed is copied to the device directly; anything else -- the reference's callers hand over
+     * ordinary pageable cv::Mat data -- is first packed into the handle's pinned staging area. */
+    const uint8_t *src = h->h_in;
+    bool direct = false;
+    if (step == (size_t)cols && (n == 1 || stride == fsz)) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, img) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+            direct = true;
+            src = img;
+        } else {
+            cudaGetLastError();
+        }
     }
-    GraphKey key = {0, nullptr, n, 0, 0, flags};
+    if (!direct)
+        for (int f = 0; f < n; ++f) {
+            const uint8_t *s = img + (size_t)f * stride;
+            uint8_t *d = h->h_in + (size_t)f * fsz;
+            if (step == (size_t)cols) std::memcpy(d, s, fsz);
+            else for (int y = 0; y < rows; ++y) std::memcpy(d + (size_t)y * cols, s + (size_t)y * step, (size_t)cols);
+        }
+    GraphKey key = {0, direct ? (const void *)img : nullptr, n, 0, 0, flags};
     rc = run_cached(h, key, [&]() -> int {
-        CU(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)n * fsz, cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->d_in, src, (size_t)n * fsz, cudaMemcpyHostToDevice, h->stream));
         int r = enqueue_kernels(h, h->d_in, n, (size_t)cols, fsz);
         if (r != BORB_OK) return r;
         return enqueue_fetch(h, n, flags);
     });
     if (rc != BORB_OK) return rc;
-    CU(cudaStreamSynchronize(h->stream));
     h->last_n = n;
+    h->pending = true;
+    h->pending_flags = flags;
+    h->results_on_host = false;
+    h->pyramid_on_host = false;
+    return BORB_OK;
+}
+
+int borb_wait(borb_extractor *h)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    if (!h->pending) return fail(BORB_ERR_STATE, "nothing submitted");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    h->pending = false;
     h->results_on_host = true;
-    h->pyramid_on_host = (flags & BORB_WANT_PYRAMID) != 0;
+    h->pyramid_on_host = (h->pending_flags & BORB_WANT_PYRAMID) != 0;
     return check_device_err(h);
+}
+
+int borb_extract_host(borb_extractor *h, const uint8_t *img, int n, int cols, int rows, size_t step,
+                      size_t stride, unsigned flags)
+{
+    const int rc = borb_submit_host(h, img, n, cols, rows, step, stride, flags);
+    return rc != BORB_OK ? rc : borb_wait(h);
+}
+
+void *borb_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        fail(BORB_ERR_CUDA, "cudaMallocHost(%zu) failed", bytes);
+        return nullptr;
+    }
+    return p;
+}
+void borb_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int borb_timer_start(borb_extractor *h)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventRecord(h->evt0, h->stream));
+    return BORB_OK;
+}
+int borb_timer_stop(borb_extractor *h)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventRecord(h->evt1, h->stream));
+    return BORB_OK;
+}
+/* milliseconds between the two marks on the handle's stream; synchronises on the stop mark */
+float borb_timer_ms(borb_extractor *h)
+{
+    float ms = -1.f;
+    if (!h || cudaSetDevice(h->device) != cudaSuccess || cudaEventSynchronize(h->evt1) != cudaSuccess ||
+        cudaEventElapsedTime(&ms, h->evt0, h->evt1) != cudaSuccess) {
+        cudaGetLastError();
+        return -1.f;
+    }
+    return ms;
+}
+
+/* One un-graphed pass with an event between stages; ms[0..4] = pyramid (all levels), FAST,
+ * quadtree, blur, orientation+descriptor+pack. */
+int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n, int cols, int rows,
+                     size_t step, size_t stride, float *ms)
+{
+    int rc = check_call(h, dev_img, n, cols, rows, step, stride);
+    if (rc != BORB_OK) return rc;
+    if (!ms) return fail(BORB_ERR_ARG, "ms is null");
+    rc = enqueue_kernels(h, dev_img, n, step, stride, true);
+    if (rc != BORB_OK) return rc;
+    CU(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < 5; ++i) CU(cudaEventElapsedTime(&ms[i], h->evs[i], h->evs[i + 1]));
+    h->last_n = n;
+    h->results_on_host = h->pyramid_on_host = false;
+    return BORB_OK;
 }
 
 int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int cols, int rows,

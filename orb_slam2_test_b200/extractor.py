@@ -32,6 +32,8 @@ SYMBOLS = [
     "borb_extract_host", "borb_extract_device", "borb_fetch", "borb_sync", "borb_result",
     "borb_pyramid", "borb_level_size", "borb_launches_per_call", "borb_last_device_ms",
     "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score",
+    "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
+    "borb_timer_stop", "borb_timer_ms", "borb_stage_times",
 ]
 
 
@@ -79,6 +81,16 @@ def load_library() -> C.CDLL:
     lib.borb_debug_blurred.argtypes = [_vp, C.c_int, C.c_int, _vp]
     lib.borb_debug_sincos.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.borb_debug_fast_score.argtypes = [_vp, C.c_int, C.c_int]
+    lib.borb_submit_host.argtypes = lib.borb_extract_host.argtypes
+    lib.borb_wait.argtypes = [_vp]
+    lib.borb_host_alloc.argtypes = [C.c_size_t]
+    lib.borb_host_alloc.restype = _vp
+    lib.borb_host_free.argtypes = [_vp]
+    lib.borb_timer_start.argtypes = [_vp]
+    lib.borb_timer_stop.argtypes = [_vp]
+    lib.borb_timer_ms.argtypes = [_vp]
+    lib.borb_timer_ms.restype = C.c_float
+    lib.borb_stage_times.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, _vp]
     _lib = lib
     return lib
 
@@ -201,6 +213,36 @@ class ORBextractor:
         _check(self._lib, self._lib.borb_fetch(self._h, BORB_WANT_PYRAMID if want_pyramid else 0))
         return [self.result(f) for f in range(self._n)]
 
+    def submit_batch(self, images: np.ndarray, want_pyramid: bool = False) -> None:
+        """Asynchronous half of extract_batch; pair with wait()."""
+        assert images.dtype == np.uint8 and images.ndim == 3 and images.flags.c_contiguous
+        n, rows, cols = images.shape
+        _check(self._lib, self._lib.borb_submit_host(self._h, images.ctypes.data, n, cols, rows, cols,
+                                                     rows * cols, BORB_WANT_PYRAMID if want_pyramid else 0))
+        self._n = n
+
+    def wait(self) -> None:
+        _check(self._lib, self._lib.borb_wait(self._h))
+
+    def timer_start(self) -> None:
+        _check(self._lib, self._lib.borb_timer_start(self._h))
+
+    def timer_stop(self) -> None:
+        _check(self._lib, self._lib.borb_timer_stop(self._h))
+
+    def timer_ms(self) -> float:
+        return self._lib.borb_timer_ms(self._h)
+
+    def stage_times(self, dev_ptr: int, n: int, cols: int, rows: int) -> dict:
+        ms = (C.c_float * 5)()
+        _check(self._lib, self._lib.borb_stage_times(self._h, dev_ptr, n, cols, rows, cols, rows * cols, ms))
+        return dict(zip(("pyramid", "fast", "quadtree", "blur", "describe"), [float(v) for v in ms]))
+
+    def count(self, frame: int = 0) -> int:
+        n = C.c_int()
+        _check(self._lib, self._lib.borb_result(self._h, frame, None, None, C.byref(n)))
+        return n.value
+
     def sync(self) -> None:
         _check(self._lib, self._lib.borb_sync(self._h))
 
@@ -251,3 +293,24 @@ class ORBextractor:
         out = np.zeros((r, c), np.uint8)
         _check(self._lib, self._lib.borb_debug_blurred(self._h, frame, level, out.ctypes.data))
         return out
+
+
+def pinned_empty(shape) -> np.ndarray:
+    """uint8 array in page-locked host memory (borb_host_alloc); freed when garbage collected."""
+    lib = load_library()
+    n = int(np.prod(shape))
+    p = lib.borb_host_alloc(n)
+    if not p:
+        raise BorbError(-2, lib.borb_last_error().decode())
+    buf = (C.c_uint8 * n).from_address(p)
+    arr = np.frombuffer(buf, np.uint8).reshape(shape)
+
+    class _Owner:
+        def __del__(self, p=p, lib=lib):
+            lib.borb_host_free(p)
+
+    _PINNED[arr.ctypes.data] = _Owner()
+    return arr
+
+
+_PINNED: dict = {}
