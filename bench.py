@@ -247,6 +247,12 @@ def run_ours(args, rank, world, local):
     ext.stage_times(dev.data_ptr(), F, COLS, ROWS)
     st = ext.stage_times(dev.data_ptr(), F, COLS, ROWS)
 
+    if args.quick:
+        if rank == 0:
+            print(json.dumps({"quick": True, "value": value, "ms_per_step": ms_max / args.steps, "stage_ms": st,
+                              "parity_check": parity, "keypoints_per_frame": n_kp}), flush=True)
+        return
+
     # ---- e2e: host-facing C ABI, pinned host buffers, H2D + D2H inside the timed region ----
     sub = min(64, F)
     n_sub = max(1, F // sub)
@@ -368,6 +374,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames-per-step", type=int, default=512)
+    ap.add_argument("--quick", action="store_true", help="value loop + stage times only (for ncu runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         rank = int(os.environ.get("RANK", "0"))
