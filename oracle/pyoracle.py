@@ -206,6 +206,8 @@ class Reference(_Base):
             path = HERE / "_ref" / ("libreforb_mono.so" if mono else "libreforb.so")
             lib = C.CDLL(str(path))
             lib.reforb_pyramid_info.argtypes = [_vp, C.c_int, _vp, _vp]
+            lib.reforb_distribute.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                              C.c_int, C.c_int, _vp, C.c_int]
             cls._libs[mono] = lib
         return cls._libs[mono]
 
@@ -222,3 +224,13 @@ class Reference(_Base):
         out = np.zeros((r + 2 * border, c + 2 * border), np.uint8)
         assert self.lib.reforb_pyramid_copy(self.h, level, border, out.ctypes.data) == 0
         return out
+
+    def distribute(self, xs, ys, resp, min_x, max_x, min_y, max_y, n_target) -> np.ndarray:
+        """The reference's own DistributeOctTree on these candidates -> survivor indices, in order."""
+        xs = np.ascontiguousarray(xs, np.int32)
+        ys = np.ascontiguousarray(ys, np.int32)
+        resp = np.ascontiguousarray(resp, np.int32)
+        out = np.zeros(len(xs) + 8, np.int32)
+        n = self.lib.reforb_distribute(self.h, xs.ctypes.data, ys.ctypes.data, resp.ctypes.data, len(xs),
+                                       min_x, max_x, min_y, max_y, n_target, out.ctypes.data, len(out))
+        return out[:n].copy()

@@ -27,6 +27,12 @@ struct Exposed : public ORB_SLAM2::ORBextractor {
     using ORB_SLAM2::ORBextractor::ORBextractor;
     const std::vector<int> &quotas() const { return mnFeaturesPerLevel; }
     const std::vector<int> &umaxv() const { return umax; }
+    /* the reference's quadtree on its own (protected member, include/ORBextractor.h:116-117) */
+    std::vector<cv::KeyPoint> distribute(const std::vector<cv::KeyPoint> &k, int min_x, int max_x, int min_y,
+                                         int max_y, int n, int level)
+    {
+        return DistributeOctTree(k, min_x, max_x, min_y, max_y, n, level);
+    }
 };
 
 #ifdef REF_MONOTONE_ALLOC
@@ -147,6 +153,29 @@ void reforb_umax(void *h, int *out)
 {
     const std::vector<int> &u = ((Exposed *)h)->umaxv();
     std::memcpy(out, u.data(), u.size() * sizeof(int));
+}
+
+/* The reference's DistributeOctTree (src/ORBextractor.cc:668-951) on caller-supplied candidates, in
+ * input order; class_id carries the candidate index through, so the survivors come back as
+ * indices in the reference's output order.  Returns their count. */
+int reforb_distribute(void *h, const int *xs, const int *ys, const int *resp, int n, int min_x, int max_x,
+                      int min_y, int max_y, int n_target, int *out_idx, int cap)
+{
+    Exposed *e = (Exposed *)h;
+    std::vector<cv::KeyPoint> in((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        in[i] = cv::KeyPoint((float)xs[i], (float)ys[i], 7.f, -1.f, (float)resp[i], 0, i);
+    }
+#ifdef REF_MONOTONE_ALLOC
+    t_used = 0;
+    t_active = true;
+#endif
+    std::vector<cv::KeyPoint> out = e->distribute(in, min_x, max_x, min_y, max_y, n_target, 0);
+#ifdef REF_MONOTONE_ALLOC
+    t_active = false;
+#endif
+    for (size_t i = 0; i < out.size() && (int)i < cap; ++i) out_idx[i] = out[i].class_id;
+    return (int)out.size();
 }
 
 /* geometry of mvImagePyramid[level] after the last call */
