@@ -1,0 +1,107 @@
+/*
+ * ORBextractor.cc -- host shim: the reference's ORB_SLAM2::ORBextractor interface over the C ABI
+ * of liborb_b200.so (include/borb.h).  Replaces the reference's src/ORBextractor.cc.
+ *
+ * What stays on the host is only what the reference's callers observe: argument conventions,
+ * the empty-image early return (reference src/ORBextractor.cc:1333-1334), the CV_8UC1 assert
+ * (:1337), clear-and-refill of the caller's containers (:1351-1362, :1395) and cv::Mat headers for
+ * mvImagePyramid (:1417).  Scale tables come from the library so that there is a single source.
+ */
+#include "ORBextractor.h"
+
+#include <cassert>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+#include "borb.h"
+
+namespace ORB_SLAM2
+{
+
+namespace
+{
+void check(int rc, const char *what)
+{
+    if (rc != BORB_OK)
+        throw std::runtime_error(std::string("ORBextractor (B200): ") + what + ": " + borb_last_error());
+}
+} // namespace
+
+ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
+    : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST),
+      minThFAST(_minThFAST), handle(NULL), device(0), downloadPyramid(true)
+{
+    if (const char *d = std::getenv("BORB_DEVICE")) device = std::atoi(d);
+    check(borb_create(nfeatures, _scaleFactor, nlevels, iniThFAST, minThFAST, device, 1, &handle), "create");
+    mvScaleFactor.resize(nlevels);
+    mvInvScaleFactor.resize(nlevels);
+    mvLevelSigma2.resize(nlevels);
+    mvInvLevelSigma2.resize(nlevels);
+    mnFeaturesPerLevel.resize(nlevels);
+    umax.resize(16);
+    borb_table(handle, 0, &mvScaleFactor[0]);
+    borb_table(handle, 1, &mvInvScaleFactor[0]);
+    borb_table(handle, 2, &mvLevelSigma2[0]);
+    borb_table(handle, 3, &mvInvLevelSigma2[0]);
+    borb_features_per_level(handle, &mnFeaturesPerLevel[0]);
+    borb_umax(handle, &umax[0]);
+    mvImagePyramid.resize(nlevels);
+}
+
+ORBextractor::~ORBextractor()
+{
+    mvImagePyramid.clear();
+    borb_destroy(handle);
+}
+
+void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint> &_keypoints,
+                              cv::OutputArray _descriptors)
+{
+    if (_image.empty())
+        return;
+
+    cv::Mat image = _image.getMat();
+    assert(image.type() == CV_8UC1);
+
+    // rows of a non-continuous cv::Mat (ROI) are image.step bytes apart; the library packs them
+    check(borb_extract_host(handle, image.data, 1, image.cols, image.rows, (size_t)image.step, 0,
+                            downloadPyramid ? BORB_WANT_PYRAMID : 0u),
+          "extract");
+
+    const borb_keypoint *kps = NULL;
+    const uint8_t *desc = NULL;
+    int n = 0;
+    check(borb_result(handle, 0, &kps, &desc, &n), "result");
+
+    if (n == 0)
+        _descriptors.release();
+    else {
+        _descriptors.create(n, 32, CV_8U);
+        cv::Mat descriptors = _descriptors.getMat();
+        for (int i = 0; i < n; ++i) std::memcpy(descriptors.ptr(i), desc + (size_t)i * 32, 32);
+    }
+
+    _keypoints.clear();
+    _keypoints.reserve(n);
+    for (int i = 0; i < n; ++i) {
+        const borb_keypoint &k = kps[i];
+        _keypoints.push_back(cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id));
+    }
+
+    if (downloadPyramid) {
+        mvImagePyramid.resize(nlevels);
+        for (int level = 0; level < nlevels; ++level) {
+            const uint8_t *data = NULL;
+            int cols = 0, rows = 0;
+            size_t step = 0;
+            check(borb_pyramid(handle, 0, level, &data, &cols, &rows, &step), "pyramid");
+            // header over the library's pinned staging memory, at pixel (0,0) of the level inside
+            // its 19-px reflect-101 frame: the same view the reference keeps (:1417)
+            mvImagePyramid[level] = cv::Mat(rows, cols, CV_8UC1, (void *)data, step);
+        }
+    }
+}
+
+} // namespace ORB_SLAM2

@@ -1,0 +1,112 @@
+/*
+ * ORBextractor.h -- drop-in replacement for the reference's include/ORBextractor.h.
+ *
+ * Same namespace, class name and public interface as ORB_SLAM2::ORBextractor
+ * (reference include/ORBextractor.h:46-144): the five-argument constructor, operator()(image,
+ * mask, keypoints, descriptors), the six scale getters and the public mvImagePyramid, so that the
+ * reference's src/Frame.cc (:101-113, :310-316, :626-757) and src/Tracking.cc (:121-127) compile
+ * and link against it unchanged.  The body is a thin host shim over the C ABI of liborb_b200.so
+ * (include/borb.h): every pixel operation runs in hand-written sm_100a CUDA kernels.  There is no
+ * CPU fallback: if the CUDA library cannot run, the constructor / operator() throw
+ * std::runtime_error.
+ *
+ * Deviations from the reference header, all source-compatible for the in-tree callers:
+ *   - includes <opencv2/core/core.hpp> instead of the legacy <opencv/cv.h> (absent in OpenCV 4);
+ *   - the destructor releases the device handle (the reference's is empty), the class is not
+ *     copyable (callers only ever hold ORBextractor* -- src/Tracking.cc:121-127);
+ *   - ExtractorNode stays declared for source compatibility but its DivideNode is not provided:
+ *     the quadtree lives on the device (csrc/k_quadtree.cuh), and no caller outside the
+ *     reference's own ORBextractor.cc uses the type.  Likewise the protected ComputePyramid /
+ *     ComputeKeyPointsOctTree / DistributeOctTree / ComputeKeyPointsOld members are gone.
+ */
+#ifndef ORBEXTRACTOR_H
+#define ORBEXTRACTOR_H
+
+#include <list>
+#include <vector>
+
+#include <opencv2/core/core.hpp>
+
+struct borb_extractor;
+
+namespace ORB_SLAM2
+{
+
+class ExtractorNode
+{
+public:
+    ExtractorNode() : bNoMore(false) {}
+
+    void DivideNode(ExtractorNode &n1, ExtractorNode &n2, ExtractorNode &n3, ExtractorNode &n4);
+
+    std::vector<cv::KeyPoint> vKeys;
+    cv::Point2i UL, UR, BL, BR;
+    std::list<ExtractorNode>::iterator lit;
+    bool bNoMore;
+};
+
+class ORBextractor
+{
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+
+    ~ORBextractor();
+
+    // Compute the ORB features and descriptors on an image.
+    // Mask is ignored, as in the reference.
+    void operator()(cv::InputArray image, cv::InputArray mask, std::vector<cv::KeyPoint> &keypoints,
+                    cv::OutputArray descriptors);
+
+    int inline GetLevels() { return nlevels; }
+
+    float inline GetScaleFactor() { return scaleFactor; }
+
+    std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
+
+    std::vector<float> inline GetInverseScaleFactors() { return mvInvScaleFactor; }
+
+    std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
+
+    std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    // Level views into page-locked memory owned by the device library; valid until the next
+    // operator() call on this instance (the reference re-creates them every call as well).
+    std::vector<cv::Mat> mvImagePyramid;
+
+    // -- extensions (not in the reference) --
+    // CUDA device of this instance: environment variable BORB_DEVICE at construction, default 0.
+    int GetDevice() const { return device; }
+    // Mono / RGB-D callers never read mvImagePyramid; turning the download off saves the
+    // device-to-host copy of the 8 levels.  Default: on (stereo matching needs it).
+    void SetPyramidDownload(bool on) { downloadPyramid = on; }
+
+protected:
+    int nfeatures;
+    double scaleFactor;
+    int nlevels;
+    int iniThFAST;
+    int minThFAST;
+
+    std::vector<int> mnFeaturesPerLevel;
+
+    std::vector<int> umax;
+
+    std::vector<float> mvScaleFactor;
+    std::vector<float> mvInvScaleFactor;
+    std::vector<float> mvLevelSigma2;
+    std::vector<float> mvInvLevelSigma2;
+
+private:
+    ORBextractor(const ORBextractor &);
+    ORBextractor &operator=(const ORBextractor &);
+
+    borb_extractor *handle;
+    int device;
+    bool downloadPyramid;
+};
+
+} // namespace ORB_SLAM2
+
+#endif

@@ -1,0 +1,132 @@
+/*
+ * tests/shim/frame_like.cc -- TEST: drives the drop-in ORB_SLAM2::ORBextractor exactly the way
+ * the reference's callers do, to show that their source compiles and links unchanged:
+ *   src/Tracking.cc:121-127  `new ORBextractor(nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST)`
+ *                            for left, right and the 2*nFeatures monocular-init extractor
+ *   src/Frame.cc:101-107     the seven getters
+ *   src/Frame.cc:110-113     left and right operator() on two std::threads
+ *   src/Frame.cc:310-316     (*mpORBextractorLeft)(im, cv::Mat(), mvKeys, mDescriptors)
+ *   src/Frame.cc:626,738-757 mvImagePyramid[level].rows/.cols/.rowRange().colRange()
+ *
+ * usage: frame_like <left.raw> <right.raw> <cols> <rows> <nfeatures> <out.bin>
+ * Writes, for left then right: int32 n, n x 28-byte keypoints, n x 32 descriptor bytes, then for
+ * each of the 8 levels int32 cols, rows and an 11x11 window checksum (sum of all level pixels via
+ * rowRange/colRange walks).  The pytest compares everything with the CPU oracle.
+ */
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "ORBextractor.h"
+
+using namespace std;
+using namespace ORB_SLAM2;
+
+struct FrameLike {
+    ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
+    vector<cv::KeyPoint> mvKeys, mvKeysRight;
+    cv::Mat mDescriptors, mDescriptorsRight;
+    int mnScaleLevels;
+    float mfScaleFactor, mfLogScaleFactor;
+    vector<float> mvScaleFactors, mvInvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
+
+    FrameLike(const cv::Mat &imLeft, const cv::Mat &imRight, ORBextractor *l, ORBextractor *r)
+        : mpORBextractorLeft(l), mpORBextractorRight(r)
+    {
+        mnScaleLevels = mpORBextractorLeft->GetLevels();
+        mfScaleFactor = mpORBextractorLeft->GetScaleFactor();
+        mfLogScaleFactor = log(mfScaleFactor);
+        mvScaleFactors = mpORBextractorLeft->GetScaleFactors();
+        mvInvScaleFactors = mpORBextractorLeft->GetInverseScaleFactors();
+        mvLevelSigma2 = mpORBextractorLeft->GetScaleSigmaSquares();
+        mvInvLevelSigma2 = mpORBextractorLeft->GetInverseScaleSigmaSquares();
+
+        thread threadLeft(&FrameLike::ExtractORB, this, 0, imLeft);
+        thread threadRight(&FrameLike::ExtractORB, this, 1, imRight);
+        threadLeft.join();
+        threadRight.join();
+    }
+
+    void ExtractORB(int flag, const cv::Mat &im)
+    {
+        if (flag == 0)
+            (*mpORBextractorLeft)(im, cv::Mat(), mvKeys, mDescriptors);
+        else
+            (*mpORBextractorRight)(im, cv::Mat(), mvKeysRight, mDescriptorsRight);
+    }
+};
+
+static vector<unsigned char> slurp(const char *path, size_t n)
+{
+    vector<unsigned char> b(n);
+    FILE *f = fopen(path, "rb");
+    if (!f || fread(b.data(), 1, n, f) != n) { fprintf(stderr, "cannot read %s\n", path); exit(2); }
+    fclose(f);
+    return b;
+}
+
+static void dump(FILE *f, const vector<cv::KeyPoint> &k, const cv::Mat &d, ORBextractor *e)
+{
+    static_assert(sizeof(cv::KeyPoint) == 28, "cv::KeyPoint layout");
+    int n = (int)k.size();
+    fwrite(&n, 4, 1, f);
+    fwrite(k.data(), 28, (size_t)n, f);
+    for (int i = 0; i < n; ++i) fwrite(d.ptr(i), 1, 32, f);
+    for (int level = 0; level < e->GetLevels(); ++level) {
+        const cv::Mat &L = e->mvImagePyramid[level];
+        int cols = L.cols, rows = L.rows;
+        long long sum = 0;
+        const int w = 5;
+        for (int y = w; y + w + 1 <= rows; y += 2 * w + 1)
+            for (int x = w; x + w + 1 <= cols; x += 2 * w + 1) {
+                cv::Mat I = L.rowRange(y - w, y + w + 1).colRange(x - w, x + w + 1);
+                for (int r = 0; r < I.rows; ++r)
+                    for (int c = 0; c < I.cols; ++c) sum += I.at<uchar>(r, c) * (long long)(1 + ((r * 11 + c) % 7));
+            }
+        fwrite(&cols, 4, 1, f);
+        fwrite(&rows, 4, 1, f);
+        fwrite(&sum, 8, 1, f);
+    }
+}
+
+int main(int argc, char **argv)
+{
+    if (argc != 7) { fprintf(stderr, "usage: %s left right cols rows nfeatures out\n", argv[0]); return 2; }
+    const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[5]);
+    vector<unsigned char> l = slurp(argv[1], (size_t)cols * rows), r = slurp(argv[2], (size_t)cols * rows);
+    cv::Mat imLeft(rows, cols, CV_8UC1, l.data()), imRight(rows, cols, CV_8UC1, r.data());
+
+    const float fScaleFactor = 1.2f;
+    const int nLevels = 8, fIniThFAST = 20, fMinThFAST = 7;
+    ORBextractor *mpORBextractorLeft = new ORBextractor(nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST);
+    ORBextractor *mpORBextractorRight = new ORBextractor(nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST);
+    ORBextractor *mpIniORBextractor = new ORBextractor(2 * nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST);
+
+    FILE *f = fopen(argv[6], "wb");
+    if (!f) return 2;
+    for (int rep = 0; rep < 3; ++rep) { /* instances are reused frame after frame */
+        FrameLike fr(imLeft, imRight, mpORBextractorLeft, mpORBextractorRight);
+        if (rep == 2) {
+            dump(f, fr.mvKeys, fr.mDescriptors, mpORBextractorLeft);
+            dump(f, fr.mvKeysRight, fr.mDescriptorsRight, mpORBextractorRight);
+        }
+    }
+    /* monocular initialisation extractor + the empty-image convention */
+    vector<cv::KeyPoint> k;
+    cv::Mat d;
+    (*mpIniORBextractor)(imLeft, cv::Mat(), k, d);
+    dump(f, k, d, mpIniORBextractor);
+    const size_t before = k.size();
+    (*mpIniORBextractor)(cv::Mat(), cv::Mat(), k, d); /* returns without touching the outputs */
+    int untouched = (k.size() == before && d.rows == (int)before);
+    fwrite(&untouched, 4, 1, f);
+    fclose(f);
+    delete mpORBextractorLeft;
+    delete mpORBextractorRight;
+    delete mpIniORBextractor;
+    printf("frame_like ok\n");
+    return 0;
+}

@@ -1,0 +1,121 @@
+"""The C++ drop-in class (orb_slam2_test_b200/shim/ORBextractor.{h,cc}) driven the way the
+reference's Frame.cc / Tracking.cc drive theirs (tests/shim/frame_like.cc)."""
+import re
+import struct
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from orb_slam2_test_b200 import synth
+
+ROOT = Path(__file__).resolve().parents[1]
+SHIM = ROOT / "orb_slam2_test_b200" / "shim"
+EXE = ROOT / "tests" / "shim" / "frame_like"
+KP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+               ("octave", "<i4"), ("class_id", "<i4")])
+
+# the public interface of the reference class, include/ORBextractor.h:50-101 (whitespace-normalised)
+REFERENCE_PUBLIC = [
+    "enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };",
+    "ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);",
+    "void operator()(cv::InputArray image, cv::InputArray mask, std::vector<cv::KeyPoint> &keypoints, cv::OutputArray descriptors);",
+    "int inline GetLevels()",
+    "float inline GetScaleFactor()",
+    "std::vector<float> inline GetScaleFactors()",
+    "std::vector<float> inline GetInverseScaleFactors()",
+    "std::vector<float> inline GetScaleSigmaSquares()",
+    "std::vector<float> inline GetInverseScaleSigmaSquares()",
+    "std::vector<cv::Mat> mvImagePyramid;",
+]
+
+
+def _norm(s):
+    s = re.sub(r"//[^\n]*", "", s)
+    s = re.sub(r"\s+", " ", s)
+    return re.sub(r"\s*([(),;&{}=])\s*", r"\1", s)
+
+
+def test_public_interface_is_the_reference_interface():
+    hdr = _norm((SHIM / "ORBextractor.h").read_text())
+    assert "namespace ORB_SLAM2" in hdr and "class ORBextractor" in hdr and "class ExtractorNode" in hdr
+    for sig in REFERENCE_PUBLIC:
+        assert _norm(sig) in hdr, sig
+    ref = Path("/root/reference/include/ORBextractor.h")
+    if ref.exists():  # in the build container also check against the reference header itself
+        rh = _norm(ref.read_text())
+        for sig in REFERENCE_PUBLIC[1:]:
+            assert _norm(sig) in rh, f"test list drifted from the reference: {sig}"
+
+
+def test_shim_has_no_pixel_code():
+    """the shim is a host wrapper: no image arithmetic, nothing from oracle/"""
+    src = (SHIM / "ORBextractor.cc").read_text()
+    for bad in ("cv::resize", "GaussianBlur", "cv::FAST", "fastAtan2", "copyMakeBorder", "oracle"):
+        assert bad not in src
+
+
+def _build():
+    subprocess.run(["make", "-s", "-C", str(SHIM)], check=True)
+    subprocess.run(["make", "-s", "-C", str(ROOT / "tests" / "shim")], check=True)
+
+
+def test_fails_loudly_without_a_gpu(tmp_path):
+    from conftest import HAVE_GPU
+    if HAVE_GPU:
+        pytest.skip("a GPU is present")
+    _build()
+    img = synth.make_frame((240, 320), seed=1, frame=0)
+    (tmp_path / "l.raw").write_bytes(img.tobytes())
+    r = subprocess.run([str(EXE), str(tmp_path / "l.raw"), str(tmp_path / "l.raw"), "320", "240", "500",
+                        str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert r.returncode != 0
+    assert "no CPU path" in r.stderr or "runtime_error" in r.stderr
+
+
+def _read_block(buf, off):
+    n, = struct.unpack_from("<i", buf, off); off += 4
+    k = np.frombuffer(buf, KP, n, off); off += 28 * n
+    d = np.frombuffer(buf, np.uint8, 32 * n, off).reshape(n, 32); off += 32 * n
+    lv = []
+    for _ in range(8):
+        c, r, s = struct.unpack_from("<iiq", buf, off); off += 16
+        lv.append((c, r, s))
+    return k, d, lv, off
+
+
+def _level_checksum(L):
+    rows, cols = L.shape
+    w, s = 5, 0
+    wt = (1 + (np.arange(121) % 7)).reshape(11, 11).astype(np.int64)
+    for y in range(w, rows - w, 11):
+        for x in range(w, cols - w, 11):
+            s += int((L[y - w:y + w + 1, x - w:x + w + 1].astype(np.int64) * wt).sum())
+    return s
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,nf", [(synth.KITTI_SHAPE, 2000), (synth.TUM_SHAPE, 1000)])
+def test_frame_like_caller_matches_oracle(shape, nf, tmp_path, oracle_built):
+    _build()
+    left = synth.make_frame(shape, seed=31, frame=0, eye=0)
+    right = synth.make_frame(shape, seed=31, frame=0, eye=1)
+    (tmp_path / "l.raw").write_bytes(left.tobytes())
+    (tmp_path / "r.raw").write_bytes(right.tobytes())
+    r = subprocess.run([str(EXE), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(shape[1]), str(shape[0]),
+                        str(nf), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = (tmp_path / "o.bin").read_bytes()
+    off = 0
+    for img, n_feat in ((left, nf), (right, nf), (left, 2 * nf)):
+        k, d, lv, off = _read_block(buf, off)
+        o = oracle_built.Oracle(n_feat, 1.2, 8, 20, 7)
+        ok, od = o.extract(img)
+        assert k.tobytes() == ok.tobytes() and d.tobytes() == od.tobytes()
+        for l in range(8):
+            c, rws = o.level_size(l)
+            assert (lv[l][0], lv[l][1]) == (c, rws)
+            assert lv[l][2] == _level_checksum(o.pyramid(l, 0))
+    untouched, = struct.unpack_from("<i", buf, off)
+    assert untouched == 1
