@@ -107,6 +107,7 @@ struct borb_extractor {
     bool have_plan = false;
     BorbPlan plan;
     int qt_M = 0;
+    int fast_smem = 0, n_sm = 148;
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
     BorbPlan *d_plan = nullptr;
@@ -288,6 +289,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
                 c.sx = (short)(j * L.w_cell); c.sy = (short)(i * L.h_cell);
                 if (c.ww < 7 || c.wh < 7) continue; /* cv::FAST finds nothing in such a window */
                 cells.push_back(c);
+                P.fast_max_wh = std::max(P.fast_max_wh, (int)c.wh);
+                P.fast_max_pix = std::max(P.fast_max_pix, (c.ww - 6) * (c.wh - 6));
                 cap += (long long)((c.ww - 6 + 1) / 2) * ((c.wh - 6 + 1) / 2);
             }
         }
@@ -357,6 +360,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMemset(h->d_blur, 0, B * (size_t)P.pyr_bytes));
     CU(cudaMemset(h->d_pyr, 0, B * (size_t)P.pyr_bytes));
 
+    h->fast_smem = fast_smem_layout(P.fast_max_wh, P.fast_max_pix).bytes;
+    CU(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
     h->qt_M = M;
     const size_t qt_smem = qt_smem_bytes(M);
     CU(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem));
@@ -391,8 +396,12 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         }
     }
     STAGE(1);
-    k_fast_cells<<<dim3(P.n_cells, n), 128, 0, st>>>(h->d_plan, h->d_cells, h->d_pyr, h->d_cand_xy,
-                                                     h->d_cand_score, h->d_ncand);
+    {   /* K2: persistent CTAs, a multiple of the SM count */
+        const int per_sm = std::max(1, std::min(16, (200 * 1024) / std::max(h->fast_smem, 1)));
+        const int grid = std::min(P.n_cells * n, h->n_sm * per_sm);
+        k_fast_cells<<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, h->d_pyr, h->d_cand_xy,
+                                                          h->d_cand_score, h->d_ncand);
+    }
     STAGE(2);
     k_quadtree<<<dim3(P.nlevels, n), QT_NT, qt_smem_bytes(h->qt_M), st>>>(
         h->d_plan, h->qt_M, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_lkp_xy,
@@ -500,7 +509,10 @@ int borb_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int 
     if (device < 0) CU(cudaGetDevice(&device));
     if (device >= ndev) return fail(BORB_ERR_ARG, "device %d of %d", device, ndev);
     CU(cudaSetDevice(device));
+    int n_sm = 0;
+    CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device));
     borb_extractor *h = new borb_extractor();
+    h->n_sm = n_sm > 0 ? n_sm : 148;
     h->nfeatures = nfeatures; h->nlevels = nlevels; h->ini_th = ini_th; h->min_th = min_th;
     h->scale_factor = scale_factor;
     h->device = device; h->max_batch = max_batch;

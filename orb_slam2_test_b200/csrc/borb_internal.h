@@ -70,6 +70,7 @@ struct BorbPlan {
     long long cand_total;   /* per frame */
     int kp_total;           /* per frame */
     int n_cells, n_tiles;
+    int fast_max_wh, fast_max_pix; /* tallest FAST window, largest detection domain (pixels) */
     int umax[16];
     BorbLevel lv[BORB_MAXL];
 };
