@@ -11,18 +11,22 @@
  * emits K(ini) if that is non-empty, else K(min).  NMS never looks across the cell's domain
  * (3 px inside the window), exactly as a per-cell cv::FAST call does.
  *
- * Execution shape (v2).  Corner-ness is sparse and its cost is wildly uneven per pixel (a 5-load
- * compass test rejects ~3/4 of the pixels, scoring a corner costs ~400 instructions), so a
- * pixel-per-thread kernel spends its time in divergent warps (v1: 17 of 32 lanes active, ALU pipe
- * 87 % busy -- profiles/r1_fast_v1_raw.csv).  v2 is a persistent kernel, one CTA per cell at a
- * time, that runs the test as four DENSE stages with a shared-memory compaction between them:
- *   stage 0  window -> shared memory, aligned 32-bit loads
- *   stage 1  every pixel: compass pre-test (two ADJACENT compass points beyond the threshold on
- *            the same side -- necessary for a 9-arc), survivors appended to list1 with their side
- *   stage 2  list1: 16-point segment test on that side, corners appended to list2
- *   stage 3  list2: score -> score plane
- *   stage 4  list2: strict 3x3 NMS on the score plane, survivors to list3, count of those >= ini
- *   emit     one global atomicAdd per cell reserves the output slots
+ * Execution shape (v3).  Corner-ness is sparse and its cost is wildly uneven per pixel (a 5-load
+ * compass test rejects over half of the pixels, the full test + score costs ~150 instructions), so
+ * a pixel-per-thread kernel spends its time in divergent warps (v1: 17 of 32 lanes active, ALU pipe
+ * 87 % busy -- profiles/r1_fast_v1_raw.csv).  This is a persistent kernel, one CTA (4 warps) per
+ * cell at a time; every warp owns a contiguous quarter of the cell's pixels and runs DENSE stages
+ * over warp-private shared-memory lists (ballot/popc compaction, no atomics):
+ *   stage 0  window -> shared memory, aligned 32-bit loads                       | barrier
+ *   stage 1  own pixels: compass pre-test (two ADJACENT compass points beyond the threshold on
+ *            the same side -- necessary for a 9-arc); (pixel, side) appended to list1
+ *   stage 2  list1: the 16 contrasts on that side, M = max over the 16 arcs of the minimum of
+ *            their 9 contrasts (sliding-window minimum: 4 min stages + 1 max tree); the pixel is
+ *            a corner at t_lo iff M > t_lo and its score is M - 1 (= OpenCV cornerScore<16>);
+ *            score -> score plane, pixel -> list2                               | barrier
+ *   stage 3  list2: strict 3x3 NMS on the score plane, survivors to list3, per-warp counts
+ *                                                                                | barrier
+ *   emit     K(ini) if any warp has a survivor >= ini, else K(min); one global atomicAdd per warp
  * The score plane is kept zero between cells by clearing only the entries of list2.
  *
  * Candidates are appended UNORDERED.  The reference order (cell row, cell col, y, x) only ever
@@ -62,9 +66,11 @@ __host__ __device__ __forceinline__ bool has_arc9(uint32_t m)
 /* Largest threshold t >= t_lo at which the 16 signed contrasts e[] (positive = beyond the centre
  * on the corner's side) still contain a 9-arc; the caller guarantees there is one at t_lo.
  * = OpenCV's cornerScore<16> for a corner (max over arcs of min contrast, minus 1).
- * Bisection over the threshold with the bit-mask arc test; NOTE: the min/max-chain formulation of
- * this score is miscompiled by ptxas 12.9 -O1..-O3 for sm_100a (3-input min/max fusion;
- * tools/dbg_fast.cu reproduces it), do not reintroduce it without that check. */
+ * Bisection over the threshold with the bit-mask arc test: exact by definition of the score.  This
+ * is the REFERENCE form (host tap, tools/dbg_*.cu); the kernel uses fast_arc_minmax below.
+ * NOTE: OpenCV's interleaved min/max chain for this score is miscompiled by ptxas 12.9 -O1..-O3 for
+ * sm_100a (tools/dbg_fast.cu reproduces it); the sliding-window form below is not
+ * (tools/dbg_score.cu: 0 mismatches vs this bisection on 0.9 M corners, int32 / float / s16x2). */
 __host__ __device__ __forceinline__ int fast_score_from_contrasts(const int *e, int t_lo)
 {
     int lo = t_lo, hi = 254;
@@ -108,26 +114,42 @@ __host__ __device__ __forceinline__ int fast_score_px(const uint8_t *p, int pitc
 __host__ __device__ __forceinline__ uint32_t fast_div_magic(int d) { return (1u << 20) / (uint32_t)d + 1u; }
 __host__ __device__ __forceinline__ int fast_div(int i, uint32_t m) { return (int)(((uint32_t)i * m) >> 20); }
 
+/* max over the 16 circular 9-arcs of the minimum contrast in the arc */
+__device__ __forceinline__ int fast_arc_minmax(const int *e)
+{
+    int m2[16], m4[16], m8[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m2[k] = min(e[k], e[(k + 1) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m4[k] = min(m2[k], m2[(k + 2) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m8[k] = min(m4[k], m4[(k + 4) & 15]);
+    int M = -65536;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) M = max(M, min(m8[k], e[(k + 8) & 15]));
+    return M;
+}
+
 /* Shared memory of one CTA, sized on the host for the largest cell of the plan (K2k: 33x40 px ->
- * 15 KB, so 14 CTAs fit on an SM; the 60x60 worst case of the cell formula needs 36 KB). */
+ * 18 KB; the 60x60 worst case of the cell formula needs 44 KB).  chunk = pixels per warp. */
+#define FAST_NW (FAST_NT / 32)
 struct FastSmemLayout {
-    int win_off, sc_off, l1_off, l2_off, l3_off, bytes;
+    int chunk, win_off, sc_off, l1_off, l2_off, l3_off, bytes;
 };
+__host__ __device__ __forceinline__ int fast_chunk(int npix) { return ((npix + FAST_NT - 1) / FAST_NT) * 32; }
 __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix)
 {
     FastSmemLayout o;
-    int b = 64; /* counters */
+    o.chunk = fast_chunk(max_pix);
+    int b = 64; /* per-warp counts */
     o.win_off = b; b += max_wh * FAST_WPITCH;
     o.sc_off = b;  b += ((max_wh - 4) * FAST_SPITCH + 15) & ~15;
-    o.l1_off = b;  b += (2 * max_pix * 2 + 15) & ~15;  /* u16 pixel | side<<12; one slot per side */
-    o.l2_off = b;  b += (max_pix * 2 + 15) & ~15;      /* u16 corners */
-    o.l3_off = b;  b += (max_pix / 4 + 64) * 4;        /* u32 NMS survivors: pixel | score<<12 */
+    o.l1_off = b;  b += FAST_NW * 2 * o.chunk * 2;        /* u16 pixel | side<<12, one slot per side */
+    o.l2_off = b;  b += FAST_NW * o.chunk * 2;            /* u16 corners */
+    o.l3_off = b;  b += FAST_NW * (o.chunk / 2 + 32) * 4; /* u32 NMS survivors: pixel | score<<12 */
     o.bytes = b;
     return o;
 }
-struct FastCounters {
-    int n1, n2, n3, n_hi, out_base, out_fill;
-};
 
 __global__ void __launch_bounds__(FAST_NT)
 k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cells, int n_frames,
@@ -136,23 +158,20 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
 {
     extern __shared__ __align__(16) unsigned char fast_raw[];
     const FastSmemLayout lay = fast_smem_layout(plan->fast_max_wh, plan->fast_max_pix);
-    struct {
-        FastCounters &c;
-        uint8_t *win, *sc;
-        uint16_t *list1, *list2;
-        uint32_t *list3;
-    } s = {*reinterpret_cast<FastCounters *>(fast_raw), fast_raw + lay.win_off, fast_raw + lay.sc_off,
-           reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off), reinterpret_cast<uint16_t *>(fast_raw + lay.l2_off),
-           reinterpret_cast<uint32_t *>(fast_raw + lay.l3_off)};
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t below = (1u << lane) - 1u;
+    int2 *wcnt = reinterpret_cast<int2 *>(fast_raw); /* per warp: (NMS survivors, of which >= ini) */
+    uint8_t *win = fast_raw + lay.win_off;
+    uint8_t *sc = fast_raw + lay.sc_off;
+    uint16_t *list1 = reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off) + warp * 2 * lay.chunk;
+    uint16_t *list2 = reinterpret_cast<uint16_t *>(fast_raw + lay.l2_off) + warp * lay.chunk;
+    uint32_t *list3 = reinterpret_cast<uint32_t *>(fast_raw + lay.l3_off) + warp * (lay.chunk / 2 + 32);
     const int n_cells = plan->n_cells;
     const int total = n_cells * n_frames;
     const int ini = plan->ini_th, mn = plan->min_th;
     const int t_lo = min(ini, mn);
 
-    for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(s.sc)[i] = 0u;
-    if (tid == 0) { s.c.n1 = 0; s.c.n2 = 0; s.c.n3 = 0; s.c.n_hi = 0; s.c.out_fill = 0; }
-    __syncthreads();
+    for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(sc)[i] = 0u;
 
     for (int work = blockIdx.x; work < total; work += gridDim.x) {
         const int frame = work / n_cells;
@@ -174,101 +193,73 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
             for (int i = tid; i < nw; i += FAST_NT) {
                 const int y = fast_div(i, wmagic), w = i - y * wpr;
                 const uint32_t v = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)(cell.y0 + y) * L.pitch + ax0) + w);
-                reinterpret_cast<uint32_t *>(s.win + y * FAST_WPITCH)[w] = v;
+                reinterpret_cast<uint32_t *>(win + y * FAST_WPITCH)[w] = v;
             }
         }
         __syncthreads();
 
-        /* ---- stage 1: compass pre-test on every pixel of the domain ---- */
-        for (int i0 = 0; i0 < npix; i0 += FAST_NT) {
-            const int i = i0 + tid;
+        /* ---- stage 1: compass pre-test on this warp's pixels ---- */
+        const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
+        const int chunk = fast_chunk(npix);
+        const int i_end = min((warp + 1) * chunk, npix);
+        int n1 = 0;
+        for (int i = warp * chunk + lane; i - lane < i_end; i += 32) {
             uint32_t side = 0;
-            int y = 0, x = 0;
-            if (i < npix) {
-                y = fast_div(i, dmagic);
-                x = i - y * dw;
-                const uint8_t *p = s.win + (y + 3) * FAST_WPITCH + xoff + x + 3;
+            uint32_t pix = 0;
+            if (i < i_end) {
+                const int y = fast_div(i, dmagic), x = i - y * dw;
+                pix = (uint32_t)(y * 64 + x);
+                const uint8_t *p = org + y * FAST_WPITCH + x;
                 const int v = p[0];
                 const int lo = v - t_lo, hi = v + t_lo;
                 const int r0 = p[3 * FAST_WPITCH], r4 = p[3], r8 = p[-3 * FAST_WPITCH], r12 = p[-3];
-                const bool b0 = r0 < lo, b4 = r4 < lo, b8 = r8 < lo, b12 = r12 < lo;
-                const bool k0 = r0 > hi, k4 = r4 > hi, k8 = r8 > hi, k12 = r12 > hi;
                 /* a 9-arc covers two adjacent compass points */
-                if ((b0 && (b4 || b12)) || (b8 && (b4 || b12))) side |= 1u;
-                if ((k0 && (k4 || k12)) || (k8 && (k4 || k12))) side |= 2u;
+                if (((r0 < lo) || (r8 < lo)) && ((r4 < lo) || (r12 < lo))) side |= 1u;
+                if (((r0 > hi) || (r8 > hi)) && ((r4 > hi) || (r12 > hi))) side |= 2u;
             }
-            const uint32_t bal = __ballot_sync(0xffffffffu, side != 0);
-            if (bal) {
-                /* both sides flagged is possible but rare: such a pixel takes two slots */
-                const uint32_t both = __ballot_sync(0xffffffffu, side == 3u);
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&s.c.n1, __popc(bal) + __popc(both));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (side) {
-                    const uint32_t below = (1u << lane) - 1u;
-                    int slot = base + __popc(bal & below) + __popc(both & below);
-                    const uint32_t pix = (uint32_t)(y * 64 + x);
-                    if (side & 1u) s.list1[slot++] = (uint16_t)(pix | (1u << 12));
-                    if (side & 2u) s.list1[slot] = (uint16_t)(pix | (2u << 12));
-                }
-            }
+            const uint32_t b1 = __ballot_sync(0xffffffffu, side & 1u), b2 = __ballot_sync(0xffffffffu, side & 2u);
+            /* both sides flagged is possible but rare: such a pixel takes two slots */
+            if (side & 1u) list1[n1 + __popc(b1 & below)] = (uint16_t)(pix | (1u << 12));
+            n1 += __popc(b1);
+            if (side & 2u) list1[n1 + __popc(b2 & below)] = (uint16_t)(pix | (2u << 12));
+            n1 += __popc(b2);
         }
-        __syncthreads();
+        __syncwarp();
 
-        /* ---- stage 2: full segment test of the listed (pixel, side) pairs ---- */
-        const int n1 = s.c.n1;
-        for (int i0 = 0; i0 < n1; i0 += FAST_NT) {
-            const int i = i0 + tid;
+        /* ---- stage 2: full test + score of the listed (pixel, side) pairs ---- */
+        int n2 = 0;
+        for (int i = lane; i - lane < n1; i += 32) {
             bool corner = false;
             uint32_t ent = 0;
             if (i < n1) {
-                ent = s.list1[i];
+                ent = list1[i];
                 const int x = ent & 63, y = (ent >> 6) & 63;
-                const uint8_t *p = s.win + (y + 3) * FAST_WPITCH + xoff + x + 3;
+                const uint8_t *p = org + y * FAST_WPITCH + x;
                 const int v = p[0];
-                /* contrast beyond the threshold on this side: g = sgn*r + off > 0 */
-                const int sgn = (ent & (1u << 12)) ? -1 : 1;
-                const int off = (ent & (1u << 12)) ? v - t_lo : -(v + t_lo);
-                uint32_t m = 0;
+                const bool bright = (ent & (1u << 12)) != 0;
+                const int sgn = bright ? -1 : 1, off = bright ? v : -v; /* contrast on this side */
+                int e[16];
 #pragma unroll
-                for (int k = 0; k < 16; ++k) m |= (uint32_t)(sgn * (int)FAST_RING(p, FAST_WPITCH, k) + off > 0) << k;
-                corner = has_arc9(m);
+                for (int k = 0; k < 16; ++k) e[k] = sgn * (int)FAST_RING(p, FAST_WPITCH, k) + off;
+                const int M = fast_arc_minmax(e);
+                corner = M > t_lo;
+                if (corner) sc[(y + 1) * FAST_SPITCH + x + 1] = (uint8_t)(M - 1);
             }
             const uint32_t bal = __ballot_sync(0xffffffffu, corner);
-            if (bal) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&s.c.n2, __popc(bal));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (corner) s.list2[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)ent;
-            }
+            if (corner) list2[n2 + __popc(bal & below)] = (uint16_t)ent;
+            n2 += __popc(bal);
         }
         __syncthreads();
 
-        /* ---- stage 3: score of every corner -> score plane ---- */
-        const int n2 = s.c.n2;
-        for (int i = tid; i < n2; i += FAST_NT) {
-            const uint32_t ent = s.list2[i];
-            const int x = ent & 63, y = (ent >> 6) & 63;
-            const uint8_t *p = s.win + (y + 3) * FAST_WPITCH + xoff + x + 3;
-            const int v = p[0];
-            const int sgn = (ent & (1u << 12)) ? -1 : 1;
-            const int off = (ent & (1u << 12)) ? v : -v;
-            int e[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) e[k] = sgn * (int)FAST_RING(p, FAST_WPITCH, k) + off;
-            s.sc[(y + 1) * FAST_SPITCH + x + 1] = (uint8_t)fast_score_from_contrasts(e, t_lo);
-        }
-        __syncthreads();
-
-        /* ---- stage 4: strict 3x3 NMS inside the domain ---- */
-        for (int i0 = 0; i0 < n2; i0 += FAST_NT) {
-            const int i = i0 + tid;
+        /* ---- stage 3: strict 3x3 NMS inside the domain ---- */
+        int n3 = 0, n3_hi = 0;
+        for (int i = lane; i - lane < n2; i += 32) {
             bool keep = false;
             uint32_t rec = 0;
             if (i < n2) {
-                const uint32_t ent = s.list2[i];
+                const uint32_t ent = list2[i];
                 const int x = ent & 63, y = (ent >> 6) & 63;
-                const uint8_t *q = s.sc + (y + 1) * FAST_SPITCH + x + 1;
+                const uint8_t *q = sc + (y + 1) * FAST_SPITCH + x + 1;
                 const int c = q[0];
                 keep = c > q[-1] && c > q[1] && c > q[-FAST_SPITCH - 1] && c > q[-FAST_SPITCH] &&
                        c > q[-FAST_SPITCH + 1] && c > q[FAST_SPITCH - 1] && c > q[FAST_SPITCH] &&
@@ -276,54 +267,48 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
                 rec = (ent & 0xfffu) | ((uint32_t)c << 12);
             }
             const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-            if (bal) {
-                const uint32_t bhi = __ballot_sync(0xffffffffu, keep && (int)(rec >> 12) >= ini);
-                int base = 0;
-                if (lane == 0) {
-                    base = atomicAdd(&s.c.n3, __popc(bal));
-                    if (bhi) atomicAdd(&s.c.n_hi, __popc(bhi));
-                }
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (keep) s.list3[base + __popc(bal & ((1u << lane) - 1u))] = rec;
-            }
+            n3_hi += __popc(__ballot_sync(0xffffffffu, keep && (int)(rec >> 12) >= ini));
+            if (keep) list3[n3 + __popc(bal & below)] = rec;
+            n3 += __popc(bal);
         }
+        if (lane == 0) wcnt[warp] = make_int2(n3, n3_hi);
         __syncthreads();
 
         /* ---- emit: K(ini) if non-empty else K(min).  (With ini < min every survivor already is
-         * >= ini, so n_hi == n3: a cell empty at ini stays empty, its second pass being a subset.) ---- */
-        const int n3 = s.c.n3, n_hi = s.c.n_hi;
-        const int t_emit = n_hi ? ini : mn;
-        const int n_emit = n_hi ? n_hi : n3;
+         * >= ini: a cell empty at ini stays empty, its second pass being a subset.) ---- */
+        int any_hi = 0;
+#pragma unroll
+        for (int w = 0; w < FAST_NW; ++w) any_hi += wcnt[w].y;
+        const int t_emit = any_hi ? ini : mn;
+        const int n_emit = any_hi ? n3_hi : n3;
         if (n_emit > 0) {
-            int *cnt = ncand + frame * BORB_MAXL + cell.level;
-            if (tid == 0) s.c.out_base = atomicAdd(cnt, n_emit);
-            __syncthreads();
-            const int base = s.c.out_base;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(ncand + frame * BORB_MAXL + cell.level, n_emit);
+            base = __shfl_sync(0xffffffffu, base, 0);
             uint32_t *oxy = cand_xy + (size_t)frame * (size_t)plan->cand_total + L.cand_off;
             uint32_t *osc = cand_score + (size_t)frame * (size_t)plan->cand_total + L.cand_off;
-            for (int i = tid; i < n3; i += FAST_NT) {
-                const uint32_t rec = s.list3[i];
+            for (int i = lane; i - lane < n3; i += 32) {
+                const uint32_t rec = i < n3 ? list3[i] : 0u;
                 const int c = (int)(rec >> 12);
-                if (c >= t_emit) {
-                    const int slot = base + atomicAdd(&s.c.out_fill, 1);
-                    if (slot < L.cand_cap) {
-                        const int x = rec & 63, y = (rec >> 6) & 63;
-                        /* window-relative (x+3, y+3) shifted by the cell origin: coords relative
-                         * to (minBorderX, minBorderY), src/ORBextractor.cc:1087-1088 */
-                        oxy[slot] = (uint32_t)(x + 3 + cell.sx) | ((uint32_t)(y + 3 + cell.sy) << 16);
-                        osc[slot] = (uint32_t)c;
-                    }
+                const bool out = i < n3 && c >= t_emit;
+                const uint32_t bal = __ballot_sync(0xffffffffu, out);
+                const int slot = base + __popc(bal & below);
+                if (out && slot < L.cand_cap) {
+                    const int x = rec & 63, y = (rec >> 6) & 63;
+                    /* window-relative (x+3, y+3) shifted by the cell origin: coords relative
+                     * to (minBorderX, minBorderY), src/ORBextractor.cc:1087-1088 */
+                    oxy[slot] = (uint32_t)(x + 3 + cell.sx) | ((uint32_t)(y + 3 + cell.sy) << 16);
+                    osc[slot] = (uint32_t)c;
                 }
+                base += __popc(bal);
             }
         }
-        /* ---- restore the all-zero score plane and the counters for the next cell ---- */
-        for (int i = tid; i < n2; i += FAST_NT) {
-            const uint32_t ent = s.list2[i];
-            s.sc[(((ent >> 6) & 63) + 1) * FAST_SPITCH + (ent & 63) + 1] = 0;
+        /* ---- restore the all-zero score plane for the next cell (own corners only) ---- */
+        for (int i = lane; i < n2; i += 32) {
+            const uint32_t ent = list2[i];
+            sc[(((ent >> 6) & 63) + 1) * FAST_SPITCH + (ent & 63) + 1] = 0;
         }
-        __syncthreads();
-        if (tid == 0) { s.c.n1 = 0; s.c.n2 = 0; s.c.n3 = 0; s.c.n_hi = 0; s.c.out_fill = 0; }
-        /* the next iteration's first write to these is after its stage-0 barrier */
+        /* the next cell's first write to the score plane / wcnt comes after its stage-0 barrier */
     }
 }
 
