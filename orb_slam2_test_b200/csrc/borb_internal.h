@@ -56,7 +56,7 @@ struct BorbCell { /* one FAST window, reference :1000-1064 */
     short sx, sy;     /* j*wCell, i*hCell: shift added to window-relative coords */
 };
 
-struct BorbTile { /* one blur tile */
+struct BorbTile { /* one blur strip: BORB_BLUR_TW columns x BORB_BLUR_TH rows of a level */
     short level;
     short pad;
     short x0, y0;
@@ -75,7 +75,7 @@ struct BorbPlan {
     BorbLevel lv[BORB_MAXL];
 };
 
-#define BORB_BLUR_TW 64
-#define BORB_BLUR_TH 16
+#define BORB_BLUR_TW 128 /* one warp x 4 columns */
+#define BORB_BLUR_TH 32
 
 #endif

@@ -6,66 +6,82 @@
  *   row pass  H = sum k[i] * src            (<= 65280, 16 bit)
  *   col pass  V = sum k[j] * H              (32 bit),   dst = (V + 32768) >> 16
  * The reference blurs an un-padded clone with BORDER_REFLECT_101; the pyramid's own 19-pixel
- * frame holds exactly those reflected values, so the tile halo is read straight from it.
+ * frame holds exactly those reflected values, so halos are read straight from it.
  *
- * One CTA per 64x16 output tile of any level (flat tile list): (16+6) x (64+6) source bytes are
- * staged in shared memory, the row pass writes 22 x 64 u16, the column pass emits 4 pixels per
- * thread as one 32-bit store.
+ * v2: no shared memory.  A warp owns a 128-column x BORB_BLUR_TH-row strip; a thread owns 4 adjacent
+ * columns (one aligned 32-bit word of every row).  Walking down the strip it loads three words per
+ * row (its own and the two neighbours': L1 hits), forms the 4 row sums with 8 byte-dot-products
+ * (dp4a with the taps packed as bytes: 18,34,48,56 | 48,34,18,0) and keeps the last 7 rows of row
+ * sums in registers (the loop is unrolled by 7 so the window is statically indexed); each new row
+ * yields one output word.  Algorithmic traffic: read 1 B + write 1 B per pixel.
  */
 #ifndef K_BLUR_CUH
 #define K_BLUR_CUH
 
 #include "borb_internal.h"
 
-#define BLUR_SP 72 /* staged row pitch, >= BORB_BLUR_TW + 6 */
+#define BLUR_NT 128 /* 4 warps = 4 consecutive strips of the tile list */
 
-__global__ void __launch_bounds__(256)
-k_blur_tiles(const BorbPlan *__restrict__ plan, const BorbTile *__restrict__ tiles,
-             const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur)
+__device__ __forceinline__ void blur_row_sums(const uint8_t *__restrict__ row, int c, int cmax, uint32_t h[4])
 {
-    __shared__ uint8_t src[(BORB_BLUR_TH + 6) * BLUR_SP];
-    __shared__ uint16_t hp[(BORB_BLUR_TH + 6) * BORB_BLUR_TW];
+    /* words at columns c-4, c, c+4 (row is 4-byte aligned at column 0; c is a multiple of 4);
+     * cmax = last readable word column of the padded row */
+    const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t *>(row + c - 4));
+    const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t *>(row + c));
+    const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t *>(row + min(c + 4, cmax)));
+    const uint32_t klo = 18u | (34u << 8) | (48u << 16) | (56u << 24); /* taps 0..3 */
+    const uint32_t khi = 48u | (34u << 8) | (18u << 16);               /* taps 4..6 */
+    /* output column c+i needs bytes c+i-3 .. c+i+3 */
+    h[0] = __dp4a(__byte_perm(w0, w1, 0x4321), klo, __dp4a(__byte_perm(w1, w2, 0x4321), khi, 0u));
+    h[1] = __dp4a(__byte_perm(w0, w1, 0x5432), klo, __dp4a(__byte_perm(w1, w2, 0x5432), khi, 0u));
+    h[2] = __dp4a(__byte_perm(w0, w1, 0x6543), klo, __dp4a(__byte_perm(w1, w2, 0x6543), khi, 0u));
+    h[3] = __dp4a(w1, klo, __dp4a(w2, khi, 0u));
+}
 
-    const BorbTile t = tiles[blockIdx.x];
+__device__ __forceinline__ uint32_t blur_col(const uint32_t a, const uint32_t b, const uint32_t c, const uint32_t d,
+                                             const uint32_t e, const uint32_t f, const uint32_t g)
+{
+    return (18u * (a + g) + 34u * (b + f) + 48u * (c + e) + 56u * d + 32768u) >> 16;
+}
+
+__global__ void __launch_bounds__(BLUR_NT)
+k_blur_strips(const BorbPlan *__restrict__ plan, const BorbTile *__restrict__ tiles,
+              const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur)
+{
+    const int lane = threadIdx.x & 31;
+    const int t_idx = blockIdx.x * (BLUR_NT / 32) + (threadIdx.x >> 5);
+    if (t_idx >= plan->n_tiles) return;
+    const BorbTile t = tiles[t_idx];
     const BorbLevel &L = plan->lv[t.level];
-    const size_t fo = (size_t)blockIdx.y * (size_t)plan->pyr_bytes + L.off;
-    /* pointer to level pixel (0,0) */
-    const uint8_t *in = pyr + fo + (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
-    uint8_t *out = blur + fo + (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
-    const int tid = threadIdx.x;
+    const int c = t.x0 + 4 * lane;
+    if (c >= L.w) return;
+    const size_t fo = (size_t)blockIdx.y * (size_t)plan->pyr_bytes + L.off + (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
+    const uint8_t *in = pyr + fo;  /* level pixel (0,0) */
+    uint8_t *out = blur + fo;
+    const int cmax = L.pitch - BORB_XPAD - 4;
+    const int rows = min(BORB_BLUR_TH, L.h - t.y0);
 
-    /* stage (x0-3 .. x0+66) x (y0-3 .. y0+18); columns/rows past the frame are clamped (their
-     * results are never stored) */
-    for (int i = tid; i < (BORB_BLUR_TH + 6) * (BORB_BLUR_TW + 6); i += 256) {
-        const int r = i / (BORB_BLUR_TW + 6), c = i - r * (BORB_BLUR_TW + 6);
-        const int y = min(t.y0 + r - 3, L.h + BORB_EDGE - 1);
-        const int x = min(t.x0 + c - 3, L.w + BORB_EDGE - 1);
-        src[r * BLUR_SP + c] = in[(ptrdiff_t)y * L.pitch + x];
-    }
-    __syncthreads();
-    for (int i = tid; i < (BORB_BLUR_TH + 6) * BORB_BLUR_TW; i += 256) {
-        const int r = i / BORB_BLUR_TW, c = i - r * BORB_BLUR_TW;
-        const uint8_t *q = src + r * BLUR_SP + c;
-        hp[i] = (uint16_t)(18 * (q[0] + q[6]) + 34 * (q[1] + q[5]) + 48 * (q[2] + q[4]) + 56 * q[3]);
-    }
-    __syncthreads();
-    {
-        const int r = tid >> 4, c4 = (tid & 15) * 4; /* 16 rows x 16 groups of 4 */
-        const int y = t.y0 + r, x = t.x0 + c4;
-        if (y < L.h && x < L.w) {
-            uint32_t v = 0;
+    uint32_t H[7][4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint16_t *h = hp + r * BORB_BLUR_TW + c4 + k;
-                const uint32_t a = 18u * ((uint32_t)h[0] + h[6 * BORB_BLUR_TW]) +
-                                   34u * ((uint32_t)h[BORB_BLUR_TW] + h[5 * BORB_BLUR_TW]) +
-                                   48u * ((uint32_t)h[2 * BORB_BLUR_TW] + h[4 * BORB_BLUR_TW]) +
-                                   56u * (uint32_t)h[3 * BORB_BLUR_TW];
-                v |= ((a + 32768u) >> 16) << (8 * k);
+    for (int r = 0; r < 6; ++r) blur_row_sums(in + (ptrdiff_t)(t.y0 - 3 + r) * L.pitch, c, cmax, H[r]);
+
+    for (int r0 = 0; r0 < rows; r0 += 7) {
+#pragma unroll
+        for (int u = 0; u < 7; ++u) {
+            const int r = r0 + u;
+            if (r < rows) {
+                /* the row entering the window is y0 + r + 3, into slot (6 + u) % 7; the window for
+                 * output row r is slots u, u+1, ..., u+6 (mod 7) */
+                blur_row_sums(in + (ptrdiff_t)(t.y0 + r + 3) * L.pitch, c, cmax, H[(6 + u) % 7]);
+                uint32_t v = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    v |= blur_col(H[u % 7][k], H[(u + 1) % 7][k], H[(u + 2) % 7][k], H[(u + 3) % 7][k],
+                                  H[(u + 4) % 7][k], H[(u + 5) % 7][k], H[(u + 6) % 7][k]) << (8 * k);
+                /* c is a multiple of 4 and the interior starts 32-byte aligned: aligned store; the
+                 * up-to-3 bytes past the last column land in our own pitch padding */
+                *reinterpret_cast<uint32_t *>(out + (size_t)(t.y0 + r) * L.pitch + c) = v;
             }
-            /* x is a multiple of 4 and the interior starts 32-byte aligned: aligned store; the
-             * up-to-3 bytes past the last column land in our own pitch padding */
-            *reinterpret_cast<uint32_t *>(out + (size_t)y * L.pitch + x) = v;
         }
     }
 }
