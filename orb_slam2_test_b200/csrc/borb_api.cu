@@ -241,7 +241,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
         L.h = round_half_even((float)rows * h->inv_scale[l]);
         if (L.w > 32767 || L.h > 32767)
             return fail(BORB_ERR_GEOMETRY, "level %d is %dx%d: coordinates are packed in 16 bits", l, L.w, L.h);
-        L.pitch = (int)align_up(BORB_XPAD + L.w + BORB_EDGE, 32);
+        /* + 3: K1 writes whole words from column -20, the last one may end 3 columns past the frame */
+        L.pitch = (int)align_up(BORB_XPAD + L.w + BORB_EDGE + 3, 32);
         L.prows = L.h + 2 * BORB_EDGE;
         L.off = pyr_off;
         pyr_off = align_up(pyr_off + (long long)L.pitch * L.prows, 256);
@@ -387,12 +388,12 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     STAGE(0);
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
-        dim3 g((L0.pitch / 4 + 255) / 256, L0.prows, n);
-        k_pyr_level0<<<g, 256, 0, st>>>(h->d_plan, dev_img, step, stride, h->d_pyr);
+        const int n0 = pyr_words_per_row(L0.w) * L0.prows;
+        k_pyr_level0<<<dim3((n0 + PYR_NT - 1) / PYR_NT, 1, n), PYR_NT, 0, st>>>(h->d_plan, dev_img, step, stride, h->d_pyr);
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
-            dim3 gl((L.pitch / 4 + 255) / 256, L.prows, n);
-            k_pyr_resize<<<gl, 256, 0, st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s, h->d_pyr);
+            const int nl = pyr_words_per_row(L.w) * ((L.prows + PYR_RS - 1) / PYR_RS);
+            k_pyr_resize<<<dim3((nl + PYR_NT - 1) / PYR_NT, 1, n), PYR_NT, 0, st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s, h->d_pyr);
         }
     }
     STAGE(1);
