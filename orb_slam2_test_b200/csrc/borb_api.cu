@@ -411,7 +411,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, 0, st>>>(h->d_plan, h->d_tiles,
                                                                                               h->d_pyr, h->d_blur);
     STAGE(4);
-    k_orient_describe<<<dim3((P.kp_total + 7) / 8, n), 256, 0, st>>>(
+    k_orient_describe<<<dim3((P.kp_total + DESC_NW * DESC_KPW - 1) / (DESC_NW * DESC_KPW), n), DESC_NT, 0, st>>>(
         h->d_plan, h->d_pattern, h->d_pyr, h->d_blur, h->d_lkp_xy, h->d_lkp_score, h->d_nlkp,
         h->d_out_kp, h->d_out_desc, h->d_nout);
     STAGE(5);
