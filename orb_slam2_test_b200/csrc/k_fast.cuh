@@ -2,14 +2,12 @@
  * k_fast.cuh -- K2: per-cell FAST-9/16 with the iniThFAST -> minThFAST fallback
  * (src/ORBextractor.cc:1000-1094; cv::FAST semantics per SURVEY.md A.3 / oracle/cvprim.c).
  *
- * The reference runs cv::FAST twice on a cell that yields nothing at the high threshold; here ONE
- * score plane is computed per cell at t_lo = min(ini, min):
- *   S(p) = (largest t for which p is still a FAST-9 corner), 0 for non-corners
- *   K(t) = { p : S(p) >= t and S(p) > S(q) for the 8 neighbours q inside the cell's domain }
- * and K(ini) = K(t_lo) restricted to S >= ini (a pixel that beats every neighbour's score beats
- * in particular those of the neighbours that are corners at the higher threshold), so the cell
- * emits K(ini) if that is non-empty, else K(min).  NMS never looks across the cell's domain
- * (3 px inside the window), exactly as a per-cell cv::FAST call does.
+ * With S(p) = the largest t for which p is still a FAST-9 corner (OpenCV's cornerScore, 0 for
+ * non-corners), cv::FAST(t, nms) on a cell returns
+ *   K(t) = { p : S(p) >= t and S(p) > S_t(q) for the 8 neighbours q inside the cell's domain },
+ * S_t(q) = S(q) if S(q) >= t else 0.  The reference keeps K(ini) if it is non-empty, else K(min).
+ * NMS never looks across the cell's domain (3 px inside the window), exactly as a per-cell
+ * cv::FAST call does.
  *
  * Execution shape (v3).  Corner-ness is sparse and its cost is wildly uneven per pixel (a 5-load
  * compass test rejects over half of the pixels, the full test + score costs ~150 instructions), so
@@ -22,11 +20,12 @@
  *            the same side -- necessary for a 9-arc); (pixel, side) appended to list1
  *   stage 2  list1: the 16 contrasts on that side, M = max over the 16 arcs of the minimum of
  *            their 9 contrasts (sliding-window minimum: 4 min stages + 1 max tree); the pixel is
- *            a corner at t_lo iff M > t_lo and its score is M - 1 (= OpenCV cornerScore<16>);
+ *            a corner at t iff M > t and its score is M - 1 (= OpenCV cornerScore<16>);
  *            score -> score plane, pixel -> list2                               | barrier
  *   stage 3  list2: strict 3x3 NMS on the score plane, survivors to list3, per-warp counts
  *                                                                                | barrier
- *   emit     K(ini) if any warp has a survivor >= ini, else K(min); one global atomicAdd per warp
+ *   stages 1-3 run at t = ini; only a cell that ends with no survivor repeats them at t = min
+ *   emit     one global atomicAdd per warp
  * The score plane is kept zero between cells by clearing only the entries of list2.
  *
  * Candidates are appended UNORDERED.  The reference order (cell row, cell col, y, x) only ever
@@ -160,7 +159,7 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     const FastSmemLayout lay = fast_smem_layout(plan->fast_max_wh, plan->fast_max_pix);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t below = (1u << lane) - 1u;
-    int2 *wcnt = reinterpret_cast<int2 *>(fast_raw); /* per warp: (NMS survivors, of which >= ini) */
+    int *wcnt = reinterpret_cast<int *>(fast_raw); /* [pass][warp]: NMS survivors */
     uint8_t *win = fast_raw + lay.win_off;
     uint8_t *sc = fast_raw + lay.sc_off;
     uint16_t *list1 = reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off) + warp * 2 * lay.chunk;
@@ -169,7 +168,6 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     const int n_cells = plan->n_cells;
     const int total = n_cells * n_frames;
     const int ini = plan->ini_th, mn = plan->min_th;
-    const int t_lo = min(ini, mn);
 
     for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(sc)[i] = 0u;
 
@@ -198,109 +196,122 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
         }
         __syncthreads();
 
-        /* ---- stage 1: compass pre-test on this warp's pixels ---- */
         const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
         const int chunk = fast_chunk(npix);
         const int i_end = min((warp + 1) * chunk, npix);
-        int n1 = 0;
-        for (int i = warp * chunk + lane; i - lane < i_end; i += 32) {
-            uint32_t side = 0;
-            uint32_t pix = 0;
-            if (i < i_end) {
-                const int y = fast_div(i, dmagic), x = i - y * dw;
-                pix = (uint32_t)(y * 64 + x);
-                const uint8_t *p = org + y * FAST_WPITCH + x;
-                const int v = p[0];
-                const int lo = v - t_lo, hi = v + t_lo;
-                const int r0 = p[3 * FAST_WPITCH], r4 = p[3], r8 = p[-3 * FAST_WPITCH], r12 = p[-3];
-                /* a 9-arc covers two adjacent compass points */
-                if (((r0 < lo) || (r8 < lo)) && ((r4 < lo) || (r12 < lo))) side |= 1u;
-                if (((r0 > hi) || (r8 > hi)) && ((r4 > hi) || (r12 > hi))) side |= 2u;
-            }
-            const uint32_t b1 = __ballot_sync(0xffffffffu, side & 1u), b2 = __ballot_sync(0xffffffffu, side & 2u);
-            /* both sides flagged is possible but rare: such a pixel takes two slots */
-            if (side & 1u) list1[n1 + __popc(b1 & below)] = (uint16_t)(pix | (1u << 12));
-            n1 += __popc(b1);
-            if (side & 2u) list1[n1 + __popc(b2 & below)] = (uint16_t)(pix | (2u << 12));
-            n1 += __popc(b2);
-        }
-        __syncwarp();
+        int n2 = 0, n3 = 0, cell_total = 0;
+        /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
+         * where the first found nothing; K(ini) needs nothing below ini: a corner's score is at
+         * least the threshold it was detected at, so neighbours that are corners only at the lower
+         * threshold can never beat it.  With ini <= min a second pass could only return a subset
+         * of the (empty) first. */
+        const int n_pass = mn < ini ? 2 : 1;
+        for (int pass = 0; pass < n_pass; ++pass) {
+            const int t = pass == 0 ? ini : mn;
 
-        /* ---- stage 2: full test + score of the listed (pixel, side) pairs ---- */
-        int n2 = 0;
-        for (int i = lane; i - lane < n1; i += 32) {
-            bool corner = false;
-            uint32_t ent = 0;
-            if (i < n1) {
-                ent = list1[i];
-                const int x = ent & 63, y = (ent >> 6) & 63;
-                const uint8_t *p = org + y * FAST_WPITCH + x;
-                const int v = p[0];
-                const bool bright = (ent & (1u << 12)) != 0;
-                const int sgn = bright ? -1 : 1, off = bright ? v : -v; /* contrast on this side */
-                int e[16];
+            /* ---- stage 1: compass pre-test on this warp's pixels ---- */
+            int n1 = 0;
+            for (int i = warp * chunk + lane; i - lane < i_end; i += 32) {
+                uint32_t side = 0;
+                uint32_t pix = 0;
+                if (i < i_end) {
+                    const int y = fast_div(i, dmagic), x = i - y * dw;
+                    pix = (uint32_t)(y * 64 + x);
+                    const uint8_t *p = org + y * FAST_WPITCH + x;
+                    const int v = p[0];
+                    const int lo = v - t, hi = v + t;
+                    const int r0 = p[3 * FAST_WPITCH], r4 = p[3], r8 = p[-3 * FAST_WPITCH], r12 = p[-3];
+                    /* a 9-arc covers two adjacent compass points */
+                    if (((r0 < lo) || (r8 < lo)) && ((r4 < lo) || (r12 < lo))) side |= 1u;
+                    if (((r0 > hi) || (r8 > hi)) && ((r4 > hi) || (r12 > hi))) side |= 2u;
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, side != 0);
+                if (side) list1[n1 + __popc(bal & below)] = (uint16_t)(pix | (side << 12));
+                n1 += __popc(bal);
+            }
+            __syncwarp();
+
+            /* ---- stage 2: full test + score of the listed pixels ---- */
+            n2 = 0;
+            for (int i = lane; i - lane < n1; i += 32) {
+                bool corner = false;
+                uint32_t ent = 0;
+                if (i < n1) {
+                    ent = list1[i];
+                    const int x = ent & 63, y = (ent >> 6) & 63;
+                    const uint8_t *p = org + y * FAST_WPITCH + x;
+                    const int v = p[0];
+                    int r[16];
 #pragma unroll
-                for (int k = 0; k < 16; ++k) e[k] = sgn * (int)FAST_RING(p, FAST_WPITCH, k) + off;
-                const int M = fast_arc_minmax(e);
-                corner = M > t_lo;
-                if (corner) sc[(y + 1) * FAST_SPITCH + x + 1] = (uint8_t)(M - 1);
-            }
-            const uint32_t bal = __ballot_sync(0xffffffffu, corner);
-            if (corner) list2[n2 + __popc(bal & below)] = (uint16_t)ent;
-            n2 += __popc(bal);
-        }
-        __syncthreads();
-
-        /* ---- stage 3: strict 3x3 NMS inside the domain ---- */
-        int n3 = 0, n3_hi = 0;
-        for (int i = lane; i - lane < n2; i += 32) {
-            bool keep = false;
-            uint32_t rec = 0;
-            if (i < n2) {
-                const uint32_t ent = list2[i];
-                const int x = ent & 63, y = (ent >> 6) & 63;
-                const uint8_t *q = sc + (y + 1) * FAST_SPITCH + x + 1;
-                const int c = q[0];
-                keep = c > q[-1] && c > q[1] && c > q[-FAST_SPITCH - 1] && c > q[-FAST_SPITCH] &&
-                       c > q[-FAST_SPITCH + 1] && c > q[FAST_SPITCH - 1] && c > q[FAST_SPITCH] &&
-                       c > q[FAST_SPITCH + 1];
-                rec = (ent & 0xfffu) | ((uint32_t)c << 12);
-            }
-            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-            n3_hi += __popc(__ballot_sync(0xffffffffu, keep && (int)(rec >> 12) >= ini));
-            if (keep) list3[n3 + __popc(bal & below)] = rec;
-            n3 += __popc(bal);
-        }
-        if (lane == 0) wcnt[warp] = make_int2(n3, n3_hi);
-        __syncthreads();
-
-        /* ---- emit: K(ini) if non-empty else K(min).  (With ini < min every survivor already is
-         * >= ini: a cell empty at ini stays empty, its second pass being a subset.) ---- */
-        int any_hi = 0;
+                    for (int k = 0; k < 16; ++k) r[k] = (int)FAST_RING(p, FAST_WPITCH, k);
+                    int M = 0;
+                    {   /* contrast on the flagged side (bright if flagged bright) */
+                        const bool bright = (ent & (1u << 12)) != 0;
+                        const int sgn = bright ? -1 : 1, off = bright ? v : -v;
+                        int e[16];
 #pragma unroll
-        for (int w = 0; w < FAST_NW; ++w) any_hi += wcnt[w].y;
-        const int t_emit = any_hi ? ini : mn;
-        const int n_emit = any_hi ? n3_hi : n3;
-        if (n_emit > 0) {
+                        for (int k = 0; k < 16; ++k) e[k] = sgn * r[k] + off;
+                        M = fast_arc_minmax(e);
+                    }
+                    if (M <= t && (ent >> 12) == 3u) { /* flagged on both sides (rare): try dark */
+                        int e[16];
+#pragma unroll
+                        for (int k = 0; k < 16; ++k) e[k] = r[k] - v;
+                        M = fast_arc_minmax(e);
+                    }
+                    corner = M > t;
+                    if (corner) sc[(y + 1) * FAST_SPITCH + x + 1] = (uint8_t)(M - 1);
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, corner);
+                if (corner) list2[n2 + __popc(bal & below)] = (uint16_t)ent;
+                n2 += __popc(bal);
+            }
+            __syncthreads();
+
+            /* ---- stage 3: strict 3x3 NMS inside the domain ---- */
+            n3 = 0;
+            for (int i = lane; i - lane < n2; i += 32) {
+                bool keep = false;
+                uint32_t rec = 0;
+                if (i < n2) {
+                    const uint32_t ent = list2[i];
+                    const int x = ent & 63, y = (ent >> 6) & 63;
+                    const uint8_t *q = sc + (y + 1) * FAST_SPITCH + x + 1;
+                    const int c = q[0];
+                    keep = c > q[-1] && c > q[1] && c > q[-FAST_SPITCH - 1] && c > q[-FAST_SPITCH] &&
+                           c > q[-FAST_SPITCH + 1] && c > q[FAST_SPITCH - 1] && c > q[FAST_SPITCH] &&
+                           c > q[FAST_SPITCH + 1];
+                    rec = (ent & 0xfffu) | ((uint32_t)c << 12);
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                if (keep) list3[n3 + __popc(bal & below)] = rec;
+                n3 += __popc(bal);
+            }
+            if (lane == 0) wcnt[pass * FAST_NW + warp] = n3;
+            __syncthreads();
+            cell_total = 0;
+#pragma unroll
+            for (int w = 0; w < FAST_NW; ++w) cell_total += wcnt[pass * FAST_NW + w];
+            if (cell_total > 0) break;
+        }
+
+        /* ---- emit this warp's survivors; one global atomicAdd per warp ---- */
+        if (cell_total > 0 && n3 > 0) {
             int base = 0;
-            if (lane == 0) base = atomicAdd(ncand + frame * BORB_MAXL + cell.level, n_emit);
+            if (lane == 0) base = atomicAdd(ncand + frame * BORB_MAXL + cell.level, n3);
             base = __shfl_sync(0xffffffffu, base, 0);
             uint32_t *oxy = cand_xy + (size_t)frame * (size_t)plan->cand_total + L.cand_off;
             uint32_t *osc = cand_score + (size_t)frame * (size_t)plan->cand_total + L.cand_off;
-            for (int i = lane; i - lane < n3; i += 32) {
-                const uint32_t rec = i < n3 ? list3[i] : 0u;
-                const int c = (int)(rec >> 12);
-                const bool out = i < n3 && c >= t_emit;
-                const uint32_t bal = __ballot_sync(0xffffffffu, out);
-                const int slot = base + __popc(bal & below);
-                if (out && slot < L.cand_cap) {
+            for (int i = lane; i < n3; i += 32) {
+                const uint32_t rec = list3[i];
+                const int slot = base + i;
+                if (slot < L.cand_cap) {
                     const int x = rec & 63, y = (rec >> 6) & 63;
                     /* window-relative (x+3, y+3) shifted by the cell origin: coords relative
                      * to (minBorderX, minBorderY), src/ORBextractor.cc:1087-1088 */
                     oxy[slot] = (uint32_t)(x + 3 + cell.sx) | ((uint32_t)(y + 3 + cell.sy) << 16);
-                    osc[slot] = (uint32_t)c;
+                    osc[slot] = rec >> 12;
                 }
-                base += __popc(bal);
             }
         }
         /* ---- restore the all-zero score plane for the next cell (own corners only) ---- */
