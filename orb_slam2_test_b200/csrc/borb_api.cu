@@ -289,6 +289,10 @@ int build_plan(borb_extractor *h, int cols, int rows)
                 c.wh = (short)((int)max_y - (int)ini_y);
                 c.sx = (short)(j * L.w_cell); c.sy = (short)(i * L.h_cell);
                 if (c.ww < 7 || c.wh < 7) continue; /* cv::FAST finds nothing in such a window */
+                c.wpr = ((c.x0 & 3) + c.ww + 3) >> 2;
+                c.dmagic = fast_div_magic(c.ww - 6);
+                c.wmagic = fast_div_magic(c.wpr);
+                c.pad2 = 0;
                 cells.push_back(c);
                 P.fast_max_wh = std::max(P.fast_max_wh, (int)c.wh);
                 P.fast_max_pix = std::max(P.fast_max_pix, (c.ww - 6) * (c.wh - 6));
@@ -397,9 +401,17 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         }
     }
     STAGE(1);
-    {   /* K2: persistent CTAs, a multiple of the SM count */
-        const int per_sm = std::max(1, std::min(16, (200 * 1024) / std::max(h->fast_smem, 1)));
-        const int grid = std::min(P.n_cells * n, h->n_sm * per_sm);
+    {   /* K2: persistent CTAs, a multiple of the SM count, walking (cell, frame) with strides
+         * (gridDim.x, gridDim.y); small jobs get one CTA per cell */
+        int per_sm = std::max(1, std::min(12, (200 * 1024) / std::max(h->fast_smem, 1))); /* measured best: 12 */
+        if (const char *e = getenv("BORB_FAST_CTAS_PER_SM")) per_sm = std::max(1, atoi(e)); /* tuning knob */
+        const int ctas = h->n_sm * per_sm;
+        dim3 grid(P.n_cells, n);
+        if ((long long)P.n_cells * n > 2LL * ctas) {
+            grid.y = std::min(n, 64);
+            if (const char *e = getenv("BORB_FAST_GRID_Y")) grid.y = std::max(1, std::min(n, atoi(e)));
+            grid.x = std::min(P.n_cells, std::max(1, ctas / (int)grid.y));
+        }
         k_fast_cells<<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, h->d_pyr, h->d_cand_xy,
                                                           h->d_cand_score, h->d_ncand);
     }

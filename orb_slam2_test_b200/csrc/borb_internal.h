@@ -54,6 +54,11 @@ struct BorbCell { /* one FAST window, reference :1000-1064 */
     short x0, y0;     /* window origin in level pixels */
     short ww, wh;     /* window size */
     short sx, sy;     /* j*wCell, i*hCell: shift added to window-relative coords */
+    /* derived, so the kernel divides by multiply-shift: words per staged row and the magic
+     * numbers of fast_div() for (ww-6) and wpr */
+    int wpr;
+    unsigned dmagic, wmagic;
+    int pad2;
 };
 
 struct BorbTile { /* one blur strip: BORB_BLUR_TW columns x BORB_BLUR_TH rows of a level */

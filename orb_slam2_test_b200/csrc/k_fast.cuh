@@ -133,7 +133,7 @@ __device__ __forceinline__ int fast_arc_minmax(const int *e)
  * 18 KB; the 60x60 worst case of the cell formula needs 44 KB).  chunk = pixels per warp. */
 #define FAST_NW (FAST_NT / 32)
 struct FastSmemLayout {
-    int chunk, win_off, sc_off, l1_off, l2_off, l3_off, bytes;
+    int chunk, win_off, win_bytes, sc_off, l1_off, l2_off, l3_off, bytes;
 };
 __host__ __device__ __forceinline__ int fast_chunk(int npix) { return ((npix + FAST_NT - 1) / FAST_NT) * 32; }
 __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix)
@@ -141,7 +141,7 @@ __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, 
     FastSmemLayout o;
     o.chunk = fast_chunk(max_pix);
     int b = 64; /* per-warp counts */
-    o.win_off = b; b += max_wh * FAST_WPITCH;
+    o.win_off = b; o.win_bytes = max_wh * FAST_WPITCH; b += 2 * o.win_bytes; /* double buffered */
     o.sc_off = b;  b += ((max_wh - 4) * FAST_SPITCH + 15) & ~15;
     o.l1_off = b;  b += FAST_NW * 2 * o.chunk * 2;        /* u16 pixel | side<<12, one slot per side */
     o.l2_off = b;  b += FAST_NW * o.chunk * 2;            /* u16 corners */
@@ -150,7 +150,28 @@ __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, 
     return o;
 }
 
-__global__ void __launch_bounds__(FAST_NT)
+/* asynchronous copy of one cell's window into shared memory (cp.async, 4 bytes per request: the
+ * window origin is only word-aligned) */
+__device__ __forceinline__ void fast_stage_window(const BorbPlan *__restrict__ plan, const BorbCell &cell, int frame,
+                                                  const uint8_t *__restrict__ pyr, uint8_t *win, int tid)
+{
+    const BorbLevel &L = plan->lv[cell.level];
+    const uint8_t *img = pyr + (size_t)frame * (size_t)plan->pyr_bytes + L.off +
+                         (size_t)(BORB_EDGE + cell.y0) * L.pitch + BORB_XPAD + (cell.x0 & ~3);
+    const int wpr = cell.wpr, nw = wpr * cell.wh;
+    const uint32_t smem = (uint32_t)__cvta_generic_to_shared(win);
+    for (int i = tid; i < nw; i += FAST_NT) {
+        const int y = fast_div(i, cell.wmagic), w = i - y * wpr;
+        const uint8_t *src = img + (size_t)y * L.pitch + 4 * w;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem + y * FAST_WPITCH + 4 * w), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+#ifndef FAST_MIN_CTAS
+#define FAST_MIN_CTAS 8
+#endif
+__global__ void __launch_bounds__(FAST_NT, FAST_MIN_CTAS)
 k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cells, int n_frames,
              const uint8_t *__restrict__ pyr, uint32_t *__restrict__ cand_xy,
              uint32_t *__restrict__ cand_score, int *__restrict__ ncand)
@@ -160,45 +181,45 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t below = (1u << lane) - 1u;
     int *wcnt = reinterpret_cast<int *>(fast_raw); /* [pass][warp]: NMS survivors */
-    uint8_t *win = fast_raw + lay.win_off;
     uint8_t *sc = fast_raw + lay.sc_off;
     uint16_t *list1 = reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off) + warp * 2 * lay.chunk;
     uint16_t *list2 = reinterpret_cast<uint16_t *>(fast_raw + lay.l2_off) + warp * lay.chunk;
     uint32_t *list3 = reinterpret_cast<uint32_t *>(fast_raw + lay.l3_off) + warp * (lay.chunk / 2 + 32);
     const int n_cells = plan->n_cells;
-    const int total = n_cells * n_frames;
     const int ini = plan->ini_th, mn = plan->min_th;
 
     for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(sc)[i] = 0u;
 
-    for (int work = blockIdx.x; work < total; work += gridDim.x) {
-        const int frame = work / n_cells;
-        const BorbCell cell = cells[work - frame * n_cells];
-        const BorbLevel &L = plan->lv[cell.level];
-        const uint8_t *img = pyr + (size_t)frame * (size_t)plan->pyr_bytes + L.off +
-                             (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
-        const int ww = cell.ww, wh = cell.wh;
-        const int dw = ww - 6, dh = wh - 6; /* detection domain */
-        const int npix = dw * dh;
-        const uint32_t dmagic = fast_div_magic(dw);
-
-        /* ---- stage 0: window -> smem, whole aligned words (level rows are 32-B aligned) ---- */
-        const int ax0 = cell.x0 & ~3, xoff = cell.x0 - ax0;
-        {
-            const int wpr = (xoff + ww + 3) >> 2; /* words per row, <= 18 */
-            const uint32_t wmagic = fast_div_magic(wpr);
-            const int nw = wpr * wh;
-            for (int i = tid; i < nw; i += FAST_NT) {
-                const int y = fast_div(i, wmagic), w = i - y * wpr;
-                const uint32_t v = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)(cell.y0 + y) * L.pitch + ax0) + w);
-                reinterpret_cast<uint32_t *>(win + y * FAST_WPITCH)[w] = v;
-            }
-        }
+    /* persistent walk over (frame, cell): cells strided by gridDim.x, frames by gridDim.y; the
+     * window of the NEXT item is copied into the other buffer while this one is processed */
+    int frame = blockIdx.y, ci = blockIdx.x, buf = 0;
+    bool have = frame < n_frames && ci < n_cells;
+    BorbCell cell;
+    if (have) {
+        cell = cells[ci];
+        fast_stage_window(plan, cell, frame, pyr, fast_raw + lay.win_off, tid);
+    }
+    while (have) {
+        int nci = ci + gridDim.x, nframe = frame;
+        if (nci >= n_cells) { nci = blockIdx.x; nframe += gridDim.y; }
+        const bool nhave = nframe < n_frames;
+        uint8_t *win = fast_raw + lay.win_off + buf * lay.win_bytes;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
+        BorbCell ncell;
+        if (nhave) {
+            ncell = cells[nci];
+            fast_stage_window(plan, ncell, nframe, pyr, fast_raw + lay.win_off + (buf ^ 1) * lay.win_bytes, tid);
+        }
+        const BorbLevel &L = plan->lv[cell.level];
+        const int xoff = cell.x0 & 3;
+        const int dw = cell.ww - 6, dh = cell.wh - 6; /* detection domain */
+        const int npix = dw * dh;
+        const uint32_t dmagic = cell.dmagic;
 
         const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
-        const int chunk = fast_chunk(npix);
-        const int i_end = min((warp + 1) * chunk, npix);
+        /* 32-pixel groups are dealt round-robin to the 4 warps, so every warp samples the whole
+         * cell and the per-warp work stays balanced when corners cluster */
         int n2 = 0, n3 = 0, cell_total = 0;
         /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
          * where the first found nothing; K(ini) needs nothing below ini: a corner's score is at
@@ -211,10 +232,19 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
 
             /* ---- stage 1: compass pre-test on this warp's pixels ---- */
             int n1 = 0;
-            for (int i = warp * chunk + lane; i - lane < i_end; i += 32) {
+#ifdef FAST_NO_INTERLEAVE
+            const int chunk_ = fast_chunk(npix), i_end_ = min((warp + 1) * chunk_, npix);
+            for (int i = warp * chunk_ + lane; i - lane < i_end_; i += 32) {
+#else
+            for (int i = warp * 32 + lane; i - lane < npix; i += FAST_NT) {
+#endif
                 uint32_t side = 0;
                 uint32_t pix = 0;
-                if (i < i_end) {
+#ifdef FAST_NO_INTERLEAVE
+                if (i < i_end_) {
+#else
+                if (i < npix) {
+#endif
                     const int y = fast_div(i, dmagic), x = i - y * dw;
                     pix = (uint32_t)(y * 64 + x);
                     const uint8_t *p = org + y * FAST_WPITCH + x;
@@ -319,7 +349,9 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
             const uint32_t ent = list2[i];
             sc[(((ent >> 6) & 63) + 1) * FAST_SPITCH + (ent & 63) + 1] = 0;
         }
-        /* the next cell's first write to the score plane / wcnt comes after its stage-0 barrier */
+        /* the next cell's first write to the score plane / wcnt comes after its top barrier */
+        have = nhave;
+        if (nhave) { cell = ncell; ci = nci; frame = nframe; buf ^= 1; }
     }
 }
 

@@ -9,12 +9,14 @@ GPU -- there is no CPU path, and importing this on a machine without the built l
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "liborb_b200.so"
+# BORB_LIB: alternative build of the same library (kernel A/B experiments); default = in-tree build
+LIB_PATH = Path(os.environ["BORB_LIB"]) if os.environ.get("BORB_LIB") else _HERE / "liborb_b200.so"
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
