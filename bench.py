@@ -194,15 +194,48 @@ def bench_config(frames_per_step: int) -> dict:
 
 # ----------------------------------------------------------------------------- GPU arm
 
+STAGE_KERNEL = {"pyramid": "k_pyr_level0 + 7 x k_pyr_resize", "fast": "k_fast_cells", "quadtree": "k_quadtree",
+                "blur": "k_blur_strips", "describe": "k_orient_describe"}
+
+
+def stage_algorithmic_bytes(n_kp: float, n_cand: float) -> dict:
+    """Algorithmic bytes per FRAME of each stage: every stage reads its input
+    and writes its output once."""
+    lp = level_pixels()
+    return {
+        "pyramid": COLS * ROWS + lp,            # read the frame, write every level once
+        "fast": lp + 8 * n_cand,                # read every level once, write candidates (xy + score)
+        "quadtree": 12 * n_cand + 8 * n_kp,     # read candidates (xy, score, node), write survivors
+        "blur": 2 * lp,                         # read + write every level
+        "describe": (60 + 749 + 1369) * n_kp,   # per keypoint: 749-px disc + 37x37 blurred patch in, 60 B out
+    }
+
+
+def ncu_traffic(kernel: str, frames: int):
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture, if it was taken at
+    this launch shape (profiles/r1_traffic.json, written by tools/ncu_traffic.py)."""
+    p = ROOT / "profiles" / "r1_traffic.json"
+    try:
+        t = json.loads(p.read_text())
+        e = t[kernel]
+        return float(e["dram_bytes"]) if int(e["frames_per_launch"]) == frames else None
+    except Exception:
+        return None
+
+
 def run_ours(args, rank, world, local):
     import torch
     from orb_slam2_test_b200 import ORBextractor, synth
     from orb_slam2_test_b200.extractor import pinned_empty
+    from orb_slam2_test_b200.sequence import shard_indices
 
     torch.cuda.set_device(local)
     F = args.frames_per_step
-    # this rank's shard of the synthetic sequence (frames are a pure function of their index)
-    uniq = synth.make_sequence((ROWS, COLS), seed=7, start=rank * UNIQUE, count=UNIQUE)
+    W = max(args.warmup, 3)
+    # this rank's shard of the synthetic sequence: frame f belongs to rank f mod world (frames are a
+    # pure function of their index); a step's batch cycles through the shard's first UNIQUE frames
+    mine = list(shard_indices(UNIQUE * world, rank, world))
+    uniq = np.stack([synth.make_frame((ROWS, COLS), seed=7, frame=f) for f in mine])
     batch = np.ascontiguousarray(uniq[np.arange(F) % UNIQUE])
     dev = torch.from_numpy(batch).cuda(local)
     torch.cuda.synchronize()
@@ -210,29 +243,42 @@ def run_ours(args, rank, world, local):
     ext = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=F,
                        want_pyramid=False)
     launches_per_call = ext.launches_per_call()
+    # stage events are recorded INSIDE the timed calls (event-record nodes of the captured graph)
+    ext.set_stage_timing(True)
 
     # ---- value: device-resident inputs, CUDA events on the library's stream ----
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(W):
         ext.extract_device(dev.data_ptr(), F, COLS, ROWS)
     ext.sync()
     sampler = ClockSampler(local)
     barrier(world)
     sampler.start()
     ext.sync()
+    stage_sum = {k: 0.0 for k in ext.STAGES}
     ext.timer_start()
     for _ in range(args.steps):
         ext.extract_device(dev.data_ptr(), F, COLS, ROWS)
     ext.timer_stop()
     ext.sync()
     ms = ext.timer_ms()
+    last_stage = ext.last_stage_ms()  # of the last timed call
     clocks = sampler.stop()
     barrier(world)
     ms_max = all_max(ms, world)
     value = world * F * args.steps / (ms_max / 1e3)
 
+    # per-stage averages over K more calls of the same graph (each read back right after its call)
+    for _ in range(args.steps):
+        ext.extract_device(dev.data_ptr(), F, COLS, ROWS)
+        st1 = ext.last_stage_ms()
+        for k in stage_sum:
+            stage_sum[k] += st1[k]
+    st = {k: v / args.steps for k, v in stage_sum.items()}
+
     # parity spot check of what was just timed (frame 0 of the batch) + mean keypoint count
     res = ext.fetch()
     n_kp = float(np.mean([len(k) for k, _ in res[:UNIQUE]]))
+    n_cand = float(np.mean([sum(len(ext.debug_candidates(f, l)[0]) for l in range(NLEVELS)) for f in range(min(4, F))]))
     parity = "skipped"
     if rank == 0:
         try:
@@ -243,15 +289,13 @@ def run_ours(args, rank, world, local):
         except Exception as e:  # the checker is optional here; tests/ are the parity gate
             parity = f"unavailable ({type(e).__name__})"
 
-    # ---- per-stage device times (same batch, un-graphed, event between kernels) ----
-    ext.stage_times(dev.data_ptr(), F, COLS, ROWS)
-    st = ext.stage_times(dev.data_ptr(), F, COLS, ROWS)
-
     if args.quick:
         if rank == 0:
             print(json.dumps({"quick": True, "value": value, "ms_per_step": ms_max / args.steps, "stage_ms": st,
-                              "parity_check": parity, "keypoints_per_frame": n_kp}), flush=True)
+                              "parity_check": parity, "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand}),
+                  flush=True)
         return
+    ext.set_stage_timing(False)
 
     # ---- e2e: host-facing C ABI, pinned host buffers, H2D + D2H inside the timed region ----
     sub = min(64, F)
@@ -281,7 +325,7 @@ def run_ours(args, rank, world, local):
             exts[k].wait()
             kp_bytes += sum(exts[k].count(f) for f in range(sub)) * 60
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(W):
         e2e_step()
     kp_bytes = 0
     barrier(world)
@@ -294,7 +338,6 @@ def run_ours(args, rank, world, local):
     barrier(world)
     e2e_ms_max = all_max(e2e_ms, world)
     e2e_value = world * n_sub * sub * args.steps / (e2e_ms_max / 1e3)
-    kp_total_cap = None
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
@@ -302,7 +345,6 @@ def run_ours(args, rank, world, local):
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
         for want_pyr, name in ((False, "p50_us"), (True, "p50_us_with_pyramid")):
-            one.want_pyramid = want_pyr
             for _ in range(20):
                 one._lib.borb_extract_host(one._h, img.ctypes.data, 1, COLS, ROWS, COLS, 0, 1 if want_pyr else 0)
             ts = []
@@ -319,22 +361,33 @@ def run_ours(args, rank, world, local):
             one.sync()
             ks.append(one.last_device_ms() * 1e3)
         lat["kernels_only_p50_us"] = float(np.percentile(ks, 50))
+        # BASELINE config 4: a stereo pair = two extractor instances driven concurrently from two
+        # host threads on two streams, as src/Frame.cc:110-113 does
+        two = [one, ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=True)]
+        imgs = [img, uniq[1 % len(uniq)].copy()]
+
+        def eye(i):
+            two[i]._lib.borb_extract_host(two[i]._h, imgs[i].ctypes.data, 1, COLS, ROWS, COLS, 0, 1)
+
+        ts = []
+        for it in range(220):
+            t1 = time.perf_counter()
+            th = threading.Thread(target=eye, args=(1,))
+            th.start()
+            eye(0)
+            th.join()
+            if it >= 20:
+                ts.append((time.perf_counter() - t1) * 1e6)
+        lat["stereo_pair_p50_us_with_pyramids"] = float(np.percentile(ts, 50))
 
     if rank != 0:
         return
     peak, peak_src = measured_peak()
-    # algorithmic bytes per frame of each stage
-    lp = level_pixels()
-    stage_bytes = {
-        "pyramid": COLS * ROWS + lp,          # read the frame, write every level once
-        "fast": lp + 8 * 11000,               # read every level once, write ~11 k candidates x 8 B
-        "quadtree": 12 * 11000 + 8 * n_kp,    # read candidates (xy, score, node), write survivors
-        "blur": 2 * lp,                       # read + write every level
-        "describe": 60 * n_kp,                # the output records (patch reads are L2 hits)
-    }
+    stage_bytes = stage_algorithmic_bytes(n_kp, n_cand)
     dom = max(st, key=st.get)
     dom_s = st[dom] / 1e3
     achieved = stage_bytes[dom] * F / dom_s / 1e9
+    step_ms = ms_max / args.steps
     cores = len(os.sched_getaffinity(0))
     cpu = None
     if world == 1:
@@ -345,7 +398,7 @@ def run_ours(args, rank, world, local):
                "single_core_frames_per_s": r1["frames_per_s"]}
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+        "warmup": W, "ms_per_step": step_ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": bench_config(F),
         "clocks": clocks,
@@ -354,14 +407,19 @@ def run_ours(args, rank, world, local):
                 "d2h_bytes_per_step": int(kp_bytes / max(args.steps, 1)),
                 "how": f"{depth} handles x {sub}-frame batches in flight, pinned host buffers, wall clock"},
         "gpu_launches": args.steps * launches_per_call,
-        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "stage_ms_per_launch": st,
+        "roofline": {"bound": "hbm", "kernel": STAGE_KERNEL[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": ncu_traffic(STAGE_KERNEL[dom], F), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": stage_bytes[dom] * F,
+                     "kernel_ms_per_launch": st[dom], "kernel_share_of_step": st[dom] / step_ms,
+                     "how": "CUDA events recorded between the stages inside the timed graph launches "
+                            "(borb_set_stage_timing), averaged over the timed calls",
+                     "stage_ms_per_launch": st, "stage_ms_last_timed_call": last_stage,
+                     "stage_GBps": {k: stage_bytes[k] * F / (st[k] / 1e3) / 1e9 for k in st},
                      "path_achieved": algorithmic_bytes(n_kp) * value / world / 1e9,
                      "path_frac": algorithmic_bytes(n_kp) * value / world / 1e9 / peak},
         "cpu_baseline": cpu,
         "latency": lat,
-        "keypoints_per_frame": n_kp,
+        "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,
     }
     print(json.dumps(line), flush=True)

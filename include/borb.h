@@ -125,6 +125,12 @@ float borb_timer_ms(borb_extractor *h);
 int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n_frames, int cols, int rows,
                      size_t step, size_t frame_stride, float *ms);
 
+/* Per-stage device times of REAL calls: with stage timing on, every extract call records a CUDA
+ * event between its stages (event-record nodes inside the captured graph), and
+ * borb_last_stage_ms() returns those of the most recent call (ms[0..4] as above). */
+int borb_set_stage_timing(borb_extractor *h, int on);
+int borb_last_stage_ms(borb_extractor *h, float *ms);
+
 /* -- stage taps for parity tests (device -> caller buffers; not part of the hot path) -------- */
 /* FAST candidates of (frame, level) before distribution, coords relative to (16,16);
  * unordered.  Returns count via *n (may exceed cap; only cap entries are written). */

@@ -102,6 +102,7 @@ struct borb_extractor {
     bool pending = false;                           /* submitted, not yet waited for */
     unsigned pending_flags = 0;
     bool use_graph = true;
+    bool stage_timing = false;                      /* record stage events inside every call */
 
     /* geometry-dependent state */
     bool have_plan = false;
@@ -385,7 +386,13 @@ namespace {
 int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t step, size_t stride,
                     bool stage_events = false)
 {
-#define STAGE(i) do { if (stage_events) CU(cudaEventRecord(h->evs[i], st)); } while (0)
+    stage_events = stage_events || h->stage_timing; /* inside a capture these become event-record nodes */
+    cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
+    CU(cudaStreamIsCapturing(h->stream, &cap_status));
+    const bool capturing = cap_status == cudaStreamCaptureStatusActive;
+/* cudaEventRecordExternal: inside a stream capture this becomes an event-record node whose event
+ * can be timed from outside the graph (a plainly captured event cannot) */
+#define STAGE(i) do { if (stage_events) CU(cudaEventRecordWithFlags(h->evs[i], st, capturing ? cudaEventRecordExternal : cudaEventRecordDefault)); } while (0)
     const BorbPlan &P = h->plan;
     cudaStream_t st = h->stream;
     CU(cudaMemsetAsync(h->d_ncand, 0, (size_t)n * BORB_MAXL * 4, st));
@@ -765,6 +772,29 @@ float borb_last_device_ms(const borb_extractor *h)
         return -1.f;
     }
     return ms;
+}
+
+int borb_set_stage_timing(borb_extractor *h, int on)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    if ((on != 0) != h->stage_timing) { /* graphs captured under the other setting are stale */
+        for (GraphEntry &g : h->graphs) cudaGraphExecDestroy(g.exec);
+        h->graphs.clear();
+    }
+    h->stage_timing = on != 0;
+    return BORB_OK;
+}
+
+int borb_last_stage_ms(borb_extractor *h, float *ms)
+{
+    if (!h || !ms) return fail(BORB_ERR_ARG, "null");
+    if (!h->stage_timing) return fail(BORB_ERR_STATE, "stage timing is off");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < 5; ++i) CU(cudaEventElapsedTime(&ms[i], h->evs[i], h->evs[i + 1]));
+    return BORB_OK;
 }
 
 int borb_launches_per_call(const borb_extractor *h) { return h ? h->nlevels + 4 : 0; }
