@@ -109,6 +109,7 @@ struct borb_extractor {
     BorbPlan plan;
     int qt_M = 0;
     int fast_smem = 0, n_sm = 148;
+    int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
     BorbPlan *d_plan = nullptr;
@@ -258,6 +259,23 @@ int build_plan(borb_extractor *h, int cols, int rows)
             L.yb_off = (int)tab_s.size(); tab_s.resize(tab_s.size() + 2 * L.h);
             resize_axis(S.w, L.w, true, &tab_i[L.xofs_off], &tab_s[L.xa_off]);
             resize_axis(S.h, L.h, false, &tab_i[L.yofs_off], &tab_s[L.yb_off]);
+            /* K1 stages, per 128 x 16 output tile, the source span its taps reach: bound both spans
+             * over all tile positions (reflected frame pixels only re-use interior taps) */
+            int span_x = 0, span_y = 0;
+            for (int x0 = 0; x0 < L.w; ++x0) {
+                const int x1 = std::min(x0 + PYR_TW - 1, L.w - 1);
+                const int lo = tab_i[L.xofs_off + x0] & ~15, hi = std::min(tab_i[L.xofs_off + x1] + 1, S.w - 1);
+                span_x = std::max(span_x, hi - lo + 1);
+            }
+            for (int y0 = 0; y0 < L.h; ++y0) {
+                const int y1 = std::min(y0 + PYR_TH - 1, L.h - 1);
+                const int lo = std::max(tab_i[L.yofs_off + y0], 0), hi = std::min(tab_i[L.yofs_off + y1] + 1, S.h - 1);
+                span_y = std::max(span_y, hi - lo + 1);
+            }
+            h->pyr_sp[l] = (int)align_up(span_x + 16, 16);
+            h->pyr_srows[l] = span_y + 1;
+            if ((long long)h->pyr_sp[l] * h->pyr_srows[l] > 160 * 1024)
+                return fail(BORB_ERR_GEOMETRY, "scale factor too large for the pyramid tile at level %d", l);
         }
         /* FAST cell grid, src/ORBextractor.cc:974-1064 (float arithmetic as written there) */
         const int min_b = BORB_FAST_MARGIN;
@@ -399,12 +417,14 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     STAGE(0);
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
-        const int n0 = pyr_words_per_row(L0.w) * L0.prows;
-        k_pyr_level0<<<dim3((n0 + PYR_NT - 1) / PYR_NT, 1, n), PYR_NT, 0, st>>>(h->d_plan, dev_img, step, stride, h->d_pyr);
+        const int units = L0.pitch / 16;
+        k_pyr_level0<<<dim3((units + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->d_plan, dev_img, step,
+                                                                                          stride, h->d_pyr);
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
-            const int nl = pyr_words_per_row(L.w) * ((L.prows + PYR_RS - 1) / PYR_RS);
-            k_pyr_resize<<<dim3((nl + PYR_NT - 1) / PYR_NT, 1, n), PYR_NT, 0, st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s, h->d_pyr);
+            const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);
+            k_pyr_resize<<<g, PYR_NT, (size_t)h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s,
+                                                                                   h->d_pyr, h->pyr_sp[l], h->pyr_srows[l]);
         }
     }
     STAGE(1);

@@ -10,10 +10,11 @@
  * The tap tables depend only on (cols, rows) and are built on the host once per geometry.
  *
  * Frame pixels are computed at their reflected interior coordinate (no second pass, no
- * intra-level synchronisation).  v2: a thread owns 4 adjacent columns (one aligned 32-bit word of
- * the padded row) over a strip of PYR_RS rows: its horizontal taps live in registers for the
- * whole strip, the row taps are warp-uniform, and the horizontal sums of a source row are reused
- * when the next output row needs the same source row (5 times out of 6 at scale 1.2).
+ * intra-level synchronisation).  v3: a CTA owns a 128 x 16 tile of the padded level and stages the
+ * source rows / columns its taps reach in shared memory (16-byte coalesced loads, 32-bit shared
+ * addressing for the byte gathers); a lane owns 4 adjacent columns (one aligned 32-bit word) with
+ * its horizontal taps in registers, a warp 4 consecutive rows, and the horizontal sums of a source
+ * row are reused when the next output row needs the same source row (5 times out of 6 at 1.2).
  */
 #ifndef K_PYRAMID_CUH
 #define K_PYRAMID_CUH
@@ -21,8 +22,10 @@
 #include "borb_internal.h"
 
 #define PYR_NT 128
-#define PYR_RS 8       /* output rows per thread */
+#define PYR_TH 16      /* padded output rows per CTA (4 per warp); measured best of 16/32/64 */
+#define PYR_TW 128     /* padded output columns per CTA (4 per lane) */
 #define PYR_LPAD 20    /* columns computed left of the image: 19-px frame rounded up to a word */
+#define PYR_SP_MAX 320 /* staged source row pitch: bytes; scale factors up to ~2.3 */
 
 __device__ __forceinline__ int reflect101(int i, int n)
 {
@@ -34,66 +37,68 @@ __device__ __forceinline__ int reflect101(int i, int n)
 
 __host__ __device__ __forceinline__ int pyr_words_per_row(int w) { return (w + BORB_EDGE + PYR_LPAD + 3) >> 2; }
 
-/* level 0: copy of the input with the frame (src/ORBextractor.cc:1436-1439); one word per thread */
+/* level 0: copy of the input with the frame (src/ORBextractor.cc:1436-1439).  A thread writes 16
+ * bytes (one aligned uint4) of a padded row; interior units read their 16 contiguous source
+ * bytes, at whatever alignment the input's row step gives them, as 5 aligned words + funnel
+ * shifts.  Grid: (units of 16 columns / 32, padded rows / 4, frames), block (32, 4). */
 __global__ void __launch_bounds__(PYR_NT)
 k_pyr_level0(const BorbPlan *__restrict__ plan, const uint8_t *__restrict__ img, size_t step,
              size_t frame_stride, uint8_t *__restrict__ pyr)
 {
     const BorbLevel &L = plan->lv[0];
-    const int wpr = pyr_words_per_row(L.w);
-    const int idx = blockIdx.x * PYR_NT + threadIdx.x;
-    const int r = idx / wpr;                      /* padded row */
-    if (r >= L.prows) return;
-    const int c = (idx - r * wpr) * 4 - PYR_LPAD; /* first of 4 level columns */
+    const int r = blockIdx.y * 4 + threadIdx.y;           /* padded row */
+    const int c = (blockIdx.x * 32 + threadIdx.x) * 16 - BORB_XPAD; /* first of 16 level columns */
+    if (r >= L.prows || c + BORB_XPAD >= L.pitch) return; /* pitch is a multiple of 16: whole units */
     const uint8_t *src = img + (size_t)blockIdx.z * frame_stride;
-    uint8_t *dst = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes + L.off;
+    uint8_t *dst = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes + L.off + (size_t)r * L.pitch + BORB_XPAD + c;
     const int y = reflect101(r - BORB_EDGE, L.h);
     const uint8_t *srow = src + (size_t)y * step;
-    uint32_t v = 0;
-    if (c >= 0 && c + 3 < L.w && y + 1 < L.h) {
-        /* interior word: 4 contiguous source bytes at arbitrary alignment (the input's row step
-         * need not be a multiple of 4) from two aligned words */
+    uint32_t v[4];
+    if (c >= 0 && c + 15 < L.w && y + 1 < L.h) {
         const uintptr_t a = reinterpret_cast<uintptr_t>(srow + c);
         const uint32_t *base = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
-        const uint32_t lo = __ldg(base), hi = (a & 3) ? __ldg(base + 1) : 0u;
-        v = __funnelshift_r(lo, hi, (uint32_t)(a & 3) * 8u);
+        const uint32_t sh = (uint32_t)(a & 3) * 8u;
+        uint32_t w[5];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) w[k] = __ldg(base + k);
+        w[4] = sh ? __ldg(base + 4) : 0u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = __funnelshift_r(w[k], w[k + 1], sh);
     } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            int x = min(c + k, L.w - 1 + BORB_EDGE); /* columns beyond the frame: don't care */
-            x = reflect101(x, L.w);
-            v |= (uint32_t)__ldg(srow + x) << (8 * k);
+            v[k] = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                int x = min(max(c + 4 * k + b, -BORB_EDGE), L.w - 1 + BORB_EDGE); /* beyond the frame: don't care */
+                x = reflect101(x, L.w);
+                v[k] |= (uint32_t)__ldg(srow + x) << (8 * b);
+            }
         }
     }
-    *reinterpret_cast<uint32_t *>(dst + (size_t)r * L.pitch + BORB_XPAD + c) = v;
+    *reinterpret_cast<uint4 *>(dst) = make_uint4(v[0], v[1], v[2], v[3]);
 }
 
-__device__ __forceinline__ void pyr_hsum(const uint8_t *__restrict__ row, const int sx[4], const int sx1[4],
-                                         const int a0[4], const int a1[4], int h[4])
-{
-#pragma unroll
-    for (int k = 0; k < 4; ++k) h[k] = (int)row[sx[k]] * a0[k] + (int)row[sx1[k]] * a1[k];
-}
-
-/* level l > 0 from level l-1 */
+/* level l > 0 from level l-1.  CTA = PYR_TW x PYR_TH tile of the padded level; the source rows and
+ * columns the tile's taps reach are staged in shared memory with 16-byte loads, then a warp
+ * produces 4 consecutive rows, a lane 4 adjacent columns of each (one aligned 32-bit store).
+ * Grid: (ceil(4*wpr / PYR_TW), ceil(prows / PYR_TH), frames). */
 __global__ void __launch_bounds__(PYR_NT)
 k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ tab_i,
-             const short *__restrict__ tab_s, uint8_t *__restrict__ pyr)
+             const short *__restrict__ tab_s, uint8_t *__restrict__ pyr, int sp /* staged pitch */, int srows)
 {
+    extern __shared__ __align__(16) unsigned char pyr_tile[];
     const BorbLevel &L = plan->lv[l];
     const BorbLevel &S = plan->lv[l - 1];
-    const int wpr = pyr_words_per_row(L.w);
-    const int idx = blockIdx.x * PYR_NT + threadIdx.x;
-    const int strip = idx / wpr;
-    const int r_begin = strip * PYR_RS;
-    if (r_begin >= L.prows) return;
-    const int c = (idx - strip * wpr) * 4 - PYR_LPAD;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * PYR_TW + 4 * lane - PYR_LPAD;
+    const int r0 = blockIdx.y * PYR_TH;
     uint8_t *frame = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes;
     const uint8_t *sbase = frame + S.off + (size_t)BORB_EDGE * S.pitch + BORB_XPAD;
-    uint8_t *dst = frame + L.off + BORB_XPAD + c;
 
-    /* horizontal taps of this thread's 4 columns */
+    /* horizontal taps of this lane's 4 columns */
     int sx[4], sx1[4], a0[4], a1[4];
+    int sx_lo = 0x7fffffff, sx_hi = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         int x = min(c + k, L.w - 1 + BORB_EDGE);
@@ -102,16 +107,48 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
         sx1[k] = min(sx[k] + 1, S.w - 1);
         a0[k] = tab_s[L.xa_off + 2 * x];
         a1[k] = tab_s[L.xa_off + 2 * x + 1];
+        sx_lo = min(sx_lo, sx[k]);
+        sx_hi = max(sx_hi, sx1[k]);
     }
+    /* source window of the tile: columns (all 4 warps hold the same columns) and rows */
+    sx_lo = __reduce_min_sync(0xffffffffu, sx_lo) & ~15;
+    sx_hi = __reduce_max_sync(0xffffffffu, sx_hi);
+    int sy_lo = 0x7fffffff, sy_hi = 0;
+    for (int rr = lane; rr < PYR_TH && r0 + rr < L.prows; rr += 32) {
+        const int y = reflect101(r0 + rr - BORB_EDGE, L.h);
+        const int sy = tab_i[L.yofs_off + y];
+        sy_lo = min(sy_lo, min(max(sy, 0), S.h - 1));
+        sy_hi = max(sy_hi, min(max(sy + 1, 0), S.h - 1));
+    }
+    sy_lo = __reduce_min_sync(0xffffffffu, sy_lo);
+    sy_hi = __reduce_max_sync(0xffffffffu, sy_hi);
+    {
+        const int vpr = (sx_hi - sx_lo) / 16 + 1;             /* uint4 per staged row */
+        const int nrow = sy_hi - sy_lo + 1;
+        const int nv = vpr * nrow;                            /* host guarantees vpr*16 <= sp, nrow <= srows */
+        const uint8_t *g = sbase + (size_t)sy_lo * S.pitch + sx_lo; /* 16-B aligned: pitch, XPAD, sx_lo are */
+        for (int i = threadIdx.x; i < nv; i += PYR_NT) {
+            const int rr = i / vpr, cc = i - rr * vpr;
+            *reinterpret_cast<uint4 *>(pyr_tile + rr * sp + cc * 16) =
+                __ldg(reinterpret_cast<const uint4 *>(g + (size_t)rr * S.pitch) + cc);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { sx[k] -= sx_lo; sx1[k] -= sx_lo; }
+    __syncthreads();
+    if (c >= L.w + BORB_EDGE) return;
 
     int rowA = -1, rowB = -1;
     int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
-    const int r_end = min(r_begin + PYR_RS, L.prows);
-    for (int r = r_begin; r < r_end; ++r) {
+    uint8_t *dst = frame + L.off + BORB_XPAD + c;
+#pragma unroll
+    for (int i = 0; i < PYR_TH / 4; ++i) {
+        const int r = r0 + warp * (PYR_TH / 4) + i;
+        if (r >= L.prows) break;
         const int y = reflect101(r - BORB_EDGE, L.h);
         const int sy = tab_i[L.yofs_off + y];
         const int b0 = tab_s[L.yb_off + 2 * y], b1 = tab_s[L.yb_off + 2 * y + 1];
-        const int sy0 = min(max(sy, 0), S.h - 1), sy1 = min(max(sy + 1, 0), S.h - 1);
+        const int sy0 = min(max(sy, 0), S.h - 1) - sy_lo, sy1 = min(max(sy + 1, 0), S.h - 1) - sy_lo;
         int n0[4], n1[4];
         if (sy0 == rowB) {
 #pragma unroll
@@ -120,7 +157,9 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
 #pragma unroll
             for (int k = 0; k < 4; ++k) n0[k] = hA[k];
         } else {
-            pyr_hsum(sbase + (size_t)sy0 * S.pitch, sx, sx1, a0, a1, n0);
+            const uint8_t *row = pyr_tile + sy0 * sp;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) n0[k] = (int)row[sx[k]] * a0[k] + (int)row[sx1[k]] * a1[k];
         }
         if (sy1 == rowB) {
 #pragma unroll
@@ -129,7 +168,9 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
 #pragma unroll
             for (int k = 0; k < 4; ++k) n1[k] = hA[k];
         } else {
-            pyr_hsum(sbase + (size_t)sy1 * S.pitch, sx, sx1, a0, a1, n1);
+            const uint8_t *row = pyr_tile + sy1 * sp;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) n1[k] = (int)row[sx[k]] * a0[k] + (int)row[sx1[k]] * a1[k];
         }
         uint32_t v = 0;
 #pragma unroll
