@@ -12,8 +12,8 @@
  * Execution shape (v3).  Corner-ness is sparse and its cost is wildly uneven per pixel (a 5-load
  * compass test rejects over half of the pixels, the full test + score costs ~150 instructions), so
  * a pixel-per-thread kernel spends its time in divergent warps (v1: 17 of 32 lanes active, ALU pipe
- * 87 % busy -- profiles/r1_fast_v1_raw.csv).  This is a persistent kernel, one CTA (4 warps) per
- * cell at a time; every warp owns a contiguous quarter of the cell's pixels and runs DENSE stages
+ * 87 % busy -- profiles/r1_fast_v1_raw.csv).  This is a persistent kernel, one CTA (2 warps) per
+ * cell at a time; 32-pixel groups of the cell are dealt round-robin to the warps, each of which runs DENSE stages
  * over warp-private shared-memory lists (ballot/popc compaction, no atomics):
  *   stage 0  window -> shared memory, aligned 32-bit loads                       | barrier
  *   stage 1  own pixels: compass pre-test (two ADJACENT compass points beyond the threshold on
@@ -37,7 +37,9 @@
 
 #include "borb_internal.h"
 
-#define FAST_NT 128
+#ifndef FAST_NT
+#define FAST_NT 64 /* 2 warps per cell: measured best of 64/128/256 on B200 */
+#endif
 #define FAST_WPITCH 72 /* >= BORB_MAXCELL + 6 + 3 (alignment slack), multiple of 4 */
 #define FAST_SPITCH 64 /* >= BORB_MAXCELL + 2 */
 #define FAST_MAXPIX (BORB_MAXCELL * BORB_MAXCELL)
@@ -169,7 +171,7 @@ __device__ __forceinline__ void fast_stage_window(const BorbPlan *__restrict__ p
 }
 
 #ifndef FAST_MIN_CTAS
-#define FAST_MIN_CTAS 8
+#define FAST_MIN_CTAS 16
 #endif
 __global__ void __launch_bounds__(FAST_NT, FAST_MIN_CTAS)
 k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cells, int n_frames,
@@ -218,7 +220,7 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
         const uint32_t dmagic = cell.dmagic;
 
         const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
-        /* 32-pixel groups are dealt round-robin to the 4 warps, so every warp samples the whole
+        /* 32-pixel groups are dealt round-robin to the warps, so every warp samples the whole
          * cell and the per-warp work stays balanced when corners cluster */
         int n2 = 0, n3 = 0, cell_total = 0;
         /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
