@@ -109,6 +109,7 @@ struct borb_extractor {
     BorbPlan plan;
     int qt_M = 0;
     int fast_smem = 0, n_sm = 148;
+    int chunk = 0; /* frames per pass of the kernel chain (0 = whole call) */
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
@@ -413,18 +414,37 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
 #define STAGE(i) do { if (stage_events) CU(cudaEventRecordWithFlags(h->evs[i], st, capturing ? cudaEventRecordExternal : cudaEventRecordDefault)); } while (0)
     const BorbPlan &P = h->plan;
     cudaStream_t st = h->stream;
-    CU(cudaMemsetAsync(h->d_ncand, 0, (size_t)n * BORB_MAXL * 4, st));
+    /* Frames are independent, so a large batch runs through the chain in sub-batches of `chunk`
+     * frames: a sub-batch's pyramid, blurred levels and candidates (~4 MB per frame) then still sit
+     * in the 126 MB L2 when the next stage reads them.  BORB_CHUNK overrides (0 = whole batch). */
+    int chunk = h->chunk > 0 ? h->chunk : n;
+    if (stage_events) chunk = n; /* stage timers describe whole-batch launches */
+    const int n_total = n;
+    const uint8_t *const img_all = dev_img;
+    for (int f0 = 0; f0 < n_total; f0 += chunk) {
+    n = std::min(chunk, n_total - f0);
+    dev_img = img_all + (size_t)f0 * stride;
+    uint8_t *const d_pyr = h->d_pyr + (size_t)f0 * (size_t)P.pyr_bytes, *const d_blur = h->d_blur + (size_t)f0 * (size_t)P.pyr_bytes;
+    uint32_t *const d_cand_xy = h->d_cand_xy + (size_t)f0 * (size_t)P.cand_total;
+    uint32_t *const d_cand_score = h->d_cand_score + (size_t)f0 * (size_t)P.cand_total;
+    uint32_t *const d_cand_node = h->d_cand_node + (size_t)f0 * (size_t)P.cand_total;
+    int *const d_ncand = h->d_ncand + (size_t)f0 * BORB_MAXL, *const d_nlkp = h->d_nlkp + (size_t)f0 * BORB_MAXL;
+    int *const d_nout = h->d_nout + f0;
+    uint32_t *const d_lkp_xy = h->d_lkp_xy + (size_t)f0 * P.kp_total, *const d_lkp_score = h->d_lkp_score + (size_t)f0 * P.kp_total;
+    BorbKpRec *const d_out_kp = h->d_out_kp + (size_t)f0 * P.kp_total;
+    uint8_t *const d_out_desc = h->d_out_desc + (size_t)f0 * P.kp_total * 32;
+    CU(cudaMemsetAsync(d_ncand, 0, (size_t)n * BORB_MAXL * 4, st));
     STAGE(0);
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         const int units = L0.pitch / 16;
         k_pyr_level0<<<dim3((units + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->d_plan, dev_img, step,
-                                                                                          stride, h->d_pyr);
+                                                                                          stride, d_pyr);
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);
             k_pyr_resize<<<g, PYR_NT, (size_t)h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s,
-                                                                                   h->d_pyr, h->pyr_sp[l], h->pyr_srows[l]);
+                                                                                   d_pyr, h->pyr_sp[l], h->pyr_srows[l]);
         }
     }
     STAGE(1);
@@ -440,21 +460,23 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             if (const char *e = getenv("BORB_FAST_GRID_Y")) grid.y = std::max(1, std::min(n, atoi(e)));
             grid.x = std::min(P.n_cells, std::max(1, ctas / (int)grid.y));
         }
-        k_fast_cells<<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, h->d_pyr, h->d_cand_xy,
-                                                          h->d_cand_score, h->d_ncand);
+        k_fast_cells<<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, d_pyr, d_cand_xy,
+                                                          d_cand_score, d_ncand);
     }
     STAGE(2);
     k_quadtree<<<dim3(P.nlevels, n), QT_NT, qt_smem_bytes(h->qt_M), st>>>(
-        h->d_plan, h->qt_M, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_lkp_xy,
-        h->d_lkp_score, h->d_nlkp, h->d_err);
+        h->d_plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy,
+        d_lkp_score, d_nlkp, h->d_err);
     STAGE(3);
     k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, 0, st>>>(h->d_plan, h->d_tiles,
-                                                                                              h->d_pyr, h->d_blur);
+                                                                                              d_pyr, d_blur);
     STAGE(4);
     k_orient_describe<<<dim3((P.kp_total + DESC_NW * DESC_KPW - 1) / (DESC_NW * DESC_KPW), n), DESC_NT, 0, st>>>(
-        h->d_plan, h->d_pattern, h->d_pyr, h->d_blur, h->d_lkp_xy, h->d_lkp_score, h->d_nlkp,
-        h->d_out_kp, h->d_out_desc, h->d_nout);
+        h->d_plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
+        d_out_kp, d_out_desc, d_nout);
     STAGE(5);
+    }
+    n = n_total;
 #undef STAGE
     CU(cudaGetLastError());
     return BORB_OK;
@@ -559,6 +581,7 @@ int borb_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int 
     h->scale_factor = scale_factor;
     h->device = device; h->max_batch = max_batch;
     build_tables(h);
+    if (const char *e = getenv("BORB_CHUNK")) h->chunk = std::max(0, atoi(e));
     const char *ng = getenv("BORB_NO_GRAPH");
     h->use_graph = !(ng && ng[0] == '1');
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);

@@ -81,6 +81,8 @@ struct BorbPlan {
 };
 
 #define BORB_BLUR_TW 128 /* one warp x 4 columns */
+#ifndef BORB_BLUR_TH
 #define BORB_BLUR_TH 32
+#endif
 
 #endif

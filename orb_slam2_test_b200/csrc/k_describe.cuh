@@ -49,13 +49,20 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
     return a;
 }
 
-#define DESC_NT 256
+#ifndef DESC_NT
+#define DESC_NT 128
+#endif
 #define DESC_NW (DESC_NT / 32)
 #define DESC_PR 37  /* staged patch rows: -18 .. +18 */
 #define DESC_PW 10  /* staged words per row: covers 37 columns at any alignment */
-#define DESC_KPW 4  /* keypoint slots per warp */
+#ifndef DESC_KPW
+#define DESC_KPW 16 /* keypoint slots per warp */
+#endif
+#ifndef DESC_MINB
+#define DESC_MINB 8 /* 64 registers: the kernel is latency bound, occupancy beats the few spills (measured) */
+#endif
 
-__global__ void __launch_bounds__(DESC_NT, 3)
+__global__ void __launch_bounds__(DESC_NT, DESC_MINB)
 k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restrict__ pattern,
                   const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur,
                   const uint32_t *__restrict__ lkp_xy, const uint32_t *__restrict__ lkp_score,
