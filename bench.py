@@ -299,9 +299,9 @@ def run_ours(args, rank, world, local):
     ext.set_stage_timing(False)
 
     # ---- e2e: host-facing C ABI, pinned host buffers, H2D + D2H inside the timed region ----
-    sub = min(128, F)  # frames per submit: launches below ~128 frames lose throughput to tail effects
+    sub = min(int(os.environ.get("BENCH_E2E_SUB", "128")), F)  # frames per submit: small launches lose throughput to tails
     n_sub = max(1, F // sub)
-    depth = min(4, n_sub)
+    depth = min(int(os.environ.get("BENCH_E2E_DEPTH", "4")), n_sub)
     hosts = []
     for i in range(depth):
         h = pinned_empty((sub, ROWS, COLS))
@@ -311,29 +311,29 @@ def run_ours(args, rank, world, local):
                          want_pyramid=False) for _ in range(depth)]
     kp_bytes = 0
 
-    def e2e_step():
+    def e2e_run(n_steps):
+        """n_steps x n_sub submits as ONE continuous pipeline with `depth` batches in flight (the
+        pipeline is drained only at the end, inside the timing)."""
         nonlocal kp_bytes
         inflight = []
-        for i in range(n_sub):
+        for i in range(n_steps * n_sub):
             j = i % depth
             if len(inflight) == depth:
                 k = inflight.pop(0)
                 exts[k].wait()
-                kp_bytes += sum(exts[k].count(f) for f in range(sub)) * 60
+                kp_bytes += int(exts[k].counts().sum()) * 60
             exts[j].submit_batch(hosts[j])
             inflight.append(j)
         for k in inflight:
             exts[k].wait()
-            kp_bytes += sum(exts[k].count(f) for f in range(sub)) * 60
+            kp_bytes += int(exts[k].counts().sum()) * 60
 
-    for _ in range(W):
-        e2e_step()
+    e2e_run(W)
     kp_bytes = 0
     barrier(world)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
+    e2e_run(args.steps)
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     barrier(world)

@@ -102,6 +102,8 @@ int borb_sync(borb_extractor *h);
  * until the next extract call on this handle.  *n may be 0 (desc/kps then still valid). */
 int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps,
                 const uint8_t **desc, int *n);
+/* keypoint counts of all frames of the last call: out[n_frames] */
+int borb_counts(const borb_extractor *h, int32_t *out);
 /* Level `level` of frame f: *data points at pixel (0,0) of the level image inside its padded
  * (19-pixel reflect-101 frame) parent, rows *step bytes apart -- the same view
  * mvImagePyramid[level] is (src/ORBextractor.cc:1417).  Needs BORB_WANT_PYRAMID. */

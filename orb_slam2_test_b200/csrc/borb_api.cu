@@ -389,7 +389,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
     h->qt_M = M;
     const size_t qt_smem = qt_smem_bytes(M);
-    CU(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem));
+    CU(cudaFuncSetAttribute(k_quadtree<QT_NT_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem));
+    CU(cudaFuncSetAttribute(k_quadtree<QT_NT_THROUGHPUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem));
     h->plan = P;
     h->cells.swap(cells);
     h->tiles.swap(tiles);
@@ -464,14 +465,19 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
                                                           d_cand_score, d_ncand);
     }
     STAGE(2);
-    k_quadtree<<<dim3(P.nlevels, n), QT_NT, qt_smem_bytes(h->qt_M), st>>>(
-        h->d_plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy,
-        d_lkp_score, d_nlkp, h->d_err);
+    if (n * P.nlevels <= 2 * h->n_sm) /* few CTAs: give each one a whole SM's worth of threads */
+        k_quadtree<QT_NT_LATENCY><<<dim3(P.nlevels, n), QT_NT_LATENCY, qt_smem_bytes(h->qt_M), st>>>(
+            h->d_plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
+    else
+        k_quadtree<QT_NT_THROUGHPUT><<<dim3(P.nlevels, n), QT_NT_THROUGHPUT, qt_smem_bytes(h->qt_M), st>>>(
+            h->d_plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
     STAGE(3);
     k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, 0, st>>>(h->d_plan, h->d_tiles,
                                                                                               d_pyr, d_blur);
     STAGE(4);
-    k_orient_describe<<<dim3((P.kp_total + DESC_NW * DESC_KPW - 1) / (DESC_NW * DESC_KPW), n), DESC_NT, 0, st>>>(
+    /* keypoint slots per warp: 16 when there are plenty of frames, 1 for a single frame */
+    const int kpw = std::max(1, std::min(DESC_KPW, n / 4));
+    k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, 0, st>>>(
         h->d_plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
         d_out_kp, d_out_desc, d_nout);
     STAGE(5);
@@ -851,6 +857,13 @@ int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps, c
     if (kps) *kps = reinterpret_cast<const borb_keypoint *>(h->h_out_kp + o);
     if (desc) *desc = h->h_out_desc + o * 32;
     if (n) *n = h->h_nout[frame];
+    return BORB_OK;
+}
+
+int borb_counts(const borb_extractor *h, int32_t *out)
+{
+    if (!h || !out || !h->results_on_host) return fail(BORB_ERR_STATE, "no results on the host");
+    std::memcpy(out, h->h_nout, (size_t)h->last_n * 4);
     return BORB_OK;
 }
 

@@ -23,11 +23,14 @@
 
 #include "borb_internal.h"
 
-#ifndef QT_NT
-#define QT_NT 256 /* measured on B200: 1024 -> 0.80 ms, 512 -> 0.51 ms, 256 -> 0.48 ms per 512 frames */
-#endif
+/* threads per CTA is a template parameter: 256 for throughput (many (level, frame) CTAs in flight;
+ * measured on B200 per 512 frames: 1024 -> 0.80 ms, 512 -> 0.51 ms, 256 -> 0.48 ms), 1024 for the
+ * latency of a single frame (8 CTAs in total: 45 us vs 78 us) */
+#define QT_NT_THROUGHPUT 256
+#define QT_NT_LATENCY 1024
 
 /* in-place exclusive scan of a[0..len), returns the total; all threads must call */
+template <int QT_NT>
 __device__ int qt_scan(int *a, int len, int *wtmp /* 33 ints */)
 {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -105,6 +108,7 @@ static inline size_t qt_smem_bytes(int M)
  * ccnt[4k+q] = points of rank k's q-th quarter, for all n_rank ranked nodes.
  * Only ranks < n_proc are actually split.  Returns the new list size; *n_exp = number of
  * children with more than one point (written to the other expandable buffer, creation order). */
+template <int QT_NT>
 __device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
                         const uint32_t *__restrict__ xy, uint32_t *__restrict__ node, int *n_exp)
 {
@@ -116,9 +120,9 @@ __device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
     }
     for (int j = tid; j < S; j += QT_NT) s.uf[j] = !(s.rank[j] >= 0 && s.rank[j] < n_proc);
     __syncthreads();
-    const int C = qt_scan(s.cf, nc, s.wtmp);
-    const int E = qt_scan(s.ef, nc, s.wtmp);
-    const int U = qt_scan(s.uf, S, s.wtmp);
+    const int C = qt_scan<QT_NT>(s.cf, nc, s.wtmp);
+    const int E = qt_scan<QT_NT>(s.ef, nc, s.wtmp);
+    const int U = qt_scan<QT_NT>(s.uf, S, s.wtmp);
     const int nxt = 1 - cur;
     for (int c = tid; c < nc; c += QT_NT) {
         const int n = s.ccnt[c];
@@ -158,6 +162,7 @@ __device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
 }
 
 /* count the quarters of every ranked node */
+template <int QT_NT>
 __device__ void qt_count(const QtSmem &s, int cur, int n_rank, int n_pts,
                          const uint32_t *__restrict__ xy, const uint32_t *__restrict__ node)
 {
@@ -175,6 +180,7 @@ __device__ void qt_count(const QtSmem &s, int cur, int n_rank, int n_pts,
     __syncthreads();
 }
 
+template <int QT_NT>
 __global__ void __launch_bounds__(QT_NT, 1024 / QT_NT)
 k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict__ cand_xy,
            const uint32_t *__restrict__ cand_score, uint32_t *__restrict__ cand_node,
@@ -230,7 +236,7 @@ k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict_
     __syncthreads();
     for (int j = tid; j < n_ini; j += QT_NT) s.cf[j] = s.ccnt[j] > 0;
     __syncthreads();
-    int S = qt_scan(s.cf, n_ini, s.wtmp);
+    int S = qt_scan<QT_NT>(s.cf, n_ini, s.wtmp);
     int cur = 0;
     for (int j = tid; j < n_ini; j += QT_NT) {
         if (s.ccnt[j] > 0) {
@@ -251,7 +257,7 @@ k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict_
         const int prev = S;
         for (int j = tid; j < S; j += QT_NT) s.ef[j] = s.cnt[cur][j] > 1;
         __syncthreads();
-        const int n_split = qt_scan(s.ef, S, s.wtmp);
+        const int n_split = qt_scan<QT_NT>(s.ef, S, s.wtmp);
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
         for (int j = tid; j < S; j += QT_NT) {
             const bool sp = s.cnt[cur][j] > 1;
@@ -259,9 +265,9 @@ k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict_
             if (sp) s.par[s.ef[j]] = j;
         }
         __syncthreads();
-        qt_count(s, cur, n_split, n, xy, node);
+        qt_count<QT_NT>(s, cur, n_split, n, xy, node);
         int n_exp;
-        S = qt_split(s, cur, S, n_split, n, xy, node, &n_exp);
+        S = qt_split<QT_NT>(s, cur, S, n_split, n, xy, node, &n_exp);
         cur = 1 - cur;
         if (S >= N || S == prev) break;
         if (S + 3 * n_exp <= N) continue;
@@ -284,7 +290,7 @@ k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict_
                 s.par[r] = s.exp_pos[cur][e];
             }
             __syncthreads();
-            qt_count(s, cur, E, n, xy, node);
+            qt_count<QT_NT>(s, cur, E, n, xy, node);
             /* size after processing ranks 0..k; stop at the first k reaching N */
             for (int k = tid; k < E; k += QT_NT) {
                 const int g = (s.ccnt[4 * k] > 0) + (s.ccnt[4 * k + 1] > 0) +
@@ -294,13 +300,13 @@ k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict_
             }
             if (tid == 0) sh_proc = E;
             __syncthreads();
-            qt_scan(s.ef, E, s.wtmp); /* exclusive prefix of the gains */
+            qt_scan<QT_NT>(s.ef, E, s.wtmp); /* exclusive prefix of the gains */
             for (int k = tid; k < E; k += QT_NT)
                 if (S + s.ef[k] + s.cf[k] >= N) atomicMin(&sh_proc, k + 1);
             __syncthreads();
             const int n_proc = sh_proc;
             __syncthreads();
-            S = qt_split(s, cur, S, n_proc, n, xy, node, &n_exp);
+            S = qt_split<QT_NT>(s, cur, S, n_proc, n, xy, node, &n_exp);
             cur = 1 - cur;
             if (S >= N || S == prev2) { done = true; break; }
         }

@@ -35,7 +35,7 @@ SYMBOLS = [
     "borb_pyramid", "borb_level_size", "borb_launches_per_call", "borb_last_device_ms",
     "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score",
     "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
-    "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms",
+    "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
 ]
 
 
@@ -93,6 +93,7 @@ def load_library() -> C.CDLL:
     lib.borb_timer_ms.argtypes = [_vp]
     lib.borb_timer_ms.restype = C.c_float
     lib.borb_stage_times.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, _vp]
+    lib.borb_counts.argtypes = [_vp, _vp]
     lib.borb_set_stage_timing.argtypes = [_vp, C.c_int]
     lib.borb_last_stage_ms.argtypes = [_vp, _vp]
     _lib = lib
@@ -251,6 +252,11 @@ class ORBextractor:
         ms = (C.c_float * 5)()
         _check(self._lib, self._lib.borb_last_stage_ms(self._h, ms))
         return dict(zip(self.STAGES, [float(v) for v in ms]))
+
+    def counts(self) -> np.ndarray:
+        out = np.zeros(self._n, np.int32)
+        _check(self._lib, self._lib.borb_counts(self._h, out.ctypes.data))
+        return out
 
     def count(self, frame: int = 0) -> int:
         n = C.c_int()
