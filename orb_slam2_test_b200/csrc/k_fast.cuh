@@ -141,13 +141,14 @@ __host__ __device__ __forceinline__ int fast_chunk(int npix) { return ((npix + F
 __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix)
 {
     FastSmemLayout o;
-    o.chunk = fast_chunk(max_pix);
+    o.chunk = fast_chunk(max_pix) + 64; /* a warp owns whole rows: up to one row (< 64 px) above its share */
     int b = 64; /* per-warp counts */
     o.win_off = b; o.win_bytes = max_wh * FAST_WPITCH; b += 2 * o.win_bytes; /* double buffered */
     o.sc_off = b;  b += ((max_wh - 4) * FAST_SPITCH + 15) & ~15;
-    o.l1_off = b;  b += FAST_NW * 2 * o.chunk * 2;        /* u16 pixel | side<<12, one slot per side */
+    /* list1 (u16 pixel | side<<12) is dead once stage 2 has consumed it; list3 (u32 NMS survivors:
+     * pixel | score<<12, at most half a warp's pixels + one per row) reuses its storage */
+    o.l1_off = b;  o.l3_off = b;  b += FAST_NW * (o.chunk + 64) * 2;
     o.l2_off = b;  b += FAST_NW * o.chunk * 2;            /* u16 corners */
-    o.l3_off = b;  b += FAST_NW * (o.chunk / 2 + 32) * 4; /* u32 NMS survivors: pixel | score<<12 */
     o.bytes = b;
     return o;
 }
@@ -184,9 +185,9 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     const uint32_t below = (1u << lane) - 1u;
     int *wcnt = reinterpret_cast<int *>(fast_raw); /* [pass][warp]: NMS survivors */
     uint8_t *sc = fast_raw + lay.sc_off;
-    uint16_t *list1 = reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off) + warp * 2 * lay.chunk;
+    uint16_t *list1 = reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off) + warp * (lay.chunk + 64);
     uint16_t *list2 = reinterpret_cast<uint16_t *>(fast_raw + lay.l2_off) + warp * lay.chunk;
-    uint32_t *list3 = reinterpret_cast<uint32_t *>(fast_raw + lay.l3_off) + warp * (lay.chunk / 2 + 32);
+    uint32_t *list3 = reinterpret_cast<uint32_t *>(list1);
     const int n_cells = plan->n_cells;
     const int ini = plan->ini_th, mn = plan->min_th;
 
@@ -220,8 +221,6 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
         const uint32_t dmagic = cell.dmagic;
 
         const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
-        /* 32-pixel groups are dealt round-robin to the warps, so every warp samples the whole
-         * cell and the per-warp work stays balanced when corners cluster */
         int n2 = 0, n3 = 0, cell_total = 0;
         /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
          * where the first found nothing; K(ini) needs nothing below ini: a corner's score is at
@@ -234,21 +233,14 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
 
             /* ---- stage 1: compass pre-test on this warp's pixels ---- */
             int n1 = 0;
-#ifdef FAST_NO_INTERLEAVE
-            const int chunk_ = fast_chunk(npix), i_end_ = min((warp + 1) * chunk_, npix);
-            for (int i = warp * chunk_ + lane; i - lane < i_end_; i += 32) {
-#else
-            for (int i = warp * 32 + lane; i - lane < npix; i += FAST_NT) {
-#endif
+            /* rows are dealt round-robin to the warps, a lane owns a column: no index arithmetic,
+             * every load is [row pointer + constant] */
+            for (int y = warp; y < dh; y += FAST_NW)
+            for (int x0 = 0; x0 < dw; x0 += 32) {
+                const int x = x0 + lane;
                 uint32_t side = 0;
-                uint32_t pix = 0;
-#ifdef FAST_NO_INTERLEAVE
-                if (i < i_end_) {
-#else
-                if (i < npix) {
-#endif
-                    const int y = fast_div(i, dmagic), x = i - y * dw;
-                    pix = (uint32_t)(y * 64 + x);
+                const uint32_t pix = (uint32_t)(y * 64 + x);
+                if (x < dw) {
                     const uint8_t *p = org + y * FAST_WPITCH + x;
                     const int v = p[0];
                     const int lo = v - t, hi = v + t;
