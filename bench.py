@@ -172,11 +172,12 @@ def run_reference_arm(args, rank, world):
         kind = r["kind"]
     value = tot / wall
     per_step = cores * per_proc
-    sample = f"{tot} frames ({per_step} per step), {cores} processes, one extractor per process"
+    sample = (f"bounded sample of the workload: {tot} frames ({per_step} per step), {cores} processes, "
+              "one extractor per process, one frame at a time each")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-            "data": "synthetic", "config": bench_config(per_step),
+            "data": "synthetic", "config": bench_config(args.frames_per_step),
             "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -392,10 +393,10 @@ def run_ours(args, rank, world, local):
     cores = len(os.sched_getaffinity(0))
     cpu = None
     if world == 1:
-        r = cpu_reference_run(cores, 8)
+        r = max((cpu_reference_run(cores, 8) for _ in range(2)), key=lambda q: q["frames_per_s"])  # best of 2
         r1 = cpu_reference_run(1, 8)
         cpu = {"value": r["frames_per_s"], "unit": "frames/s", "cores": cores, "kind": r["kind"],
-               "sample": f"{r['frames']} KITTI-shape frames, {cores} processes x 8 frames, one extractor each",
+               "sample": f"{r['frames']} KITTI-shape frames, {cores} processes x 8 frames, one extractor each, best of 2 runs",
                "single_core_frames_per_s": r1["frames_per_s"]}
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,

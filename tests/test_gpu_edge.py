@@ -1,0 +1,147 @@
+"""GPU edge cases the reference never tested: determinism, concurrent instances,
+strided input, odd geometries and parameters, error paths.  All through the C ABI."""
+import threading
+
+import numpy as np
+import pytest
+
+from orb_slam2_test_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _same(a, b):
+    return a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
+
+
+def test_determinism_100_runs_one_instance():
+    from orb_slam2_test_b200 import ORBextractor
+    ext = ORBextractor(2000, 1.2, 8, 20, 7, want_pyramid=False)
+    img = synth.make_frame(synth.KITTI_SHAPE, seed=9, frame=0)
+    first = ext(img)
+    for _ in range(100):
+        assert _same(ext(img), first)
+
+
+def test_two_concurrent_instances_like_stereo(oracle_built):
+    """src/Frame.cc:110-113: left and right extractors run on two threads."""
+    from orb_slam2_test_b200 import ORBextractor
+    imgs = [synth.make_frame(synth.KITTI_SHAPE, seed=9, frame=0, eye=e) for e in (0, 1)]
+    exts = [ORBextractor(2000, 1.2, 8, 20, 7) for _ in (0, 1)]
+    want = [oracle_built.Oracle(2000, 1.2, 8, 20, 7).extract(im) for im in imgs]
+    out = [None, None]
+
+    def run(i):
+        for _ in range(25):
+            out[i] = exts[i](imgs[i])
+
+    th = [threading.Thread(target=run, args=(i,)) for i in (0, 1)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert _same(out[0], want[0]) and _same(out[1], want[1])
+
+
+def test_non_contiguous_roi_input(oracle_built):
+    from orb_slam2_test_b200 import ORBextractor
+    big = synth.make_frame((420, 700), seed=4, frame=0)
+    roi = big[17:390, 33:677]  # step 700 > cols 644, as a cv::Mat ROI
+    got = ORBextractor(1000, 1.2, 8, 20, 7)(roi)
+    want = oracle_built.Oracle(1000, 1.2, 8, 20, 7).extract(np.ascontiguousarray(roi))
+    assert _same(got, want)
+
+
+PARAMS = [((480, 752), (1200, 1.2, 8, 20, 7)),      # EuRoC.yaml
+          (synth.KITTI_SHAPE, (2000, 1.2, 8, 12, 7)),  # KITTI04-12.yaml
+          ((211, 333), (700, 1.3, 5, 30, 5)),
+          ((240, 320), (300, 1.1, 12, 20, 7)),
+          ((300, 400), (500, 1.5, 4, 25, 10)),
+          ((200, 260), (50, 2.0, 2, 20, 7)),
+          ((240, 320), (1000, 1.2, 8, 7, 20)),        # ini < min: a second pass can add nothing
+          ((360, 1100), (1500, 1.2, 6, 130, 100))]    # thresholds above 127
+
+
+@pytest.mark.parametrize("shape,p", PARAMS)
+def test_other_parameters_and_shapes(shape, p, oracle_built):
+    from orb_slam2_test_b200 import ORBextractor
+    ext, ora = ORBextractor(*p), oracle_built.Oracle(*p)
+    for img in (synth.make_frame(shape, seed=17, frame=0), synth.make_noise_frame(shape, seed=3)):
+        got, want = ext(img), ora.extract(img)
+        assert len(got[0]) == len(want[0])
+        assert _same(got, want)
+
+
+def test_geometry_change_between_calls(oracle_built):
+    from orb_slam2_test_b200 import ORBextractor
+    ext, ora = ORBextractor(1000, 1.2, 8, 20, 7), oracle_built.Oracle(1000, 1.2, 8, 20, 7)
+    for shape in (synth.TUM_SHAPE, (240, 320), synth.KITTI_SHAPE, synth.TUM_SHAPE):
+        img = synth.make_frame(shape, seed=2, frame=1)
+        assert _same(ext(img), ora.extract(img))
+
+
+def test_half_flat_half_textured_and_low_contrast(oracle_built):
+    """cells with nothing at 20 (retry at 7), cells with nothing at all, saturated regions"""
+    from orb_slam2_test_b200 import ORBextractor
+    img = synth.make_frame(synth.TUM_SHAPE, seed=5, frame=0).astype(np.int32)
+    img[:, :200] = 128 + (img[:, :200] - 128) // 6   # low contrast: only the min threshold fires
+    img[300:, :] = 40                                 # flat
+    img[:60, 400:] = 255                              # saturated
+    img = np.clip(img, 0, 255).astype(np.uint8)
+    got = ORBextractor(1000, 1.2, 8, 20, 7)(img)
+    want = oracle_built.Oracle(1000, 1.2, 8, 20, 7).extract(img)
+    assert len(want[0]) > 100 and _same(got, want)
+
+
+def test_errors_are_reported_not_hidden():
+    from orb_slam2_test_b200 import BorbError, ORBextractor
+    ext = ORBextractor(1000, 1.2, 8, 20, 7)
+    with pytest.raises(BorbError) as e:   # level 7 smaller than one FAST cell
+        ext(np.zeros((100, 120), np.uint8))
+    assert e.value.code == -3
+    with pytest.raises(BorbError) as e:   # aspect ratio < 0.5: the reference divides by zero (nIni == 0)
+        ext(np.zeros((900, 300), np.uint8))
+    assert e.value.code == -3
+    with pytest.raises(TypeError):
+        ext(np.zeros((240, 320), np.float32))
+    assert ext(np.zeros((0, 0), np.uint8)) is None  # empty image: silent return, src/ORBextractor.cc:1333
+    with pytest.raises(BorbError) as e:   # more frames than max_batch
+        ext.extract_batch(np.zeros((2, 240, 320), np.uint8))
+    assert e.value.code == -4
+    img = synth.make_frame((240, 320), seed=1, frame=0)
+    assert len(ext(img)[0]) > 0           # the handle is still usable after errors
+
+
+def test_batch_tum_and_mixed_content(oracle_built):
+    from orb_slam2_test_b200 import ORBextractor
+    ext, ora = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=6), oracle_built.Oracle(1000, 1.2, 8, 20, 7)
+    imgs = np.stack([synth.make_frame(synth.TUM_SHAPE, seed=8, frame=0), synth.make_noise_frame(synth.TUM_SHAPE, seed=8),
+                     np.full(synth.TUM_SHAPE, 99, np.uint8), synth.make_frame(synth.TUM_SHAPE, seed=8, frame=3),
+                     synth.make_frame(synth.TUM_SHAPE, seed=11, frame=0)])
+    res = ext.extract_batch(imgs)
+    for f in range(len(imgs)):
+        assert _same(res[f], ora.extract(imgs[f])), f
+    # async halves give the same
+    ext.submit_batch(imgs)
+    ext.wait()
+    for f in range(len(imgs)):
+        assert _same(ext.result(f), res[f])
+
+
+def test_sequence_shard_runner_on_gpu(oracle_built):
+    """BASELINE config 5 in miniature: a stereo sequence through sequence.run_shard with the real
+    extractor (batched calls), every (frame, eye) digest equal to the oracle's."""
+    from orb_slam2_test_b200 import ORBextractor, sequence
+    n_frames, world = 7, 2
+    ext = ORBextractor(2000, 1.2, 8, 20, 7, max_batch=4, want_pyramid=False)
+    ora = oracle_built.Oracle(2000, 1.2, 8, 20, 7)
+
+    def load(f, e):
+        return synth.make_frame(synth.KITTI_SHAPE, seed=41, frame=f, eye=e)
+
+    allr = []
+    for rank in range(world):  # the two shards one after the other on this one GPU
+        allr += sequence.run_shard(sequence.shard_indices(n_frames, rank, world), load, ext.extract_batch, 4, True)
+    allr = sequence.gather_to_rank0(allr, 0, 1)
+    sequence.check_complete(allr, n_frames, True)
+    for r in allr:
+        k, d = ora.extract(load(r.frame, r.eye))
+        assert sequence.FrameResult.of(r.frame, r.eye, k, d).digest == r.digest
