@@ -275,7 +275,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
             }
             h->pyr_sp[l] = (int)align_up(span_x + 16, 16);
             h->pyr_srows[l] = span_y + 1;
-            if ((long long)h->pyr_sp[l] * h->pyr_srows[l] > 160 * 1024)
+            if ((long long)2 * h->pyr_sp[l] * h->pyr_srows[l] > 48 * 1024)
                 return fail(BORB_ERR_GEOMETRY, "scale factor too large for the pyramid tile at level %d", l);
         }
         /* FAST cell grid, src/ORBextractor.cc:974-1064 (float arithmetic as written there) */
@@ -444,7 +444,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);
-            k_pyr_resize<<<g, PYR_NT, (size_t)h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s,
+            k_pyr_resize<<<g, PYR_NT, (size_t)2 * h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s,
                                                                                    d_pyr, h->pyr_sp[l], h->pyr_srows[l]);
         }
     }

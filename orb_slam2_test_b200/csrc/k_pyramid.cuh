@@ -96,19 +96,18 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
     uint8_t *frame = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes;
     const uint8_t *sbase = frame + S.off + (size_t)BORB_EDGE * S.pitch + BORB_XPAD;
 
-    /* horizontal taps of this lane's 4 columns */
-    int sx[4], sx1[4], a0[4], a1[4];
+    /* horizontal taps of this lane's 4 columns: source column and the weight pair (a0 | a1 << 16) */
+    int sx[4];
+    uint32_t aw[4];
     int sx_lo = 0x7fffffff, sx_hi = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         int x = min(c + k, L.w - 1 + BORB_EDGE);
         x = reflect101(x, L.w);
         sx[k] = tab_i[L.xofs_off + x];
-        sx1[k] = min(sx[k] + 1, S.w - 1);
-        a0[k] = tab_s[L.xa_off + 2 * x];
-        a1[k] = tab_s[L.xa_off + 2 * x + 1];
+        aw[k] = (uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x] | ((uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x + 1] << 16);
         sx_lo = min(sx_lo, sx[k]);
-        sx_hi = max(sx_hi, sx1[k]);
+        sx_hi = max(sx_hi, min(sx[k] + 1, S.w - 1));
     }
     /* source window of the tile: columns (all 4 warps hold the same columns) and rows */
     sx_lo = __reduce_min_sync(0xffffffffu, sx_lo) & ~15;
@@ -122,24 +121,41 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
     }
     sy_lo = __reduce_min_sync(0xffffffffu, sy_lo);
     sy_hi = __reduce_max_sync(0xffffffffu, sy_hi);
+    /* Stage the window as byte PAIRS: element i of a staged row is (s[i], s[i+1]) as one aligned
+     * 16-bit value, so a horizontal tap pair is one LDS.U16 and the horizontal sum
+     * s[x0]*a0 + s[x0+1]*a1 one dp2a.  (Where cv::resize clamps x0+1 to the last column its weight
+     * a1 is 0, so the pair's second byte is immaterial there.) */
+    const int sp2 = 2 * sp;
     {
-        const int vpr = (sx_hi - sx_lo) / 16 + 1;             /* uint4 per staged row */
+        const int vpr = (sx_hi - sx_lo) / 16 + 1;             /* uint4 per source row */
         const int nrow = sy_hi - sy_lo + 1;
         const int nv = vpr * nrow;                            /* host guarantees vpr*16 <= sp, nrow <= srows */
         const uint8_t *g = sbase + (size_t)sy_lo * S.pitch + sx_lo; /* 16-B aligned: pitch, XPAD, sx_lo are */
         for (int i = threadIdx.x; i < nv; i += PYR_NT) {
             const int rr = i / vpr, cc = i - rr * vpr;
-            *reinterpret_cast<uint4 *>(pyr_tile + rr * sp + cc * 16) =
-                __ldg(reinterpret_cast<const uint4 *>(g + (size_t)rr * S.pitch) + cc);
+            const uint32_t *gw = reinterpret_cast<const uint32_t *>(g + (size_t)rr * S.pitch) + 4 * cc;
+            const uint4 q = __ldg(reinterpret_cast<const uint4 *>(gw));
+            const uint32_t w[5] = {q.x, q.y, q.z, q.w, __ldg(gw + 4)};
+            uint32_t o[8];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                o[2 * m] = __byte_perm(w[m], 0u, 0x2110);            /* (b0,b1) (b1,b2) */
+                o[2 * m + 1] = __byte_perm(w[m], w[m + 1], 0x4332);  /* (b2,b3) (b3,b4) */
+            }
+            uint4 *dstv = reinterpret_cast<uint4 *>(pyr_tile + rr * sp2 + cc * 32);
+            dstv[0] = make_uint4(o[0], o[1], o[2], o[3]);
+            dstv[1] = make_uint4(o[4], o[5], o[6], o[7]);
         }
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { sx[k] -= sx_lo; sx1[k] -= sx_lo; }
+    for (int k = 0; k < 4; ++k) sx[k] = 2 * (sx[k] - sx_lo); /* byte offset of the pair in a staged row */
     __syncthreads();
     if (c >= L.w + BORB_EDGE) return;
 
+    /* hA / hB: horizontal sums (already >> 4, as the vertical pass uses them) of the two source rows
+     * of the previous output row */
     int rowA = -1, rowB = -1;
-    int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
+    uint32_t hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
     uint8_t *dst = frame + L.off + BORB_XPAD + c;
 #pragma unroll
     for (int i = 0; i < PYR_TH / 4; ++i) {
@@ -147,9 +163,10 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
         if (r >= L.prows) break;
         const int y = reflect101(r - BORB_EDGE, L.h);
         const int sy = tab_i[L.yofs_off + y];
-        const int b0 = tab_s[L.yb_off + 2 * y], b1 = tab_s[L.yb_off + 2 * y + 1];
+        /* (b * h) >> 16 as the high word of (b << 16) * h: operands are non-negative */
+        const uint32_t b0 = (uint32_t)tab_s[L.yb_off + 2 * y] << 16, b1 = (uint32_t)tab_s[L.yb_off + 2 * y + 1] << 16;
         const int sy0 = min(max(sy, 0), S.h - 1) - sy_lo, sy1 = min(max(sy + 1, 0), S.h - 1) - sy_lo;
-        int n0[4], n1[4];
+        uint32_t n0[4], n1[4];
         if (sy0 == rowB) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) n0[k] = hB[k];
@@ -157,9 +174,10 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
 #pragma unroll
             for (int k = 0; k < 4; ++k) n0[k] = hA[k];
         } else {
-            const uint8_t *row = pyr_tile + sy0 * sp;
+            const uint8_t *row = pyr_tile + sy0 * sp2;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) n0[k] = (int)row[sx[k]] * a0[k] + (int)row[sx1[k]] * a1[k];
+            for (int k = 0; k < 4; ++k)
+                n0[k] = __dp2a_lo(aw[k], (uint32_t) * reinterpret_cast<const uint16_t *>(row + sx[k]), 0u) >> 4;
         }
         if (sy1 == rowB) {
 #pragma unroll
@@ -168,15 +186,16 @@ k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ t
 #pragma unroll
             for (int k = 0; k < 4; ++k) n1[k] = hA[k];
         } else {
-            const uint8_t *row = pyr_tile + sy1 * sp;
+            const uint8_t *row = pyr_tile + sy1 * sp2;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) n1[k] = (int)row[sx[k]] * a0[k] + (int)row[sx1[k]] * a1[k];
+            for (int k = 0; k < 4; ++k)
+                n1[k] = __dp2a_lo(aw[k], (uint32_t) * reinterpret_cast<const uint16_t *>(row + sx[k]), 0u) >> 4;
         }
         uint32_t v = 0;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const int d = (((b0 * (n0[k] >> 4)) >> 16) + ((b1 * (n1[k] >> 4)) >> 16) + 2) >> 2;
-            v |= (uint32_t)d << (8 * k);
+            const uint32_t d = (__umulhi(b0, n0[k]) + __umulhi(b1, n1[k]) + 2u) >> 2;
+            v |= d << (8 * k);
             hA[k] = n0[k];
             hB[k] = n1[k];
         }
