@@ -109,6 +109,24 @@ int borb_counts(const borb_extractor *h, int32_t *out);
  * mvImagePyramid[level] is (src/ORBextractor.cc:1417).  Needs BORB_WANT_PYRAMID. */
 int borb_pyramid(const borb_extractor *h, int frame, int level, const uint8_t **data, int *cols,
                  int *rows, size_t *step);
+/* -- stereo association: replaces Frame::ComputeStereoMatches (src/Frame.cc:619-834) ---------- */
+
+#define BORB_STEREO_KEEP_ON_DEVICE 1u /* enqueue only; no download, borb_stereo_result unavailable */
+
+/* For every keypoint of `left`'s last call, frame by frame against the same frame of `right`'s
+ * last call (both handles on one device, same image size and pyramid parameters, same number of
+ * frames): best right keypoint by descriptor distance inside the row band, 11x11 SAD refinement on
+ * the two device-resident pyramids, parabola sub-pixel fit, the median-SAD outlier cut -- giving
+ * mvuRight[i] and mvDepth[i] (-1 where unmatched).  mbf = baseline * fx (Frame::mbf), mb = the
+ * baseline used for the search range minD = 0, maxD = mbf / mb (src/Frame.cc:651-653).  The work
+ * runs on left's stream, ordered after right's; neither pyramid leaves the device.
+ * The row-band bookkeeping uses (size_t)y of the LEFT keypoint exactly as the reference does. */
+int borb_stereo_match(borb_extractor *left, borb_extractor *right, float mbf, float mb, unsigned flags);
+/* frame f of the last borb_stereo_match: u_right[n], depth[n] parallel to borb_result()'s
+ * keypoints of `left`; *n_matched = entries with depth > 0.  Pinned memory of `left`. */
+int borb_stereo_result(const borb_extractor *left, int frame, const float **u_right, const float **depth,
+                       int *n, int *n_matched);
+
 /* geometry only (valid after any extract call) */
 int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows);
 

@@ -174,6 +174,38 @@ def distribute(xs, ys, resp, min_x, max_x, min_y, max_y, n_target):
     return out[:n].copy()
 
 
+class _SoLevel(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("cols", C.c_int), ("rows", C.c_int), ("step", C.c_size_t)]
+
+
+def stereo_match(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, mbf: float, mb: float):
+    """Frame::ComputeStereoMatches restated (oracle/stereo_oracle.cpp).  pyr_l / pyr_r: lists of
+    2-D uint8 level images (un-padded).  -> (uRight[n], depth[n], sad[n], kept)."""
+    lib = Oracle.load()
+    lib.so_stereo_match.argtypes = [_vp, _vp, C.c_int, _vp, _vp, C.c_int, _vp, _vp, C.c_int, _vp, _vp,
+                                    C.c_float, C.c_float, _vp, _vp, _vp]
+    kl = np.ascontiguousarray(kl); kr = np.ascontiguousarray(kr)
+    dl = np.ascontiguousarray(dl); dr = np.ascontiguousarray(dr)
+    keep = []
+
+    def levels(pyr):
+        arr = (_SoLevel * len(pyr))()
+        for i, im in enumerate(pyr):
+            im = np.ascontiguousarray(im)
+            keep.append(im)
+            arr[i] = _SoLevel(im.ctypes.data, im.shape[1], im.shape[0], im.strides[0])
+        return arr
+
+    pl, pr = levels(pyr_l), levels(pyr_r)
+    scale = np.ascontiguousarray(scale, np.float32); inv_scale = np.ascontiguousarray(inv_scale, np.float32)
+    n = len(kl)
+    u = np.zeros(max(n, 1), np.float32); z = np.zeros(max(n, 1), np.float32); sad = np.zeros(max(n, 1), np.int32)
+    kept = lib.so_stereo_match(kl.ctypes.data, dl.ctypes.data, n, kr.ctypes.data, dr.ctypes.data, len(kr),
+                               C.addressof(pl), C.addressof(pr), len(pyr_l), scale.ctypes.data, inv_scale.ctypes.data,
+                               mbf, mb, u.ctypes.data, z.ctypes.data, sad.ctypes.data)
+    return u[:n], z[:n], sad[:n], kept
+
+
 def describe(img: np.ndarray, x: int, y: int, angle_deg: float) -> np.ndarray:
     out = np.zeros(32, np.uint8)
     Oracle.load().orbo_describe(img.ctypes.data, img.strides[0], x, y, angle_deg, out.ctypes.data)

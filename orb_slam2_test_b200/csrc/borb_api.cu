@@ -27,6 +27,7 @@
 #include "k_fast.cuh"
 #include "k_pyramid.cuh"
 #include "k_quadtree.cuh"
+#include "k_stereo.cuh"
 
 static_assert(sizeof(borb_keypoint) == 28 && sizeof(BorbKpRec) == 28, "cv::KeyPoint layout");
 
@@ -129,6 +130,11 @@ struct borb_extractor {
     uint8_t *h_in = nullptr, *h_pyr = nullptr, *h_out_desc = nullptr;
     BorbKpRec *h_out_kp = nullptr;
     int *h_nout = nullptr, *h_err = nullptr;
+    /* stereo association (left handle only), allocated on first use */
+    float *d_st_u = nullptr, *d_st_z = nullptr, *h_st_u = nullptr, *h_st_z = nullptr;
+    int *d_st_sad = nullptr, *d_st_kept = nullptr, *h_st_kept = nullptr;
+    cudaEvent_t ev_peer = nullptr; /* recorded on this handle's stream for a peer handle to wait on */
+    bool stereo_on_host = false;
 
     std::vector<GraphEntry> graphs;
     int last_n = 0;          /* frames of the last call */
@@ -202,10 +208,15 @@ void free_geometry(borb_extractor *h)
     h->graphs.clear();
     void *dev[] = {h->d_plan, h->d_cells, h->d_tiles, h->d_tab_i, h->d_tab_s, h->d_in, h->d_pyr,
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
-                   h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc};
+                   h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
+                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept};
     for (void *p : dev) if (p) cudaFree(p);
-    void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err};
+    void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
+                    h->h_st_u, h->h_st_z, h->h_st_kept};
     for (void *p : host) if (p) cudaFreeHost(p);
+    h->d_st_u = h->d_st_z = h->h_st_u = h->h_st_z = nullptr;
+    h->d_st_sad = h->d_st_kept = h->h_st_kept = nullptr;
+    h->stereo_on_host = false;
     h->d_plan = nullptr; h->d_cells = nullptr; h->d_tiles = nullptr; h->d_tab_i = nullptr;
     h->d_tab_s = nullptr; h->d_in = h->d_pyr = h->d_blur = nullptr;
     h->d_cand_xy = h->d_cand_score = h->d_cand_node = nullptr;
@@ -250,6 +261,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
         L.off = pyr_off;
         pyr_off = align_up(pyr_off + (long long)L.pitch * L.prows, 256);
         L.scale = h->scale[l];
+        L.inv_scale = h->inv_scale[l];
         L.patch_size = (float)(int)(31 * h->scale[l]);
         L.quota = h->quota[l];
         if (l > 0) {
@@ -618,6 +630,7 @@ void borb_destroy(borb_extractor *h)
     if (h->evt0) cudaEventDestroy(h->evt0);
     if (h->evt1) cudaEventDestroy(h->evt1);
     for (int i = 0; i < 8; ++i) if (h->evs[i]) cudaEventDestroy(h->evs[i]);
+    if (h->ev_peer) cudaEventDestroy(h->ev_peer);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -864,6 +877,68 @@ int borb_counts(const borb_extractor *h, int32_t *out)
 {
     if (!h || !out || !h->results_on_host) return fail(BORB_ERR_STATE, "no results on the host");
     std::memcpy(out, h->h_nout, (size_t)h->last_n * 4);
+    return BORB_OK;
+}
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:619-834) on the two handles' device-resident results */
+int borb_stereo_match(borb_extractor *l, borb_extractor *r, float mbf, float mb, unsigned flags)
+{
+    if (!l || !r || l == r) return fail(BORB_ERR_ARG, "two distinct handles are needed");
+    if (!l->have_plan || !r->have_plan || l->last_n < 1 || l->last_n != r->last_n)
+        return fail(BORB_ERR_STATE, "both handles need a finished extract call over the same number of frames");
+    if (l->device != r->device) return fail(BORB_ERR_ARG, "handles live on devices %d and %d", l->device, r->device);
+    if (l->plan.cols != r->plan.cols || l->plan.rows != r->plan.rows || l->nlevels != r->nlevels ||
+        l->scale_factor != r->scale_factor || l->plan.kp_total != r->plan.kp_total)
+        return fail(BORB_ERR_ARG, "left and right extractor differ in geometry or pyramid parameters");
+    if (!(mbf > 0.f) || !(mb > 0.f)) return fail(BORB_ERR_ARG, "mbf %g, mb %g", (double)mbf, (double)mb);
+    CU(cudaSetDevice(l->device));
+    const BorbPlan &P = l->plan;
+    const size_t B = (size_t)l->max_batch, K = (size_t)P.kp_total;
+    if (!l->d_st_u) {
+        CU(cudaMalloc(&l->d_st_u, B * K * 4));
+        CU(cudaMalloc(&l->d_st_z, B * K * 4));
+        CU(cudaMalloc(&l->d_st_sad, B * K * 4));
+        CU(cudaMalloc(&l->d_st_kept, B * 4));
+        CU(cudaMallocHost(&l->h_st_u, B * K * 4));
+        CU(cudaMallocHost(&l->h_st_z, B * K * 4));
+        CU(cudaMallocHost(&l->h_st_kept, B * 4));
+    }
+    if (!r->ev_peer) CU(cudaEventCreateWithFlags(&r->ev_peer, cudaEventDisableTiming));
+    const int n = l->last_n;
+    /* the right extractor's kernels run on its own stream: order the match after them */
+    CU(cudaEventRecord(r->ev_peer, r->stream));
+    CU(cudaStreamWaitEvent(l->stream, r->ev_peer, 0));
+    const dim3 grid((unsigned)((K + ST_NT / 32 - 1) / (ST_NT / 32)), (unsigned)n);
+    k_stereo_match<<<grid, ST_NT, 0, l->stream>>>(l->d_plan, l->d_out_kp, l->d_out_desc, l->d_nout, r->d_out_kp,
+                                                  r->d_out_desc, r->d_nout, l->d_pyr, r->d_pyr, mbf, mb,
+                                                  l->d_st_u, l->d_st_z, l->d_st_sad);
+    k_stereo_cut<<<n, 256, 0, l->stream>>>(l->d_plan, l->d_nout, l->d_st_u, l->d_st_z, l->d_st_sad, l->d_st_kept);
+    CU(cudaGetLastError());
+    /* the right handle must not start its next call before the match has read its buffers */
+    if (!l->ev_peer) CU(cudaEventCreateWithFlags(&l->ev_peer, cudaEventDisableTiming));
+    CU(cudaEventRecord(l->ev_peer, l->stream));
+    CU(cudaStreamWaitEvent(r->stream, l->ev_peer, 0));
+    l->stereo_on_host = false;
+    if (flags & BORB_STEREO_KEEP_ON_DEVICE) return BORB_OK;
+    CU(cudaMemcpyAsync(l->h_st_u, l->d_st_u, (size_t)n * K * 4, cudaMemcpyDeviceToHost, l->stream));
+    CU(cudaMemcpyAsync(l->h_st_z, l->d_st_z, (size_t)n * K * 4, cudaMemcpyDeviceToHost, l->stream));
+    CU(cudaMemcpyAsync(l->h_st_kept, l->d_st_kept, (size_t)n * 4, cudaMemcpyDeviceToHost, l->stream));
+    CU(cudaMemcpyAsync(l->h_nout, l->d_nout, (size_t)n * 4, cudaMemcpyDeviceToHost, l->stream));
+    CU(cudaStreamSynchronize(l->stream));
+    l->stereo_on_host = true;
+    return BORB_OK;
+}
+
+int borb_stereo_result(const borb_extractor *l, int frame, const float **u_right, const float **depth,
+                       int *n, int *n_matched)
+{
+    if (!l || !l->stereo_on_host) return fail(BORB_ERR_STATE, "no stereo result on the host");
+    if (frame < 0 || frame >= l->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, l->last_n);
+    const size_t o = (size_t)frame * l->plan.kp_total;
+    if (u_right) *u_right = l->h_st_u + o;
+    if (depth) *depth = l->h_st_z + o;
+    if (n) *n = l->h_nout[frame];
+    if (n_matched) *n_matched = l->h_st_kept[frame];
     return BORB_OK;
 }
 

@@ -11,6 +11,8 @@
  *   ncand  [B][L]           candidate counters (atomics), zeroed each call
  *   lkp    [B][kp_total]    per-level survivors (x, y, score) at lv[l].kp_off, nlkp [B][L]
  *   out    [B][kp_total]    final cv::KeyPoint records + [B][kp_total][32] descriptors, nout [B]
+ *   stereo [B][kp_total]    uRight, depth (float) and SAD (int) per left keypoint, kept [B]
+ *                           (allocated by the first borb_stereo_match on the left handle)
  */
 #ifndef BORB_INTERNAL_H
 #define BORB_INTERNAL_H
@@ -45,6 +47,7 @@ struct BorbLevel {
     int cand_cap;           /* candidate capacity */
     long long cand_off;     /* offset into per-frame candidate arrays */
     float scale;            /* mvScaleFactor[l] */
+    float inv_scale;        /* mvInvScaleFactor[l] */
     float patch_size;       /* (float)(int)(31*scale) */
 };
 

@@ -36,6 +36,7 @@ SYMBOLS = [
     "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score",
     "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
+    "borb_stereo_match", "borb_stereo_result",
 ]
 
 
@@ -96,6 +97,9 @@ def load_library() -> C.CDLL:
     lib.borb_counts.argtypes = [_vp, _vp]
     lib.borb_set_stage_timing.argtypes = [_vp, C.c_int]
     lib.borb_last_stage_ms.argtypes = [_vp, _vp]
+    lib.borb_stereo_match.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_uint]
+    lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
+                                       C.POINTER(C.c_int)]
     _lib = lib
     return lib
 
@@ -281,6 +285,23 @@ class ORBextractor:
         kps = np.ctypeslib.as_array(C.cast(kp, C.POINTER(C.c_uint8)), shape=(cnt * 28,)).view(KP_DTYPE)
         desc = np.ctypeslib.as_array(C.cast(de, C.POINTER(C.c_uint8)), shape=(cnt, 32))
         return (kps.copy(), desc.copy()) if copy else (kps, desc)
+
+    def stereo_match(self, right: "ORBextractor", mbf: float, mb: float, keep_on_device: bool = False) -> None:
+        """Frame::ComputeStereoMatches (src/Frame.cc:619-834) of this (left) extractor's last call
+        against `right`'s, on the device; see include/borb.h."""
+        _check(self._lib, self._lib.borb_stereo_match(self._h, right._h, mbf, mb, 1 if keep_on_device else 0))
+
+    def stereo_result(self, frame: int = 0):
+        """(mvuRight, mvDepth, matched count) of frame `frame` of the last stereo_match."""
+        u, z, n, m = _vp(), _vp(), C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_stereo_result(self._h, frame, C.byref(u), C.byref(z), C.byref(n),
+                                                       C.byref(m)))
+        cnt = n.value
+        if cnt == 0:
+            return np.zeros(0, np.float32), np.zeros(0, np.float32), 0
+        ur = np.ctypeslib.as_array(C.cast(u, C.POINTER(C.c_float)), shape=(cnt,)).copy()
+        dz = np.ctypeslib.as_array(C.cast(z, C.POINTER(C.c_float)), shape=(cnt,)).copy()
+        return ur, dz, m.value
 
     def level_size(self, level: int):
         c, r = C.c_int(), C.c_int()
