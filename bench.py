@@ -224,6 +224,92 @@ def ncu_traffic(kernel: str, frames: int):
         return None
 
 
+def stereo_section(ORBextractor, synth, local, two, dev):
+    """SURVEY.md 8(f)-1: Frame::ComputeStereoMatches on the device (borb_stereo_match).  Reported
+    beside the headline, not part of `value`: (1) a stereo pair through the host ABI with the match on
+    the device and NO pyramid download, against the same pair with both pyramids brought back for a
+    host-side match; (2) batched pairs, device resident: both eyes' extraction + match per pair;
+    (3) the CPU restatement of the match alone on one host core."""
+    import threading
+    BF, FX = 386.1448, 718.856
+    mb = BF / FX
+    out = {"reference": "src/Frame.cc:619-834", "parity": "bit-exact against oracle/stereo_oracle.cpp (oracle unpinned)"}
+    li = synth.make_frame((ROWS, COLS), seed=31, frame=0, eye=0)
+    ri = synth.make_frame((ROWS, COLS), seed=31, frame=0, eye=1)
+    imgs = [li, ri]
+
+    def eye(i):
+        two[i]._lib.borb_extract_host(two[i]._h, imgs[i].ctypes.data, 1, COLS, ROWS, COLS, 0, 0)
+        two[i]._n = 1
+
+    ts = []
+    for it in range(220):
+        t1 = time.perf_counter()
+        th = threading.Thread(target=eye, args=(1,))
+        th.start()
+        eye(0)
+        th.join()
+        two[0].stereo_match(two[1], BF, mb)
+        if it >= 20:
+            ts.append((time.perf_counter() - t1) * 1e6)
+    out["pair_extract_plus_device_match_p50_us"] = float(np.percentile(ts, 50))
+    u, z, kept = two[0].stereo_result(0)
+    out["matched_per_pair"] = kept
+    # the match alone, CUDA events on the left handle's stream
+    ms = []
+    for _ in range(50):
+        two[0].timer_start()
+        two[0].stereo_match(two[1], BF, mb, keep_on_device=True)
+        two[0].timer_stop()
+        two[0].sync()
+        ms.append(two[0].timer_ms())
+    out["match_kernels_p50_us_one_pair"] = float(np.percentile(ms, 50) * 1e3)
+    # CPU restatement of the match alone (inputs: this run's keypoints, descriptors, pyramids)
+    try:
+        from oracle import pyoracle
+        for e in two:
+            e.fetch(want_pyramid=True)
+        kl, dl = two[0].result(0)
+        kr, dr = two[1].result(0)
+        pl = [two[0].pyramid_level(0, l) for l in range(NLEVELS)]
+        pr = [two[1].pyramid_level(0, l) for l in range(NLEVELS)]
+        t1 = time.perf_counter()
+        for _ in range(20):
+            wu, wz, _, wk = pyoracle.stereo_match(kl, dl, kr, dr, pl, pr, two[0].GetScaleFactors(),
+                                                  two[0].GetInverseScaleFactors(), BF, mb)
+        out["cpu_match_us_one_pair_one_core"] = (time.perf_counter() - t1) / 20 * 1e6
+        out["parity_check"] = "bit-exact" if (wu.tobytes() == u.tobytes() and wz.tobytes() == z.tobytes()) else "MISMATCH"
+    except Exception as e:
+        out["parity_check"] = f"unavailable ({type(e).__name__})"
+    # batched pairs, device resident: frames 2i / 2i+1 of the resident batch stand for the two eyes
+    # (timing only -- these are not rectified pairs, so few of them match)
+    P = max(1, min(128, dev.shape[0] // 2))
+    lb = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=P, want_pyramid=False)
+    rb = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=P, want_pyramid=False)
+    lp = dev.data_ptr()
+    rp = dev.data_ptr() + P * ROWS * COLS
+    for rep in range(5):
+        if rep == 2:
+            lb.sync(); rb.sync()
+            lb.timer_start()
+        lb.extract_device(lp, P, COLS, ROWS)
+        rb.extract_device(rp, P, COLS, ROWS)
+        lb.stereo_match(rb, BF, mb, keep_on_device=True)
+    lb.timer_stop()
+    rb.sync(); lb.sync()
+    out["batched_pairs_per_s_device_resident"] = 3 * P / (lb.timer_ms() / 1e3)
+    ms = []
+    for _ in range(5):
+        lb.timer_start()
+        lb.stereo_match(rb, BF, mb, keep_on_device=True)
+        lb.timer_stop()
+        lb.sync()
+        ms.append(lb.timer_ms())
+    out["match_ms_per_batch"] = float(np.median(ms))
+    out["pairs_per_batch"] = P
+    return out
+
+
 def run_ours(args, rank, world, local):
     import torch
     from orb_slam2_test_b200 import ORBextractor, synth
@@ -343,6 +429,7 @@ def run_ours(args, rank, world, local):
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
+    stereo = None
     if rank == 0:
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
@@ -381,6 +468,7 @@ def run_ours(args, rank, world, local):
             if it >= 20:
                 ts.append((time.perf_counter() - t1) * 1e6)
         lat["stereo_pair_p50_us_with_pyramids"] = float(np.percentile(ts, 50))
+        stereo = stereo_section(ORBextractor, synth, local, two, dev)
 
     if rank != 0:
         return
@@ -421,6 +509,7 @@ def run_ours(args, rank, world, local):
                      "path_frac": algorithmic_bytes(n_kp) * value / world / 1e9 / peak},
         "cpu_baseline": cpu,
         "latency": lat,
+        "stereo": stereo,
         "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,
     }

@@ -104,4 +104,15 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     }
 }
 
+void ORBextractor::ComputeStereoMatches(ORBextractor &right, float mbf, float mb, std::vector<float> &mvuRight,
+                                        std::vector<float> &mvDepth)
+{
+    check(borb_stereo_match(handle, right.handle, mbf, mb, 0u), "stereo match");
+    const float *u = NULL, *z = NULL;
+    int n = 0;
+    check(borb_stereo_result(handle, 0, &u, &z, &n, NULL), "stereo result");
+    mvuRight.assign(u, u + n);
+    mvDepth.assign(z, z + n);
+}
+
 } // namespace ORB_SLAM2

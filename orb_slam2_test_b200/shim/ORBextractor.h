@@ -81,6 +81,12 @@ public:
     // Mono / RGB-D callers never read mvImagePyramid; turning the download off saves the
     // device-to-host copy of the 8 levels.  Default: on (stereo matching needs it).
     void SetPyramidDownload(bool on) { downloadPyramid = on; }
+    // Frame::ComputeStereoMatches (reference src/Frame.cc:619-834) on the device, for *this as the
+    // left extractor: fills mvuRight / mvDepth (size = left keypoint count, -1 where unmatched)
+    // from the last operator() results of both instances.  Call it after both extraction threads
+    // have joined (src/Frame.cc:110-113); neither pyramid has to be downloaded for it.
+    void ComputeStereoMatches(ORBextractor &right, float mbf, float mb, std::vector<float> &mvuRight,
+                              std::vector<float> &mvDepth);
 
 protected:
     int nfeatures;

@@ -7,11 +7,13 @@
  *   src/Frame.cc:110-113     left and right operator() on two std::threads
  *   src/Frame.cc:310-316     (*mpORBextractorLeft)(im, cv::Mat(), mvKeys, mDescriptors)
  *   src/Frame.cc:626,738-757 mvImagePyramid[level].rows/.cols/.rowRange().colRange()
+ *   src/Frame.cc:120         ComputeStereoMatches() -- here the one-line device version
  *
  * usage: frame_like <left.raw> <right.raw> <cols> <rows> <nfeatures> <out.bin>
  * Writes, for left then right: int32 n, n x 28-byte keypoints, n x 32 descriptor bytes, then for
  * each of the 8 levels int32 cols, rows and an 11x11 window checksum (sum of all level pixels via
- * rowRange/colRange walks).  The pytest compares everything with the CPU oracle.
+ * rowRange/colRange walks); at the very end int32 n, n x float mvuRight, n x float mvDepth of the
+ * stereo pair.  The pytest compares everything with the CPU oracle.
  */
 #include <cmath>
 #include <cstdio>
@@ -32,6 +34,8 @@ struct FrameLike {
     int mnScaleLevels;
     float mfScaleFactor, mfLogScaleFactor;
     vector<float> mvScaleFactors, mvInvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
+    vector<float> mvuRight, mvDepth;
+    float mbf, mb;
 
     FrameLike(const cv::Mat &imLeft, const cv::Mat &imRight, ORBextractor *l, ORBextractor *r)
         : mpORBextractorLeft(l), mpORBextractorRight(r)
@@ -48,6 +52,16 @@ struct FrameLike {
         thread threadRight(&FrameLike::ExtractORB, this, 1, imRight);
         threadLeft.join();
         threadRight.join();
+
+        /* src/Frame.cc:86-87 (mb is derived from mbf and fx), :120 ComputeStereoMatches() */
+        mbf = 386.1448f;
+        mb = mbf / 718.856f;
+        ComputeStereoMatches();
+    }
+
+    void ComputeStereoMatches()
+    {
+        mpORBextractorLeft->ComputeStereoMatches(*mpORBextractorRight, mbf, mb, mvuRight, mvDepth);
     }
 
     void ExtractORB(int flag, const cv::Mat &im)
@@ -107,11 +121,14 @@ int main(int argc, char **argv)
 
     FILE *f = fopen(argv[6], "wb");
     if (!f) return 2;
+    vector<float> uRight, depth;
     for (int rep = 0; rep < 3; ++rep) { /* instances are reused frame after frame */
         FrameLike fr(imLeft, imRight, mpORBextractorLeft, mpORBextractorRight);
         if (rep == 2) {
             dump(f, fr.mvKeys, fr.mDescriptors, mpORBextractorLeft);
             dump(f, fr.mvKeysRight, fr.mDescriptorsRight, mpORBextractorRight);
+            uRight = fr.mvuRight;
+            depth = fr.mvDepth;
         }
     }
     /* monocular initialisation extractor + the empty-image convention */
@@ -123,6 +140,10 @@ int main(int argc, char **argv)
     (*mpIniORBextractor)(cv::Mat(), cv::Mat(), k, d); /* returns without touching the outputs */
     int untouched = (k.size() == before && d.rows == (int)before);
     fwrite(&untouched, 4, 1, f);
+    int ns = (int)uRight.size();
+    fwrite(&ns, 4, 1, f);
+    fwrite(uRight.data(), 4, (size_t)ns, f);
+    fwrite(depth.data(), 4, (size_t)ns, f);
     fclose(f);
     delete mpORBextractorLeft;
     delete mpORBextractorRight;

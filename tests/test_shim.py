@@ -119,3 +119,16 @@ def test_frame_like_caller_matches_oracle(shape, nf, tmp_path, oracle_built):
             assert lv[l][2] == _level_checksum(o.pyramid(l, 0))
     untouched, = struct.unpack_from("<i", buf, off)
     assert untouched == 1
+    # the stereo association the Frame-like caller ran on the device
+    ns, = struct.unpack_from("<i", buf, off + 4)
+    u = np.frombuffer(buf, "<f4", ns, off + 8)
+    z = np.frombuffer(buf, "<f4", ns, off + 8 + 4 * ns)
+    py = oracle_built
+    ol, orr = py.Oracle(nf, 1.2, 8, 20, 7), py.Oracle(nf, 1.2, 8, 20, 7)
+    kl, dl = ol.extract(left)
+    kr, dr = orr.extract(right)
+    wu, wz, _, kept = py.stereo_match(kl, dl, kr, dr, [ol.pyramid(l, 0) for l in range(8)],
+                                      [orr.pyramid(l, 0) for l in range(8)], ol.table(0), ol.table(1),
+                                      np.float32(386.1448), np.float32(386.1448) / np.float32(718.856))
+    assert ns == len(kl) and kept > 100
+    assert u.tobytes() == wu.tobytes() and z.tobytes() == wz.tobytes()
