@@ -118,7 +118,8 @@ int borb_pyramid(const borb_extractor *h, int frame, int level, const uint8_t **
  * frames): best right keypoint by descriptor distance inside the row band, 11x11 SAD refinement on
  * the two device-resident pyramids, parabola sub-pixel fit, the median-SAD outlier cut -- giving
  * mvuRight[i] and mvDepth[i] (-1 where unmatched).  mbf = baseline * fx (Frame::mbf), mb = the
- * baseline used for the search range minD = 0, maxD = mbf / mb (src/Frame.cc:651-653).  The work
+ * baseline used for the search range minD = 0, maxD = mbf / mb (src/Frame.cc:661-663; the reference reads
+ * its mb member there before its constructor assigns it, :124 vs :148 -- pass mbf/fx).  The work
  * runs on left's stream, ordered after right's; neither pyramid leaves the device.
  * The row-band bookkeeping uses (size_t)y of the LEFT keypoint exactly as the reference does. */
 int borb_stereo_match(borb_extractor *left, borb_extractor *right, float mbf, float mb, unsigned flags);
