@@ -66,6 +66,27 @@ int borb_table(const borb_extractor *h, int which, float *out);
 int borb_features_per_level(const borb_extractor *h, int32_t *out); /* mnFeaturesPerLevel */
 int borb_umax(const borb_extractor *h, int32_t *out);               /* 16 entries         */
 
+/* -- the step before the extractor (optional): replaces cv::cvtColor in Tracking::GrabImage*
+ *    (src/Tracking.cc:176-201, :213-227, :245-259) and the stereo drivers' cv::remap
+ *    (Examples/Stereo/stereo_euroc.cc:136-137), in the order the reference applies them ------ */
+
+/* channel layout of the 8-bit images handed to the extract calls from now on (default gray);
+ * RGB/BGR = the reference's Camera.RGB 1/0.  Colour frames are converted on the device with
+ * OpenCV's 8-bit formula, Y = (B*3735 + G*19235 + R*9798 + 2^14) >> 15. */
+#define BORB_GRAY8 0
+#define BORB_BGR8 1
+#define BORB_RGB8 2
+#define BORB_BGRA8 3
+#define BORB_RGBA8 4
+int borb_set_input_format(borb_extractor *h, int format);
+/* Rectification maps as cv::initUndistortRectifyMap(..., CV_32F, M1, M2) gives them: map_x/map_y
+ * [rows][map_step floats], (cols, rows) = size of the RECTIFIED image, which becomes the extractor's
+ * geometry; the extract calls' (cols, rows, step) then describe the raw source frames.  Sampling is
+ * cv::remap(INTER_LINEAR, BORDER_CONSTANT 0) bit for bit (1/32-pixel fixed point).  NULL, NULL
+ * removes the map.  The maps are copied; the call synchronises the handle. */
+int borb_set_rectify_map(borb_extractor *h, const float *map_x, const float *map_y, int cols, int rows,
+                         size_t map_step);
+
 /* -- extraction: replaces ORBextractor::operator() (src/ORBextractor.cc:1330-1397) ------------ */
 
 /* flags */

@@ -67,6 +67,19 @@ void cvp_gaussian7_sigma2(const uint8_t *src, size_t sstep, uint8_t *dst, size_t
 /* degrees in [0,360), scalar float32 polynomial, every operation individually rounded */
 float cvp_fast_atan2(float y, float x);
 
+/* -- the step before the extractor (oracle/cvprim_pre.c) -------------------- */
+
+/* cv::cvtColor to gray for 8-bit 1/3/4-channel rows; rgb_order != 0: channel 0 is R (CV_RGB2GRAY,
+ * CV_RGBA2GRAY), else channel 0 is B.  One channel: copy. */
+void cvp_cvt_gray(const uint8_t *src, size_t sstep, int cols, int rows, int channels, int rgb_order,
+                  uint8_t *dst, size_t dstep);
+
+/* cv::remap(src, dst, map_x, map_y, INTER_LINEAR), CV_32FC1 maps, BORDER_CONSTANT 0, 8-bit with
+ * `channels` interleaved channels.  map_step in floats. */
+void cvp_remap_linear(const uint8_t *src, size_t sstep, int scols, int srows, int channels,
+                      const float *map_x, const float *map_y, size_t map_step,
+                      uint8_t *dst, size_t dstep, int dcols, int drows);
+
 #ifdef __cplusplus
 }
 #endif

@@ -206,6 +206,35 @@ def stereo_match(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, mbf: float, mb:
     return u[:n], z[:n], sad[:n], kept
 
 
+def cvt_gray(img: np.ndarray, rgb_order: bool) -> np.ndarray:
+    """cv::cvtColor(..., CV_{RGB,BGR,RGBA,BGRA}2GRAY) restated (oracle/cvprim_pre.c)."""
+    lib = Oracle.load()
+    lib.cvp_cvt_gray.argtypes = [_vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_size_t]
+    img = np.ascontiguousarray(img)
+    rows, cols = img.shape[:2]
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    out = np.empty((rows, cols), np.uint8)
+    lib.cvp_cvt_gray(img.ctypes.data, img.strides[0], cols, rows, ch, int(rgb_order), out.ctypes.data, cols)
+    return out
+
+
+def remap_linear(img: np.ndarray, map_x: np.ndarray, map_y: np.ndarray) -> np.ndarray:
+    """cv::remap(img, ., map_x, map_y, INTER_LINEAR) restated (oracle/cvprim_pre.c)."""
+    lib = Oracle.load()
+    lib.cvp_remap_linear.argtypes = [_vp, C.c_size_t, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_size_t, _vp,
+                                     C.c_size_t, C.c_int, C.c_int]
+    img = np.ascontiguousarray(img)
+    map_x = np.ascontiguousarray(map_x, np.float32); map_y = np.ascontiguousarray(map_y, np.float32)
+    assert map_x.shape == map_y.shape
+    rows, cols = img.shape[:2]
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    dr, dc = map_x.shape
+    out = np.empty((dr, dc) if img.ndim == 2 else (dr, dc, ch), np.uint8)
+    lib.cvp_remap_linear(img.ctypes.data, img.strides[0], cols, rows, ch, map_x.ctypes.data, map_y.ctypes.data,
+                         dc, out.ctypes.data, dc * ch, dc, dr)
+    return out
+
+
 def describe(img: np.ndarray, x: int, y: int, angle_deg: float) -> np.ndarray:
     out = np.zeros(32, np.uint8)
     Oracle.load().orbo_describe(img.ctypes.data, img.strides[0], x, y, angle_deg, out.ctypes.data)

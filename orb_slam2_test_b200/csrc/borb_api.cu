@@ -25,6 +25,7 @@
 #include "k_blur.cuh"
 #include "k_describe.cuh"
 #include "k_fast.cuh"
+#include "k_prestep.cuh"
 #include "k_pyramid.cuh"
 #include "k_quadtree.cuh"
 #include "k_stereo.cuh"
@@ -74,10 +75,11 @@ struct GraphKey {
     int n;
     size_t step, stride;
     unsigned flags;
+    int scols, srows; /* source image size (differs from the plan's when a rectification map is set) */
     bool operator==(const GraphKey &o) const
     {
         return mode == o.mode && src == o.src && n == o.n && step == o.step && stride == o.stride &&
-               flags == o.flags;
+               flags == o.flags && scols == o.scols && srows == o.srows;
     }
 };
 struct GraphEntry {
@@ -130,6 +132,14 @@ struct borb_extractor {
     uint8_t *h_in = nullptr, *h_pyr = nullptr, *h_out_desc = nullptr;
     BorbKpRec *h_out_kp = nullptr;
     int *h_nout = nullptr, *h_err = nullptr;
+    /* the step before the extractor (K0): channel layout of the images handed in, rectification map */
+    int in_format = 0, in_ch = 1;
+    int map_cols = 0, map_rows = 0, map_pitch = 0;
+    uint32_t *d_map_xy = nullptr;
+    uint16_t *d_map_fr = nullptr;
+    uint8_t *d_gray = nullptr; /* [B][rows][gray_pitch]: K0's output, K1's input */
+    int gray_pitch = 0;
+    size_t in_cap = 0;         /* bytes per frame d_in / h_in can hold */
     /* stereo association (left handle only), allocated on first use */
     float *d_st_u = nullptr, *d_st_z = nullptr, *h_st_u = nullptr, *h_st_z = nullptr;
     int *d_st_sad = nullptr, *d_st_kept = nullptr, *h_st_kept = nullptr;
@@ -209,11 +219,13 @@ void free_geometry(borb_extractor *h)
     void *dev[] = {h->d_plan, h->d_cells, h->d_tiles, h->d_tab_i, h->d_tab_s, h->d_in, h->d_pyr,
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
-                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept};
+                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_gray};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
                     h->h_st_u, h->h_st_z, h->h_st_kept};
     for (void *p : host) if (p) cudaFreeHost(p);
+    h->d_gray = nullptr;
+    h->in_cap = 0;
     h->d_st_u = h->d_st_z = h->h_st_u = h->h_st_z = nullptr;
     h->d_st_sad = h->d_st_kept = h->h_st_kept = nullptr;
     h->stereo_on_host = false;
@@ -368,7 +380,6 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMalloc(&h->d_tiles, tiles.size() * sizeof(BorbTile)));
     CU(cudaMalloc(&h->d_tab_i, std::max<size_t>(tab_i.size(), 1) * sizeof(int)));
     CU(cudaMalloc(&h->d_tab_s, std::max<size_t>(tab_s.size(), 1) * sizeof(short)));
-    CU(cudaMalloc(&h->d_in, B * (size_t)cols * rows));
     CU(cudaMalloc(&h->d_pyr, B * (size_t)P.pyr_bytes));
     CU(cudaMalloc(&h->d_blur, B * (size_t)P.pyr_bytes));
     CU(cudaMalloc(&h->d_cand_xy, B * (size_t)P.cand_total * 4));
@@ -382,7 +393,6 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMalloc(&h->d_lkp_score, B * (size_t)P.kp_total * 4));
     CU(cudaMalloc(&h->d_out_kp, B * (size_t)P.kp_total * sizeof(BorbKpRec)));
     CU(cudaMalloc(&h->d_out_desc, B * (size_t)P.kp_total * 32));
-    CU(cudaMallocHost(&h->h_in, B * (size_t)cols * rows));
     CU(cudaMallocHost(&h->h_out_kp, B * (size_t)P.kp_total * sizeof(BorbKpRec)));
     CU(cudaMallocHost(&h->h_out_desc, B * (size_t)P.kp_total * 32));
     CU(cudaMallocHost(&h->h_nout, B * 4));
@@ -414,9 +424,11 @@ int build_plan(borb_extractor *h, int cols, int rows)
 
 namespace {
 
+bool pre_active(const borb_extractor *h) { return h->in_ch > 1 || h->d_map_xy != nullptr; }
+
 /* Enqueue the whole per-call chain for n frames whose pixels are at dev_img on the device. */
 int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t step, size_t stride,
-                    bool stage_events = false)
+                    int scols, int srows, bool stage_events = false)
 {
     stage_events = stage_events || h->stage_timing; /* inside a capture these become event-record nodes */
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
@@ -434,8 +446,11 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     if (stage_events) chunk = n; /* stage timers describe whole-batch launches */
     const int n_total = n;
     const uint8_t *const img_all = dev_img;
+    const size_t in_step = step, in_stride = stride;
     for (int f0 = 0; f0 < n_total; f0 += chunk) {
     n = std::min(chunk, n_total - f0);
+    step = in_step;
+    stride = in_stride;
     dev_img = img_all + (size_t)f0 * stride;
     uint8_t *const d_pyr = h->d_pyr + (size_t)f0 * (size_t)P.pyr_bytes, *const d_blur = h->d_blur + (size_t)f0 * (size_t)P.pyr_bytes;
     uint32_t *const d_cand_xy = h->d_cand_xy + (size_t)f0 * (size_t)P.cand_total;
@@ -448,6 +463,24 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     uint8_t *const d_out_desc = h->d_out_desc + (size_t)f0 * P.kp_total * 32;
     CU(cudaMemsetAsync(d_ncand, 0, (size_t)n * BORB_MAXL * 4, st));
     STAGE(0);
+    if (pre_active(h)) { /* K0: rectify and/or convert to gray; K1 then reads its output */
+        const int C = h->in_ch, rgb = (h->in_format == BORB_RGB8 || h->in_format == BORB_RGBA8) ? 1 : 0;
+        const size_t gstride = (size_t)h->gray_pitch * P.rows;
+        uint8_t *gray = h->d_gray + (size_t)f0 * gstride;
+        const dim3 g((P.cols + PRE_PX - 1) / PRE_PX, P.rows, n);
+        if (h->d_map_xy) {
+#define PRE_REMAP(CH) k_pre_remap<CH><<<g, PRE_NT, 0, st>>>(dev_img, step, stride, scols, srows, h->d_map_xy, h->d_map_fr, \
+                                                        h->map_pitch, rgb, gray, h->gray_pitch, gstride, P.cols)
+            if (C == 1) PRE_REMAP(1); else if (C == 3) PRE_REMAP(3); else PRE_REMAP(4);
+#undef PRE_REMAP
+        } else {
+            if (C == 3) k_pre_gray<3><<<g, PRE_NT, 0, st>>>(dev_img, step, stride, P.cols, rgb, gray, h->gray_pitch, gstride);
+            else k_pre_gray<4><<<g, PRE_NT, 0, st>>>(dev_img, step, stride, P.cols, rgb, gray, h->gray_pitch, gstride);
+        }
+        dev_img = gray;
+        step = (size_t)h->gray_pitch;
+        stride = gstride;
+    }
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         const int units = L0.pitch / 16;
@@ -625,6 +658,8 @@ void borb_destroy(borb_extractor *h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_geometry(h);
     if (h->d_pattern) cudaFree(h->d_pattern);
+    if (h->d_map_xy) cudaFree(h->d_map_xy);
+    if (h->d_map_fr) cudaFree(h->d_map_fr);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evt0) cudaEventDestroy(h->evt0);
@@ -659,15 +694,42 @@ int borb_umax(const borb_extractor *h, int32_t *out)
     return BORB_OK;
 }
 
+/* device / pinned input staging for frames of `bytes` bytes (grows on demand) */
+static int ensure_input(borb_extractor *h, size_t bytes)
+{
+    if (h->d_in && bytes <= h->in_cap) return BORB_OK;
+    CU(cudaStreamSynchronize(h->stream));
+    for (GraphEntry &g : h->graphs) cudaGraphExecDestroy(g.exec); /* they hold the old pointers */
+    h->graphs.clear();
+    if (h->d_in) cudaFree(h->d_in);
+    if (h->h_in) cudaFreeHost(h->h_in);
+    h->d_in = h->h_in = nullptr;
+    h->in_cap = 0;
+    CU(cudaMalloc(&h->d_in, (size_t)h->max_batch * bytes));
+    CU(cudaMallocHost(&h->h_in, (size_t)h->max_batch * bytes));
+    h->in_cap = bytes;
+    return BORB_OK;
+}
+
+/* cols x rows: the SOURCE image (in_ch interleaved channels); the extractor's geometry is the
+ * rectification map's when one is set */
 static int check_call(borb_extractor *h, const void *img, int n, int cols, int rows, size_t step,
                       size_t stride)
 {
     if (!h || !img) return fail(BORB_ERR_ARG, "null handle or image");
-    if (n < 1 || cols < 1 || rows < 1 || step < (size_t)cols || (n > 1 && stride < step * (size_t)(rows - 1) + cols))
+    const size_t row_bytes = (size_t)cols * h->in_ch;
+    if (n < 1 || cols < 1 || rows < 1 || step < row_bytes || (n > 1 && stride < step * (size_t)(rows - 1) + row_bytes))
         return fail(BORB_ERR_ARG, "bad image geometry");
     if (n > h->max_batch) return fail(BORB_ERR_CAPACITY, "%d frames > max_batch %d", n, h->max_batch);
     CU(cudaSetDevice(h->device));
-    return build_plan(h, cols, rows);
+    const int ocols = h->d_map_xy ? h->map_cols : cols, orows = h->d_map_xy ? h->map_rows : rows;
+    int rc = build_plan(h, ocols, orows);
+    if (rc != BORB_OK) return rc;
+    if (pre_active(h) && !h->d_gray) {
+        h->gray_pitch = (ocols + 3) & ~3;
+        CU(cudaMalloc(&h->d_gray, (size_t)h->max_batch * h->gray_pitch * orows));
+    }
+    return BORB_OK;
 }
 
 int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int rows, size_t step,
@@ -677,13 +739,14 @@ int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int
     if (rc != BORB_OK) return rc;
     if (h->pending) return fail(BORB_ERR_STATE, "previous submit has not been waited for");
     if ((flags & BORB_WANT_PYRAMID) && (rc = ensure_pyr_host(h)) != BORB_OK) return rc;
-    const size_t fsz = (size_t)cols * rows;
+    const size_t rowb = (size_t)cols * h->in_ch, fsz = rowb * rows;
+    if ((rc = ensure_input(h, fsz)) != BORB_OK) return rc;
     /* Caller memory that is already page-locked (borb_host_alloc / cudaHostRegister) and densely
      * packed is copied to the device directly; anything else -- the reference's callers hand over
      * ordinary pageable cv::Mat data -- is first packed into the handle's pinned staging area. */
     const uint8_t *src = h->h_in;
     bool direct = false;
-    if (step == (size_t)cols && (n == 1 || stride == fsz)) {
+    if (step == rowb && (n == 1 || stride == fsz)) {
         cudaPointerAttributes at;
         if (cudaPointerGetAttributes(&at, img) == cudaSuccess && at.type == cudaMemoryTypeHost) {
             direct = true;
@@ -696,13 +759,13 @@ int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int
         for (int f = 0; f < n; ++f) {
             const uint8_t *s = img + (size_t)f * stride;
             uint8_t *d = h->h_in + (size_t)f * fsz;
-            if (step == (size_t)cols) std::memcpy(d, s, fsz);
-            else for (int y = 0; y < rows; ++y) std::memcpy(d + (size_t)y * cols, s + (size_t)y * step, (size_t)cols);
+            if (step == rowb) std::memcpy(d, s, fsz);
+            else for (int y = 0; y < rows; ++y) std::memcpy(d + (size_t)y * rowb, s + (size_t)y * step, rowb);
         }
-    GraphKey key = {0, direct ? (const void *)img : nullptr, n, 0, 0, flags};
+    GraphKey key = {0, direct ? (const void *)img : nullptr, n, 0, 0, flags, cols, rows};
     rc = run_cached(h, key, [&]() -> int {
         CU(cudaMemcpyAsync(h->d_in, src, (size_t)n * fsz, cudaMemcpyHostToDevice, h->stream));
-        int r = enqueue_kernels(h, h->d_in, n, (size_t)cols, fsz);
+        int r = enqueue_kernels(h, h->d_in, n, rowb, fsz, cols, rows);
         if (r != BORB_OK) return r;
         return enqueue_fetch(h, n, flags);
     });
@@ -780,7 +843,7 @@ int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n, int cols,
     int rc = check_call(h, dev_img, n, cols, rows, step, stride);
     if (rc != BORB_OK) return rc;
     if (!ms) return fail(BORB_ERR_ARG, "ms is null");
-    rc = enqueue_kernels(h, dev_img, n, step, stride, true);
+    rc = enqueue_kernels(h, dev_img, n, step, stride, cols, rows, true);
     if (rc != BORB_OK) return rc;
     CU(cudaStreamSynchronize(h->stream));
     for (int i = 0; i < 5; ++i) CU(cudaEventElapsedTime(&ms[i], h->evs[i], h->evs[i + 1]));
@@ -794,9 +857,9 @@ int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int co
 {
     int rc = check_call(h, dev_img, n, cols, rows, step, stride);
     if (rc != BORB_OK) return rc;
-    GraphKey key = {1, dev_img, n, step, stride, 0};
+    GraphKey key = {1, dev_img, n, step, stride, 0, cols, rows};
     CU(cudaEventRecord(h->ev0, h->stream));
-    rc = run_cached(h, key, [&]() -> int { return enqueue_kernels(h, dev_img, n, step, stride); });
+    rc = run_cached(h, key, [&]() -> int { return enqueue_kernels(h, dev_img, n, step, stride, cols, rows); });
     if (rc != BORB_OK) return rc;
     CU(cudaEventRecord(h->ev1, h->stream));
     h->last_n = n;
@@ -877,6 +940,67 @@ int borb_counts(const borb_extractor *h, int32_t *out)
 {
     if (!h || !out || !h->results_on_host) return fail(BORB_ERR_STATE, "no results on the host");
     std::memcpy(out, h->h_nout, (size_t)h->last_n * 4);
+    return BORB_OK;
+}
+
+/* -- the step before the extractor (K0) -- */
+int borb_set_input_format(borb_extractor *h, int format)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    if (format < BORB_GRAY8 || format > BORB_RGBA8) return fail(BORB_ERR_ARG, "unknown pixel format %d", format);
+    if (h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    for (GraphEntry &g : h->graphs) cudaGraphExecDestroy(g.exec);
+    h->graphs.clear();
+    h->in_format = format;
+    h->in_ch = format == BORB_GRAY8 ? 1 : (format == BORB_BGR8 || format == BORB_RGB8) ? 3 : 4;
+    return BORB_OK;
+}
+
+int borb_set_rectify_map(borb_extractor *h, const float *map_x, const float *map_y, int cols, int rows,
+                         size_t map_step)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    if (h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    for (GraphEntry &g : h->graphs) cudaGraphExecDestroy(g.exec);
+    h->graphs.clear();
+    if (h->d_map_xy) cudaFree(h->d_map_xy);
+    if (h->d_map_fr) cudaFree(h->d_map_fr);
+    h->d_map_xy = nullptr;
+    h->d_map_fr = nullptr;
+    h->map_cols = h->map_rows = h->map_pitch = 0;
+    if (!map_x && !map_y) return BORB_OK; /* map cleared */
+    if (!map_x || !map_y || cols < 1 || rows < 1 || map_step < (size_t)cols)
+        return fail(BORB_ERR_ARG, "bad rectification map");
+    /* cv::remap's own first step (convertMaps to 1/32-pixel fixed point), done once here:
+     * s = cvRound(map * 32) with the product in float; values outside int range (and NaN) go far
+     * outside every image, where all four taps read the constant border */
+    const int pitch = (cols + 3) & ~3;
+    std::vector<uint32_t> xy((size_t)pitch * rows, 0x80008000u);
+    std::vector<uint16_t> fr((size_t)pitch * rows, 0);
+    auto fix = [](float m) -> int {
+        const float v = m * 32.f;
+        if (!(v > -1073741824.f)) return -1073741824; /* also NaN */
+        if (v > 1073741824.f) return 1073741824;
+        return (int)lrintf(v);
+    };
+    auto sat = [](int v) -> int { return v < -32768 ? -32768 : v > 32767 ? 32767 : v; };
+    for (int y = 0; y < rows; ++y)
+        for (int x = 0; x < cols; ++x) {
+            const int sx = fix(map_x[(size_t)y * map_step + x]), sy = fix(map_y[(size_t)y * map_step + x]);
+            xy[(size_t)y * pitch + x] = (uint32_t)(sat(sx >> 5) & 0xffff) | ((uint32_t)(sat(sy >> 5) & 0xffff) << 16);
+            fr[(size_t)y * pitch + x] = (uint16_t)(((sy & 31) << 5) | (sx & 31));
+        }
+    CU(cudaMalloc(&h->d_map_xy, xy.size() * 4));
+    CU(cudaMalloc(&h->d_map_fr, fr.size() * 2));
+    CU(cudaMemcpy(h->d_map_xy, xy.data(), xy.size() * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_map_fr, fr.data(), fr.size() * 2, cudaMemcpyHostToDevice));
+    h->map_cols = cols;
+    h->map_rows = rows;
+    h->map_pitch = pitch;
     return BORB_OK;
 }
 

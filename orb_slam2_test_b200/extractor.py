@@ -36,7 +36,7 @@ SYMBOLS = [
     "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score",
     "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
-    "borb_stereo_match", "borb_stereo_result",
+    "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
 ]
 
 
@@ -97,6 +97,8 @@ def load_library() -> C.CDLL:
     lib.borb_counts.argtypes = [_vp, _vp]
     lib.borb_set_stage_timing.argtypes = [_vp, C.c_int]
     lib.borb_last_stage_ms.argtypes = [_vp, _vp]
+    lib.borb_set_input_format.argtypes = [_vp, C.c_int]
+    lib.borb_set_rectify_map.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_size_t]
     lib.borb_stereo_match.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_uint]
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
                                        C.POINTER(C.c_int)]
@@ -137,6 +139,35 @@ class ORBextractor:
         self.want_pyramid = want_pyramid
         self.mvImagePyramid: list[np.ndarray] = []
         self._n = 0
+        self._ch = 1
+
+    # -- the step before the extractor: cvtColor (src/Tracking.cc:176-201) and cv::remap
+    #    (Examples/Stereo/stereo_euroc.cc:136-137) on the device --
+    FORMATS = {"gray": (0, 1), "bgr": (1, 3), "rgb": (2, 3), "bgra": (3, 4), "rgba": (4, 4)}
+
+    def set_input_format(self, fmt: str) -> None:
+        code, ch = self.FORMATS[fmt]
+        _check(self._lib, self._lib.borb_set_input_format(self._h, code))
+        self._ch = ch
+
+    def set_rectify_map(self, map_x: np.ndarray | None, map_y: np.ndarray | None) -> None:
+        """CV_32F maps of cv::initUndistortRectifyMap; their shape is the rectified image's."""
+        if map_x is None and map_y is None:
+            _check(self._lib, self._lib.borb_set_rectify_map(self._h, None, None, 0, 0, 0))
+            return
+        map_x = np.ascontiguousarray(map_x, np.float32)
+        map_y = np.ascontiguousarray(map_y, np.float32)
+        assert map_x.shape == map_y.shape and map_x.ndim == 2
+        rows, cols = map_x.shape
+        _check(self._lib, self._lib.borb_set_rectify_map(self._h, map_x.ctypes.data, map_y.ctypes.data, cols,
+                                                         rows, cols))
+
+    def _check_image(self, shape, ndim_gray: int):
+        if self._ch == 1:
+            if len(shape) != ndim_gray:
+                raise TypeError("image must be CV_8UC1 (2-D uint8)")  # reference: assert, :1337
+        elif len(shape) != ndim_gray + 1 or shape[-1] != self._ch:
+            raise TypeError(f"image must have {self._ch} interleaved channels")
 
     def close(self) -> None:
         if getattr(self, "_h", None):
@@ -188,11 +219,12 @@ class ORBextractor:
         """mask is ignored, as in the reference (include/ORBextractor.h:72)."""
         if image is None or image.size == 0:
             return None  # the reference returns without touching its outputs (:1333-1334)
-        if image.dtype != np.uint8 or image.ndim != 2:
+        if image.dtype != np.uint8:
             raise TypeError("image must be CV_8UC1 (2-D uint8)")  # reference: assert, :1337
-        if image.strides[1] != 1:
+        self._check_image(image.shape, 2)
+        if image.strides[-1] != 1 or (image.ndim == 3 and image.strides[1] != self._ch):
             image = np.ascontiguousarray(image)
-        rows, cols = image.shape
+        rows, cols = image.shape[:2]
         flags = BORB_WANT_PYRAMID if self.want_pyramid else 0
         _check(self._lib, self._lib.borb_extract_host(self._h, image.ctypes.data, 1, cols, rows,
                                                       image.strides[0], 0, flags))
@@ -202,18 +234,21 @@ class ORBextractor:
         return self.result(0)
 
     def extract_batch(self, images: np.ndarray, want_pyramid: bool = False):
-        """images: [n, rows, cols] uint8, C-contiguous.  Returns a list of (kps, desc)."""
-        assert images.dtype == np.uint8 and images.ndim == 3 and images.flags.c_contiguous
-        n, rows, cols = images.shape
-        _check(self._lib, self._lib.borb_extract_host(self._h, images.ctypes.data, n, cols, rows, cols,
-                                                      rows * cols, BORB_WANT_PYRAMID if want_pyramid else 0))
+        """images: [n, rows, cols] (or [n, rows, cols, channels]) uint8, C-contiguous.  Returns a list
+        of (kps, desc)."""
+        assert images.dtype == np.uint8 and images.flags.c_contiguous
+        self._check_image(images.shape, 3)
+        n, rows, cols = images.shape[:3]
+        _check(self._lib, self._lib.borb_extract_host(self._h, images.ctypes.data, n, cols, rows, cols * self._ch,
+                                                      rows * cols * self._ch,
+                                                      BORB_WANT_PYRAMID if want_pyramid else 0))
         self._n = n
         return [self.result(f) for f in range(n)]
 
     def extract_device(self, dev_ptr: int, n: int, cols: int, rows: int, step: int | None = None,
                        frame_stride: int | None = None) -> None:
         """Frames already in device memory (e.g. tensor.data_ptr()); asynchronous."""
-        step = cols if step is None else step
+        step = cols * self._ch if step is None else step
         frame_stride = rows * step if frame_stride is None else frame_stride
         _check(self._lib, self._lib.borb_extract_device(self._h, dev_ptr, n, cols, rows, step, frame_stride))
         self._n = n
@@ -224,10 +259,12 @@ class ORBextractor:
 
     def submit_batch(self, images: np.ndarray, want_pyramid: bool = False) -> None:
         """Asynchronous half of extract_batch; pair with wait()."""
-        assert images.dtype == np.uint8 and images.ndim == 3 and images.flags.c_contiguous
-        n, rows, cols = images.shape
-        _check(self._lib, self._lib.borb_submit_host(self._h, images.ctypes.data, n, cols, rows, cols,
-                                                     rows * cols, BORB_WANT_PYRAMID if want_pyramid else 0))
+        assert images.dtype == np.uint8 and images.flags.c_contiguous
+        self._check_image(images.shape, 3)
+        n, rows, cols = images.shape[:3]
+        _check(self._lib, self._lib.borb_submit_host(self._h, images.ctypes.data, n, cols, rows, cols * self._ch,
+                                                     rows * cols * self._ch,
+                                                     BORB_WANT_PYRAMID if want_pyramid else 0))
         self._n = n
 
     def wait(self) -> None:

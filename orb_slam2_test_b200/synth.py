@@ -99,3 +99,58 @@ def make_noise_frame(shape, seed: int = 0) -> np.ndarray:
 def make_sequence(shape=KITTI_SHAPE, seed: int = 0, start: int = 0, count: int = 1, eye: int = 0) -> np.ndarray:
     """[count, rows, cols] uint8, frames start .. start+count-1 of the sequence `seed`."""
     return np.stack([make_frame(shape, seed, start + i, eye) for i in range(count)])
+
+
+# ---- inputs for the step before the extractor (colour frames, stereo rectification maps) -------
+
+EUROC_SHAPE = (480, 752)
+# (K, D, R, P) of the left and right camera, Examples/Stereo/EuRoC.yaml (LEFT.* / RIGHT.*)
+EUROC = (
+    ([458.654, 0.0, 367.215, 0.0, 457.296, 248.375, 0.0, 0.0, 1.0],
+     [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0],
+     [0.999966347530033, -0.001422739138722922, 0.008079580483432283, 0.001365741834644127, 0.9999741760894847,
+      0.007055629199258132, -0.008089410156878961, -0.007044357138835809, 0.9999424675829176],
+     [435.2046959714599, 0, 367.4517211914062, 0, 0, 435.2046959714599, 252.2008514404297, 0, 0, 0, 1, 0]),
+    ([457.587, 0.0, 379.999, 0.0, 456.134, 255.238, 0.0, 0.0, 1],
+     [-0.28368365, 0.07451284, -0.00010473, -3.555907e-05, 0.0],
+     [0.9999633526194376, -0.003625811871560086, 0.007755443660172947, 0.003680398547259526, 0.9999684752771629,
+      -0.007035845251224894, -0.007729688520722713, 0.007064130529506649, 0.999945173484644],
+     [435.2046959714599, 0, 367.4517211914062, -47.90639384423901, 0, 435.2046959714599, 252.2008514404297, 0,
+      0, 0, 1, 0]),
+)
+
+
+def rectify_maps(K, D, R, P, size):
+    """float32 (map_x, map_y) of shape (rows, cols): where each rectified pixel samples the raw
+    image -- the quantity cv::initUndistortRectifyMap(K, D, R, P, size, CV_32F, M1, M2) produces
+    (Examples/Stereo/stereo_euroc.cc:107-108).  The maps are INPUT DATA of the remap step; this is a
+    plain float64 evaluation of the pinhole + radial/tangential model, not a bit-level restatement."""
+    cols, rows = size
+    K = np.asarray(K, np.float64).reshape(3, 3)
+    R = np.asarray(R, np.float64).reshape(3, 3)
+    P = np.asarray(P, np.float64).reshape(3, 4)[:, :3]
+    k1, k2, p1, p2, k3 = (list(D) + [0.0] * 5)[:5]
+    ir = np.linalg.inv(P @ R)
+    u, v = np.meshgrid(np.arange(cols, dtype=np.float64), np.arange(rows, dtype=np.float64))
+    X = ir[0, 0] * u + ir[0, 1] * v + ir[0, 2]
+    Y = ir[1, 0] * u + ir[1, 1] * v + ir[1, 2]
+    Wd = ir[2, 0] * u + ir[2, 1] * v + ir[2, 2]
+    x, y = X / Wd, Y / Wd
+    r2 = x * x + y * y
+    kr = 1 + ((k3 * r2 + k2) * r2 + k1) * r2
+    xd = x * kr + 2 * p1 * x * y + p2 * (r2 + 2 * x * x)
+    yd = y * kr + p1 * (r2 + 2 * y * y) + 2 * p2 * x * y
+    return ((K[0, 0] * xd + K[0, 2]).astype(np.float32), (K[1, 1] * yd + K[1, 2]).astype(np.float32))
+
+
+def make_color_frame(shape=TUM_SHAPE, seed: int = 0, frame: int = 0, eye: int = 0, channels: int = 3) -> np.ndarray:
+    """[rows, cols, channels] uint8: the gray synthetic frame with a smooth per-channel tint and
+    independent per-channel noise (so the three channels differ and the weights matter)."""
+    g = make_frame(shape, seed, frame, eye).astype(np.float32)
+    rng = _rng(seed, frame + 7, eye + 2)
+    rows, cols = g.shape
+    out = np.empty((rows, cols, channels), np.uint8)
+    for c in range(channels):
+        tint = _value_noise(rng, rows, cols, 64, 30.0)
+        out[..., c] = np.clip(np.rint(g * (0.8 + 0.1 * c) + tint + rng.uniform(-3, 3, g.shape)), 0, 255).astype(np.uint8)
+    return out

@@ -136,3 +136,54 @@ def test_threshold_fallback_identity(lib):
         assert k20 == [k for k in k7 if k[2] >= 20]
         checked += n7
     assert checked > 2000
+
+
+# ---- the step before the extractor: cvtColor and remap -------------------
+
+@pytest.mark.parametrize("code,ch,rgb", [("COLOR_BGR2GRAY", 3, False), ("COLOR_RGB2GRAY", 3, True),
+                                         ("COLOR_BGRA2GRAY", 4, False), ("COLOR_RGBA2GRAY", 4, True)])
+def test_cvt_gray_matches_cv2(code, ch, rgb, oracle_built):
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 256, (97, 333, ch), dtype=np.uint8)
+    assert np.array_equal(oracle_built.cvt_gray(img, rgb), cv2.cvtColor(img, getattr(cv2, code)))
+
+
+def test_cvt_gray_exhaustive(oracle_built):
+    v = np.arange(256, dtype=np.uint8)
+    full = np.stack(np.meshgrid(v, v, v, indexing="ij"), -1).reshape(4096, 4096, 3)
+    assert np.array_equal(oracle_built.cvt_gray(full, False), cv2.cvtColor(full, cv2.COLOR_BGR2GRAY))
+
+
+def _euroc_maps(eye):
+    from orb_slam2_test_b200 import synth
+    K, D, R, P = synth.EUROC[eye]
+    m1, m2 = cv2.initUndistortRectifyMap(np.array(K).reshape(3, 3), np.array(D), np.array(R).reshape(3, 3),
+                                         np.array(P).reshape(3, 4)[:, :3], (752, 480), cv2.CV_32F)
+    return m1, m2
+
+
+@pytest.mark.parametrize("ch", [1, 3, 4])
+def test_remap_matches_cv2(ch, oracle_built):
+    rng = np.random.default_rng(12 + ch)
+    src = rng.integers(0, 256, (120, 200) if ch == 1 else (120, 200, ch), dtype=np.uint8)
+    h, w = 100, 180
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    cases = [((xx * 1.07 - 8 + rng.normal(0, 1.5, (h, w))).astype(np.float32),
+              (yy * 1.15 - 6 + rng.normal(0, 1.5, (h, w))).astype(np.float32)),
+             (rng.uniform(-5, 205, (h, w)).astype(np.float32), rng.uniform(-5, 125, (h, w)).astype(np.float32)),
+             (xx + np.float32(1 / 64), yy + np.float32(3 / 64)),            # ties of the 1/32 quantisation
+             (rng.uniform(-7e4, 7e4, (h, w)).astype(np.float32), rng.uniform(-7e4, 7e4, (h, w)).astype(np.float32))]
+    for mx, my in cases:
+        assert np.array_equal(oracle_built.remap_linear(src, mx, my), cv2.remap(src, mx, my, cv2.INTER_LINEAR))
+
+
+@pytest.mark.parametrize("eye", [0, 1])
+def test_remap_euroc_rectification_matches_cv2(eye, oracle_built):
+    """The call of Examples/Stereo/stereo_euroc.cc:136-137 with the maps of :107-108."""
+    from orb_slam2_test_b200 import synth
+    m1, m2 = _euroc_maps(eye)
+    img = synth.make_frame((480, 752), seed=40, eye=eye)
+    assert np.array_equal(oracle_built.remap_linear(img, m1, m2), cv2.remap(img, m1, m2, cv2.INTER_LINEAR))
+    # the package's own map generator (inputs for the GPU tests) agrees with OpenCV's to float rounding
+    x, y = synth.rectify_maps(*synth.EUROC[eye], size=(752, 480))
+    assert np.abs(x - m1).max() < 1e-3 and np.abs(y - m2).max() < 1e-3
