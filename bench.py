@@ -224,6 +224,50 @@ def ncu_traffic(kernel: str, frames: int):
         return None
 
 
+def prestep_section(ORBextractor, synth, local, peak):
+    """colour conversion and stereo rectification in front of the pyramid (K0).
+    Device-resident raw frames; K0 is timed by events inside the real calls.  Algorithmic bytes per
+    output pixel: C source bytes + 1 written (+ 6 map bytes when rectifying, L2-resident across
+    frames: the map is shared by every frame of the batch)."""
+    import torch
+    out = {"reference": "src/Tracking.cc:176-201 (cvtColor), Examples/Stereo/stereo_euroc.cc:136-137 (remap)",
+           "parity": "bit-exact against oracle/cvprim_pre.c, which is pinned to cv2 4.13.0"}
+    n = 128
+
+    def run(name, frames, fmt, maps, nfeat):
+        dev = torch.from_numpy(frames).cuda(local)
+        rows, cols = frames.shape[1:3]
+        ch = 1 if frames.ndim == 3 else frames.shape[3]
+        ext = ORBextractor(nfeat, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=n, want_pyramid=False)
+        ext.set_input_format(fmt)
+        if maps is not None:
+            ext.set_rectify_map(*maps)
+        ext.set_stage_timing(True)
+        ms, tot = [], []
+        for it in range(8):
+            ext.timer_start()
+            ext.extract_device(dev.data_ptr(), n, cols, rows)
+            ext.timer_stop()
+            ext.sync()
+            if it >= 3:
+                ms.append(ext.last_prestep_ms())
+                tot.append(ext.timer_ms())
+        k0 = float(np.median(ms))
+        opix = (maps[0].size if maps is not None else rows * cols)
+        alg = n * (rows * cols * ch + opix)
+        out[name] = {"frames": n, "k0_ms": k0, "call_ms": float(np.median(tot)), "frames_per_s": n / (float(np.median(tot)) / 1e3),
+                     "k0_GBps": alg / (k0 / 1e3) / 1e9, "k0_frac_of_hbm_peak": alg / (k0 / 1e3) / 1e9 / peak,
+                     "algorithmic_bytes": alg}
+        del ext, dev
+
+    kitti = np.stack([synth.make_color_frame((ROWS, COLS), seed=7, frame=f % 8) for f in range(8)])
+    run("bgr_to_gray_kitti", np.ascontiguousarray(kitti[np.arange(n) % 8]), "bgr", None, NFEATURES)
+    euroc = np.stack([synth.make_frame(synth.EUROC_SHAPE, seed=40, frame=f) for f in range(8)])
+    maps = synth.rectify_maps(*synth.EUROC[0], size=(752, 480))
+    run("rectify_euroc_gray", np.ascontiguousarray(euroc[np.arange(n) % 8]), "gray", maps, 1200)
+    return out
+
+
 def stereo_section(ORBextractor, synth, local, two, dev):
     """SURVEY.md 8(f)-1: Frame::ComputeStereoMatches on the device (borb_stereo_match).  Reported
     beside the headline, not part of `value`: (1) a stereo pair through the host ABI with the match on
@@ -429,7 +473,7 @@ def run_ours(args, rank, world, local):
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
-    stereo = None
+    stereo = prestep = None
     if rank == 0:
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
@@ -469,6 +513,7 @@ def run_ours(args, rank, world, local):
                 ts.append((time.perf_counter() - t1) * 1e6)
         lat["stereo_pair_p50_us_with_pyramids"] = float(np.percentile(ts, 50))
         stereo = stereo_section(ORBextractor, synth, local, two, dev)
+        prestep = prestep_section(ORBextractor, synth, local, measured_peak()[0])
 
     if rank != 0:
         return
@@ -510,6 +555,7 @@ def run_ours(args, rank, world, local):
         "cpu_baseline": cpu,
         "latency": lat,
         "stereo": stereo,
+        "prestep": prestep,
         "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,
     }

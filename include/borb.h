@@ -172,6 +172,9 @@ int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n_frames, in
  * borb_last_stage_ms() returns those of the most recent call (ms[0..4] as above). */
 int borb_set_stage_timing(borb_extractor *h, int on);
 int borb_last_stage_ms(borb_extractor *h, float *ms);
+/* time of the pre-step kernel (colour conversion / rectification) inside the last call's pyramid
+ * stage, milliseconds; < 0 when stage timing is off or no pre-step is configured */
+float borb_last_prestep_ms(borb_extractor *h);
 
 /* -- stage taps for parity tests (device -> caller buffers; not part of the hot path) -------- */
 /* FAST candidates of (frame, level) before distribution, coords relative to (16,16);

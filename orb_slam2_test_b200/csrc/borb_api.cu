@@ -480,6 +480,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         dev_img = gray;
         step = (size_t)h->gray_pitch;
         stride = gstride;
+        STAGE(6); /* K0 = evs[0] .. evs[6]; the pyramid stage time includes it */
     }
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
@@ -923,7 +924,19 @@ int borb_last_stage_ms(borb_extractor *h, float *ms)
     return BORB_OK;
 }
 
-int borb_launches_per_call(const borb_extractor *h) { return h ? h->nlevels + 4 : 0; }
+float borb_last_prestep_ms(borb_extractor *h)
+{
+    float ms = -1.f;
+    if (!h || !h->stage_timing || !pre_active(h)) return -1.f;
+    if (cudaSetDevice(h->device) != cudaSuccess || cudaStreamSynchronize(h->stream) != cudaSuccess ||
+        cudaEventElapsedTime(&ms, h->evs[0], h->evs[6]) != cudaSuccess) {
+        cudaGetLastError();
+        return -1.f;
+    }
+    return ms;
+}
+
+int borb_launches_per_call(const borb_extractor *h) { return h ? h->nlevels + 4 + (pre_active(h) ? 1 : 0) : 0; }
 
 int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps, const uint8_t **desc, int *n)
 {

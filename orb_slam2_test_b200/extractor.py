@@ -37,6 +37,7 @@ SYMBOLS = [
     "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
     "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
+    "borb_last_prestep_ms",
 ]
 
 
@@ -97,6 +98,8 @@ def load_library() -> C.CDLL:
     lib.borb_counts.argtypes = [_vp, _vp]
     lib.borb_set_stage_timing.argtypes = [_vp, C.c_int]
     lib.borb_last_stage_ms.argtypes = [_vp, _vp]
+    lib.borb_last_prestep_ms.argtypes = [_vp]
+    lib.borb_last_prestep_ms.restype = C.c_float
     lib.borb_set_input_format.argtypes = [_vp, C.c_int]
     lib.borb_set_rectify_map.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_size_t]
     lib.borb_stereo_match.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_uint]
@@ -161,6 +164,9 @@ class ORBextractor:
         rows, cols = map_x.shape
         _check(self._lib, self._lib.borb_set_rectify_map(self._h, map_x.ctypes.data, map_y.ctypes.data, cols,
                                                          rows, cols))
+
+    def last_prestep_ms(self) -> float:
+        return self._lib.borb_last_prestep_ms(self._h)
 
     def _check_image(self, shape, ndim_gray: int):
         if self._ch == 1:

@@ -31,7 +31,8 @@ void check(int rc, const char *what)
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST),
-      minThFAST(_minThFAST), handle(NULL), device(0), downloadPyramid(true)
+      minThFAST(_minThFAST), handle(NULL), device(0), downloadPyramid(true), colorInput(false), colorRGB(false),
+      inputFormat(BORB_GRAY8)
 {
     if (const char *d = std::getenv("BORB_DEVICE")) device = std::atoi(d);
     check(borb_create(nfeatures, _scaleFactor, nlevels, iniThFAST, minThFAST, device, 1, &handle), "create");
@@ -63,7 +64,16 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
         return;
 
     cv::Mat image = _image.getMat();
-    assert(image.type() == CV_8UC1);
+    assert(image.type() == CV_8UC1 || (colorInput && (image.type() == CV_8UC3 || image.type() == CV_8UC4)));
+
+    // colour frames are converted on the device (extension, see SetColorInput)
+    const int format = image.type() == CV_8UC1 ? BORB_GRAY8
+                       : image.type() == CV_8UC3 ? (colorRGB ? BORB_RGB8 : BORB_BGR8)
+                                                 : (colorRGB ? BORB_RGBA8 : BORB_BGRA8);
+    if (format != inputFormat) {
+        check(borb_set_input_format(handle, format), "input format");
+        inputFormat = format;
+    }
 
     // rows of a non-continuous cv::Mat (ROI) are image.step bytes apart; the library packs them
     check(borb_extract_host(handle, image.data, 1, image.cols, image.rows, (size_t)image.step, 0,
@@ -102,6 +112,19 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
             mvImagePyramid[level] = cv::Mat(rows, cols, CV_8UC1, (void *)data, step);
         }
     }
+}
+
+void ORBextractor::SetRectifyMap(const cv::Mat &M1, const cv::Mat &M2)
+{
+    if (M1.empty() && M2.empty()) {
+        check(borb_set_rectify_map(handle, NULL, NULL, 0, 0, 0), "rectify map");
+        return;
+    }
+    assert(M1.type() == CV_32FC1 && M2.type() == CV_32FC1 && M1.rows == M2.rows && M1.cols == M2.cols &&
+           M1.step == M2.step);
+    check(borb_set_rectify_map(handle, (const float *)M1.data, (const float *)M2.data, M1.cols, M1.rows,
+                               (size_t)M1.step / sizeof(float)),
+          "rectify map");
 }
 
 void ORBextractor::ComputeStereoMatches(ORBextractor &right, float mbf, float mb, std::vector<float> &mvuRight,

@@ -81,6 +81,15 @@ public:
     // Mono / RGB-D callers never read mvImagePyramid; turning the download off saves the
     // device-to-host copy of the 8 levels.  Default: on (stereo matching needs it).
     void SetPyramidDownload(bool on) { downloadPyramid = on; }
+    // The step before the extractor, on the device.  (1) Colour frames: with colour input enabled,
+    // operator() also accepts CV_8UC3 / CV_8UC4 images and converts them exactly as
+    // Tracking::GrabImage* does with cv::cvtColor (reference src/Tracking.cc:176-201); rgb = the
+    // settings file's Camera.RGB.  (2) Stereo rectification: M1, M2 are the CV_32F maps of
+    // cv::initUndistortRectifyMap; operator() then takes the RAW frame and rectifies it exactly as
+    // cv::remap(im, rect, M1, M2, cv::INTER_LINEAR) does (Examples/Stereo/stereo_euroc.cc:136-137).
+    // Empty maps remove the rectification.
+    void SetColorInput(bool enabled, bool rgb) { colorInput = enabled; colorRGB = rgb; }
+    void SetRectifyMap(const cv::Mat &M1, const cv::Mat &M2);
     // Frame::ComputeStereoMatches (reference src/Frame.cc:619-834) on the device, for *this as the
     // left extractor: fills mvuRight / mvDepth (size = left keypoint count, -1 where unmatched)
     // from the last operator() results of both instances.  Call it after both extraction threads
@@ -111,6 +120,8 @@ private:
     borb_extractor *handle;
     int device;
     bool downloadPyramid;
+    bool colorInput, colorRGB;
+    int inputFormat; // BORB_* format the handle is currently set to
 };
 
 } // namespace ORB_SLAM2

@@ -2,7 +2,7 @@
  * nocv/opencv2/core/core.hpp -- build-only stand-in for <opencv2/core/core.hpp>.
  *
  * This image (and the GPU box) has no OpenCV C++ headers or libraries.  The host shim
- * (../../ORBextractor.{h,cc}) touches only four OpenCV types -- cv::Mat (8-bit single channel),
+ * (../../ORBextractor.{h,cc}) touches only four OpenCV types -- cv::Mat (8-bit 1/3/4 channels, float maps),
  * cv::KeyPoint, cv::InputArray, cv::OutputArray -- and a caller written like the reference's
  * Frame.cc additionally uses Mat::rowRange/colRange/at/ptr.  This header declares exactly that
  * slice with OpenCV's public semantics so the shim and its link test can be compiled here.  With a
@@ -19,6 +19,10 @@
 
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_8UC3 16
+#define CV_8UC4 24
+#define CV_32F 5
+#define CV_32FC1 5
 #define BORB_NOCV 1
 
 typedef unsigned char uchar;
@@ -51,29 +55,32 @@ public:
     uchar *data;
     size_t step;
 
-    Mat() : rows(0), cols(0), data(NULL), step(0) {}
-    Mat(int r, int c, int type) : rows(0), cols(0), data(NULL), step(0) { create(r, c, type); }
-    Mat(int r, int c, int, void *ext, size_t ext_step = 0)
-        : rows(r), cols(c), data((uchar *)ext), step(ext_step ? ext_step : (size_t)c) {}
+    Mat() : rows(0), cols(0), data(NULL), step(0), type_(CV_8UC1) {}
+    Mat(int r, int c, int type) : rows(0), cols(0), data(NULL), step(0), type_(type) { create(r, c, type); }
+    Mat(int r, int c, int type, void *ext, size_t ext_step = 0)
+        : rows(r), cols(c), data((uchar *)ext), step(0), type_(type) { step = ext_step ? ext_step : (size_t)c * elemSize(); }
 
-    void create(int r, int c, int)
+    void create(int r, int c, int type)
     {
-        if (data && own_ && r == rows && c == cols) return;
-        rows = r; cols = c; step = (size_t)c;
-        own_.reset(new uchar[(size_t)r * c + 1], std::default_delete<uchar[]>());
+        if (data && own_ && r == rows && c == cols && type == type_) return;
+        type_ = type;
+        rows = r; cols = c; step = (size_t)c * elemSize();
+        own_.reset(new uchar[(size_t)r * step + 1], std::default_delete<uchar[]>());
         data = own_.get();
     }
     void release() { own_.reset(); data = NULL; rows = cols = 0; step = 0; }
     bool empty() const { return !data || rows == 0 || cols == 0; }
-    int type() const { return CV_8UC1; }
-    bool isContinuous() const { return step == (size_t)cols || rows <= 1; }
+    int type() const { return type_; }
+    int channels() const { return (type_ >> 3) + 1; }
+    size_t elemSize() const { return (size_t)channels() * ((type_ & 7) == CV_32F ? 4 : 1); }
+    bool isContinuous() const { return step == (size_t)cols * elemSize() || rows <= 1; }
 
     Mat rowRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * step; m.rows = b - a; return m; }
-    Mat colRange(int a, int b) const { Mat m(*this); m.data = data + a; m.cols = b - a; return m; }
+    Mat colRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * elemSize(); m.cols = b - a; return m; }
     Mat clone() const
     {
-        Mat m(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols);
+        Mat m(rows, cols, type_);
+        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols * elemSize());
         return m;
     }
     uchar *ptr(int y = 0) { return data + (size_t)y * step; }
@@ -83,6 +90,7 @@ public:
 
 private:
     std::shared_ptr<uchar> own_;
+    int type_;
 };
 
 class _InputArray

@@ -9,6 +9,10 @@
  *   src/Frame.cc:626,738-757 mvImagePyramid[level].rows/.cols/.rowRange().colRange()
  *   src/Frame.cc:120         ComputeStereoMatches() -- here the one-line device version
  *
+ *   src/Tracking.cc:176-201 + Examples/Stereo/stereo_euroc.cc:136-137 -- `pre` mode: a raw RGB
+ *                            frame goes in, rectification and gray conversion run on the device
+ *
+ * usage: frame_like pre <rgb.raw> <cols> <rows> <mapx.f32> <mapy.f32> <nfeatures> <out.bin>
  * usage: frame_like <left.raw> <right.raw> <cols> <rows> <nfeatures> <out.bin>
  * Writes, for left then right: int32 n, n x 28-byte keypoints, n x 32 descriptor bytes, then for
  * each of the 8 levels int32 cols, rows and an 11x11 window checksum (sum of all level pixels via
@@ -106,8 +110,30 @@ static void dump(FILE *f, const vector<cv::KeyPoint> &k, const cv::Mat &d, ORBex
     }
 }
 
+static int pre_mode(char **argv)
+{
+    const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[7]);
+    vector<unsigned char> rgb = slurp(argv[2], (size_t)cols * rows * 3);
+    vector<unsigned char> mx = slurp(argv[5], (size_t)cols * rows * 4), my = slurp(argv[6], (size_t)cols * rows * 4);
+    cv::Mat im(rows, cols, CV_8UC3, rgb.data());
+    cv::Mat M1(rows, cols, CV_32FC1, mx.data()), M2(rows, cols, CV_32FC1, my.data());
+    ORBextractor ext(nFeatures, 1.2f, 8, 20, 7);
+    ext.SetColorInput(true, /*rgb=*/true); /* Camera.RGB: 1 */
+    ext.SetRectifyMap(M1, M2);
+    vector<cv::KeyPoint> k;
+    cv::Mat d;
+    ext(im, cv::Mat(), k, d);
+    FILE *f = fopen(argv[8], "wb");
+    if (!f) return 2;
+    dump(f, k, d, &ext);
+    fclose(f);
+    printf("frame_like pre ok\n");
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
+    if (argc == 9 && !strcmp(argv[1], "pre")) return pre_mode(argv);
     if (argc != 7) { fprintf(stderr, "usage: %s left right cols rows nfeatures out\n", argv[0]); return 2; }
     const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[5]);
     vector<unsigned char> l = slurp(argv[1], (size_t)cols * rows), r = slurp(argv[2], (size_t)cols * rows);

@@ -132,3 +132,23 @@ def test_frame_like_caller_matches_oracle(shape, nf, tmp_path, oracle_built):
                                       np.float32(386.1448), np.float32(386.1448) / np.float32(718.856))
     assert ns == len(kl) and kept > 100
     assert u.tobytes() == wu.tobytes() and z.tobytes() == wz.tobytes()
+
+
+@pytest.mark.gpu
+def test_prestep_through_the_shim(tmp_path, oracle_built):
+    """Raw RGB frame + rectification maps handed to the C++ class (SetColorInput / SetRectifyMap)."""
+    _build()
+    rows, cols = synth.EUROC_SHAPE
+    img = synth.make_color_frame(synth.EUROC_SHAPE, seed=43, channels=3)
+    mx, my = synth.rectify_maps(*synth.EUROC[0], size=(cols, rows))
+    (tmp_path / "c.raw").write_bytes(img.tobytes())
+    (tmp_path / "mx.f32").write_bytes(mx.tobytes())
+    (tmp_path / "my.f32").write_bytes(my.tobytes())
+    r = subprocess.run([str(EXE), "pre", str(tmp_path / "c.raw"), str(cols), str(rows), str(tmp_path / "mx.f32"),
+                        str(tmp_path / "my.f32"), "1200", str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    k, d, lv, _ = _read_block((tmp_path / "o.bin").read_bytes(), 0)
+    gray = oracle_built.cvt_gray(oracle_built.remap_linear(img, mx, my), True)
+    ok, od = oracle_built.Oracle(1200, 1.2, 8, 20, 7).extract(gray)
+    assert k.tobytes() == ok.tobytes() and d.tobytes() == od.tobytes()
+    assert lv[0][2] == _level_checksum(gray)
