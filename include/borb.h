@@ -130,6 +130,22 @@ int borb_counts(const borb_extractor *h, int32_t *out);
  * mvImagePyramid[level] is (src/ORBextractor.cc:1417).  Needs BORB_WANT_PYRAMID. */
 int borb_pyramid(const borb_extractor *h, int frame, int level, const uint8_t **data, int *cols,
                  int *rows, size_t *step);
+/* -- the per-keypoint step after the extractor: replaces Frame::UndistortKeyPoints
+ *    (src/Frame.cc:542-572), Frame::ComputeImageBounds (:574-609) and
+ *    Frame::AssignFeaturesToGrid / PosInGrid (:292-307, :510-520) -------------------------------- */
+
+/* K = {fx, fy, cx, cy} and dist = {k1, k2, p1, p2[, k3]} as the reference holds them in mK and
+ * mDistCoef (floats).  While a camera is set, every extract call also produces, per frame, the
+ * undistorted keypoint positions (cv::undistortPoints(pts, pts, K, dist, Mat(), K), bit for bit;
+ * identity when k1 == 0 exactly as the reference's shortcut) and the 64 x 48 keypoint grid.
+ * K = NULL turns it off. */
+int borb_set_camera(borb_extractor *h, const float *K, const float *dist, int n_dist);
+/* frame f of the last call: xy_un[2n] = mvKeysUn[i].pt; cell (i, j), i < 64 columns, j < 48 rows, is
+ * cell_idx[cell_start[i*48 + j] .. cell_start[i*48 + j + 1]) = mGrid[i][j] (keypoint indices in
+ * ascending order); cell_start has 64*48 + 1 entries; bounds[4] = mnMinX, mnMaxX, mnMinY, mnMaxY. */
+int borb_frame_grid(const borb_extractor *h, int frame, const float **xy_un, const int32_t **cell_start,
+                    const int32_t **cell_idx, float *bounds);
+
 /* -- stereo association: replaces Frame::ComputeStereoMatches (src/Frame.cc:619-834) ---------- */
 
 #define BORB_STEREO_KEEP_ON_DEVICE 1u /* enqueue only; no download, borb_stereo_result unavailable */

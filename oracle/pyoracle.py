@@ -206,6 +206,42 @@ def stereo_match(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, mbf: float, mb:
     return u[:n], z[:n], sad[:n], kept
 
 
+def _cam(K, dist) -> np.ndarray:
+    d = list(dist) + [0.0] * (5 - len(dist))
+    return np.asarray(list(K) + d, np.float32)
+
+
+def undistort_points(xy: np.ndarray, K, dist) -> np.ndarray:
+    """cv::undistortPoints(xy, ., mK, mDistCoef, Mat(), mK) restated (oracle/frame_oracle.c)."""
+    lib = Oracle.load()
+    lib.fo_undistort_points.argtypes = [_vp, C.c_int, _vp, _vp]
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    out = np.empty_like(xy)
+    cam = _cam(K, dist)
+    lib.fo_undistort_points(xy.ctypes.data, len(xy), cam.ctypes.data, out.ctypes.data)
+    return out
+
+
+def frame_post(kps: np.ndarray, cols: int, rows: int, K, dist):
+    """Frame::UndistortKeyPoints + ComputeImageBounds + AssignFeaturesToGrid restated.
+    -> (xy_un [n,2] f32, cell_start [3073] i32, cell_idx [n_in_grid] i32, bounds [4] f32)."""
+    lib = Oracle.load()
+    lib.fo_undistort_keypoints.argtypes = [_vp, C.c_int, _vp, _vp]
+    lib.fo_image_bounds.argtypes = [C.c_int, C.c_int, _vp, _vp]
+    lib.fo_assign_grid.argtypes = [_vp, C.c_int, _vp, _vp, _vp]
+    cam = _cam(K, dist)
+    n = len(kps)
+    xy = np.ascontiguousarray(np.stack([kps["x"], kps["y"]], 1).astype(np.float32)) if n else np.zeros((0, 2), np.float32)
+    un = np.zeros((max(n, 1), 2), np.float32)
+    lib.fo_undistort_keypoints(xy.ctypes.data, n, cam.ctypes.data, un.ctypes.data)
+    bounds = np.zeros(4, np.float32)
+    lib.fo_image_bounds(cols, rows, cam.ctypes.data, bounds.ctypes.data)
+    start = np.zeros(64 * 48 + 1, np.int32)
+    idx = np.zeros(max(n, 1), np.int32)
+    m = lib.fo_assign_grid(un.ctypes.data, n, bounds.ctypes.data, start.ctypes.data, idx.ctypes.data)
+    return un[:n], start, idx[:m], bounds
+
+
 def cvt_gray(img: np.ndarray, rgb_order: bool) -> np.ndarray:
     """cv::cvtColor(..., CV_{RGB,BGR,RGBA,BGRA}2GRAY) restated (oracle/cvprim_pre.c)."""
     lib = Oracle.load()

@@ -25,6 +25,7 @@
 #include "k_blur.cuh"
 #include "k_describe.cuh"
 #include "k_fast.cuh"
+#include "k_frame.cuh"
 #include "k_prestep.cuh"
 #include "k_pyramid.cuh"
 #include "k_quadtree.cuh"
@@ -140,6 +141,13 @@ struct borb_extractor {
     uint8_t *d_gray = nullptr; /* [B][rows][gray_pitch]: K0's output, K1's input */
     int gray_pitch = 0;
     size_t in_cap = 0;         /* bytes per frame d_in / h_in can hold */
+    /* the per-keypoint step after the extractor (K8): undistortion + 64x48 grid, when a camera is set */
+    bool have_cam = false;
+    BorbCamera cam;
+    float2 *d_un_xy = nullptr, *h_un_xy = nullptr;
+    int *d_cell_start = nullptr, *d_cell_idx = nullptr, *d_cell_of = nullptr, *h_cell_start = nullptr, *h_cell_idx = nullptr;
+    float *d_bounds = nullptr, *h_bounds = nullptr;
+    bool frame_on_host = false;
     /* stereo association (left handle only), allocated on first use */
     float *d_st_u = nullptr, *d_st_z = nullptr, *h_st_u = nullptr, *h_st_z = nullptr;
     int *d_st_sad = nullptr, *d_st_kept = nullptr, *h_st_kept = nullptr;
@@ -219,13 +227,18 @@ void free_geometry(borb_extractor *h)
     void *dev[] = {h->d_plan, h->d_cells, h->d_tiles, h->d_tab_i, h->d_tab_s, h->d_in, h->d_pyr,
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
-                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_gray};
+                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_gray,
+                   h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
-                    h->h_st_u, h->h_st_z, h->h_st_kept};
+                    h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds};
     for (void *p : host) if (p) cudaFreeHost(p);
     h->d_gray = nullptr;
     h->in_cap = 0;
+    h->d_un_xy = h->h_un_xy = nullptr;
+    h->d_cell_start = h->d_cell_idx = h->d_cell_of = h->h_cell_start = h->h_cell_idx = nullptr;
+    h->d_bounds = h->h_bounds = nullptr;
+    h->frame_on_host = false;
     h->d_st_u = h->d_st_z = h->h_st_u = h->h_st_z = nullptr;
     h->d_st_sad = h->d_st_kept = h->h_st_kept = nullptr;
     h->stereo_on_host = false;
@@ -526,6 +539,12 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, 0, st>>>(
         h->d_plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
         d_out_kp, d_out_desc, d_nout);
+    if (h->have_cam) /* K8: rides in the describe stage's time slot */
+        k_frame_undistort_grid<<<n, FR_NT, 0, st>>>(h->d_plan, h->cam, d_out_kp, d_nout,
+                                                    h->d_un_xy + (size_t)f0 * P.kp_total,
+                                                    h->d_cell_start + (size_t)f0 * (FR_CELLS + 1),
+                                                    h->d_cell_idx + (size_t)f0 * P.kp_total,
+                                                    h->d_cell_of + (size_t)f0 * P.kp_total, h->d_bounds + (size_t)f0 * 4);
     STAGE(5);
     }
     n = n_total;
@@ -547,6 +566,12 @@ int enqueue_fetch(borb_extractor *h, int n, unsigned flags)
     if (flags & BORB_WANT_PYRAMID)
         CU(cudaMemcpyAsync(h->h_pyr, h->d_pyr, (size_t)n * (size_t)P.pyr_bytes,
                            cudaMemcpyDeviceToHost, st));
+    if (h->have_cam) {
+        CU(cudaMemcpyAsync(h->h_un_xy, h->d_un_xy, (size_t)n * P.kp_total * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h->h_cell_start, h->d_cell_start, (size_t)n * (FR_CELLS + 1) * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h->h_cell_idx, h->d_cell_idx, (size_t)n * P.kp_total * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h->h_bounds, h->d_bounds, (size_t)n * 16, cudaMemcpyDeviceToHost, st));
+    }
     return BORB_OK;
 }
 
@@ -726,6 +751,18 @@ static int check_call(borb_extractor *h, const void *img, int n, int cols, int r
     const int ocols = h->d_map_xy ? h->map_cols : cols, orows = h->d_map_xy ? h->map_rows : rows;
     int rc = build_plan(h, ocols, orows);
     if (rc != BORB_OK) return rc;
+    if (h->have_cam && !h->d_un_xy) {
+        const size_t B = (size_t)h->max_batch, K = (size_t)h->plan.kp_total;
+        CU(cudaMalloc(&h->d_un_xy, B * K * 8));
+        CU(cudaMalloc(&h->d_cell_start, B * (FR_CELLS + 1) * 4));
+        CU(cudaMalloc(&h->d_cell_idx, B * K * 4));
+        CU(cudaMalloc(&h->d_cell_of, B * K * 4));
+        CU(cudaMalloc(&h->d_bounds, B * 16));
+        CU(cudaMallocHost(&h->h_un_xy, B * K * 8));
+        CU(cudaMallocHost(&h->h_cell_start, B * (FR_CELLS + 1) * 4));
+        CU(cudaMallocHost(&h->h_cell_idx, B * K * 4));
+        CU(cudaMallocHost(&h->h_bounds, B * 16));
+    }
     if (pre_active(h) && !h->d_gray) {
         h->gray_pitch = (ocols + 3) & ~3;
         CU(cudaMalloc(&h->d_gray, (size_t)h->max_batch * h->gray_pitch * orows));
@@ -936,7 +973,10 @@ float borb_last_prestep_ms(borb_extractor *h)
     return ms;
 }
 
-int borb_launches_per_call(const borb_extractor *h) { return h ? h->nlevels + 4 + (pre_active(h) ? 1 : 0) : 0; }
+int borb_launches_per_call(const borb_extractor *h)
+{
+    return h ? h->nlevels + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0) : 0;
+}
 
 int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps, const uint8_t **desc, int *n)
 {
@@ -953,6 +993,39 @@ int borb_counts(const borb_extractor *h, int32_t *out)
 {
     if (!h || !out || !h->results_on_host) return fail(BORB_ERR_STATE, "no results on the host");
     std::memcpy(out, h->h_nout, (size_t)h->last_n * 4);
+    return BORB_OK;
+}
+
+/* -- the per-keypoint step after the extractor (K8) -- */
+int borb_set_camera(borb_extractor *h, const float *K4, const float *dist, int n_dist)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null");
+    if (h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    if (K4 && (n_dist < 0 || n_dist > 5 || (n_dist > 0 && !dist) || !(K4[0] != 0.f) || !(K4[1] != 0.f)))
+        return fail(BORB_ERR_ARG, "bad camera");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    for (GraphEntry &g : h->graphs) cudaGraphExecDestroy(g.exec); /* the camera is a kernel argument */
+    h->graphs.clear();
+    h->frame_on_host = false;
+    h->have_cam = K4 != nullptr;
+    if (!K4) return BORB_OK;
+    h->cam.fx = K4[0]; h->cam.fy = K4[1]; h->cam.cx = K4[2]; h->cam.cy = K4[3];
+    for (int i = 0; i < 5; ++i) h->cam.k[i] = i < n_dist ? dist[i] : 0.f;
+    return BORB_OK;
+}
+
+int borb_frame_grid(const borb_extractor *h, int frame, const float **xy_un, const int32_t **cell_start,
+                    const int32_t **cell_idx, float *bounds)
+{
+    if (!h || !h->have_cam || !h->results_on_host || !h->h_un_xy)
+        return fail(BORB_ERR_STATE, "no camera set, or no results on the host");
+    if (frame < 0 || frame >= h->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, h->last_n);
+    const size_t o = (size_t)frame * h->plan.kp_total;
+    if (xy_un) *xy_un = reinterpret_cast<const float *>(h->h_un_xy + o);
+    if (cell_start) *cell_start = h->h_cell_start + (size_t)frame * (FR_CELLS + 1);
+    if (cell_idx) *cell_idx = h->h_cell_idx + o;
+    if (bounds) std::memcpy(bounds, h->h_bounds + (size_t)frame * 4, 16);
     return BORB_OK;
 }
 

@@ -37,7 +37,7 @@ SYMBOLS = [
     "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
     "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
-    "borb_last_prestep_ms",
+    "borb_last_prestep_ms", "borb_set_camera", "borb_frame_grid",
 ]
 
 
@@ -98,6 +98,8 @@ def load_library() -> C.CDLL:
     lib.borb_counts.argtypes = [_vp, _vp]
     lib.borb_set_stage_timing.argtypes = [_vp, C.c_int]
     lib.borb_last_stage_ms.argtypes = [_vp, _vp]
+    lib.borb_set_camera.argtypes = [_vp, _vp, _vp, C.c_int]
+    lib.borb_frame_grid.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _vp]
     lib.borb_last_prestep_ms.argtypes = [_vp]
     lib.borb_last_prestep_ms.restype = C.c_float
     lib.borb_set_input_format.argtypes = [_vp, C.c_int]
@@ -164,6 +166,31 @@ class ORBextractor:
         rows, cols = map_x.shape
         _check(self._lib, self._lib.borb_set_rectify_map(self._h, map_x.ctypes.data, map_y.ctypes.data, cols,
                                                          rows, cols))
+
+    # -- the per-keypoint step after the extractor (src/Frame.cc:542-572, :574-609, :292-307) --
+    def set_camera(self, K=None, dist=()) -> None:
+        """K = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3]); None turns the step off."""
+        if K is None:
+            _check(self._lib, self._lib.borb_set_camera(self._h, None, None, 0))
+            return
+        k = np.asarray(K, np.float32)
+        d = np.asarray(dist, np.float32)
+        _check(self._lib, self._lib.borb_set_camera(self._h, k.ctypes.data, d.ctypes.data if len(d) else None, len(d)))
+
+    def frame_grid(self, frame: int = 0):
+        """(mvKeysUn positions [n,2], cell_start [3073], cell_idx [n_in_grid], bounds [4])."""
+        xy, cs, ci = _vp(), _vp(), _vp()
+        bounds = np.zeros(4, np.float32)
+        _check(self._lib, self._lib.borb_frame_grid(self._h, frame, C.byref(xy), C.byref(cs), C.byref(ci),
+                                                    bounds.ctypes.data))
+        n = self.count(frame)
+        start = np.ctypeslib.as_array(C.cast(cs, C.POINTER(C.c_int32)), shape=(64 * 48 + 1,)).copy()
+        un = (np.ctypeslib.as_array(C.cast(xy, C.POINTER(C.c_float)), shape=(n, 2)).copy() if n
+              else np.zeros((0, 2), np.float32))
+        m = int(start[-1])
+        idx = (np.ctypeslib.as_array(C.cast(ci, C.POINTER(C.c_int32)), shape=(m,)).copy() if m
+               else np.zeros(0, np.int32))
+        return un, start, idx, bounds
 
     def last_prestep_ms(self) -> float:
         return self._lib.borb_last_prestep_ms(self._h)
