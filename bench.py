@@ -268,6 +268,50 @@ def prestep_section(ORBextractor, synth, local, peak):
     return out
 
 
+def poststep_section(ORBextractor, synth, local):
+    """keypoint undistortion + 64x48 grid (K8) appended to the call.  K8 has no
+    stage slot of its own: its time is the growth of the describe stage when a camera is set."""
+    import torch
+    K, dist = (517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+    n = 128
+    frames = np.stack([synth.make_frame(synth.TUM_SHAPE, seed=51, frame=f) for f in range(8)])
+    frames = np.ascontiguousarray(frames[np.arange(n) % 8])
+    dev = torch.from_numpy(frames).cuda(local)
+    ext = ORBextractor(1000, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=n, want_pyramid=False)
+    ext.set_stage_timing(True)
+    res = {}
+    for cam in (None, K):
+        ext.set_camera(cam, dist if cam else ())
+        d, tot = [], []
+        for it in range(8):
+            ext.timer_start()
+            ext.extract_device(dev.data_ptr(), n, 640, 480)
+            ext.timer_stop()
+            ext.sync()
+            if it >= 3:
+                d.append(ext.last_stage_ms()["describe"])
+                tot.append(ext.timer_ms())
+        res["with" if cam else "without"] = (float(np.median(d)), float(np.median(tot)))
+    out = {"reference": "src/Frame.cc:542-572, :574-609, :292-307", "config": "TUM1.yaml camera, 640x480, 1000 kp, 128 frames",
+           "parity": "bit-exact against oracle/frame_oracle.c (undistortPoints pinned to cv2 4.13.0)",
+           "k8_ms_per_128_frames": res["with"][0] - res["without"][0],
+           "call_ms_without": res["without"][1], "call_ms_with": res["with"][1]}
+    try:
+        from oracle import pyoracle
+        kps, _ = ext.fetch()[0]
+        t1 = time.perf_counter()
+        for _ in range(200):
+            pyoracle.frame_post(kps, 640, 480, K, dist)
+        out["cpu_us_per_frame_one_core"] = (time.perf_counter() - t1) / 200 * 1e6
+        un, start, idx, b = ext.frame_grid(0)
+        wun, wstart, widx, wb = pyoracle.frame_post(kps, 640, 480, K, dist)
+        out["parity_check"] = "bit-exact" if (un.tobytes() == wun.tobytes() and np.array_equal(start, wstart)
+                                              and np.array_equal(idx, widx)) else "MISMATCH"
+    except Exception as e:
+        out["parity_check"] = f"unavailable ({type(e).__name__})"
+    return out
+
+
 def stereo_section(ORBextractor, synth, local, two, dev):
     """SURVEY.md 8(f)-1: Frame::ComputeStereoMatches on the device (borb_stereo_match).  Reported
     beside the headline, not part of `value`: (1) a stereo pair through the host ABI with the match on
@@ -473,7 +517,7 @@ def run_ours(args, rank, world, local):
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
-    stereo = prestep = None
+    stereo = prestep = poststep = None
     if rank == 0:
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
@@ -514,6 +558,7 @@ def run_ours(args, rank, world, local):
         lat["stereo_pair_p50_us_with_pyramids"] = float(np.percentile(ts, 50))
         stereo = stereo_section(ORBextractor, synth, local, two, dev)
         prestep = prestep_section(ORBextractor, synth, local, measured_peak()[0])
+        poststep = poststep_section(ORBextractor, synth, local)
 
     if rank != 0:
         return
@@ -556,6 +601,7 @@ def run_ours(args, rank, world, local):
         "latency": lat,
         "stereo": stereo,
         "prestep": prestep,
+        "poststep": poststep,
         "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,
     }

@@ -127,6 +127,39 @@ void ORBextractor::SetRectifyMap(const cv::Mat &M1, const cv::Mat &M2)
           "rectify map");
 }
 
+void ORBextractor::SetCamera(const cv::Mat &K, const cv::Mat &DistCoef)
+{
+    if (K.empty()) {
+        check(borb_set_camera(handle, NULL, NULL, 0), "camera");
+        return;
+    }
+    assert(K.type() == CV_32F && K.rows == 3 && K.cols == 3 && DistCoef.type() == CV_32F);
+    const float k4[4] = {K.at<float>(0, 0), K.at<float>(1, 1), K.at<float>(0, 2), K.at<float>(1, 2)};
+    float d[5] = {0, 0, 0, 0, 0};
+    const int nd = DistCoef.rows * DistCoef.cols;
+    assert(nd == 4 || nd == 5);
+    for (int i = 0; i < nd; ++i) d[i] = DistCoef.rows == 1 ? DistCoef.at<float>(0, i) : DistCoef.at<float>(i, 0);
+    check(borb_set_camera(handle, k4, d, nd), "camera");
+}
+
+void ORBextractor::FillFrame(const std::vector<cv::KeyPoint> &mvKeys, std::vector<cv::KeyPoint> &mvKeysUn,
+                             std::vector<std::size_t> mGrid[64][48], float bounds[4])
+{
+    const float *xy = NULL;
+    const int32_t *start = NULL, *idx = NULL;
+    check(borb_frame_grid(handle, 0, &xy, &start, &idx, bounds), "frame grid");
+    mvKeysUn = mvKeys; // reference :563-571: a copy of each keypoint with pt replaced
+    for (size_t i = 0; i < mvKeysUn.size(); ++i) {
+        mvKeysUn[i].pt.x = xy[2 * i];
+        mvKeysUn[i].pt.y = xy[2 * i + 1];
+    }
+    for (int i = 0; i < 64; ++i)
+        for (int j = 0; j < 48; ++j) {
+            const int c = i * 48 + j;
+            mGrid[i][j].assign(idx + start[c], idx + start[c + 1]);
+        }
+}
+
 void ORBextractor::ComputeStereoMatches(ORBextractor &right, float mbf, float mb, std::vector<float> &mvuRight,
                                         std::vector<float> &mvDepth)
 {

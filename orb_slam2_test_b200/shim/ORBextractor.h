@@ -90,6 +90,15 @@ public:
     // Empty maps remove the rectification.
     void SetColorInput(bool enabled, bool rgb) { colorInput = enabled; colorRGB = rgb; }
     void SetRectifyMap(const cv::Mat &M1, const cv::Mat &M2);
+    // The per-keypoint step after the extractor, on the device: with a camera set (mK 3x3 CV_32F,
+    // mDistCoef 4x1 / 5x1 CV_32F as Tracking builds them, src/Tracking.cc:56-80), every operator()
+    // call also undistorts the keypoints and bins them into the 64 x 48 grid; FillFrame then
+    // hands back what Frame::UndistortKeyPoints (reference src/Frame.cc:542-572),
+    // Frame::ComputeImageBounds (:574-609) and Frame::AssignFeaturesToGrid (:292-307) compute:
+    // mvKeysUn, mGrid[64][48] and {mnMinX, mnMaxX, mnMinY, mnMaxY}.
+    void SetCamera(const cv::Mat &K, const cv::Mat &DistCoef);
+    void FillFrame(const std::vector<cv::KeyPoint> &mvKeys, std::vector<cv::KeyPoint> &mvKeysUn,
+                   std::vector<std::size_t> mGrid[64][48], float bounds[4]);
     // Frame::ComputeStereoMatches (reference src/Frame.cc:619-834) on the device, for *this as the
     // left extractor: fills mvuRight / mvDepth (size = left keypoint count, -1 where unmatched)
     // from the last operator() results of both instances.  Call it after both extraction threads

@@ -17,7 +17,9 @@
  * Writes, for left then right: int32 n, n x 28-byte keypoints, n x 32 descriptor bytes, then for
  * each of the 8 levels int32 cols, rows and an 11x11 window checksum (sum of all level pixels via
  * rowRange/colRange walks); at the very end int32 n, n x float mvuRight, n x float mvDepth of the
- * stereo pair.  The pytest compares everything with the CPU oracle.
+ * stereo pair, then int32 n, n x 2 float mvKeysUn positions, the 64x48 grid as int32 counts and
+ * indices, and the four image bounds (camera: TUM1.yaml).  The pytest compares everything with the
+ * CPU oracle.
  */
 #include <cmath>
 #include <cstdio>
@@ -40,6 +42,9 @@ struct FrameLike {
     vector<float> mvScaleFactors, mvInvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
     vector<float> mvuRight, mvDepth;
     float mbf, mb;
+    vector<cv::KeyPoint> mvKeysUn;
+    std::vector<std::size_t> mGrid[64][48];
+    float mnBounds[4];
 
     FrameLike(const cv::Mat &imLeft, const cv::Mat &imRight, ORBextractor *l, ORBextractor *r)
         : mpORBextractorLeft(l), mpORBextractorRight(r)
@@ -61,6 +66,9 @@ struct FrameLike {
         mbf = 386.1448f;
         mb = mbf / 718.856f;
         ComputeStereoMatches();
+
+        /* src/Frame.cc:116 UndistortKeyPoints(), :132 ComputeImageBounds(), :150 AssignFeaturesToGrid() */
+        mpORBextractorLeft->FillFrame(mvKeys, mvKeysUn, mGrid, mnBounds);
     }
 
     void ComputeStereoMatches()
@@ -145,9 +153,19 @@ int main(int argc, char **argv)
     ORBextractor *mpORBextractorRight = new ORBextractor(nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST);
     ORBextractor *mpIniORBextractor = new ORBextractor(2 * nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST);
 
+    /* mK and mDistCoef as src/Tracking.cc:56-80 builds them (TUM1.yaml values) */
+    cv::Mat K(3, 3, CV_32F), DistCoef(5, 1, CV_32F);
+    memset(K.data, 0, 36);
+    K.at<float>(0, 0) = 517.306408f; K.at<float>(1, 1) = 516.469215f;
+    K.at<float>(0, 2) = 318.643040f; K.at<float>(1, 2) = 255.313989f; K.at<float>(2, 2) = 1.f;
+    DistCoef.at<float>(0, 0) = 0.262383f; DistCoef.at<float>(1, 0) = -0.953104f; DistCoef.at<float>(2, 0) = -0.005358f;
+    DistCoef.at<float>(3, 0) = 0.002628f; DistCoef.at<float>(4, 0) = 1.163314f;
+    mpORBextractorLeft->SetCamera(K, DistCoef);
+
     FILE *f = fopen(argv[6], "wb");
     if (!f) return 2;
-    vector<float> uRight, depth;
+    vector<float> uRight, depth, unxy, bnd;
+    vector<int> gcount, gidx;
     for (int rep = 0; rep < 3; ++rep) { /* instances are reused frame after frame */
         FrameLike fr(imLeft, imRight, mpORBextractorLeft, mpORBextractorRight);
         if (rep == 2) {
@@ -155,6 +173,13 @@ int main(int argc, char **argv)
             dump(f, fr.mvKeysRight, fr.mDescriptorsRight, mpORBextractorRight);
             uRight = fr.mvuRight;
             depth = fr.mvDepth;
+            for (size_t i = 0; i < fr.mvKeysUn.size(); ++i) { unxy.push_back(fr.mvKeysUn[i].pt.x); unxy.push_back(fr.mvKeysUn[i].pt.y); }
+            for (int i = 0; i < 64; ++i)
+                for (int j = 0; j < 48; ++j) {
+                    gcount.push_back((int)fr.mGrid[i][j].size());
+                    for (size_t q = 0; q < fr.mGrid[i][j].size(); ++q) gidx.push_back((int)fr.mGrid[i][j][q]);
+                }
+            bnd.assign(fr.mnBounds, fr.mnBounds + 4);
         }
     }
     /* monocular initialisation extractor + the empty-image convention */
@@ -170,6 +195,13 @@ int main(int argc, char **argv)
     fwrite(&ns, 4, 1, f);
     fwrite(uRight.data(), 4, (size_t)ns, f);
     fwrite(depth.data(), 4, (size_t)ns, f);
+    int nu = (int)unxy.size() / 2, ng = (int)gidx.size();
+    fwrite(&nu, 4, 1, f);
+    fwrite(unxy.data(), 4, unxy.size(), f);
+    fwrite(gcount.data(), 4, gcount.size(), f);
+    fwrite(&ng, 4, 1, f);
+    fwrite(gidx.data(), 4, gidx.size(), f);
+    fwrite(bnd.data(), 4, 4, f);
     fclose(f);
     delete mpORBextractorLeft;
     delete mpORBextractorRight;

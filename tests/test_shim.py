@@ -132,6 +132,18 @@ def test_frame_like_caller_matches_oracle(shape, nf, tmp_path, oracle_built):
                                       np.float32(386.1448), np.float32(386.1448) / np.float32(718.856))
     assert ns == len(kl) and kept > 100
     assert u.tobytes() == wu.tobytes() and z.tobytes() == wz.tobytes()
+    # mvKeysUn, mGrid and the image bounds the caller got from FillFrame (camera: TUM1.yaml)
+    off += 8 + 8 * ns
+    nu, = struct.unpack_from("<i", buf, off); off += 4
+    un = np.frombuffer(buf, "<f4", 2 * nu, off).reshape(nu, 2); off += 8 * nu
+    gcount = np.frombuffer(buf, "<i4", 64 * 48, off); off += 4 * 64 * 48
+    ng, = struct.unpack_from("<i", buf, off); off += 4
+    gidx = np.frombuffer(buf, "<i4", ng, off); off += 4 * ng
+    bnd = np.frombuffer(buf, "<f4", 4, off)
+    from test_oracle_frame import CAMS
+    wun, wstart, widx, wb = py.frame_post(kl, shape[1], shape[0], *CAMS["TUM1"])
+    assert nu == len(kl) and un.tobytes() == wun.tobytes() and bnd.tobytes() == wb.tobytes()
+    assert np.array_equal(gcount, np.diff(wstart)) and np.array_equal(gidx, widx)
 
 
 @pytest.mark.gpu
