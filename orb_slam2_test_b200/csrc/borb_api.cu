@@ -151,6 +151,9 @@ struct borb_extractor {
     /* stereo association (left handle only), allocated on first use */
     float *d_st_u = nullptr, *d_st_z = nullptr, *h_st_u = nullptr, *h_st_z = nullptr;
     int *d_st_sad = nullptr, *d_st_kept = nullptr, *h_st_kept = nullptr;
+    int *d_st_rows = nullptr;      /* [B][rows+1] CSR starts of the right keypoints listed per image row */
+    uint16_t *d_st_ent = nullptr;  /* [B][kp_total * st_span] */
+    int st_span = 0;
     cudaEvent_t ev_peer = nullptr; /* recorded on this handle's stream for a peer handle to wait on */
     bool stereo_on_host = false;
 
@@ -227,7 +230,7 @@ void free_geometry(borb_extractor *h)
     void *dev[] = {h->d_plan, h->d_cells, h->d_tiles, h->d_tab_i, h->d_tab_s, h->d_in, h->d_pyr,
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
-                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_gray,
+                   h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
@@ -241,6 +244,8 @@ void free_geometry(borb_extractor *h)
     h->frame_on_host = false;
     h->d_st_u = h->d_st_z = h->h_st_u = h->h_st_z = nullptr;
     h->d_st_sad = h->d_st_kept = h->h_st_kept = nullptr;
+    h->d_st_rows = nullptr;
+    h->d_st_ent = nullptr;
     h->stereo_on_host = false;
     h->d_plan = nullptr; h->d_cells = nullptr; h->d_tiles = nullptr; h->d_tab_i = nullptr;
     h->d_tab_s = nullptr; h->d_in = h->d_pyr = h->d_blur = nullptr;
@@ -539,12 +544,13 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, 0, st>>>(
         h->d_plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
         d_out_kp, d_out_desc, d_nout);
-    if (h->have_cam) /* K8: rides in the describe stage's time slot */
-        k_frame_undistort_grid<<<n, FR_NT, 0, st>>>(h->d_plan, h->cam, d_out_kp, d_nout,
-                                                    h->d_un_xy + (size_t)f0 * P.kp_total,
-                                                    h->d_cell_start + (size_t)f0 * (FR_CELLS + 1),
-                                                    h->d_cell_idx + (size_t)f0 * P.kp_total,
-                                                    h->d_cell_of + (size_t)f0 * P.kp_total, h->d_bounds + (size_t)f0 * 4);
+    if (h->have_cam) { /* K8: rides in the describe stage's time slot */
+#define K8(NT) k_frame_undistort_grid<NT><<<n, NT, 0, st>>>(h->d_plan, h->cam, d_out_kp, d_nout, \
+        h->d_un_xy + (size_t)f0 * P.kp_total, h->d_cell_start + (size_t)f0 * (FR_CELLS + 1), \
+        h->d_cell_idx + (size_t)f0 * P.kp_total, h->d_cell_of + (size_t)f0 * P.kp_total, h->d_bounds + (size_t)f0 * 4)
+        if (n <= 2 * h->n_sm) K8(FR_NT_LATENCY); else K8(FR_NT_THROUGHPUT);
+#undef K8
+    }
     STAGE(5);
     }
     n = n_total;
@@ -1109,6 +1115,11 @@ int borb_stereo_match(borb_extractor *l, borb_extractor *r, float mbf, float mb,
         CU(cudaMalloc(&l->d_st_z, B * K * 4));
         CU(cudaMalloc(&l->d_st_sad, B * K * 4));
         CU(cudaMalloc(&l->d_st_kept, B * 4));
+        l->st_span = (int)(4.f * l->scale[l->nlevels - 1]) + 3;
+        CU(cudaMalloc(&l->d_st_rows, B * (size_t)(P.rows + 1) * 4));
+        CU(cudaMalloc(&l->d_st_ent, B * K * (size_t)l->st_span * 2));
+        CU(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)((2 * (size_t)P.rows + ST_ROWS_NT) * 4)));
         CU(cudaMallocHost(&l->h_st_u, B * K * 4));
         CU(cudaMallocHost(&l->h_st_z, B * K * 4));
         CU(cudaMallocHost(&l->h_st_kept, B * 4));
@@ -1119,10 +1130,12 @@ int borb_stereo_match(borb_extractor *l, borb_extractor *r, float mbf, float mb,
     CU(cudaEventRecord(r->ev_peer, r->stream));
     CU(cudaStreamWaitEvent(l->stream, r->ev_peer, 0));
     const dim3 grid((unsigned)((K + ST_NT / 32 - 1) / (ST_NT / 32)), (unsigned)n);
+    k_stereo_rows<<<n, ST_ROWS_NT, (2 * (size_t)P.rows + ST_ROWS_NT) * 4, l->stream>>>(
+        l->d_plan, r->d_out_kp, r->d_nout, l->st_span, l->d_st_rows, l->d_st_ent);
     k_stereo_match<<<grid, ST_NT, 0, l->stream>>>(l->d_plan, l->d_out_kp, l->d_out_desc, l->d_nout, r->d_out_kp,
-                                                  r->d_out_desc, r->d_nout, l->d_pyr, r->d_pyr, mbf, mb,
-                                                  l->d_st_u, l->d_st_z, l->d_st_sad);
-    k_stereo_cut<<<n, 256, 0, l->stream>>>(l->d_plan, l->d_nout, l->d_st_u, l->d_st_z, l->d_st_sad, l->d_st_kept);
+                                                  r->d_out_desc, r->d_nout, l->st_span, l->d_st_rows, l->d_st_ent,
+                                                  l->d_pyr, r->d_pyr, mbf, mb, l->d_st_u, l->d_st_z, l->d_st_sad);
+    k_stereo_cut<<<n, ST_CUT_NT, 0, l->stream>>>(l->d_plan, l->d_nout, l->d_st_u, l->d_st_z, l->d_st_sad, l->d_st_kept);
     CU(cudaGetLastError());
     /* the right handle must not start its next call before the match has read its buffers */
     if (!l->ev_peer) CU(cudaEventCreateWithFlags(&l->ev_peer, cudaEventDisableTiming));

@@ -21,8 +21,10 @@
 
 #include "borb_internal.h"
 #include "k_describe.cuh"
+#include "borb_cta.cuh"
 
-#define FR_NT 256
+#define FR_NT_THROUGHPUT 256 /* many frames per call: several CTAs per SM */
+#define FR_NT_LATENCY 1024   /* a few frames: one keypoint per thread, the double-precision chains run side by side */
 #define FR_GRID_COLS 64 /* FRAME_GRID_COLS, include/Frame.h:38 */
 #define FR_GRID_ROWS 48 /* FRAME_GRID_ROWS, include/Frame.h:37 */
 #define FR_CELLS (FR_GRID_COLS * FR_GRID_ROWS)
@@ -64,6 +66,7 @@ __device__ __forceinline__ void fr_undistort(const BorbCamera &cam, float u, flo
 #undef A
 }
 
+template <int FR_NT>
 __global__ void __launch_bounds__(FR_NT)
 k_frame_undistort_grid(const BorbPlan *__restrict__ plan, BorbCamera cam, const BorbKpRec *__restrict__ kp,
                        const int *__restrict__ n_kp, float2 *__restrict__ un_xy, int *__restrict__ cell_start,
@@ -71,7 +74,7 @@ k_frame_undistort_grid(const BorbPlan *__restrict__ plan, BorbCamera cam, const 
 {
     __shared__ int cnt[FR_CELLS];
     __shared__ int cur[FR_CELLS];
-    __shared__ int part[FR_NT];
+    __shared__ int part[32];
     __shared__ float corner[4][2];
     __shared__ float bnd[6]; /* minX maxX minY maxY invW invH */
     const int frame = blockIdx.x, tid = threadIdx.x;
@@ -116,26 +119,19 @@ k_frame_undistort_grid(const BorbPlan *__restrict__ plan, BorbCamera cam, const 
     }
     __syncthreads();
 
-    /* pass 2: exclusive scan of the 3072 counts (12 consecutive cells per thread) */
+    /* pass 2: exclusive scan of the 3072 counts (FR_CELLS / FR_NT consecutive cells per thread) */
     const int per = FR_CELLS / FR_NT;
     int sum = 0;
     for (int c = 0; c < per; ++c) sum += cnt[tid * per + c];
-    part[tid] = sum;
-    __syncthreads();
-    for (int off = 1; off < FR_NT; off <<= 1) {
-        const int v = tid >= off ? part[tid - off] : 0;
-        __syncthreads();
-        part[tid] += v;
-        __syncthreads();
-    }
-    int base = part[tid] - sum;
+    int total;
+    int base = cta_exscan<FR_NT>(sum, part, &total);
     int *start = cell_start + (size_t)frame * (FR_CELLS + 1);
     for (int c = 0; c < per; ++c) {
         start[tid * per + c] = base;
         cur[tid * per + c] = base;
         base += cnt[tid * per + c];
     }
-    if (tid == FR_NT - 1) start[FR_CELLS] = base;
+    if (tid == 0) start[FR_CELLS] = total;
     __syncthreads();
 
     /* pass 3: scatter */

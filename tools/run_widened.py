@@ -1,0 +1,46 @@
+"""One pass over every kernel of the widened rows for ncu launch lists:
+K0 colour->gray and rectification, the extraction chain, K8 undistort+grid, S0/S1/S2 stereo match.
+usage: python tools/run_widened.py [pairs]   (default 1 stereo pair per call; e.g. 64 for batches)"""
+import sys
+from pathlib import Path
+
+import numpy as np
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from orb_slam2_test_b200 import ORBextractor, synth  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+BF, FX = 386.1448, 718.856
+# EuRoC-style stereo: raw gray frames rectified on the device, then matched on the device
+mxl, myl = synth.rectify_maps(*synth.EUROC[0], size=(752, 480))
+mxr, myr = synth.rectify_maps(*synth.EUROC[1], size=(752, 480))
+L = ORBextractor(1200, 1.2, 8, 20, 7, max_batch=n, want_pyramid=False)
+R = ORBextractor(1200, 1.2, 8, 20, 7, max_batch=n, want_pyramid=False)
+L.set_rectify_map(mxl, myl)
+R.set_rectify_map(mxr, myr)
+L.set_camera((435.2046959714599, 435.2046959714599, 367.4517211914062, 252.2008514404297), (0, 0, 0, 0))
+li = synth.make_sequence(synth.EUROC_SHAPE, seed=40, start=0, count=n, eye=0)
+ri = synth.make_sequence(synth.EUROC_SHAPE, seed=40, start=0, count=n, eye=1)
+for _ in range(3):
+    L.extract_batch(li)
+    R.extract_batch(ri)
+    L.stereo_match(R, 47.90639384423901, 47.90639384423901 / 435.2046959714599)
+print("euroc pairs:", n, "matched", [L.stereo_result(f)[2] for f in range(min(n, 4))])
+# TUM colour frames with the TUM1 camera
+C = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=n, want_pyramid=False)
+C.set_input_format("rgb")
+C.set_camera((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314))
+ci = np.stack([synth.make_color_frame(synth.TUM_SHAPE, seed=21, frame=f) for f in range(n)])
+for _ in range(3):
+    C.extract_batch(ci)
+print("tum colour frames:", n, "in grid", int(C.frame_grid(0)[1][-1]), "of", C.count(0))
+# KITTI stereo pair (no rectification): the K2k match
+KL = ORBextractor(2000, 1.2, 8, 20, 7, max_batch=n, want_pyramid=False)
+KR = ORBextractor(2000, 1.2, 8, 20, 7, max_batch=n, want_pyramid=False)
+kl = synth.make_sequence(synth.KITTI_SHAPE, seed=31, start=0, count=n, eye=0)
+kr = synth.make_sequence(synth.KITTI_SHAPE, seed=31, start=0, count=n, eye=1)
+for _ in range(3):
+    KL.extract_batch(kl)
+    KR.extract_batch(kr)
+    KL.stereo_match(KR, BF, BF / FX)
+print("kitti pairs:", n, "matched", [KL.stereo_result(f)[2] for f in range(min(n, 4))])
