@@ -55,6 +55,8 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 #define DESC_NW (DESC_NT / 32)
 #define DESC_PR 37  /* staged patch rows: -18 .. +18 */
 #define DESC_PW 10  /* staged words per row: covers 37 columns at any alignment */
+#define DESC_IR 31  /* staged rows of the unblurred level for IC_Angle: -15 .. +15 */
+#define DESC_BUF ((DESC_PR + DESC_IR) * DESC_PW) /* words per buffer */
 #ifndef DESC_KPW
 #define DESC_KPW 16 /* keypoint slots per warp */
 #endif
@@ -69,7 +71,8 @@ k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restri
                   const int *__restrict__ nlkp, BorbKpRec *__restrict__ out_kp,
                   uint8_t *__restrict__ out_desc, int *__restrict__ nout)
 {
-    __shared__ uint32_t patch_all[DESC_NW][DESC_PR * DESC_PW];
+    /* per warp, twice: the blurred 37-row patch and the unblurred 31-row disc region */
+    __shared__ uint32_t patch_all[DESC_NW][2 * (DESC_PR + DESC_IR) * DESC_PW];
     const int frame = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *patch = patch_all[warp];
@@ -103,44 +106,93 @@ k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restri
     const int ic_vmax = lane < 31 ? plan->umax[ic_u < 0 ? -ic_u : ic_u] : -1;
 
     const int warps_per_frame = gridDim.x * DESC_NW;
-    for (int slot = blockIdx.x * DESC_NW + warp; slot < kp_total; slot += warps_per_frame) {
-        const int level = __popc(__ballot_sync(0xffffffffu, slot >= my_off)) - 1;
-        const int idx = slot - __shfl_sync(0xffffffffu, my_off, level);
-        if (idx >= __shfl_sync(0xffffffffu, my_cnt, level)) continue;
-        const int o = __shfl_sync(0xffffffffu, my_base, level) + idx;
+    const size_t fkp = (size_t)frame * kp_total;
+    const uint32_t patch_s = (uint32_t)__cvta_generic_to_shared(patch);
+
+    /* A warp walks its slots as a three-deep software pipeline: in the iteration that orients and
+     * describes keypoint i, the blurred patch and the unblurred disc region of keypoint i+1 are on
+     * their way into the other half of the warp's shared memory (cp.async), and the coordinates
+     * of keypoint i+2 are being loaded -- no global-load latency is left on the critical path. */
+    int slot = blockIdx.x * DESC_NW + warp;
+    struct Item { int level, o, slot; uint32_t v; bool ok; };
+/* resolve the next occupied slot at or after `slot` and start the load of its coordinates */
+#define DESC_NEXT(I)                                                                         \
+    do {                                                                                     \
+        I.ok = false; I.level = 0; I.o = 0; I.slot = 0; I.v = 0;                             \
+        while (slot < kp_total) {                                                            \
+            const int lv_ = __popc(__ballot_sync(0xffffffffu, slot >= my_off)) - 1;          \
+            const int idx_ = slot - __shfl_sync(0xffffffffu, my_off, lv_);                   \
+            const int s_ = slot;                                                             \
+            slot += warps_per_frame;                                                         \
+            if (idx_ < __shfl_sync(0xffffffffu, my_cnt, lv_)) {                              \
+                I.ok = true; I.level = lv_; I.slot = s_;                                     \
+                I.o = __shfl_sync(0xffffffffu, my_base, lv_) + idx_;                         \
+                I.v = lkp_xy[fkp + s_];                                                      \
+                break;                                                                       \
+            }                                                                                \
+        }                                                                                    \
+    } while (0)
+/* into buffer `bufi`: blurred rows y-18..y+18 from the aligned word holding x-18 (37 rows), then
+ * unblurred rows y-15..y+15 from the aligned word holding x-15 (31 rows); lanes 0..29 cover
+ * 3 rows x 10 words per step */
+#define DESC_CP(dst_, src_) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_), "l"(src_) : "memory")
+#define DESC_STAGE(I, bufi)                                                                  \
+    do {                                                                                     \
+        if (I.ok && lane < 30) {                                                             \
+            const BorbLevel &Ls = plan->lv[I.level];                                         \
+            const int xs = (int)(I.v & 0xffff), ys = (int)(I.v >> 16);                       \
+            const size_t lo_ = (size_t)frame * (size_t)plan->pyr_bytes + Ls.off +            \
+                               (size_t)BORB_EDGE * Ls.pitch + BORB_XPAD;                     \
+            const ptrdiff_t adv = (ptrdiff_t)3 * Ls.pitch;                                   \
+            const uint8_t *bp = blur + lo_ + (ptrdiff_t)(ys - 18 + st_r) * Ls.pitch + ((xs - 18) & ~3) + 4 * st_w; \
+            uint32_t dst = patch_s + ((bufi) * DESC_BUF + st_r * DESC_PW + st_w) * 4;        \
+            _Pragma("unroll") for (int it = 0; it < 12; ++it) {                              \
+                DESC_CP(dst, bp);                                                            \
+                bp += adv;                                                                   \
+                dst += 3 * DESC_PW * 4;                                                      \
+            }                                                                                \
+            if (st_r == 0) DESC_CP(dst, bp); /* row 36 */                                    \
+            const uint8_t *ip = pyr + lo_ + (ptrdiff_t)(ys - 15 + st_r) * Ls.pitch + ((xs - 15) & ~3) + 4 * st_w; \
+            dst = patch_s + ((bufi) * DESC_BUF + (DESC_PR + st_r) * DESC_PW + st_w) * 4;     \
+            _Pragma("unroll") for (int it = 0; it < 10; ++it) {                              \
+                DESC_CP(dst, ip);                                                            \
+                ip += adv;                                                                   \
+                dst += 3 * DESC_PW * 4;                                                      \
+            }                                                                                \
+            if (st_r == 0) DESC_CP(dst, ip); /* row 30 */                                    \
+        }                                                                                    \
+        asm volatile("cp.async.commit_group;" ::: "memory");                                 \
+    } while (0)
+
+    Item cur, nxt;
+    DESC_NEXT(cur);
+    DESC_STAGE(cur, 0);
+    DESC_NEXT(nxt);
+    int buf = 0;
+    while (cur.ok) {
+        DESC_STAGE(nxt, buf ^ 1); /* commits a (possibly empty) group: the count stays in step */
+        Item nn;
+        DESC_NEXT(nn);
+
+        const int level = cur.level, o = cur.o;
         const BorbLevel &L = plan->lv[level];
-        const int pitch = L.pitch;
-
-        const uint32_t v = lkp_xy[(size_t)frame * kp_total + slot];
-        const int x = (int)(v & 0xffff), y = (int)(v >> 16);
-        const size_t lo = (size_t)frame * (size_t)plan->pyr_bytes + L.off + (size_t)BORB_EDGE * pitch + BORB_XPAD;
-
-        /* ---- K6 staging first (independent of the angle): blurred rows y-18..y+18, columns from
-         * the aligned word holding x-18.  Lanes 0..29 cover 3 rows x 10 words per step. ---- */
-        const int xa = (x - 18) & ~3, xo = (x - 18) - xa;
-        if (lane < 30) {
-            const uint8_t *bp = blur + lo + (ptrdiff_t)(y - 18 + st_r) * pitch + xa + 4 * st_w;
-            const ptrdiff_t adv = (ptrdiff_t)3 * pitch;
-            uint32_t *pp = patch + st_r * DESC_PW + st_w;
-#pragma unroll
-            for (int it = 0; it < 12; ++it) {
-                pp[it * 3 * DESC_PW] = __ldg(reinterpret_cast<const uint32_t *>(bp));
-                bp += adv;
-            }
-            if (st_r == 0) pp[12 * 3 * DESC_PW] = __ldg(reinterpret_cast<const uint32_t *>(bp)); /* row 36 */
-        }
+        const int x = (int)(cur.v & 0xffff), y = (int)(cur.v >> 16);
+        const int xo = (x - 18) & 3;
+        const uint32_t *bufp = patch + buf * DESC_BUF;
+        asm volatile("cp.async.wait_group 1;" ::: "memory"); /* this keypoint's two regions have landed */
+        __syncwarp();
 
         /* ---- K4: lane u-15 owns disc column u and the rows |v| <= umax[|u|] (the disc is
          * symmetric: column u reaches as far as row u does, src/ORBextractor.cc:504-520) ---- */
         int m10 = 0, m01 = 0;
         if (lane < 31) {
-            const uint8_t *dn = pyr + lo + (ptrdiff_t)y * pitch + x + ic_u;
+            const uint8_t *dn = reinterpret_cast<const uint8_t *>(bufp + (DESC_PR + 15) * DESC_PW) + ((x - 15) & 3) + lane;
             const uint8_t *up = dn;
             int colsum = *dn;
 #pragma unroll
             for (int vr = 1; vr <= 15; ++vr) {
-                dn += pitch;
-                up -= pitch;
+                dn += DESC_PW * 4;
+                up -= DESC_PW * 4;
                 if (vr <= ic_vmax) {
                     const int pd = *dn, pu = *up;
                     colsum += pd + pu;
@@ -160,8 +212,7 @@ k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restri
         const float factor_pi = (float)(3.1415926535897932384626433832795 / 180.f);
         float a, b;
         orb_sincosf_exact(__fmul_rn(angle, factor_pi), &b, &a);
-        __syncwarp();
-        const uint8_t *c = reinterpret_cast<const uint8_t *>(patch) + 18 * (DESC_PW * 4) + xo + 18;
+        const uint8_t *c = reinterpret_cast<const uint8_t *>(bufp) + 18 * (DESC_PW * 4) + xo + 18;
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -177,7 +228,7 @@ k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restri
             val |= (t[0] < t[1]) << k;
         }
         out_desc[((size_t)frame * kp_total + o) * 32 + lane] = (uint8_t)val;
-        __syncwarp(); /* the patch is rewritten by the next keypoint */
+        __syncwarp(); /* this half of the patch buffer is refilled during the next iteration */
 
         /* ---- K7: lanes 0..6 write one 4-byte field each of the cv::KeyPoint record ---- */
         if (lane < 7) {
@@ -187,12 +238,18 @@ k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restri
             else if (lane == 1) f = __float_as_uint(level != 0 ? __fmul_rn((float)y, s) : (float)y);
             else if (lane == 2) f = __float_as_uint(L.patch_size);
             else if (lane == 3) f = __float_as_uint(angle);
-            else if (lane == 4) f = __float_as_uint((float)lkp_score[(size_t)frame * kp_total + slot]);
+            else if (lane == 4) f = __float_as_uint((float)lkp_score[fkp + cur.slot]);
             else if (lane == 5) f = (uint32_t)level;
             else f = 0xffffffffu; /* class_id = -1 */
             reinterpret_cast<uint32_t *>(out_kp + (size_t)frame * kp_total + o)[lane] = f;
         }
+        cur = nxt;
+        nxt = nn;
+        buf ^= 1;
     }
+#undef DESC_NEXT
+#undef DESC_STAGE
+#undef DESC_CP
 }
 
 #endif
