@@ -21,14 +21,22 @@
 #include "borb_internal.h"
 
 #define BLUR_NT 128 /* 4 warps = 4 consecutive strips of the tile list */
+#ifndef BLUR_PF
+#define BLUR_PF 2 /* rows prefetched ahead */
+#endif
 
-__device__ __forceinline__ void blur_row_sums(const uint8_t *__restrict__ row, int c, int cmax, uint32_t h[4])
+/* words at columns c-4, c, c+4 of a row (row is 4-byte aligned at column 0; c is a multiple of 4);
+ * c2 = min(c + 4, last readable word column of the padded row) */
+__device__ __forceinline__ uint3 blur_load(const uint8_t *__restrict__ row, int c, int c2)
 {
-    /* words at columns c-4, c, c+4 (row is 4-byte aligned at column 0; c is a multiple of 4);
-     * cmax = last readable word column of the padded row */
-    const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t *>(row + c - 4));
-    const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t *>(row + c));
-    const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t *>(row + min(c + 4, cmax)));
+    return make_uint3(__ldg(reinterpret_cast<const uint32_t *>(row + c - 4)),
+                      __ldg(reinterpret_cast<const uint32_t *>(row + c)),
+                      __ldg(reinterpret_cast<const uint32_t *>(row + c2)));
+}
+
+__device__ __forceinline__ void blur_row_sums(const uint3 w, uint32_t h[4])
+{
+    const uint32_t w0 = w.x, w1 = w.y, w2 = w.z;
     const uint32_t klo = 18u | (34u << 8) | (48u << 16) | (56u << 24); /* taps 0..3 */
     const uint32_t khi = 48u | (34u << 8) | (18u << 16);               /* taps 4..6 */
     /* output column c+i needs bytes c+i-3 .. c+i+3 */
@@ -61,10 +69,17 @@ k_blur_strips(const BorbPlan *__restrict__ plan, const BorbTile *__restrict__ ti
     const int cmax = L.pitch - BORB_XPAD - 4;
     const int rows = min(BORB_BLUR_TH, L.h - t.y0);
 
+    const int c2 = min(c + 4, cmax);
     uint32_t H[7][4];
 #pragma unroll
-    for (int r = 0; r < 6; ++r) blur_row_sums(in + (ptrdiff_t)(t.y0 - 3 + r) * L.pitch, c, cmax, H[r]);
+    for (int r = 0; r < 6; ++r) blur_row_sums(blur_load(in + (ptrdiff_t)(t.y0 - 3 + r) * L.pitch, c, c2), H[r]);
 
+    /* the words of the BLUR_PF rows after the one being filtered are already in flight (software
+     * prefetch: the kernel is bound by load latency, not by bandwidth) */
+    uint3 q[BLUR_PF]; /* q[i] = row y0 + 3 + r + i when output row r is next */
+#pragma unroll
+    for (int i = 0; i < BLUR_PF; ++i) q[i] = blur_load(in + (ptrdiff_t)(t.y0 + 3 + min(i, rows - 1)) * L.pitch, c, c2);
+    const uint8_t *nrow = in + (ptrdiff_t)(t.y0 + 3 + BLUR_PF) * L.pitch;
     for (int r0 = 0; r0 < rows; r0 += 7) {
 #pragma unroll
         for (int u = 0; u < 7; ++u) {
@@ -72,7 +87,12 @@ k_blur_strips(const BorbPlan *__restrict__ plan, const BorbTile *__restrict__ ti
             if (r < rows) {
                 /* the row entering the window is y0 + r + 3, into slot (6 + u) % 7; the window for
                  * output row r is slots u, u+1, ..., u+6 (mod 7) */
-                blur_row_sums(in + (ptrdiff_t)(t.y0 + r + 3) * L.pitch, c, cmax, H[(6 + u) % 7]);
+                const uint3 w = q[0];
+#pragma unroll
+                for (int i = 0; i + 1 < BLUR_PF; ++i) q[i] = q[i + 1];
+                if (r + BLUR_PF < rows) q[BLUR_PF - 1] = blur_load(nrow, c, c2);
+                nrow += L.pitch;
+                blur_row_sums(w, H[(6 + u) % 7]);
                 uint32_t v = 0;
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
