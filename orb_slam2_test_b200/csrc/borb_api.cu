@@ -352,7 +352,11 @@ int build_plan(borb_extractor *h, int cols, int rows)
                 c.sx = (short)(j * L.w_cell); c.sy = (short)(i * L.h_cell);
                 if (c.ww < 7 || c.wh < 7) continue; /* cv::FAST finds nothing in such a window */
                 c.wpr = ((c.x0 & 3) + c.ww + 3) >> 2;
-                c.dmagic = fast_div_magic(c.ww - 6);
+                {   /* stage-1 geometry of K2: Q words cover a domain row, R = rows per warp step */
+                    const int b0 = (c.x0 & 3) + 3, dw = c.ww - 6;
+                    const int Q = ((b0 + dw - 1) >> 2) - (b0 >> 2) + 1;
+                    c.dmagic = (unsigned)Q | ((unsigned)std::min(8, 32 / Q) << 8);
+                }
                 c.wmagic = fast_div_magic(c.wpr);
                 c.pad2 = 0;
                 cells.push_back(c);

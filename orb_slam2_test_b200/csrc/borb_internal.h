@@ -57,8 +57,8 @@ struct BorbCell { /* one FAST window, reference :1000-1064 */
     short x0, y0;     /* window origin in level pixels */
     short ww, wh;     /* window size */
     short sx, sy;     /* j*wCell, i*hCell: shift added to window-relative coords */
-    /* derived, so the kernel divides by multiply-shift: words per staged row and the magic
-     * numbers of fast_div() for (ww-6) and wpr */
+    /* derived on the host: words per staged row, its fast_div() magic number, and the stage-1
+     * lane geometry dmagic = Q | R << 8 (Q words cover a detection-domain row, R rows per warp step) */
     int wpr;
     unsigned dmagic, wmagic;
     int pad2;

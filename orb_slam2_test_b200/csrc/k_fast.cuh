@@ -217,10 +217,25 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
         const BorbLevel &L = plan->lv[cell.level];
         const int xoff = cell.x0 & 3;
         const int dw = cell.ww - 6, dh = cell.wh - 6; /* detection domain */
-        const int npix = dw * dh;
-        const uint32_t dmagic = cell.dmagic;
 
         const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
+        /* stage-1 lane geometry: Q words cover a domain row (byte xoff+3 .. xoff+3+dw-1 of the staged
+         * row), R rows per warp step; this lane: row s1_rig of the step, word s1_ql of the row */
+        const int s1_b0 = xoff + 3, s1_w0 = s1_b0 >> 2;
+        const int s1_Q = ((s1_b0 + dw - 1) >> 2) - s1_w0 + 1;
+        const int s1_R = (int)(cell.dmagic >> 8);
+        int s1_rig = 0;
+#pragma unroll
+        for (int k = 1; k < 8; ++k) s1_rig += lane >= k * s1_Q;
+        const bool s1_on = s1_rig < s1_R;
+        const int s1_ql = lane - s1_rig * s1_Q;
+        const int s1_col = 4 * (s1_w0 + s1_ql) - s1_b0; /* domain x of this lane's first pixel (may be < 0) */
+        const uint32_t s1_vlo = ((unsigned)s1_col < (unsigned)dw ? 0x00000600u : 0u) |
+                                ((unsigned)(s1_col + 1) < (unsigned)dw ? 0x06000000u : 0u);
+        const uint32_t s1_vhi = ((unsigned)(s1_col + 2) < (unsigned)dw ? 0x00000600u : 0u) |
+                                ((unsigned)(s1_col + 3) < (unsigned)dw ? 0x06000000u : 0u);
+        const uint32_t *s1_qp = reinterpret_cast<const uint32_t *>(win + 3 * FAST_WPITCH) + s1_w0 + s1_ql +
+                                s1_rig * (FAST_WPITCH / 4);
         int n2 = 0, n3 = 0, cell_total = 0;
         /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
          * where the first found nothing; K(ini) needs nothing below ini: a corner's score is at
@@ -231,27 +246,60 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
         for (int pass = 0; pass < n_pass; ++pass) {
             const int t = pass == 0 ? ini : mn;
 
-            /* ---- stage 1: compass pre-test on this warp's pixels ---- */
+            /* ---- stage 1: compass pre-test, four pixels per lane ----
+             * A lane owns one aligned word (4 adjacent pixels) of a staged row; a warp covers R = 32/Q
+             * rows at a time (Q = words covering a domain row), row groups dealt round-robin to the
+             * warps.  The pixels are widened to two 16-bit fields per register so that one integer
+             * add/subtract tests two pixels against a ring pixel without borrows between fields:
+             *   dark   r < v - t  <=>  bit 9 of (v + 511 - t) - r     (field value in [1, 766])
+             *   bright r > v + t  <=>  bit 9 of (511 - t - v) + r
+             * a 9-arc covers two adjacent compass points, so the pre-test is (N|S) & (E|W). */
             int n1 = 0;
-            /* rows are dealt round-robin to the warps, a lane owns a column: no index arithmetic,
-             * every load is [row pointer + constant] */
-            for (int y = warp; y < dh; y += FAST_NW)
-            for (int x0 = 0; x0 < dw; x0 += 32) {
-                const int x = x0 + lane;
-                uint32_t side = 0;
-                const uint32_t pix = (uint32_t)(y * 64 + x);
-                if (x < dw) {
-                    const uint8_t *p = org + y * FAST_WPITCH + x;
-                    const int v = p[0];
-                    const int lo = v - t, hi = v + t;
-                    const int r0 = p[3 * FAST_WPITCH], r4 = p[3], r8 = p[-3 * FAST_WPITCH], r12 = p[-3];
-                    /* a 9-arc covers two adjacent compass points */
-                    if (((r0 < lo) || (r8 < lo)) && ((r4 < lo) || (r12 < lo))) side |= 1u;
-                    if (((r0 > hi) || (r8 > hi)) && ((r4 > hi) || (r12 > hi))) side |= 2u;
+            const uint32_t Kt = (uint32_t)(511 - min(t, 255)) * 0x00010001u;
+            for (int y0 = warp * s1_R; y0 < dh; y0 += FAST_NW * s1_R) {
+                const int y = y0 + s1_rig;
+                uint32_t s_lo = 0, s_hi = 0;
+                if (s1_on && y < dh) {
+                    const uint32_t *rw = s1_qp + y0 * (FAST_WPITCH / 4);
+                    const uint32_t C = rw[0], N = rw[-3 * (FAST_WPITCH / 4)], S = rw[3 * (FAST_WPITCH / 4)];
+                    const uint32_t E = __byte_perm(C, rw[1], 0x6543), W = __byte_perm(rw[-1], C, 0x4321);
+#define F16LO(X) __byte_perm(X, 0u, 0x4140)
+#define F16HI(X) __byte_perm(X, 0u, 0x4342)
+                    {
+                        const uint32_t v = F16LO(C), A = v + Kt, B = Kt - v;
+                        const uint32_t n = F16LO(N), s_ = F16LO(S), e = F16LO(E), w = F16LO(W);
+                        const uint32_t dk = ((A - n) | (A - s_)) & ((A - e) | (A - w));
+                        const uint32_t br = ((B + n) | (B + s_)) & ((B + e) | (B + w));
+                        s_lo = ((dk & 0x02000200u) | ((br & 0x02000200u) << 1)) & s1_vlo;
+                    }
+                    {
+                        const uint32_t v = F16HI(C), A = v + Kt, B = Kt - v;
+                        const uint32_t n = F16HI(N), s_ = F16HI(S), e = F16HI(E), w = F16HI(W);
+                        const uint32_t dk = ((A - n) | (A - s_)) & ((A - e) | (A - w));
+                        const uint32_t br = ((B + n) | (B + s_)) & ((B + e) | (B + w));
+                        s_hi = ((dk & 0x02000200u) | ((br & 0x02000200u) << 1)) & s1_vhi;
+                    }
+#undef F16LO
+#undef F16HI
                 }
-                const uint32_t bal = __ballot_sync(0xffffffffu, side != 0);
-                if (side) list1[n1 + __popc(bal & below)] = (uint16_t)(pix | (side << 12));
-                n1 += __popc(bal);
+                /* flagged pixels of this lane (bit 9 = dark, bit 10 = bright, per field) */
+                const uint32_t any_lo = (s_lo | (s_lo >> 1)) & 0x02000200u, any_hi = (s_hi | (s_hi >> 1)) & 0x02000200u;
+                const int c = __popc(any_lo | (any_hi >> 1));
+                if (__ballot_sync(0xffffffffu, c != 0) == 0u) continue;
+                int inc = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int up = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += up;
+                }
+                uint16_t *dst = list1 + n1 + inc - c;
+                n1 += __shfl_sync(0xffffffffu, inc, 31);
+                const uint32_t pixb = (uint32_t)((y << 6) + s1_col);
+                const uint32_t sd0 = (s_lo >> 9) & 3u, sd1 = (s_lo >> 25) & 3u, sd2 = (s_hi >> 9) & 3u, sd3 = (s_hi >> 25) & 3u;
+                if (sd0) *dst++ = (uint16_t)(pixb | (sd0 << 12));
+                if (sd1) *dst++ = (uint16_t)((pixb + 1) | (sd1 << 12));
+                if (sd2) *dst++ = (uint16_t)((pixb + 2) | (sd2 << 12));
+                if (sd3) *dst++ = (uint16_t)((pixb + 3) | (sd3 << 12));
             }
             __syncwarp();
 
