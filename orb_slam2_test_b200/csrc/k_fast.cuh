@@ -131,6 +131,26 @@ __device__ __forceinline__ int fast_arc_minmax(const int *e)
     return M;
 }
 
+/* The same on 16-bit pairs: P[j] holds the (biased, positive) contrasts of ring positions j and
+ * j + 8 in its two halves, so one packed min/max (VIMNMX.S16x2) advances two arc positions; the
+ * wrap-around of the circular windows is a half-word swap.  Inputs in [0, 32767]; returns the
+ * max over the 16 circular 9-arcs of the arc minimum (same bias as the inputs). */
+__device__ __forceinline__ uint32_t fast_swap16(uint32_t v) { return __byte_perm(v, 0u, 0x1032); }
+__device__ __forceinline__ int fast_arc_minmax_s16x2(const uint32_t *P)
+{
+    uint32_t Q[8], R[8], S[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) Q[j] = __vmins2(P[j], j + 1 < 8 ? P[j + 1] : fast_swap16(P[j + 1 - 8]));
+#pragma unroll
+    for (int j = 0; j < 8; ++j) R[j] = __vmins2(Q[j], j + 2 < 8 ? Q[j + 2] : fast_swap16(Q[j + 2 - 8]));
+#pragma unroll
+    for (int j = 0; j < 8; ++j) S[j] = __vmins2(R[j], j + 4 < 8 ? R[j + 4] : fast_swap16(R[j + 4 - 8]));
+    uint32_t M = 0u;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) M = __vmaxs2(M, __vmins2(S[j], fast_swap16(P[j])));
+    return max((int)(M & 0xffffu), (int)(M >> 16));
+}
+
 /* Shared memory of one CTA, sized on the host for the largest cell of the plan (K2k: 33x40 px ->
  * 18 KB; the 60x60 worst case of the cell formula needs 44 KB).  chunk = pixels per warp. */
 #define FAST_NW (FAST_NT / 32)
@@ -313,23 +333,28 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
                     const int x = ent & 63, y = (ent >> 6) & 63;
                     const uint8_t *p = org + y * FAST_WPITCH + x;
                     const int v = p[0];
-                    int r[16];
+                    /* ring positions j and j + 8 packed as 16-bit halves */
+                    uint32_t rp[8];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) r[k] = (int)FAST_RING(p, FAST_WPITCH, k);
+                    for (int k = 0; k < 8; ++k)
+                        rp[k] = (uint32_t)FAST_RING(p, FAST_WPITCH, k) | ((uint32_t)FAST_RING(p, FAST_WPITCH, k + 8) << 16);
                     int M = 0;
-                    {   /* contrast on the flagged side (bright if flagged bright) */
-                        const bool bright = (ent & (1u << 12)) != 0;
-                        const int sgn = bright ? -1 : 1, off = bright ? v : -v;
-                        int e[16];
+                    {   /* contrast on the flagged side, biased by 256 so both halves stay positive:
+                         * ring darker (bit 12): 256 + v - r, else 256 + r - v */
+                        const bool darker = (ent & (1u << 12)) != 0;
+                        const int sgn = darker ? -1 : 1;
+                        const uint32_t off = (uint32_t)(256 + (darker ? v : -v)) * 0x00010001u;
+                        uint32_t e[8];
 #pragma unroll
-                        for (int k = 0; k < 16; ++k) e[k] = sgn * r[k] + off;
-                        M = fast_arc_minmax(e);
+                        for (int k = 0; k < 8; ++k) e[k] = (uint32_t)sgn * rp[k] + off;
+                        M = fast_arc_minmax_s16x2(e) - 256;
                     }
-                    if (M <= t && (ent >> 12) == 3u) { /* flagged on both sides (rare): try dark */
-                        int e[16];
+                    if (M <= t && (ent >> 12) == 3u) { /* flagged on both sides (rare): try the other */
+                        const uint32_t off = (uint32_t)(256 - v) * 0x00010001u;
+                        uint32_t e[8];
 #pragma unroll
-                        for (int k = 0; k < 16; ++k) e[k] = r[k] - v;
-                        M = fast_arc_minmax(e);
+                        for (int k = 0; k < 8; ++k) e[k] = rp[k] + off;
+                        M = fast_arc_minmax_s16x2(e) - 256;
                     }
                     corner = M > t;
                     if (corner) sc[(y + 1) * FAST_SPITCH + x + 1] = (uint8_t)(M - 1);
