@@ -67,21 +67,56 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """SM clock and throttle reasons sampled WHILE the timed region runs: NVML every 5 ms from a
+    thread (a timed region is tens of milliseconds; an nvidia-smi subprocess cannot sample that
+    fast, least of all on an 8-GPU box); nvidia-smi -lms as the fallback when pynvml is missing."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    BITS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
     def __init__(self, gpu: int):
         self.gpu, self.rows, self.proc = gpu, [], None
+        self.sm, self.mx, self.reasons, self.stop_flag, self.thread, self.src = [], [], set(), False, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # LOCAL_RANK indexes CUDA_VISIBLE_DEVICES; NVML indexes physical devices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[gpu]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else gpu
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.src = "nvml"
+        except Exception:
+            self.nv = None
+
+    def _poll(self):
+        nv, h = self.nv, self.h
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                self.mx.append(float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)))
+                get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                mask = int(get(h))
+                for name, bit in self.BITS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def start(self):
+        if self.nv is not None:
+            self.stop_flag = False
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
+            self.src = "nvidia-smi"
         except Exception:
             self.proc = None
 
@@ -90,10 +125,13 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self) -> dict:
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join()
         if self.proc:
             time.sleep(0.15)
             self.proc.terminate()
-        sm, mx, reasons = [], [], set()
+        sm, mx, reasons = list(self.sm), list(self.mx), set(self.reasons)
         for r in self.rows:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
@@ -103,7 +141,36 @@ class ClockSampler:
             except Exception:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.src}
+
+
+def bind_near_gpu(local: int) -> str:
+    """Run this rank (and so first-touch its pinned buffers) on the CPU cores of the NUMA node the
+    GPU hangs off: with several GPUs per box the host<->device copies of the e2e measurement
+    otherwise cross the socket interconnect.  Returns a note for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else local
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(idx)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return "numa: single node"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"numa: bound to node {node} ({len(cpus)} cpus)"
+        return f"numa: node {node} has no allowed cpus"
+    except Exception as e:
+        return f"numa: not bound ({type(e).__name__})"
 
 
 def dist_setup(n_gpus: int):
@@ -405,6 +472,8 @@ def run_ours(args, rank, world, local):
     from orb_slam2_test_b200.sequence import shard_indices
 
     torch.cuda.set_device(local)
+    all_cpus = os.sched_getaffinity(0)
+    numa_note = bind_near_gpu(local)  # before any pinned allocation (first touch)
     F = args.frames_per_step
     W = max(args.warmup, 3)
     # this rank's shard of the synthetic sequence: frame f belongs to rank f mod world (frames are a
@@ -568,6 +637,7 @@ def run_ours(args, rank, world, local):
     dom_s = st[dom] / 1e3
     achieved = stage_bytes[dom] * F / dom_s / 1e9
     step_ms = ms_max / args.steps
+    os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core
     cores = len(os.sched_getaffinity(0))
     cpu = None
     if world == 1:
@@ -585,7 +655,7 @@ def run_ours(args, rank, world, local):
         "e2e": {"value": e2e_value, "unit": "frames/s",
                 "h2d_bytes_per_step": n_sub * sub * ROWS * COLS,
                 "d2h_bytes_per_step": int(kp_bytes / max(args.steps, 1)),
-                "how": f"{depth} handles x {sub}-frame batches in flight, pinned host buffers, wall clock"},
+                "how": f"{depth} handles x {sub}-frame batches in flight, pinned host buffers, wall clock; {numa_note}"},
         "gpu_launches": args.steps * launches_per_call,
         "roofline": {"bound": "hbm", "kernel": STAGE_KERNEL[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(STAGE_KERNEL[dom], F), "peak_source": peak_src,
