@@ -360,7 +360,7 @@ def poststep_section(ORBextractor, synth, local):
                 tot.append(ext.timer_ms())
         res["with" if cam else "without"] = (float(np.median(d)), float(np.median(tot)))
     out = {"reference": "src/Frame.cc:542-572, :574-609, :292-307", "config": "TUM1.yaml camera, 640x480, 1000 kp, 128 frames",
-           "parity": "bit-exact against oracle/frame_oracle.c (undistortPoints pinned to cv2 4.13.0)",
+           "parity": "bit-exact against oracle/frame_oracle.c (undistortPoints pinned to cv2 4.13.0; whole step pinned to the reference's own Frame.cc, oracle/_ref/libreframe.so)",
            "k8_ms_per_128_frames": res["with"][0] - res["without"][0],
            "call_ms_without": res["without"][1], "call_ms_with": res["with"][1]}
     try:
@@ -388,7 +388,7 @@ def stereo_section(ORBextractor, synth, local, two, dev):
     import threading
     BF, FX = 386.1448, 718.856
     mb = BF / FX
-    out = {"reference": "src/Frame.cc:619-834", "parity": "bit-exact against oracle/stereo_oracle.cpp (oracle unpinned)"}
+    out = {"reference": "src/Frame.cc:619-834", "parity": "bit-exact against oracle/stereo_oracle.cpp, which is pinned to the reference's own Frame.cc (oracle/_ref/libreframe.so)"}
     li = synth.make_frame((ROWS, COLS), seed=31, frame=0, eye=0)
     ri = synth.make_frame((ROWS, COLS), seed=31, frame=0, eye=1)
     imgs = [li, ri]

@@ -8,6 +8,10 @@
  * u8 plane with ROI views; assignment from Mat::zeros() fills an already-allocated destination in
  * place (as cv::MatExpr does), which the reference relies on at src/ORBextractor.cc:1313.
  * The five image primitives forward to oracle/cvprim.c, pinned bit-exact to OpenCV 4.13.0.
+ * For the reference's src/Frame.cc (oracle/_ref/libreframe.so) cv::Mat also carries an element type
+ * (8-bit or float, 1-2 channels) with the small float algebra that file uses (t(), *, +, -, norm,
+ * Mat_<float> comma initialiser, reshape); cv::undistortPoints forwards to oracle/frame_oracle.c,
+ * pinned bit-exact to OpenCV 4.13.0.
  *
  * The same header doubles as the "no OpenCV on this box" build of the product's C++ host shim
  * (orb_slam2_test_b200/shim), which needs nothing beyond Mat/KeyPoint/InputArray/OutputArray.
@@ -17,6 +21,7 @@
 
 #include <algorithm>
 #include <cassert>
+#include <climits>
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
@@ -32,6 +37,9 @@
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_32F 5
+#define CV_32FC1 5
+#define CV_32FC2 13
 #define CVCOMPAT_SHIM 1
 
 typedef unsigned char uchar;
@@ -116,20 +124,24 @@ public:
     uchar *data;
     size_t step;
 
-    Mat() : rows(0), cols(0), data(nullptr), step(0) {}
-    Mat(Size sz, int type) : rows(0), cols(0), data(nullptr), step(0) { create(sz.height, sz.width, type); }
-    Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr), step(0) { create(r, c, type); }
+    Mat() : rows(0), cols(0), data(nullptr), step(0), type_(CV_8UC1) {}
+    Mat(Size sz, int type) : rows(0), cols(0), data(nullptr), step(0), type_(type) { create(sz.height, sz.width, type); }
+    Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr), step(0), type_(type) { create(r, c, type); }
     /* header over caller-owned memory (no ownership) */
-    Mat(int r, int c, int /*type*/, void *ext, size_t ext_step = 0)
-        : rows(r), cols(c), data((uchar *)ext), step(ext_step ? ext_step : (size_t)c) {}
-
-    void create(int r, int c, int /*type*/)
+    Mat(int r, int c, int type, void *ext, size_t ext_step = 0)
+        : rows(r), cols(c), data((uchar *)ext), step(0), type_(type)
     {
-        if (data && r == rows && c == cols) return;
+        step = ext_step ? ext_step : (size_t)c * elemSize();
+    }
+
+    void create(int r, int c, int type)
+    {
+        if (data && r == rows && c == cols && type == type_) return;
+        type_ = type;
         rows = r;
         cols = c;
-        step = (size_t)c;
-        const size_t n = (size_t)r * (size_t)c;
+        step = (size_t)c * elemSize();
+        const size_t n = (size_t)r * step;
         store_.reset(n ? new uchar[n] : nullptr, std::default_delete<uchar[]>());
         data = store_.get();
     }
@@ -142,37 +154,55 @@ public:
         step = 0;
     }
 
-    int type() const { return CV_8UC1; }
+    int type() const { return type_; }
+    int channels() const { return (type_ >> 3) + 1; }
+    size_t elemSize() const { return (size_t)channels() * ((type_ & 7) == CV_32F ? 4 : 1); }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     size_t step1() const { return step; }
-    bool isContinuous() const { return step == (size_t)cols || rows <= 1; }
+    bool isContinuous() const { return step == (size_t)cols * elemSize() || rows <= 1; }
     size_t total() const { return (size_t)rows * (size_t)cols; }
 
     Mat operator()(const Rect &r) const
     {
         Mat m(*this);
-        m.data = data + (size_t)r.y * step + r.x;
+        m.data = data + (size_t)r.y * step + (size_t)r.x * elemSize();
         m.rows = r.height;
         m.cols = r.width;
         return m;
     }
     Mat rowRange(int a, int b) const { return (*this)(Rect(0, a, cols, b - a)); }
     Mat colRange(int a, int b) const { return (*this)(Rect(a, 0, b - a, rows)); }
+    Mat row(int y) const { return rowRange(y, y + 1); }
+    Mat col(int x) const { return colRange(x, x + 1); }
 
     Mat clone() const
     {
-        Mat m(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols);
+        Mat m(rows, cols, type_);
+        for (int y = 0; y < rows; ++y)
+            std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols * elemSize());
         return m;
     }
     void copyTo(Mat &dst) const
     {
-        dst.create(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(dst.data + (size_t)y * dst.step, data + (size_t)y * step, (size_t)cols);
+        dst.create(rows, cols, type_);
+        for (int y = 0; y < rows; ++y)
+            std::memcpy(dst.data + (size_t)y * dst.step, data + (size_t)y * step, (size_t)cols * elemSize());
+    }
+    /* same data, `cn` channels per element (rows unchanged), as cv::Mat::reshape(cn) on a continuous matrix */
+    Mat reshape(int cn) const
+    {
+        Mat m(*this);
+        const int scalars = cols * channels();
+        m.type_ = (type_ & 7) | ((cn - 1) << 3);
+        m.cols = scalars / cn;
+        return m;
     }
 
     template <typename T> T &at(int y, int x) { return *(T *)(data + (size_t)y * step + (size_t)x * sizeof(T)); }
     template <typename T> const T &at(int y, int x) const { return *(const T *)(data + (size_t)y * step + (size_t)x * sizeof(T)); }
+    /* single index: element i of a row or column vector */
+    template <typename T> T &at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+    template <typename T> const T &at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
     uchar *ptr(int y = 0) { return data + (size_t)y * step; }
     const uchar *ptr(int y = 0) const { return data + (size_t)y * step; }
     template <typename T> T *ptr(int y = 0) { return (T *)(data + (size_t)y * step); }
@@ -183,12 +213,114 @@ public:
     Mat &operator=(const MatZeros &z)
     {
         create(z.rows, z.cols, z.type);
-        for (int y = 0; y < rows; ++y) std::memset(data + (size_t)y * step, 0, (size_t)cols);
+        for (int y = 0; y < rows; ++y) std::memset(data + (size_t)y * step, 0, (size_t)cols * elemSize());
         return *this;
+    }
+
+    /* 8-bit -> float conversion (the SAD windows of Frame::ComputeStereoMatches); may alias */
+    void convertTo(Mat &dst, int type) const
+    {
+        assert(type == CV_32F);
+        Mat m(rows, cols, CV_32F);
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x)
+                m.at<float>(y, x) = (type_ & 7) == CV_32F ? at<float>(y, x) : (float)at<uchar>(y, x);
+        dst = m;
+    }
+    static Mat ones(int r, int c, int type)
+    {
+        Mat m(r, c, type);
+        for (int y = 0; y < r; ++y)
+            for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.f;
+        return m;
+    }
+    double dot(const Mat &o) const
+    {
+        double s = 0;
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) s += (double)at<float>(y, x) * o.at<float>(y, x);
+        return s;
+    }
+
+    /* float (CV_32F, one channel) algebra used by the reference's Frame.cc pose code */
+    Mat t() const
+    {
+        Mat m(cols, rows, type_);
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
+        return m;
     }
 
 private:
     std::shared_ptr<uchar> store_;
+    int type_;
+};
+
+inline Mat operator*(const Mat &a, const Mat &b)
+{
+    Mat m(a.rows, b.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < b.cols; ++x) {
+            float s = 0.f;
+            for (int k = 0; k < a.cols; ++k) s += a.at<float>(y, k) * b.at<float>(k, x);
+            m.at<float>(y, x) = s;
+        }
+    return m;
+}
+inline Mat mat_lin_(const Mat &a, float sa, const Mat *b, float sb)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = sa * a.at<float>(y, x) + (b ? sb * b->at<float>(y, x) : 0.f);
+    return m;
+}
+inline Mat operator+(const Mat &a, const Mat &b) { return mat_lin_(a, 1.f, &b, 1.f); }
+inline Mat operator-(const Mat &a, const Mat &b) { return mat_lin_(a, 1.f, &b, -1.f); }
+inline Mat operator-(const Mat &a) { return mat_lin_(a, -1.f, nullptr, 0.f); }
+inline Mat operator*(float s, const Mat &a) { return mat_lin_(a, s, nullptr, 0.f); }
+enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
+/* L1 norm of a - b, accumulated in double as OpenCV does for CV_32F */
+inline double norm(const Mat &a, const Mat &b, int type)
+{
+    assert(type == NORM_L1);
+    (void)type;
+    double s = 0;
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) s += std::fabs((double)a.at<float>(y, x) - (double)b.at<float>(y, x));
+    return s;
+}
+inline double norm(const Mat &a)
+{
+    double s = 0;
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) s += (double)a.at<float>(y, x) * a.at<float>(y, x);
+    return std::sqrt(s);
+}
+
+/* (cv::Mat_<float>(r, c) << a, b, c) */
+template <typename T> class Mat_;
+template <typename T> class MatCommaInit_ {
+public:
+    MatCommaInit_(Mat m) : m_(m), i_(0) {}
+    MatCommaInit_ &operator,(T v)
+    {
+        m_.template at<T>(i_ / m_.cols, i_ % m_.cols) = v;
+        ++i_;
+        return *this;
+    }
+    operator Mat() const { return m_; }
+    Mat m_;
+    int i_;
+};
+template <typename T> class Mat_ : public Mat {
+public:
+    Mat_(int r, int c) : Mat(r, c, CV_32F) {}
+    MatCommaInit_<T> operator<<(T v)
+    {
+        MatCommaInit_<T> ci(*this);
+        ci, v;
+        return ci;
+    }
 };
 
 class _InputArray {
@@ -232,6 +364,8 @@ void GaussianBlur(InputArray src, OutputArray dst, Size ksize, double sigmaX, do
 void FAST(InputArray image, std::vector<KeyPoint> &keypoints, int threshold,
           bool nonmaxSuppression = true);
 float fastAtan2(float y, float x);
+/* float points [N x 1, 2 channels] (or N x 2), K and P 3x3 CV_32F, dist 4/5 x 1 CV_32F, R empty */
+void undistortPoints(InputArray src, OutputArray dst, InputArray K, InputArray dist, InputArray R, InputArray P);
 
 struct KeyPointsFilter {
     static void retainBest(std::vector<KeyPoint> &keypoints, int npoints);

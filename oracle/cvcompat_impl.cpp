@@ -8,6 +8,8 @@
  *   cv::GaussianBlur    <- :1377
  *   cv::FAST            <- :1069, :1074 (and the dead legacy path :1210, :1214)
  *   cv::fastAtan2       <- :110
+ * and, for the reference's src/Frame.cc (oracle/_ref/libreframe.so),
+ *   cv::undistortPoints <- /root/reference/src/Frame.cc:560, :594  -> oracle/frame_oracle.c
  */
 #include "opencv2/core/core.hpp"
 
@@ -77,6 +79,29 @@ void FAST(InputArray _img, std::vector<KeyPoint> &keypoints, int threshold, bool
 }
 
 float fastAtan2(float y, float x) { return cvp_fast_atan2(y, x); }
+
+extern "C" void fo_undistort_points(const float *xy, int n, const float *cam, float *out);
+
+/* the one call shape the reference uses: N float points, P == K, R empty */
+void undistortPoints(InputArray _src, OutputArray _dst, InputArray _K, InputArray _dist, InputArray, InputArray)
+{
+    const Mat src = _src.getMat(), K = _K.getMat(), D = _dist.getMat();
+    const int n = src.rows;
+    float cam[9] = {K.at<float>(0, 0), K.at<float>(1, 1), K.at<float>(0, 2), K.at<float>(1, 2), 0, 0, 0, 0, 0};
+    const int nd = D.rows * D.cols;
+    for (int i = 0; i < nd && i < 5; ++i) cam[4 + i] = D.at<float>(i);
+    std::vector<float> in((size_t)2 * n), out((size_t)2 * n);
+    for (int i = 0; i < n; ++i) {
+        in[2 * i] = src.ptr<float>(i)[0];
+        in[2 * i + 1] = src.ptr<float>(i)[1];
+    }
+    fo_undistort_points(in.data(), n, cam, out.data());
+    Mat &dst = _dst.getMatRef(); /* in place in the reference: same geometry */
+    for (int i = 0; i < n; ++i) {
+        dst.ptr<float>(i)[0] = out[2 * i];
+        dst.ptr<float>(i)[1] = out[2 * i + 1];
+    }
+}
 
 void KeyPointsFilter::retainBest(std::vector<KeyPoint> &, int)
 {

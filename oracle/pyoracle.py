@@ -331,3 +331,56 @@ class Reference(_Base):
         n = self.lib.reforb_distribute(self.h, xs.ctypes.data, ys.ctypes.data, resp.ctypes.data, len(xs),
                                        min_x, max_x, min_y, max_y, n_target, out.ctypes.data, len(out))
         return out[:n].copy()
+
+
+class _RefFrameOut(C.Structure):
+    _fields_ = [("n_left", C.c_int), ("n_right", C.c_int), ("bounds", C.c_float * 4)]
+
+
+class RefFrame:
+    """The reference's own src/Frame.cc (oracle/_ref/libreframe.so, built by oracle/Makefile):
+    its stereo constructor run on the reference's own extractor objects."""
+
+    _lib = None
+
+    @classmethod
+    def available(cls) -> bool:
+        return (HERE / "_ref" / "libreframe.so").exists()
+
+    @classmethod
+    def load(cls) -> C.CDLL:
+        if cls._lib is None:
+            lib = C.CDLL(str(HERE / "_ref" / "libreframe.so"))
+            lib.refframe_stereo.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int,
+                                            _vp, _vp, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int] + [_vp] * 10
+            cls._lib = lib
+        return cls._lib
+
+    @classmethod
+    def stereo(cls, left: np.ndarray, right: np.ndarray, K, dist, bf: float, mb: float, nfeatures=2000,
+               scale=1.2, nlevels=8, ini_th=20, min_th=7, canonical=True) -> dict:
+        """Frame(imLeft, imRight, ...) of the reference -> its mvKeys / mDescriptors (both eyes),
+        mvKeysUn positions, mvuRight, mvDepth, mGrid (as CSR) and image bounds.  `mb` is the value the
+        uninitialised member holds when ComputeStereoMatches reads it (see oracle/frame_driver.cpp);
+        canonical=True runs the two extraction threads with the monotone node allocator, so the
+        keypoints are the canonical ones (= oracle = CUDA path)."""
+        lib = cls.load()
+        left = np.ascontiguousarray(left); right = np.ascontiguousarray(right)
+        rows, cols = left.shape
+        cap = nfeatures + 64 * nlevels + 4096
+        kl = np.zeros(cap, KP_DTYPE); kr = np.zeros(cap, KP_DTYPE)
+        dl = np.zeros((cap, 32), np.uint8); dr = np.zeros((cap, 32), np.uint8)
+        un = np.zeros((cap, 2), np.float32); u = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32)
+        gc = np.zeros(64 * 48, np.int32); gi = np.zeros(cap, np.int32)
+        k4 = np.asarray(K, np.float32); d = np.asarray(dist, np.float32)
+        out = _RefFrameOut()
+        rc = lib.refframe_stereo(left.ctypes.data, right.ctypes.data, cols, rows, nfeatures, scale, nlevels, ini_th,
+                                 min_th, k4.ctypes.data, d.ctypes.data, len(d), bf, mb, int(canonical), cap, kl.ctypes.data,
+                                 dl.ctypes.data, kr.ctypes.data, dr.ctypes.data, un.ctypes.data, u.ctypes.data,
+                                 z.ctypes.data, gc.ctypes.data, gi.ctypes.data, C.addressof(out))
+        assert rc == 0
+        nl, nr = out.n_left, out.n_right
+        start = np.concatenate([[0], np.cumsum(gc)]).astype(np.int32)
+        return {"kps_l": kl[:nl].copy(), "desc_l": dl[:nl].copy(), "kps_r": kr[:nr].copy(), "desc_r": dr[:nr].copy(),
+                "un_xy": un[:nl].copy(), "u_right": u[:nl].copy(), "depth": z[:nl].copy(), "cell_start": start,
+                "cell_idx": gi[:start[-1]].copy(), "bounds": np.array(list(out.bounds), np.float32)}

@@ -3,9 +3,13 @@
  *
  * CPU restatement of Frame::ComputeStereoMatches (/root/reference/src/Frame.cc:619-834) with
  * ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1846-1862, TH_HIGH/TH_LOW :37-38), on flat
- * arrays.  PARITY UNPINNED: Frame.cc cannot be compiled here (it pulls in Eigen, g2o and DBoW2 types
- * through Frame.h/KeyFrame.h/MapPoint.h, none buildable on this image) and the reference has no test
- * for it, so this restatement is checked only against itself and the CUDA path.
+ * arrays.  PINNED against the reference's own src/Frame.cc: oracle/Makefile compiles that file where
+ * it lies into oracle/_ref/libreframe.so (stand-ins for the five headers it cannot have here are in
+ * oracle/framecompat/), and tests/test_oracle_frame_vs_reference.py requires this restatement, fed
+ * the reference Frame's own keypoints and descriptors, to reproduce its mvuRight / mvDepth bit for
+ * bit; tests/golden/frame_expected.npz carries such outputs to machines without the reference.
+ * (DescriptorDistance and TH_LOW/TH_HIGH are restated in framecompat/ORBmatcher.h: src/ORBmatcher.cc
+ * is not compilable here.)
  *
  * Notes on the reference's behaviour that are kept:
  *  - minZ = mb is read BEFORE the constructor assigns mb (src/Frame.cc:117 vs :140), i.e. it is

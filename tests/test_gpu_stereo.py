@@ -2,7 +2,9 @@
 restatement of Frame::ComputeStereoMatches (oracle/stereo_oracle.cpp, src/Frame.cc:619-834).
 
 Bar: mvuRight and mvDepth bit-exact (float32 bit patterns), same matched count.  The oracle for
-this row is PARITY UNPINNED (Frame.cc does not compile here: it needs OpenCV, DBoW2 and g2o).
+this row is pinned to the reference's own src/Frame.cc compiled in place (oracle/_ref/libreframe.so,
+tests/test_oracle_frame_vs_reference.py); tests/test_golden_frame.py compares the CUDA path with the
+reference Frame's outputs directly.
 """
 import numpy as np
 import pytest

@@ -1,6 +1,7 @@
 """CPU checks of the stereo oracle (oracle/stereo_oracle.cpp, a restatement of
-Frame::ComputeStereoMatches, src/Frame.cc:619-834).  PARITY UNPINNED: Frame.cc cannot be compiled
-here (OpenCV/DBoW2/g2o), so these are the properties the algorithm guarantees, not golden vectors.
+Frame::ComputeStereoMatches, src/Frame.cc:619-834): the properties the algorithm guarantees.  The pin
+against the reference's own compiled Frame.cc is tests/test_oracle_frame_vs_reference.py, the golden
+vectors generated from it are checked by tests/test_golden_frame.py.
 """
 import numpy as np
 
