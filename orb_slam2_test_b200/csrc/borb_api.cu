@@ -113,6 +113,8 @@ struct borb_extractor {
     BorbPlan plan;
     int qt_M = 0;
     int fast_smem = 0, n_sm = 148;
+    int fast_wp = 64;                   /* staged window pitch of K2 = TMA box width */
+    FastMaps fast_maps;                 /* one TMA descriptor per level, passed by value to K2 */
     int chunk = 0; /* frames per pass of the kernel chain (0 = whole call) */
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     std::vector<BorbCell> cells;
@@ -353,7 +355,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
                 if (c.ww < 7 || c.wh < 7) continue; /* cv::FAST finds nothing in such a window */
                 c.wpr = ((c.x0 & 3) + c.ww + 3) >> 2;
                 {   /* stage-1 geometry of K2: Q words cover a domain row, R = rows per warp step */
-                    const int b0 = (c.x0 & 3) + 3, dw = c.ww - 6;
+                    const int b0 = FAST_DOMAIN_BYTE(c.x0), dw = c.ww - 6;
                     const int Q = ((b0 + dw - 1) >> 2) - (b0 >> 2) + 1;
                     c.dmagic = (unsigned)Q | ((unsigned)std::min(8, 32 / Q) << 8);
                 }
@@ -361,6 +363,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
                 c.pad2 = 0;
                 cells.push_back(c);
                 P.fast_max_wh = std::max(P.fast_max_wh, (int)c.wh);
+                P.fast_max_ww = std::max(P.fast_max_ww, (int)c.ww);
                 P.fast_max_pix = std::max(P.fast_max_pix, (c.ww - 6) * (c.wh - 6));
                 cap += (long long)((c.ww - 6 + 1) / 2) * ((c.wh - 6 + 1) / 2);
             }
@@ -429,8 +432,34 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMemset(h->d_blur, 0, B * (size_t)P.pyr_bytes));
     CU(cudaMemset(h->d_pyr, 0, B * (size_t)P.pyr_bytes));
 
-    h->fast_smem = fast_smem_layout(P.fast_max_wh, P.fast_max_pix).bytes;
-    CU(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    h->fast_wp = FAST_WP_FOR(P.fast_max_ww);
+    h->fast_smem = fast_smem_layout(P.fast_max_wh, P.fast_max_pix, h->fast_wp).bytes;
+        CU(cudaFuncSetAttribute(k_fast_cells<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    CU(cudaFuncSetAttribute(k_fast_cells<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    CU(cudaFuncSetAttribute(k_fast_cells<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    {   /* TMA descriptors of K2's window loads: one 3-D map (column bytes, rows, frames) per padded
+         * level plane; box = fast_wp bytes x fast_max_wh rows x 1 frame */
+        typedef CUresult (*EncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                        const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (!fn || qres != cudaDriverEntryPointSuccess) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
+        CUtensorMap *maps = h->fast_maps.m;
+        std::memset(&h->fast_maps, 0, sizeof h->fast_maps);
+        for (int l = 0; l < P.nlevels; ++l) {
+            const BorbLevel &L = P.lv[l];
+            const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.prows, (cuuint64_t)B};
+            const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.pyr_bytes};
+            const cuuint32_t box[3] = {(cuuint32_t)h->fast_wp, (cuuint32_t)P.fast_max_wh, 1u};
+            const cuuint32_t estr[3] = {1u, 1u, 1u};
+            const CUresult r = ((EncodeTiled)fn)(&maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->d_pyr + L.off, dims, strides, box,
+                                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                 CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled(level %d) failed: %d", l, (int)r);
+        }
+    }
     h->qt_M = M;
     const size_t qt_smem = qt_smem_bytes(M);
     CU(cudaFuncSetAttribute(k_quadtree<QT_NT_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem));
@@ -529,8 +558,10 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             if (const char *e = getenv("BORB_FAST_GRID_Y")) grid.y = std::max(1, std::min(n, atoi(e)));
             grid.x = std::min(P.n_cells, std::max(1, ctas / (int)grid.y));
         }
-        k_fast_cells<<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, d_pyr, d_cand_xy,
-                                                          d_cand_score, d_ncand);
+#define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, h->fast_maps, f0, \
+                                                                   d_cand_xy, d_cand_score, d_ncand)
+        if (h->fast_wp == 64) K2(64); else if (h->fast_wp == 80) K2(80); else K2(96);
+#undef K2
     }
     STAGE(2);
     if (n * P.nlevels <= 2 * h->n_sm) /* few CTAs: give each one a whole SM's worth of threads */

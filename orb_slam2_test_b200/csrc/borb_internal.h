@@ -79,6 +79,7 @@ struct BorbPlan {
     int kp_total;           /* per frame */
     int n_cells, n_tiles;
     int fast_max_wh, fast_max_pix; /* tallest FAST window, largest detection domain (pixels) */
+    int fast_max_ww;               /* widest FAST window */
     int umax[16];
     BorbLevel lv[BORB_MAXL];
 };

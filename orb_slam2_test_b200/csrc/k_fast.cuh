@@ -35,12 +35,20 @@
 #ifndef K_FAST_CUH
 #define K_FAST_CUH
 
+#include <cuda.h> /* CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint) */
+
 #include "borb_internal.h"
 
 #ifndef FAST_NT
 #define FAST_NT 64 /* 2 warps per cell: measured best of 64/128/256 on B200 */
 #endif
-#define FAST_WPITCH 72 /* >= BORB_MAXCELL + 6 + 3 (alignment slack), multiple of 4 */
+/* staged window row pitch WP (template parameter of the kernel) = width of the TMA box.  A box must
+ * start on a 16-byte boundary of the plane row (measured: any other start coordinate faults), so the
+ * detection domain begins at byte 4..19 of a staged row; WP is the smallest of 64 / 80 / 96 that
+ * holds that offset, the widest domain of the plan and the word stage 1 reads past it */
+#define FAST_WP_FOR(max_ww) ((max_ww) + 20 <= 64 ? 64 : (max_ww) + 20 <= 80 ? 80 : 96)
+/* byte of a staged row at which the detection domain of a window with origin x0 begins */
+#define FAST_DOMAIN_BYTE(x0) (4 + (((x0) - 1) & 15))
 #define FAST_SPITCH 64 /* >= BORB_MAXCELL + 2 */
 #define FAST_MAXPIX (BORB_MAXCELL * BORB_MAXCELL)
 
@@ -158,12 +166,12 @@ struct FastSmemLayout {
     int chunk, win_off, win_bytes, sc_off, l1_off, l2_off, l3_off, bytes;
 };
 __host__ __device__ __forceinline__ int fast_chunk(int npix) { return ((npix + FAST_NT - 1) / FAST_NT) * 32; }
-__host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix)
+__host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix, int wp)
 {
     FastSmemLayout o;
     o.chunk = fast_chunk(max_pix) + 64; /* a warp owns whole rows: up to one row (< 64 px) above its share */
-    int b = 64; /* per-warp counts */
-    o.win_off = b; o.win_bytes = max_wh * FAST_WPITCH; b += 2 * o.win_bytes; /* double buffered */
+    int b = 128; /* per-warp counts [0,64), the two window mbarriers [64,80) */
+    o.win_off = b; o.win_bytes = (max_wh * wp + 127) & ~127; b += 2 * o.win_bytes; /* double buffered, 128-B aligned (TMA) */
     o.sc_off = b;  b += ((max_wh - 4) * FAST_SPITCH + 15) & ~15;
     /* list1 (u16 pixel | side<<12) is dead once stage 2 has consumed it; list3 (u32 NMS survivors:
      * pixel | score<<12, at most half a warp's pixels + one per row) reuses its storage */
@@ -173,34 +181,47 @@ __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, 
     return o;
 }
 
-/* asynchronous copy of one cell's window into shared memory (cp.async, 4 bytes per request: the
- * window origin is only word-aligned) */
-__device__ __forceinline__ void fast_stage_window(const BorbPlan *__restrict__ plan, const BorbCell &cell, int frame,
-                                                  const uint8_t *__restrict__ pyr, uint8_t *win, int tid)
+/* One cell's window into shared memory by TMA: a single thread arms the buffer's mbarrier with the
+ * box size and issues one cp.async.bulk.tensor (box WP bytes x max_wh rows x 1 frame of the level's
+ * padded plane; rows / columns of the box past the plane are zero-filled and never read).  The box
+ * starts at the 16-byte boundary at or before the column left of the window. */
+__device__ __forceinline__ uint32_t fast_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+struct FastMaps { /* kernel parameter (__grid_constant__): one TMA descriptor per pyramid level */
+    CUtensorMap m[BORB_MAXL];
+};
+
+__device__ __forceinline__ void fast_tma_window(const CUtensorMap *maps, const BorbCell &cell, int frame, uint32_t dst,
+                                                uint32_t bar, uint32_t bytes)
 {
-    const BorbLevel &L = plan->lv[cell.level];
-    const uint8_t *img = pyr + (size_t)frame * (size_t)plan->pyr_bytes + L.off +
-                         (size_t)(BORB_EDGE + cell.y0) * L.pitch + BORB_XPAD + (cell.x0 & ~3);
-    const int wpr = cell.wpr, nw = wpr * cell.wh;
-    const uint32_t smem = (uint32_t)__cvta_generic_to_shared(win);
-    for (int i = tid; i < nw; i += FAST_NT) {
-        const int y = fast_div(i, cell.wmagic), w = i - y * wpr;
-        const uint8_t *src = img + (size_t)y * L.pitch + 4 * w;
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem + y * FAST_WPITCH + 4 * w), "l"(src) : "memory");
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
+    const int x = BORB_XPAD + ((cell.x0 - 1) & ~15), y = BORB_EDGE + cell.y0; /* BORB_XPAD is a multiple of 16 */
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(maps + cell.level), "r"(x), "r"(y), "r"(frame), "r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ void fast_mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tFAST_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@p bra FAST_DONE;\n\tbra FAST_WAIT;\n\tFAST_DONE:\n\t}" ::"r"(bar), "r"(parity)
+                 : "memory");
 }
 
 #ifndef FAST_MIN_CTAS
 #define FAST_MIN_CTAS 16
 #endif
+template <int WP>
 __global__ void __launch_bounds__(FAST_NT, FAST_MIN_CTAS)
 k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cells, int n_frames,
-             const uint8_t *__restrict__ pyr, uint32_t *__restrict__ cand_xy,
+             const __grid_constant__ FastMaps tmaps, int frame0, uint32_t *__restrict__ cand_xy,
              uint32_t *__restrict__ cand_score, int *__restrict__ ncand)
 {
-    extern __shared__ __align__(16) unsigned char fast_raw[];
-    const FastSmemLayout lay = fast_smem_layout(plan->fast_max_wh, plan->fast_max_pix);
+    extern __shared__ __align__(128) unsigned char fast_raw[];
+    const FastSmemLayout lay = fast_smem_layout(plan->fast_max_wh, plan->fast_max_pix, WP);
+    const uint32_t bar0 = fast_smem_u32(fast_raw + 64), win0 = fast_smem_u32(fast_raw + lay.win_off);
+    const uint32_t box_bytes = (uint32_t)(WP * plan->fast_max_wh);
+    const CUtensorMap *maps = tmaps.m;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t below = (1u << lane) - 1u;
     int *wcnt = reinterpret_cast<int *>(fast_raw); /* [pass][warp]: NMS survivors */
@@ -218,30 +239,38 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     int frame = blockIdx.y, ci = blockIdx.x, buf = 0;
     bool have = frame < n_frames && ci < n_cells;
     BorbCell cell;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
     if (have) {
         cell = cells[ci];
-        fast_stage_window(plan, cell, frame, pyr, fast_raw + lay.win_off, tid);
+        if (tid == 0) fast_tma_window(maps, cell, frame0 + frame, win0, bar0, box_bytes);
     }
+    uint32_t it = 0;
     while (have) {
         int nci = ci + gridDim.x, nframe = frame;
         if (nci >= n_cells) { nci = blockIdx.x; nframe += gridDim.y; }
         const bool nhave = nframe < n_frames;
         uint8_t *win = fast_raw + lay.win_off + buf * lay.win_bytes;
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        __syncthreads();
+        fast_mbar_wait(bar0 + 8 * buf, (it >> 1) & 1u); /* this item's window has landed */
+        __syncthreads(); /* and everybody is done with the other buffer and the lists of the previous item */
         BorbCell ncell;
         if (nhave) {
             ncell = cells[nci];
-            fast_stage_window(plan, ncell, nframe, pyr, fast_raw + lay.win_off + (buf ^ 1) * lay.win_bytes, tid);
+            if (tid == 0)
+                fast_tma_window(maps, ncell, frame0 + nframe, win0 + (buf ^ 1) * lay.win_bytes, bar0 + 8 * (buf ^ 1), box_bytes);
         }
+        ++it;
         const BorbLevel &L = plan->lv[cell.level];
-        const int xoff = cell.x0 & 3;
         const int dw = cell.ww - 6, dh = cell.wh - 6; /* detection domain */
 
-        const uint8_t *org = win + 3 * FAST_WPITCH + xoff + 3; /* domain pixel (0,0) */
-        /* stage-1 lane geometry: Q words cover a domain row (byte xoff+3 .. xoff+3+dw-1 of the staged
-         * row), R rows per warp step; this lane: row s1_rig of the step, word s1_ql of the row */
-        const int s1_b0 = xoff + 3, s1_w0 = s1_b0 >> 2;
+        /* stage-1 lane geometry: Q words cover a domain row (bytes b0 .. b0+dw-1 of the staged row),
+         * R rows per warp step; this lane: row s1_rig of the step, word s1_ql of the row */
+        const int s1_b0 = FAST_DOMAIN_BYTE(cell.x0), s1_w0 = s1_b0 >> 2;
+        const uint8_t *org = win + 3 * WP + s1_b0; /* domain pixel (0,0): staged row 3 */
         const int s1_Q = ((s1_b0 + dw - 1) >> 2) - s1_w0 + 1;
         const int s1_R = (int)(cell.dmagic >> 8);
         int s1_rig = 0;
@@ -254,8 +283,8 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
                                 ((unsigned)(s1_col + 1) < (unsigned)dw ? 0x06000000u : 0u);
         const uint32_t s1_vhi = ((unsigned)(s1_col + 2) < (unsigned)dw ? 0x00000600u : 0u) |
                                 ((unsigned)(s1_col + 3) < (unsigned)dw ? 0x06000000u : 0u);
-        const uint32_t *s1_qp = reinterpret_cast<const uint32_t *>(win + 3 * FAST_WPITCH) + s1_w0 + s1_ql +
-                                s1_rig * (FAST_WPITCH / 4);
+        const uint32_t *s1_qp = reinterpret_cast<const uint32_t *>(win + 3 * WP) + s1_w0 + s1_ql +
+                                s1_rig * (WP / 4);
         int n2 = 0, n3 = 0, cell_total = 0;
         /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
          * where the first found nothing; K(ini) needs nothing below ini: a corner's score is at
@@ -280,8 +309,8 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
                 const int y = y0 + s1_rig;
                 uint32_t s_lo = 0, s_hi = 0;
                 if (s1_on && y < dh) {
-                    const uint32_t *rw = s1_qp + y0 * (FAST_WPITCH / 4);
-                    const uint32_t C = rw[0], N = rw[-3 * (FAST_WPITCH / 4)], S = rw[3 * (FAST_WPITCH / 4)];
+                    const uint32_t *rw = s1_qp + y0 * (WP / 4);
+                    const uint32_t C = rw[0], N = rw[-3 * (WP / 4)], S = rw[3 * (WP / 4)];
                     const uint32_t E = __byte_perm(C, rw[1], 0x6543), W = __byte_perm(rw[-1], C, 0x4321);
 #define F16LO(X) __byte_perm(X, 0u, 0x4140)
 #define F16HI(X) __byte_perm(X, 0u, 0x4342)
@@ -331,13 +360,13 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
                 if (i < n1) {
                     ent = list1[i];
                     const int x = ent & 63, y = (ent >> 6) & 63;
-                    const uint8_t *p = org + y * FAST_WPITCH + x;
+                    const uint8_t *p = org + y * WP + x;
                     const int v = p[0];
                     /* ring positions j and j + 8 packed as 16-bit halves */
                     uint32_t rp[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k)
-                        rp[k] = (uint32_t)FAST_RING(p, FAST_WPITCH, k) | ((uint32_t)FAST_RING(p, FAST_WPITCH, k + 8) << 16);
+                        rp[k] = (uint32_t)FAST_RING(p, WP, k) | ((uint32_t)FAST_RING(p, WP, k + 8) << 16);
                     int M = 0;
                     {   /* contrast on the flagged side, biased by 256 so both halves stay positive:
                          * ring darker (bit 12): 256 + v - r, else 256 + r - v */
