@@ -448,6 +448,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
         if (!fn || qres != cudaDriverEntryPointSuccess) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
         CUtensorMap *maps = h->fast_maps.m;
         std::memset(&h->fast_maps, 0, sizeof h->fast_maps);
+        h->fast_maps.max_wh = P.fast_max_wh; h->fast_maps.max_pix = P.fast_max_pix; h->fast_maps.n_cells = P.n_cells;
+        h->fast_maps.ini_th = P.ini_th; h->fast_maps.min_th = P.min_th;
         for (int l = 0; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
             const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.prows, (cuuint64_t)B};

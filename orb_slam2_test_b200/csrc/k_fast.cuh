@@ -187,8 +187,10 @@ __host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, 
  * starts at the 16-byte boundary at or before the column left of the window. */
 __device__ __forceinline__ uint32_t fast_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-struct FastMaps { /* kernel parameter (__grid_constant__): one TMA descriptor per pyramid level */
+struct FastMaps { /* kernel parameter (__grid_constant__): one TMA descriptor per pyramid level, and the
+                     plan constants every CTA needs at once (a parameter read, not a global load) */
     CUtensorMap m[BORB_MAXL];
+    int max_wh, max_pix, n_cells, ini_th, min_th;
 };
 
 __device__ __forceinline__ void fast_tma_window(const CUtensorMap *maps, const BorbCell &cell, int frame, uint32_t dst,
@@ -218,9 +220,9 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
              uint32_t *__restrict__ cand_score, int *__restrict__ ncand)
 {
     extern __shared__ __align__(128) unsigned char fast_raw[];
-    const FastSmemLayout lay = fast_smem_layout(plan->fast_max_wh, plan->fast_max_pix, WP);
+    const FastSmemLayout lay = fast_smem_layout(tmaps.max_wh, tmaps.max_pix, WP);
     const uint32_t bar0 = fast_smem_u32(fast_raw + 64), win0 = fast_smem_u32(fast_raw + lay.win_off);
-    const uint32_t box_bytes = (uint32_t)(WP * plan->fast_max_wh);
+    const uint32_t box_bytes = (uint32_t)(WP * tmaps.max_wh);
     const CUtensorMap *maps = tmaps.m;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t below = (1u << lane) - 1u;
@@ -229,8 +231,8 @@ k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cel
     uint16_t *list1 = reinterpret_cast<uint16_t *>(fast_raw + lay.l1_off) + warp * (lay.chunk + 64);
     uint16_t *list2 = reinterpret_cast<uint16_t *>(fast_raw + lay.l2_off) + warp * lay.chunk;
     uint32_t *list3 = reinterpret_cast<uint32_t *>(list1);
-    const int n_cells = plan->n_cells;
-    const int ini = plan->ini_th, mn = plan->min_th;
+    const int n_cells = tmaps.n_cells;
+    const int ini = tmaps.ini_th, mn = tmaps.min_th;
 
     for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(sc)[i] = 0u;
 

@@ -33,7 +33,7 @@ def main():
     res = {}
     for r in rows[2:]:
         d = dict(zip(hdr, r))
-        name = d["Kernel Name"].split("(")[0]
+        name = d["Kernel Name"].split("(")[0].replace("void ", "").split("<")[0]
         e = {"frames_per_launch": frames}
         for i, h in enumerate(hdr):
             if h in WANT and r[i] not in ("", "n/a"):
