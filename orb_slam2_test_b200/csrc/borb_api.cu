@@ -538,12 +538,12 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         const int units = L0.pitch / 16;
-        k_pyr_level0<<<dim3((units + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->d_plan, dev_img, step,
+        k_pyr_level0<<<dim3((units + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->plan, dev_img, step,
                                                                                           stride, d_pyr);
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);
-            k_pyr_resize<<<g, PYR_NT, (size_t)2 * h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->d_plan, l, h->d_tab_i, h->d_tab_s,
+            k_pyr_resize<<<g, PYR_NT, (size_t)2 * h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->plan, l, h->d_tab_i, h->d_tab_s,
                                                                                    d_pyr, h->pyr_sp[l], h->pyr_srows[l]);
         }
     }
@@ -560,7 +560,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             if (const char *e = getenv("BORB_FAST_GRID_Y")) grid.y = std::max(1, std::min(n, atoi(e)));
             grid.x = std::min(P.n_cells, std::max(1, ctas / (int)grid.y));
         }
-#define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->d_plan, h->d_cells, n, h->fast_maps, f0, \
+#define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->plan, h->d_cells, n, h->fast_maps, f0, \
                                                                    d_cand_xy, d_cand_score, d_ncand)
         if (h->fast_wp == 64) K2(64); else if (h->fast_wp == 80) K2(80); else K2(96);
 #undef K2
@@ -568,18 +568,18 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     STAGE(2);
     if (n * P.nlevels <= 2 * h->n_sm) /* few CTAs: give each one a whole SM's worth of threads */
         k_quadtree<QT_NT_LATENCY><<<dim3(P.nlevels, n), QT_NT_LATENCY, qt_smem_bytes(h->qt_M), st>>>(
-            h->d_plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
+            h->plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
     else
         k_quadtree<QT_NT_THROUGHPUT><<<dim3(P.nlevels, n), QT_NT_THROUGHPUT, qt_smem_bytes(h->qt_M), st>>>(
-            h->d_plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
+            h->plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
     STAGE(3);
-    k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, 0, st>>>(h->d_plan, h->d_tiles,
+    k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, 0, st>>>(h->plan, h->d_tiles,
                                                                                               d_pyr, d_blur);
     STAGE(4);
     /* keypoint slots per warp: 16 when there are plenty of frames, 1 for a single frame */
     const int kpw = std::max(1, std::min(DESC_KPW, n / 4));
     k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, 0, st>>>(
-        h->d_plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
+        h->plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
         d_out_kp, d_out_desc, d_nout);
     if (h->have_cam) { /* K8: rides in the describe stage's time slot */
 #define K8(NT) k_frame_undistort_grid<NT><<<n, NT, 0, st>>>(h->d_plan, h->cam, d_out_kp, d_nout, \

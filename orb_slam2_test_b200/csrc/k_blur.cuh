@@ -53,9 +53,10 @@ __device__ __forceinline__ uint32_t blur_col(const uint32_t a, const uint32_t b,
 }
 
 __global__ void __launch_bounds__(BLUR_NT)
-k_blur_strips(const BorbPlan *__restrict__ plan, const BorbTile *__restrict__ tiles,
+k_blur_strips(const __grid_constant__ BorbPlan plan_c, const BorbTile *__restrict__ tiles,
               const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur)
 {
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     const int lane = threadIdx.x & 31;
     const int t_idx = blockIdx.x * (BLUR_NT / 32) + (threadIdx.x >> 5);
     if (t_idx >= plan->n_tiles) return;

@@ -65,12 +65,13 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 #endif
 
 __global__ void __launch_bounds__(DESC_NT, DESC_MINB)
-k_orient_describe(const BorbPlan *__restrict__ plan, const signed char *__restrict__ pattern,
+k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__restrict__ pattern,
                   const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur,
                   const uint32_t *__restrict__ lkp_xy, const uint32_t *__restrict__ lkp_score,
                   const int *__restrict__ nlkp, BorbKpRec *__restrict__ out_kp,
                   uint8_t *__restrict__ out_desc, int *__restrict__ nout)
 {
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     /* per warp, twice: the blurred 37-row patch and the unblurred 31-row disc region */
     __shared__ uint32_t patch_all[DESC_NW][2 * (DESC_PR + DESC_IR) * DESC_PW];
     const int frame = blockIdx.y;

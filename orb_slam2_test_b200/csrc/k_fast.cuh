@@ -215,10 +215,11 @@ __device__ __forceinline__ void fast_mbar_wait(uint32_t bar, uint32_t parity)
 #endif
 template <int WP>
 __global__ void __launch_bounds__(FAST_NT, FAST_MIN_CTAS)
-k_fast_cells(const BorbPlan *__restrict__ plan, const BorbCell *__restrict__ cells, int n_frames,
+k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict__ cells, int n_frames,
              const __grid_constant__ FastMaps tmaps, int frame0, uint32_t *__restrict__ cand_xy,
              uint32_t *__restrict__ cand_score, int *__restrict__ ncand)
 {
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     extern __shared__ __align__(128) unsigned char fast_raw[];
     const FastSmemLayout lay = fast_smem_layout(tmaps.max_wh, tmaps.max_pix, WP);
     const uint32_t bar0 = fast_smem_u32(fast_raw + 64), win0 = fast_smem_u32(fast_raw + lay.win_off);

@@ -44,9 +44,10 @@ __host__ __device__ __forceinline__ int pyr_words_per_row(int w) { return (w + B
  * bytes, at whatever alignment the input's row step gives them, as 5 aligned words + funnel
  * shifts.  Grid: (units of 16 columns / 32, padded rows / 4, frames), block (32, 4). */
 __global__ void __launch_bounds__(PYR_NT)
-k_pyr_level0(const BorbPlan *__restrict__ plan, const uint8_t *__restrict__ img, size_t step,
+k_pyr_level0(const __grid_constant__ BorbPlan plan_c, const uint8_t *__restrict__ img, size_t step,
              size_t frame_stride, uint8_t *__restrict__ pyr)
 {
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     const BorbLevel &L = plan->lv[0];
     const int r = blockIdx.y * 4 + threadIdx.y;           /* padded row */
     const int c = (blockIdx.x * 32 + threadIdx.x) * 16 - BORB_XPAD; /* first of 16 level columns */
@@ -86,9 +87,10 @@ k_pyr_level0(const BorbPlan *__restrict__ plan, const uint8_t *__restrict__ img,
  * produces 4 consecutive rows, a lane 4 adjacent columns of each (one aligned 32-bit store).
  * Grid: (ceil(4*wpr / PYR_TW), ceil(prows / PYR_TH), frames). */
 __global__ void __launch_bounds__(PYR_NT)
-k_pyr_resize(const BorbPlan *__restrict__ plan, int l, const int *__restrict__ tab_i,
+k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restrict__ tab_i,
              const short *__restrict__ tab_s, uint8_t *__restrict__ pyr, int sp /* staged pitch */, int srows)
 {
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     extern __shared__ __align__(16) unsigned char pyr_tile[];
     const BorbLevel &L = plan->lv[l];
     const BorbLevel &S = plan->lv[l - 1];

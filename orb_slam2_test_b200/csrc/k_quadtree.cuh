@@ -182,11 +182,12 @@ __device__ void qt_count(const QtSmem &s, int cur, int n_rank, int n_pts,
 
 template <int QT_NT>
 __global__ void __launch_bounds__(QT_NT, 1024 / QT_NT)
-k_quadtree(const BorbPlan *__restrict__ plan, int M, const uint32_t *__restrict__ cand_xy,
+k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__restrict__ cand_xy,
            const uint32_t *__restrict__ cand_score, uint32_t *__restrict__ cand_node,
            const int *__restrict__ ncand, uint32_t *__restrict__ lkp_xy,
            uint32_t *__restrict__ lkp_score, int *__restrict__ nlkp, int *__restrict__ err)
 {
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     extern __shared__ __align__(16) unsigned char qt_raw[];
     __shared__ int sh_proc;
     QtSmem s;
