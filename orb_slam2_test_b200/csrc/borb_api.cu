@@ -881,7 +881,9 @@ int borb_extract_host(borb_extractor *h, const uint8_t *img, int n, int cols, in
 void *borb_host_alloc(size_t bytes)
 {
     void *p = nullptr;
-    if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+    /* BORB_HOST_WC=1: write-combined pages (the CPU only writes frames into them, the GPU reads) */
+    const char *wc = getenv("BORB_HOST_WC");
+    if (cudaHostAlloc(&p, bytes, wc && atoi(wc) ? cudaHostAllocWriteCombined : cudaHostAllocDefault) != cudaSuccess) {
         cudaGetLastError();
         fail(BORB_ERR_CUDA, "cudaMallocHost(%zu) failed", bytes);
         return nullptr;

@@ -145,3 +145,17 @@ def test_sequence_shard_runner_on_gpu(oracle_built):
     for r in allr:
         k, d = ora.extract(load(r.frame, r.eye))
         assert sequence.FrameResult.of(r.frame, r.eye, k, d).digest == r.digest
+
+
+@pytest.mark.parametrize("shape,nlevels", [((120, 91), 1), ((100, 77), 1), ((97, 152), 1), ((200, 121), 2)])
+def test_wide_cells_use_the_wider_tma_boxes(shape, nlevels, oracle_built):
+    """Narrow images give one or two FAST cells per row, up to 59 px wide (window 65 px): the
+    window loads then need the 80- and 96-byte TMA boxes instead of the 64-byte one."""
+    from orb_slam2_test_b200 import ORBextractor
+    ext = ORBextractor(300, 1.2, nlevels, 20, 7)
+    ora = oracle_built.Oracle(300, 1.2, nlevels, 20, 7)
+    for seed in (1, 2):
+        img = synth.make_frame(shape, seed=seed)
+        assert _same(ext(img), ora.extract(img)), f"{shape} seed {seed}"
+    img = synth.make_noise_frame(shape, seed=3)
+    assert _same(ext(img), ora.extract(img)), f"{shape} noise"
