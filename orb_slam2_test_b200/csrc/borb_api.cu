@@ -115,6 +115,7 @@ struct borb_extractor {
     int fast_smem = 0, n_sm = 148;
     int fast_wp = 64;                   /* staged window pitch of K2 = TMA box width */
     FastMaps fast_maps;                 /* one TMA descriptor per level, passed by value to K2 */
+    BlurMaps blur_maps;                 /* the same planes with K5's box */
     int chunk = 0; /* frames per pass of the kernel chain (0 = whole call) */
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     std::vector<BorbCell> cells;
@@ -460,7 +461,13 @@ int build_plan(borb_extractor *h, int cols, int rows)
                                                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
             if (r != CUDA_SUCCESS) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled(level %d) failed: %d", l, (int)r);
+            const cuuint32_t bbox[3] = {(cuuint32_t)BLUR_BOX_W, (cuuint32_t)BLUR_BOX_H, 1u};
+            const CUresult rb = ((EncodeTiled)fn)(&h->blur_maps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->d_pyr + L.off, dims,
+                                                  strides, bbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (rb != CUDA_SUCCESS) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled(blur, level %d) failed: %d", l, (int)rb);
         }
+        CU(cudaFuncSetAttribute(k_blur_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, BLUR_SMEM_BYTES));
     }
     h->qt_M = M;
     const size_t qt_smem = qt_smem_bytes(M);
@@ -573,8 +580,9 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         k_quadtree<QT_NT_THROUGHPUT><<<dim3(P.nlevels, n), QT_NT_THROUGHPUT, qt_smem_bytes(h->qt_M), st>>>(
             h->plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
     STAGE(3);
-    k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, 0, st>>>(h->plan, h->d_tiles,
-                                                                                              d_pyr, d_blur);
+    /* the descriptors address the whole slab: frame index = f0 + blockIdx.y */
+    k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, BLUR_SMEM_BYTES, st>>>(
+        h->plan, h->blur_maps, h->d_tiles, f0, h->d_blur);
     STAGE(4);
     /* keypoint slots per warp: 16 when there are plenty of frames, 1 for a single frame */
     const int kpw = std::max(1, std::min(DESC_KPW, n / 4));

@@ -86,7 +86,7 @@ struct BorbPlan {
 
 #define BORB_BLUR_TW 128 /* one warp x 4 columns */
 #ifndef BORB_BLUR_TH
-#define BORB_BLUR_TH 32
+#define BORB_BLUR_TH 36 /* a multiple of 6: K5 unrolls its row loop by 6 */
 #endif
 
 #endif
