@@ -116,6 +116,7 @@ struct borb_extractor {
     int fast_wp = 64;                   /* staged window pitch of K2 = TMA box width */
     FastMaps fast_maps;                 /* one TMA descriptor per level, passed by value to K2 */
     BlurMaps blur_maps;                 /* the same planes with K5's box */
+    DescMaps desc_maps;                 /* unblurred + blurred planes with K4/K6's boxes, and the plan fields they read */
     int chunk = 0; /* frames per pass of the kernel chain (0 = whole call) */
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     std::vector<BorbCell> cells;
@@ -449,6 +450,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
         if (!fn || qres != cudaDriverEntryPointSuccess) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
         CUtensorMap *maps = h->fast_maps.m;
         std::memset(&h->fast_maps, 0, sizeof h->fast_maps);
+        std::memset(&h->desc_maps, 0, sizeof h->desc_maps);
         h->fast_maps.max_wh = P.fast_max_wh; h->fast_maps.max_pix = P.fast_max_pix; h->fast_maps.n_cells = P.n_cells;
         h->fast_maps.ini_th = P.ini_th; h->fast_maps.min_th = P.min_th;
         for (int l = 0; l < P.nlevels; ++l) {
@@ -466,7 +468,20 @@ int build_plan(borb_extractor *h, int cols, int rows)
                                                   strides, bbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
             if (rb != CUDA_SUCCESS) return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled(blur, level %d) failed: %d", l, (int)rb);
+            const cuuint32_t ibox[3] = {(cuuint32_t)DESC_IB, (cuuint32_t)DESC_IR, 1u}, pbox[3] = {(cuuint32_t)DESC_PB, (cuuint32_t)DESC_PR, 1u};
+            const CUresult ri = ((EncodeTiled)fn)(&h->desc_maps.pyr[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->d_pyr + L.off, dims,
+                                                  strides, ibox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            const CUresult rp = ((EncodeTiled)fn)(&h->desc_maps.blur[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->d_blur + L.off, dims,
+                                                  strides, pbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (ri != CUDA_SUCCESS || rp != CUDA_SUCCESS)
+                return fail(BORB_ERR_CUDA, "cuTensorMapEncodeTiled(describe, level %d) failed: %d / %d", l, (int)ri, (int)rp);
+            h->desc_maps.kp_off[l] = L.kp_off; h->desc_maps.scale[l] = L.scale; h->desc_maps.patch_size[l] = L.patch_size;
         }
+        h->desc_maps.nlevels = P.nlevels; h->desc_maps.kp_total = P.kp_total;
+        std::memcpy(h->desc_maps.umax, P.umax, sizeof P.umax);
+        CU(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES));
         CU(cudaFuncSetAttribute(k_blur_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, BLUR_SMEM_BYTES));
     }
     h->qt_M = M;
@@ -586,8 +601,8 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     STAGE(4);
     /* keypoint slots per warp: 16 when there are plenty of frames, 1 for a single frame */
     const int kpw = std::max(1, std::min(DESC_KPW, n / 4));
-    k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, 0, st>>>(
-        h->plan, h->d_pattern, d_pyr, d_blur, d_lkp_xy, d_lkp_score, d_nlkp,
+    k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, DESC_SMEM_BYTES, st>>>(
+        h->desc_maps, h->d_pattern, f0, d_lkp_xy, d_lkp_score, d_nlkp,
         d_out_kp, d_out_desc, d_nout);
     if (h->have_cam) { /* K8: rides in the describe stage's time slot */
 #define K8(NT) k_frame_undistort_grid<NT><<<n, NT, 0, st>>>(h->d_plan, h->cam, d_out_kp, d_nout, \

@@ -9,7 +9,7 @@
  *       reduction, then cv::fastAtan2 (scalar float32 polynomial, every operation individually
  *       rounded).
  *   K6  computeOrbDescriptor (:117-157) on the BLURRED level: the 37x37 patch the rotated pattern
- *       can reach (|offset| <= 18) is staged into shared memory with aligned word loads, then lane
+ *       can reach (|offset| <= 18) is staged into shared memory by one TMA box load, then lane
  *       k builds descriptor byte k from 16 pattern points gathered from the staged patch;
  *       rotation in the FMA-contracted form the reference's -O3 -march=native object contains,
  *       sin/cos as glibc's sincosf (orb_sincos.cuh), cvRound = round-half-even.
@@ -18,6 +18,8 @@
  */
 #ifndef K_DESCRIBE_CUH
 #define K_DESCRIBE_CUH
+
+#include <cuda.h>
 
 #include "borb_internal.h"
 #include "orb_sincos.cuh"
@@ -54,31 +56,54 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 #endif
 #define DESC_NW (DESC_NT / 32)
 #define DESC_PR 37  /* staged patch rows: -18 .. +18 */
-#define DESC_PW 10  /* staged words per row: covers 37 columns at any alignment */
+#define DESC_PB 64  /* staged bytes per patch row: 37 columns from a 16-byte boundary (<= 15 + 37) */
 #define DESC_IR 31  /* staged rows of the unblurred level for IC_Angle: -15 .. +15 */
-#define DESC_BUF ((DESC_PR + DESC_IR) * DESC_PW) /* words per buffer */
+#define DESC_IB 48  /* staged bytes per disc row: 31 columns from a 16-byte boundary (<= 15 + 31) */
+#define DESC_PBYTES (DESC_PR * DESC_PB)
+#define DESC_IBYTES (DESC_IR * DESC_IB)
+#define DESC_POFF 0
+#define DESC_IOFF ((DESC_PBYTES + 127) & ~127)
+#define DESC_BUF ((DESC_IOFF + DESC_IBYTES + 127) & ~127) /* bytes per buffer, 128-B aligned (TMA) */
+#define DESC_SMEM_BYTES (128 + DESC_NW * 2 * DESC_BUF)
 #ifndef DESC_KPW
 #define DESC_KPW 16 /* keypoint slots per warp */
 #endif
 #ifndef DESC_MINB
-#define DESC_MINB 8 /* 64 registers: the kernel is latency bound, occupancy beats the few spills (measured) */
+#define DESC_MINB 7 /* shared memory allows 7 CTAs per SM */
 #endif
 
+struct DescMaps { /* kernel parameter (__grid_constant__): TMA descriptors of the unblurred and the blurred
+                     planes of every level (boxes DESC_IB x DESC_IR and DESC_PB x DESC_PR x 1 frame) and the
+                     few plan fields the kernel reads */
+    CUtensorMap pyr[BORB_MAXL], blur[BORB_MAXL];
+    int nlevels, kp_total;
+    int umax[16];
+    int kp_off[BORB_MAXL];
+    float scale[BORB_MAXL], patch_size[BORB_MAXL];
+};
+
 __global__ void __launch_bounds__(DESC_NT, DESC_MINB)
-k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__restrict__ pattern,
-                  const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur,
+k_orient_describe(const __grid_constant__ DescMaps dm, const signed char *__restrict__ pattern, const int frame0,
                   const uint32_t *__restrict__ lkp_xy, const uint32_t *__restrict__ lkp_score,
                   const int *__restrict__ nlkp, BorbKpRec *__restrict__ out_kp,
                   uint8_t *__restrict__ out_desc, int *__restrict__ nout)
 {
-    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
-    /* per warp, twice: the blurred 37-row patch and the unblurred 31-row disc region */
-    __shared__ uint32_t patch_all[DESC_NW][2 * (DESC_PR + DESC_IR) * DESC_PW];
+    /* [0,64): mbarriers [warp][buffer]; per warp two buffers, each the blurred 37-row patch and the
+     * unblurred 31-row disc region of one keypoint */
+    extern __shared__ __align__(128) unsigned char desc_smem[];
     const int frame = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t *patch = patch_all[warp];
-    const int nl = plan->nlevels;
-    const int kp_total = plan->kp_total;
+    const unsigned char *patch = desc_smem + 128 + warp * (2 * DESC_BUF);
+    const uint32_t patch_s = (uint32_t)__cvta_generic_to_shared(patch);
+    const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(desc_smem + 16 * warp);
+    const int nl = dm.nlevels;
+    const int kp_total = dm.kp_total;
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s + 8) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
 
     /* the 8 pattern words of this lane: bit k of descriptor byte `lane` compares the blurred
      * image at pattern points (xa, ya) and (xb, yb), packed as 4 int8 */
@@ -91,7 +116,7 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
     }
     /* lane l < nl: survivors of level l, slot offset of level l, output offset of level l */
     const int my_cnt = lane < nl ? nlkp[frame * BORB_MAXL + lane] : 0;
-    const int my_off = lane < nl ? plan->lv[lane].kp_off : 0x7fffffff;
+    const int my_off = lane < nl ? dm.kp_off[lane] : 0x7fffffff;
     int my_base = my_cnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -101,19 +126,18 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
     if (blockIdx.x == 0 && warp == 0 && lane == 31) nout[frame] = my_base; /* total of the frame */
     my_base -= my_cnt; /* exclusive */
 
-    /* per-lane constants: staging position (3 rows x 10 words per step), disc column */
-    const int st_r = lane / DESC_PW, st_w = lane - st_r * DESC_PW;
-    const int ic_u = lane - 15;
-    const int ic_vmax = lane < 31 ? plan->umax[ic_u < 0 ? -ic_u : ic_u] : -1;
+    const int ic_u = lane - 15; /* disc column of this lane */
+    const int ic_vmax = lane < 31 ? dm.umax[ic_u < 0 ? -ic_u : ic_u] : -1;
 
     const int warps_per_frame = gridDim.x * DESC_NW;
     const size_t fkp = (size_t)frame * kp_total;
-    const uint32_t patch_s = (uint32_t)__cvta_generic_to_shared(patch);
 
     /* A warp walks its slots as a three-deep software pipeline: in the iteration that orients and
      * describes keypoint i, the blurred patch and the unblurred disc region of keypoint i+1 are on
-     * their way into the other half of the warp's shared memory (cp.async), and the coordinates
-     * of keypoint i+2 are being loaded -- no global-load latency is left on the critical path. */
+     * their way into the other buffer (two TMA box loads issued by lane 0, completion on the
+     * buffer's mbarrier), and the coordinates of keypoint i+2 are being loaded -- no global-load
+     * latency is left on the critical path and staging costs the warp a handful of instructions
+     * (v3 issued 23 four-byte cp.async per lane: 18 % of the kernel's instructions). */
     int slot = blockIdx.x * DESC_NW + warp;
     struct Item { int level, o, slot; uint32_t v; bool ok; };
 /* resolve the next occupied slot at or after `slot` and start the load of its coordinates */
@@ -133,36 +157,22 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
             }                                                                                \
         }                                                                                    \
     } while (0)
-/* into buffer `bufi`: blurred rows y-18..y+18 from the aligned word holding x-18 (37 rows), then
- * unblurred rows y-15..y+15 from the aligned word holding x-15 (31 rows); lanes 0..29 cover
- * 3 rows x 10 words per step */
-#define DESC_CP(dst_, src_) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_), "l"(src_) : "memory")
+/* into buffer `bufi`: blurred rows y-18..y+18 from the 16-byte boundary at or before x-18, unblurred
+ * rows y-15..y+15 from the 16-byte boundary at or before x-15 (a TMA box starts on a 16-byte
+ * boundary; BORB_XPAD is a multiple of 16); box parts past the padded plane are zero-filled and
+ * never read */
+#define DESC_TMA(dst_, map_, x_, y_, bar_)                                                                       \
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" \
+                 ::"r"(dst_), "l"(map_), "r"(x_), "r"(y_), "r"(frame0 + frame), "r"(bar_) : "memory")
 #define DESC_STAGE(I, bufi)                                                                  \
     do {                                                                                     \
-        if (I.ok && lane < 30) {                                                             \
-            const BorbLevel &Ls = plan->lv[I.level];                                         \
+        if (I.ok && lane == 0) {                                                             \
             const int xs = (int)(I.v & 0xffff), ys = (int)(I.v >> 16);                       \
-            const size_t lo_ = (size_t)frame * (size_t)plan->pyr_bytes + Ls.off +            \
-                               (size_t)BORB_EDGE * Ls.pitch + BORB_XPAD;                     \
-            const ptrdiff_t adv = (ptrdiff_t)3 * Ls.pitch;                                   \
-            const uint8_t *bp = blur + lo_ + (ptrdiff_t)(ys - 18 + st_r) * Ls.pitch + ((xs - 18) & ~3) + 4 * st_w; \
-            uint32_t dst = patch_s + ((bufi) * DESC_BUF + st_r * DESC_PW + st_w) * 4;        \
-            _Pragma("unroll") for (int it = 0; it < 12; ++it) {                              \
-                DESC_CP(dst, bp);                                                            \
-                bp += adv;                                                                   \
-                dst += 3 * DESC_PW * 4;                                                      \
-            }                                                                                \
-            if (st_r == 0) DESC_CP(dst, bp); /* row 36 */                                    \
-            const uint8_t *ip = pyr + lo_ + (ptrdiff_t)(ys - 15 + st_r) * Ls.pitch + ((xs - 15) & ~3) + 4 * st_w; \
-            dst = patch_s + ((bufi) * DESC_BUF + (DESC_PR + st_r) * DESC_PW + st_w) * 4;     \
-            _Pragma("unroll") for (int it = 0; it < 10; ++it) {                              \
-                DESC_CP(dst, ip);                                                            \
-                ip += adv;                                                                   \
-                dst += 3 * DESC_PW * 4;                                                      \
-            }                                                                                \
-            if (st_r == 0) DESC_CP(dst, ip); /* row 30 */                                    \
+            const uint32_t b_ = bar_s + 8 * (bufi), d_ = patch_s + (bufi) * DESC_BUF;        \
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b_), "r"(DESC_PBYTES + DESC_IBYTES) : "memory"); \
+            DESC_TMA(d_ + DESC_POFF, &dm.blur[I.level], BORB_XPAD + ((xs - 18) & ~15), BORB_EDGE + ys - 18, b_); \
+            DESC_TMA(d_ + DESC_IOFF, &dm.pyr[I.level], BORB_XPAD + ((xs - 15) & ~15), BORB_EDGE + ys - 15, b_);  \
         }                                                                                    \
-        asm volatile("cp.async.commit_group;" ::: "memory");                                 \
     } while (0)
 
     Item cur, nxt;
@@ -170,30 +180,33 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
     DESC_STAGE(cur, 0);
     DESC_NEXT(nxt);
     int buf = 0;
+    uint32_t it = 0;
     while (cur.ok) {
-        DESC_STAGE(nxt, buf ^ 1); /* commits a (possibly empty) group: the count stays in step */
+        DESC_STAGE(nxt, buf ^ 1);
         Item nn;
         DESC_NEXT(nn);
 
         const int level = cur.level, o = cur.o;
-        const BorbLevel &L = plan->lv[level];
         const int x = (int)(cur.v & 0xffff), y = (int)(cur.v >> 16);
-        const int xo = (x - 18) & 3;
-        const uint32_t *bufp = patch + buf * DESC_BUF;
-        asm volatile("cp.async.wait_group 1;" ::: "memory"); /* this keypoint's two regions have landed */
-        __syncwarp();
+        const unsigned char *bufp = patch + buf * DESC_BUF;
+        {   /* this keypoint's two regions have landed */
+            const uint32_t b_ = bar_s + 8 * buf, par_ = (it >> 1) & 1u;
+            asm volatile("{\n\t.reg .pred p;\n\tDESC_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                         "@p bra DESC_DONE;\n\tbra DESC_WAIT;\n\tDESC_DONE:\n\t}" ::"r"(b_), "r"(par_) : "memory");
+        }
+        ++it;
 
         /* ---- K4: lane u-15 owns disc column u and the rows |v| <= umax[|u|] (the disc is
          * symmetric: column u reaches as far as row u does, src/ORBextractor.cc:504-520) ---- */
         int m10 = 0, m01 = 0;
         if (lane < 31) {
-            const uint8_t *dn = reinterpret_cast<const uint8_t *>(bufp + (DESC_PR + 15) * DESC_PW) + ((x - 15) & 3) + lane;
+            const uint8_t *dn = bufp + DESC_IOFF + 15 * DESC_IB + ((x - 15) & 15) + lane;
             const uint8_t *up = dn;
             int colsum = *dn;
 #pragma unroll
             for (int vr = 1; vr <= 15; ++vr) {
-                dn += DESC_PW * 4;
-                up -= DESC_PW * 4;
+                dn += DESC_IB;
+                up -= DESC_IB;
                 if (vr <= ic_vmax) {
                     const int pd = *dn, pu = *up;
                     colsum += pd + pu;
@@ -213,7 +226,7 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
         const float factor_pi = (float)(3.1415926535897932384626433832795 / 180.f);
         float a, b;
         orb_sincosf_exact(__fmul_rn(angle, factor_pi), &b, &a);
-        const uint8_t *c = reinterpret_cast<const uint8_t *>(bufp) + 18 * (DESC_PW * 4) + xo + 18;
+        const uint8_t *c = bufp + DESC_POFF + 18 * DESC_PB + ((x - 18) & 15) + 18;
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -224,20 +237,20 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
                 const float py = (float)(int)(signed char)(pw[k] >> (16 * e + 8));
                 const int row = __float2int_rn(__fmaf_rn(px, b, __fmul_rn(py, a)));
                 const int col = __float2int_rn(__fmaf_rn(px, a, -__fmul_rn(py, b)));
-                t[e] = c[row * (DESC_PW * 4) + col];
+                t[e] = c[row * DESC_PB + col];
             }
             val |= (t[0] < t[1]) << k;
         }
         out_desc[((size_t)frame * kp_total + o) * 32 + lane] = (uint8_t)val;
-        __syncwarp(); /* this half of the patch buffer is refilled during the next iteration */
+        __syncwarp(); /* this buffer is refilled during the next iteration */
 
         /* ---- K7: lanes 0..6 write one 4-byte field each of the cv::KeyPoint record ---- */
         if (lane < 7) {
-            const float s = level != 0 ? L.scale : 1.f;
+            const float s = level != 0 ? dm.scale[level] : 1.f;
             uint32_t f;
             if (lane == 0) f = __float_as_uint(level != 0 ? __fmul_rn((float)x, s) : (float)x);
             else if (lane == 1) f = __float_as_uint(level != 0 ? __fmul_rn((float)y, s) : (float)y);
-            else if (lane == 2) f = __float_as_uint(L.patch_size);
+            else if (lane == 2) f = __float_as_uint(dm.patch_size[level]);
             else if (lane == 3) f = __float_as_uint(angle);
             else if (lane == 4) f = __float_as_uint((float)lkp_score[fkp + cur.slot]);
             else if (lane == 5) f = (uint32_t)level;
@@ -250,7 +263,7 @@ k_orient_describe(const __grid_constant__ BorbPlan plan_c, const signed char *__
     }
 #undef DESC_NEXT
 #undef DESC_STAGE
-#undef DESC_CP
+#undef DESC_TMA
 }
 
 #endif
