@@ -116,15 +116,23 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     /* source window of the tile: columns (all 4 warps hold the same columns) and rows */
     sx_lo = __reduce_min_sync(0xffffffffu, sx_lo) & ~15;
     sx_hi = __reduce_max_sync(0xffffffffu, sx_hi);
-    int sy_lo = 0x7fffffff, sy_hi = 0;
-    for (int rr = lane; rr < PYR_TH && r0 + rr < L.prows; rr += 32) {
-        const int y = reflect101(r0 + rr - BORB_EDGE, L.h);
+    /* Row geometry once per CTA: lane rr of every warp holds output row r0 + rr of the tile (PYR_TH <= 32):
+     * its two clamped source rows and the vertical weight pair; the row loop fetches them by shuffle. */
+    static_assert(PYR_TH <= 32, "one tile row per lane");
+    int sy_lo = 0x7fffffff, sy_hi = 0, my_sy0 = 0, my_sy1 = 0;
+    uint32_t my_b = 0;
+    if (lane < PYR_TH && r0 + lane < L.prows) {
+        const int y = reflect101(r0 + lane - BORB_EDGE, L.h);
         const int sy = tab_i[L.yofs_off + y];
-        sy_lo = min(sy_lo, min(max(sy, 0), S.h - 1));
-        sy_hi = max(sy_hi, min(max(sy + 1, 0), S.h - 1));
+        my_sy0 = min(max(sy, 0), S.h - 1);
+        my_sy1 = min(max(sy + 1, 0), S.h - 1);
+        my_b = *reinterpret_cast<const uint32_t *>(tab_s + L.yb_off + 2 * y); /* b0 | b1 << 16 */
+        sy_lo = my_sy0;
+        sy_hi = my_sy1;
     }
     sy_lo = __reduce_min_sync(0xffffffffu, sy_lo);
     sy_hi = __reduce_max_sync(0xffffffffu, sy_hi);
+    const uint32_t my_rows = (uint32_t)(my_sy0 - sy_lo) | ((uint32_t)(my_sy1 - sy_lo) << 16);
     /* Stage the window as byte PAIRS: element i of a staged row is (s[i], s[i+1]) as one aligned
      * 16-bit value, so a horizontal tap pair is one LDS.U16 and the horizontal sum
      * s[x0]*a0 + s[x0+1]*a1 one dp2a.  (Where cv::resize clamps x0+1 to the last column its weight
@@ -135,8 +143,9 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
         const int nrow = sy_hi - sy_lo + 1;
         const int nv = vpr * nrow;                            /* host guarantees vpr*16 <= sp, nrow <= srows */
         const uint8_t *g = sbase + (size_t)sy_lo * S.pitch + sx_lo; /* 16-B aligned: pitch, XPAD, sx_lo are */
+        const uint32_t vmagic = 65536u / (uint32_t)vpr + 1u;  /* i / vpr for i < 4096, vpr <= 32 */
         for (int i = threadIdx.x; i < nv; i += PYR_NT) {
-            const int rr = i / vpr, cc = i - rr * vpr;
+            const int rr = (int)(((uint32_t)i * vmagic) >> 16), cc = i - rr * vpr;
             const uint32_t *gw = reinterpret_cast<const uint32_t *>(g + (size_t)rr * S.pitch) + 4 * cc;
             const uint4 q = __ldg(reinterpret_cast<const uint4 *>(gw));
             const uint32_t w[5] = {q.x, q.y, q.z, q.w, __ldg(gw + 4)};
@@ -154,7 +163,7 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
 #pragma unroll
     for (int k = 0; k < 4; ++k) sx[k] = 2 * (sx[k] - sx_lo); /* byte offset of the pair in a staged row */
     __syncthreads();
-    if (c >= L.w + BORB_EDGE) return;
+    const bool col_on = c < L.w + BORB_EDGE; /* lanes past the frame keep running: they serve the row shuffles */
 
     /* hA / hB: horizontal sums (already >> 4, as the vertical pass uses them) of the two source rows
      * of the previous output row */
@@ -165,11 +174,11 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     for (int i = 0; i < PYR_TH / 4; ++i) {
         const int r = r0 + warp * (PYR_TH / 4) + i;
         if (r >= L.prows) break;
-        const int y = reflect101(r - BORB_EDGE, L.h);
-        const int sy = tab_i[L.yofs_off + y];
         /* (b * h) >> 16 as the high word of (b << 16) * h: operands are non-negative */
-        const uint32_t b0 = (uint32_t)tab_s[L.yb_off + 2 * y] << 16, b1 = (uint32_t)tab_s[L.yb_off + 2 * y + 1] << 16;
-        const int sy0 = min(max(sy, 0), S.h - 1) - sy_lo, sy1 = min(max(sy + 1, 0), S.h - 1) - sy_lo;
+        const uint32_t rw_ = __shfl_sync(0xffffffffu, my_rows, warp * (PYR_TH / 4) + i);
+        const uint32_t bw_ = __shfl_sync(0xffffffffu, my_b, warp * (PYR_TH / 4) + i);
+        const uint32_t b0 = bw_ << 16, b1 = bw_ & 0xffff0000u;
+        const int sy0 = (int)(rw_ & 0xffffu), sy1 = (int)(rw_ >> 16);
         uint32_t n0[4], n1[4];
         if (sy0 == rowB) {
 #pragma unroll
@@ -205,7 +214,7 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
         }
         rowA = sy0;
         rowB = sy1;
-        *reinterpret_cast<uint32_t *>(dst + (size_t)r * L.pitch) = v;
+        if (col_on) *reinterpret_cast<uint32_t *>(dst + (size_t)r * L.pitch) = v;
     }
 }
 
