@@ -527,7 +527,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     step = in_step;
     stride = in_stride;
     dev_img = img_all + (size_t)f0 * stride;
-    uint8_t *const d_pyr = h->d_pyr + (size_t)f0 * (size_t)P.pyr_bytes, *const d_blur = h->d_blur + (size_t)f0 * (size_t)P.pyr_bytes;
+    uint8_t *const d_pyr = h->d_pyr + (size_t)f0 * (size_t)P.pyr_bytes;
     uint32_t *const d_cand_xy = h->d_cand_xy + (size_t)f0 * (size_t)P.cand_total;
     uint32_t *const d_cand_score = h->d_cand_score + (size_t)f0 * (size_t)P.cand_total;
     uint32_t *const d_cand_node = h->d_cand_node + (size_t)f0 * (size_t)P.cand_total;
