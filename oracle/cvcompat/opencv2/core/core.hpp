@@ -256,7 +256,16 @@ private:
     int type_;
 };
 
-inline Mat operator*(const Mat &a, const Mat &b)
+/* OpenCV's own gemm / arithmetic live in a library built without FMA contraction (cv2 4.13: the small-
+ * matrix float product is a left-to-right sum of individually rounded products, tests/test_oracle_match.py);
+ * a reference translation unit compiled with -march=x86-64-v3 must not contract them when it inlines
+ * these stand-ins. */
+#if defined(__GNUC__) && !defined(__clang__) && !defined(__CUDACC__)
+#define CVCOMPAT_NOFMA __attribute__((optimize("fp-contract=off"), noinline))
+#else
+#define CVCOMPAT_NOFMA
+#endif
+CVCOMPAT_NOFMA inline Mat operator*(const Mat &a, const Mat &b)
 {
     Mat m(a.rows, b.cols, CV_32F);
     for (int y = 0; y < a.rows; ++y)
@@ -267,7 +276,7 @@ inline Mat operator*(const Mat &a, const Mat &b)
         }
     return m;
 }
-inline Mat mat_lin_(const Mat &a, float sa, const Mat *b, float sb)
+CVCOMPAT_NOFMA inline Mat mat_lin_(const Mat &a, float sa, const Mat *b, float sb)
 {
     Mat m(a.rows, a.cols, CV_32F);
     for (int y = 0; y < a.rows; ++y)
@@ -278,6 +287,7 @@ inline Mat operator+(const Mat &a, const Mat &b) { return mat_lin_(a, 1.f, &b, 1
 inline Mat operator-(const Mat &a, const Mat &b) { return mat_lin_(a, 1.f, &b, -1.f); }
 inline Mat operator-(const Mat &a) { return mat_lin_(a, -1.f, nullptr, 0.f); }
 inline Mat operator*(float s, const Mat &a) { return mat_lin_(a, s, nullptr, 0.f); }
+inline Mat operator/(const Mat &a, float s) { return mat_lin_(a, 1.f / s, nullptr, 0.f); } /* only named by keyframe matchers nobody runs here */
 enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
 /* L1 norm of a - b, accumulated in double as OpenCV does for CV_32F */
 inline double norm(const Mat &a, const Mat &b, int type)

@@ -1,0 +1,196 @@
+/*
+ * oracle/match_oracle.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU restatement, on flat arrays, of the tracking thread's frame-to-frame matcher
+ *   ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
+ *       /root/reference/src/ORBmatcher.cc:1503-1668
+ * with Frame::GetFeaturesInArea (src/Frame.cc:421-508), ORBmatcher::ComputeThreeMaxima
+ * (src/ORBmatcher.cc:1800-1843), DescriptorDistance (:1846-1862), TH_HIGH = 100 (:35),
+ * HISTO_LENGTH = 30 (:36).
+ * PINNED against the reference's own object code: oracle/Makefile compiles src/ORBmatcher.cc and
+ * src/Frame.cc where they lie into oracle/_ref/librefmatch.so (oracle/matcher_driver.cpp feeds it),
+ * and tests/test_oracle_match_vs_reference.py requires identical CurrentFrame.mvpMapPoints and
+ * nmatches; tests/golden/match_*.npz carries such outputs to machines without the reference.
+ *
+ * Float forms, read off the reference object (g++ -O3 -march=x86-64-v3, objdump of
+ * _ref/ORBmatcher.o) and kept here with explicit fmaf under -ffp-contract=off:
+ *   x3Dc   = Rcw * x3Dw + tcw   OpenCV gemm on 3x3 * 3x1 floats: left-to-right sum of individually
+ *                               rounded products (cv2 4.13: tests/test_oracle_match.py), then + tcw
+ *   invzc  = 1.0f / zc          (the double division, narrowed, is the float division)
+ *   u      = fmaf(fx * xc, invzc, cx),  v likewise           (:1548-1549)
+ *   radius = th * mvScaleFactors[octave]                     (:1561)
+ *   ur     = fmaf(-mbf, invzc, u);  er = fabsf(ur - mvuRight[i2])   (:1593-1594)
+ *   rot    = angleLast - angleCur; if (rot < 0) rot += 360.f; bin = round(rot * (1.f / 30))  (:1617-1622)
+ *   tlc    = Rlw * (-Rcw^T * tcw) + tlw, same product form   (:1515-1521)
+ *
+ * The reference loop is sequential: a current keypoint that already holds a map point with
+ * Observations() > 0 is skipped by every later query (:1583-1585), one holding a map point without
+ * observations can be overwritten (:1610).  nmatches counts every accepted query, and every entry
+ * of a discarded orientation bin subtracts one and clears its slot, whoever holds it (:1638-1647).
+ */
+#include <climits>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+extern "C" {
+
+struct mo_kp { float x, y, size, angle, response; int octave, class_id; };
+
+struct mo_frame { /* same layout as refmatch_frame in oracle/matcher_driver.cpp */
+    int n;
+    const uint8_t *kps;
+    const float *un_xy;
+    const uint8_t *desc;
+    const float *u_right;
+    const int32_t *grid_count, *grid_idx;
+    const float *Tcw;
+};
+
+static int mo_hamming256(const uint8_t *a, const uint8_t *b)
+{
+    int d = 0;
+    for (int i = 0; i < 8; ++i) {
+        uint32_t x, y;
+        std::memcpy(&x, a + 4 * i, 4);
+        std::memcpy(&y, b + 4 * i, 4);
+        d += __builtin_popcount(x ^ y);
+    }
+    return d;
+}
+
+/* row r of a 3x4 pose times a 3-vector: OpenCV's small-matrix float product */
+static float mo_dot3(const float *row, int stride, const float *x)
+{
+    float s = 0.f;
+    for (int k = 0; k < 3; ++k) s += row[k * stride] * x[k];
+    return s;
+}
+
+enum { MO_COLS = 64, MO_ROWS = 48, MO_HISTO = 30, MO_TH_HIGH = 100 };
+
+/* ORBmatcher::ComputeThreeMaxima on the bin sizes */
+void mo_three_maxima(const int *sz, int L, int *ind1, int *ind2, int *ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    *ind1 = *ind2 = *ind3 = -1;
+    for (int i = 0; i < L; ++i) {
+        const int s = sz[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; *ind3 = *ind2; *ind2 = *ind1; *ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; *ind3 = *ind2; *ind2 = i; }
+        else if (s > max3) { max3 = s; *ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { *ind2 = -1; *ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { *ind3 = -1; }
+}
+
+int mo_search_by_projection(const mo_frame *cur, const mo_frame *last, const float *cam, const float *bounds,
+                            const float *scale, int nlevels, const uint8_t *mp_flags, const float *mp_xyz,
+                            const uint8_t *mp_desc, float th, int mono, int check_ori, int32_t *out_match)
+{
+    (void)nlevels;
+    const float fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3], mbf = cam[4], mb = cam[5];
+    const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+    const float winv = (float)MO_COLS / (max_x - min_x), hinv = (float)MO_ROWS / (max_y - min_y);
+    const mo_kp *ck = reinterpret_cast<const mo_kp *>(cur->kps), *lk = reinterpret_cast<const mo_kp *>(last->kps);
+    const float *Tc = cur->Tcw, *Tl = last->Tcw;
+    /* twc = -Rcw^T * tcw; tlc = Rlw * twc + tlw */
+    float twc[3], tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    for (int y = 0; y < 3; ++y) {
+        float s = 0.f;
+        for (int k = 0; k < 3; ++k) s += (-Tc[4 * k + y]) * tcw[k];
+        twc[y] = s;
+    }
+    const float tlc_z = mo_dot3(Tl + 8, 1, twc) + Tl[11];
+    const bool forward = tlc_z > mb && !mono, backward = -tlc_z > mb && !mono;
+
+    /* cell-major prefix of the current frame's grid */
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    if (cur->grid_count)
+        for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + cur->grid_count[c];
+
+    for (int i = 0; i < cur->n; ++i) out_match[i] = -1;
+    std::vector<int> hist[MO_HISTO];
+    const float factor = 1.0f / MO_HISTO;
+    int nmatches = 0;
+
+    for (int i = 0; i < last->n; ++i) {
+        if (!(mp_flags[i] & 1) || (mp_flags[i] & 4)) continue;
+        const float *X = mp_xyz + 3 * i;
+        const float xc = mo_dot3(Tc, 1, X) + Tc[3], yc = mo_dot3(Tc + 4, 1, X) + Tc[7], zc = mo_dot3(Tc + 8, 1, X) + Tc[11];
+        const float invzc = 1.0f / zc;
+        if (invzc < 0) continue;
+        const float u = std::fmaf(fx * xc, invzc, cx), v = std::fmaf(fy * yc, invzc, cy);
+        if (u < min_x || u > max_x) continue;
+        if (v < min_y || v > max_y) continue;
+        const int oct = lk[i].octave;
+        const float radius = th * scale[oct];
+        int min_level, max_level;
+        if (forward) { min_level = oct; max_level = -1; }
+        else if (backward) { min_level = 0; max_level = oct; }
+        else { min_level = oct - 1; max_level = oct + 1; }
+
+        /* Frame::GetFeaturesInArea(u, v, radius, min_level, max_level) fused with the candidate loop */
+        const int cx0 = std::max(0, (int)std::floor((u - min_x - radius) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((u - min_x + radius) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((v - min_y - radius) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((v - min_y + radius) * hinv));
+        if (cy1 < 0) continue;
+        const bool check_levels = (min_level > 0) || (max_level >= 0);
+
+        int best = 256, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int i2 = cur->grid_idx[q];
+                    if (check_levels) {
+                        if (ck[i2].octave < min_level) continue;
+                        if (max_level >= 0 && ck[i2].octave > max_level) continue;
+                    }
+                    const float dx = cur->un_xy[2 * i2] - u, dy = cur->un_xy[2 * i2 + 1] - v;
+                    if (!(std::fabs(dx) < radius && std::fabs(dy) < radius)) continue;
+                    /* the candidate loop proper (:1578-1607) */
+                    if (out_match[i2] >= 0 && (mp_flags[out_match[i2]] & 2)) continue;
+                    const float ur2 = cur->u_right ? cur->u_right[i2] : -1.f;
+                    if (ur2 > 0) {
+                        const float ur = std::fmaf(-mbf, invzc, u);
+                        const float er = std::fabs(ur - ur2);
+                        if (er > radius) continue;
+                    }
+                    const int d = mo_hamming256(mp_desc + (size_t)i * 32, cur->desc + (size_t)i2 * 32);
+                    if (d < best) { best = d; best_idx = i2; }
+                }
+            }
+        if (best <= MO_TH_HIGH) {
+            out_match[best_idx] = i;
+            ++nmatches;
+            if (check_ori) {
+                float rot = lk[i].angle - ck[best_idx].angle;
+                if (rot < 0.0f) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == MO_HISTO) bin = 0;
+                hist[bin].push_back(best_idx);
+            }
+        }
+    }
+    if (check_ori) {
+        int sz[MO_HISTO], i1, i2, i3;
+        for (int b = 0; b < MO_HISTO; ++b) sz[b] = (int)hist[b].size();
+        mo_three_maxima(sz, MO_HISTO, &i1, &i2, &i3);
+        for (int b = 0; b < MO_HISTO; ++b) {
+            if (b == i1 || b == i2 || b == i3) continue;
+            for (size_t j = 0; j < hist[b].size(); ++j) {
+                out_match[hist[b][j]] = -1;
+                --nmatches;
+            }
+        }
+    }
+    return nmatches;
+}
+
+} // extern "C"

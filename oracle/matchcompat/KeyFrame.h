@@ -1,0 +1,36 @@
+/* oracle/matchcompat -- TEST INFRASTRUCTURE.  Shadow of include/KeyFrame.h: the members
+ * src/ORBmatcher.cc names in its keyframe matchers (SearchByBoW, Fuse, SearchBySim3, ...), none of
+ * which the driver calls -- every method aborts.  Only there so that the translation unit compiles. */
+#ifndef KEYFRAME_H
+#define KEYFRAME_H
+#include <cstdlib>
+#include <set>
+#include <vector>
+#include <opencv2/core/core.hpp>
+#include "Thirdparty/DBoW2/DBoW2/BowVector.h"
+#include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
+namespace ORB_SLAM2 {
+class MapPoint;
+class KeyFrame {
+public:
+    std::vector<MapPoint *> GetMapPointMatches() { std::abort(); }
+    std::set<MapPoint *> GetMapPoints() { std::abort(); }
+    MapPoint *GetMapPoint(const size_t &) { std::abort(); }
+    cv::Mat GetRotation() { std::abort(); }
+    cv::Mat GetTranslation() { std::abort(); }
+    cv::Mat GetCameraCenter() { std::abort(); }
+    cv::Mat GetPose() { std::abort(); }
+    std::vector<size_t> GetFeaturesInArea(const float &, const float &, const float &) const { std::abort(); }
+    bool IsInImage(const float &, const float &) const { std::abort(); }
+    void AddMapPoint(MapPoint *, const size_t &) { std::abort(); }
+    DBoW2::FeatureVector mFeatVec;
+    std::vector<cv::KeyPoint> mvKeysUn, mvKeys;
+    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
+    cv::Mat mDescriptors;
+    float fx, fy, cx, cy, invfx, invfy, mbf, mb, mThDepth, mfLogScaleFactor;
+    int N, mnScaleLevels;
+    long unsigned int mnId;
+    int mnMinX, mnMinY, mnMaxX, mnMaxY;
+};
+} // namespace ORB_SLAM2
+#endif

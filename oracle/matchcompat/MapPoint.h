@@ -1,0 +1,41 @@
+/* oracle/matchcompat -- TEST INFRASTRUCTURE.  Shadow of the reference's include/MapPoint.h for
+ * compiling src/ORBmatcher.cc (and src/Frame.cc beside it) where they lie, without the map, g2o
+ * and Eigen.  A map point here is a plain record holding what the matchers read through the
+ * reference's accessors (GetWorldPos, GetDescriptor, Observations, isBad); the driver
+ * (oracle/matcher_driver.cpp) fills it.  Members the exercised functions never reach abort. */
+#ifndef MAPPOINT_H
+#define MAPPOINT_H
+#include <cstdlib>
+#include <map>
+#include <opencv2/core/core.hpp>
+namespace ORB_SLAM2 {
+class Frame;
+class KeyFrame;
+class MapPoint {
+public:
+    cv::Mat mWorldPos, mDescriptor; /* 3x1 CV_32F, 1x32 CV_8U */
+    int nObs = 0;
+    bool mbBad = false;
+
+    cv::Mat GetWorldPos() { return mWorldPos.clone(); }
+    cv::Mat GetDescriptor() { return mDescriptor.clone(); }
+    int Observations() { return nObs; }
+    bool isBad() { return mbBad; }
+
+    cv::Mat GetNormal() { std::abort(); }
+    float GetMaxDistanceInvariance() { std::abort(); }
+    float GetMinDistanceInvariance() { std::abort(); }
+    int PredictScale(const float &, Frame *) { std::abort(); }
+    int PredictScale(const float &, KeyFrame *) { std::abort(); }
+    bool IsInKeyFrame(KeyFrame *) { std::abort(); }
+    void Replace(MapPoint *) { std::abort(); }
+    void AddObservation(KeyFrame *, size_t) { std::abort(); }
+    int GetIndexInKeyFrame(KeyFrame *) { std::abort(); }
+
+    float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 0;
+    bool mbTrackInView = false;
+    int mnTrackScaleLevel = 0;
+    long unsigned int mnId = 0, mnLastFrameSeen = 0, mnFuseCandidateForKF = 0;
+};
+} // namespace ORB_SLAM2
+#endif

@@ -1,0 +1,119 @@
+/*
+ * oracle/matcher_driver.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * C entry point over the reference's OWN src/ORBmatcher.cc and src/Frame.cc (compiled where they
+ * lie, see oracle/Makefile: _ref/librefmatch.so) for the descriptor consumer built on the device:
+ *   ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
+ *       src/ORBmatcher.cc:1503-1668, with Frame::GetFeaturesInArea src/Frame.cc:421-508,
+ *       ORBmatcher::ComputeThreeMaxima :1800-1843 and DescriptorDistance :1846-1862.
+ * The two reference Frame objects are default-constructed (src/Frame.cc:43) and their public members
+ * filled from flat arrays -- keypoints, descriptors, grid and stereo coordinates are the outputs the
+ * other rows already pin (tests/test_oracle_frame_vs_reference.py); map points are the records of
+ * oracle/matchcompat/MapPoint.h.  The call itself, including every float expression in it, is the
+ * reference's object code (-O3 -march=x86-64-v3, contraction as GCC decides).
+ */
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "Frame.h"
+#include "ORBmatcher.h"
+
+using namespace ORB_SLAM2;
+
+namespace {
+
+cv::Mat pose_mat(const float *T12)
+{
+    cv::Mat T(4, 4, CV_32F);
+    for (int c = 0; c < 4; ++c) T.at<float>(3, c) = c == 3 ? 1.f : 0.f;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) T.at<float>(r, c) = T12[4 * r + c];
+    return T;
+}
+
+} // namespace
+
+extern "C" {
+
+struct refmatch_frame { /* one side of the call, flat */
+    int n;
+    const uint8_t *kps;      /* n x 28 B cv::KeyPoint (mvKeys) */
+    const float *un_xy;      /* n x 2 (mvKeysUn positions; octave / angle as in kps) */
+    const uint8_t *desc;     /* n x 32 */
+    const float *u_right;    /* n (mvuRight), may be null: all -1 */
+    const int32_t *grid_count, *grid_idx; /* 64*48 cell-major counts + concatenated indices, may be null */
+    const float *Tcw;        /* 3 x 4 row-major */
+};
+
+/* cam = fx, fy, cx, cy, mbf, mb; bounds = mnMinX, mnMaxX, mnMinY, mnMaxY; scale = mvScaleFactors.
+ * Map points of the last frame: mp_flags[i] bit 0 = LastFrame.mvpMapPoints[i] != NULL, bit 1 =
+ * Observations() > 0, bit 2 = LastFrame.mvbOutlier[i]; world position mp_xyz[3i..], descriptor
+ * mp_desc[32i..].  out_match[i2] = index i of the last-frame map point CurrentFrame.mvpMapPoints[i2]
+ * ends up with, or -1.  Returns nmatches. */
+int refmatch_search_by_projection(const refmatch_frame *cur, const refmatch_frame *last, const float *cam,
+                                  const float *bounds, const float *scale, int nlevels, const uint8_t *mp_flags,
+                                  const float *mp_xyz, const uint8_t *mp_desc, float th, int mono, int check_ori,
+                                  int32_t *out_match)
+{
+    Frame::fx = cam[0]; Frame::fy = cam[1]; Frame::cx = cam[2]; Frame::cy = cam[3];
+    Frame::invfx = 1.0f / cam[0]; Frame::invfy = 1.0f / cam[1];
+    Frame::mnMinX = bounds[0]; Frame::mnMaxX = bounds[1]; Frame::mnMinY = bounds[2]; Frame::mnMaxY = bounds[3];
+    /* as the Frame constructors compute them, src/Frame.cc:135-136 */
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);
+    Frame::mbInitialComputations = false;
+
+    Frame F[2];
+    const refmatch_frame *src[2] = {cur, last};
+    for (int s = 0; s < 2; ++s) {
+        Frame &f = F[s];
+        const refmatch_frame &r = *src[s];
+        f.N = r.n;
+        f.mbf = cam[4];
+        f.mb = cam[5];
+        f.mvKeys.resize(r.n);
+        if (r.n) std::memcpy(f.mvKeys.data(), r.kps, (size_t)r.n * 28);
+        f.mvKeysUn = f.mvKeys;
+        for (int i = 0; i < r.n; ++i) { f.mvKeysUn[i].pt.x = r.un_xy[2 * i]; f.mvKeysUn[i].pt.y = r.un_xy[2 * i + 1]; }
+        f.mDescriptors = cv::Mat(r.n, 32, CV_8UC1);
+        for (int i = 0; i < r.n; ++i) std::memcpy(f.mDescriptors.ptr(i), r.desc + (size_t)i * 32, 32);
+        f.mvuRight.assign(r.n, -1.f);
+        if (r.u_right) for (int i = 0; i < r.n; ++i) f.mvuRight[i] = r.u_right[i];
+        f.mvDepth.assign(r.n, -1.f);
+        f.mvpMapPoints.assign(r.n, static_cast<MapPoint *>(NULL));
+        f.mvbOutlier.assign(r.n, false);
+        f.mnScaleLevels = nlevels;
+        f.mvScaleFactors.assign(scale, scale + nlevels);
+        if (r.grid_count) {
+            int k = 0;
+            for (int i = 0; i < FRAME_GRID_COLS; ++i)
+                for (int j = 0; j < FRAME_GRID_ROWS; ++j) {
+                    const int c = r.grid_count[i * FRAME_GRID_ROWS + j];
+                    f.mGrid[i][j].assign(r.grid_idx + k, r.grid_idx + k + c);
+                    k += c;
+                }
+        }
+        f.SetPose(pose_mat(r.Tcw));
+    }
+    Frame &C = F[0], &L = F[1];
+    std::vector<MapPoint> mps(last->n);
+    for (int i = 0; i < last->n; ++i) {
+        if (!(mp_flags[i] & 1)) continue;
+        MapPoint &m = mps[i];
+        m.mWorldPos = cv::Mat(3, 1, CV_32F);
+        for (int k = 0; k < 3; ++k) m.mWorldPos.at<float>(k) = mp_xyz[3 * i + k];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1);
+        std::memcpy(m.mDescriptor.ptr(0), mp_desc + (size_t)i * 32, 32);
+        m.nObs = (mp_flags[i] & 2) ? 1 : 0;
+        L.mvpMapPoints[i] = &m;
+        L.mvbOutlier[i] = (mp_flags[i] & 4) != 0;
+    }
+    ORBmatcher matcher(0.9f, check_ori != 0);
+    const int nm = matcher.SearchByProjection(C, L, th, mono != 0);
+    for (int i2 = 0; i2 < cur->n; ++i2)
+        out_match[i2] = C.mvpMapPoints[i2] ? (int32_t)(C.mvpMapPoints[i2] - mps.data()) : -1;
+    return nm;
+}
+
+} // extern "C"

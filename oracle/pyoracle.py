@@ -206,6 +206,70 @@ def stereo_match(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, mbf: float, mb:
     return u[:n], z[:n], sad[:n], kept
 
 
+class _MatchFrame(C.Structure):
+    _fields_ = [("n", C.c_int), ("kps", _vp), ("un_xy", _vp), ("desc", _vp), ("u_right", _vp),
+                ("grid_count", _vp), ("grid_idx", _vp), ("Tcw", _vp)]
+
+
+def _match_call(fn, cur: dict, last: dict, cam, bounds, scale, th: float, mono: bool, check_ori: bool):
+    """Common marshalling for mo_search_by_projection / refmatch_search_by_projection.
+    cur / last: dicts with kps (KP_DTYPE), un_xy [n,2] f32, desc [n,32] u8, Tcw [3,4] f32; cur also
+    u_right [n] f32 (or None), cell_start [3073] i32, cell_idx; last also mp_flags [n] u8 (bit 0 map
+    point, bit 1 Observations() > 0, bit 2 outlier), mp_xyz [n,3] f32, mp_desc [n,32] u8.
+    -> (match [n_cur] i32: index of the last-frame map point or -1, nmatches)."""
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+
+    def frame(d, with_grid):
+        f = _MatchFrame()
+        f.n = len(d["kps"])
+        f.kps = arr(d["kps"], KP_DTYPE)
+        f.un_xy = arr(d["un_xy"], np.float32)
+        f.desc = arr(d["desc"], np.uint8)
+        f.u_right = arr(d["u_right"], np.float32) if d.get("u_right") is not None else None
+        if with_grid:
+            f.grid_count = arr(np.diff(d["cell_start"]), np.int32)
+            f.grid_idx = arr(d["cell_idx"], np.int32)
+        f.Tcw = arr(d["Tcw"], np.float32)
+        return f
+
+    fc, fl = frame(cur, True), frame(last, False)
+    scale = np.ascontiguousarray(scale, np.float32)
+    out = np.full(max(fc.n, 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, C.c_int, _vp]
+    nm = fn(C.addressof(fc), C.addressof(fl), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data,
+            len(scale), arr(last["mp_flags"], np.uint8), arr(last["mp_xyz"], np.float32), arr(last["mp_desc"], np.uint8),
+            float(th), int(mono), int(check_ori), out.ctypes.data)
+    return out[:fc.n], int(nm)
+
+
+def search_by_projection(cur, last, cam, bounds, scale, th, mono=False, check_ori=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) restated (oracle/match_oracle.cpp).
+    cam = (fx, fy, cx, cy, mbf, mb)."""
+    return _match_call(Oracle.load().mo_search_by_projection, cur, last, cam, bounds, scale, th, mono, check_ori)
+
+
+class RefMatcher:
+    """The reference's own src/ORBmatcher.cc + src/Frame.cc (oracle/_ref/librefmatch.so)."""
+
+    _lib = None
+
+    @classmethod
+    def available(cls) -> bool:
+        return (HERE / "_ref" / "librefmatch.so").exists()
+
+    @classmethod
+    def search_by_projection(cls, cur, last, cam, bounds, scale, th, mono=False, check_ori=True):
+        if cls._lib is None:
+            cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
+        return _match_call(cls._lib.refmatch_search_by_projection, cur, last, cam, bounds, scale, th, mono, check_ori)
+
+
 def _cam(K, dist) -> np.ndarray:
     d = list(dist) + [0.0] * (5 - len(dist))
     return np.asarray(list(K) + d, np.float32)

@@ -1,0 +1,112 @@
+"""Scenario builder for the frame-to-frame matcher row (ORBmatcher::SearchByProjection(Frame, Frame),
+src/ORBmatcher.cc:1503-1668): two consecutive synthetic stereo frames, the last frame's map points
+un-projected from its stereo depths (Frame::UnprojectStereo, src/Frame.cc:836-850), and a current pose
+that predicts the (3, 1) px shift of the synthetic sequence.  TEST INFRASTRUCTURE (uses the oracle)."""
+from __future__ import annotations
+
+import numpy as np
+
+from orb_slam2_test_b200 import synth
+
+KITTI_K = (718.856, 718.856, 607.1928, 185.2157)
+KITTI_BF = 386.1448
+TUM1_K = (517.306408, 516.469215, 318.643040, 255.313989)
+TUM1_D = (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+
+
+def _rot(rx: float, ry: float, rz: float) -> np.ndarray:
+    cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return Rz @ Ry @ Rx
+
+
+def pose(rx=0.0, ry=0.0, rz=0.0, t=(0.0, 0.0, 0.0)) -> np.ndarray:
+    T = np.zeros((3, 4))
+    T[:, :3] = _rot(rx, ry, rz)
+    T[:, 3] = t
+    return T.astype(np.float32)
+
+
+def compose(A: np.ndarray, B: np.ndarray) -> np.ndarray:
+    """Tcw of A after B (A * B as 4x4)."""
+    A4 = np.vstack([A.astype(np.float64), [0, 0, 0, 1]])
+    B4 = np.vstack([B.astype(np.float64), [0, 0, 0, 1]])
+    return (A4 @ B4)[:3].astype(np.float32)
+
+
+def oracle_frame(left, right, K, dist, bf, mb, nf=2000):
+    """One stereo (or mono, right=None) frame through the CPU oracle: the fields a Frame holds."""
+    from oracle import pyoracle
+    rows, cols = left.shape
+    ol = pyoracle.Oracle(nf, 1.2, 8, 20, 7)
+    kl, dl = ol.extract(left)
+    un, start, idx, bounds = pyoracle.frame_post(kl, cols, rows, K, dist)
+    scale = ol.table(0)
+    f = {"kps": kl, "desc": dl, "un_xy": un, "cell_start": start, "cell_idx": idx, "bounds": bounds, "scale": scale,
+         "u_right": None, "depth": None}
+    if right is not None:
+        orr = pyoracle.Oracle(nf, 1.2, 8, 20, 7)
+        kr, dr = orr.extract(right)
+        pl = [ol.pyramid(l, 0) for l in range(8)]
+        pr = [orr.pyramid(l, 0) for l in range(8)]
+        u, z, _, _ = pyoracle.stereo_match(kl, dl, kr, dr, pl, pr, scale, ol.table(1), bf, mb)
+        f["u_right"], f["depth"] = u, z
+    return f
+
+
+def map_points(last: dict, Tcw_last: np.ndarray, K, rng: np.random.Generator, obs_rate=0.7, outlier_rate=0.05,
+               flip_bits=6, synth_depth=None, copies=1):
+    """Map points for the last frame: keypoint i with depth z > 0 (or a made-up depth when the frame
+    is monocular) is un-projected with the last pose; its descriptor is the keypoint's with a few bits
+    flipped.  copies > 1 repeats every entry (crowding: several queries want the same keypoint)."""
+    fx, fy, cx, cy = K
+    n = len(last["kps"])
+    z = last["depth"] if last["depth"] is not None else np.full(n, -1.0, np.float32)
+    z = z.astype(np.float64).copy()
+    if synth_depth is not None:
+        lo, hi = synth_depth
+        fill = rng.uniform(lo, hi, n)
+        z = np.where(z > 0, z, np.where(rng.random(n) < 0.8, fill, -1.0))
+    has = z > 0
+    u, v = last["un_xy"][:, 0].astype(np.float64), last["un_xy"][:, 1].astype(np.float64)
+    Xc = np.stack([(u - cx) * z / fx, (v - cy) * z / fy, z], 1)
+    R, t = Tcw_last[:, :3].astype(np.float64), Tcw_last[:, 3].astype(np.float64)
+    Xw = (Xc - t) @ R  # R^T (Xc - t)
+    flags = (has.astype(np.uint8) | ((rng.random(n) < obs_rate).astype(np.uint8) << 1)
+             | ((rng.random(n) < outlier_rate).astype(np.uint8) << 2))
+    desc = last["desc"].copy()
+    for i in range(n):
+        for b in rng.integers(0, 256, rng.integers(0, flip_bits + 1)):
+            desc[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    out = dict(last)
+    out.update({"mp_flags": flags, "mp_xyz": np.where(has[:, None], Xw, 0).astype(np.float32), "mp_desc": desc,
+                "Tcw": Tcw_last})
+    if copies > 1:
+        for k in ("kps", "desc", "un_xy", "mp_flags", "mp_xyz", "mp_desc"):
+            out[k] = np.concatenate([out[k]] * copies)
+        # the copies differ a little so that they do not all tie
+        jitter = rng.normal(0, 0.02, out["mp_xyz"].shape).astype(np.float32)
+        out["mp_xyz"] = (out["mp_xyz"] + jitter * (out["mp_xyz"][:, 2:3] > 0)).astype(np.float32)
+        out["mp_flags"] = out["mp_flags"].copy()
+        out["mp_flags"][n:] = (out["mp_flags"][n:] & 5) | ((rng.random(len(out["mp_flags"]) - n) < obs_rate).astype(np.uint8) << 1)
+    return out
+
+
+def make_case(seed=0, shape=synth.KITTI_SHAPE, K=KITTI_K, dist=(0.0, 0.0, 0.0, 0.0), bf=KITTI_BF, stereo=True,
+              dz=0.0, nf=2000, obs_rate=0.7, outlier_rate=0.05, copies=1, frame=0):
+    """-> (cur, last, cam, bounds, scale): dicts as oracle.pyoracle.search_by_projection takes them."""
+    rng = np.random.default_rng(1000 + seed)
+    mb = bf / K[0]
+    imgs = {(f, e): synth.make_frame(shape, seed=seed, frame=frame + f, eye=e) for f in (0, 1) for e in ((0, 1) if stereo else (0,))}
+    last = oracle_frame(imgs[(0, 0)], imgs.get((0, 1)), K, dist, bf, mb, nf)
+    cur = oracle_frame(imgs[(1, 0)], imgs.get((1, 1)), K, dist, bf, mb, nf)
+    T_last = pose(0.01, -0.02, 0.005, (0.3, -0.1, 0.2))
+    # frame i+1 is frame i shifted by (3, 1) px: a small yaw / pitch of the camera predicts that shift
+    rel = pose(rx=1.0 / K[1], ry=-3.0 / K[0], t=(0.0, 0.0, -dz))
+    T_cur = compose(rel, T_last)
+    last = map_points(last, T_last, K, rng, obs_rate, outlier_rate, synth_depth=None if stereo else (4.0, 60.0), copies=copies)
+    cur["Tcw"] = T_cur
+    cam = np.array([K[0], K[1], K[2], K[3], bf, mb], np.float32)
+    return cur, last, cam, cur["bounds"], cur["scale"]
