@@ -165,6 +165,46 @@ int borb_stereo_match(borb_extractor *left, borb_extractor *right, float mbf, fl
 int borb_stereo_result(const borb_extractor *left, int frame, const float **u_right, const float **depth,
                        int *n, int *n_matched);
 
+/* -- frame-to-frame matcher: replaces ORBmatcher::SearchByProjection(Frame &CurrentFrame,
+ *    const Frame &LastFrame, const float th, const bool bMono) (src/ORBmatcher.cc:1503-1668), the
+ *    matcher of Tracking::TrackWithMotionModel (src/Tracking.cc:868-936) ------------------------- */
+
+/* The last frame as the matcher reads it: entry i is LastFrame keypoint i.
+ *   flags[i]  bit 0: LastFrame.mvpMapPoints[i] != NULL, bit 1: that map point's Observations() > 0,
+ *             bit 2: LastFrame.mvbOutlier[i]
+ *   xyz[3i..] pMP->GetWorldPos(), desc[32i..] pMP->GetDescriptor() (read only where bit 0 is set)
+ *   octave[i] LastFrame.mvKeys[i].octave, angle[i] LastFrame.mvKeysUn[i].angle
+ *   Tcw       LastFrame.mTcw, rows 0-2 (3 x 4, row-major) */
+typedef struct borb_last_frame {
+    int n;
+    const float *xyz;
+    const uint8_t *desc;
+    const uint8_t *flags;
+    const int32_t *octave;
+    const float *angle;
+    const float *Tcw;
+} borb_last_frame;
+
+#define BORB_MATCH_MONO 1u          /* bMono: no forward / backward octave rule */
+#define BORB_MATCH_NO_ORIENTATION 2u /* ORBmatcher(nnratio, checkOri = false) */
+#define BORB_MATCH_USE_STEREO 4u    /* CurrentFrame.mvuRight = the result of the last borb_stereo_match with
+                                       `cur` as the left handle (else all -1, a monocular frame) */
+
+/* CurrentFrame = frame `frame` of cur's last extract call: keypoints, descriptors, mvKeysUn, mGrid and the
+ * image bounds stay on the device (borb_set_camera must be on: K gives fx, fy, cx, cy).  Tcw_cur =
+ * CurrentFrame.mTcw rows 0-2; mbf, mb = CurrentFrame.mbf, mb; th as the caller passes it (15 mono, 7
+ * stereo, doubled on the retry, src/Tracking.cc:893-906).  match[i2], i2 < *n_cur, = index into `last` of
+ * the map point CurrentFrame.mvpMapPoints[i2] ends up with, or -1 (the reference expects the caller to
+ * have cleared mvpMapPoints, :890); *nmatches = the function's return value.  match must hold
+ * borb_result()'s n entries of that frame. */
+int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_frame *last, const float *Tcw_cur,
+                              float mbf, float mb, float th, unsigned flags, int32_t *match, int *n_cur,
+                              int *nmatches);
+/* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
+int borb_max_keypoints(const borb_extractor *h);
+/* rounds the last call's fixed-point iteration took (>= 1; see csrc/k_match.cuh) */
+int borb_match_rounds(const borb_extractor *cur);
+
 /* geometry only (valid after any extract call) */
 int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows);
 

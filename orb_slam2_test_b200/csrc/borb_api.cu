@@ -30,6 +30,7 @@
 #include "k_pyramid.cuh"
 #include "k_quadtree.cuh"
 #include "k_stereo.cuh"
+#include "k_match.cuh"
 
 static_assert(sizeof(borb_keypoint) == 28 && sizeof(BorbKpRec) == 28, "cv::KeyPoint layout");
 
@@ -160,6 +161,12 @@ struct borb_extractor {
     int st_span = 0;
     cudaEvent_t ev_peer = nullptr; /* recorded on this handle's stream for a peer handle to wait on */
     bool stereo_on_host = false;
+    /* frame-to-frame matcher (M1), allocated on first use: the last frame's packed arrays
+     * [desc 32c][xyz 12c][angle 4c][octave 4c][flags c] for a capacity of c = mt_cap queries */
+    unsigned char *d_mt_last = nullptr, *h_mt_last = nullptr;
+    size_t mt_cap = 0;
+    int *d_mt_choice = nullptr, *d_mt_taker = nullptr, *d_mt_match = nullptr, *h_mt_match = nullptr; /* match[K] + nm[2] */
+    int mt_rounds = 0;
 
     std::vector<GraphEntry> graphs;
     int last_n = 0;          /* frames of the last call */
@@ -235,11 +242,16 @@ void free_geometry(borb_extractor *h)
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
-                   h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds};
+                   h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
+                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
-                    h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds};
+                    h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
+                    h->h_mt_last, h->h_mt_match};
     for (void *p : host) if (p) cudaFreeHost(p);
+    h->d_mt_last = h->h_mt_last = nullptr;
+    h->mt_cap = 0;
+    h->d_mt_choice = h->d_mt_taker = h->d_mt_match = h->h_mt_match = nullptr;
     h->d_gray = nullptr;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
@@ -1226,6 +1238,94 @@ int borb_stereo_result(const borb_extractor *l, int frame, const float **u_right
     if (n_matched) *n_matched = l->h_st_kept[frame];
     return BORB_OK;
 }
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1503-1668) against the
+ * device-resident results of frame `frame` of cur's last call */
+int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_frame *last, const float *Tcw_cur,
+                              float mbf, float mb, float th, unsigned flags, int32_t *match, int *n_cur,
+                              int *nmatches)
+{
+    if (!cur || !last || !Tcw_cur || !match) return fail(BORB_ERR_ARG, "null argument");
+    if (!cur->have_plan || cur->last_n < 1) return fail(BORB_ERR_STATE, "no finished extract call");
+    if (!cur->have_cam || !cur->d_un_xy) return fail(BORB_ERR_STATE, "borb_set_camera must be on: the matcher reads mvKeysUn, mGrid and K");
+    if (cur->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    if (frame < 0 || frame >= cur->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, cur->last_n);
+    if (last->n < 0 || (last->n > 0 && (!last->xyz || !last->desc || !last->flags || !last->octave || !last->angle)) || !last->Tcw)
+        return fail(BORB_ERR_ARG, "last frame arrays");
+    if ((flags & BORB_MATCH_USE_STEREO) && !cur->d_st_u) return fail(BORB_ERR_STATE, "no stereo result on this handle");
+    for (int i = 0; i < last->n; ++i)
+        if ((last->flags[i] & 1) && (last->octave[i] < 0 || last->octave[i] >= cur->nlevels))
+            return fail(BORB_ERR_ARG, "octave %d of last keypoint %d", last->octave[i], i);
+    CU(cudaSetDevice(cur->device));
+    const BorbPlan &P = cur->plan;
+    const size_t K = (size_t)P.kp_total;
+    if (!cur->d_mt_match) {
+        CU(cudaMalloc(&cur->d_mt_taker, 2 * K * 4));
+        CU(cudaMalloc(&cur->d_mt_match, (K + 2) * 4));
+        CU(cudaMallocHost(&cur->h_mt_match, (K + 2) * 4));
+    }
+    if ((size_t)last->n > cur->mt_cap || !cur->d_mt_last) {
+        const size_t cap = (((size_t)std::max(last->n, 1) + 1023) / 1024) * 1024;
+        CU(cudaStreamSynchronize(cur->stream));
+        if (cur->d_mt_last) cudaFree(cur->d_mt_last);
+        if (cur->h_mt_last) cudaFreeHost(cur->h_mt_last);
+        if (cur->d_mt_choice) cudaFree(cur->d_mt_choice);
+        cur->d_mt_last = cur->h_mt_last = nullptr; cur->d_mt_choice = nullptr; cur->mt_cap = 0;
+        CU(cudaMalloc(&cur->d_mt_last, cap * 53));
+        CU(cudaMallocHost(&cur->h_mt_last, cap * 53));
+        CU(cudaMalloc(&cur->d_mt_choice, cap * 4));
+        cur->mt_cap = cap;
+    }
+    const size_t c = cur->mt_cap, n = (size_t)last->n;
+    unsigned char *hp = cur->h_mt_last, *dp = cur->d_mt_last;
+    if (n) {
+        std::memcpy(hp, last->desc, n * 32);
+        std::memcpy(hp + 32 * c, last->xyz, n * 12);
+        std::memcpy(hp + 44 * c, last->angle, n * 4);
+        std::memcpy(hp + 48 * c, last->octave, n * 4);
+        std::memcpy(hp + 52 * c, last->flags, n);
+    }
+    cudaStream_t st = cur->stream;
+    /* one contiguous upload when the arrays are nearly full, else five short ones */
+    if (n * 2 >= c) CU(cudaMemcpyAsync(dp, hp, 53 * c, cudaMemcpyHostToDevice, st));
+    else if (n) {
+        CU(cudaMemcpyAsync(dp, hp, n * 32, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 32 * c, hp + 32 * c, n * 12, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 44 * c, hp + 44 * c, n * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 48 * c, hp + 48 * c, n * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 52 * c, hp + 52 * c, n, cudaMemcpyHostToDevice, st));
+    }
+    MatchParams mp;
+    std::memcpy(mp.Tc, Tcw_cur, 48);
+    std::memcpy(mp.Tl, last->Tcw, 48);
+    mp.fx = cur->cam.fx; mp.fy = cur->cam.fy; mp.cx = cur->cam.cx; mp.cy = cur->cam.cy;
+    mp.mbf = mbf; mp.mb = mb; mp.th = th;
+    mp.mono = (flags & BORB_MATCH_MONO) ? 1 : 0;
+    mp.check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
+    mp.n_last = last->n;
+    for (int l = 0; l < BORB_MAXL; ++l) mp.scale[l] = l < cur->nlevels ? cur->scale[l] : 0.f;
+    const size_t fo = (size_t)frame * K;
+    k_search_by_projection<<<1, MT_NT, 0, st>>>(
+        mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cur->d_cell_start + (size_t)frame * (FR_CELLS + 1),
+        cur->d_cell_idx + fo, cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame,
+        (flags & BORB_MATCH_USE_STEREO) ? cur->d_st_u + fo : nullptr, reinterpret_cast<const float *>(dp + 32 * c),
+        reinterpret_cast<const float *>(dp + 44 * c), reinterpret_cast<const int *>(dp + 48 * c),
+        reinterpret_cast<const uint4 *>(dp), dp + 52 * c, cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,
+        cur->d_mt_match + K);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 2) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const int nc = std::min(cur->h_nout[frame], (int)K);
+    std::memcpy(match, cur->h_mt_match, (size_t)nc * 4);
+    if (n_cur) *n_cur = nc;
+    if (nmatches) *nmatches = cur->h_mt_match[K];
+    cur->mt_rounds = cur->h_mt_match[K + 1];
+    return BORB_OK;
+}
+
+int borb_match_rounds(const borb_extractor *cur) { return cur ? cur->mt_rounds : 0; }
+int borb_max_keypoints(const borb_extractor *h) { return h && h->have_plan ? h->plan.kp_total : 0; }
 
 int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows)
 {

@@ -1,0 +1,221 @@
+/*
+ * k_match.cuh -- M1: the tracking thread's frame-to-frame matcher on the device,
+ *   ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
+ *       /root/reference/src/ORBmatcher.cc:1503-1668
+ * with Frame::GetFeaturesInArea (src/Frame.cc:421-508), ComputeThreeMaxima (:1800-1843) and
+ * DescriptorDistance (:1846-1862), over the CURRENT frame's device-resident results: cv::KeyPoint
+ * records and descriptors (K7), undistorted positions, the 64 x 48 grid and the image bounds (K8),
+ * mvuRight (S1/S2).  The last frame's map points arrive as flat arrays (world position, representative
+ * descriptor, octave and angle of the keypoint they were seen at, flags).
+ *
+ * The reference loop is sequential in the last frame's index i: a current keypoint that holds a map
+ * point with Observations() > 0 is skipped by every later query (:1583-1585).  Restated as a fixed
+ * point: with taker[c] = the smallest i with observations whose best candidate is c, query i may use
+ * candidate c iff taker[c] >= i.  Rounds of (all queries choose given the previous takers -> new
+ * takers) reach the unique fixed point of that recurrence -- the sequential result -- after as many
+ * rounds as the longest chain of displaced queries (2-4 on real frames); a round in which no choice
+ * changes ends the loop.  The rest is order-free: nmatches counts the accepted queries, a slot ends
+ * up with the LARGEST query index that chose it (later assignments overwrite, :1610), every entry of
+ * an orientation bin outside the three maxima clears its slot and subtracts one (:1638-1647).
+ *
+ * One CTA per call (thread per query, a thread walks its query's grid cells in the reference's
+ * (ix, iy, cell order) so the first smallest distance wins as there).  Float forms as the reference
+ * object has them (oracle/match_oracle.cpp): products summed left to right for the 3x3 * 3x1 gemm,
+ * u = fma(fx*xc, 1/zc, cx), ur = fma(-mbf, 1/zc, u); the library is built with --fmad=false, so
+ * only the fmaf() written here fuses.
+ */
+#ifndef K_MATCH_CUH
+#define K_MATCH_CUH
+
+#include "borb_internal.h"
+#include "k_describe.cuh" /* BorbKpRec */
+
+#define MT_NT 1024
+#define MT_COLS 64
+#define MT_ROWS 48
+#define MT_HISTO 30
+#define MT_TH_HIGH 100
+
+struct MatchParams {
+    float Tc[12], Tl[12]; /* Tcw of the current and the last frame, 3 x 4 row-major */
+    float fx, fy, cx, cy, mbf, mb, th;
+    int mono, check_ori, n_last;
+    float scale[BORB_MAXL];
+};
+
+__device__ __forceinline__ float mt_dot3(const float *row, const float *x)
+{
+    float s = 0.f;
+    s += row[0] * x[0];
+    s += row[1] * x[1];
+    s += row[2] * x[2];
+    return s;
+}
+
+__device__ __forceinline__ int mt_hamming(const uint4 a0, const uint4 a1, const uint4 *b)
+{
+    const uint4 b0 = b[0], b1 = b[1];
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+/* half away from zero, exactly (std::round) */
+__device__ __forceinline__ int mt_round(float x)
+{
+    float t = truncf(x);
+    if (fabsf(x - t) >= 0.5f) t += copysignf(1.f, x);
+    return (int)t;
+}
+
+__device__ __forceinline__ int mt_bin(float a_last, float a_cur)
+{
+    float rot = a_last - a_cur;
+    if (rot < 0.0f) rot += 360.0f;
+    int bin = mt_round(rot * (1.0f / MT_HISTO));
+    if (bin == MT_HISTO) bin = 0;
+    return bin;
+}
+
+/* last frame: xyz [3n], angle [n], octave [n], desc [n] x 32 B (16-byte aligned), flags [n] (bit 0 map
+ * point, bit 1 Observations() > 0, bit 2 outlier).  Scratch: choice [n_last], taker [2][kp_total].
+ * Out: match [kp_total] = index of the last-frame map point per current keypoint or -1; nm[0] =
+ * nmatches, nm[1] = rounds taken. */
+__global__ void __launch_bounds__(MT_NT, 1)
+k_search_by_projection(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
+                       const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
+                       const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
+                       const float *__restrict__ bounds, const int *__restrict__ n_cur_p,
+                       const float *__restrict__ u_right, const float *__restrict__ l_xyz,
+                       const float *__restrict__ l_angle, const int *__restrict__ l_octave,
+                       const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
+                       int *__restrict__ choice, int *__restrict__ taker, int kp_total, int *__restrict__ match,
+                       int *__restrict__ nm)
+{
+    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_dir;
+    const int tid = threadIdx.x;
+    const int n_cur = min(*n_cur_p, kp_total), n_last = mp.n_last;
+    const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+    const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
+
+    if (tid == 0) { /* twc = -Rcw^T tcw; tlc = Rlw twc + tlw; only its z decides the search direction (:1515-1526) */
+        float twc[3];
+        const float tcw[3] = {mp.Tc[3], mp.Tc[7], mp.Tc[11]};
+#pragma unroll
+        for (int y = 0; y < 3; ++y) {
+            float s = 0.f;
+            s += (-mp.Tc[y]) * tcw[0];
+            s += (-mp.Tc[4 + y]) * tcw[1];
+            s += (-mp.Tc[8 + y]) * tcw[2];
+            twc[y] = s;
+        }
+        const float tlc_z = mt_dot3(mp.Tl + 8, twc) + mp.Tl[11];
+        const bool fwd = tlc_z > mp.mb && !mp.mono, bwd = -tlc_z > mp.mb && !mp.mono;
+        s_dir = fwd ? 1 : bwd ? 2 : 0;
+        s_nm = 0;
+    }
+    if (tid < MT_HISTO) s_hist[tid] = 0;
+    for (int i = tid; i < n_last; i += MT_NT) choice[i] = -1;
+    for (int c = tid; c < kp_total; c += MT_NT) { taker[c] = 0x7fffffff; match[c] = -1; }
+    __syncthreads();
+    const int dir = s_dir;
+
+    int round = 0;
+    for (;; ++round) {
+        const int *tk_prev = taker + (round & 1) * kp_total;
+        int *tk_new = taker + ((round + 1) & 1) * kp_total;
+        for (int c = tid; c < n_cur; c += MT_NT) tk_new[c] = 0x7fffffff;
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        for (int i = tid; i < n_last; i += MT_NT) {
+            const uint32_t fl = l_flags[i];
+            int best = 256, best_idx = -1;
+            if ((fl & 1u) && !(fl & 4u)) {
+                const float X[3] = {l_xyz[3 * i], l_xyz[3 * i + 1], l_xyz[3 * i + 2]};
+                const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7],
+                            zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
+                const float invzc = 1.0f / zc;
+                const float u = fmaf(mp.fx * xc, invzc, mp.cx), v = fmaf(mp.fy * yc, invzc, mp.cy);
+                bool ok = !(invzc < 0) && !(u < min_x || u > max_x) && !(v < min_y || v > max_y);
+                const int oct = l_octave[i];
+                const float radius = mp.th * mp.scale[oct];
+                int min_level, max_level;
+                if (dir == 1) { min_level = oct; max_level = -1; }
+                else if (dir == 2) { min_level = 0; max_level = oct; }
+                else { min_level = oct - 1; max_level = oct + 1; }
+                /* Frame::GetFeaturesInArea */
+                const int cx0 = max(0, (int)floorf((u - min_x - radius) * winv));
+                const int cx1 = min(MT_COLS - 1, (int)ceilf((u - min_x + radius) * winv));
+                const int cy0 = max(0, (int)floorf((v - min_y - radius) * hinv));
+                const int cy1 = min(MT_ROWS - 1, (int)ceilf((v - min_y + radius) * hinv));
+                ok = ok && cx0 < MT_COLS && cx1 >= 0 && cy0 < MT_ROWS && cy1 >= 0;
+                if (ok) {
+                    const bool check_levels = (min_level > 0) || (max_level >= 0);
+                    const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
+                    const float ur = fmaf(-mp.mbf, invzc, u);
+                    for (int ix = cx0; ix <= cx1; ++ix) {
+                        /* the cells (ix, cy0..cy1) are consecutive in the cell-major lists */
+                        const int q0 = cell_start[ix * MT_ROWS + cy0], q1 = cell_start[ix * MT_ROWS + cy1 + 1];
+                        for (int q = q0; q < q1; ++q) {
+                            const int i2 = cell_idx[q];
+                            const int o2 = kp[i2].octave;
+                            if (check_levels && (o2 < min_level || (max_level >= 0 && o2 > max_level))) continue;
+                            const float2 p = un_xy[i2];
+                            if (!(fabsf(p.x - u) < radius && fabsf(p.y - v) < radius)) continue;
+                            if (tk_prev[i2] < i) continue; /* holds a map point with observations (:1583-1585) */
+                            if (u_right) {
+                                const float ur2 = u_right[i2];
+                                if (ur2 > 0 && fabsf(ur - ur2) > radius) continue;
+                            }
+                            const int d = mt_hamming(d0, d1, reinterpret_cast<const uint4 *>(desc) + 2 * i2);
+                            if (d < best) { best = d; best_idx = i2; }
+                        }
+                    }
+                }
+            }
+            const int ch = best <= MT_TH_HIGH ? best_idx : -1;
+            if (ch != choice[i]) { choice[i] = ch; s_changed = 1; }
+            if (ch >= 0 && (fl & 2u)) atomicMin(&tk_new[ch], i);
+        }
+        __syncthreads();
+        const int changed = s_changed;
+        __syncthreads();
+        if (!changed) break;
+    }
+
+    /* ---- assignment, orientation histogram, three maxima ---- */
+    for (int i = tid; i < n_last; i += MT_NT) {
+        const int ch = choice[i];
+        if (ch >= 0) {
+            atomicAdd(&s_nm, 1);
+            atomicMax(&match[ch], i);
+            if (mp.check_ori) atomicAdd(&s_hist[mt_bin(l_angle[i], kp[ch].angle)], 1);
+        }
+    }
+    __syncthreads();
+    if (mp.check_ori) {
+        if (tid == 0) {
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int b = 0; b < MT_HISTO; ++b) {
+                const int s = s_hist[b];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
+                else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
+                else if (s > max3) { max3 = s; ind3 = b; }
+            }
+            if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+            else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+            for (int b = 0; b < MT_HISTO; ++b) s_keep[b] = (b == ind1 || b == ind2 || b == ind3);
+        }
+        __syncthreads();
+        for (int i = tid; i < n_last; i += MT_NT) {
+            const int ch = choice[i];
+            if (ch >= 0 && !s_keep[mt_bin(l_angle[i], kp[ch].angle)]) {
+                match[ch] = -1;
+                atomicSub(&s_nm, 1);
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; }
+}
+
+#endif

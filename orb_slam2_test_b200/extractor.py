@@ -105,6 +105,10 @@ def load_library() -> C.CDLL:
     lib.borb_set_input_format.argtypes = [_vp, C.c_int]
     lib.borb_set_rectify_map.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, C.c_size_t]
     lib.borb_stereo_match.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_uint]
+    lib.borb_search_by_projection.argtypes = [_vp, C.c_int, _vp, _vp, C.c_float, C.c_float, C.c_float, C.c_uint, _vp,
+                                              C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_match_rounds.argtypes = [_vp]
+    lib.borb_max_keypoints.argtypes = [_vp]
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
                                        C.POINTER(C.c_int)]
     _lib = lib
@@ -121,6 +125,11 @@ def debug_sincos(radians: float):
     s, c = C.c_float(), C.c_float()
     lib.borb_debug_sincos(radians, C.byref(s), C.byref(c))
     return s.value, c.value
+
+
+class _LastFrame(C.Structure):  # == borb_last_frame
+    _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("octave", _vp), ("angle", _vp),
+                ("Tcw", _vp)]
 
 
 class ORBextractor:
@@ -372,6 +381,27 @@ class ORBextractor:
         ur = np.ctypeslib.as_array(C.cast(u, C.POINTER(C.c_float)), shape=(cnt,)).copy()
         dz = np.ctypeslib.as_array(C.cast(z, C.POINTER(C.c_float)), shape=(cnt,)).copy()
         return ur, dz, m.value
+
+    def search_by_projection(self, last: dict, Tcw_cur, mbf: float, mb: float, th: float, frame: int = 0,
+                             mono: bool = False, check_orientation: bool = True, use_stereo: bool = False):
+        """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1503-1668)
+        with frame `frame` of this extractor's last call as the CurrentFrame, on the device (needs
+        set_camera).  last: dict with mp_xyz [n,3] f32, mp_desc [n,32] u8, mp_flags [n] u8, octave [n] i32,
+        angle [n] f32, Tcw [3,4] f32 (see include/borb.h).  -> (match [n_cur] i32, nmatches)."""
+        keep = [np.ascontiguousarray(last["mp_xyz"], np.float32), np.ascontiguousarray(last["mp_desc"], np.uint8),
+                np.ascontiguousarray(last["mp_flags"], np.uint8), np.ascontiguousarray(last["octave"], np.int32),
+                np.ascontiguousarray(last["angle"], np.float32), np.ascontiguousarray(last["Tcw"], np.float32)]
+        lf = _LastFrame(len(keep[2]), *[a.ctypes.data for a in keep])
+        tc = np.ascontiguousarray(Tcw_cur, np.float32)
+        out = np.full(max(self._lib.borb_max_keypoints(self._h), 1), -1, np.int32)
+        n, nm = C.c_int(), C.c_int()
+        flags = (1 if mono else 0) | (0 if check_orientation else 2) | (4 if use_stereo else 0)
+        _check(self._lib, self._lib.borb_search_by_projection(self._h, frame, C.addressof(lf), tc.ctypes.data, mbf, mb, th,
+                                                              flags, out.ctypes.data, C.byref(n), C.byref(nm)))
+        return out[:n.value].copy(), nm.value
+
+    def match_rounds(self) -> int:
+        return self._lib.borb_match_rounds(self._h)
 
     def level_size(self, level: int):
         c, r = C.c_int(), C.c_int()

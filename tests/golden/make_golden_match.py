@@ -1,0 +1,48 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/match_expected.npz: outputs of the REFERENCE's own src/ORBmatcher.cc
+(ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono), compiled in place into
+oracle/_ref/librefmatch.so) on the scenarios of tests/matchcase.py, which are a pure function of
+their arguments (synthetic frames -> oracle extractor -> map points), so only the outputs are stored.
+
+Run in the build container (needs /root/reference):   python tests/golden/make_golden_match.py
+"""
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[2]
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+import matchcase  # noqa: E402
+from oracle.pyoracle import RefMatcher  # noqa: E402
+from orb_slam2_test_b200 import synth  # noqa: E402
+
+HERE = Path(__file__).resolve().parent
+
+# name -> (make_case kwargs, mono flag, thresholds)
+CASES = {
+    "kitti_still": (dict(seed=11), False, (7.0, 15.0)),
+    "kitti_forward": (dict(seed=12, dz=1.0), False, (7.0, 14.0)),
+    "kitti_backward": (dict(seed=13, dz=-1.0), False, (7.0, 14.0)),
+    "kitti_crowded": (dict(seed=14, copies=3, obs_rate=0.9), False, (15.0,)),
+    "tum_mono": (dict(seed=15, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False,
+                      nf=1000), True, (15.0, 30.0)),
+}
+
+
+def main():
+    out = {}
+    for name, (kw, mono, ths) in CASES.items():
+        cur, last, cam, bounds, scale = matchcase.make_case(**kw)
+        for th in ths:
+            for ori in (1, 0):
+                m, nm = RefMatcher.search_by_projection(cur, last, cam, bounds, scale, th, mono=mono, check_ori=bool(ori))
+                out[f"{name}_th{int(th)}_ori{ori}_match"] = m
+                out[f"{name}_th{int(th)}_ori{ori}_nm"] = np.array([nm, len(last["kps"]), int((m >= 0).sum())], np.int32)
+                print(name, th, ori, "nmatches", nm, "slots", int((m >= 0).sum()))
+    np.savez_compressed(HERE / "match_expected.npz", **out)
+
+
+if __name__ == "__main__":
+    main()

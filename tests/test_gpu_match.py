@@ -1,0 +1,103 @@
+"""GPU parity for the frame-to-frame matcher (first consumer):
+borb_search_by_projection against the CPU restatement of ORBmatcher::SearchByProjection(Frame, Frame)
+(oracle/match_oracle.cpp, src/ORBmatcher.cc:1503-1668), which tests/test_oracle_match_vs_reference.py
+pins to the reference's own ORBmatcher.cc compiled in place.
+
+Bar: CurrentFrame.mvpMapPoints (as indices into the last frame) and nmatches identical.  The current
+frame is extracted on the GPU (bit-exact with the oracle frame the scenario was built from, so the
+indices mean the same keypoints); its descriptors, undistorted positions, grid, bounds and mvuRight never
+leave the device."""
+import numpy as np
+import pytest
+
+from orb_slam2_test_b200 import synth
+
+import matchcase
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_frame(shape, seed, frame, K, dist, stereo, nf, bf, mb):
+    from orb_slam2_test_b200 import ORBextractor
+    left = ORBextractor(nf, 1.2, 8, 20, 7)
+    left.set_camera(K, dist)
+    left(synth.make_frame(shape, seed=seed, frame=frame, eye=0))
+    right = None
+    if stereo:
+        right = ORBextractor(nf, 1.2, 8, 20, 7)
+        right(synth.make_frame(shape, seed=seed, frame=frame, eye=1))
+        left.stereo_match(right, bf, mb)
+    return left, right
+
+
+def _last_for_abi(last):
+    d = dict(last)
+    d["octave"] = last["kps"]["octave"]
+    d["angle"] = last["kps"]["angle"]
+    return d
+
+
+def _check(tag, oracle, ths=(7.0, 15.0, 30.0), mono_flag=False, **kw):
+    cur, last, cam, bounds, scale = matchcase.make_case(**kw)
+    stereo = kw.get("stereo", True)
+    K = kw.get("K", matchcase.KITTI_K)
+    dist = kw.get("dist", (0.0, 0.0, 0.0, 0.0))
+    bf = float(cam[4]); mb = float(cam[5])
+    ext, right = _gpu_frame(kw.get("shape", synth.KITTI_SHAPE), kw.get("seed", 0), kw.get("frame", 0) + 1, K, dist,
+                            stereo, kw.get("nf", 2000), bf, mb)
+    kps, desc = ext.result(0)
+    assert kps.tobytes() == cur["kps"].tobytes() and np.array_equal(desc, cur["desc"]), f"{tag}: current frame differs"
+    total = 0
+    for th in ths:
+        for check_ori in (True, False):
+            want, wnm = oracle.search_by_projection(cur, last, cam, bounds, scale, th, mono=mono_flag, check_ori=check_ori)
+            got, nm = ext.search_by_projection(_last_for_abi(last), cur["Tcw"], bf, mb, th, mono=mono_flag,
+                                               check_orientation=check_ori, use_stereo=stereo)
+            assert len(got) == len(want)
+            bad = np.nonzero(got != want)[0]
+            assert bad.size == 0, f"{tag} th={th} ori={check_ori}: {bad.size} slots differ, e.g. {bad[:5]}: {got[bad[:5]]} vs {want[bad[:5]]}"
+            assert nm == wnm, f"{tag} th={th}: nmatches {nm} vs {wnm}"
+            assert 1 <= ext.match_rounds() <= 64
+            total += wnm
+    return total
+
+
+@pytest.mark.parametrize("seed,dz", [(1, 0.0), (2, 1.0), (3, -1.0)])
+def test_kitti_stereo_tracking(seed, dz, oracle_built):
+    """dz = 0: the +-1 octave rule; dz = +-1 m: the forward / backward rules (tlc.z against mb, :1524-1526)."""
+    assert _check(f"kitti seed {seed} dz {dz}", oracle_built, seed=seed, dz=dz) > 2000
+
+
+def test_crowded_queries_exercise_the_observation_rule(oracle_built):
+    """Every map point three times, 90 % with observations: later copies must skip the keypoints earlier
+    ones hold (:1583-1585), copies without observations get overwritten (:1610); more than one round."""
+    from orb_slam2_test_b200 import ORBextractor  # noqa: F401
+    _check("crowded", oracle_built, seed=4, copies=3, obs_rate=0.9)
+
+
+def test_monocular_tum_with_distortion(oracle_built):
+    """bMono, TUM1 camera with distortion (mvKeysUn != mvKeys, bounds beyond the image), no mvuRight."""
+    assert _check("tum mono", oracle_built, ths=(15.0, 30.0), mono_flag=True, seed=5, shape=synth.TUM_SHAPE,
+                  K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False, nf=1000) > 200
+
+
+def test_no_map_points_and_argument_errors(oracle_built):
+    from orb_slam2_test_b200 import ORBextractor
+    from orb_slam2_test_b200.extractor import BorbError
+    cur, last, cam, bounds, scale = matchcase.make_case(seed=6)
+    ext = ORBextractor(2000, 1.2, 8, 20, 7)
+    ext(synth.make_frame(synth.KITTI_SHAPE, seed=6, frame=1))
+    with pytest.raises(BorbError):  # no camera: no mvKeysUn / grid on the device
+        ext.search_by_projection(_last_for_abi(last), cur["Tcw"], 386.0, 0.5, 7.0)
+    ext.set_camera(matchcase.KITTI_K, (0.0, 0.0, 0.0, 0.0))
+    ext(synth.make_frame(synth.KITTI_SHAPE, seed=6, frame=1))
+    with pytest.raises(BorbError):  # no stereo result on this handle
+        ext.search_by_projection(_last_for_abi(last), cur["Tcw"], 386.0, 0.5, 7.0, use_stereo=True)
+    empty = _last_for_abi(last)
+    empty["mp_flags"] = np.zeros_like(last["mp_flags"])
+    got, nm = ext.search_by_projection(empty, cur["Tcw"], 386.0, 0.5, 7.0)
+    assert nm == 0 and (got == -1).all() and ext.match_rounds() == 1
+    bad = _last_for_abi(last)
+    bad["octave"] = np.full(len(last["kps"]), 9, np.int32)
+    with pytest.raises(BorbError):
+        ext.search_by_projection(bad, cur["Tcw"], 386.0, 0.5, 7.0)

@@ -1,0 +1,56 @@
+"""The restatement of ORBmatcher::SearchByProjection(Frame, Frame) (oracle/match_oracle.cpp) against the
+reference's OWN src/ORBmatcher.cc + src/Frame.cc compiled in place (oracle/_ref/librefmatch.so, driven by
+oracle/matcher_driver.cpp): CurrentFrame.mvpMapPoints and nmatches identical.  Needs /root/reference at
+build time; tests/test_golden_match.py carries the same outputs to machines without it."""
+import numpy as np
+import pytest
+
+from orb_slam2_test_b200 import synth
+
+import matchcase
+
+
+@pytest.fixture(scope="module")
+def ref(oracle_built):
+    if not oracle_built.RefMatcher.available():
+        pytest.skip("oracle/_ref/librefmatch.so not built (no reference tree)")
+    return oracle_built.RefMatcher
+
+
+def _compare(py, ref, tag, ths, mono=False, **kw):
+    cur, last, cam, bounds, scale = matchcase.make_case(**kw)
+    total = 0
+    for th in ths:
+        for ori in (True, False):
+            want, wnm = ref.search_by_projection(cur, last, cam, bounds, scale, th, mono=mono, check_ori=ori)
+            got, nm = py.search_by_projection(cur, last, cam, bounds, scale, th, mono=mono, check_ori=ori)
+            assert np.array_equal(got, want), f"{tag} th={th} ori={ori}: {(got != want).sum()} slots differ"
+            assert nm == wnm, f"{tag} th={th} ori={ori}: nmatches {nm} vs {wnm}"
+            total += wnm
+    return total
+
+
+@pytest.mark.parametrize("seed,dz", [(1, 0.0), (2, 1.0), (3, -1.0), (7, 0.3), (8, -0.6)])
+def test_kitti_stereo(seed, dz, oracle_built, ref):
+    """still / forward / backward (tlc.z against mb) and the two motions just either side of mb = 0.537 m"""
+    assert _compare(oracle_built, ref, f"kitti {seed} dz {dz}", (7.0, 14.0, 30.0), seed=seed, dz=dz) > 1500
+
+
+@pytest.mark.parametrize("obs_rate", [0.0, 0.5, 1.0])
+def test_crowded_queries(obs_rate, oracle_built, ref):
+    """three copies of every map point: the Observations() > 0 skip and the overwrite of points without"""
+    _compare(oracle_built, ref, f"crowded {obs_rate}", (15.0, 40.0), seed=4, copies=3, obs_rate=obs_rate)
+
+
+def test_monocular_distorted(oracle_built, ref):
+    assert _compare(oracle_built, ref, "tum mono", (15.0, 30.0), mono=True, seed=5, shape=synth.TUM_SHAPE,
+                    K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False, nf=1000) > 500
+
+
+def test_points_behind_and_outside(oracle_built, ref):
+    """a current pose looking the other way: invzc < 0 and out-of-bounds projections reject everything"""
+    cur, last, cam, bounds, scale = matchcase.make_case(seed=9)
+    cur["Tcw"] = matchcase.compose(matchcase.pose(ry=np.pi), cur["Tcw"])
+    want, wnm = ref.search_by_projection(cur, last, cam, bounds, scale, 15.0)
+    got, nm = oracle_built.search_by_projection(cur, last, cam, bounds, scale, 15.0)
+    assert nm == wnm == 0 and np.array_equal(got, want) and (got == -1).all()
