@@ -38,6 +38,7 @@ SYMBOLS = [
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
     "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
     "borb_last_prestep_ms", "borb_set_camera", "borb_frame_grid",
+    "borb_search_by_projection", "borb_match_rounds", "borb_max_keypoints",
 ]
 
 
