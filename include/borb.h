@@ -202,7 +202,8 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
                               int *nmatches);
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
-/* rounds the last call's fixed-point iteration took (>= 1; see csrc/k_match.cuh) */
+/* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans
+ * (queries whose cached candidates were all held; see csrc/k_match.cuh) */
 int borb_match_rounds(const borb_extractor *cur);
 
 /* geometry only (valid after any extract call) */

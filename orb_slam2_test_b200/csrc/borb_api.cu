@@ -165,7 +165,10 @@ struct borb_extractor {
      * [desc 32c][xyz 12c][angle 4c][octave 4c][flags c] for a capacity of c = mt_cap queries */
     unsigned char *d_mt_last = nullptr, *h_mt_last = nullptr;
     size_t mt_cap = 0;
-    int *d_mt_choice = nullptr, *d_mt_taker = nullptr, *d_mt_match = nullptr, *h_mt_match = nullptr; /* match[K] + nm[2] */
+    int *d_mt_choice = nullptr, *d_mt_taker = nullptr, *d_mt_match = nullptr, *h_mt_match = nullptr; /* match[K] + nm[4] */
+    uint32_t *d_mt_cache = nullptr; /* [mt_cap][MT_K] candidate keys */
+    uint8_t *d_mt_more = nullptr;
+    int mt_rescans = 0;
     int mt_rounds = 0;
 
     std::vector<GraphEntry> graphs;
@@ -243,7 +246,7 @@ void free_geometry(borb_extractor *h)
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
-                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match};
+                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
@@ -252,6 +255,7 @@ void free_geometry(borb_extractor *h)
     h->d_mt_last = h->h_mt_last = nullptr;
     h->mt_cap = 0;
     h->d_mt_choice = h->d_mt_taker = h->d_mt_match = h->h_mt_match = nullptr;
+    h->d_mt_cache = nullptr; h->d_mt_more = nullptr;
     h->d_gray = nullptr;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
@@ -1259,10 +1263,11 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
     CU(cudaSetDevice(cur->device));
     const BorbPlan &P = cur->plan;
     const size_t K = (size_t)P.kp_total;
+    if (K > 65535) return fail(BORB_ERR_ARG, "the matcher packs list positions in 16 bits: %zu keypoint slots per frame", K);
     if (!cur->d_mt_match) {
         CU(cudaMalloc(&cur->d_mt_taker, 2 * K * 4));
-        CU(cudaMalloc(&cur->d_mt_match, (K + 2) * 4));
-        CU(cudaMallocHost(&cur->h_mt_match, (K + 2) * 4));
+        CU(cudaMalloc(&cur->d_mt_match, (K + 4) * 4));
+        CU(cudaMallocHost(&cur->h_mt_match, (K + 4) * 4));
     }
     if ((size_t)last->n > cur->mt_cap || !cur->d_mt_last) {
         const size_t cap = (((size_t)std::max(last->n, 1) + 1023) / 1024) * 1024;
@@ -1270,10 +1275,15 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
         if (cur->d_mt_last) cudaFree(cur->d_mt_last);
         if (cur->h_mt_last) cudaFreeHost(cur->h_mt_last);
         if (cur->d_mt_choice) cudaFree(cur->d_mt_choice);
+        if (cur->d_mt_cache) cudaFree(cur->d_mt_cache);
+        if (cur->d_mt_more) cudaFree(cur->d_mt_more);
         cur->d_mt_last = cur->h_mt_last = nullptr; cur->d_mt_choice = nullptr; cur->mt_cap = 0;
+        cur->d_mt_cache = nullptr; cur->d_mt_more = nullptr;
         CU(cudaMalloc(&cur->d_mt_last, cap * 53));
         CU(cudaMallocHost(&cur->h_mt_last, cap * 53));
         CU(cudaMalloc(&cur->d_mt_choice, cap * 4));
+        CU(cudaMalloc(&cur->d_mt_cache, cap * MT_K * 4));
+        CU(cudaMalloc(&cur->d_mt_more, cap));
         cur->mt_cap = cap;
     }
     const size_t c = cur->mt_cap, n = (size_t)last->n;
@@ -1304,16 +1314,38 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
     mp.check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
     mp.n_last = last->n;
     for (int l = 0; l < BORB_MAXL; ++l) mp.scale[l] = l < cur->nlevels ? cur->scale[l] : 0.f;
+    {   /* search direction (:1515-1526): twc = -Rcw^T tcw, tlc = Rlw twc + tlw, OpenCV's small float gemm
+         * (products summed left to right); this file is compiled without contraction */
+        const float *Tc = mp.Tc, *Tl = mp.Tl;
+        float twc[3];
+        for (int y = 0; y < 3; ++y) {
+            float sacc = 0.f;
+            for (int k = 0; k < 3; ++k) sacc += (-Tc[4 * k + y]) * Tc[4 * k + 3];
+            twc[y] = sacc;
+        }
+        float sacc = 0.f;
+        for (int k = 0; k < 3; ++k) sacc += Tl[8 + k] * twc[k];
+        const float tlc_z = sacc + Tl[11];
+        const bool fwd = tlc_z > mb && !mp.mono, bwd = -tlc_z > mb && !mp.mono;
+        mp.dir = fwd ? 1 : bwd ? 2 : 0;
+    }
     const size_t fo = (size_t)frame * K;
-    k_search_by_projection<<<1, MT_NT, 0, st>>>(
-        mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cur->d_cell_start + (size_t)frame * (FR_CELLS + 1),
-        cur->d_cell_idx + fo, cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame,
-        (flags & BORB_MATCH_USE_STEREO) ? cur->d_st_u + fo : nullptr, reinterpret_cast<const float *>(dp + 32 * c),
-        reinterpret_cast<const float *>(dp + 44 * c), reinterpret_cast<const int *>(dp + 48 * c),
-        reinterpret_cast<const uint4 *>(dp), dp + 52 * c, cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,
-        cur->d_mt_match + K);
+    const float *d_ur = (flags & BORB_MATCH_USE_STEREO) ? cur->d_st_u + fo : nullptr;
+    const float *l_xyz = reinterpret_cast<const float *>(dp + 32 * c), *l_angle = reinterpret_cast<const float *>(dp + 44 * c);
+    const int *l_oct = reinterpret_cast<const int *>(dp + 48 * c);
+    const uint4 *l_desc = reinterpret_cast<const uint4 *>(dp);
+    const uint8_t *l_flags = dp + 52 * c;
+    const int *cs = cur->d_cell_start + (size_t)frame * (FR_CELLS + 1), *ci = cur->d_cell_idx + fo;
+    if (last->n > 0)
+        k_match_candidates<<<(last->n + MT_CAND_NT / 32 - 1) / (MT_CAND_NT / 32), MT_CAND_NT, 0, st>>>(
+            mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4,
+            d_ur, l_xyz, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);
+    k_match_resolve<<<1, MT_NT, 0, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci,
+                                         cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame, d_ur, l_xyz, l_angle, l_oct,
+                                         l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more, cur->d_mt_choice, cur->d_mt_taker,
+                                         (int)K, cur->d_mt_match, cur->d_mt_match + K);
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 2) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     const int nc = std::min(cur->h_nout[frame], (int)K);
@@ -1321,10 +1353,11 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
     if (n_cur) *n_cur = nc;
     if (nmatches) *nmatches = cur->h_mt_match[K];
     cur->mt_rounds = cur->h_mt_match[K + 1];
+    cur->mt_rescans = cur->h_mt_match[K + 2];
     return BORB_OK;
 }
 
-int borb_match_rounds(const borb_extractor *cur) { return cur ? cur->mt_rounds : 0; }
+int borb_match_rounds(const borb_extractor *cur) { return cur ? cur->mt_rounds | (cur->mt_rescans << 8) : 0; }
 int borb_max_keypoints(const borb_extractor *h) { return h && h->have_plan ? h->plan.kp_total : 0; }
 
 int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows)

@@ -18,11 +18,20 @@
  * up with the LARGEST query index that chose it (later assignments overwrite, :1610), every entry of
  * an orientation bin outside the three maxima clears its slot and subtracts one (:1638-1647).
  *
- * One CTA per call (thread per query, a thread walks its query's grid cells in the reference's
- * (ix, iy, cell order) so the first smallest distance wins as there).  Float forms as the reference
- * object has them (oracle/match_oracle.cpp): products summed left to right for the 3x3 * 3x1 gemm,
- * u = fma(fx*xc, 1/zc, cx), ur = fma(-mbf, 1/zc, u); the library is built with --fmad=false, so
- * only the fmaf() written here fuses.
+ * Two kernels per call:
+ *   M1a k_match_candidates  warp per query, grid over the whole GPU: projection, the grid cells of
+ *       GetFeaturesInArea walked 32 candidates at a time (in a column of cells the cell-major lists are
+ *       consecutive, and the list position q grows in the reference's scan order ix, iy, j), octave /
+ *       window / mvuRight filters, 256-bit Hamming by popc; the MT_K best (distance << 16 | q) keys --
+ *       i.e. best first, ties in scan order as the reference's strict < keeps the first -- are cached
+ *       per query together with "there were more".
+ *   M1b k_match_resolve     one CTA: the rounds of the fixed point on the cached keys (a query's
+ *       choice is its first cached candidate nobody earlier holds; only a query whose MT_K cached
+ *       candidates are all held AND that had more rescans its cells), then assignment, orientation
+ *       histogram, ComputeThreeMaxima, removal.
+ * Float forms as the reference object has them (oracle/match_oracle.cpp): products summed left to
+ * right for the 3x3 * 3x1 gemm, u = fma(fx*xc, 1/zc, cx), ur = fma(-mbf, 1/zc, u); the library is
+ * built with --fmad=false, so only the fmaf() written here fuses.
  */
 #ifndef K_MATCH_CUH
 #define K_MATCH_CUH
@@ -40,6 +49,7 @@ struct MatchParams {
     float Tc[12], Tl[12]; /* Tcw of the current and the last frame, 3 x 4 row-major */
     float fx, fy, cx, cy, mbf, mb, th;
     int mono, check_ori, n_last;
+    int dir; /* 1 forward, 2 backward, 0 neither: from tlc.z against mb (:1515-1526), evaluated on the host */
     float scale[BORB_MAXL];
 };
 
@@ -76,48 +86,144 @@ __device__ __forceinline__ int mt_bin(float a_last, float a_cur)
     return bin;
 }
 
-/* last frame: xyz [3n], angle [n], octave [n], desc [n] x 32 B (16-byte aligned), flags [n] (bit 0 map
- * point, bit 1 Observations() > 0, bit 2 outlier).  Scratch: choice [n_last], taker [2][kp_total].
- * Out: match [kp_total] = index of the last-frame map point per current keypoint or -1; nm[0] =
- * nmatches, nm[1] = rounds taken. */
-__global__ void __launch_bounds__(MT_NT, 1)
-k_search_by_projection(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
-                       const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
-                       const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
-                       const float *__restrict__ bounds, const int *__restrict__ n_cur_p,
-                       const float *__restrict__ u_right, const float *__restrict__ l_xyz,
-                       const float *__restrict__ l_angle, const int *__restrict__ l_octave,
-                       const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
-                       int *__restrict__ choice, int *__restrict__ taker, int kp_total, int *__restrict__ match,
-                       int *__restrict__ nm)
+#define MT_K 8            /* cached candidates per query */
+#define MT_CAND_NT 256    /* M1a: 8 queries per CTA */
+#define MT_NOKEY 0xffffffffu
+
+struct MtQuery { /* what the candidate scan of one query needs (:1537-1572) */
+    bool ok, check_levels;
+    float u, v, radius, ur;
+    int min_level, max_level, cx0, cx1, cy0, cy1;
+};
+
+__device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *__restrict__ l_xyz, int oct, int i,
+                                            float min_x, float max_x, float min_y, float max_y, float winv, float hinv)
 {
-    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_dir;
+    MtQuery Q;
+    const float X[3] = {l_xyz[3 * i], l_xyz[3 * i + 1], l_xyz[3 * i + 2]};
+    const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7], zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
+    const float invzc = 1.0f / zc;
+    Q.u = fmaf(mp.fx * xc, invzc, mp.cx);
+    Q.v = fmaf(mp.fy * yc, invzc, mp.cy);
+    Q.ok = !(invzc < 0) && !(Q.u < min_x || Q.u > max_x) && !(Q.v < min_y || Q.v > max_y);
+    Q.radius = mp.th * mp.scale[oct];
+    if (mp.dir == 1) { Q.min_level = oct; Q.max_level = -1; }
+    else if (mp.dir == 2) { Q.min_level = 0; Q.max_level = oct; }
+    else { Q.min_level = oct - 1; Q.max_level = oct + 1; }
+    /* Frame::GetFeaturesInArea (src/Frame.cc:446-462) */
+    Q.cx0 = max(0, (int)floorf((Q.u - min_x - Q.radius) * winv));
+    Q.cx1 = min(MT_COLS - 1, (int)ceilf((Q.u - min_x + Q.radius) * winv));
+    Q.cy0 = max(0, (int)floorf((Q.v - min_y - Q.radius) * hinv));
+    Q.cy1 = min(MT_ROWS - 1, (int)ceilf((Q.v - min_y + Q.radius) * hinv));
+    Q.ok = Q.ok && Q.cx0 < MT_COLS && Q.cx1 >= 0 && Q.cy0 < MT_ROWS && Q.cy1 >= 0;
+    Q.check_levels = (Q.min_level > 0) || (Q.max_level >= 0);
+    Q.ur = fmaf(-mp.mbf, invzc, Q.u);
+    return Q;
+}
+
+/* the filters of GetFeaturesInArea (:480-495) and of the candidate loop that do not depend on earlier
+ * queries (:1587-1595), then the distance; -1 = rejected */
+__device__ __forceinline__ int mt_candidate(const MtQuery &Q, int i2, const BorbKpRec *__restrict__ kp,
+                                            const float2 *__restrict__ un_xy, const float *__restrict__ u_right,
+                                            const uint8_t *__restrict__ desc, const uint4 d0, const uint4 d1)
+{
+    const int o2 = kp[i2].octave;
+    if (Q.check_levels && (o2 < Q.min_level || (Q.max_level >= 0 && o2 > Q.max_level))) return -1;
+    const float2 p = un_xy[i2];
+    if (!(fabsf(p.x - Q.u) < Q.radius && fabsf(p.y - Q.v) < Q.radius)) return -1;
+    if (u_right) {
+        const float ur2 = u_right[i2];
+        if (ur2 > 0 && fabsf(Q.ur - ur2) > Q.radius) return -1;
+    }
+    return mt_hamming(d0, d1, reinterpret_cast<const uint4 *>(desc) + 2 * i2);
+}
+
+/* last frame: xyz [3n], octave [n], desc [n] x 32 B (16-byte aligned), flags [n] (bit 0 map point,
+ * bit 1 Observations() > 0, bit 2 outlier).  Out: cache [n_last][MT_K] keys (distance << 16 | list
+ * position q, ascending; MT_NOKEY = none), more [n_last] = the query had more than MT_K candidates. */
+__global__ void __launch_bounds__(MT_CAND_NT)
+k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
+                   const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
+                   const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
+                   const float *__restrict__ bounds, const float *__restrict__ u_right,
+                   const float *__restrict__ l_xyz, const int *__restrict__ l_octave,
+                   const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
+                   uint32_t *__restrict__ cache, uint8_t *__restrict__ more)
+{
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (MT_CAND_NT / 32) + (threadIdx.x >> 5);
+    if (i >= mp.n_last) return; /* whole warp */
+    uint32_t T[MT_K];
+#pragma unroll
+    for (int k = 0; k < MT_K; ++k) T[k] = MT_NOKEY;
+    int cnt = 0;
+    const uint32_t fl = l_flags[i];
+    if ((fl & 1u) && !(fl & 4u)) {
+        const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+        const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
+        const MtQuery Q = mt_query(mp, l_xyz, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+        if (Q.ok) {
+            const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
+            for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
+                const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
+                for (int qb = q0; qb < q1; qb += 32) {
+                    const int q = qb + lane;
+                    uint32_t key = MT_NOKEY;
+                    if (q < q1) {
+                        const int d = mt_candidate(Q, cell_idx[q], kp, un_xy, u_right, desc, d0, d1);
+                        if (d >= 0) key = ((uint32_t)d << 16) | (uint32_t)q;
+                    }
+                    cnt += __popc(__ballot_sync(0xffffffffu, key != MT_NOKEY));
+                    while (true) { /* move this chunk's keys that beat the cached worst into the sorted cache */
+                        const uint32_t m = __reduce_min_sync(0xffffffffu, key);
+                        if (m >= T[MT_K - 1]) break;
+                        if (key == m) key = MT_NOKEY;
+                        uint32_t carry = m;
+#pragma unroll
+                        for (int k = 0; k < MT_K; ++k) {
+                            const uint32_t lo = min(T[k], carry);
+                            carry = max(T[k], carry);
+                            T[k] = lo;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    if (lane < MT_K) {
+        uint32_t v = T[0];
+#pragma unroll
+        for (int k = 1; k < MT_K; ++k) if (lane == k) v = T[k];
+        cache[(size_t)i * MT_K + lane] = v;
+    }
+    if (lane == 0) more[i] = cnt > MT_K;
+}
+
+/* Scratch: choice [n_last], taker [2][kp_total].  Out: match [kp_total] = index of the last-frame map point
+ * per current keypoint or -1; nm[0] = nmatches, nm[1] = rounds taken, nm[2] = rescans. */
+__global__ void __launch_bounds__(MT_NT, 1)
+k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
+                const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
+                const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
+                const float *__restrict__ bounds, const int *__restrict__ n_cur_p,
+                const float *__restrict__ u_right, const float *__restrict__ l_xyz,
+                const float *__restrict__ l_angle, const int *__restrict__ l_octave,
+                const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
+                const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more,
+                int *__restrict__ choice, int *__restrict__ taker, int kp_total, int *__restrict__ match,
+                int *__restrict__ nm)
+{
+    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans;
     const int tid = threadIdx.x;
     const int n_cur = min(*n_cur_p, kp_total), n_last = mp.n_last;
     const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
     const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
 
-    if (tid == 0) { /* twc = -Rcw^T tcw; tlc = Rlw twc + tlw; only its z decides the search direction (:1515-1526) */
-        float twc[3];
-        const float tcw[3] = {mp.Tc[3], mp.Tc[7], mp.Tc[11]};
-#pragma unroll
-        for (int y = 0; y < 3; ++y) {
-            float s = 0.f;
-            s += (-mp.Tc[y]) * tcw[0];
-            s += (-mp.Tc[4 + y]) * tcw[1];
-            s += (-mp.Tc[8 + y]) * tcw[2];
-            twc[y] = s;
-        }
-        const float tlc_z = mt_dot3(mp.Tl + 8, twc) + mp.Tl[11];
-        const bool fwd = tlc_z > mp.mb && !mp.mono, bwd = -tlc_z > mp.mb && !mp.mono;
-        s_dir = fwd ? 1 : bwd ? 2 : 0;
-        s_nm = 0;
-    }
+    if (tid == 0) { s_nm = 0; s_rescans = 0; }
     if (tid < MT_HISTO) s_hist[tid] = 0;
     for (int i = tid; i < n_last; i += MT_NT) choice[i] = -1;
     for (int c = tid; c < kp_total; c += MT_NT) { taker[c] = 0x7fffffff; match[c] = -1; }
     __syncthreads();
-    const int dir = s_dir;
 
     int round = 0;
     for (;; ++round) {
@@ -127,54 +233,34 @@ k_search_by_projection(const __grid_constant__ MatchParams mp, const BorbKpRec *
         if (tid == 0) s_changed = 0;
         __syncthreads();
         for (int i = tid; i < n_last; i += MT_NT) {
-            const uint32_t fl = l_flags[i];
-            int best = 256, best_idx = -1;
-            if ((fl & 1u) && !(fl & 4u)) {
-                const float X[3] = {l_xyz[3 * i], l_xyz[3 * i + 1], l_xyz[3 * i + 2]};
-                const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7],
-                            zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
-                const float invzc = 1.0f / zc;
-                const float u = fmaf(mp.fx * xc, invzc, mp.cx), v = fmaf(mp.fy * yc, invzc, mp.cy);
-                bool ok = !(invzc < 0) && !(u < min_x || u > max_x) && !(v < min_y || v > max_y);
-                const int oct = l_octave[i];
-                const float radius = mp.th * mp.scale[oct];
-                int min_level, max_level;
-                if (dir == 1) { min_level = oct; max_level = -1; }
-                else if (dir == 2) { min_level = 0; max_level = oct; }
-                else { min_level = oct - 1; max_level = oct + 1; }
-                /* Frame::GetFeaturesInArea */
-                const int cx0 = max(0, (int)floorf((u - min_x - radius) * winv));
-                const int cx1 = min(MT_COLS - 1, (int)ceilf((u - min_x + radius) * winv));
-                const int cy0 = max(0, (int)floorf((v - min_y - radius) * hinv));
-                const int cy1 = min(MT_ROWS - 1, (int)ceilf((v - min_y + radius) * hinv));
-                ok = ok && cx0 < MT_COLS && cx1 >= 0 && cy0 < MT_ROWS && cy1 >= 0;
-                if (ok) {
-                    const bool check_levels = (min_level > 0) || (max_level >= 0);
-                    const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
-                    const float ur = fmaf(-mp.mbf, invzc, u);
-                    for (int ix = cx0; ix <= cx1; ++ix) {
-                        /* the cells (ix, cy0..cy1) are consecutive in the cell-major lists */
-                        const int q0 = cell_start[ix * MT_ROWS + cy0], q1 = cell_start[ix * MT_ROWS + cy1 + 1];
-                        for (int q = q0; q < q1; ++q) {
-                            const int i2 = cell_idx[q];
-                            const int o2 = kp[i2].octave;
-                            if (check_levels && (o2 < min_level || (max_level >= 0 && o2 > max_level))) continue;
-                            const float2 p = un_xy[i2];
-                            if (!(fabsf(p.x - u) < radius && fabsf(p.y - v) < radius)) continue;
-                            if (tk_prev[i2] < i) continue; /* holds a map point with observations (:1583-1585) */
-                            if (u_right) {
-                                const float ur2 = u_right[i2];
-                                if (ur2 > 0 && fabsf(ur - ur2) > radius) continue;
-                            }
-                            const int d = mt_hamming(d0, d1, reinterpret_cast<const uint4 *>(desc) + 2 * i2);
-                            if (d < best) { best = d; best_idx = i2; }
-                        }
+            int ch = -1;
+            bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
+#pragma unroll
+            for (int k = 0; k < MT_K; ++k) {
+                if (!all_held) continue;
+                const uint32_t key = cache[(size_t)i * MT_K + k];
+                if (key == MT_NOKEY || (key >> 16) > MT_TH_HIGH) { all_held = false; continue; }
+                const int c = cell_idx[key & 0xffffu];
+                if (tk_prev[c] >= i) { ch = c; all_held = false; }
+            }
+            if (all_held && more[i]) { /* rare: walk the cells again, now with the holders known */
+                atomicAdd(&s_rescans, 1);
+                const MtQuery Q = mt_query(mp, l_xyz, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+                const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
+                int best = 256, best_idx = -1;
+                for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
+                    const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
+                    for (int q = q0; q < q1; ++q) {
+                        const int i2 = cell_idx[q];
+                        if (tk_prev[i2] < i) continue;
+                        const int d = mt_candidate(Q, i2, kp, un_xy, u_right, desc, d0, d1);
+                        if (d >= 0 && d < best) { best = d; best_idx = i2; }
                     }
                 }
+                ch = best <= MT_TH_HIGH ? best_idx : -1;
             }
-            const int ch = best <= MT_TH_HIGH ? best_idx : -1;
             if (ch != choice[i]) { choice[i] = ch; s_changed = 1; }
-            if (ch >= 0 && (fl & 2u)) atomicMin(&tk_new[ch], i);
+            if (ch >= 0 && (l_flags[i] & 2u)) atomicMin(&tk_new[ch], i);
         }
         __syncthreads();
         const int changed = s_changed;
@@ -215,7 +301,7 @@ k_search_by_projection(const __grid_constant__ MatchParams mp, const BorbKpRec *
         }
         __syncthreads();
     }
-    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; }
+    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; }
 }
 
 #endif

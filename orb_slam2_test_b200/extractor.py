@@ -402,7 +402,10 @@ class ORBextractor:
         return out[:n.value].copy(), nm.value
 
     def match_rounds(self) -> int:
-        return self._lib.borb_match_rounds(self._h)
+        return self._lib.borb_match_rounds(self._h) & 0xff
+
+    def match_rescans(self) -> int:
+        return self._lib.borb_match_rounds(self._h) >> 8
 
     def level_size(self, level: int):
         c, r = C.c_int(), C.c_int()

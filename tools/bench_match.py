@@ -17,4 +17,4 @@ for th in (7.0,15.0,30.0):
     tc=[]
     for _ in range(20):
         t0=time.perf_counter(); w,wnm=pyoracle.search_by_projection(cur,last,cam,bounds,scale,th); tc.append((time.perf_counter()-t0)*1e6)
-    print('th',th,'gpu call p50 us',np.median(ts),'rounds',L.match_rounds(),'nm',nm,'cpu oracle p50 us',np.median(tc), 'equal', np.array_equal(g,w))
+    print('th',th,'gpu call p50 us',np.median(ts),'rounds',L.match_rounds(),'rescans',L.match_rescans(),'nm',nm,'cpu oracle p50 us',np.median(tc), 'equal', np.array_equal(g,w))
