@@ -171,4 +171,29 @@ void ORBextractor::ComputeStereoMatches(ORBextractor &right, float mbf, float mb
     mvDepth.assign(z, z + n);
 }
 
+int ORBextractor::SearchByProjection(const cv::Mat &TcwCur, const cv::Mat &TcwLast, int nLast, const float *worldPos,
+                                     const unsigned char *mpDescriptors, const unsigned char *flags, const int *octave,
+                                     const float *angle, float mbf, float mb, float th, bool bMono,
+                                     bool checkOrientation, bool useStereo, std::vector<int> &vnMatches)
+{
+    assert(TcwCur.type() == CV_32F && TcwCur.rows >= 3 && TcwCur.cols == 4 && TcwLast.type() == CV_32F);
+    float tc[12], tl[12];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) {
+            tc[4 * r + c] = TcwCur.at<float>(r, c);
+            tl[4 * r + c] = TcwLast.at<float>(r, c);
+        }
+    borb_last_frame last;
+    last.n = nLast; last.xyz = worldPos; last.desc = mpDescriptors; last.flags = flags;
+    last.octave = octave; last.angle = angle; last.Tcw = tl;
+    vnMatches.assign((size_t)borb_max_keypoints(handle), -1);
+    int n = 0, nmatches = 0;
+    const unsigned f = (bMono ? BORB_MATCH_MONO : 0u) | (checkOrientation ? 0u : BORB_MATCH_NO_ORIENTATION) |
+                       (useStereo ? BORB_MATCH_USE_STEREO : 0u);
+    check(borb_search_by_projection(handle, 0, &last, tc, mbf, mb, th, f, vnMatches.data(), &n, &nmatches),
+          "search by projection");
+    vnMatches.resize((size_t)n);
+    return nmatches;
+}
+
 } // namespace ORB_SLAM2

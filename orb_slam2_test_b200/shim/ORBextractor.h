@@ -105,6 +105,17 @@ public:
     // have joined (src/Frame.cc:110-113); neither pyramid has to be downloaded for it.
     void ComputeStereoMatches(ORBextractor &right, float mbf, float mb, std::vector<float> &mvuRight,
                               std::vector<float> &mvDepth);
+    // ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono) (reference
+    // src/ORBmatcher.cc:1503-1668) on the device, for *this as CurrentFrame.mpORBextractorLeft after
+    // its operator() call (SetCamera on; useStereo: ComputeStereoMatches has run).  The last frame
+    // arrives as the flat arrays include/borb.h describes (entry i = LastFrame keypoint i: flags bit 0
+    // map point present, bit 1 Observations() > 0, bit 2 outlier; GetWorldPos(), GetDescriptor(),
+    // mvKeys[i].octave, mvKeysUn[i].angle); TcwCur / TcwLast are the 4x4 CV_32F mTcw.
+    // vnMatches[i2] = i of the map point CurrentFrame.mvpMapPoints[i2] receives, or -1; returns nmatches.
+    int SearchByProjection(const cv::Mat &TcwCur, const cv::Mat &TcwLast, int nLast, const float *worldPos,
+                           const unsigned char *mpDescriptors, const unsigned char *flags, const int *octave,
+                           const float *angle, float mbf, float mb, float th, bool bMono, bool checkOrientation,
+                           bool useStereo, std::vector<int> &vnMatches);
 
 protected:
     int nfeatures;

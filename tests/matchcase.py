@@ -95,10 +95,10 @@ def map_points(last: dict, Tcw_last: np.ndarray, K, rng: np.random.Generator, ob
 
 
 def make_case(seed=0, shape=synth.KITTI_SHAPE, K=KITTI_K, dist=(0.0, 0.0, 0.0, 0.0), bf=KITTI_BF, stereo=True,
-              dz=0.0, nf=2000, obs_rate=0.7, outlier_rate=0.05, copies=1, frame=0):
+              dz=0.0, nf=2000, obs_rate=0.7, outlier_rate=0.05, copies=1, frame=0, mb=None):
     """-> (cur, last, cam, bounds, scale): dicts as oracle.pyoracle.search_by_projection takes them."""
     rng = np.random.default_rng(1000 + seed)
-    mb = bf / K[0]
+    mb = bf / K[0] if mb is None else mb
     imgs = {(f, e): synth.make_frame(shape, seed=seed, frame=frame + f, eye=e) for f in (0, 1) for e in ((0, 1) if stereo else (0,))}
     last = oracle_frame(imgs[(0, 0)], imgs.get((0, 1)), K, dist, bf, mb, nf)
     cur = oracle_frame(imgs[(1, 0)], imgs.get((1, 1)), K, dist, bf, mb, nf)

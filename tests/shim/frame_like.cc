@@ -139,8 +139,59 @@ static int pre_mode(char **argv)
     return 0;
 }
 
+/* `match` mode: the tracking thread's frame-to-frame matcher through the shim.  argv: match left right cols
+ * rows nfeatures last.bin out.bin; last.bin = int32 n, float K[4], float mbf, mb, th, int32 mono, float
+ * TcwCur[16], TcwLast[16], then xyz[3n], desc[32n], flags[n], octave[n], angle[n] (the arrays of
+ * include/borb.h: borb_last_frame).  The current frame is a stereo frame built the way Frame's constructor
+ * does (extraction on two threads, device stereo association), then
+ * ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (reference src/ORBmatcher.cc:1503-1668)
+ * runs on the device.  out.bin = int32 nmatches, n_cur, then n_cur int32 matches. */
+static int match_mode(char **argv)
+{
+    const int cols = atoi(argv[4]), rows = atoi(argv[5]), nFeatures = atoi(argv[6]);
+    vector<unsigned char> l = slurp(argv[2], (size_t)cols * rows), r = slurp(argv[3], (size_t)cols * rows);
+    cv::Mat imLeft(rows, cols, CV_8UC1, l.data()), imRight(rows, cols, CV_8UC1, r.data());
+    FILE *in = fopen(argv[7], "rb");
+    if (!in) return 2;
+    int n = 0, mono = 0;
+    float K4[4], mbf, mb, th, tc[16], tl[16];
+    if (fread(&n, 4, 1, in) != 1 || fread(K4, 4, 4, in) != 4 || fread(&mbf, 4, 1, in) != 1 || fread(&mb, 4, 1, in) != 1 ||
+        fread(&th, 4, 1, in) != 1 || fread(&mono, 4, 1, in) != 1 || fread(tc, 4, 16, in) != 16 || fread(tl, 4, 16, in) != 16)
+        return 2;
+    vector<float> xyz((size_t)3 * n), angle((size_t)n);
+    vector<unsigned char> desc((size_t)32 * n), flags((size_t)n);
+    vector<int> octave((size_t)n);
+    if (fread(xyz.data(), 4, xyz.size(), in) != xyz.size() || fread(desc.data(), 1, desc.size(), in) != desc.size() ||
+        fread(flags.data(), 1, flags.size(), in) != flags.size() || fread(octave.data(), 4, octave.size(), in) != octave.size() ||
+        fread(angle.data(), 4, angle.size(), in) != angle.size())
+        return 2;
+    fclose(in);
+    cv::Mat K(3, 3, CV_32F), DistCoef(4, 1, CV_32F), TcwCur(4, 4, CV_32F), TcwLast(4, 4, CV_32F);
+    memset(K.data, 0, 36);
+    memset(DistCoef.data, 0, 16);
+    K.at<float>(0, 0) = K4[0]; K.at<float>(1, 1) = K4[1]; K.at<float>(0, 2) = K4[2]; K.at<float>(1, 2) = K4[3]; K.at<float>(2, 2) = 1.f;
+    memcpy(TcwCur.data, tc, 64);
+    memcpy(TcwLast.data, tl, 64);
+    ORBextractor left(nFeatures, 1.2f, 8, 20, 7), right(nFeatures, 1.2f, 8, 20, 7);
+    left.SetCamera(K, DistCoef);
+    FrameLike fr(imLeft, imRight, &left, &right); /* KITTI mbf / mb inside, as the other mode */
+    vector<int> vnMatches;
+    const int nmatches = left.SearchByProjection(TcwCur, TcwLast, n, xyz.data(), desc.data(), flags.data(), octave.data(),
+                                                 angle.data(), mbf, mb, th, mono != 0, true, true, vnMatches);
+    FILE *f = fopen(argv[8], "wb");
+    if (!f) return 2;
+    int nc = (int)vnMatches.size();
+    fwrite(&nmatches, 4, 1, f);
+    fwrite(&nc, 4, 1, f);
+    fwrite(vnMatches.data(), 4, vnMatches.size(), f);
+    fclose(f);
+    printf("frame_like match ok\n");
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
+    if (argc == 9 && !strcmp(argv[1], "match")) return match_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "pre")) return pre_mode(argv);
     if (argc != 7) { fprintf(stderr, "usage: %s left right cols rows nfeatures out\n", argv[0]); return 2; }
     const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[5]);

@@ -164,3 +164,34 @@ def test_prestep_through_the_shim(tmp_path, oracle_built):
     ok, od = oracle_built.Oracle(1200, 1.2, 8, 20, 7).extract(gray)
     assert k.tobytes() == ok.tobytes() and d.tobytes() == od.tobytes()
     assert lv[0][2] == _level_checksum(gray)
+
+
+@pytest.mark.gpu
+def test_frame_to_frame_matcher_through_the_shim(tmp_path, oracle_built):
+    """ORBextractor::SearchByProjection (shim) = ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th,
+    bMono) restated (oracle/match_oracle.cpp, pinned to the reference's ORBmatcher.cc): the Frame-like caller
+    builds the current stereo frame on the device and matches the last frame's map points against it."""
+    import matchcase
+    _build()
+    bf = np.float32(386.1448)
+    mb = bf / np.float32(718.856)  # as tests/shim/frame_like.cc computes it
+    cur, last, cam, bounds, scale = matchcase.make_case(seed=33, bf=float(bf), mb=float(mb), dz=1.0)
+    shape = synth.KITTI_SHAPE
+    (tmp_path / "l.raw").write_bytes(synth.make_frame(shape, seed=33, frame=1, eye=0).tobytes())
+    (tmp_path / "r.raw").write_bytes(synth.make_frame(shape, seed=33, frame=1, eye=1).tobytes())
+    th = 7.0
+    n = len(last["kps"])
+    T4 = lambda T: np.vstack([T, [0, 0, 0, 1]]).astype("<f4")
+    blob = struct.pack("<i4ffffi", n, *matchcase.KITTI_K, float(bf), float(mb), th, 0)
+    blob += T4(cur["Tcw"]).tobytes() + T4(last["Tcw"]).tobytes()
+    blob += last["mp_xyz"].astype("<f4").tobytes() + last["mp_desc"].tobytes() + last["mp_flags"].tobytes()
+    blob += last["kps"]["octave"].astype("<i4").tobytes() + last["kps"]["angle"].astype("<f4").tobytes()
+    (tmp_path / "last.bin").write_bytes(blob)
+    r = subprocess.run([str(EXE), "match", str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(shape[1]), str(shape[0]),
+                        "2000", str(tmp_path / "last.bin"), str(tmp_path / "m.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = (tmp_path / "m.bin").read_bytes()
+    nm, nc = struct.unpack_from("<ii", buf, 0)
+    got = np.frombuffer(buf, "<i4", nc, 8)
+    want, wnm = oracle_built.search_by_projection(cur, last, cam, bounds, scale, th)
+    assert nc == len(want) and np.array_equal(got, want) and nm == wnm and nm > 300
