@@ -379,6 +379,67 @@ def poststep_section(ORBextractor, synth, local):
     return out
 
 
+def matcher_section(ORBextractor, synth, local):
+    """SURVEY.md 8(f)-4, first consumer: the tracking thread's frame-to-frame matcher
+    ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) on the device
+    (borb_search_by_projection).  Scenario: two consecutive KITTI-shape stereo frames extracted and
+    stereo-matched on the GPU; the last frame's stereo depths become map points (tests/matchcase.py);
+    the current frame's keypoints, descriptors, grid and mvuRight stay on the device.  The timed call is
+    the whole host call (upload of the last frame's 53 B per keypoint, two kernels, download of the matches)."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import matchcase
+    K, BF = matchcase.KITTI_K, matchcase.KITTI_BF
+    mb = BF / K[0]
+
+    def gpu_frame(frame):
+        l = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        r = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        l.set_camera(K, (0.0, 0.0, 0.0, 0.0))
+        l(synth.make_frame((ROWS, COLS), seed=71, frame=frame, eye=0))
+        r(synth.make_frame((ROWS, COLS), seed=71, frame=frame, eye=1))
+        l.stereo_match(r, BF, mb)
+        kps, desc = l.result(0)
+        u, z, _ = l.stereo_result(0)
+        un, start, idx, bounds = l.frame_grid(0)
+        return l, r, {"kps": kps, "desc": desc, "un_xy": un, "u_right": u, "depth": z, "cell_start": start,
+                      "cell_idx": idx, "bounds": bounds}
+    _, _, last = gpu_frame(0)
+    ext, right, cur = gpu_frame(1)
+    T_last = matchcase.pose(0.01, -0.02, 0.005, (0.3, -0.1, 0.2))
+    cur["Tcw"] = matchcase.compose(matchcase.pose(rx=1.0 / K[1], ry=-3.0 / K[0]), T_last)
+    last = matchcase.map_points(last, T_last, K, np.random.default_rng(71))
+    lf = dict(last)
+    lf["octave"], lf["angle"] = last["kps"]["octave"], last["kps"]["angle"]
+    out = {"reference": "src/ORBmatcher.cc:1503-1668 (+ Frame::GetFeaturesInArea src/Frame.cc:421-508)",
+           "parity": "identical mvpMapPoints and nmatches against oracle/match_oracle.cpp, which is pinned to the reference's own ORBmatcher.cc (oracle/_ref/librefmatch.so)",
+           "config": "KITTI stereo frame pair, 2000 kp, %d map points in the last frame" % int((last["mp_flags"] & 1).sum())}
+    scale = ext.GetScaleFactors()
+    cam = np.array([K[0], K[1], K[2], K[3], BF, mb], np.float32)
+    for th in (7.0, 15.0):
+        for _ in range(10):
+            m, nm = ext.search_by_projection(lf, cur["Tcw"], BF, mb, th, use_stereo=True)
+        ts = []
+        for _ in range(100):
+            t1 = time.perf_counter()
+            m, nm = ext.search_by_projection(lf, cur["Tcw"], BF, mb, th, use_stereo=True)
+            ts.append((time.perf_counter() - t1) * 1e6)
+        e = {"call_p50_us": float(np.percentile(ts, 50)), "nmatches": nm, "rounds": ext.match_rounds(),
+             "rescans": ext.match_rescans()}
+        try:
+            from oracle import pyoracle
+            tc = []
+            for _ in range(20):
+                t1 = time.perf_counter()
+                w, wnm = pyoracle.search_by_projection(cur, last, cam, cur["bounds"], scale, th)
+                tc.append((time.perf_counter() - t1) * 1e6)
+            e["cpu_p50_us_one_core"] = float(np.percentile(tc, 50))
+            e["parity_check"] = "identical" if (np.array_equal(m, w) and nm == wnm) else "MISMATCH"
+        except Exception as ex:
+            e["parity_check"] = f"unavailable ({type(ex).__name__})"
+        out["th_%d" % int(th)] = e
+    return out
+
+
 def stereo_section(ORBextractor, synth, local, two, dev):
     """SURVEY.md 8(f)-1: Frame::ComputeStereoMatches on the device (borb_stereo_match).  Reported
     beside the headline, not part of `value`: (1) a stereo pair through the host ABI with the match on
@@ -586,7 +647,7 @@ def run_ours(args, rank, world, local):
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
-    stereo = prestep = poststep = None
+    stereo = prestep = poststep = matcher = None
     if rank == 0:
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
@@ -628,6 +689,7 @@ def run_ours(args, rank, world, local):
         stereo = stereo_section(ORBextractor, synth, local, two, dev)
         prestep = prestep_section(ORBextractor, synth, local, measured_peak()[0])
         poststep = poststep_section(ORBextractor, synth, local)
+        matcher = matcher_section(ORBextractor, synth, local)
 
     if rank != 0:
         return
@@ -672,6 +734,7 @@ def run_ours(args, rank, world, local):
         "stereo": stereo,
         "prestep": prestep,
         "poststep": poststep,
+        "matcher": matcher,
         "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,
     }

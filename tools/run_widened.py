@@ -1,5 +1,6 @@
 """One pass over every kernel of the widened rows for ncu launch lists:
-K0 colour->gray and rectification, the extraction chain, K8 undistort+grid, S0/S1/S2 stereo match.
+K0 colour->gray and rectification, the extraction chain, K8 undistort+grid, S0/S1/S2 stereo match,
+M1a/M1b frame-to-frame matcher.
 usage: python tools/run_widened.py [pairs]   (default 1 stereo pair per call; e.g. 64 for batches)"""
 import sys
 from pathlib import Path
@@ -44,3 +45,26 @@ for _ in range(3):
     KR.extract_batch(kr)
     KL.stereo_match(KR, BF, BF / FX)
 print("kitti pairs:", n, "matched", [KL.stereo_result(f)[2] for f in range(min(n, 4))])
+# the frame-to-frame matcher (M1a / M1b) on a KITTI stereo frame pair: last frame's stereo depths as map points
+sys.path.insert(0, str(Path(__file__).resolve().parents[1] / "tests"))
+import matchcase  # noqa: E402
+
+K = matchcase.KITTI_K
+ML = ORBextractor(2000, 1.2, 8, 20, 7)
+MR = ORBextractor(2000, 1.2, 8, 20, 7)
+ML.set_camera(K, (0.0, 0.0, 0.0, 0.0))
+frames = {}
+for f in (0, 1):
+    ML(synth.make_frame(synth.KITTI_SHAPE, seed=71, frame=f, eye=0))
+    MR(synth.make_frame(synth.KITTI_SHAPE, seed=71, frame=f, eye=1))
+    ML.stereo_match(MR, BF, BF / FX)
+    kps, desc = ML.result(0)
+    u, z, _ = ML.stereo_result(0)
+    frames[f] = {"kps": kps, "desc": desc, "un_xy": ML.frame_grid(0)[0], "depth": z}
+T_last = matchcase.pose(0.01, -0.02, 0.005, (0.3, -0.1, 0.2))
+T_cur = matchcase.compose(matchcase.pose(rx=1.0 / K[1], ry=-3.0 / K[0]), T_last)
+last = matchcase.map_points(frames[0], T_last, K, np.random.default_rng(71))
+last["octave"], last["angle"] = last["kps"]["octave"], last["kps"]["angle"]
+for th in (7.0, 15.0, 7.0):
+    m, nm = ML.search_by_projection(last, T_cur, BF, BF / FX, th, use_stereo=True)
+print("matcher: nmatches", nm, "rounds", ML.match_rounds(), "rescans", ML.match_rescans())
