@@ -193,4 +193,80 @@ int mo_search_by_projection(const mo_frame *cur, const mo_frame *last, const flo
     return nmatches;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, const float th)
+ *     /root/reference/src/ORBmatcher.cc:59-154 -- the matcher of Tracking::SearchLocalPoints
+ *     (src/Tracking.cc:1055-1103), with RadiusByViewingCos (:156-162).
+ * Map point iMP arrives as what Frame::isInFrustum left in it: proj[4 iMP ..] = mTrackProjX,
+ * mTrackProjY, mTrackProjXR, mTrackViewCos; level = mnTrackScaleLevel; flags bit 0 = mbTrackInView
+ * && !isBad(), bit 1 = Observations() > 0.  occupied[i2] = 2 where F.mvpMapPoints[i2] holds a point
+ * with observations on entry (such slots are never touched, :92-94), anything else is free.
+ * out_match[i2] = iMP assigned by this call, -1 where the slot is left as it was.
+ * Float forms: r = 2.5 / 4.0 by (double)viewCos > 0.998, r *= th if th != 1.0, radius = r * scale[level]
+ * (two single multiplications); the ratio test compares (float)bestDist with mfNNratio * (float)bestDist2.
+ */
+int mo_search_local_points(const mo_frame *cur, const float *bounds, const float *scale, int nlevels, int n_mp,
+                           const float *proj, const uint8_t *mp_desc, const uint8_t *mp_flags, const int32_t *level,
+                           const uint8_t *occupied, float th, float nnratio, int32_t *out_match)
+{
+    (void)nlevels;
+    const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+    const float winv = (float)MO_COLS / (max_x - min_x), hinv = (float)MO_ROWS / (max_y - min_y);
+    const mo_kp *ck = reinterpret_cast<const mo_kp *>(cur->kps);
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    if (cur->grid_count)
+        for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + cur->grid_count[c];
+    for (int i = 0; i < cur->n; ++i) out_match[i] = -1;
+    const bool b_factor = th != 1.0;
+    int nmatches = 0;
+    for (int i = 0; i < n_mp; ++i) {
+        if (!(mp_flags[i] & 1)) continue;
+        const int lvl = level[i];
+        float r = (double)proj[4 * i + 3] > 0.998 ? 2.5f : 4.0f;
+        if (b_factor) r *= th;
+        const float radius = r * scale[lvl];
+        const float u = proj[4 * i], v = proj[4 * i + 1], xr = proj[4 * i + 2];
+        const int min_level = lvl - 1, max_level = lvl;
+        const int cx0 = std::max(0, (int)std::floor((u - min_x - radius) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((u - min_x + radius) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((v - min_y - radius) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((v - min_y + radius) * hinv));
+        if (cy1 < 0) continue;
+        const bool check_levels = (min_level > 0) || (max_level >= 0);
+        int best = 256, best_level = -1, best2 = 256, best_level2 = -1, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int i2 = cur->grid_idx[q];
+                    if (check_levels) {
+                        if (ck[i2].octave < min_level) continue;
+                        if (max_level >= 0 && ck[i2].octave > max_level) continue;
+                    }
+                    const float dx = cur->un_xy[2 * i2] - u, dy = cur->un_xy[2 * i2 + 1] - v;
+                    if (!(std::fabs(dx) < radius && std::fabs(dy) < radius)) continue;
+                    if (occupied[i2] == 2) continue;
+                    if (out_match[i2] >= 0 && (mp_flags[out_match[i2]] & 2)) continue;
+                    const float ur2 = cur->u_right ? cur->u_right[i2] : -1.f;
+                    if (ur2 > 0) {
+                        const float er = std::fabs(xr - ur2);
+                        if (er > radius) continue;
+                    }
+                    const int d = mo_hamming256(mp_desc + (size_t)i * 32, cur->desc + (size_t)i2 * 32);
+                    if (d < best) { best2 = best; best = d; best_level2 = best_level; best_level = ck[i2].octave; best_idx = i2; }
+                    else if (d < best2) { best_level2 = ck[i2].octave; best2 = d; }
+                }
+            }
+        if (best <= MO_TH_HIGH) {
+            if (best_level == best_level2 && (float)best > nnratio * (float)best2) continue;
+            out_match[best_idx] = i;
+            ++nmatches;
+        }
+    }
+    return nmatches;
+}
+
 } // extern "C"

@@ -116,4 +116,66 @@ int refmatch_search_by_projection(const refmatch_frame *cur, const refmatch_fram
     return nm;
 }
 
+/* ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:59-154).
+ * proj[4i..] = mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos; level[i] = mnTrackScaleLevel; mp_flags bit 0 =
+ * mbTrackInView && !isBad(), bit 1 = Observations() > 0.  occupied[i2]: 0 = F.mvpMapPoints[i2] is NULL on entry, 1 =
+ * it holds a point without observations, 2 = with.  out_match[i2] = index of the map point this call put there, -1
+ * where the slot still holds what it held. */
+int refmatch_search_local_points(const refmatch_frame *cur, const float *bounds, const float *scale, int nlevels, int n_mp,
+                                 const float *proj, const uint8_t *mp_desc, const uint8_t *mp_flags, const int32_t *level,
+                                 const uint8_t *occupied, float th, float nnratio, int32_t *out_match)
+{
+    Frame::mnMinX = bounds[0]; Frame::mnMaxX = bounds[1]; Frame::mnMinY = bounds[2]; Frame::mnMaxY = bounds[3];
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);
+    Frame::mbInitialComputations = false;
+    Frame f;
+    const refmatch_frame &r = *cur;
+    f.N = r.n;
+    f.mvKeys.resize(r.n);
+    if (r.n) std::memcpy(f.mvKeys.data(), r.kps, (size_t)r.n * 28);
+    f.mvKeysUn = f.mvKeys;
+    for (int i = 0; i < r.n; ++i) { f.mvKeysUn[i].pt.x = r.un_xy[2 * i]; f.mvKeysUn[i].pt.y = r.un_xy[2 * i + 1]; }
+    f.mDescriptors = cv::Mat(r.n, 32, CV_8UC1);
+    for (int i = 0; i < r.n; ++i) std::memcpy(f.mDescriptors.ptr(i), r.desc + (size_t)i * 32, 32);
+    f.mvuRight.assign(r.n, -1.f);
+    if (r.u_right) for (int i = 0; i < r.n; ++i) f.mvuRight[i] = r.u_right[i];
+    f.mnScaleLevels = nlevels;
+    f.mvScaleFactors.assign(scale, scale + nlevels);
+    int k = 0;
+    for (int i = 0; i < FRAME_GRID_COLS; ++i)
+        for (int j = 0; j < FRAME_GRID_ROWS; ++j) {
+            const int c = r.grid_count[i * FRAME_GRID_ROWS + j];
+            f.mGrid[i][j].assign(r.grid_idx + k, r.grid_idx + k + c);
+            k += c;
+        }
+    MapPoint held[2]; /* what occupied slots point at on entry */
+    held[0].nObs = 0;
+    held[1].nObs = 1;
+    f.mvpMapPoints.assign(r.n, static_cast<MapPoint *>(NULL));
+    for (int i = 0; i < r.n; ++i)
+        if (occupied[i]) f.mvpMapPoints[i] = &held[occupied[i] == 2];
+    std::vector<MapPoint> mps(n_mp);
+    std::vector<MapPoint *> vp(n_mp);
+    for (int i = 0; i < n_mp; ++i) {
+        MapPoint &m = mps[i];
+        m.mbTrackInView = (mp_flags[i] & 1) != 0;
+        m.mbBad = false;
+        m.nObs = (mp_flags[i] & 2) ? 1 : 0;
+        m.mTrackProjX = proj[4 * i]; m.mTrackProjY = proj[4 * i + 1]; m.mTrackProjXR = proj[4 * i + 2];
+        m.mTrackViewCos = proj[4 * i + 3];
+        m.mnTrackScaleLevel = level[i];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1);
+        std::memcpy(m.mDescriptor.ptr(0), mp_desc + (size_t)i * 32, 32);
+        vp[i] = &m;
+    }
+    ORBmatcher matcher(nnratio, true);
+    const int nm = matcher.SearchByProjection(f, vp, th);
+    for (int i2 = 0; i2 < r.n; ++i2) {
+        MapPoint *p = f.mvpMapPoints[i2];
+        out_match[i2] = (p && p != &held[0] && p != &held[1]) ? (int32_t)(p - mps.data()) : -1;
+    }
+    return nm;
+}
+
 } // extern "C"

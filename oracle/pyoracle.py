@@ -254,6 +254,42 @@ def search_by_projection(cur, last, cam, bounds, scale, th, mono=False, check_or
     return _match_call(Oracle.load().mo_search_by_projection, cur, last, cam, bounds, scale, th, mono, check_ori)
 
 
+def _local_call(fn, cur: dict, bounds, scale, mps: dict, occupied, th: float, nnratio: float):
+    """Common marshalling for mo_search_local_points / refmatch_search_local_points.  mps: proj [n,4] f32
+    (mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos), desc [n,32] u8, flags [n] u8 (bit 0 in view and not
+    bad, bit 1 Observations() > 0), level [n] i32.  occupied [n_cur] u8 (2 = holds a point with observations).
+    -> (match [n_cur] i32: map point put there by this call or -1, nmatches)."""
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+
+    f = _MatchFrame()
+    f.n = len(cur["kps"])
+    f.kps = arr(cur["kps"], KP_DTYPE)
+    f.un_xy = arr(cur["un_xy"], np.float32)
+    f.desc = arr(cur["desc"], np.uint8)
+    f.u_right = arr(cur["u_right"], np.float32) if cur.get("u_right") is not None else None
+    f.grid_count = arr(np.diff(cur["cell_start"]), np.int32)
+    f.grid_idx = arr(cur["cell_idx"], np.int32)
+    f.Tcw = None
+    scale = np.ascontiguousarray(scale, np.float32)
+    out = np.full(max(f.n, 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_float, C.c_float, _vp]
+    nm = fn(C.addressof(f), arr(bounds, np.float32), scale.ctypes.data, len(scale), len(mps["flags"]), arr(mps["proj"], np.float32),
+            arr(mps["desc"], np.uint8), arr(mps["flags"], np.uint8), arr(mps["level"], np.int32), arr(occupied, np.uint8),
+            float(th), float(nnratio), out.ctypes.data)
+    return out[:f.n], int(nm)
+
+
+def search_local_points(cur, bounds, scale, mps, occupied, th=1.0, nnratio=0.8):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154) restated (oracle/match_oracle.cpp)."""
+    return _local_call(Oracle.load().mo_search_local_points, cur, bounds, scale, mps, occupied, th, nnratio)
+
+
 class RefMatcher:
     """The reference's own src/ORBmatcher.cc + src/Frame.cc (oracle/_ref/librefmatch.so)."""
 
@@ -268,6 +304,12 @@ class RefMatcher:
         if cls._lib is None:
             cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
         return _match_call(cls._lib.refmatch_search_by_projection, cur, last, cam, bounds, scale, th, mono, check_ori)
+
+    @classmethod
+    def search_local_points(cls, cur, bounds, scale, mps, occupied, th=1.0, nnratio=0.8):
+        if cls._lib is None:
+            cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
+        return _local_call(cls._lib.refmatch_search_local_points, cur, bounds, scale, mps, occupied, th, nnratio)
 
 
 def _cam(K, dist) -> np.ndarray:

@@ -110,3 +110,40 @@ def make_case(seed=0, shape=synth.KITTI_SHAPE, K=KITTI_K, dist=(0.0, 0.0, 0.0, 0
     cur["Tcw"] = T_cur
     cam = np.array([K[0], K[1], K[2], K[3], bf, mb], np.float32)
     return cur, last, cam, cur["bounds"], cur["scale"]
+
+
+def make_local_case(seed=0, copies=2, obs_rate=0.9, **kw):
+    """Scenario for ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154), the matcher of
+    Tracking::SearchLocalPoints: the current frame after the motion-model matcher has run (its matches occupy
+    slots), and a local map = the last frame's map points not matched yet plus jittered copies, projected with
+    the current pose the way Frame::isInFrustum leaves them (mTrackProjX/Y/XR, mTrackViewCos, mnTrackScaleLevel).
+    -> (cur, bounds, scale, mps, occupied)"""
+    from oracle import pyoracle
+    cur, last, cam, bounds, scale = make_case(seed=seed, **kw)
+    rng = np.random.default_rng(5000 + seed)
+    m, _ = pyoracle.search_by_projection(cur, last, cam, bounds, scale, 7.0 if kw.get("stereo", True) else 15.0,
+                                         mono=not kw.get("stereo", True))
+    occupied = np.zeros(len(m), np.uint8)
+    held = m >= 0
+    occupied[held] = np.where(last["mp_flags"][m[held]] & 2, 2, 1)
+    n = len(last["kps"])
+    matched = np.zeros(n, bool)
+    matched[m[held]] = True
+    xyz = np.concatenate([last["mp_xyz"]] + [last["mp_xyz"] + rng.normal(0, 0.03, last["mp_xyz"].shape).astype(np.float32)
+                                             for _ in range(copies - 1)]).astype(np.float64)
+    has = np.concatenate([(last["mp_flags"] & 1).astype(bool) & ~matched] + [(last["mp_flags"] & 1).astype(bool)] * (copies - 1))
+    desc = np.concatenate([last["mp_desc"]] * copies)
+    octv = np.concatenate([last["kps"]["octave"]] * copies)
+    T = cur["Tcw"].astype(np.float64)
+    Xc = xyz @ T[:, :3].T + T[:, 3]
+    z = np.where(np.abs(Xc[:, 2]) > 1e-6, Xc[:, 2], 1.0)
+    u = cam[0] * Xc[:, 0] / z + cam[2]
+    v = cam[1] * Xc[:, 1] / z + cam[3]
+    inside = (Xc[:, 2] > 0) & (u > bounds[0]) & (u < bounds[1]) & (v > bounds[2]) & (v < bounds[3])
+    N = len(xyz)
+    proj = np.stack([u, v, u - cam[4] / z, rng.uniform(0.99, 1.0, N)], 1).astype(np.float32)
+    proj[~np.isfinite(proj)] = 0
+    level = np.clip(octv + rng.integers(-1, 2, N), 0, 7).astype(np.int32)
+    flags = ((has & inside).astype(np.uint8) | ((rng.random(N) < obs_rate).astype(np.uint8) << 1))
+    mps = {"proj": proj, "desc": desc, "flags": flags, "level": level}
+    return cur, bounds, scale, mps, occupied
