@@ -200,6 +200,31 @@ typedef struct borb_last_frame {
 int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_frame *last, const float *Tcw_cur,
                               float mbf, float mb, float th, unsigned flags, int32_t *match, int *n_cur,
                               int *nmatches);
+/* -- local-map matcher: replaces ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*>
+ *    &vpMapPoints, const float th) (src/ORBmatcher.cc:59-154), the matcher of
+ *    Tracking::SearchLocalPoints (src/Tracking.cc:1055-1103) -------------------------------------- */
+
+/* The local map as Frame::isInFrustum (src/Frame.cc:348-407) left it: entry i is vpMapPoints[i].
+ *   flags[i]   bit 0: pMP->mbTrackInView && !pMP->isBad(), bit 1: pMP->Observations() > 0
+ *   proj[4i..] mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos;  level[i] mnTrackScaleLevel
+ *   desc[32i..] pMP->GetDescriptor() */
+typedef struct borb_map_points {
+    int n;
+    const float *proj;
+    const uint8_t *desc;
+    const uint8_t *flags;
+    const int32_t *level;
+} borb_map_points;
+
+/* F = frame `frame` of cur's last extract call (as borb_search_by_projection).  occupied[i2], i2 < the
+ * frame's keypoint count: 2 where F.mvpMapPoints[i2] holds a map point with Observations() > 0 on entry
+ * (such keypoints are skipped, :92-94), anything else where the slot is free to take (NULL = all free).
+ * th as the caller passes it (1, 3 for RGB-D, 5 after a relocalisation), nnratio = the matcher's
+ * mfNNratio (0.8 in SearchLocalPoints).  flags: BORB_MATCH_USE_STEREO.  match[i2] = index into mps of the
+ * map point this call puts into F.mvpMapPoints[i2], -1 where the slot keeps what it held. */
+int borb_search_local_points(borb_extractor *cur, int frame, const borb_map_points *mps, const uint8_t *occupied,
+                             float th, float nnratio, unsigned flags, int32_t *match, int *n_cur, int *nmatches);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

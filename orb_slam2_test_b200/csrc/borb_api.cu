@@ -167,7 +167,7 @@ struct borb_extractor {
     size_t mt_cap = 0;
     int *d_mt_choice = nullptr, *d_mt_taker = nullptr, *d_mt_match = nullptr, *h_mt_match = nullptr; /* match[K] + nm[4] */
     uint32_t *d_mt_cache = nullptr; /* [mt_cap][MT_K] candidate keys */
-    uint8_t *d_mt_more = nullptr;
+    uint8_t *d_mt_more = nullptr, *d_mt_occ = nullptr, *h_mt_occ = nullptr; /* occupancy of the local-map matcher */
     int mt_rescans = 0;
     int mt_rounds = 0;
 
@@ -246,16 +246,16 @@ void free_geometry(borb_extractor *h)
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
-                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more};
+                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
-                    h->h_mt_last, h->h_mt_match};
+                    h->h_mt_last, h->h_mt_match, h->h_mt_occ};
     for (void *p : host) if (p) cudaFreeHost(p);
     h->d_mt_last = h->h_mt_last = nullptr;
     h->mt_cap = 0;
     h->d_mt_choice = h->d_mt_taker = h->d_mt_match = h->h_mt_match = nullptr;
-    h->d_mt_cache = nullptr; h->d_mt_more = nullptr;
+    h->d_mt_cache = nullptr; h->d_mt_more = nullptr; h->d_mt_occ = h->h_mt_occ = nullptr;
     h->d_gray = nullptr;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
@@ -1243,23 +1243,23 @@ int borb_stereo_result(const borb_extractor *l, int frame, const float **u_right
     return BORB_OK;
 }
 
-/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1503-1668) against the
- * device-resident results of frame `frame` of cur's last call */
-int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_frame *last, const float *Tcw_cur,
-                              float mbf, float mb, float th, unsigned flags, int32_t *match, int *n_cur,
-                              int *nmatches)
+namespace {
+
+/* Both matchers (k_match.cuh): upload the query side's packed arrays [desc 32c][geo 16c][angle 4c][octave 4c][flags c]
+ * (+ the occupancy bytes of the local-map matcher), M1a over the whole GPU, M1b in one CTA, download the matches. */
+int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *geo, int geo_stride, const uint8_t *desc,
+                const uint8_t *qflags, const int32_t *octave, const float *angle, const uint8_t *occupied, MatchParams &mp,
+                bool use_stereo, int32_t *match, int *n_cur, int *nmatches)
 {
-    if (!cur || !last || !Tcw_cur || !match) return fail(BORB_ERR_ARG, "null argument");
     if (!cur->have_plan || cur->last_n < 1) return fail(BORB_ERR_STATE, "no finished extract call");
     if (!cur->have_cam || !cur->d_un_xy) return fail(BORB_ERR_STATE, "borb_set_camera must be on: the matcher reads mvKeysUn, mGrid and K");
     if (cur->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
     if (frame < 0 || frame >= cur->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, cur->last_n);
-    if (last->n < 0 || (last->n > 0 && (!last->xyz || !last->desc || !last->flags || !last->octave || !last->angle)) || !last->Tcw)
-        return fail(BORB_ERR_ARG, "last frame arrays");
-    if ((flags & BORB_MATCH_USE_STEREO) && !cur->d_st_u) return fail(BORB_ERR_STATE, "no stereo result on this handle");
-    for (int i = 0; i < last->n; ++i)
-        if ((last->flags[i] & 1) && (last->octave[i] < 0 || last->octave[i] >= cur->nlevels))
-            return fail(BORB_ERR_ARG, "octave %d of last keypoint %d", last->octave[i], i);
+    if (n < 0 || (n > 0 && (!geo || !desc || !qflags || !octave))) return fail(BORB_ERR_ARG, "query arrays");
+    if (use_stereo && !cur->d_st_u) return fail(BORB_ERR_STATE, "no stereo result on this handle");
+    for (int i = 0; i < n; ++i)
+        if ((qflags[i] & 1) && (octave[i] < 0 || octave[i] >= cur->nlevels))
+            return fail(BORB_ERR_ARG, "octave %d of query %d", octave[i], i);
     CU(cudaSetDevice(cur->device));
     const BorbPlan &P = cur->plan;
     const size_t K = (size_t)P.kp_total;
@@ -1268,9 +1268,11 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
         CU(cudaMalloc(&cur->d_mt_taker, 2 * K * 4));
         CU(cudaMalloc(&cur->d_mt_match, (K + 4) * 4));
         CU(cudaMallocHost(&cur->h_mt_match, (K + 4) * 4));
+        CU(cudaMalloc(&cur->d_mt_occ, K));
+        CU(cudaMallocHost(&cur->h_mt_occ, K));
     }
-    if ((size_t)last->n > cur->mt_cap || !cur->d_mt_last) {
-        const size_t cap = (((size_t)std::max(last->n, 1) + 1023) / 1024) * 1024;
+    if ((size_t)n > cur->mt_cap || !cur->d_mt_last) {
+        const size_t cap = (((size_t)std::max(n, 1) + 1023) / 1024) * 1024;
         CU(cudaStreamSynchronize(cur->stream));
         if (cur->d_mt_last) cudaFree(cur->d_mt_last);
         if (cur->h_mt_last) cudaFreeHost(cur->h_mt_last);
@@ -1279,41 +1281,100 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
         if (cur->d_mt_more) cudaFree(cur->d_mt_more);
         cur->d_mt_last = cur->h_mt_last = nullptr; cur->d_mt_choice = nullptr; cur->mt_cap = 0;
         cur->d_mt_cache = nullptr; cur->d_mt_more = nullptr;
-        CU(cudaMalloc(&cur->d_mt_last, cap * 53));
-        CU(cudaMallocHost(&cur->h_mt_last, cap * 53));
+        CU(cudaMalloc(&cur->d_mt_last, cap * 57));
+        CU(cudaMallocHost(&cur->h_mt_last, cap * 57));
         CU(cudaMalloc(&cur->d_mt_choice, cap * 4));
         CU(cudaMalloc(&cur->d_mt_cache, cap * MT_K * 4));
         CU(cudaMalloc(&cur->d_mt_more, cap));
         cur->mt_cap = cap;
     }
-    const size_t c = cur->mt_cap, n = (size_t)last->n;
+    const size_t c = cur->mt_cap, un = (size_t)n;
     unsigned char *hp = cur->h_mt_last, *dp = cur->d_mt_last;
     if (n) {
-        std::memcpy(hp, last->desc, n * 32);
-        std::memcpy(hp + 32 * c, last->xyz, n * 12);
-        std::memcpy(hp + 44 * c, last->angle, n * 4);
-        std::memcpy(hp + 48 * c, last->octave, n * 4);
-        std::memcpy(hp + 52 * c, last->flags, n);
+        std::memcpy(hp, desc, un * 32);
+        float *g = reinterpret_cast<float *>(hp + 32 * c);
+        if (geo_stride == 4) std::memcpy(g, geo, un * 16);
+        else
+            for (size_t i = 0; i < un; ++i) { g[4 * i] = geo[3 * i]; g[4 * i + 1] = geo[3 * i + 1]; g[4 * i + 2] = geo[3 * i + 2]; g[4 * i + 3] = 0.f; }
+        if (angle) std::memcpy(hp + 48 * c, angle, un * 4);
+        std::memcpy(hp + 52 * c, octave, un * 4);
+        std::memcpy(hp + 56 * c, qflags, un);
     }
     cudaStream_t st = cur->stream;
-    /* one contiguous upload when the arrays are nearly full, else five short ones */
-    if (n * 2 >= c) CU(cudaMemcpyAsync(dp, hp, 53 * c, cudaMemcpyHostToDevice, st));
+    /* one contiguous upload when the arrays are nearly full, else one per array */
+    if (un * 2 >= c) CU(cudaMemcpyAsync(dp, hp, 57 * c, cudaMemcpyHostToDevice, st));
     else if (n) {
-        CU(cudaMemcpyAsync(dp, hp, n * 32, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(dp + 32 * c, hp + 32 * c, n * 12, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(dp + 44 * c, hp + 44 * c, n * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(dp + 48 * c, hp + 48 * c, n * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(dp + 52 * c, hp + 52 * c, n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp, hp, un * 32, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 32 * c, hp + 32 * c, un * 16, cudaMemcpyHostToDevice, st));
+        if (angle) CU(cudaMemcpyAsync(dp + 48 * c, hp + 48 * c, un * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 52 * c, hp + 52 * c, un * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dp + 56 * c, hp + 56 * c, un, cudaMemcpyHostToDevice, st));
     }
+    const uint8_t *d_occ = nullptr;
+    if (occupied) { /* the caller's view of F.mvpMapPoints on entry; sized by the frame's keypoint count, which is on the host */
+        CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        const size_t nc0 = (size_t)std::min(cur->h_nout[frame], (int)K);
+        std::memset(cur->h_mt_occ, 0, K);
+        std::memcpy(cur->h_mt_occ, occupied, nc0);
+        CU(cudaMemcpyAsync(cur->d_mt_occ, cur->h_mt_occ, K, cudaMemcpyHostToDevice, st));
+        d_occ = cur->d_mt_occ;
+    }
+    mp.fx = cur->cam.fx; mp.fy = cur->cam.fy; mp.cx = cur->cam.cx; mp.cy = cur->cam.cy;
+    mp.n_last = n;
+    for (int l = 0; l < BORB_MAXL; ++l) mp.scale[l] = l < cur->nlevels ? cur->scale[l] : 0.f;
+    const size_t fo = (size_t)frame * K;
+    const float *d_ur = use_stereo ? cur->d_st_u + fo : nullptr;
+    const float *l_geo = reinterpret_cast<const float *>(dp + 32 * c), *l_angle = reinterpret_cast<const float *>(dp + 48 * c);
+    const int *l_oct = reinterpret_cast<const int *>(dp + 52 * c);
+    const uint4 *l_desc = reinterpret_cast<const uint4 *>(dp);
+    const uint8_t *l_flags = dp + 56 * c;
+    const int *cs = cur->d_cell_start + (size_t)frame * (FR_CELLS + 1), *ci = cur->d_cell_idx + fo;
+    const int cand_grid = (n + MT_CAND_NT / 32 - 1) / (MT_CAND_NT / 32);
+#define MATCH_LAUNCH(MODE)                                                                                                   \
+    do {                                                                                                                     \
+        if (n > 0)                                                                                                           \
+            k_match_candidates<MODE><<<cand_grid, MT_CAND_NT, 0, st>>>(                                                       \
+                mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4, \
+                d_ur, d_occ, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);                                 \
+        k_match_resolve<MODE><<<1, MT_NT, 0, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, \
+                                                   cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame, d_ur, d_occ, l_geo,  \
+                                                   l_angle, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more,           \
+                                                   cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,                 \
+                                                   cur->d_mt_match + K);                                                     \
+    } while (0)
+    if (mode == 1) MATCH_LAUNCH(1); else MATCH_LAUNCH(2);
+#undef MATCH_LAUNCH
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const int nc = std::min(cur->h_nout[frame], (int)K);
+    std::memcpy(match, cur->h_mt_match, (size_t)nc * 4);
+    if (n_cur) *n_cur = nc;
+    if (nmatches) *nmatches = cur->h_mt_match[K];
+    cur->mt_rounds = cur->h_mt_match[K + 1];
+    cur->mt_rescans = cur->h_mt_match[K + 2];
+    return BORB_OK;
+}
+
+} // namespace
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1503-1668) against the
+ * device-resident results of frame `frame` of cur's last call */
+int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_frame *last, const float *Tcw_cur,
+                              float mbf, float mb, float th, unsigned flags, int32_t *match, int *n_cur,
+                              int *nmatches)
+{
+    if (!cur || !last || !Tcw_cur || !match) return fail(BORB_ERR_ARG, "null argument");
+    if (!last->Tcw || (last->n > 0 && !last->angle)) return fail(BORB_ERR_ARG, "last frame arrays");
     MatchParams mp;
+    std::memset(&mp, 0, sizeof mp);
     std::memcpy(mp.Tc, Tcw_cur, 48);
     std::memcpy(mp.Tl, last->Tcw, 48);
-    mp.fx = cur->cam.fx; mp.fy = cur->cam.fy; mp.cx = cur->cam.cx; mp.cy = cur->cam.cy;
     mp.mbf = mbf; mp.mb = mb; mp.th = th;
     mp.mono = (flags & BORB_MATCH_MONO) ? 1 : 0;
     mp.check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
-    mp.n_last = last->n;
-    for (int l = 0; l < BORB_MAXL; ++l) mp.scale[l] = l < cur->nlevels ? cur->scale[l] : 0.f;
     {   /* search direction (:1515-1526): twc = -Rcw^T tcw, tlc = Rlw twc + tlw, OpenCV's small float gemm
          * (products summed left to right); this file is compiled without contraction */
         const float *Tc = mp.Tc, *Tl = mp.Tl;
@@ -1329,32 +1390,21 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
         const bool fwd = tlc_z > mb && !mp.mono, bwd = -tlc_z > mb && !mp.mono;
         mp.dir = fwd ? 1 : bwd ? 2 : 0;
     }
-    const size_t fo = (size_t)frame * K;
-    const float *d_ur = (flags & BORB_MATCH_USE_STEREO) ? cur->d_st_u + fo : nullptr;
-    const float *l_xyz = reinterpret_cast<const float *>(dp + 32 * c), *l_angle = reinterpret_cast<const float *>(dp + 44 * c);
-    const int *l_oct = reinterpret_cast<const int *>(dp + 48 * c);
-    const uint4 *l_desc = reinterpret_cast<const uint4 *>(dp);
-    const uint8_t *l_flags = dp + 52 * c;
-    const int *cs = cur->d_cell_start + (size_t)frame * (FR_CELLS + 1), *ci = cur->d_cell_idx + fo;
-    if (last->n > 0)
-        k_match_candidates<<<(last->n + MT_CAND_NT / 32 - 1) / (MT_CAND_NT / 32), MT_CAND_NT, 0, st>>>(
-            mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4,
-            d_ur, l_xyz, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);
-    k_match_resolve<<<1, MT_NT, 0, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci,
-                                         cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame, d_ur, l_xyz, l_angle, l_oct,
-                                         l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more, cur->d_mt_choice, cur->d_mt_taker,
-                                         (int)K, cur->d_mt_match, cur->d_mt_match + K);
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    const int nc = std::min(cur->h_nout[frame], (int)K);
-    std::memcpy(match, cur->h_mt_match, (size_t)nc * 4);
-    if (n_cur) *n_cur = nc;
-    if (nmatches) *nmatches = cur->h_mt_match[K];
-    cur->mt_rounds = cur->h_mt_match[K + 1];
-    cur->mt_rescans = cur->h_mt_match[K + 2];
-    return BORB_OK;
+    return run_matcher(cur, frame, 1, last->n, last->xyz, 3, last->desc, last->flags, last->octave, last->angle, nullptr, mp,
+                       (flags & BORB_MATCH_USE_STEREO) != 0, match, n_cur, nmatches);
+}
+
+/* ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154), the matcher of Tracking::SearchLocalPoints */
+int borb_search_local_points(borb_extractor *cur, int frame, const borb_map_points *mps, const uint8_t *occupied, float th,
+                             float nnratio, unsigned flags, int32_t *match, int *n_cur, int *nmatches)
+{
+    if (!cur || !mps || !match) return fail(BORB_ERR_ARG, "null argument");
+    MatchParams mp;
+    std::memset(&mp, 0, sizeof mp);
+    mp.th = th;
+    mp.nnratio = nnratio;
+    return run_matcher(cur, frame, 2, mps->n, mps->proj, 4, mps->desc, mps->flags, mps->level, nullptr, occupied, mp,
+                       (flags & BORB_MATCH_USE_STEREO) != 0, match, n_cur, nmatches);
 }
 
 int borb_match_rounds(const borb_extractor *cur) { return cur ? cur->mt_rounds | (cur->mt_rescans << 8) : 0; }

@@ -48,6 +48,7 @@
 struct MatchParams {
     float Tc[12], Tl[12]; /* Tcw of the current and the last frame, 3 x 4 row-major */
     float fx, fy, cx, cy, mbf, mb, th;
+    float nnratio; /* M2: mfNNratio of the local-map matcher */
     int mono, check_ori, n_last;
     int dir; /* 1 forward, 2 backward, 0 neither: from tlc.z against mb (:1515-1526), evaluated on the host */
     float scale[BORB_MAXL];
@@ -96,20 +97,40 @@ struct MtQuery { /* what the candidate scan of one query needs (:1537-1572) */
     int min_level, max_level, cx0, cx1, cy0, cy1;
 };
 
-__device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *__restrict__ l_xyz, int oct, int i,
+/* MODE 1: the frame-to-frame matcher (geo = world position; src/ORBmatcher.cc:1537-1572).
+ * MODE 2: the local-map matcher, ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154) of
+ *         Tracking::SearchLocalPoints: geo = mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos as
+ *         Frame::isInFrustum left them, lvl = mnTrackScaleLevel; r = RadiusByViewingCos (:156-162), r *= th unless
+ *         th == 1, window r * scale[lvl], octaves lvl-1 .. lvl (:72-79). */
+template <int MODE>
+__device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *__restrict__ l_geo, int oct, int i,
                                             float min_x, float max_x, float min_y, float max_y, float winv, float hinv)
 {
     MtQuery Q;
-    const float X[3] = {l_xyz[3 * i], l_xyz[3 * i + 1], l_xyz[3 * i + 2]};
-    const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7], zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
-    const float invzc = 1.0f / zc;
-    Q.u = fmaf(mp.fx * xc, invzc, mp.cx);
-    Q.v = fmaf(mp.fy * yc, invzc, mp.cy);
-    Q.ok = !(invzc < 0) && !(Q.u < min_x || Q.u > max_x) && !(Q.v < min_y || Q.v > max_y);
-    Q.radius = mp.th * mp.scale[oct];
-    if (mp.dir == 1) { Q.min_level = oct; Q.max_level = -1; }
-    else if (mp.dir == 2) { Q.min_level = 0; Q.max_level = oct; }
-    else { Q.min_level = oct - 1; Q.max_level = oct + 1; }
+    const float4 g = reinterpret_cast<const float4 *>(l_geo)[i];
+    if (MODE == 1) {
+        const float X[3] = {g.x, g.y, g.z};
+        const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7], zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
+        const float invzc = 1.0f / zc;
+        Q.u = fmaf(mp.fx * xc, invzc, mp.cx);
+        Q.v = fmaf(mp.fy * yc, invzc, mp.cy);
+        Q.ok = !(invzc < 0) && !(Q.u < min_x || Q.u > max_x) && !(Q.v < min_y || Q.v > max_y);
+        Q.radius = mp.th * mp.scale[oct];
+        if (mp.dir == 1) { Q.min_level = oct; Q.max_level = -1; }
+        else if (mp.dir == 2) { Q.min_level = 0; Q.max_level = oct; }
+        else { Q.min_level = oct - 1; Q.max_level = oct + 1; }
+        Q.ur = fmaf(-mp.mbf, invzc, Q.u);
+    } else {
+        float r = (double)g.w > 0.998 ? 2.5f : 4.0f;
+        if (mp.th != 1.0f) r *= mp.th;
+        Q.radius = r * mp.scale[oct];
+        Q.u = g.x;
+        Q.v = g.y;
+        Q.ur = g.z;
+        Q.min_level = oct - 1;
+        Q.max_level = oct;
+        Q.ok = true;
+    }
     /* Frame::GetFeaturesInArea (src/Frame.cc:446-462) */
     Q.cx0 = max(0, (int)floorf((Q.u - min_x - Q.radius) * winv));
     Q.cx1 = min(MT_COLS - 1, (int)ceilf((Q.u - min_x + Q.radius) * winv));
@@ -117,7 +138,6 @@ __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *
     Q.cy1 = min(MT_ROWS - 1, (int)ceilf((Q.v - min_y + Q.radius) * hinv));
     Q.ok = Q.ok && Q.cx0 < MT_COLS && Q.cx1 >= 0 && Q.cy0 < MT_ROWS && Q.cy1 >= 0;
     Q.check_levels = (Q.min_level > 0) || (Q.max_level >= 0);
-    Q.ur = fmaf(-mp.mbf, invzc, Q.u);
     return Q;
 }
 
@@ -125,8 +145,10 @@ __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *
  * queries (:1587-1595), then the distance; -1 = rejected */
 __device__ __forceinline__ int mt_candidate(const MtQuery &Q, int i2, const BorbKpRec *__restrict__ kp,
                                             const float2 *__restrict__ un_xy, const float *__restrict__ u_right,
-                                            const uint8_t *__restrict__ desc, const uint4 d0, const uint4 d1)
+                                            const uint8_t *__restrict__ occupied, const uint8_t *__restrict__ desc,
+                                            const uint4 d0, const uint4 d1)
 {
+    if (occupied && occupied[i2] == 2) return -1; /* M2: holds a point with observations on entry (:92-94) */
     const int o2 = kp[i2].octave;
     if (Q.check_levels && (o2 < Q.min_level || (Q.max_level >= 0 && o2 > Q.max_level))) return -1;
     const float2 p = un_xy[i2];
@@ -138,15 +160,16 @@ __device__ __forceinline__ int mt_candidate(const MtQuery &Q, int i2, const Borb
     return mt_hamming(d0, d1, reinterpret_cast<const uint4 *>(desc) + 2 * i2);
 }
 
-/* last frame: xyz [3n], octave [n], desc [n] x 32 B (16-byte aligned), flags [n] (bit 0 map point,
+/* last frame / local map: geo [4n], octave [n], desc [n] x 32 B (16-byte aligned), flags [n] (bit 0 map point,
  * bit 1 Observations() > 0, bit 2 outlier).  Out: cache [n_last][MT_K] keys (distance << 16 | list
  * position q, ascending; MT_NOKEY = none), more [n_last] = the query had more than MT_K candidates. */
+template <int MODE>
 __global__ void __launch_bounds__(MT_CAND_NT)
 k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
                    const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
                    const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
                    const float *__restrict__ bounds, const float *__restrict__ u_right,
-                   const float *__restrict__ l_xyz, const int *__restrict__ l_octave,
+                   const uint8_t *__restrict__ occupied, const float *__restrict__ l_geo, const int *__restrict__ l_octave,
                    const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
                    uint32_t *__restrict__ cache, uint8_t *__restrict__ more)
 {
@@ -161,7 +184,7 @@ k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__re
     if ((fl & 1u) && !(fl & 4u)) {
         const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
         const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
-        const MtQuery Q = mt_query(mp, l_xyz, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+        const MtQuery Q = mt_query<MODE>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
         if (Q.ok) {
             const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
             for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
@@ -170,7 +193,7 @@ k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__re
                     const int q = qb + lane;
                     uint32_t key = MT_NOKEY;
                     if (q < q1) {
-                        const int d = mt_candidate(Q, cell_idx[q], kp, un_xy, u_right, desc, d0, d1);
+                        const int d = mt_candidate(Q, cell_idx[q], kp, un_xy, u_right, occupied, desc, d0, d1);
                         if (d >= 0) key = ((uint32_t)d << 16) | (uint32_t)q;
                     }
                     cnt += __popc(__ballot_sync(0xffffffffu, key != MT_NOKEY));
@@ -201,13 +224,14 @@ k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__re
 
 /* Scratch: choice [n_last], taker [2][kp_total].  Out: match [kp_total] = index of the last-frame map point
  * per current keypoint or -1; nm[0] = nmatches, nm[1] = rounds taken, nm[2] = rescans. */
+template <int MODE>
 __global__ void __launch_bounds__(MT_NT, 1)
 k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
                 const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
                 const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
                 const float *__restrict__ bounds, const int *__restrict__ n_cur_p,
-                const float *__restrict__ u_right, const float *__restrict__ l_xyz,
-                const float *__restrict__ l_angle, const int *__restrict__ l_octave,
+                const float *__restrict__ u_right, const uint8_t *__restrict__ occupied,
+                const float *__restrict__ l_geo, const float *__restrict__ l_angle, const int *__restrict__ l_octave,
                 const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
                 const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more,
                 int *__restrict__ choice, int *__restrict__ taker, int kp_total, int *__restrict__ match,
@@ -234,30 +258,66 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
         __syncthreads();
         for (int i = tid; i < n_last; i += MT_NT) {
             int ch = -1;
-            bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
+            if (MODE == 1) {
+                bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
 #pragma unroll
-            for (int k = 0; k < MT_K; ++k) {
-                if (!all_held) continue;
-                const uint32_t key = cache[(size_t)i * MT_K + k];
-                if (key == MT_NOKEY || (key >> 16) > MT_TH_HIGH) { all_held = false; continue; }
-                const int c = cell_idx[key & 0xffffu];
-                if (tk_prev[c] >= i) { ch = c; all_held = false; }
-            }
-            if (all_held && more[i]) { /* rare: walk the cells again, now with the holders known */
-                atomicAdd(&s_rescans, 1);
-                const MtQuery Q = mt_query(mp, l_xyz, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
-                const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
-                int best = 256, best_idx = -1;
-                for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
-                    const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
-                    for (int q = q0; q < q1; ++q) {
-                        const int i2 = cell_idx[q];
-                        if (tk_prev[i2] < i) continue;
-                        const int d = mt_candidate(Q, i2, kp, un_xy, u_right, desc, d0, d1);
-                        if (d >= 0 && d < best) { best = d; best_idx = i2; }
+                for (int k = 0; k < MT_K; ++k) {
+                    if (!all_held) continue;
+                    const uint32_t key = cache[(size_t)i * MT_K + k];
+                    if (key == MT_NOKEY || (key >> 16) > MT_TH_HIGH) { all_held = false; continue; }
+                    const int c = cell_idx[key & 0xffffu];
+                    if (tk_prev[c] >= i) { ch = c; all_held = false; }
+                }
+                if (all_held && more[i]) { /* rare: walk the cells again, now with the holders known */
+                    atomicAdd(&s_rescans, 1);
+                    const MtQuery Q = mt_query<1>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+                    const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
+                    int best = 256, best_idx = -1;
+                    for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
+                        const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
+                        for (int q = q0; q < q1; ++q) {
+                            const int i2 = cell_idx[q];
+                            if (tk_prev[i2] < i) continue;
+                            const int d = mt_candidate(Q, i2, kp, un_xy, u_right, occupied, desc, d0, d1);
+                            if (d >= 0 && d < best) { best = d; best_idx = i2; }
+                        }
+                    }
+                    ch = best <= MT_TH_HIGH ? best_idx : -1;
+                }
+            } else {
+                /* best and second best among the candidates nobody earlier holds (:84-115): the first two free
+                 * entries of the cached (distance, scan order) list */
+                int found = 0, bd = 256, bl = -1, bd2 = 256, bl2 = -1, bidx = -1;
+                bool decided = false;
+#pragma unroll
+                for (int k = 0; k < MT_K; ++k) {
+                    if (decided) continue;
+                    const uint32_t key = cache[(size_t)i * MT_K + k];
+                    if (key == MT_NOKEY) { decided = true; continue; }
+                    const int c = cell_idx[key & 0xffffu];
+                    if (tk_prev[c] < i) continue;
+                    const int d = (int)(key >> 16);
+                    if (found == 0) { bd = d; bl = kp[c].octave; bidx = c; found = 1; if (d > MT_TH_HIGH) decided = true; }
+                    else { bd2 = d; bl2 = kp[c].octave; found = 2; decided = true; }
+                }
+                if (!decided && more[i]) { /* fewer than two free candidates among the cached ones and there were more */
+                    atomicAdd(&s_rescans, 1);
+                    const MtQuery Q = mt_query<2>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+                    const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
+                    bd = 256; bl = -1; bd2 = 256; bl2 = -1; bidx = -1;
+                    for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
+                        const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
+                        for (int q = q0; q < q1; ++q) {
+                            const int i2 = cell_idx[q];
+                            if (tk_prev[i2] < i) continue;
+                            const int d = mt_candidate(Q, i2, kp, un_xy, u_right, occupied, desc, d0, d1);
+                            if (d < 0) continue;
+                            if (d < bd) { bd2 = bd; bd = d; bl2 = bl; bl = kp[i2].octave; bidx = i2; }
+                            else if (d < bd2) { bl2 = kp[i2].octave; bd2 = d; }
+                        }
                     }
                 }
-                ch = best <= MT_TH_HIGH ? best_idx : -1;
+                if (bd <= MT_TH_HIGH && !(bl == bl2 && (float)bd > mp.nnratio * (float)bd2)) ch = bidx;
             }
             if (ch != choice[i]) { choice[i] = ch; s_changed = 1; }
             if (ch >= 0 && (l_flags[i] & 2u)) atomicMin(&tk_new[ch], i);
@@ -274,11 +334,11 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
         if (ch >= 0) {
             atomicAdd(&s_nm, 1);
             atomicMax(&match[ch], i);
-            if (mp.check_ori) atomicAdd(&s_hist[mt_bin(l_angle[i], kp[ch].angle)], 1);
+            if (MODE == 1 && mp.check_ori) atomicAdd(&s_hist[mt_bin(l_angle[i], kp[ch].angle)], 1);
         }
     }
     __syncthreads();
-    if (mp.check_ori) {
+    if (MODE == 1 && mp.check_ori) {
         if (tid == 0) {
             int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
             for (int b = 0; b < MT_HISTO; ++b) {

@@ -38,7 +38,7 @@ SYMBOLS = [
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
     "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
     "borb_last_prestep_ms", "borb_set_camera", "borb_frame_grid",
-    "borb_search_by_projection", "borb_match_rounds", "borb_max_keypoints",
+    "borb_search_by_projection", "borb_search_local_points", "borb_match_rounds", "borb_max_keypoints",
 ]
 
 
@@ -108,6 +108,8 @@ def load_library() -> C.CDLL:
     lib.borb_stereo_match.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_uint]
     lib.borb_search_by_projection.argtypes = [_vp, C.c_int, _vp, _vp, C.c_float, C.c_float, C.c_float, C.c_uint, _vp,
                                               C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_search_local_points.argtypes = [_vp, C.c_int, _vp, _vp, C.c_float, C.c_float, C.c_uint, _vp,
+                                             C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.borb_match_rounds.argtypes = [_vp]
     lib.borb_max_keypoints.argtypes = [_vp]
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
@@ -126,6 +128,10 @@ def debug_sincos(radians: float):
     s, c = C.c_float(), C.c_float()
     lib.borb_debug_sincos(radians, C.byref(s), C.byref(c))
     return s.value, c.value
+
+
+class _MapPoints(C.Structure):  # == borb_map_points
+    _fields_ = [("n", C.c_int), ("proj", _vp), ("desc", _vp), ("flags", _vp), ("level", _vp)]
 
 
 class _LastFrame(C.Structure):  # == borb_last_frame
@@ -399,6 +405,22 @@ class ORBextractor:
         flags = (1 if mono else 0) | (0 if check_orientation else 2) | (4 if use_stereo else 0)
         _check(self._lib, self._lib.borb_search_by_projection(self._h, frame, C.addressof(lf), tc.ctypes.data, mbf, mb, th,
                                                               flags, out.ctypes.data, C.byref(n), C.byref(nm)))
+        return out[:n.value].copy(), nm.value
+
+    def search_local_points(self, mps: dict, occupied=None, th: float = 1.0, nnratio: float = 0.8, frame: int = 0,
+                            use_stereo: bool = False):
+        """ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154) with frame `frame` of this
+        extractor's last call as F, on the device.  mps: dict with proj [n,4] f32, desc [n,32] u8, flags [n] u8,
+        level [n] i32 (see include/borb.h); occupied [n_cur] u8 or None.  -> (match [n_cur] i32, nmatches)."""
+        keep = [np.ascontiguousarray(mps["proj"], np.float32), np.ascontiguousarray(mps["desc"], np.uint8),
+                np.ascontiguousarray(mps["flags"], np.uint8), np.ascontiguousarray(mps["level"], np.int32)]
+        mp = _MapPoints(len(keep[2]), *[a.ctypes.data for a in keep])
+        occ = np.ascontiguousarray(occupied, np.uint8) if occupied is not None else None
+        out = np.full(max(self._lib.borb_max_keypoints(self._h), 1), -1, np.int32)
+        n, nm = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_search_local_points(self._h, frame, C.addressof(mp), occ.ctypes.data if occ is not None else None,
+                                                             th, nnratio, 4 if use_stereo else 0, out.ctypes.data,
+                                                             C.byref(n), C.byref(nm)))
         return out[:n.value].copy(), nm.value
 
     def match_rounds(self) -> int:

@@ -101,3 +101,46 @@ def test_no_map_points_and_argument_errors(oracle_built):
     bad["octave"] = np.full(len(last["kps"]), 9, np.int32)
     with pytest.raises(BorbError):
         ext.search_by_projection(bad, cur["Tcw"], 386.0, 0.5, 7.0)
+
+
+# ---- the local-map matcher: ORBmatcher::SearchByProjection(F, vpMapPoints, th), src/ORBmatcher.cc:59-154 ----
+
+def _check_local(tag, oracle, ths=(1.0, 3.0, 5.0), ratios=(0.8, 0.6), **kw):
+    cur, bounds, scale, mps, occ = matchcase.make_local_case(**kw)
+    stereo = kw.get("stereo", True)
+    K = kw.get("K", matchcase.KITTI_K)
+    bf = kw.get("bf", matchcase.KITTI_BF)
+    ext, right = _gpu_frame(kw.get("shape", synth.KITTI_SHAPE), kw.get("seed", 0), 1, K, kw.get("dist", (0.0, 0.0, 0.0, 0.0)),
+                            stereo, kw.get("nf", 2000), bf, bf / K[0])
+    kps, desc = ext.result(0)
+    assert kps.tobytes() == cur["kps"].tobytes() and np.array_equal(desc, cur["desc"]), f"{tag}: current frame differs"
+    total = 0
+    for th in ths:
+        for ratio in ratios:
+            want, wnm = oracle.search_local_points(cur, bounds, scale, mps, occ, th, ratio)
+            got, nm = ext.search_local_points(mps, occ, th, ratio, use_stereo=stereo)
+            bad = np.nonzero(got != want)[0]
+            assert bad.size == 0, f"{tag} th={th} ratio={ratio}: {bad.size} slots differ, e.g. {bad[:5]}: {got[bad[:5]]} vs {want[bad[:5]]}"
+            assert nm == wnm, f"{tag} th={th} ratio={ratio}: nmatches {nm} vs {wnm}"
+            total += wnm
+    return total
+
+
+@pytest.mark.parametrize("seed,copies,obs", [(1, 2, 0.9), (2, 3, 0.5), (3, 4, 1.0)])
+def test_local_map_kitti(seed, copies, obs, oracle_built):
+    assert _check_local(f"local kitti {seed}", oracle_built, seed=seed, copies=copies, obs_rate=obs) > 2000
+
+
+def test_local_map_monocular_tum(oracle_built):
+    assert _check_local("local tum", oracle_built, seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
+                        bf=40.0, stereo=False, nf=1000) > 1000
+
+
+def test_local_map_without_occupancy(oracle_built):
+    """occupied = NULL: every slot is free (a frame nobody matched yet)"""
+    cur, bounds, scale, mps, occ = matchcase.make_local_case(seed=6)
+    ext, _ = _gpu_frame(synth.KITTI_SHAPE, 6, 1, matchcase.KITTI_K, (0.0, 0.0, 0.0, 0.0), True, 2000, matchcase.KITTI_BF,
+                        matchcase.KITTI_BF / matchcase.KITTI_K[0])
+    want, wnm = oracle_built.search_local_points(cur, bounds, scale, mps, np.zeros(len(occ), np.uint8), 3.0, 0.8)
+    got, nm = ext.search_local_points(mps, None, 3.0, 0.8, use_stereo=True)
+    assert np.array_equal(got, want) and nm == wnm > 500
