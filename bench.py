@@ -437,6 +437,53 @@ def matcher_section(ORBextractor, synth, local):
         except Exception as ex:
             e["parity_check"] = f"unavailable ({type(ex).__name__})"
         out["th_%d" % int(th)] = e
+    # the local-map matcher of Tracking::SearchLocalPoints on the same current frame: the motion-model matches
+    # occupy their slots, the local map = the unmatched map points plus two jittered copies (tests/matchcase.py)
+    try:
+        from oracle import pyoracle
+        m7, _ = ext.search_by_projection(lf, cur["Tcw"], BF, mb, 7.0, use_stereo=True)
+        occ = np.zeros(len(m7), np.uint8)
+        held = m7 >= 0
+        occ[held] = np.where(last["mp_flags"][m7[held]] & 2, 2, 1)
+        rng = np.random.default_rng(72)
+        copies = 3
+        matched = np.zeros(len(last["kps"]), bool)
+        matched[m7[held]] = True
+        xyz = np.concatenate([last["mp_xyz"]] + [last["mp_xyz"] + rng.normal(0, 0.03, last["mp_xyz"].shape).astype(np.float32)
+                                                 for _ in range(copies - 1)]).astype(np.float64)
+        has = np.concatenate([(last["mp_flags"] & 1).astype(bool) & ~matched] + [(last["mp_flags"] & 1).astype(bool)] * (copies - 1))
+        T = cur["Tcw"].astype(np.float64)
+        Xc = xyz @ T[:, :3].T + T[:, 3]
+        z = np.where(np.abs(Xc[:, 2]) > 1e-6, Xc[:, 2], 1.0)
+        u, v = K[0] * Xc[:, 0] / z + K[2], K[1] * Xc[:, 1] / z + K[3]
+        b = cur["bounds"]
+        inside = (Xc[:, 2] > 0) & (u > b[0]) & (u < b[1]) & (v > b[2]) & (v < b[3])
+        N = len(xyz)
+        proj = np.stack([u, v, u - BF / z, rng.uniform(0.99, 1.0, N)], 1).astype(np.float32)
+        mps = {"proj": proj, "desc": np.concatenate([last["mp_desc"]] * copies),
+               "flags": ((has & inside).astype(np.uint8) | ((rng.random(N) < 0.9).astype(np.uint8) << 1)),
+               "level": np.clip(np.concatenate([last["kps"]["octave"]] * copies) + rng.integers(-1, 2, N), 0, 7).astype(np.int32)}
+        loc = {"reference": "src/ORBmatcher.cc:59-154 (Tracking::SearchLocalPoints)",
+               "config": "%d local map points, %d in view, %d slots held" % (N, int((mps["flags"] & 1).sum()), int((occ == 2).sum()))}
+        for th in (1.0, 3.0):
+            for _ in range(10):
+                m, nm = ext.search_local_points(mps, occ, th, 0.8, use_stereo=True)
+            ts = []
+            for _ in range(100):
+                t1 = time.perf_counter()
+                m, nm = ext.search_local_points(mps, occ, th, 0.8, use_stereo=True)
+                ts.append((time.perf_counter() - t1) * 1e6)
+            tc = []
+            for _ in range(20):
+                t1 = time.perf_counter()
+                w, wnm = pyoracle.search_local_points(cur, cur["bounds"], scale, mps, occ, th, 0.8)
+                tc.append((time.perf_counter() - t1) * 1e6)
+            loc["th_%d" % int(th)] = {"call_p50_us": float(np.percentile(ts, 50)), "nmatches": nm, "rounds": ext.match_rounds(),
+                                      "rescans": ext.match_rescans(), "cpu_p50_us_one_core": float(np.percentile(tc, 50)),
+                                      "parity_check": "identical" if (np.array_equal(m, w) and nm == wnm) else "MISMATCH"}
+        out["local_map"] = loc
+    except Exception as ex:
+        out["local_map"] = f"unavailable ({type(ex).__name__}: {ex})"
     return out
 
 

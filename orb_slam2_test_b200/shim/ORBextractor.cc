@@ -196,4 +196,19 @@ int ORBextractor::SearchByProjection(const cv::Mat &TcwCur, const cv::Mat &TcwLa
     return nmatches;
 }
 
+int ORBextractor::SearchLocalPoints(int nPoints, const float *proj, const unsigned char *mpDescriptors,
+                                    const unsigned char *flags, const int *level, const unsigned char *occupied, float th,
+                                    float nnRatio, bool useStereo, std::vector<int> &vnMatches)
+{
+    borb_map_points mps;
+    mps.n = nPoints; mps.proj = proj; mps.desc = mpDescriptors; mps.flags = flags; mps.level = level;
+    vnMatches.assign((size_t)borb_max_keypoints(handle), -1);
+    int n = 0, nmatches = 0;
+    check(borb_search_local_points(handle, 0, &mps, occupied, th, nnRatio, useStereo ? BORB_MATCH_USE_STEREO : 0u,
+                                   vnMatches.data(), &n, &nmatches),
+          "search local points");
+    vnMatches.resize((size_t)n);
+    return nmatches;
+}
+
 } // namespace ORB_SLAM2

@@ -116,6 +116,15 @@ public:
                            const unsigned char *mpDescriptors, const unsigned char *flags, const int *octave,
                            const float *angle, float mbf, float mb, float th, bool bMono, bool checkOrientation,
                            bool useStereo, std::vector<int> &vnMatches);
+    // ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (reference
+    // src/ORBmatcher.cc:59-154, the matcher of Tracking::SearchLocalPoints) on the device, *this = F's left
+    // extractor.  Entry i = vpMapPoints[i] as Frame::isInFrustum left it: proj[4i..] = mTrackProjX, mTrackProjY,
+    // mTrackProjXR, mTrackViewCos; level[i] = mnTrackScaleLevel; flags bit 0 = mbTrackInView && !isBad(), bit 1 =
+    // Observations() > 0; occupied[i2] = 2 where F.mvpMapPoints[i2] holds a point with observations (may be NULL).
+    // vnMatches[i2] = i put into F.mvpMapPoints[i2] by this call, -1 = slot unchanged; returns nmatches.
+    int SearchLocalPoints(int nPoints, const float *proj, const unsigned char *mpDescriptors, const unsigned char *flags,
+                          const int *level, const unsigned char *occupied, float th, float nnRatio, bool useStereo,
+                          std::vector<int> &vnMatches);
 
 protected:
     int nfeatures;

@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """Generate tests/golden/match_expected.npz: outputs of the REFERENCE's own src/ORBmatcher.cc
-(ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono), compiled in place into
+(ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono) and SearchByProjection(Frame&, const
+vector<MapPoint*>&, th), compiled in place into
 oracle/_ref/librefmatch.so) on the scenarios of tests/matchcase.py, which are a pure function of
 their arguments (synthetic frames -> oracle extractor -> map points), so only the outputs are stored.
 
@@ -31,8 +32,24 @@ CASES = {
 }
 
 
+# name -> (make_local_case kwargs, thresholds): ORBmatcher::SearchByProjection(F, vpMapPoints, th), nnratio 0.8
+LOCAL_CASES = {
+    "local_kitti": (dict(seed=16, copies=2, obs_rate=0.9), (1.0, 3.0)),
+    "local_kitti_crowded": (dict(seed=17, copies=4, obs_rate=0.5), (1.0, 5.0)),
+    "local_tum_mono": (dict(seed=18, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False,
+                            nf=1000), (1.0, 5.0)),
+}
+
+
 def main():
     out = {}
+    for name, (kw, ths) in LOCAL_CASES.items():
+        cur, bounds, scale, mps, occ = matchcase.make_local_case(**kw)
+        for th in ths:
+            m, nm = RefMatcher.search_local_points(cur, bounds, scale, mps, occ, th, 0.8)
+            out[f"{name}_th{int(th)}_match"] = m
+            out[f"{name}_th{int(th)}_nm"] = np.array([nm, len(mps["flags"]), int((m >= 0).sum())], np.int32)
+            print(name, th, "nmatches", nm, "slots", int((m >= 0).sum()))
     for name, (kw, mono, ths) in CASES.items():
         cur, last, cam, bounds, scale = matchcase.make_case(**kw)
         for th in ths:

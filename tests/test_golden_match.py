@@ -11,7 +11,7 @@ import matchcase
 
 HERE = Path(__file__).resolve().parent
 sys.path.insert(0, str(HERE / "golden"))
-from make_golden_match import CASES  # noqa: E402
+from make_golden_match import CASES, LOCAL_CASES  # noqa: E402
 
 
 def _golden():
@@ -55,3 +55,38 @@ def test_cuda_reproduces_the_reference_matcher(name, oracle_built):
                                              check_orientation=bool(ori), use_stereo=stereo)
             key = f"{name}_th{int(th)}_ori{ori}"
             assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+
+
+@pytest.mark.parametrize("name", sorted(LOCAL_CASES))
+def test_oracle_reproduces_the_reference_local_matcher(name, oracle_built):
+    g = _golden()
+    kw, ths = LOCAL_CASES[name]
+    cur, bounds, scale, mps, occ = matchcase.make_local_case(**kw)
+    for th in ths:
+        m, nm = oracle_built.search_local_points(cur, bounds, scale, mps, occ, th, 0.8)
+        key = f"{name}_th{int(th)}"
+        assert len(mps["flags"]) == g[key + "_nm"][1], "the scenario is not the one the golden file was made from"
+        assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(LOCAL_CASES))
+def test_cuda_reproduces_the_reference_local_matcher(name, oracle_built):
+    from orb_slam2_test_b200 import ORBextractor, synth
+    g = _golden()
+    kw, ths = LOCAL_CASES[name]
+    cur, bounds, scale, mps, occ = matchcase.make_local_case(**kw)
+    stereo = kw.get("stereo", True)
+    shape, seed, nf = kw.get("shape", synth.KITTI_SHAPE), kw["seed"], kw.get("nf", 2000)
+    K, bf = kw.get("K", matchcase.KITTI_K), kw.get("bf", matchcase.KITTI_BF)
+    ext = ORBextractor(nf, 1.2, 8, 20, 7)
+    ext.set_camera(K, kw.get("dist", (0.0, 0.0, 0.0, 0.0)))
+    ext(synth.make_frame(shape, seed=seed, frame=1, eye=0))
+    if stereo:
+        right = ORBextractor(nf, 1.2, 8, 20, 7)
+        right(synth.make_frame(shape, seed=seed, frame=1, eye=1))
+        ext.stereo_match(right, bf, bf / K[0])
+    for th in ths:
+        m, nm = ext.search_local_points(mps, occ, th, 0.8, use_stereo=stereo)
+        key = f"{name}_th{int(th)}"
+        assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key

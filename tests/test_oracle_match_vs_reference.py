@@ -54,3 +54,21 @@ def test_points_behind_and_outside(oracle_built, ref):
     want, wnm = ref.search_by_projection(cur, last, cam, bounds, scale, 15.0)
     got, nm = oracle_built.search_by_projection(cur, last, cam, bounds, scale, 15.0)
     assert nm == wnm == 0 and np.array_equal(got, want) and (got == -1).all()
+
+
+# ---- the local-map matcher: ORBmatcher::SearchByProjection(F, vpMapPoints, th), src/ORBmatcher.cc:59-154 ----
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, copies=3, obs_rate=0.5), dict(seed=3, copies=4, obs_rate=1.0),
+                                dict(seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0,
+                                     stereo=False, nf=1000)], ids=["kitti", "kitti-half-observed", "kitti-crowded", "tum-mono"])
+def test_local_map_matcher(kw, oracle_built, ref):
+    """RadiusByViewingCos either side of 0.998, th = 1 (no factor) / 3 / 5, two ratio thresholds, slots occupied by the
+    motion-model matcher with and without observations"""
+    cur, bounds, scale, mps, occ = matchcase.make_local_case(**kw)
+    assert (occ == 2).sum() > 100 and (occ == 1).sum() > 10
+    for th in (1.0, 3.0, 5.0):
+        for ratio in (0.8, 0.6):
+            want, wnm = ref.search_local_points(cur, bounds, scale, mps, occ, th, ratio)
+            got, nm = oracle_built.search_local_points(cur, bounds, scale, mps, occ, th, ratio)
+            assert np.array_equal(got, want) and nm == wnm, f"th={th} ratio={ratio}"
+            assert not (got[occ == 2] >= 0).any()
