@@ -379,6 +379,48 @@ def poststep_section(ORBextractor, synth, local):
     return out
 
 
+def tum_section(ORBextractor, synth, local):
+    """BASELINE.json configs[0] / configs[1]: TUM shape (640x480), 1000 keypoints (TUM1.yaml) and the 2000-keypoint
+    monocular-initialisation extractor -- device-resident throughput (512 frames per call, CUDA events) and the
+    single-frame host-call latency, beside the headline KITTI numbers."""
+    import torch
+    F = 512
+    uniq = np.stack([synth.make_frame(synth.TUM_SHAPE, seed=7, frame=f) for f in range(UNIQUE)])
+    batch = np.ascontiguousarray(uniq[np.arange(F) % UNIQUE])
+    dev = torch.from_numpy(batch).cuda(local)
+    out = {}
+    for name, nf in (("T1k", 1000), ("T2k", 2000)):
+        ext = ORBextractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=F, want_pyramid=False)
+        for _ in range(3):
+            ext.extract_device(dev.data_ptr(), F, 640, 480)
+        ext.sync()
+        ext.timer_start()
+        for _ in range(5):
+            ext.extract_device(dev.data_ptr(), F, 640, 480)
+        ext.timer_stop()
+        ext.sync()
+        ms = ext.timer_ms() / 5
+        res = ext.fetch()
+        one = ORBextractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
+        img = batch[0].copy()
+        ts = []
+        for it in range(220):
+            t1 = time.perf_counter()
+            one._lib.borb_extract_host(one._h, img.ctypes.data, 1, 640, 480, 640, 0, 0)
+            if it >= 20:
+                ts.append((time.perf_counter() - t1) * 1e6)
+        e = {"nfeatures": nf, "frames_per_s_device_resident": F / (ms / 1e3), "ms_per_512_frames": ms,
+             "keypoints_per_frame": float(np.mean([len(k) for k, _ in res[:UNIQUE]])), "latency_p50_us": float(np.percentile(ts, 50))}
+        try:
+            from oracle.pyoracle import Oracle
+            ok, od = Oracle(nf, SCALE, NLEVELS, INI_TH, MIN_TH).extract(batch[0])
+            e["parity_check"] = "bit-exact" if (res[0][0].tobytes() == ok.tobytes() and res[0][1].tobytes() == od.tobytes()) else "MISMATCH"
+        except Exception as ex:
+            e["parity_check"] = f"unavailable ({type(ex).__name__})"
+        out[name] = e
+    return out
+
+
 def matcher_section(ORBextractor, synth, local):
     """SURVEY.md 8(f)-4, first consumer: the tracking thread's frame-to-frame matcher
     ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) on the device
@@ -694,7 +736,7 @@ def run_ours(args, rank, world, local):
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
-    stereo = prestep = poststep = matcher = None
+    stereo = prestep = poststep = matcher = tum = None
     if rank == 0:
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
@@ -737,6 +779,7 @@ def run_ours(args, rank, world, local):
         prestep = prestep_section(ORBextractor, synth, local, measured_peak()[0])
         poststep = poststep_section(ORBextractor, synth, local)
         matcher = matcher_section(ORBextractor, synth, local)
+        tum = tum_section(ORBextractor, synth, local)
 
     if rank != 0:
         return
@@ -782,6 +825,7 @@ def run_ours(args, rank, world, local):
         "prestep": prestep,
         "poststep": poststep,
         "matcher": matcher,
+        "tum": tum,
         "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,
     }
