@@ -119,6 +119,10 @@ struct borb_extractor {
     BlurMaps blur_maps;                 /* the same planes with K5's box */
     DescMaps desc_maps;                 /* unblurred + blurred planes with K4/K6's boxes, and the plan fields they read */
     int chunk = 0; /* frames per pass of the kernel chain (0 = whole call) */
+    /* side stream for the latency shape: K5 (blur) needs only the pyramid, so for a frame or two it runs beside
+     * K2 + K3 (fork / join by events; inside a capture this becomes a parallel graph branch) */
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
@@ -586,6 +590,19 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         }
     }
     STAGE(1);
+    /* latency shape (a frame or two: every grid is far smaller than the machine): the blur runs beside FAST and the
+     * quadtree.  Throughput shapes keep the serial chain: measured no gain there (every kernel is issue-bound and the
+     * quadtree's CTAs hold an SM's shared memory), and the stage timers describe a serial chain. */
+    static const bool blur_serial = getenv("BORB_BLUR_SERIAL") != nullptr; /* A/B knob */
+    const bool blur_beside = !blur_serial && !stage_events && n * P.nlevels <= 2 * h->n_sm;
+#define K5_ON(S_) k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, BLUR_SMEM_BYTES, S_>>>( \
+        h->plan, h->blur_maps, h->d_tiles, f0, h->d_blur)
+    if (blur_beside) {
+        CU(cudaEventRecord(h->ev_fork, st));
+        CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+        K5_ON(h->stream2);
+        CU(cudaEventRecord(h->ev_join, h->stream2));
+    }
     {   /* K2: persistent CTAs, a multiple of the SM count, walking (cell, frame) with strides
          * (gridDim.x, gridDim.y); small jobs get one CTA per cell */
         int per_sm = 256; /* far more CTAs than fit at once: the hardware scheduler evens out the uneven
@@ -612,8 +629,9 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             h->plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
     STAGE(3);
     /* the descriptors address the whole slab: frame index = f0 + blockIdx.y */
-    k_blur_strips<<<dim3((P.n_tiles + BLUR_NT / 32 - 1) / (BLUR_NT / 32), n), BLUR_NT, BLUR_SMEM_BYTES, st>>>(
-        h->plan, h->blur_maps, h->d_tiles, f0, h->d_blur);
+    if (blur_beside) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
+    else K5_ON(st);
+#undef K5_ON
     STAGE(4);
     /* keypoint slots per warp: 16 when there are plenty of frames, 1 for a single frame */
     const int kpw = std::max(1, std::min(DESC_KPW, n / 4));
@@ -744,6 +762,9 @@ int borb_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int 
     const char *ng = getenv("BORB_NO_GRAPH");
     h->use_graph = !(ng && ng[0] == '1');
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
     if (e == cudaSuccess) e = cudaEventCreate(&h->evt0);
@@ -774,6 +795,9 @@ void borb_destroy(borb_extractor *h)
     if (h->evt1) cudaEventDestroy(h->evt1);
     for (int i = 0; i < 8; ++i) if (h->evs[i]) cudaEventDestroy(h->evs[i]);
     if (h->ev_peer) cudaEventDestroy(h->ev_peer);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
