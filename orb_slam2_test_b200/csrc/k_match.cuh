@@ -87,7 +87,7 @@ __device__ __forceinline__ int mt_bin(float a_last, float a_cur)
     return bin;
 }
 
-#define MT_K 8            /* cached candidates per query */
+#define MT_K 8            /* cached candidates per query (M1b loads them as two uint4) */
 #define MT_CAND_NT 256    /* M1a: 8 queries per CTA */
 #define MT_NOKEY 0xffffffffu
 
@@ -161,8 +161,8 @@ __device__ __forceinline__ int mt_candidate(const MtQuery &Q, int i2, const Borb
 }
 
 /* last frame / local map: geo [4n], octave [n], desc [n] x 32 B (16-byte aligned), flags [n] (bit 0 map point,
- * bit 1 Observations() > 0, bit 2 outlier).  Out: cache [n_last][MT_K] keys (distance << 16 | list
- * position q, ascending; MT_NOKEY = none), more [n_last] = the query had more than MT_K candidates. */
+ * bit 1 Observations() > 0, bit 2 outlier).  Out: cache [n_last][MT_K] entries (distance << 16 | keypoint
+ * index, in ascending (distance, list position q) order; MT_NOKEY = none), more [n_last] = the query had more than MT_K candidates. */
 template <int MODE>
 __global__ void __launch_bounds__(MT_CAND_NT)
 k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
@@ -217,6 +217,8 @@ k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__re
         uint32_t v = T[0];
 #pragma unroll
         for (int k = 1; k < MT_K; ++k) if (lane == k) v = T[k];
+        /* the order is fixed now: keep (distance << 16 | keypoint index), which is what the rounds of M1b read */
+        if (v != MT_NOKEY) v = (v & 0xffff0000u) | (uint32_t)cell_idx[v & 0xffffu];
         cache[(size_t)i * MT_K + lane] = v;
     }
     if (lane == 0) more[i] = cnt > MT_K;
@@ -258,15 +260,26 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
         __syncthreads();
         for (int i = tid; i < n_last; i += MT_NT) {
             int ch = -1;
+            /* the query's cached entries and who holds each of them, loaded side by side (two 16-byte loads, then
+             * MT_K independent ones) */
+            uint32_t keys[MT_K];
+            int held_by[MT_K];
+            {
+                const uint4 k0 = reinterpret_cast<const uint4 *>(cache)[(size_t)i * (MT_K / 4)];
+                const uint4 k1 = reinterpret_cast<const uint4 *>(cache)[(size_t)i * (MT_K / 4) + 1];
+                keys[0] = k0.x; keys[1] = k0.y; keys[2] = k0.z; keys[3] = k0.w;
+                keys[4] = k1.x; keys[5] = k1.y; keys[6] = k1.z; keys[7] = k1.w;
+#pragma unroll
+                for (int k = 0; k < MT_K; ++k) held_by[k] = keys[k] != MT_NOKEY ? tk_prev[keys[k] & 0xffffu] : 0x7fffffff;
+            }
             if (MODE == 1) {
                 bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
 #pragma unroll
                 for (int k = 0; k < MT_K; ++k) {
                     if (!all_held) continue;
-                    const uint32_t key = cache[(size_t)i * MT_K + k];
+                    const uint32_t key = keys[k];
                     if (key == MT_NOKEY || (key >> 16) > MT_TH_HIGH) { all_held = false; continue; }
-                    const int c = cell_idx[key & 0xffffu];
-                    if (tk_prev[c] >= i) { ch = c; all_held = false; }
+                    if (held_by[k] >= i) { ch = (int)(key & 0xffffu); all_held = false; }
                 }
                 if (all_held && more[i]) { /* rare: walk the cells again, now with the holders known */
                     atomicAdd(&s_rescans, 1);
@@ -292,10 +305,10 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
 #pragma unroll
                 for (int k = 0; k < MT_K; ++k) {
                     if (decided) continue;
-                    const uint32_t key = cache[(size_t)i * MT_K + k];
+                    const uint32_t key = keys[k];
                     if (key == MT_NOKEY) { decided = true; continue; }
-                    const int c = cell_idx[key & 0xffffu];
-                    if (tk_prev[c] < i) continue;
+                    const int c = (int)(key & 0xffffu);
+                    if (held_by[k] < i) continue;
                     const int d = (int)(key >> 16);
                     if (found == 0) { bd = d; bl = kp[c].octave; bidx = c; found = 1; if (d > MT_TH_HIGH) decided = true; }
                     else { bd2 = d; bl2 = kp[c].octave; found = 2; decided = true; }
