@@ -1355,17 +1355,22 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     const uint8_t *l_flags = dp + 56 * c;
     const int *cs = cur->d_cell_start + (size_t)frame * (FR_CELLS + 1), *ci = cur->d_cell_idx + fo;
     const int cand_grid = (n + MT_CAND_NT / 32 - 1) / (MT_CAND_NT / 32);
+    const size_t tk_smem = 2 * K * 4 <= 96 * 1024 ? 2 * K * 4 : 0; /* takers in shared memory when they fit */
+    if (tk_smem > 48 * 1024) {
+        CU(cudaFuncSetAttribute(k_match_resolve<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
+        CU(cudaFuncSetAttribute(k_match_resolve<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
+    }
 #define MATCH_LAUNCH(MODE)                                                                                                   \
     do {                                                                                                                     \
         if (n > 0)                                                                                                           \
             k_match_candidates<MODE><<<cand_grid, MT_CAND_NT, 0, st>>>(                                                       \
                 mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4, \
                 d_ur, d_occ, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);                                 \
-        k_match_resolve<MODE><<<1, MT_NT, 0, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, \
+        k_match_resolve<MODE><<<1, MT_NT, tk_smem, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, \
                                                    cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame, d_ur, d_occ, l_geo,  \
                                                    l_angle, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more,           \
                                                    cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,                 \
-                                                   cur->d_mt_match + K);                                                     \
+                                                   cur->d_mt_match + K, tk_smem ? 1 : 0);                                    \
     } while (0)
     if (mode == 1) MATCH_LAUNCH(1); else MATCH_LAUNCH(2);
 #undef MATCH_LAUNCH

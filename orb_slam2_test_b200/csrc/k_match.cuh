@@ -236,9 +236,13 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                 const float *__restrict__ l_geo, const float *__restrict__ l_angle, const int *__restrict__ l_octave,
                 const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
                 const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more,
-                int *__restrict__ choice, int *__restrict__ taker, int kp_total, int *__restrict__ match,
-                int *__restrict__ nm)
+                int *__restrict__ choice, int *__restrict__ taker_g, int kp_total, int *__restrict__ match,
+                int *__restrict__ nm, int taker_in_smem)
 {
+    /* the two taker arrays live in shared memory when they fit (2 x kp_total ints): a round is then three
+     * barriers apart instead of three global-memory round trips */
+    extern __shared__ int mt_taker_s[];
+    int *taker = taker_in_smem ? mt_taker_s : taker_g;
     __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans;
     const int tid = threadIdx.x;
     const int n_cur = min(*n_cur_p, kp_total), n_last = mp.n_last;
