@@ -269,4 +269,89 @@ int mo_search_local_points(const mo_frame *cur, const float *bounds, const float
     return nmatches;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f> &vbPrevMatched,
+ *     vector<int> &vnMatches12, int windowSize)      /root/reference/src/ORBmatcher.cc:487-632
+ * -- the matcher of Tracking::MonocularInitialization (src/Tracking.cc:570-646): level-0 keypoints
+ * of the initial frame F1 against the level-0 keypoints of F2 in a window around where each was
+ * matched last; TH_LOW = 50 (:34), ratio test against (float)bestDist2 * mfNNratio, a match on an
+ * already matched F2 keypoint needs a strictly smaller distance and then takes it over (:526-527,
+ * :552-558), orientation histogram over ALL accepted matches incl. the ones taken over later (:562-577).
+ * f1: kps (octave, angle), desc; f2: kps, un_xy, desc, grid.  prev[2 n1] is vbPrevMatched, updated in
+ * place for the matched entries (:621-623).  matches12[n1] = vnMatches12.  Returns nmatches.
+ */
+int mo_search_for_initialization(const mo_frame *f1, const mo_frame *f2, const float *bounds, float *prev,
+                                 int window_size, float nnratio, int check_ori, int32_t *matches12)
+{
+    const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+    const float winv = (float)MO_COLS / (max_x - min_x), hinv = (float)MO_ROWS / (max_y - min_y);
+    const mo_kp *k1 = reinterpret_cast<const mo_kp *>(f1->kps), *k2 = reinterpret_cast<const mo_kp *>(f2->kps);
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + f2->grid_count[c];
+    int nmatches = 0;
+    for (int i = 0; i < f1->n; ++i) matches12[i] = -1;
+    std::vector<int> hist[MO_HISTO];
+    const float factor = 1.0f / MO_HISTO;
+    std::vector<int> matched_distance(f2->n, INT_MAX), matches21(f2->n, -1);
+    const float r = (float)window_size;
+    for (int i1 = 0; i1 < f1->n; ++i1) {
+        if (k1[i1].octave > 0) continue;
+        const float x = prev[2 * i1], y = prev[2 * i1 + 1];
+        const int cx0 = std::max(0, (int)std::floor((x - min_x - r) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((x - min_x + r) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((y - min_y - r) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((y - min_y + r) * hinv));
+        if (cy1 < 0) continue;
+        int best = INT_MAX, best2 = INT_MAX, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int i2 = f2->grid_idx[q];
+                    if (k2[i2].octave < 0 || k2[i2].octave > 0) continue; /* minLevel = maxLevel = 0 */
+                    const float dx = f2->un_xy[2 * i2] - x, dy = f2->un_xy[2 * i2 + 1] - y;
+                    if (!(std::fabs(dx) < r && std::fabs(dy) < r)) continue;
+                    const int d = mo_hamming256(f1->desc + (size_t)i1 * 32, f2->desc + (size_t)i2 * 32);
+                    if (matched_distance[i2] <= d) continue;
+                    if (d < best) { best2 = best; best = d; best_idx = i2; }
+                    else if (d < best2) best2 = d;
+                }
+            }
+        if (best <= 50) {
+            if ((float)best < (float)best2 * nnratio) {
+                if (matches21[best_idx] >= 0) { matches12[matches21[best_idx]] = -1; --nmatches; }
+                matches12[i1] = best_idx;
+                matches21[best_idx] = i1;
+                matched_distance[best_idx] = best;
+                ++nmatches;
+                if (check_ori) {
+                    float rot = k1[i1].angle - k2[best_idx].angle;
+                    if (rot < 0.0f) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == MO_HISTO) bin = 0;
+                    hist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (check_ori) {
+        int sz[MO_HISTO], i1, i2, i3;
+        for (int b = 0; b < MO_HISTO; ++b) sz[b] = (int)hist[b].size();
+        mo_three_maxima(sz, MO_HISTO, &i1, &i2, &i3);
+        for (int b = 0; b < MO_HISTO; ++b) {
+            if (b == i1 || b == i2 || b == i3) continue;
+            for (size_t j = 0; j < hist[b].size(); ++j) {
+                const int idx1 = hist[b][j];
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; --nmatches; }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < f1->n; ++i1)
+        if (matches12[i1] >= 0) { prev[2 * i1] = f2->un_xy[2 * matches12[i1]]; prev[2 * i1 + 1] = f2->un_xy[2 * matches12[i1] + 1]; }
+    return nmatches;
+}
+
 } // extern "C"

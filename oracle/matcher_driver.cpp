@@ -178,4 +178,44 @@ int refmatch_search_local_points(const refmatch_frame *cur, const float *bounds,
     return nm;
 }
 
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:487-632).
+ * f1 / f2 as refmatch_frame (f1 needs no grid; Tcw unused); prev[2 n1] = vbPrevMatched in and out. */
+int refmatch_search_for_initialization(const refmatch_frame *f1, const refmatch_frame *f2, const float *bounds, float *prev,
+                                       int window_size, float nnratio, int check_ori, int32_t *matches12)
+{
+    Frame::mnMinX = bounds[0]; Frame::mnMaxX = bounds[1]; Frame::mnMinY = bounds[2]; Frame::mnMaxY = bounds[3];
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);
+    Frame::mbInitialComputations = false;
+    Frame F[2];
+    const refmatch_frame *src[2] = {f1, f2};
+    for (int s = 0; s < 2; ++s) {
+        Frame &f = F[s];
+        const refmatch_frame &r = *src[s];
+        f.N = r.n;
+        f.mvKeys.resize(r.n);
+        if (r.n) std::memcpy(f.mvKeys.data(), r.kps, (size_t)r.n * 28);
+        f.mvKeysUn = f.mvKeys;
+        for (int i = 0; i < r.n; ++i) { f.mvKeysUn[i].pt.x = r.un_xy[2 * i]; f.mvKeysUn[i].pt.y = r.un_xy[2 * i + 1]; }
+        f.mDescriptors = cv::Mat(r.n, 32, CV_8UC1);
+        for (int i = 0; i < r.n; ++i) std::memcpy(f.mDescriptors.ptr(i), r.desc + (size_t)i * 32, 32);
+        if (r.grid_count) {
+            int k = 0;
+            for (int i = 0; i < FRAME_GRID_COLS; ++i)
+                for (int j = 0; j < FRAME_GRID_ROWS; ++j) {
+                    const int c = r.grid_count[i * FRAME_GRID_ROWS + j];
+                    f.mGrid[i][j].assign(r.grid_idx + k, r.grid_idx + k + c);
+                    k += c;
+                }
+        }
+    }
+    std::vector<cv::Point2f> vbPrev(f1->n);
+    for (int i = 0; i < f1->n; ++i) vbPrev[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher matcher(nnratio, check_ori != 0);
+    const int nm = matcher.SearchForInitialization(F[0], F[1], vbPrev, m12, window_size);
+    for (int i = 0; i < f1->n; ++i) { matches12[i] = m12[i]; prev[2 * i] = vbPrev[i].x; prev[2 * i + 1] = vbPrev[i].y; }
+    return nm;
+}
+
 } // extern "C"

@@ -290,6 +290,45 @@ def search_local_points(cur, bounds, scale, mps, occupied, th=1.0, nnratio=0.8):
     return _local_call(Oracle.load().mo_search_local_points, cur, bounds, scale, mps, occupied, th, nnratio)
 
 
+def _init_call(fn, f1: dict, f2: dict, bounds, prev, window: int, nnratio: float, check_ori: bool):
+    """Common marshalling for mo_search_for_initialization / refmatch_search_for_initialization.
+    f1: kps, un_xy, desc; f2: kps, un_xy, desc, cell_start, cell_idx; prev [n1,2] f32 = vbPrevMatched.
+    -> (vnMatches12 [n1] i32, updated vbPrevMatched [n1,2], nmatches)."""
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+
+    def frame(d, with_grid):
+        f = _MatchFrame()
+        f.n = len(d["kps"])
+        f.kps = arr(d["kps"], KP_DTYPE)
+        f.un_xy = arr(d["un_xy"], np.float32)
+        f.desc = arr(d["desc"], np.uint8)
+        f.u_right = None
+        if with_grid:
+            f.grid_count = arr(np.diff(d["cell_start"]), np.int32)
+            f.grid_idx = arr(d["cell_idx"], np.int32)
+        f.Tcw = None
+        return f
+
+    a, b = frame(f1, False), frame(f2, True)
+    pv = np.array(prev, np.float32, copy=True, order="C")
+    out = np.full(max(a.n, 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_float, C.c_int, _vp]
+    nm = fn(C.addressof(a), C.addressof(b), arr(bounds, np.float32), pv.ctypes.data, int(window), float(nnratio),
+            int(check_ori), out.ctypes.data)
+    return out[:a.n], pv, int(nm)
+
+
+def search_for_initialization(f1, f2, bounds, prev, window=100, nnratio=0.9, check_ori=True):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:487-632) restated (oracle/match_oracle.cpp)."""
+    return _init_call(Oracle.load().mo_search_for_initialization, f1, f2, bounds, prev, window, nnratio, check_ori)
+
+
 class RefMatcher:
     """The reference's own src/ORBmatcher.cc + src/Frame.cc (oracle/_ref/librefmatch.so)."""
 
@@ -310,6 +349,12 @@ class RefMatcher:
         if cls._lib is None:
             cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
         return _local_call(cls._lib.refmatch_search_local_points, cur, bounds, scale, mps, occupied, th, nnratio)
+
+    @classmethod
+    def search_for_initialization(cls, f1, f2, bounds, prev, window=100, nnratio=0.9, check_ori=True):
+        if cls._lib is None:
+            cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
+        return _init_call(cls._lib.refmatch_search_for_initialization, f1, f2, bounds, prev, window, nnratio, check_ori)
 
 
 def _cam(K, dist) -> np.ndarray:

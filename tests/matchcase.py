@@ -147,3 +147,27 @@ def make_local_case(seed=0, copies=2, obs_rate=0.9, **kw):
     flags = ((has & inside).astype(np.uint8) | ((rng.random(N) < obs_rate).astype(np.uint8) << 1))
     mps = {"proj": proj, "desc": desc, "flags": flags, "level": level}
     return cur, bounds, scale, mps, occupied
+
+
+def make_init_case(seed=0, shape=synth.TUM_SHAPE, K=TUM1_K, dist=TUM1_D, nf=2000, step=1, frame=0, copies=1):
+    """Scenario for ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:487-632): the monocular-initialisation
+    extractor (2 x nFeatures, src/Tracking.cc:124-125) on an initial frame and on a later frame of the same
+    synthetic sequence; vbPrevMatched starts as the initial frame's undistorted keypoints (src/Tracking.cc:587-589).
+    -> (f1, f2, bounds, prev)"""
+    f1 = oracle_frame(synth.make_frame(shape, seed=seed, frame=frame), None, K, dist, 0.0, 0.0, nf)
+    f2 = oracle_frame(synth.make_frame(shape, seed=seed, frame=frame + step), None, K, dist, 0.0, 0.0, nf)
+    if copies > 1:  # several initial keypoints want the same current keypoint, at different distances: take-overs
+        rng = np.random.default_rng(7000 + seed)
+        n = len(f1["kps"])
+        desc = [f1["desc"]]
+        for _ in range(copies - 1):
+            d = f1["desc"].copy()
+            for i in range(n):
+                for b in rng.integers(0, 256, rng.integers(0, 9)):
+                    d[i, b >> 3] ^= np.uint8(1 << (b & 7))
+            desc.append(d)
+        f1 = dict(f1)
+        f1["kps"] = np.concatenate([f1["kps"]] * copies)
+        f1["un_xy"] = np.concatenate([f1["un_xy"]] * copies)
+        f1["desc"] = np.concatenate(desc)
+    return f1, f2, f2["bounds"], f1["un_xy"].copy()
