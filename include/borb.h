@@ -225,6 +225,26 @@ typedef struct borb_map_points {
 int borb_search_local_points(borb_extractor *cur, int frame, const borb_map_points *mps, const uint8_t *occupied,
                              float th, float nnratio, unsigned flags, int32_t *match, int *n_cur, int *nmatches);
 
+/* -- monocular-initialisation matcher: replaces ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2,
+ *    vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12, int windowSize)
+ *    (src/ORBmatcher.cc:487-632), called by Tracking::MonocularInitialization (src/Tracking.cc:570-646) --- */
+
+/* The initial frame F1 as the matcher reads it: octave[i] = F1.mvKeysUn[i].octave (only level 0 is
+ * matched), angle[i] = F1.mvKeysUn[i].angle, desc[32i..] = F1.mDescriptors.row(i). */
+typedef struct borb_init_frame {
+    int n;
+    const int32_t *octave;
+    const float *angle;
+    const uint8_t *desc;
+} borb_init_frame;
+
+/* F2 = frame `frame` of cur's last extract call (device-resident keypoints, descriptors, mvKeysUn, mGrid,
+ * bounds; borb_set_camera on).  prev_matched[2 n] = vbPrevMatched on entry, updated for the matched entries
+ * as the reference does (:621-623).  nnratio = mfNNratio (0.9 there), flags: BORB_MATCH_NO_ORIENTATION.
+ * matches12[i] = vnMatches12[i] (index into F2's keypoints or -1); *nmatches = the return value. */
+int borb_search_for_initialization(borb_extractor *cur, int frame, const borb_init_frame *f1, float *prev_matched,
+                                   int window_size, float nnratio, unsigned flags, int32_t *matches12, int *nmatches);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

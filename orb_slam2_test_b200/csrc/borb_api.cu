@@ -173,6 +173,10 @@ struct borb_extractor {
     uint32_t *d_mt_cache = nullptr; /* [mt_cap][MT_K] candidate keys */
     uint8_t *d_mt_more = nullptr, *d_mt_occ = nullptr, *h_mt_occ = nullptr; /* occupancy of the local-map matcher */
     int mt_rescans = 0;
+    /* monocular-initialisation matcher (M3): chooser lists [2][K][MT_CH] + counts [2][K], result [mt_cap] + F2's mvKeysUn */
+    uint32_t *d_mt_ent = nullptr;
+    int *d_mt_cnt = nullptr, *d_mt_m12 = nullptr, *h_mt_m12 = nullptr;
+    float *h_mt_unxy = nullptr;
     int mt_rounds = 0;
 
     std::vector<GraphEntry> graphs;
@@ -250,16 +254,17 @@ void free_geometry(borb_extractor *h)
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
-                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ};
+                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
-                    h->h_mt_last, h->h_mt_match, h->h_mt_occ};
+                    h->h_mt_last, h->h_mt_match, h->h_mt_occ, h->h_mt_m12, h->h_mt_unxy};
     for (void *p : host) if (p) cudaFreeHost(p);
     h->d_mt_last = h->h_mt_last = nullptr;
     h->mt_cap = 0;
     h->d_mt_choice = h->d_mt_taker = h->d_mt_match = h->h_mt_match = nullptr;
     h->d_mt_cache = nullptr; h->d_mt_more = nullptr; h->d_mt_occ = h->h_mt_occ = nullptr;
+    h->d_mt_ent = nullptr; h->d_mt_cnt = h->d_mt_m12 = h->h_mt_m12 = nullptr; h->h_mt_unxy = nullptr;
     h->d_gray = nullptr;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
@@ -1303,11 +1308,16 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         if (cur->d_mt_choice) cudaFree(cur->d_mt_choice);
         if (cur->d_mt_cache) cudaFree(cur->d_mt_cache);
         if (cur->d_mt_more) cudaFree(cur->d_mt_more);
+        if (cur->d_mt_m12) cudaFree(cur->d_mt_m12);
+        if (cur->h_mt_m12) cudaFreeHost(cur->h_mt_m12);
+        cur->d_mt_m12 = cur->h_mt_m12 = nullptr;
         cur->d_mt_last = cur->h_mt_last = nullptr; cur->d_mt_choice = nullptr; cur->mt_cap = 0;
         cur->d_mt_cache = nullptr; cur->d_mt_more = nullptr;
         CU(cudaMalloc(&cur->d_mt_last, cap * 57));
         CU(cudaMallocHost(&cur->h_mt_last, cap * 57));
-        CU(cudaMalloc(&cur->d_mt_choice, cap * 4));
+        CU(cudaMalloc(&cur->d_mt_choice, cap * 8));
+        CU(cudaMalloc(&cur->d_mt_m12, cap * 4));
+        CU(cudaMallocHost(&cur->h_mt_m12, cap * 4));
         CU(cudaMalloc(&cur->d_mt_cache, cap * MT_K * 4));
         CU(cudaMalloc(&cur->d_mt_more, cap));
         cur->mt_cap = cap;
@@ -1318,6 +1328,8 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         std::memcpy(hp, desc, un * 32);
         float *g = reinterpret_cast<float *>(hp + 32 * c);
         if (geo_stride == 4) std::memcpy(g, geo, un * 16);
+        else if (geo_stride == 2)
+            for (size_t i = 0; i < un; ++i) { g[4 * i] = geo[2 * i]; g[4 * i + 1] = geo[2 * i + 1]; g[4 * i + 2] = 0.f; g[4 * i + 3] = 0.f; }
         else
             for (size_t i = 0; i < un; ++i) { g[4 * i] = geo[3 * i]; g[4 * i + 1] = geo[3 * i + 1]; g[4 * i + 2] = geo[3 * i + 2]; g[4 * i + 3] = 0.f; }
         if (angle) std::memcpy(hp + 48 * c, angle, un * 4);
@@ -1372,7 +1384,35 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
                                                    cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,                 \
                                                    cur->d_mt_match + K, tk_smem ? 1 : 0);                                    \
     } while (0)
-    if (mode == 1) MATCH_LAUNCH(1); else MATCH_LAUNCH(2);
+    if (mode == 1) MATCH_LAUNCH(1);
+    else if (mode == 2) MATCH_LAUNCH(2);
+    else {
+        if (!cur->d_mt_ent) {
+            CU(cudaMalloc(&cur->d_mt_ent, 2 * K * MT_CH * 4));
+            CU(cudaMalloc(&cur->d_mt_cnt, 2 * K * 4));
+            CU(cudaMallocHost(&cur->h_mt_unxy, K * 8));
+        }
+        if (n > 0)
+            k_match_candidates<3><<<cand_grid, MT_CAND_NT, 0, st>>>(
+                mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4,
+                nullptr, nullptr, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);
+        k_match_resolve_init<<<1, MT_NT, 0, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci,
+                                                  cur->d_bounds + (size_t)frame * 4, l_geo, l_angle, l_oct, l_desc, l_flags,
+                                                  cur->d_mt_cache, cur->d_mt_more, cur->d_mt_choice, cur->d_mt_ent, cur->d_mt_cnt,
+                                                  (int)K, cur->d_mt_match, cur->d_mt_m12, cur->d_mt_match + K);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(cur->h_mt_m12, cur->d_mt_m12, std::max<size_t>(un, 1) * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(cur->h_mt_match + K, cur->d_mt_match + K, 16, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(cur->h_mt_unxy, cur->d_un_xy + fo, K * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        cur->mt_rounds = cur->h_mt_match[K + 1];
+        cur->mt_rescans = cur->h_mt_match[K + 2];
+        if (cur->h_mt_match[K + 3]) return fail(BORB_ERR_STATE, "initialisation matcher: more than %d queries chose one keypoint in a round", MT_CH);
+        if (n) std::memcpy(match, cur->h_mt_m12, un * 4);
+        if (nmatches) *nmatches = cur->h_mt_match[K];
+        if (n_cur) *n_cur = n;
+        return BORB_OK;
+    }
 #undef MATCH_LAUNCH
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
@@ -1434,6 +1474,31 @@ int borb_search_local_points(borb_extractor *cur, int frame, const borb_map_poin
     mp.nnratio = nnratio;
     return run_matcher(cur, frame, 2, mps->n, mps->proj, 4, mps->desc, mps->flags, mps->level, nullptr, occupied, mp,
                        (flags & BORB_MATCH_USE_STEREO) != 0, match, n_cur, nmatches);
+}
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:487-632) */
+int borb_search_for_initialization(borb_extractor *cur, int frame, const borb_init_frame *f1, float *prev_matched,
+                                   int window_size, float nnratio, unsigned flags, int32_t *matches12, int *nmatches)
+{
+    if (!cur || !f1 || !matches12 || (f1->n > 0 && (!prev_matched || !f1->octave || !f1->angle || !f1->desc)))
+        return fail(BORB_ERR_ARG, "null argument");
+    if (f1->n < 0 || window_size < 0) return fail(BORB_ERR_ARG, "n %d, window %d", f1->n, window_size);
+    MatchParams mp;
+    std::memset(&mp, 0, sizeof mp);
+    mp.th = (float)window_size;
+    mp.nnratio = nnratio;
+    mp.check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
+    std::vector<uint8_t> qf((size_t)std::max(f1->n, 1));
+    std::vector<int32_t> lvl((size_t)std::max(f1->n, 1), 0);
+    for (int i = 0; i < f1->n; ++i) qf[i] = f1->octave[i] > 0 ? 0 : 1; /* only level 0 is searched (:507-508) */
+    int nm = 0;
+    const int rc = run_matcher(cur, frame, 3, f1->n, prev_matched, 2, f1->desc, qf.data(), lvl.data(), f1->angle, nullptr, mp,
+                               false, matches12, nullptr, &nm);
+    if (rc != BORB_OK) return rc;
+    for (int i = 0; i < f1->n; ++i) /* :621-623 */
+        if (matches12[i] >= 0) { prev_matched[2 * i] = cur->h_mt_unxy[2 * matches12[i]]; prev_matched[2 * i + 1] = cur->h_mt_unxy[2 * matches12[i] + 1]; }
+    if (nmatches) *nmatches = nm;
+    return BORB_OK;
 }
 
 int borb_match_rounds(const borb_extractor *cur) { return cur ? cur->mt_rounds | (cur->mt_rescans << 8) : 0; }

@@ -98,6 +98,7 @@ struct MtQuery { /* what the candidate scan of one query needs (:1537-1572) */
 };
 
 /* MODE 1: the frame-to-frame matcher (geo = world position; src/ORBmatcher.cc:1537-1572).
+ * MODE 3: the monocular-initialisation matcher (k_match_resolve_init below): geo = vbPrevMatched[i1].
  * MODE 2: the local-map matcher, ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154) of
  *         Tracking::SearchLocalPoints: geo = mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos as
  *         Frame::isInFrustum left them, lvl = mnTrackScaleLevel; r = RadiusByViewingCos (:156-162), r *= th unless
@@ -120,6 +121,14 @@ __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *
         else if (mp.dir == 2) { Q.min_level = 0; Q.max_level = oct; }
         else { Q.min_level = oct - 1; Q.max_level = oct + 1; }
         Q.ur = fmaf(-mp.mbf, invzc, Q.u);
+    } else if (MODE == 3) { /* SearchForInitialization: window of windowSize (= mp.th) around vbPrevMatched, level 0 only (:510) */
+        Q.radius = mp.th;
+        Q.u = g.x;
+        Q.v = g.y;
+        Q.ur = 0.f;
+        Q.min_level = 0;
+        Q.max_level = 0;
+        Q.ok = true;
     } else {
         float r = (double)g.w > 0.998 ? 2.5f : 4.0f;
         if (mp.th != 1.0f) r *= mp.th;
@@ -379,6 +388,147 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
         __syncthreads();
     }
     if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; }
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * M3: ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+ *     /root/reference/src/ORBmatcher.cc:487-632, the matcher of Tracking::MonocularInitialization.
+ * Candidates by k_match_candidates<3>.  The sequential rule here: a match on an F2 keypoint that is
+ * already matched needs a strictly smaller distance (vMatchedDistance[i2] <= dist skips it, :526-527) and
+ * then takes the keypoint over (:552-558).  With a(i) = the accepted (keypoint, distance) of query i,
+ * candidate (c, d) is open to query i iff no earlier query i' < i has a(i') = (c, d') with d' <= d; a(i)
+ * depends on earlier queries only, so the rounds below (all queries choose given the previous round's
+ * chooser lists) reach the unique sequential solution.  At the end keypoint c belongs to its LAST
+ * accepted chooser, the orientation histogram counts every accepted query (also the ones taken over
+ * later, :562-577), and entries of discarded bins are cleared only where they still hold (:606-613).
+ * ent [2][kp_total][MT_CH] chooser records (query << 8 | distance), cnt [2][kp_total]; overflow of a list
+ * is reported through nm[3] (the host turns it into an error, nothing is returned silently wrong).
+ */
+#define MT_CH 32
+#define MT_TH_LOW 50
+
+__device__ __forceinline__ bool mt_init_closed(const uint32_t *__restrict__ ent, const int *__restrict__ cnt, int c, int i, int d)
+{
+    const int n = min(cnt[c], MT_CH);
+    for (int k = 0; k < n; ++k) {
+        const uint32_t e = ent[(size_t)c * MT_CH + k];
+        if ((int)(e >> 8) < i && (int)(e & 0xffu) <= d) return true;
+    }
+    return false;
+}
+
+__global__ void __launch_bounds__(MT_NT, 1)
+k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__restrict__ kp,
+                     const uint8_t *__restrict__ desc, const float2 *__restrict__ un_xy,
+                     const int *__restrict__ cell_start, const int *__restrict__ cell_idx,
+                     const float *__restrict__ bounds, const float *__restrict__ l_geo,
+                     const float *__restrict__ l_angle, const int *__restrict__ l_octave,
+                     const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
+                     const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more,
+                     int *__restrict__ choice /* [n][2]: keypoint, distance */, uint32_t *__restrict__ ent,
+                     int *__restrict__ cnt, int kp_total, int *__restrict__ owner /* [kp_total] */,
+                     int *__restrict__ m12 /* [n] */, int *__restrict__ nm)
+{
+    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans, s_overflow;
+    const int tid = threadIdx.x, n1 = mp.n_last;
+    const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+    const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
+    if (tid == 0) { s_nm = 0; s_rescans = 0; s_overflow = 0; }
+    if (tid < MT_HISTO) { s_hist[tid] = 0; s_keep[tid] = 1; }
+    for (int i = tid; i < n1; i += MT_NT) { choice[2 * i] = -1; choice[2 * i + 1] = 0; }
+    for (int c = tid; c < kp_total; c += MT_NT) { cnt[c] = 0; owner[c] = -1; }
+    __syncthreads();
+
+    int round = 0;
+    for (;; ++round) {
+        const uint32_t *ent_prev = ent + (size_t)(round & 1) * kp_total * MT_CH;
+        uint32_t *ent_new = ent + (size_t)((round + 1) & 1) * kp_total * MT_CH;
+        const int *cnt_prev = cnt + (round & 1) * kp_total;
+        int *cnt_new = cnt + ((round + 1) & 1) * kp_total;
+        for (int c = tid; c < kp_total; c += MT_NT) cnt_new[c] = 0;
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        for (int i = tid; i < n1; i += MT_NT) {
+            int found = 0, bd = 0x7fffffff, bd2 = 0x7fffffff, bidx = -1;
+            bool decided = !(l_flags[i] & 1u);
+#pragma unroll
+            for (int k = 0; k < MT_K; ++k) {
+                if (decided) continue;
+                const uint32_t key = cache[(size_t)i * MT_K + k];
+                if (key == MT_NOKEY) { decided = true; continue; }
+                const int c = (int)(key & 0xffffu), d = (int)(key >> 16);
+                if (found == 0 && d > MT_TH_LOW) { decided = true; continue; } /* the best open one can only be worse */
+                if (mt_init_closed(ent_prev, cnt_prev, c, i, d)) continue;
+                if (found == 0) { bd = d; bidx = c; found = 1; }
+                else { bd2 = d; found = 2; decided = true; }
+            }
+            if (!decided && more[i]) { /* fewer than two open candidates among the cached ones and there were more */
+                atomicAdd(&s_rescans, 1);
+                const MtQuery Q = mt_query<3>(mp, l_geo, 0, i, min_x, max_x, min_y, max_y, winv, hinv);
+                const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
+                bd = 0x7fffffff; bd2 = 0x7fffffff; bidx = -1;
+                if (Q.ok)
+                    for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
+                        const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
+                        for (int q = q0; q < q1; ++q) {
+                            const int i2 = cell_idx[q];
+                            const int d = mt_candidate(Q, i2, kp, un_xy, nullptr, nullptr, desc, d0, d1);
+                            if (d < 0 || mt_init_closed(ent_prev, cnt_prev, i2, i, d)) continue;
+                            if (d < bd) { bd2 = bd; bd = d; bidx = i2; }
+                            else if (d < bd2) bd2 = d;
+                        }
+                    }
+            }
+            int ch = -1, chd = 0;
+            if (bidx >= 0 && bd <= MT_TH_LOW && (float)bd < (float)bd2 * mp.nnratio) { ch = bidx; chd = bd; }
+            if (ch != choice[2 * i] || chd != choice[2 * i + 1]) { choice[2 * i] = ch; choice[2 * i + 1] = chd; s_changed = 1; }
+            if (ch >= 0) {
+                const int slot = atomicAdd(&cnt_new[ch], 1);
+                if (slot < MT_CH) ent_new[(size_t)ch * MT_CH + slot] = ((uint32_t)i << 8) | (uint32_t)chd;
+                else s_overflow = 1;
+            }
+        }
+        __syncthreads();
+        const int changed = s_changed;
+        __syncthreads();
+        if (!changed) break;
+    }
+
+    /* ---- ownership (the last accepted chooser), orientation histogram over every accepted query ---- */
+    for (int i = tid; i < n1; i += MT_NT) {
+        const int ch = choice[2 * i];
+        if (ch >= 0) {
+            atomicMax(&owner[ch], i);
+            if (mp.check_ori) atomicAdd(&s_hist[mt_bin(l_angle[i], kp[ch].angle)], 1);
+        }
+    }
+    __syncthreads();
+    if (mp.check_ori) {
+        if (tid == 0) {
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int b = 0; b < MT_HISTO; ++b) {
+                const int s = s_hist[b];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
+                else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
+                else if (s > max3) { max3 = s; ind3 = b; }
+            }
+            if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+            else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+            for (int b = 0; b < MT_HISTO; ++b) s_keep[b] = (b == ind1 || b == ind2 || b == ind3);
+        }
+        __syncthreads();
+    }
+    for (int i = tid; i < n1; i += MT_NT) {
+        const int ch = choice[2 * i];
+        int out = -1;
+        if (ch >= 0 && owner[ch] == i && (!mp.check_ori || s_keep[mt_bin(l_angle[i], kp[ch].angle)])) {
+            out = ch;
+            atomicAdd(&s_nm, 1);
+        }
+        m12[i] = out;
+    }
+    __syncthreads();
+    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; nm[3] = s_overflow; }
 }
 
 #endif

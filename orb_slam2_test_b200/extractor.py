@@ -38,7 +38,7 @@ SYMBOLS = [
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
     "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
     "borb_last_prestep_ms", "borb_set_camera", "borb_frame_grid",
-    "borb_search_by_projection", "borb_search_local_points", "borb_match_rounds", "borb_max_keypoints",
+    "borb_search_by_projection", "borb_search_local_points", "borb_search_for_initialization", "borb_match_rounds", "borb_max_keypoints",
 ]
 
 
@@ -110,6 +110,7 @@ def load_library() -> C.CDLL:
                                               C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.borb_search_local_points.argtypes = [_vp, C.c_int, _vp, _vp, C.c_float, C.c_float, C.c_uint, _vp,
                                              C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_search_for_initialization.argtypes = [_vp, C.c_int, _vp, _vp, C.c_int, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_match_rounds.argtypes = [_vp]
     lib.borb_max_keypoints.argtypes = [_vp]
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
@@ -128,6 +129,10 @@ def debug_sincos(radians: float):
     s, c = C.c_float(), C.c_float()
     lib.borb_debug_sincos(radians, C.byref(s), C.byref(c))
     return s.value, c.value
+
+
+class _InitFrame(C.Structure):  # == borb_init_frame
+    _fields_ = [("n", C.c_int), ("octave", _vp), ("angle", _vp), ("desc", _vp)]
 
 
 class _MapPoints(C.Structure):  # == borb_map_points
@@ -422,6 +427,22 @@ class ORBextractor:
                                                              th, nnratio, 4 if use_stereo else 0, out.ctypes.data,
                                                              C.byref(n), C.byref(nm)))
         return out[:n.value].copy(), nm.value
+
+    def search_for_initialization(self, f1: dict, prev, window: int = 100, nnratio: float = 0.9, frame: int = 0,
+                                  check_orientation: bool = True):
+        """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:487-632) with frame `frame` of this extractor's last
+        call as F2, on the device.  f1: dict with kps (octave, angle) and desc of the initial frame; prev [n1,2] f32 =
+        vbPrevMatched.  -> (vnMatches12 [n1] i32, updated vbPrevMatched, nmatches)."""
+        keep = [np.ascontiguousarray(f1["kps"]["octave"], np.int32), np.ascontiguousarray(f1["kps"]["angle"], np.float32),
+                np.ascontiguousarray(f1["desc"], np.uint8)]
+        fr = _InitFrame(len(keep[0]), *[a.ctypes.data for a in keep])
+        pv = np.array(prev, np.float32, copy=True, order="C")
+        out = np.full(max(fr.n, 1), -1, np.int32)
+        nm = C.c_int()
+        _check(self._lib, self._lib.borb_search_for_initialization(self._h, frame, C.addressof(fr), pv.ctypes.data, window,
+                                                                   nnratio, 0 if check_orientation else 2, out.ctypes.data,
+                                                                   C.byref(nm)))
+        return out[:fr.n].copy(), pv, nm.value
 
     def match_rounds(self) -> int:
         return self._lib.borb_match_rounds(self._h) & 0xff

@@ -144,3 +144,39 @@ def test_local_map_without_occupancy(oracle_built):
     want, wnm = oracle_built.search_local_points(cur, bounds, scale, mps, np.zeros(len(occ), np.uint8), 3.0, 0.8)
     got, nm = ext.search_local_points(mps, None, 3.0, 0.8, use_stereo=True)
     assert np.array_equal(got, want) and nm == wnm > 500
+
+
+# ---- the monocular-initialisation matcher: ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:487-632 ----
+
+def _check_init(tag, oracle, windows=(100, 30, 300), **kw):
+    from orb_slam2_test_b200 import ORBextractor
+    f1, f2, bounds, prev = matchcase.make_init_case(**kw)
+    shape = kw.get("shape", synth.TUM_SHAPE)
+    ext = ORBextractor(kw.get("nf", 2000), 1.2, 8, 20, 7)
+    ext.set_camera(kw.get("K", matchcase.TUM1_K), kw.get("dist", matchcase.TUM1_D))
+    kps, desc = ext(synth.make_frame(shape, seed=kw.get("seed", 0), frame=kw.get("frame", 0) + kw.get("step", 1)))
+    assert kps.tobytes() == f2["kps"].tobytes() and np.array_equal(desc, f2["desc"]), f"{tag}: current frame differs"
+    total = 0
+    for win in windows:
+        for ratio, ori in ((0.9, True), (0.7, False)):
+            want, wprev, wnm = oracle.search_for_initialization(f1, f2, bounds, prev, win, ratio, ori)
+            got, gprev, nm = ext.search_for_initialization(f1, prev, win, ratio, check_orientation=ori)
+            bad = np.nonzero(got != want)[0]
+            assert bad.size == 0, f"{tag} win={win} ratio={ratio}: {bad.size} entries differ, e.g. {bad[:5]}: {got[bad[:5]]} vs {want[bad[:5]]}"
+            assert nm == wnm and np.array_equal(gprev.view(np.uint32), wprev.view(np.uint32)), f"{tag} win={win}: nmatches {nm} vs {wnm}"
+            total += wnm
+    return total
+
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, step=3), dict(seed=4, nf=4000, step=2),
+                                dict(seed=3, shape=synth.KITTI_SHAPE, K=matchcase.KITTI_K, dist=(0.0, 0.0, 0.0, 0.0))],
+                         ids=["tum", "tum-3-frames-later", "tum-4000", "kitti"])
+def test_initialisation_matcher(kw, oracle_built):
+    assert _check_init("init", oracle_built, **kw) > 800
+
+
+@pytest.mark.parametrize("copies", [2, 4])
+def test_initialisation_matcher_take_overs(copies, oracle_built):
+    """several initial keypoints want the same current keypoint at different distances: a later, strictly better
+    one takes it over (:552-558), an equal or worse one is skipped (:526-527)"""
+    _check_init(f"init x{copies}", oracle_built, windows=(100, 40), seed=9, copies=copies)
