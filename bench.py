@@ -526,6 +526,39 @@ def matcher_section(ORBextractor, synth, local):
         out["local_map"] = loc
     except Exception as ex:
         out["local_map"] = f"unavailable ({type(ex).__name__}: {ex})"
+    # the monocular-initialisation matcher (ORBmatcher::SearchForInitialization, window 100) on two TUM-shape frames of
+    # the 2 x nFeatures initialisation extractor
+    try:
+        from oracle import pyoracle
+        Kt, Dt = matchcase.TUM1_K, matchcase.TUM1_D
+        ini = ORBextractor(2000, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        ini.set_camera(Kt, Dt)
+        frames = {}
+        for f in (0, 1):
+            kps, desc = ini(synth.make_frame(synth.TUM_SHAPE, seed=73, frame=f))
+            un, start, idx, b = ini.frame_grid(0)
+            frames[f] = {"kps": kps, "desc": desc, "un_xy": un, "cell_start": start, "cell_idx": idx, "bounds": b}
+        f1, f2 = frames[0], frames[1]
+        prev = f1["un_xy"].copy()
+        for _ in range(10):
+            m, pv, nm = ini.search_for_initialization(f1, prev, 100, 0.9)
+        ts = []
+        for _ in range(100):
+            t1 = time.perf_counter()
+            m, pv, nm = ini.search_for_initialization(f1, prev, 100, 0.9)
+            ts.append((time.perf_counter() - t1) * 1e6)
+        tc = []
+        for _ in range(10):
+            t1 = time.perf_counter()
+            w, wpv, wnm = pyoracle.search_for_initialization(f1, f2, f2["bounds"], prev, 100, 0.9, True)
+            tc.append((time.perf_counter() - t1) * 1e6)
+        out["initialisation"] = {"reference": "src/ORBmatcher.cc:487-632 (Tracking::MonocularInitialization)",
+                                 "config": "TUM 640x480, 2000 kp per frame, %d level-0 queries, window 100" % int((f1["kps"]["octave"] == 0).sum()),
+                                 "call_p50_us": float(np.percentile(ts, 50)), "nmatches": nm, "rounds": ini.match_rounds(),
+                                 "rescans": ini.match_rescans(), "cpu_p50_us_one_core": float(np.percentile(tc, 50)),
+                                 "parity_check": "identical" if (np.array_equal(m, w) and nm == wnm and np.array_equal(pv, wpv)) else "MISMATCH"}
+    except Exception as ex:
+        out["initialisation"] = f"unavailable ({type(ex).__name__}: {ex})"
     return out
 
 

@@ -211,4 +211,31 @@ int ORBextractor::SearchLocalPoints(int nPoints, const float *proj, const unsign
     return nmatches;
 }
 
+int ORBextractor::SearchForInitialization(const std::vector<cv::KeyPoint> &F1KeysUn, const cv::Mat &F1Descriptors,
+                                          std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12,
+                                          int windowSize, float nnRatio, bool checkOrientation)
+{
+    const int n = (int)F1KeysUn.size();
+    assert(F1Descriptors.rows == n && (n == 0 || F1Descriptors.cols == 32) && (int)vbPrevMatched.size() == n);
+    std::vector<int> octave((size_t)n);
+    std::vector<float> angle((size_t)n), prev((size_t)2 * n);
+    std::vector<unsigned char> desc((size_t)32 * n);
+    for (int i = 0; i < n; ++i) {
+        octave[i] = F1KeysUn[i].octave;
+        angle[i] = F1KeysUn[i].angle;
+        prev[2 * i] = vbPrevMatched[i].x;
+        prev[2 * i + 1] = vbPrevMatched[i].y;
+        memcpy(&desc[(size_t)32 * i], F1Descriptors.ptr(i), 32);
+    }
+    borb_init_frame f1;
+    f1.n = n; f1.octave = octave.data(); f1.angle = angle.data(); f1.desc = desc.data();
+    vnMatches12.assign((size_t)n, -1);
+    int nmatches = 0;
+    check(borb_search_for_initialization(handle, 0, &f1, prev.data(), windowSize, nnRatio,
+                                         checkOrientation ? 0u : BORB_MATCH_NO_ORIENTATION, vnMatches12.data(), &nmatches),
+          "search for initialization");
+    for (int i = 0; i < n; ++i) vbPrevMatched[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
+    return nmatches;
+}
+
 } // namespace ORB_SLAM2

@@ -125,6 +125,13 @@ public:
     int SearchLocalPoints(int nPoints, const float *proj, const unsigned char *mpDescriptors, const unsigned char *flags,
                           const int *level, const unsigned char *occupied, float th, float nnRatio, bool useStereo,
                           std::vector<int> &vnMatches);
+    // ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (reference
+    // src/ORBmatcher.cc:487-632, Tracking::MonocularInitialization) on the device, *this = F2's extractor after its
+    // operator() call (SetCamera on).  F1 arrives as its mvKeysUn (octave, angle) and descriptors (CV_8U, n x 32).
+    // vbPrevMatched is updated as the reference does; returns nmatches.
+    int SearchForInitialization(const std::vector<cv::KeyPoint> &F1KeysUn, const cv::Mat &F1Descriptors,
+                                std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12, int windowSize,
+                                float nnRatio, bool checkOrientation);
 
 protected:
     int nfeatures;

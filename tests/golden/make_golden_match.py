@@ -41,8 +41,24 @@ LOCAL_CASES = {
 }
 
 
+# name -> (make_init_case kwargs, windows): ORBmatcher::SearchForInitialization, nnratio 0.9, orientation check on
+INIT_CASES = {
+    "init_tum": (dict(seed=19), (100, 30)),
+    "init_tum_takeovers": (dict(seed=20, copies=3), (100,)),
+    "init_kitti": (dict(seed=21, shape=synth.KITTI_SHAPE, K=matchcase.KITTI_K, dist=(0.0, 0.0, 0.0, 0.0)), (100,)),
+}
+
+
 def main():
     out = {}
+    for name, (kw, wins) in INIT_CASES.items():
+        f1, f2, bounds, prev = matchcase.make_init_case(**kw)
+        for win in wins:
+            m, pv, nm = RefMatcher.search_for_initialization(f1, f2, bounds, prev, win, 0.9, True)
+            out[f"{name}_w{win}_match"] = m
+            out[f"{name}_w{win}_prev"] = pv
+            out[f"{name}_w{win}_nm"] = np.array([nm, len(f1["kps"])], np.int32)
+            print(name, win, "nmatches", nm)
     for name, (kw, ths) in LOCAL_CASES.items():
         cur, bounds, scale, mps, occ = matchcase.make_local_case(**kw)
         for th in ths:

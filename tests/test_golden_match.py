@@ -11,7 +11,7 @@ import matchcase
 
 HERE = Path(__file__).resolve().parent
 sys.path.insert(0, str(HERE / "golden"))
-from make_golden_match import CASES, LOCAL_CASES  # noqa: E402
+from make_golden_match import CASES, INIT_CASES, LOCAL_CASES  # noqa: E402
 
 
 def _golden():
@@ -90,3 +90,33 @@ def test_cuda_reproduces_the_reference_local_matcher(name, oracle_built):
         m, nm = ext.search_local_points(mps, occ, th, 0.8, use_stereo=stereo)
         key = f"{name}_th{int(th)}"
         assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+
+
+@pytest.mark.parametrize("name", sorted(INIT_CASES))
+def test_oracle_reproduces_the_reference_initialisation_matcher(name, oracle_built):
+    g = _golden()
+    kw, wins = INIT_CASES[name]
+    f1, f2, bounds, prev = matchcase.make_init_case(**kw)
+    for win in wins:
+        m, pv, nm = oracle_built.search_for_initialization(f1, f2, bounds, prev, win, 0.9, True)
+        key = f"{name}_w{win}"
+        assert len(f1["kps"]) == g[key + "_nm"][1], "the scenario is not the one the golden file was made from"
+        assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+        assert np.array_equal(pv.view(np.uint32), g[key + "_prev"].view(np.uint32)), key
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(INIT_CASES))
+def test_cuda_reproduces_the_reference_initialisation_matcher(name, oracle_built):
+    from orb_slam2_test_b200 import ORBextractor, synth
+    g = _golden()
+    kw, wins = INIT_CASES[name]
+    f1, f2, bounds, prev = matchcase.make_init_case(**kw)
+    ext = ORBextractor(kw.get("nf", 2000), 1.2, 8, 20, 7)
+    ext.set_camera(kw.get("K", matchcase.TUM1_K), kw.get("dist", matchcase.TUM1_D))
+    ext(synth.make_frame(kw.get("shape", synth.TUM_SHAPE), seed=kw["seed"], frame=kw.get("step", 1)))
+    for win in wins:
+        m, pv, nm = ext.search_for_initialization(f1, prev, win, 0.9)
+        key = f"{name}_w{win}"
+        assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+        assert np.array_equal(pv.view(np.uint32), g[key + "_prev"].view(np.uint32)), key

@@ -72,3 +72,25 @@ def test_local_map_matcher(kw, oracle_built, ref):
             got, nm = oracle_built.search_local_points(cur, bounds, scale, mps, occ, th, ratio)
             assert np.array_equal(got, want) and nm == wnm, f"th={th} ratio={ratio}"
             assert not (got[occ == 2] >= 0).any()
+
+
+# ---- the monocular-initialisation matcher: ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:487-632 ----
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, step=3), dict(seed=4, nf=4000, step=2), dict(seed=9, copies=2),
+                                dict(seed=9, copies=4),
+                                dict(seed=3, shape=synth.KITTI_SHAPE, K=matchcase.KITTI_K, dist=(0.0, 0.0, 0.0, 0.0))],
+                         ids=["tum", "tum-3-later", "tum-4000", "takeovers-x2", "takeovers-x4", "kitti"])
+def test_initialisation_matcher(kw, oracle_built, ref):
+    """windows 100 (the reference's), 30 and 300; ratio 0.9 / 0.7; with and without the orientation check; then the
+    call chained on a later frame with the vbPrevMatched the first call updated (src/Tracking.cc:616)"""
+    f1, f2, bounds, prev = matchcase.make_init_case(**kw)
+    for win in (100, 30, 300):
+        for ratio, ori in ((0.9, True), (0.7, False)):
+            want, wprev, wnm = ref.search_for_initialization(f1, f2, bounds, prev, win, ratio, ori)
+            got, gprev, nm = oracle_built.search_for_initialization(f1, f2, bounds, prev, win, ratio, ori)
+            assert np.array_equal(got, want) and nm == wnm and np.array_equal(gprev.view(np.uint32), wprev.view(np.uint32))
+    _, pv, _ = ref.search_for_initialization(f1, f2, bounds, prev, 100, 0.9, True)
+    f3 = matchcase.make_init_case(**{**kw, "copies": 1, "step": kw.get("step", 1) + 1})[1]
+    a = ref.search_for_initialization(f1, f3, bounds, pv, 100, 0.9, True)
+    b = oracle_built.search_for_initialization(f1, f3, bounds, pv, 100, 0.9, True)
+    assert np.array_equal(a[0], b[0]) and a[2] == b[2] and np.array_equal(a[1], b[1])
