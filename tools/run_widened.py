@@ -68,3 +68,24 @@ last["octave"], last["angle"] = last["kps"]["octave"], last["kps"]["angle"]
 for th in (7.0, 15.0, 7.0):
     m, nm = ML.search_by_projection(last, T_cur, BF, BF / FX, th, use_stereo=True)
 print("matcher: nmatches", nm, "rounds", ML.match_rounds(), "rescans", ML.match_rescans())
+# the local-map matcher (MODE 2) and the monocular-initialisation matcher (MODE 3 + M3) on the same kind of frames
+occ = np.where(m >= 0, 2, 0).astype(np.uint8)
+rng = np.random.default_rng(72)
+Xc = last["mp_xyz"].astype(np.float64) @ T_cur[:, :3].T.astype(np.float64) + T_cur[:, 3]
+z = np.where(np.abs(Xc[:, 2]) > 1e-6, Xc[:, 2], 1.0)
+proj = np.stack([K[0] * Xc[:, 0] / z + K[2], K[1] * Xc[:, 1] / z + K[3], K[0] * Xc[:, 0] / z + K[2] - BF / z,
+                 rng.uniform(0.99, 1.0, len(z))], 1).astype(np.float32)
+mps = {"proj": proj, "desc": last["mp_desc"], "flags": ((last["mp_flags"] & 1) | 2).astype(np.uint8),
+       "level": last["kps"]["octave"].astype(np.int32)}
+for th in (1.0, 3.0, 1.0):
+    lm, lnm = ML.search_local_points(mps, occ, th, 0.8, use_stereo=True)
+print("local-map matcher: nmatches", lnm, "rounds", ML.match_rounds())
+INI = ORBextractor(2000, 1.2, 8, 20, 7)
+INI.set_camera(matchcase.TUM1_K, matchcase.TUM1_D)
+k0, d0 = INI(synth.make_frame(synth.TUM_SHAPE, seed=73, frame=0))
+f1 = {"kps": k0, "desc": d0}
+prev = INI.frame_grid(0)[0].copy()
+INI(synth.make_frame(synth.TUM_SHAPE, seed=73, frame=1))
+for _ in range(3):
+    im, ipv, inm = INI.search_for_initialization(f1, prev, 100, 0.9)
+print("initialisation matcher: nmatches", inm, "rounds", INI.match_rounds())
