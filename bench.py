@@ -526,6 +526,36 @@ def matcher_section(ORBextractor, synth, local):
         out["local_map"] = loc
     except Exception as ex:
         out["local_map"] = f"unavailable ({type(ex).__name__}: {ex})"
+    # the whole per-frame front end of the tracking thread for a stereo frame, as one sequence through the host ABI:
+    # both eyes extracted on two threads (+ undistortion / grid), stereo association, frame-to-frame matcher,
+    # local-map matcher -- the current frame's keypoints, descriptors, grid and mvuRight never leave the device
+    # in between (the 28+32 B per keypoint results are still downloaded by the extract calls, as the shim needs them)
+    try:
+        import threading
+        imgs = [synth.make_frame((ROWS, COLS), seed=71, frame=1, eye=e) for e in (0, 1)]
+        pair = [ext, right]
+
+        def eye(i):
+            pair[i]._lib.borb_extract_host(pair[i]._h, imgs[i].ctypes.data, 1, COLS, ROWS, COLS, 0, 0)
+            pair[i]._n = 1
+        mps_ok = isinstance(out.get("local_map"), dict)
+        ts = []
+        for it in range(120):
+            t1 = time.perf_counter()
+            th_ = threading.Thread(target=eye, args=(1,))
+            th_.start()
+            eye(0)
+            th_.join()
+            ext.stereo_match(right, BF, mb, keep_on_device=True)
+            m7, _ = ext.search_by_projection(lf, cur["Tcw"], BF, mb, 7.0, use_stereo=True)
+            if mps_ok:
+                ext.search_local_points(mps, occ, 1.0, 0.8, use_stereo=True)
+            if it >= 20:
+                ts.append((time.perf_counter() - t1) * 1e6)
+        out["stereo_front_end_p50_us"] = float(np.percentile(ts, 50))
+        out["stereo_front_end"] = "extract L+R (2 threads) + undistort/grid + stereo association + SearchByProjection(th 7) + SearchLocalPoints(th 1), one KITTI stereo frame, host call sequence"
+    except Exception as ex:
+        out["stereo_front_end_p50_us"] = f"unavailable ({type(ex).__name__}: {ex})"
     # the monocular-initialisation matcher (ORBmatcher::SearchForInitialization, window 100) on two TUM-shape frames of
     # the 2 x nFeatures initialisation extractor
     try:
