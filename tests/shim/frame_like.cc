@@ -184,13 +184,93 @@ static int match_mode(char **argv)
     fwrite(&nmatches, 4, 1, f);
     fwrite(&nc, 4, 1, f);
     fwrite(vnMatches.data(), 4, vnMatches.size(), f);
+    /* then the local-map matcher on the same frame (reference src/ORBmatcher.cc:59-154): the map points are the last
+     * frame's again, projected the way the motion-model matcher just did (what Frame::isInFrustum would leave), viewing
+     * cosine 1, predicted level = the octave they were seen at; the slots the first matcher filled count as held */
+    {
+        vector<float> proj((size_t)4 * n);
+        vector<unsigned char> lflags((size_t)n), occupied((size_t)nc);
+        for (int i2 = 0; i2 < nc; ++i2) occupied[i2] = vnMatches[i2] >= 0 ? 2 : 0;
+        for (int i = 0; i < n; ++i) {
+            const float *X = &xyz[(size_t)3 * i];
+            const double xc = (double)tc[0] * X[0] + (double)tc[1] * X[1] + (double)tc[2] * X[2] + tc[3];
+            const double yc = (double)tc[4] * X[0] + (double)tc[5] * X[1] + (double)tc[6] * X[2] + tc[7];
+            const double zc = (double)tc[8] * X[0] + (double)tc[9] * X[1] + (double)tc[10] * X[2] + tc[11];
+            const bool front = (flags[i] & 1) && zc > 0.1;
+            const float u = front ? (float)(K4[0] * xc / zc + K4[2]) : 0.f, v = front ? (float)(K4[1] * yc / zc + K4[3]) : 0.f;
+            proj[4 * i] = u; proj[4 * i + 1] = v; proj[4 * i + 2] = front ? (float)(u - mbf / zc) : 0.f; proj[4 * i + 3] = 1.f;
+            lflags[i] = (unsigned char)((front && u > 0.f && u < (float)cols && v > 0.f && v < (float)rows ? 1 : 0) | (flags[i] & 2));
+        }
+        vector<int> vnLocal;
+        const int nlocal = left.SearchLocalPoints(n, proj.data(), desc.data(), lflags.data(), octave.data(), occupied.data(), 3.f,
+                                                  0.8f, true, vnLocal);
+        int nl = (int)vnLocal.size();
+        fwrite(&nlocal, 4, 1, f);
+        fwrite(&nl, 4, 1, f);
+        fwrite(vnLocal.data(), 4, vnLocal.size(), f);
+        fwrite(proj.data(), 4, proj.size(), f);
+        fwrite(lflags.data(), 1, lflags.size(), f);
+    }
     fclose(f);
     printf("frame_like match ok\n");
     return 0;
 }
 
+/* `init` mode: ORBmatcher::SearchForInitialization through the shim (reference src/ORBmatcher.cc:487-632).  argv: init
+ * image cols rows nfeatures f1.bin out.bin; f1.bin = int32 n, window, float nnratio, then octave[n] (int32), angle[n],
+ * desc[32n], prev[2n].  The image is the CURRENT frame (the mpIniORBextractor instance, TUM1 camera); out.bin = int32
+ * nmatches, n, then n int32 vnMatches12 and 2n float vbPrevMatched. */
+static int init_mode(char **argv)
+{
+    const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[5]);
+    vector<unsigned char> im = slurp(argv[2], (size_t)cols * rows);
+    cv::Mat image(rows, cols, CV_8UC1, im.data());
+    FILE *in = fopen(argv[6], "rb");
+    if (!in) return 2;
+    int n = 0, window = 0;
+    float ratio = 0.f;
+    if (fread(&n, 4, 1, in) != 1 || fread(&window, 4, 1, in) != 1 || fread(&ratio, 4, 1, in) != 1) return 2;
+    vector<int> octave((size_t)n);
+    vector<float> angle((size_t)n), prev((size_t)2 * n);
+    cv::Mat desc(n, 32, CV_8UC1);
+    if (fread(octave.data(), 4, (size_t)n, in) != (size_t)n || fread(angle.data(), 4, (size_t)n, in) != (size_t)n) return 2;
+    for (int i = 0; i < n; ++i) if (fread(desc.ptr(i), 1, 32, in) != 32) return 2;
+    if (fread(prev.data(), 4, prev.size(), in) != prev.size()) return 2;
+    fclose(in);
+    cv::Mat K(3, 3, CV_32F), DistCoef(5, 1, CV_32F);
+    memset(K.data, 0, 36);
+    K.at<float>(0, 0) = 517.306408f; K.at<float>(1, 1) = 516.469215f;
+    K.at<float>(0, 2) = 318.643040f; K.at<float>(1, 2) = 255.313989f; K.at<float>(2, 2) = 1.f;
+    DistCoef.at<float>(0, 0) = 0.262383f; DistCoef.at<float>(1, 0) = -0.953104f; DistCoef.at<float>(2, 0) = -0.005358f;
+    DistCoef.at<float>(3, 0) = 0.002628f; DistCoef.at<float>(4, 0) = 1.163314f;
+    ORBextractor ini(nFeatures, 1.2f, 8, 20, 7);
+    ini.SetCamera(K, DistCoef);
+    vector<cv::KeyPoint> k2;
+    cv::Mat d2;
+    ini(image, cv::Mat(), k2, d2);
+    vector<cv::KeyPoint> F1KeysUn((size_t)n);
+    vector<cv::Point2f> vbPrevMatched((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        F1KeysUn[i].octave = octave[i];
+        F1KeysUn[i].angle = angle[i];
+        vbPrevMatched[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
+    }
+    vector<int> vnMatches12;
+    const int nmatches = ini.SearchForInitialization(F1KeysUn, desc, vbPrevMatched, vnMatches12, window, ratio, true);
+    FILE *f = fopen(argv[7], "wb");
+    if (!f) return 2;
+    fwrite(&nmatches, 4, 1, f);
+    fwrite(&n, 4, 1, f);
+    fwrite(vnMatches12.data(), 4, vnMatches12.size(), f);
+    for (int i = 0; i < n; ++i) { fwrite(&vbPrevMatched[i].x, 4, 1, f); fwrite(&vbPrevMatched[i].y, 4, 1, f); }
+    fclose(f);
+    printf("frame_like init ok\n");
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
+    if (argc == 8 && !strcmp(argv[1], "init")) return init_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "match")) return match_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "pre")) return pre_mode(argv);
     if (argc != 7) { fprintf(stderr, "usage: %s left right cols rows nfeatures out\n", argv[0]); return 2; }

@@ -195,3 +195,38 @@ def test_frame_to_frame_matcher_through_the_shim(tmp_path, oracle_built):
     got = np.frombuffer(buf, "<i4", nc, 8)
     want, wnm = oracle_built.search_by_projection(cur, last, cam, bounds, scale, th)
     assert nc == len(want) and np.array_equal(got, want) and nm == wnm and nm > 300
+    # ORBextractor::SearchLocalPoints on the same frame: the caller wrote the projections it used next to its result
+    off = 8 + 4 * nc
+    nlocal, nl = struct.unpack_from("<ii", buf, off); off += 8
+    gl = np.frombuffer(buf, "<i4", nl, off); off += 4 * nl
+    proj = np.frombuffer(buf, "<f4", 4 * n, off).reshape(n, 4); off += 16 * n
+    lflags = np.frombuffer(buf, "u1", n, off)
+    mps = {"proj": proj, "desc": last["mp_desc"], "flags": lflags, "level": last["kps"]["octave"].astype(np.int32)}
+    occ = np.where(want >= 0, 2, 0).astype(np.uint8)
+    wl, wlnm = oracle_built.search_local_points(cur, bounds, scale, mps, occ, 3.0, 0.8)
+    assert nl == len(wl) and np.array_equal(gl, wl) and nlocal == wlnm and nlocal > 50
+
+
+@pytest.mark.gpu
+def test_initialisation_matcher_through_the_shim(tmp_path, oracle_built):
+    """ORBextractor::SearchForInitialization (shim) = ORBmatcher::SearchForInitialization restated (pinned to the
+    reference's ORBmatcher.cc): the Frame-like caller extracts the current frame with the initialisation extractor and
+    matches the initial frame's level-0 keypoints against it."""
+    import matchcase
+    _build()
+    f1, f2, bounds, prev = matchcase.make_init_case(seed=34)
+    (tmp_path / "cur.raw").write_bytes(synth.make_frame(synth.TUM_SHAPE, seed=34, frame=1).tobytes())
+    n = len(f1["kps"])
+    blob = struct.pack("<iif", n, 100, 0.9) + f1["kps"]["octave"].astype("<i4").tobytes()
+    blob += f1["kps"]["angle"].astype("<f4").tobytes() + f1["desc"].tobytes() + prev.astype("<f4").tobytes()
+    (tmp_path / "f1.bin").write_bytes(blob)
+    r = subprocess.run([str(EXE), "init", str(tmp_path / "cur.raw"), "640", "480", "2000", str(tmp_path / "f1.bin"),
+                        str(tmp_path / "i.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = (tmp_path / "i.bin").read_bytes()
+    nm, nn = struct.unpack_from("<ii", buf, 0)
+    got = np.frombuffer(buf, "<i4", nn, 8)
+    gprev = np.frombuffer(buf, "<f4", 2 * nn, 8 + 4 * nn).reshape(nn, 2)
+    want, wprev, wnm = oracle_built.search_for_initialization(f1, f2, bounds, prev, 100, np.float32(0.9), True)
+    assert nn == n and np.array_equal(got, want) and nm == wnm > 150
+    assert np.array_equal(gprev.view(np.uint32), wprev.view(np.uint32))
