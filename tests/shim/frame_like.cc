@@ -25,6 +25,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <chrono>
 #include <thread>
 #include <vector>
 
@@ -178,6 +180,19 @@ static int match_mode(char **argv)
     vector<int> vnMatches;
     const int nmatches = left.SearchByProjection(TcwCur, TcwLast, n, xyz.data(), desc.data(), flags.data(), octave.data(),
                                                  angle.data(), mbf, mb, th, mono != 0, true, true, vnMatches);
+    if (getenv("FRAME_LIKE_TIME")) { /* C++ call latency of the matcher (bench note in DESIGN.md 4e) */
+        vector<double> us;
+        vector<int> tmp;
+        for (int it = 0; it < 220; ++it) {
+            const auto t0 = std::chrono::steady_clock::now();
+            left.SearchByProjection(TcwCur, TcwLast, n, xyz.data(), desc.data(), flags.data(), octave.data(), angle.data(), mbf,
+                                    mb, th, mono != 0, true, true, tmp);
+            const auto t1 = std::chrono::steady_clock::now();
+            if (it >= 20) us.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+        }
+        std::sort(us.begin(), us.end());
+        printf("SearchByProjection through the shim: p50 %.1f us, p99 %.1f us\n", us[us.size() / 2], us[us.size() * 99 / 100]);
+    }
     FILE *f = fopen(argv[8], "wb");
     if (!f) return 2;
     int nc = (int)vnMatches.size();
