@@ -417,6 +417,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
                 tiles.push_back(t);
             }
     }
+    M = (int)align_up(M, 4); /* K3 clears a node's four quarter counters with one 16-byte store */
     if (M > BORB_QT_MAXNODES)
         return fail(BORB_ERR_CAPACITY, "%d features on one level exceed the shared-memory quadtree "
                     "capacity (%d)", M, BORB_QT_MAXNODES);

@@ -29,42 +29,51 @@
 #define QT_NT_THROUGHPUT 256
 #define QT_NT_LATENCY 1024
 
-/* in-place exclusive scan of a[0..len), returns the total; all threads must call */
-template <int QT_NT>
-__device__ int qt_scan(int *a, int len, int *wtmp /* 33 ints */)
+/* Block-wide exclusive scan of up to three 21-bit fields packed in a 64-bit word.  gen(i) is the
+ * packed value of element i in [0, len); thread t owns a contiguous run of elements, so no array of
+ * flags has to be written (and fenced) first.  After the two internal barriers every thread calls
+ * emit(i, g, before, total) for its own elements: g = gen(i), before = packed sums of the elements in
+ * front of i, total = packed sums of all.  emit must not write what gen reads.  One trailing barrier
+ * publishes what emit wrote; three barriers in all.  All threads must call. */
+#define QT_F 21
+#define QT_FMASK ((1u << QT_F) - 1u)
+typedef unsigned long long qt_u64;
+
+template <int QT_NT, typename Gen, typename Emit>
+__device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words */, Gen gen, Emit emit)
 {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int per = (len + QT_NT - 1) / QT_NT;
     const int b = min(tid * per, len), e = min(b + per, len);
-    int s = 0;
-    for (int i = b; i < e; ++i) s += a[i];
-    int v = s;
+    qt_u64 s = 0;
+    for (int i = b; i < e; ++i) s += gen(i);
+    qt_u64 v = s;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        const qt_u64 t = __shfl_up_sync(0xffffffffu, v, o);
         if (lane >= o) v += t;
     }
     if (lane == 31) wtmp[w] = v;
     __syncthreads();
     if (w == 0) {
-        const int t = lane < QT_NT / 32 ? wtmp[lane] : 0;
-        int u = t;
+        const qt_u64 t = lane < QT_NT / 32 ? wtmp[lane] : 0ull;
+        qt_u64 u = t;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int z = __shfl_up_sync(0xffffffffu, u, o);
+            const qt_u64 z = __shfl_up_sync(0xffffffffu, u, o);
             if (lane >= o) u += z;
         }
         wtmp[lane] = u - t;
         if (lane == 31) wtmp[32] = u;
     }
     __syncthreads();
-    int run = wtmp[w] + v - s;
+    qt_u64 run = wtmp[w] + v - s;
+    const qt_u64 total = wtmp[32];
     for (int i = b; i < e; ++i) {
-        const int t = a[i];
-        a[i] = run;
-        run += t;
+        const qt_u64 g = gen(i);
+        emit(i, g, run, total);
+        run += g;
     }
-    const int total = wtmp[32];
     __syncthreads();
     return total;
 }
@@ -72,10 +81,10 @@ __device__ int qt_scan(int *a, int len, int *wtmp /* 33 ints */)
 struct QtSmem {
     int4 *box[2];
     int *cnt[2];
-    int *rank, *par, *uf, *ccnt, *cf, *ef;
+    int *rank, *par, *uf, *ccnt, *cf;
     int *exp_pos[2], *exp_size[2];
     unsigned long long *best;
-    int *wtmp;
+    qt_u64 *wtmp;
 };
 
 __device__ __forceinline__ int qt_quadrant(int x, int y, const int4 b)
@@ -100,52 +109,58 @@ __device__ __forceinline__ int4 qt_child_box(const int4 b, int q)
 /* bytes of dynamic shared memory for a list capacity of M nodes */
 static inline size_t qt_smem_bytes(int M)
 {
-    return (size_t)M * (2 * 16 + 2 * 4 + 3 * 4 + 3 * 16 + 4 * 4 + 8) + 64 * 4;
+    return (size_t)M * (2 * 16 + 8 + 2 * 4 + 3 * 4 + 2 * 16 + 4 * 4) + 40 * 8;
 }
 
 /* One split pass over the current list (cur) into (1-cur).
  * On entry: rank[j] = processing rank of list node j (or -1), par[k] = node of rank k,
- * ccnt[4k+q] = points of rank k's q-th quarter, for all n_rank ranked nodes.
+ * ccnt[4k+q] = points of rank k's q-th quarter, for all ranked nodes.
  * Only ranks < n_proc are actually split.  Returns the new list size; *n_exp = number of
- * children with more than one point (written to the other expandable buffer, creation order). */
+ * children with more than one point (written to the other expandable buffer, creation order).
+ * One packed scan gives the positions of the non-empty children (field 0), of the expandable ones
+ * (field 1) and of the nodes that stay (field 2). */
 template <int QT_NT>
 __device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
                         const uint32_t *__restrict__ xy, uint32_t *__restrict__ node, int *n_exp)
 {
     const int tid = threadIdx.x;
     const int nc = 4 * n_proc;
-    for (int c = tid; c < nc; c += QT_NT) {
-        s.cf[c] = s.ccnt[c] > 0;
-        s.ef[c] = s.ccnt[c] > 1;
-    }
-    for (int j = tid; j < S; j += QT_NT) s.uf[j] = !(s.rank[j] >= 0 && s.rank[j] < n_proc);
-    __syncthreads();
-    const int C = qt_scan<QT_NT>(s.cf, nc, s.wtmp);
-    const int E = qt_scan<QT_NT>(s.ef, nc, s.wtmp);
-    const int U = qt_scan<QT_NT>(s.uf, S, s.wtmp);
     const int nxt = 1 - cur;
-    for (int c = tid; c < nc; c += QT_NT) {
-        const int n = s.ccnt[c];
-        if (n > 0) {
-            const int p = C - 1 - s.cf[c];
-            s.box[nxt][p] = qt_child_box(s.box[cur][s.par[c >> 2]], c & 3);
-            s.cnt[nxt][p] = n;
-            s.cf[c] = p;
-            if (n > 1) {
-                s.exp_pos[nxt][s.ef[c]] = p;
-                s.exp_size[nxt][s.ef[c]] = n;
+    const qt_u64 tot = qt_scan_emit<QT_NT>(
+        max(nc, S), s.wtmp,
+        [&](int i) -> qt_u64 {
+            qt_u64 g = 0;
+            if (i < nc) {
+                const int n = s.ccnt[i];
+                g = (qt_u64)(n > 0) | ((qt_u64)(n > 1) << QT_F);
             }
-        }
-    }
-    for (int j = tid; j < S; j += QT_NT) {
-        if (!(s.rank[j] >= 0 && s.rank[j] < n_proc)) {
-            const int p = C + s.uf[j];
-            s.box[nxt][p] = s.box[cur][j];
-            s.cnt[nxt][p] = s.cnt[cur][j];
-            s.uf[j] = p;
-        }
-    }
-    __syncthreads();
+            if (i < S) {
+                const int r = s.rank[i];
+                g |= (qt_u64)!(r >= 0 && r < n_proc) << (2 * QT_F);
+            }
+            return g;
+        },
+        [&](int i, qt_u64 g, qt_u64 before, qt_u64 total) {
+            const int C = (int)(total & QT_FMASK);
+            if (g & 1) {
+                const int n = s.ccnt[i];
+                const int p = C - 1 - (int)(before & QT_FMASK);
+                s.box[nxt][p] = qt_child_box(s.box[cur][s.par[i >> 2]], i & 3);
+                s.cnt[nxt][p] = n;
+                s.cf[i] = p;
+                if (n > 1) {
+                    const int e = (int)((before >> QT_F) & QT_FMASK);
+                    s.exp_pos[nxt][e] = p;
+                    s.exp_size[nxt][e] = n;
+                }
+            }
+            if ((g >> (2 * QT_F)) & 1) {
+                const int p = C + (int)(before >> (2 * QT_F));
+                s.box[nxt][p] = s.box[cur][i];
+                s.cnt[nxt][p] = s.cnt[cur][i];
+                s.uf[i] = p;
+            }
+        });
     for (int i = tid; i < n_pts; i += QT_NT) {
         const int j = (int)node[i];
         const int k = s.rank[j];
@@ -157,18 +172,16 @@ __device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
         }
     }
     __syncthreads();
-    *n_exp = E;
-    return C + U;
+    *n_exp = (int)((tot >> QT_F) & QT_FMASK);
+    return (int)(tot & QT_FMASK) + (int)(tot >> (2 * QT_F));
 }
 
-/* count the quarters of every ranked node */
+/* count the quarters of every ranked node; ccnt[0 .. 4 * ranked) must be zero on entry */
 template <int QT_NT>
-__device__ void qt_count(const QtSmem &s, int cur, int n_rank, int n_pts,
+__device__ void qt_count(const QtSmem &s, int cur, int n_pts,
                          const uint32_t *__restrict__ xy, const uint32_t *__restrict__ node)
 {
     const int tid = threadIdx.x;
-    for (int c = tid; c < 4 * n_rank; c += QT_NT) s.ccnt[c] = 0;
-    __syncthreads();
     for (int i = tid; i < n_pts; i += QT_NT) {
         const int j = (int)node[i];
         const int k = s.rank[j];
@@ -196,6 +209,7 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
         s.box[0] = (int4 *)p; p += (size_t)M * 16;
         s.box[1] = (int4 *)p; p += (size_t)M * 16;
         s.best = (unsigned long long *)p; p += (size_t)M * 8;
+        s.wtmp = (qt_u64 *)p; p += 40 * 8;
         s.cnt[0] = (int *)p; p += (size_t)M * 4;
         s.cnt[1] = (int *)p; p += (size_t)M * 4;
         s.rank = (int *)p; p += (size_t)M * 4;
@@ -203,12 +217,10 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
         s.uf = (int *)p; p += (size_t)M * 4;
         s.ccnt = (int *)p; p += (size_t)M * 16;
         s.cf = (int *)p; p += (size_t)M * 16;
-        s.ef = (int *)p; p += (size_t)M * 16;
         s.exp_pos[0] = (int *)p; p += (size_t)M * 4;
         s.exp_pos[1] = (int *)p; p += (size_t)M * 4;
         s.exp_size[0] = (int *)p; p += (size_t)M * 4;
-        s.exp_size[1] = (int *)p; p += (size_t)M * 4;
-        s.wtmp = (int *)p;
+        s.exp_size[1] = (int *)p;
     }
     const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
     const BorbLevel &L = plan->lv[level];
@@ -235,38 +247,37 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
         atomicAdd(&s.ccnt[r], 1);
     }
     __syncthreads();
-    for (int j = tid; j < n_ini; j += QT_NT) s.cf[j] = s.ccnt[j] > 0;
-    __syncthreads();
-    int S = qt_scan<QT_NT>(s.cf, n_ini, s.wtmp);
     int cur = 0;
-    for (int j = tid; j < n_ini; j += QT_NT) {
-        if (s.ccnt[j] > 0) {
-            const int p = s.cf[j];
-            s.box[cur][p] = make_int4((int)__fmul_rn(hx, (float)j), 0,
-                                      (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
-            s.cnt[cur][p] = s.ccnt[j];
-        }
-    }
-    __syncthreads();
+    int S = (int)qt_scan_emit<QT_NT>(
+        n_ini, s.wtmp, [&](int j) -> qt_u64 { return (qt_u64)(s.ccnt[j] > 0); },
+        [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
+            if (g) {
+                const int p = (int)before;
+                s.box[0][p] = make_int4((int)__fmul_rn(hx, (float)j), 0, (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
+                s.cnt[0][p] = s.ccnt[j];
+                s.cf[j] = p;
+            }
+        });
     for (int i = tid; i < n; i += QT_NT) node[i] = (uint32_t)s.cf[node[i]];
     __syncthreads();
 
     /* ---- split passes (:741-927) ---- */
     bool done = (S == 0);
     while (!done) {
-        /* breadth pass: rank the multi-point nodes in list order */
+        /* breadth pass: rank the multi-point nodes in list order (and clear their quarter counters) */
         const int prev = S;
-        for (int j = tid; j < S; j += QT_NT) s.ef[j] = s.cnt[cur][j] > 1;
-        __syncthreads();
-        const int n_split = qt_scan<QT_NT>(s.ef, S, s.wtmp);
+        const int n_split = (int)qt_scan_emit<QT_NT>(
+            S, s.wtmp, [&](int j) -> qt_u64 { return (qt_u64)(s.cnt[cur][j] > 1); },
+            [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
+                const int k = (int)before;
+                s.rank[j] = g ? k : -1;
+                if (g) {
+                    s.par[k] = j;
+                    *reinterpret_cast<int4 *>(&s.ccnt[4 * k]) = make_int4(0, 0, 0, 0);
+                }
+            });
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
-        for (int j = tid; j < S; j += QT_NT) {
-            const bool sp = s.cnt[cur][j] > 1;
-            s.rank[j] = sp ? s.ef[j] : -1;
-            if (sp) s.par[s.ef[j]] = j;
-        }
-        __syncthreads();
-        qt_count<QT_NT>(s, cur, n_split, n, xy, node);
+        qt_count<QT_NT>(s, cur, n, xy, node);
         int n_exp;
         S = qt_split<QT_NT>(s, cur, S, n_split, n, xy, node, &n_exp);
         cur = 1 - cur;
@@ -279,6 +290,8 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
             const int E = n_exp;
             if (E == 0) { done = true; break; }
             for (int j = tid; j < S; j += QT_NT) s.rank[j] = -1;
+            for (int c = tid; c < 4 * E; c += QT_NT) s.ccnt[c] = 0;
+            if (tid == 0) sh_proc = E;
             __syncthreads();
             for (int e = tid; e < E; e += QT_NT) {
                 const int sz = s.exp_size[cur][e];
@@ -291,22 +304,18 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
                 s.par[r] = s.exp_pos[cur][e];
             }
             __syncthreads();
-            qt_count<QT_NT>(s, cur, E, n, xy, node);
+            qt_count<QT_NT>(s, cur, n, xy, node);
             /* size after processing ranks 0..k; stop at the first k reaching N */
-            for (int k = tid; k < E; k += QT_NT) {
-                const int g = (s.ccnt[4 * k] > 0) + (s.ccnt[4 * k + 1] > 0) +
-                              (s.ccnt[4 * k + 2] > 0) + (s.ccnt[4 * k + 3] > 0) - 1;
-                s.cf[k] = g;
-                s.ef[k] = g;
-            }
-            if (tid == 0) sh_proc = E;
-            __syncthreads();
-            qt_scan<QT_NT>(s.ef, E, s.wtmp); /* exclusive prefix of the gains */
-            for (int k = tid; k < E; k += QT_NT)
-                if (S + s.ef[k] + s.cf[k] >= N) atomicMin(&sh_proc, k + 1);
-            __syncthreads();
+            qt_scan_emit<QT_NT>(
+                E, s.wtmp,
+                [&](int k) -> qt_u64 {
+                    const int4 c = *reinterpret_cast<const int4 *>(&s.ccnt[4 * k]);
+                    return (qt_u64)((c.x > 0) + (c.y > 0) + (c.z > 0) + (c.w > 0) - 1);
+                },
+                [&](int k, qt_u64 g, qt_u64 before, qt_u64) {
+                    if (S + (int)before + (int)g >= N) atomicMin(&sh_proc, k + 1);
+                });
             const int n_proc = sh_proc;
-            __syncthreads();
             S = qt_split<QT_NT>(s, cur, S, n_proc, n, xy, node, &n_exp);
             cur = 1 - cur;
             if (S >= N || S == prev2) { done = true; break; }
