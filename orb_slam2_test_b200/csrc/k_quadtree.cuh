@@ -78,13 +78,17 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
     return total;
 }
 
-struct QtSmem {
-    int4 *box[2];
-    int *cnt[2];
+struct QtSmem { /* the double-buffered arrays are base + buffer * M: no pointer table indexed at run time (local memory) */
+    int4 *box_;
+    int *cnt_, *exp_pos_, *exp_size_;
     int *rank, *par, *uf, *ccnt, *cf;
-    int *exp_pos[2], *exp_size[2];
     unsigned long long *best;
     qt_u64 *wtmp;
+    int M;
+    __device__ __forceinline__ int4 *box(int b) const { return box_ + b * M; }
+    __device__ __forceinline__ int *cnt(int b) const { return cnt_ + b * M; }
+    __device__ __forceinline__ int *exp_pos(int b) const { return exp_pos_ + b * M; }
+    __device__ __forceinline__ int *exp_size(int b) const { return exp_size_ + b * M; }
 };
 
 __device__ __forceinline__ int qt_quadrant(int x, int y, const int4 b)
@@ -112,6 +116,61 @@ static inline size_t qt_smem_bytes(int M)
     return (size_t)M * (2 * 16 + 8 + 2 * 4 + 3 * 4 + 2 * 16 + 4 * 4) + 40 * 8;
 }
 
+/* The candidates of a (level, frame): in the latency shape (1024 threads, a CTA alone on its SM) a thread keeps
+ * its candidates and their node numbers in registers as long as there are at most QT_RPT per thread; otherwise
+ * (and always in the throughput shape) they are read from and written back to global memory every pass. */
+#define QT_RPT 8
+template <int QT_NT, bool REG>
+struct QtPts {
+    const uint32_t *__restrict__ xy;
+    uint32_t *__restrict__ node;
+    int n;
+    uint32_t rxy[REG ? QT_RPT : 1], rnode[REG ? QT_RPT : 1];
+    __device__ __forceinline__ void load()
+    {
+        if (REG) {
+#pragma unroll
+            for (int u = 0; u < QT_RPT; ++u) {
+                const int i = threadIdx.x + u * QT_NT;
+                rxy[u] = i < n ? xy[i] : 0u;
+            }
+        }
+    }
+    /* first assignment of the node numbers: body(xy) -> node */
+    template <typename F>
+    __device__ __forceinline__ void init(F body)
+    {
+        if (REG) {
+#pragma unroll
+            for (int u = 0; u < QT_RPT; ++u) {
+                const int i = threadIdx.x + u * QT_NT;
+                if (i < n) rnode[u] = body(rxy[u]);
+            }
+        } else {
+            for (int i = threadIdx.x; i < n; i += QT_NT) node[i] = body(xy[i]);
+        }
+    }
+    /* body(i, xy, node&) for each of this thread's candidates */
+    template <typename F>
+    __device__ __forceinline__ void each(F body)
+    {
+        if (REG) {
+#pragma unroll
+            for (int u = 0; u < QT_RPT; ++u) {
+                const int i = threadIdx.x + u * QT_NT;
+                if (i < n) body(i, rxy[u], rnode[u]);
+            }
+        } else {
+            for (int i = threadIdx.x; i < n; i += QT_NT) {
+                uint32_t nd = node[i];
+                const uint32_t before = nd;
+                body(i, xy[i], nd);
+                if (nd != before) node[i] = nd;
+            }
+        }
+    }
+};
+
 /* One split pass over the current list (cur) into (1-cur).
  * On entry: rank[j] = processing rank of list node j (or -1), par[k] = node of rank k,
  * ccnt[4k+q] = points of rank k's q-th quarter, for all ranked nodes.
@@ -119,11 +178,9 @@ static inline size_t qt_smem_bytes(int M)
  * children with more than one point (written to the other expandable buffer, creation order).
  * One packed scan gives the positions of the non-empty children (field 0), of the expandable ones
  * (field 1) and of the nodes that stay (field 2). */
-template <int QT_NT>
-__device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
-                        const uint32_t *__restrict__ xy, uint32_t *__restrict__ node, int *n_exp)
+template <int QT_NT, bool REG>
+__device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, QtPts<QT_NT, REG> &pts, int *n_exp)
 {
-    const int tid = threadIdx.x;
     const int nc = 4 * n_proc;
     const int nxt = 1 - cur;
     const qt_u64 tot = qt_scan_emit<QT_NT>(
@@ -145,94 +202,79 @@ __device__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, int n_pts,
             if (g & 1) {
                 const int n = s.ccnt[i];
                 const int p = C - 1 - (int)(before & QT_FMASK);
-                s.box[nxt][p] = qt_child_box(s.box[cur][s.par[i >> 2]], i & 3);
-                s.cnt[nxt][p] = n;
+                s.box(nxt)[p] = qt_child_box(s.box(cur)[s.par[i >> 2]], i & 3);
+                s.cnt(nxt)[p] = n;
                 s.cf[i] = p;
                 if (n > 1) {
                     const int e = (int)((before >> QT_F) & QT_FMASK);
-                    s.exp_pos[nxt][e] = p;
-                    s.exp_size[nxt][e] = n;
+                    s.exp_pos(nxt)[e] = p;
+                    s.exp_size(nxt)[e] = n;
                 }
             }
             if ((g >> (2 * QT_F)) & 1) {
                 const int p = C + (int)(before >> (2 * QT_F));
-                s.box[nxt][p] = s.box[cur][i];
-                s.cnt[nxt][p] = s.cnt[cur][i];
+                s.box(nxt)[p] = s.box(cur)[i];
+                s.cnt(nxt)[p] = s.cnt(cur)[i];
                 s.uf[i] = p;
             }
         });
-    for (int i = tid; i < n_pts; i += QT_NT) {
-        const int j = (int)node[i];
+    pts.each([&](int, uint32_t v, uint32_t &nd) {
+        const int j = (int)nd;
         const int k = s.rank[j];
-        if (k >= 0 && k < n_proc) {
-            const uint32_t v = xy[i];
-            node[i] = (uint32_t)s.cf[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box[cur][j])];
-        } else {
-            node[i] = (uint32_t)s.uf[j];
-        }
-    }
+        if (k >= 0 && k < n_proc)
+            nd = (uint32_t)s.cf[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])];
+        else
+            nd = (uint32_t)s.uf[j];
+    });
     __syncthreads();
     *n_exp = (int)((tot >> QT_F) & QT_FMASK);
     return (int)(tot & QT_FMASK) + (int)(tot >> (2 * QT_F));
 }
 
 /* count the quarters of every ranked node; ccnt[0 .. 4 * ranked) must be zero on entry */
-template <int QT_NT>
-__device__ void qt_count(const QtSmem &s, int cur, int n_pts,
-                         const uint32_t *__restrict__ xy, const uint32_t *__restrict__ node)
+template <int QT_NT, bool REG>
+__device__ __forceinline__ void qt_count(const QtSmem &s, int cur, QtPts<QT_NT, REG> &pts)
 {
-    const int tid = threadIdx.x;
-    for (int i = tid; i < n_pts; i += QT_NT) {
-        const int j = (int)node[i];
+    pts.each([&](int, uint32_t v, uint32_t &nd) {
+        const int j = (int)nd;
         const int k = s.rank[j];
-        if (k >= 0) {
-            const uint32_t v = xy[i];
-            atomicAdd(&s.ccnt[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box[cur][j])], 1);
-        }
-    }
+        if (k >= 0)
+            atomicAdd(&s.ccnt[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])], 1);
+    });
     __syncthreads();
 }
 
-template <int QT_NT>
-__global__ void __launch_bounds__(QT_NT, 1024 / QT_NT)
-k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__restrict__ cand_xy,
-           const uint32_t *__restrict__ cand_score, uint32_t *__restrict__ cand_node,
-           const int *__restrict__ ncand, uint32_t *__restrict__ lkp_xy,
-           uint32_t *__restrict__ lkp_score, int *__restrict__ nlkp, int *__restrict__ err)
+template <int QT_NT, bool REG>
+__device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32_t *__restrict__ cand_xy,
+                                       const uint32_t *__restrict__ cand_score, uint32_t *__restrict__ cand_node,
+                                       int n, uint32_t *__restrict__ lkp_xy, uint32_t *__restrict__ lkp_score,
+                                       int *__restrict__ nlkp, int *__restrict__ err, unsigned char *qt_raw, int &sh_proc)
 {
-    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
-    extern __shared__ __align__(16) unsigned char qt_raw[];
-    __shared__ int sh_proc;
     QtSmem s;
     {
         unsigned char *p = qt_raw;
-        s.box[0] = (int4 *)p; p += (size_t)M * 16;
-        s.box[1] = (int4 *)p; p += (size_t)M * 16;
+        s.M = M;
+        s.box_ = (int4 *)p; p += (size_t)M * 32;
         s.best = (unsigned long long *)p; p += (size_t)M * 8;
         s.wtmp = (qt_u64 *)p; p += 40 * 8;
-        s.cnt[0] = (int *)p; p += (size_t)M * 4;
-        s.cnt[1] = (int *)p; p += (size_t)M * 4;
+        s.cnt_ = (int *)p; p += (size_t)M * 8;
         s.rank = (int *)p; p += (size_t)M * 4;
         s.par = (int *)p; p += (size_t)M * 4;
         s.uf = (int *)p; p += (size_t)M * 4;
         s.ccnt = (int *)p; p += (size_t)M * 16;
         s.cf = (int *)p; p += (size_t)M * 16;
-        s.exp_pos[0] = (int *)p; p += (size_t)M * 4;
-        s.exp_pos[1] = (int *)p; p += (size_t)M * 4;
-        s.exp_size[0] = (int *)p; p += (size_t)M * 4;
-        s.exp_size[1] = (int *)p;
+        s.exp_pos_ = (int *)p; p += (size_t)M * 8;
+        s.exp_size_ = (int *)p;
     }
     const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
     const BorbLevel &L = plan->lv[level];
     const size_t cbase = (size_t)frame * (size_t)plan->cand_total + L.cand_off;
-    const uint32_t *xy = cand_xy + cbase;
     const uint32_t *score = cand_score + cbase;
-    uint32_t *node = cand_node + cbase;
-    int n = ncand[frame * BORB_MAXL + level];
-    if (n > L.cand_cap) { /* cannot happen (capacity is the NMS bound); never truncate silently */
-        if (tid == 0) atomicExch(err, 1);
-        n = L.cand_cap;
-    }
+    QtPts<QT_NT, REG> pts;
+    pts.xy = cand_xy + cbase;
+    pts.node = cand_node + cbase;
+    pts.n = n;
+    pts.load();
     const int N = L.quota;
 
     /* ---- roots (:674-739): point -> root by FLOAT division, empty roots dropped ---- */
@@ -240,12 +282,12 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
     const float hx = L.hx;
     for (int j = tid; j < n_ini; j += QT_NT) s.ccnt[j] = 0;
     __syncthreads();
-    for (int i = tid; i < n; i += QT_NT) {
-        int r = (int)__fdiv_rn((float)(xy[i] & 0xffff), hx);
+    pts.init([&](uint32_t v) -> uint32_t {
+        int r = (int)__fdiv_rn((float)(v & 0xffff), hx);
         r = min(max(r, 0), n_ini - 1);
-        node[i] = (uint32_t)r;
         atomicAdd(&s.ccnt[r], 1);
-    }
+        return (uint32_t)r;
+    });
     __syncthreads();
     int cur = 0;
     int S = (int)qt_scan_emit<QT_NT>(
@@ -253,12 +295,12 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
         [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
             if (g) {
                 const int p = (int)before;
-                s.box[0][p] = make_int4((int)__fmul_rn(hx, (float)j), 0, (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
-                s.cnt[0][p] = s.ccnt[j];
+                s.box(0)[p] = make_int4((int)__fmul_rn(hx, (float)j), 0, (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
+                s.cnt(0)[p] = s.ccnt[j];
                 s.cf[j] = p;
             }
         });
-    for (int i = tid; i < n; i += QT_NT) node[i] = (uint32_t)s.cf[node[i]];
+    pts.each([&](int, uint32_t, uint32_t &nd) { nd = (uint32_t)s.cf[nd]; });
     __syncthreads();
 
     /* ---- split passes (:741-927) ---- */
@@ -267,7 +309,7 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
         /* breadth pass: rank the multi-point nodes in list order (and clear their quarter counters) */
         const int prev = S;
         const int n_split = (int)qt_scan_emit<QT_NT>(
-            S, s.wtmp, [&](int j) -> qt_u64 { return (qt_u64)(s.cnt[cur][j] > 1); },
+            S, s.wtmp, [&](int j) -> qt_u64 { return (qt_u64)(s.cnt(cur)[j] > 1); },
             [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
                 const int k = (int)before;
                 s.rank[j] = g ? k : -1;
@@ -277,9 +319,9 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
                 }
             });
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
-        qt_count<QT_NT>(s, cur, n, xy, node);
+        qt_count<QT_NT, REG>(s, cur, pts);
         int n_exp;
-        S = qt_split<QT_NT>(s, cur, S, n_split, n, xy, node, &n_exp);
+        S = qt_split<QT_NT, REG>(s, cur, S, n_split, pts, &n_exp);
         cur = 1 - cur;
         if (S >= N || S == prev) break;
         if (S + 3 * n_exp <= N) continue;
@@ -294,17 +336,17 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
             if (tid == 0) sh_proc = E;
             __syncthreads();
             for (int e = tid; e < E; e += QT_NT) {
-                const int sz = s.exp_size[cur][e];
+                const int sz = s.exp_size(cur)[e];
                 int r = 0;
                 for (int f = 0; f < E; ++f) {
-                    const int sf = s.exp_size[cur][f];
+                    const int sf = s.exp_size(cur)[f];
                     r += (sf > sz) || (sf == sz && f > e);
                 }
-                s.rank[s.exp_pos[cur][e]] = r;
-                s.par[r] = s.exp_pos[cur][e];
+                s.rank[s.exp_pos(cur)[e]] = r;
+                s.par[r] = s.exp_pos(cur)[e];
             }
             __syncthreads();
-            qt_count<QT_NT>(s, cur, n, xy, node);
+            qt_count<QT_NT, REG>(s, cur, pts);
             /* size after processing ranks 0..k; stop at the first k reaching N */
             qt_scan_emit<QT_NT>(
                 E, s.wtmp,
@@ -316,7 +358,7 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
                     if (S + (int)before + (int)g >= N) atomicMin(&sh_proc, k + 1);
                 });
             const int n_proc = sh_proc;
-            S = qt_split<QT_NT>(s, cur, S, n_proc, n, xy, node, &n_exp);
+            S = qt_split<QT_NT, REG>(s, cur, S, n_proc, pts, &n_exp);
             cur = 1 - cur;
             if (S >= N || S == prev2) { done = true; break; }
         }
@@ -326,8 +368,7 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
     if (S > M) { if (tid == 0) atomicExch(err, 2); S = M; }
     for (int j = tid; j < S; j += QT_NT) s.best[j] = 0ull;
     __syncthreads();
-    for (int i = tid; i < n; i += QT_NT) {
-        const uint32_t v = xy[i];
+    pts.each([&](int i, uint32_t v, uint32_t &nd) {
         const unsigned x = v & 0xffff, y = v >> 16;
         const unsigned cr = (y - 3) / (unsigned)L.h_cell, cc = (x - 3) / (unsigned)L.w_cell;
         const unsigned long long key = ((unsigned long long)score[i] << 56) |
@@ -335,8 +376,8 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
                                        ((unsigned long long)(4095u - cc) << 32) |
                                        ((unsigned long long)(65535u - y) << 16) |
                                        (unsigned long long)(65535u - x);
-        atomicMax(&s.best[node[i]], key);
-    }
+        atomicMax(&s.best[nd], key);
+    });
     __syncthreads();
     uint32_t *oxy = lkp_xy + (size_t)frame * plan->kp_total + L.kp_off;
     uint32_t *osc = lkp_score + (size_t)frame * plan->kp_total + L.kp_off;
@@ -348,6 +389,29 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
         osc[j] = (uint32_t)(b >> 56);
     }
     if (tid == 0) nlkp[frame * BORB_MAXL + level] = S;
+}
+
+
+template <int QT_NT>
+__global__ void __launch_bounds__(QT_NT, 1024 / QT_NT)
+k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__restrict__ cand_xy,
+           const uint32_t *__restrict__ cand_score, uint32_t *__restrict__ cand_node,
+           const int *__restrict__ ncand, uint32_t *__restrict__ lkp_xy,
+           uint32_t *__restrict__ lkp_score, int *__restrict__ nlkp, int *__restrict__ err)
+{
+    const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
+    extern __shared__ __align__(16) unsigned char qt_raw[];
+    __shared__ int sh_proc;
+    const BorbLevel &L = plan->lv[blockIdx.x];
+    int n = ncand[blockIdx.y * BORB_MAXL + blockIdx.x];
+    if (n > L.cand_cap) { /* cannot happen (capacity is the NMS bound); never truncate silently */
+        if (threadIdx.x == 0) atomicExch(err, 1);
+        n = L.cand_cap;
+    }
+    if (QT_NT == QT_NT_LATENCY && n <= QT_RPT * QT_NT)
+        qt_run<QT_NT, QT_NT == QT_NT_LATENCY>(plan, M, cand_xy, cand_score, cand_node, n, lkp_xy, lkp_score, nlkp, err, qt_raw, sh_proc);
+    else
+        qt_run<QT_NT, false>(plan, M, cand_xy, cand_score, cand_node, n, lkp_xy, lkp_score, nlkp, err, qt_raw, sh_proc);
 }
 
 #endif
