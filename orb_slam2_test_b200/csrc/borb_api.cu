@@ -124,6 +124,9 @@ struct borb_extractor {
     cudaStream_t stream2 = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
+    /* single-launch level chain of the latency shape (k_pyr_chain): per (tile, level) rectangles, shared-memory layout */
+    PyrChainRect *d_chain = nullptr;
+    int chain_tiles = 0, chain_off_b = 0, chain_off_t = 0, chain_smem = 0;
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
     BorbPlan *d_plan = nullptr;
@@ -254,7 +257,7 @@ void free_geometry(borb_extractor *h)
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
-                   h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
+                   h->d_chain, h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
@@ -266,6 +269,7 @@ void free_geometry(borb_extractor *h)
     h->d_mt_cache = nullptr; h->d_mt_more = nullptr; h->d_mt_occ = h->h_mt_occ = nullptr;
     h->d_mt_ent = nullptr; h->d_mt_cnt = h->d_mt_m12 = h->h_mt_m12 = nullptr; h->h_mt_unxy = nullptr;
     h->d_gray = nullptr;
+    h->d_chain = nullptr; h->chain_tiles = 0;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
     h->d_cell_start = h->d_cell_idx = h->d_cell_of = h->h_cell_start = h->h_cell_idx = nullptr;
@@ -286,6 +290,71 @@ void free_geometry(borb_extractor *h)
     h->have_plan = false;
     h->results_on_host = h->pyramid_on_host = false;
     h->last_n = 0;
+}
+
+/* Rectangles of k_pyr_chain: the levels are cut by one gx x gy grid (x cuts on multiples of 4 so that a tile's
+ * rows are whole words of the padded plane); from the last level back, a tile needs its own rectangle, the
+ * interior pixels its part of the reflect-101 frame mirrors, and whatever the taps of its next level's rectangle
+ * reach (cv::resize's clamped x taps, run-time clipped y taps: resize_axis above). */
+int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &tab_i)
+{
+    const int nl = P.nlevels;
+    const BorbLevel &Z = P.lv[nl - 1];
+    const int gx = std::max(1, Z.w / PCH_TW), gy = std::max(1, Z.h / PCH_TH);
+    std::vector<PyrChainRect> rects((size_t)gx * gy * nl);
+    long long max_a = 0, max_b = 0, max_t = 0;
+    for (int ty = 0; ty < gy; ++ty)
+        for (int tx = 0; tx < gx; ++tx) {
+            PyrChainRect *R = &rects[((size_t)ty * gx + tx) * nl];
+            int nx0 = 0, ny0 = 0, nx1 = 0, ny1 = 0; /* need(l + 1) */
+            long long t = 0;
+            for (int l = nl - 1; l >= 0; --l) {
+                const BorbLevel &L = P.lv[l];
+                const int ox0 = tx == 0 ? 0 : (int)((long long)tx * L.w / gx) & ~3;
+                const int ox1 = tx == gx - 1 ? L.w : (int)((long long)(tx + 1) * L.w / gx) & ~3;
+                const int oy0 = (int)((long long)ty * L.h / gy), oy1 = (int)((long long)(ty + 1) * L.h / gy);
+                int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1; /* need(l), exclusive upper bounds */
+                const bool own = ox1 > ox0 && oy1 > oy0;
+                if (own) {
+                    x0 = ox0; x1 = ox1; y0 = oy0; y1 = oy1;
+                    if (ox0 == 0) x1 = std::max(x1, std::min(BORB_EDGE, L.w - 1) + 1);
+                    if (ox1 == L.w) x0 = std::min(x0, std::max(0, L.w - 1 - BORB_EDGE));
+                    if (oy0 == 0) y1 = std::max(y1, std::min(BORB_EDGE, L.h - 1) + 1);
+                    if (oy1 == L.h) y0 = std::min(y0, std::max(0, L.h - 1 - BORB_EDGE));
+                }
+                if (l < nl - 1 && nx1 > nx0 && ny1 > ny0) {
+                    const BorbLevel &D = P.lv[l + 1];
+                    const int *xo = &tab_i[D.xofs_off], *yo = &tab_i[D.yofs_off];
+                    auto cy = [&](int v) { return std::min(std::max(v, 0), L.h - 1); };
+                    x0 = std::min(x0, xo[nx0]);
+                    x1 = std::max(x1, std::min(xo[nx1 - 1] + 1, L.w - 1) + 1);
+                    y0 = std::min(y0, cy(yo[ny0]));
+                    y1 = std::max(y1, cy(yo[ny1 - 1] + 1) + 1);
+                }
+                PyrChainRect &r = R[l];
+                if (x1 > x0 && y1 > y0) {
+                    r.nx0 = (short)x0; r.ny0 = (short)y0; r.nw = (short)(x1 - x0); r.nh = (short)(y1 - y0);
+                } else {
+                    r.nx0 = r.ny0 = r.nw = r.nh = 0;
+                    x0 = y0 = x1 = y1 = 0;
+                }
+                r.ox0 = (short)ox0; r.oy0 = (short)oy0; r.ox1 = (short)(own ? ox1 : ox0); r.oy1 = (short)(own ? oy1 : oy0);
+                const long long bytes = (long long)pch_pitch(r.nw) * r.nh + 16; /* + slack: the x tap pair of the last pixel */
+                if (l & 1) max_b = std::max(max_b, bytes); else max_a = std::max(max_a, bytes);
+                if (l > 0) t += (long long)(pch_pitch(r.nw) + r.nh) * 8;
+                nx0 = x0; ny0 = y0; nx1 = x1; ny1 = y1;
+            }
+            max_t = std::max(max_t, t);
+        }
+    h->chain_tiles = 0;
+    const long long off_b = align_up(max_a, 16), off_t = align_up(off_b + max_b, 16), total = off_t + max_t;
+    if (total > 160 * 1024) return BORB_OK; /* tiles of this geometry do not fit: the per-level kernels serve every shape */
+    CU(cudaMalloc(&h->d_chain, rects.size() * sizeof(PyrChainRect)));
+    CU(cudaMemcpy(h->d_chain, rects.data(), rects.size() * sizeof(PyrChainRect), cudaMemcpyHostToDevice));
+    CU(cudaFuncSetAttribute(k_pyr_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total));
+    h->chain_tiles = gx * gy;
+    h->chain_off_b = (int)off_b; h->chain_off_t = (int)off_t; h->chain_smem = (int)total;
+    return BORB_OK;
 }
 
 /* everything that depends on (cols, rows) */
@@ -455,6 +524,10 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMemcpy(h->d_tiles, tiles.data(), tiles.size() * sizeof(BorbTile), cudaMemcpyHostToDevice));
     if (!tab_i.empty()) CU(cudaMemcpy(h->d_tab_i, tab_i.data(), tab_i.size() * sizeof(int), cudaMemcpyHostToDevice));
     if (!tab_s.empty()) CU(cudaMemcpy(h->d_tab_s, tab_s.data(), tab_s.size() * sizeof(short), cudaMemcpyHostToDevice));
+    {
+        const int rc = build_chain(h, P, tab_i);
+        if (rc != BORB_OK) return rc;
+    }
     CU(cudaMemset(h->d_err, 0, 4));
     /* the blurred slab's frame/padding is never written; keep it defined */
     CU(cudaMemset(h->d_blur, 0, B * (size_t)P.pyr_bytes));
@@ -583,7 +656,12 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         stride = gstride;
         STAGE(6); /* K0 = evs[0] .. evs[6]; the pyramid stage time includes it */
     }
-    {   /* K1 */
+    static const bool chain_off = getenv("BORB_PYR_LEVELS") != nullptr; /* A/B knob: per-level kernels in every shape */
+    if (!chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm) {
+        /* K1, latency shape: the whole chain in one launch */
+        k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_tab_i, h->d_tab_s, dev_img,
+                                                                         step, stride, d_pyr, h->chain_off_b, h->chain_off_t);
+    } else {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         const int units = L0.pitch / 16;
         k_pyr_level0<<<dim3((units + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->plan, dev_img, step,

@@ -82,3 +82,28 @@ def test_flat_image_gives_nothing(oracle_built):
     k, d = ext(img)
     wk, wd = ora.extract(img)
     assert len(k) == 0 and len(wk) == 0 and d.shape == (0, 32)
+
+
+@pytest.mark.parametrize("shape", [synth.KITTI_SHAPE, synth.TUM_SHAPE, (251, 397), (263, 1001), (1080, 1920)])
+def test_pyramid_planes_in_both_launch_shapes(shape, oracle_built):
+    """K1 has two launch shapes: one launch for the whole level chain when the call is a frame or two
+    (k_pyr_chain), one launch per level otherwise.  Both must give the oracle's planes, frame included."""
+    from oracle.pyoracle import Oracle
+    from orb_slam2_test_b200 import ORBextractor
+    nb = 8
+    ext = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=nb)
+    ora = Oracle(1000, 1.2, 8, 20, 7)
+    imgs = np.stack([synth.make_noise_frame(shape, seed=11 + f) if f % 2 else synth.make_frame(shape, seed=11, frame=f)
+                     for f in range(nb)])
+    want = {}
+    for f in (0, nb - 1):
+        ora.extract(imgs[f])
+        want[f] = [ora.pyramid(l, 19) for l in range(8)]
+    ext.extract_batch(imgs, want_pyramid=True)  # per-level kernels
+    for f in (0, nb - 1):
+        for l in range(8):
+            assert np.array_equal(ext.pyramid_level(f, l, border=19), want[f][l]), f"per-level kernels, frame {f} L{l}"
+    for f in (0, nb - 1):            # the chain kernel
+        ext(imgs[f])
+        for l in range(8):
+            assert np.array_equal(ext.pyramid_level(0, l, border=19), want[f][l]), f"chain kernel, frame {f} L{l}"
