@@ -125,7 +125,9 @@ struct borb_extractor {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
     /* single-launch level chain of the latency shape (k_pyr_chain): per (tile, level) rectangles, shared-memory layout */
-    PyrChainRect *d_chain = nullptr;
+    PyrChainTile *d_chain = nullptr;
+    uint2 *d_chain_tabs = nullptr;
+    int chain_tstride = 0;
     int chain_tiles = 0, chain_off_b = 0, chain_off_t = 0, chain_smem = 0;
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
@@ -257,7 +259,7 @@ void free_geometry(borb_extractor *h)
                    h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
-                   h->d_chain, h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
+                   h->d_chain, h->d_chain_tabs, h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
@@ -269,7 +271,7 @@ void free_geometry(borb_extractor *h)
     h->d_mt_cache = nullptr; h->d_mt_more = nullptr; h->d_mt_occ = h->h_mt_occ = nullptr;
     h->d_mt_ent = nullptr; h->d_mt_cnt = h->d_mt_m12 = h->h_mt_m12 = nullptr; h->h_mt_unxy = nullptr;
     h->d_gray = nullptr;
-    h->d_chain = nullptr; h->chain_tiles = 0;
+    h->d_chain = nullptr; h->d_chain_tabs = nullptr; h->chain_tiles = 0;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
     h->d_cell_start = h->d_cell_idx = h->d_cell_of = h->h_cell_start = h->h_cell_idx = nullptr;
@@ -296,16 +298,19 @@ void free_geometry(borb_extractor *h)
  * rows are whole words of the padded plane); from the last level back, a tile needs its own rectangle, the
  * interior pixels its part of the reflect-101 frame mirrors, and whatever the taps of its next level's rectangle
  * reach (cv::resize's clamped x taps, run-time clipped y taps: resize_axis above). */
-int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &tab_i)
+int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &tab_i, const std::vector<short> &tab_s)
 {
     const int nl = P.nlevels;
     const BorbLevel &Z = P.lv[nl - 1];
-    const int gx = std::max(1, Z.w / PCH_TW), gy = std::max(1, Z.h / PCH_TH);
-    std::vector<PyrChainRect> rects((size_t)gx * gy * nl);
+    const char *etw = getenv("BORB_PCH_TW"), *eth = getenv("BORB_PCH_TH"); /* tuning knobs */
+    const int tw = etw ? std::max(4, atoi(etw)) : PCH_TW, th = eth ? std::max(2, atoi(eth)) : PCH_TH;
+    const int gx = std::max(1, Z.w / tw), gy = std::max(1, Z.h / th);
+    std::vector<PyrChainTile> tiles((size_t)gx * gy);
+    std::memset(tiles.data(), 0, tiles.size() * sizeof(PyrChainTile));
     long long max_a = 0, max_b = 0, max_t = 0;
     for (int ty = 0; ty < gy; ++ty)
         for (int tx = 0; tx < gx; ++tx) {
-            PyrChainRect *R = &rects[((size_t)ty * gx + tx) * nl];
+            PyrChainRect *R = tiles[(size_t)ty * gx + tx].r;
             int nx0 = 0, ny0 = 0, nx1 = 0, ny1 = 0; /* need(l + 1) */
             long long t = 0;
             for (int l = nl - 1; l >= 0; --l) {
@@ -347,11 +352,51 @@ int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &ta
             max_t = std::max(max_t, t);
         }
     h->chain_tiles = 0;
+    max_t = align_up(max_t, 16);
     const long long off_b = align_up(max_a, 16), off_t = align_up(off_b + max_b, 16), total = off_t + max_t;
     if (total > 160 * 1024) return BORB_OK; /* tiles of this geometry do not fit: the per-level kernels serve every shape */
-    CU(cudaMalloc(&h->d_chain, rects.size() * sizeof(PyrChainRect)));
-    CU(cudaMemcpy(h->d_chain, rects.data(), rects.size() * sizeof(PyrChainRect), cudaMemcpyHostToDevice));
+    /* per tile: table offsets, loop divisors, and the tap tables themselves relative to the source rectangles --
+     * x entries {sx | sx1 << 16, a0 | a1 << 16} (padded to a multiple of 4 with copies of the last), then y entries
+     * {sy0 | sy1 << 16, b0 | b1 << 16} -- so that the kernel's prologue is plain copies with no dependent loads */
+    const size_t tstride = (size_t)max_t / 8;
+    std::vector<uint2> tabs(tiles.size() * tstride, make_uint2(0u, 0u));
+    auto magic = [](int w) { return w > 1 ? 0xffffffffu / (uint32_t)w + 1u : 0u; };
+    for (size_t t = 0; t < tiles.size(); ++t) {
+        PyrChainTile &T = tiles[t];
+        uint2 *tab = &tabs[t * tstride];
+        int off = 0;
+        for (int l = 0; l < nl; ++l) {
+            const BorbLevel &L = P.lv[l];
+            const PyrChainRect &r = T.r[l];
+            T.toff[l] = off;
+            const int ex0 = r.ox0 == 0 ? -BORB_XPAD : r.ox0, ex1 = r.ox1 == L.w ? L.pitch - BORB_XPAD : r.ox1;
+            T.magic[l][0] = magic(pch_pitch(r.nw) >> 2);
+            T.magic[l][1] = magic((ex1 - ex0) >> 2);
+            if (l == 0 || r.nw == 0) continue;
+            const BorbLevel &S = P.lv[l - 1];
+            const PyrChainRect &q = T.r[l - 1];
+            const int nx = pch_pitch(r.nw);
+            for (int j = 0; j < nx; ++j) {
+                const int x = r.nx0 + std::min(j, r.nw - 1), sx = tab_i[L.xofs_off + x];
+                tab[off + j].x = (uint32_t)(sx - q.nx0) | ((uint32_t)(std::min(sx + 1, S.w - 1) - q.nx0) << 16);
+                tab[off + j].y = (uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x] | ((uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x + 1] << 16);
+            }
+            for (int j = 0; j < r.nh; ++j) {
+                const int y = r.ny0 + j, sy = tab_i[L.yofs_off + y];
+                const int sy0 = std::min(std::max(sy, 0), S.h - 1), sy1 = std::min(std::max(sy + 1, 0), S.h - 1);
+                tab[off + nx + j].x = (uint32_t)(sy0 - q.ny0) | ((uint32_t)(sy1 - q.ny0) << 16);
+                tab[off + nx + j].y = (uint32_t)(uint16_t)tab_s[L.yb_off + 2 * y] | ((uint32_t)(uint16_t)tab_s[L.yb_off + 2 * y + 1] << 16);
+            }
+            off += nx + r.nh;
+        }
+        T.toff[nl] = off;
+    }
+    CU(cudaMalloc(&h->d_chain, tiles.size() * sizeof(PyrChainTile)));
+    CU(cudaMemcpy(h->d_chain, tiles.data(), tiles.size() * sizeof(PyrChainTile), cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&h->d_chain_tabs, tabs.size() * sizeof(uint2)));
+    CU(cudaMemcpy(h->d_chain_tabs, tabs.data(), tabs.size() * sizeof(uint2), cudaMemcpyHostToDevice));
     CU(cudaFuncSetAttribute(k_pyr_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total));
+    h->chain_tstride = (int)tstride;
     h->chain_tiles = gx * gy;
     h->chain_off_b = (int)off_b; h->chain_off_t = (int)off_t; h->chain_smem = (int)total;
     return BORB_OK;
@@ -525,7 +570,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
     if (!tab_i.empty()) CU(cudaMemcpy(h->d_tab_i, tab_i.data(), tab_i.size() * sizeof(int), cudaMemcpyHostToDevice));
     if (!tab_s.empty()) CU(cudaMemcpy(h->d_tab_s, tab_s.data(), tab_s.size() * sizeof(short), cudaMemcpyHostToDevice));
     {
-        const int rc = build_chain(h, P, tab_i);
+        const int rc = build_chain(h, P, tab_i, tab_s);
         if (rc != BORB_OK) return rc;
     }
     CU(cudaMemset(h->d_err, 0, 4));
@@ -659,8 +704,8 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     static const bool chain_off = getenv("BORB_PYR_LEVELS") != nullptr; /* A/B knob: per-level kernels in every shape */
     if (!chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm) {
         /* K1, latency shape: the whole chain in one launch */
-        k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_tab_i, h->d_tab_s, dev_img,
-                                                                         step, stride, d_pyr, h->chain_off_b, h->chain_off_t);
+        k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_chain_tabs, h->chain_tstride,
+                                                                         dev_img, step, stride, d_pyr, h->chain_off_b, h->chain_off_t);
     } else {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         const int units = L0.pitch / 16;

@@ -226,84 +226,98 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
  * level l+1.  A pixel is a pure function of the previous level's pixels, so the few halo pixels that neighbouring
  * CTAs compute twice are identical: the planes are bit-for-bit those of k_pyr_level0 + k_pyr_resize.  The host
  * closes the dependencies per tile: need(l) = own(l) + frame sources + taps of need(l+1)  (PyrChainRect). */
+#ifndef PCH_NT
 #define PCH_NT 512
-#define PCH_TW 24 /* tile size aimed at on the LAST level */
-#define PCH_TH 16
+#endif
+#define PCH_TW 20 /* tile size aimed at on the LAST level (measured, single KITTI frame: 24x16 -> 62.0, 20x16 -> 61.3, 20x12 -> 60.0 us per call) */
+#define PCH_TH 12
 
 struct PyrChainRect {
     short nx0, ny0, nw, nh;   /* rectangle of the level this CTA computes (level pixels) */
     short ox0, oy0, ox1, oy1; /* rectangle it writes out; x bounds are multiples of 4 or the level width */
 };
 
+struct PyrChainTile { /* one per tile, built on the host (borb_api.cu: build_chain) */
+    PyrChainRect r[BORB_MAXL];
+    int toff[BORB_MAXL + 1];      /* first tap-table entry of level l; [nlevels] = entries in all */
+    uint32_t magic[BORB_MAXL][2]; /* divisors of the two per-level loops: words per computed row, per written row */
+    int pad[3];                   /* sizeof is a multiple of 16 */
+};
+static_assert(sizeof(PyrChainTile) % 16 == 0, "copied as uint4");
+
 __host__ __device__ __forceinline__ int pch_pitch(int nw) { return (nw + 3) & ~3; }
+/* i / w for i, w < 65536 by one multiply (the divisor is the same for the whole CTA) */
+__device__ __forceinline__ uint32_t pch_magic(int w) { return w > 1 ? 0xffffffffu / (uint32_t)w + 1u : 0u; }
+__device__ __forceinline__ int pch_div(int i, uint32_t m, int w) { return w > 1 ? (int)__umulhi((uint32_t)i, m) : i; }
 
 __global__ void __launch_bounds__(PCH_NT)
-k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainRect *__restrict__ rects,
-            const int *__restrict__ tab_i, const short *__restrict__ tab_s, const uint8_t *__restrict__ img, size_t step,
+k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restrict__ tiles,
+            const uint2 *__restrict__ gtabs, int tstride, const uint8_t *__restrict__ img, size_t step,
             size_t frame_stride, uint8_t *__restrict__ pyr, int off_b, int off_t)
 {
     const BorbPlan *plan = &plan_c;
     extern __shared__ __align__(16) unsigned char pch_smem[];
     const int tid = threadIdx.x, nl = plan->nlevels;
-    const PyrChainRect *R = rects + (size_t)blockIdx.x * nl;
+    const PyrChainTile *const gT = tiles + blockIdx.x;
     uint2 *const tabs = reinterpret_cast<uint2 *>(pch_smem + off_t);
     uint8_t *const frame = pyr + (size_t)blockIdx.y * (size_t)plan->pyr_bytes;
 
-    /* tap tables of every level, relative to the source rectangle: x entries {sx | sx1 << 16, a0 | a1 << 16}
-     * (padded to a multiple of 4 with copies of the last), then y entries {sy0 | sy1 << 16, b0 | b1 << 16} */
-    for (int l = 1, toff = 0; l < nl; ++l) {
-        const BorbLevel &L = plan->lv[l];
-        const BorbLevel &S = plan->lv[l - 1];
-        const PyrChainRect r = R[l], q = R[l - 1];
-        const int nx = pch_pitch(r.nw);
-        for (int i = tid; i < nx + r.nh; i += PCH_NT) {
-            uint2 e;
-            if (i < nx) {
-                const int x = r.nx0 + min(i, r.nw - 1);
-                const int sx = tab_i[L.xofs_off + x];
-                e.x = (uint32_t)(sx - q.nx0) | ((uint32_t)(min(sx + 1, S.w - 1) - q.nx0) << 16);
-                e.y = *reinterpret_cast<const uint32_t *>(tab_s + L.xa_off + 2 * x);
-            } else {
-                const int y = r.ny0 + i - nx;
-                const int sy = tab_i[L.yofs_off + y];
-                e.x = (uint32_t)(min(max(sy, 0), S.h - 1) - q.ny0) | ((uint32_t)(min(max(sy + 1, 0), S.h - 1) - q.ny0) << 16);
-                e.y = *reinterpret_cast<const uint32_t *>(tab_s + L.yb_off + 2 * y);
-            }
-            if (r.nw > 0) tabs[toff + i] = e;
-        }
-        toff += nx + r.nh;
-    }
-    /* level 0 of the tile: aligned words of the input (whatever its row step), stored byte by byte */
+    /* prologue, all plain copies in flight together: the tile's header and tap tables (built on the host) and
+     * level 0 of the tile from the input */
+    __shared__ __align__(16) PyrChainTile sT_;
+    if (tid < (int)(sizeof(PyrChainTile) / 16))
+        reinterpret_cast<uint4 *>(&sT_)[tid] = __ldg(reinterpret_cast<const uint4 *>(gT) + tid);
     {
-        const PyrChainRect r = R[0];
+        const int n4 = (__ldg(&gT->toff[nl]) + 1) >> 1; /* uint4 = two entries */
+        const uint4 *g4 = reinterpret_cast<const uint4 *>(gtabs + (size_t)blockIdx.x * tstride);
+        for (int i = tid; i < n4; i += PCH_NT) reinterpret_cast<uint4 *>(tabs)[i] = __ldg(g4 + i);
+    }
+    {   /* aligned words of the input (whatever its row step), stored byte by byte */
+        const PyrChainRect r = gT->r[0];
         const int pitch = pch_pitch(r.nw), K = (r.nw + 6) >> 2;
         const uint8_t *src = img + (size_t)blockIdx.y * frame_stride + (size_t)r.ny0 * step + r.nx0;
-        for (int i = tid; i < K * r.nh; i += PCH_NT) {
-            const int rr = i / K, k = i - rr * K;
-            const uintptr_t a = reinterpret_cast<uintptr_t>(src + (size_t)rr * step);
-            const int ph = (int)(a & 3), p0 = 4 * k - ph;
-            if (p0 >= r.nw) continue; /* every word read holds at least one byte of the row */
-            const uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(a - ph) + k);
-            uint8_t *d = pch_smem + rr * pitch;
+        const uint32_t km = pch_magic(K);
+        for (int i0 = tid; i0 < K * r.nh; i0 += 4 * PCH_NT) {
+            uint32_t w[4];
+            int p0[4], rr[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (p0 + j >= 0 && p0 + j < r.nw) d[p0 + j] = (uint8_t)(w >> (8 * j));
+            for (int u = 0; u < 4; ++u) { /* the loads of four words first, then their stores */
+                const int i = i0 + u * PCH_NT;
+                rr[u] = pch_div(i, km, K);
+                const int k = i - rr[u] * K;
+                const uintptr_t a = reinterpret_cast<uintptr_t>(src + (size_t)rr[u] * step);
+                const int ph = (int)(a & 3);
+                p0[u] = 4 * k - ph;
+                const bool on = i < K * r.nh && p0[u] < r.nw; /* every word read holds at least one byte of the row */
+                w[u] = on ? __ldg(reinterpret_cast<const uint32_t *>(a - ph) + k) : 0u;
+                if (!on) p0[u] = r.nw;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint8_t *d = pch_smem + rr[u] * pitch;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (p0[u] + j >= 0 && p0[u] + j < r.nw) d[p0[u] + j] = (uint8_t)(w[u] >> (8 * j));
+            }
         }
     }
     __syncthreads();
+    const PyrChainRect *const sR = sT_.r;
+    const int *const sToff = sT_.toff;
 
-    for (int l = 0, toff = 0; l < nl; ++l) {
+    for (int l = 0; l < nl; ++l) {
         const BorbLevel &L = plan->lv[l];
-        const PyrChainRect r = R[l];
+        const PyrChainRect r = sR[l];
         uint8_t *const buf = pch_smem + ((l & 1) ? off_b : 0);
         const int pitch = pch_pitch(r.nw);
         if (l > 0) {
             const uint8_t *const sbuf = pch_smem + ((l & 1) ? 0 : off_b);
-            const int spitch = pch_pitch(R[l - 1].nw);
-            const uint2 *const xt = tabs + toff, *const yt = xt + pitch;
+            const int spitch = pch_pitch(sR[l - 1].nw);
+            const uint2 *const xt = tabs + sToff[l], *const yt = xt + pitch;
             const int wpr = pitch >> 2;
+            const uint32_t wm = sT_.magic[l][0];
             for (int i = tid; i < wpr * r.nh; i += PCH_NT) {
-                const int y = i / wpr, xw = i - y * wpr;
+                const int y = pch_div(i, wm, wpr), xw = i - y * wpr;
                 const uint2 ey = yt[y];
                 const uint8_t *row0 = sbuf + (ey.x & 0xffffu) * spitch, *row1 = sbuf + (ey.x >> 16) * spitch;
                 const uint32_t b0 = ey.y << 16, b1 = ey.y & 0xffff0000u;
@@ -318,28 +332,33 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainRect *__restr
                 }
                 *reinterpret_cast<uint32_t *>(buf + y * pitch + 4 * xw) = v;
             }
-            toff += pitch + r.nh;
             __syncthreads();
         }
-        /* write the tile out, with the frame where it touches the image edge */
+            /* write the tile out, with the frame where it touches the image edge */
         if (r.ox1 > r.ox0 && r.oy1 > r.oy0) {
             const int ex0 = r.ox0 == 0 ? -BORB_XPAD : r.ox0, ex1 = r.ox1 == L.w ? L.pitch - BORB_XPAD : r.ox1;
             const int ey0 = r.oy0 == 0 ? -BORB_EDGE : r.oy0, ey1 = r.oy1 == L.h ? L.h + BORB_EDGE : r.oy1;
             const int wpr = (ex1 - ex0) >> 2;
             uint8_t *const dst = frame + L.off + (size_t)BORB_EDGE * L.pitch + BORB_XPAD;
+            const uint32_t om = sT_.magic[l][1], osh = (uint32_t)((-r.nx0) & 3) * 8u; /* px is a multiple of 4 */
             for (int i = tid; i < wpr * (ey1 - ey0); i += PCH_NT) {
-                const int yy = i / wpr, py = ey0 + yy, px = ex0 + 4 * (i - yy * wpr);
+                const int yy = pch_div(i, om, wpr), py = ey0 + yy, px = ex0 + 4 * (i - yy * wpr);
                 const uint8_t *row = buf + (reflect101(py, L.h) - r.ny0) * pitch - r.nx0;
                 uint32_t v = 0;
+                if (px >= 0 && px + 3 < L.w) { /* four interior columns: two aligned words of the staged row */
+                    const uint32_t *w = reinterpret_cast<const uint32_t *>(row + r.nx0 + ((px - r.nx0) & ~3));
+                    v = __funnelshift_r(w[0], w[1], osh);
+                } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int x = reflect101(min(max(px + j, -BORB_EDGE), L.w - 1 + BORB_EDGE), L.w); /* beyond the frame: don't care */
-                    v |= (uint32_t)row[x] << (8 * j);
+                    for (int j = 0; j < 4; ++j) {
+                        const int x = reflect101(min(max(px + j, -BORB_EDGE), L.w - 1 + BORB_EDGE), L.w); /* beyond the frame: don't care */
+                        v |= (uint32_t)row[x] << (8 * j);
+                    }
                 }
                 *reinterpret_cast<uint32_t *>(dst + (long long)py * L.pitch + px) = v;
             }
         }
-    }
+        }
 }
 
 #endif
