@@ -35,6 +35,7 @@
  * emit(i, g, before, total) for its own elements: g = gen(i), before = packed sums of the elements in
  * front of i, total = packed sums of all.  emit must not write what gen reads.  One trailing barrier
  * publishes what emit wrote; three barriers in all.  All threads must call. */
+#define QT_EBITS 11 /* creation index of an expandable node: < BORB_QT_MAXNODES = 2048 */
 #define QT_F 21
 #define QT_FMASK ((1u << QT_F) - 1u)
 typedef unsigned long long qt_u64;
@@ -113,7 +114,7 @@ __device__ __forceinline__ int4 qt_child_box(const int4 b, int q)
 /* bytes of dynamic shared memory for a list capacity of M nodes */
 static inline size_t qt_smem_bytes(int M)
 {
-    return (size_t)M * (2 * 16 + 8 + 2 * 4 + 3 * 4 + 2 * 16 + 4 * 4) + 40 * 8;
+    return (size_t)M * (2 * 16 + 8 + 2 * 4 + 3 * 4 + 2 * 16 + 4 * 4) + 40 * 8 + 16; /* + 16: zero padding of the rank keys */
 }
 
 /* The candidates of a (level, frame): in the latency shape (1024 threads, a CTA alone on its SM) a thread keeps
@@ -179,7 +180,7 @@ struct QtPts {
  * One packed scan gives the positions of the non-empty children (field 0), of the expandable ones
  * (field 1) and of the nodes that stay (field 2). */
 template <int QT_NT, bool REG>
-__device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, QtPts<QT_NT, REG> &pts, int *n_exp)
+__device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, QtPts<QT_NT, REG> &pts, int *n_exp, bool packed)
 {
     const int nc = 4 * n_proc;
     const int nxt = 1 - cur;
@@ -208,7 +209,7 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
                 if (n > 1) {
                     const int e = (int)((before >> QT_F) & QT_FMASK);
                     s.exp_pos(nxt)[e] = p;
-                    s.exp_size(nxt)[e] = n;
+                    s.exp_size(nxt)[e] = packed ? (n << QT_EBITS) | e : n; /* the ordered phase ranks by (size, creation order) */
                 }
             }
             if ((g >> (2 * QT_F)) & 1) {
@@ -275,6 +276,8 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     pts.node = cand_node + cbase;
     pts.n = n;
     pts.load();
+    for (int i = tid * 8; i < n; i += QT_NT * 8) /* the scores are read once, at the very end: have them in L1 by then */
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(score + i));
     const int N = L.quota;
 
     /* ---- roots (:674-739): point -> root by FLOAT division, empty roots dropped ---- */
@@ -304,6 +307,8 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     __syncthreads();
 
     /* ---- split passes (:741-927) ---- */
+    static_assert(BORB_QT_MAXNODES <= (1 << QT_EBITS), "rank key");
+    const bool packed = n < (1 << (31 - QT_EBITS)); /* (size << 11 | creation index) fits a positive int */
     bool done = (S == 0);
     while (!done) {
         /* breadth pass: rank the multi-point nodes in list order (and clear their quarter counters) */
@@ -321,7 +326,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
         qt_count<QT_NT, REG>(s, cur, pts);
         int n_exp;
-        S = qt_split<QT_NT, REG>(s, cur, S, n_split, pts, &n_exp);
+        S = qt_split<QT_NT, REG>(s, cur, S, n_split, pts, &n_exp, packed);
         cur = 1 - cur;
         if (S >= N || S == prev) break;
         if (S + 3 * n_exp <= N) continue;
@@ -334,16 +339,31 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
             for (int j = tid; j < S; j += QT_NT) s.rank[j] = -1;
             for (int c = tid; c < 4 * E; c += QT_NT) s.ccnt[c] = 0;
             if (tid == 0) sh_proc = E;
+            if (tid < 4) s.exp_size(cur)[E + tid] = 0; /* padding of the rank keys (the array has 4 spare entries) */
             __syncthreads();
-            for (int e = tid; e < E; e += QT_NT) {
-                const int sz = s.exp_size(cur)[e];
-                int r = 0;
-                for (int f = 0; f < E; ++f) {
-                    const int sf = s.exp_size(cur)[f];
-                    r += (sf > sz) || (sf == sz && f > e);
+            if (packed) { /* rank = number of larger keys; four keys per shared-memory load (zero padding never counts) */
+                const int4 *keys = reinterpret_cast<const int4 *>(s.exp_size(cur));
+                for (int e = tid; e < E; e += QT_NT) {
+                    const int key = s.exp_size(cur)[e];
+                    int r = 0;
+                    for (int f = 0; f < (E + 3) >> 2; ++f) {
+                        const int4 k = keys[f];
+                        r += (k.x > key) + (k.y > key) + (k.z > key) + (k.w > key);
+                    }
+                    s.rank[s.exp_pos(cur)[e]] = r;
+                    s.par[r] = s.exp_pos(cur)[e];
                 }
-                s.rank[s.exp_pos(cur)[e]] = r;
-                s.par[r] = s.exp_pos(cur)[e];
+            } else {
+                for (int e = tid; e < E; e += QT_NT) {
+                    const int sz = s.exp_size(cur)[e];
+                    int r = 0;
+                    for (int f = 0; f < E; ++f) {
+                        const int sf = s.exp_size(cur)[f];
+                        r += (sf > sz) || (sf == sz && f > e);
+                    }
+                    s.rank[s.exp_pos(cur)[e]] = r;
+                    s.par[r] = s.exp_pos(cur)[e];
+                }
             }
             __syncthreads();
             qt_count<QT_NT, REG>(s, cur, pts);
@@ -358,19 +378,20 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                     if (S + (int)before + (int)g >= N) atomicMin(&sh_proc, k + 1);
                 });
             const int n_proc = sh_proc;
-            S = qt_split<QT_NT, REG>(s, cur, S, n_proc, pts, &n_exp);
+            S = qt_split<QT_NT, REG>(s, cur, S, n_proc, pts, &n_exp, packed);
             cur = 1 - cur;
             if (S >= N || S == prev2) { done = true; break; }
         }
     }
 
     /* ---- one survivor per node (:930-948) ---- */
+    const uint32_t mh = 0xffffffffu / (uint32_t)L.h_cell + 1u, mw = 0xffffffffu / (uint32_t)L.w_cell + 1u; /* exact for 16-bit dividends */
     if (S > M) { if (tid == 0) atomicExch(err, 2); S = M; }
     for (int j = tid; j < S; j += QT_NT) s.best[j] = 0ull;
     __syncthreads();
     pts.each([&](int i, uint32_t v, uint32_t &nd) {
         const unsigned x = v & 0xffff, y = v >> 16;
-        const unsigned cr = (y - 3) / (unsigned)L.h_cell, cc = (x - 3) / (unsigned)L.w_cell;
+        const unsigned cr = L.h_cell > 1 ? __umulhi(y - 3, mh) : y - 3, cc = L.w_cell > 1 ? __umulhi(x - 3, mw) : x - 3;
         const unsigned long long key = ((unsigned long long)score[i] << 56) |
                                        ((unsigned long long)(4095u - cr) << 44) |
                                        ((unsigned long long)(4095u - cc) << 32) |
