@@ -254,7 +254,8 @@ int borb_match_rounds(const borb_extractor *cur);
 /* geometry only (valid after any extract call) */
 int borb_level_size(const borb_extractor *h, int level, int *cols, int *rows);
 
-/* number of kernel launches one extract call enqueues (for bench.py's gpu_launches) */
+/* number of kernel launches an extract call of the last call's shape enqueues (a frame or two: the level chain is
+ * one launch; before the first call: the count of the batched shape); for bench.py's gpu_launches */
 int borb_launches_per_call(const borb_extractor *h);
 /* CUDA-event time of the last borb_extract_device call's kernels, milliseconds (<0: n/a) */
 float borb_last_device_ms(const borb_extractor *h);

@@ -186,6 +186,7 @@ struct borb_extractor {
 
     std::vector<GraphEntry> graphs;
     int last_n = 0;          /* frames of the last call */
+    int last_launches = 0;   /* kernels the last call's shape enqueues */
     bool results_on_host = false, pyramid_on_host = false;
     float last_ms = -1.f;
 };
@@ -702,7 +703,9 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         STAGE(6); /* K0 = evs[0] .. evs[6]; the pyramid stage time includes it */
     }
     static const bool chain_off = getenv("BORB_PYR_LEVELS") != nullptr; /* A/B knob: per-level kernels in every shape */
-    if (!chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm) {
+    const bool chain = !chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm;
+    h->last_launches = (chain ? 1 : P.nlevels) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
+    if (chain) {
         /* K1, latency shape: the whole chain in one launch */
         k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_chain_tabs, h->chain_tstride,
                                                                          dev_img, step, stride, d_pyr, h->chain_off_b, h->chain_off_t);
@@ -1212,7 +1215,8 @@ float borb_last_prestep_ms(borb_extractor *h)
 
 int borb_launches_per_call(const borb_extractor *h)
 {
-    return h ? h->nlevels + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0) : 0;
+    if (!h) return 0;
+    return h->last_launches ? h->last_launches : h->nlevels + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
 }
 
 int borb_result(const borb_extractor *h, int frame, const borb_keypoint **kps, const uint8_t **desc, int *n)
