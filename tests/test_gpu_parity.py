@@ -107,3 +107,19 @@ def test_pyramid_planes_in_both_launch_shapes(shape, oracle_built):
         ext(imgs[f])
         for l in range(8):
             assert np.array_equal(ext.pyramid_level(0, l, border=19), want[f][l]), f"chain kernel, frame {f} L{l}"
+
+
+@pytest.mark.parametrize("cfg,count", [("K2k", 2), ("T1k", 3)])
+def test_chain_shape_with_several_frames(cfg, count, oracle_built):
+    """The single-launch level chain also serves calls of two or three frames (grid.y > 1): every frame's planes and
+    results against the oracle."""
+    shape, nf = CONFIGS[cfg]
+    ext, ora = _pair(nf, max_batch=count)
+    imgs = synth.make_sequence(shape, seed=9, start=2, count=count)
+    res = ext.extract_batch(imgs, want_pyramid=True)
+    assert ext.launches_per_call() == 5, "expected the single-frame launch shape"
+    for f in range(count):
+        want = ora.extract(imgs[f])
+        for l in range(8):
+            assert np.array_equal(ext.pyramid_level(f, l, border=19), ora.pyramid(l, 19)), f"frame {f} L{l}"
+        _assert_same(res[f], want, f"{cfg} frame {f} of {count}")
