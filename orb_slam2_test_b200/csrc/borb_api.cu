@@ -188,6 +188,7 @@ struct borb_extractor {
     int last_n = 0;          /* frames of the last call */
     int last_launches = 0;   /* kernels the last call's shape enqueues */
     bool results_on_host = false, pyramid_on_host = false;
+    int nout_frame_on_host = -1; /* a matcher call has downloaded this frame's keypoint count since the last extract call */
     float last_ms = -1.f;
 };
 
@@ -292,6 +293,7 @@ void free_geometry(borb_extractor *h)
     h->h_nout = h->h_err = nullptr;
     h->have_plan = false;
     h->results_on_host = h->pyramid_on_host = false;
+    h->nout_frame_on_host = -1;
     h->last_n = 0;
 }
 
@@ -1050,6 +1052,7 @@ int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int
     h->pending = true;
     h->pending_flags = flags;
     h->results_on_host = false;
+    h->nout_frame_on_host = -1;
     h->pyramid_on_host = false;
     return BORB_OK;
 }
@@ -1142,6 +1145,7 @@ int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int co
     CU(cudaEventRecord(h->ev1, h->stream));
     h->last_n = n;
     h->results_on_host = false;
+    h->nout_frame_on_host = -1;
     h->pyramid_on_host = false;
     return BORB_OK;
 }
@@ -1476,8 +1480,11 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     }
     const uint8_t *d_occ = nullptr;
     if (occupied) { /* the caller's view of F.mvpMapPoints on entry; sized by the frame's keypoint count, which is on the host */
-        CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+        if (!cur->results_on_host && cur->nout_frame_on_host != frame) { /* else the count is on the host already */
+            CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            cur->nout_frame_on_host = frame;
+        }
         const size_t nc0 = (size_t)std::min(cur->h_nout[frame], (int)K);
         std::memset(cur->h_mt_occ, 0, K);
         std::memcpy(cur->h_mt_occ, occupied, nc0);
@@ -1546,6 +1553,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    cur->nout_frame_on_host = frame;
     const int nc = std::min(cur->h_nout[frame], (int)K);
     std::memcpy(match, cur->h_mt_match, (size_t)nc * 4);
     if (n_cur) *n_cur = nc;
