@@ -159,3 +159,25 @@ def test_wide_cells_use_the_wider_tma_boxes(shape, nlevels, oracle_built):
         assert _same(ext(img), ora.extract(img)), f"{shape} seed {seed}"
     img = synth.make_noise_frame(shape, seed=3)
     assert _same(ext(img), ora.extract(img)), f"{shape} noise"
+
+
+@pytest.mark.parametrize("count", [1, 6])
+def test_device_input_with_odd_row_step_and_unaligned_base(count, oracle_built):
+    """borb_extract_device on a region of a larger device buffer: row step 701 (odd), base address 1 mod 4, frames
+    421 rows apart.  count = 1 runs the single-launch level chain, count = 6 the per-level kernels; both read the
+    input through aligned words at whatever alignment each row has."""
+    import torch
+    from orb_slam2_test_b200 import ORBextractor
+    rows, cols, step, frows = 373, 641, 701, 421
+    big = np.stack([synth.make_frame((frows, step), seed=21, frame=f) for f in range(count)])
+    dev = torch.from_numpy(big).cuda()
+    y0, x0 = 17, 32
+    base = dev.data_ptr() + y0 * step + x0
+    assert base % 4 == 1
+    ext = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=count)
+    ext.extract_device(base, count, cols, rows, step=step, frame_stride=frows * step)
+    got = ext.fetch()
+    ora = oracle_built.Oracle(1000, 1.2, 8, 20, 7)
+    for f in range(count):
+        want = ora.extract(np.ascontiguousarray(big[f, y0:y0 + rows, x0:x0 + cols]))
+        assert _same(got[f], want), f"frame {f}"
