@@ -141,6 +141,11 @@ struct borb_extractor {
     uint32_t *d_cand_xy = nullptr, *d_cand_score = nullptr, *d_cand_node = nullptr;
     int *d_ncand = nullptr, *d_nlkp = nullptr, *d_nout = nullptr, *d_err = nullptr;
     uint32_t *d_lkp_xy = nullptr, *d_lkp_score = nullptr;
+    /* one result slab on each side -- [records][descriptors][counts][error word] -- so that a call that fills the
+     * handle (n == max_batch, the single-frame case) brings everything back with ONE copy; d_out_kp, d_out_desc,
+     * d_nout, d_err and their h_ twins point into it */
+    uint8_t *d_res = nullptr, *h_res = nullptr;
+    size_t res_bytes = 0;
     BorbKpRec *d_out_kp = nullptr;
     uint8_t *d_out_desc = nullptr;
     /* pinned staging */
@@ -258,12 +263,12 @@ void free_geometry(borb_extractor *h)
     h->graphs.clear();
     void *dev[] = {h->d_plan, h->d_cells, h->d_tiles, h->d_tab_i, h->d_tab_s, h->d_in, h->d_pyr,
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
-                   h->d_nout, h->d_err, h->d_lkp_xy, h->d_lkp_score, h->d_out_kp, h->d_out_desc,
+                   h->d_res, h->d_lkp_xy, h->d_lkp_score,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
                    h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
                    h->d_chain, h->d_chain_tabs, h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
     for (void *p : dev) if (p) cudaFree(p);
-    void *host[] = {h->h_in, h->h_pyr, h->h_out_desc, h->h_out_kp, h->h_nout, h->h_err,
+    void *host[] = {h->h_in, h->h_pyr, h->h_res,
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
                     h->h_mt_last, h->h_mt_match, h->h_mt_occ, h->h_mt_m12, h->h_mt_unxy};
     for (void *p : host) if (p) cudaFreeHost(p);
@@ -291,6 +296,7 @@ void free_geometry(borb_extractor *h)
     h->d_lkp_xy = h->d_lkp_score = nullptr; h->d_out_kp = nullptr; h->d_out_desc = nullptr;
     h->h_in = h->h_pyr = h->h_out_desc = nullptr; h->h_out_kp = nullptr;
     h->h_nout = h->h_err = nullptr;
+    h->d_res = h->h_res = nullptr; h->res_bytes = 0;
     h->have_plan = false;
     h->results_on_host = h->pyramid_on_host = false;
     h->nout_frame_on_host = -1;
@@ -557,16 +563,22 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMalloc(&h->d_cand_node, B * (size_t)P.cand_total * 4));
     CU(cudaMalloc(&h->d_ncand, B * BORB_MAXL * 4));
     CU(cudaMalloc(&h->d_nlkp, B * BORB_MAXL * 4));
-    CU(cudaMalloc(&h->d_nout, B * 4));
-    CU(cudaMalloc(&h->d_err, 4));
+    {
+        const size_t o_desc = (size_t)align_up((long long)(B * (size_t)P.kp_total * sizeof(BorbKpRec)), 256);
+        const size_t o_nout = o_desc + (size_t)align_up((long long)(B * (size_t)P.kp_total * 32), 256);
+        const size_t o_err = o_nout + (size_t)align_up((long long)(B * 4), 16);
+        h->res_bytes = o_err + 16;
+        CU(cudaMalloc(&h->d_res, h->res_bytes));
+        CU(cudaMallocHost(&h->h_res, h->res_bytes));
+        CU(cudaMemset(h->d_res, 0, h->res_bytes));
+        std::memset(h->h_res, 0, h->res_bytes);
+        h->d_out_kp = reinterpret_cast<BorbKpRec *>(h->d_res); h->h_out_kp = reinterpret_cast<BorbKpRec *>(h->h_res);
+        h->d_out_desc = h->d_res + o_desc; h->h_out_desc = h->h_res + o_desc;
+        h->d_nout = reinterpret_cast<int *>(h->d_res + o_nout); h->h_nout = reinterpret_cast<int *>(h->h_res + o_nout);
+        h->d_err = reinterpret_cast<int *>(h->d_res + o_err); h->h_err = reinterpret_cast<int *>(h->h_res + o_err);
+    }
     CU(cudaMalloc(&h->d_lkp_xy, B * (size_t)P.kp_total * 4));
     CU(cudaMalloc(&h->d_lkp_score, B * (size_t)P.kp_total * 4));
-    CU(cudaMalloc(&h->d_out_kp, B * (size_t)P.kp_total * sizeof(BorbKpRec)));
-    CU(cudaMalloc(&h->d_out_desc, B * (size_t)P.kp_total * 32));
-    CU(cudaMallocHost(&h->h_out_kp, B * (size_t)P.kp_total * sizeof(BorbKpRec)));
-    CU(cudaMallocHost(&h->h_out_desc, B * (size_t)P.kp_total * 32));
-    CU(cudaMallocHost(&h->h_nout, B * 4));
-    CU(cudaMallocHost(&h->h_err, 4));
     CU(cudaMemcpy(h->d_plan, &P, sizeof P, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(h->d_cells, cells.data(), cells.size() * sizeof(BorbCell), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(h->d_tiles, tiles.data(), tiles.size() * sizeof(BorbTile), cudaMemcpyHostToDevice));
@@ -791,12 +803,16 @@ int enqueue_fetch(borb_extractor *h, int n, unsigned flags)
 {
     const BorbPlan &P = h->plan;
     cudaStream_t st = h->stream;
-    CU(cudaMemcpyAsync(h->h_nout, h->d_nout, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(h->h_out_kp, h->d_out_kp, (size_t)n * P.kp_total * sizeof(BorbKpRec),
-                       cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(h->h_out_desc, h->d_out_desc, (size_t)n * P.kp_total * 32,
-                       cudaMemcpyDeviceToHost, st));
+    if (n == h->max_batch) { /* the whole result slab in one copy */
+        CU(cudaMemcpyAsync(h->h_res, h->d_res, h->res_bytes, cudaMemcpyDeviceToHost, st));
+    } else {
+        CU(cudaMemcpyAsync(h->h_nout, h->d_nout, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h->h_out_kp, h->d_out_kp, (size_t)n * P.kp_total * sizeof(BorbKpRec),
+                           cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h->h_out_desc, h->d_out_desc, (size_t)n * P.kp_total * 32,
+                           cudaMemcpyDeviceToHost, st));
+    }
     if (flags & BORB_WANT_PYRAMID)
         CU(cudaMemcpyAsync(h->h_pyr, h->d_pyr, (size_t)n * (size_t)P.pyr_bytes,
                            cudaMemcpyDeviceToHost, st));
