@@ -163,6 +163,8 @@ struct borb_extractor {
     /* the per-keypoint step after the extractor (K8): undistortion + 64x48 grid, when a camera is set */
     bool have_cam = false;
     BorbCamera cam;
+    uint8_t *d_fr = nullptr, *h_fr = nullptr; /* one slab for K8's outputs, like d_res / h_res: [un_xy][cell_start][cell_idx][bounds] */
+    size_t fr_bytes = 0;
     float2 *d_un_xy = nullptr, *h_un_xy = nullptr;
     int *d_cell_start = nullptr, *d_cell_idx = nullptr, *d_cell_of = nullptr, *h_cell_start = nullptr, *h_cell_idx = nullptr;
     float *d_bounds = nullptr, *h_bounds = nullptr;
@@ -265,11 +267,11 @@ void free_geometry(borb_extractor *h)
                    h->d_blur, h->d_cand_xy, h->d_cand_score, h->d_cand_node, h->d_ncand, h->d_nlkp,
                    h->d_res, h->d_lkp_xy, h->d_lkp_score,
                    h->d_st_u, h->d_st_z, h->d_st_sad, h->d_st_kept, h->d_st_rows, h->d_st_ent, h->d_gray,
-                   h->d_un_xy, h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds,
+                   h->d_fr, h->d_cell_of,
                    h->d_chain, h->d_chain_tabs, h->d_mt_last, h->d_mt_choice, h->d_mt_taker, h->d_mt_match, h->d_mt_cache, h->d_mt_more, h->d_mt_occ, h->d_mt_ent, h->d_mt_cnt, h->d_mt_m12};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {h->h_in, h->h_pyr, h->h_res,
-                    h->h_st_u, h->h_st_z, h->h_st_kept, h->h_un_xy, h->h_cell_start, h->h_cell_idx, h->h_bounds,
+                    h->h_st_u, h->h_st_z, h->h_st_kept, h->h_fr,
                     h->h_mt_last, h->h_mt_match, h->h_mt_occ, h->h_mt_m12, h->h_mt_unxy};
     for (void *p : host) if (p) cudaFreeHost(p);
     h->d_mt_last = h->h_mt_last = nullptr;
@@ -281,6 +283,7 @@ void free_geometry(borb_extractor *h)
     h->d_chain = nullptr; h->d_chain_tabs = nullptr; h->chain_tiles = 0;
     h->in_cap = 0;
     h->d_un_xy = h->h_un_xy = nullptr;
+    h->d_fr = h->h_fr = nullptr; h->fr_bytes = 0;
     h->d_cell_start = h->d_cell_idx = h->d_cell_of = h->h_cell_start = h->h_cell_idx = nullptr;
     h->d_bounds = h->h_bounds = nullptr;
     h->frame_on_host = false;
@@ -817,10 +820,14 @@ int enqueue_fetch(borb_extractor *h, int n, unsigned flags)
         CU(cudaMemcpyAsync(h->h_pyr, h->d_pyr, (size_t)n * (size_t)P.pyr_bytes,
                            cudaMemcpyDeviceToHost, st));
     if (h->have_cam) {
-        CU(cudaMemcpyAsync(h->h_un_xy, h->d_un_xy, (size_t)n * P.kp_total * 8, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(h->h_cell_start, h->d_cell_start, (size_t)n * (FR_CELLS + 1) * 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(h->h_cell_idx, h->d_cell_idx, (size_t)n * P.kp_total * 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(h->h_bounds, h->d_bounds, (size_t)n * 16, cudaMemcpyDeviceToHost, st));
+        if (n == h->max_batch) {
+            CU(cudaMemcpyAsync(h->h_fr, h->d_fr, h->fr_bytes, cudaMemcpyDeviceToHost, st));
+        } else {
+            CU(cudaMemcpyAsync(h->h_un_xy, h->d_un_xy, (size_t)n * P.kp_total * 8, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h->h_cell_start, h->d_cell_start, (size_t)n * (FR_CELLS + 1) * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h->h_cell_idx, h->d_cell_idx, (size_t)n * P.kp_total * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h->h_bounds, h->d_bounds, (size_t)n * 16, cudaMemcpyDeviceToHost, st));
+        }
     }
     return BORB_OK;
 }
@@ -1009,15 +1016,18 @@ static int check_call(borb_extractor *h, const void *img, int n, int cols, int r
     if (rc != BORB_OK) return rc;
     if (h->have_cam && !h->d_un_xy) {
         const size_t B = (size_t)h->max_batch, K = (size_t)h->plan.kp_total;
-        CU(cudaMalloc(&h->d_un_xy, B * K * 8));
-        CU(cudaMalloc(&h->d_cell_start, B * (FR_CELLS + 1) * 4));
-        CU(cudaMalloc(&h->d_cell_idx, B * K * 4));
+        const size_t o_cs = (size_t)align_up((long long)(B * K * 8), 256);
+        const size_t o_ci = o_cs + (size_t)align_up((long long)(B * (FR_CELLS + 1) * 4), 256);
+        const size_t o_bd = o_ci + (size_t)align_up((long long)(B * K * 4), 256);
+        h->fr_bytes = o_bd + B * 16;
+        CU(cudaMalloc(&h->d_fr, h->fr_bytes));
+        CU(cudaMallocHost(&h->h_fr, h->fr_bytes));
+        CU(cudaMemset(h->d_fr, 0, h->fr_bytes));
         CU(cudaMalloc(&h->d_cell_of, B * K * 4));
-        CU(cudaMalloc(&h->d_bounds, B * 16));
-        CU(cudaMallocHost(&h->h_un_xy, B * K * 8));
-        CU(cudaMallocHost(&h->h_cell_start, B * (FR_CELLS + 1) * 4));
-        CU(cudaMallocHost(&h->h_cell_idx, B * K * 4));
-        CU(cudaMallocHost(&h->h_bounds, B * 16));
+        h->d_un_xy = reinterpret_cast<float2 *>(h->d_fr); h->h_un_xy = reinterpret_cast<float2 *>(h->h_fr);
+        h->d_cell_start = reinterpret_cast<int *>(h->d_fr + o_cs); h->h_cell_start = reinterpret_cast<int *>(h->h_fr + o_cs);
+        h->d_cell_idx = reinterpret_cast<int *>(h->d_fr + o_ci); h->h_cell_idx = reinterpret_cast<int *>(h->h_fr + o_ci);
+        h->d_bounds = reinterpret_cast<float *>(h->d_fr + o_bd); h->h_bounds = reinterpret_cast<float *>(h->h_fr + o_bd);
     }
     if (pre_active(h) && !h->d_gray) {
         h->gray_pitch = (ocols + 3) & ~3;
