@@ -165,6 +165,7 @@ class ORBextractor:
         self.want_pyramid = want_pyramid
         self.mvImagePyramid: list[np.ndarray] = []
         self._n = 0
+        self._views = {}
         self._ch = 1
 
     # -- the step before the extractor: cvtColor (src/Tracking.cc:176-201) and cv::remap
@@ -373,8 +374,18 @@ class ORBextractor:
         cnt = n.value
         if cnt == 0:
             return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
-        kps = np.ctypeslib.as_array(C.cast(kp, C.POINTER(C.c_uint8)), shape=(cnt * 28,)).view(KP_DTYPE)
-        desc = np.ctypeslib.as_array(C.cast(de, C.POINTER(C.c_uint8)), shape=(cnt, 32))
+        # numpy views over the library's pinned result slots, made once per (slot address, capacity): building
+        # them per call through np.ctypeslib costs more than the call's kernels
+        K = self._lib.borb_max_keypoints(self._h)
+        key = (kp.value, de.value, K)
+        v = self._views.get(key)
+        if v is None:
+            if len(self._views) > 4096:
+                self._views.clear()
+            kb = (C.c_uint8 * (K * 28)).from_address(kp.value)
+            db = (C.c_uint8 * (K * 32)).from_address(de.value)
+            v = self._views[key] = (np.frombuffer(kb, dtype=KP_DTYPE), np.frombuffer(db, dtype=np.uint8).reshape(K, 32))
+        kps, desc = v[0][:cnt], v[1][:cnt]
         return (kps.copy(), desc.copy()) if copy else (kps, desc)
 
     def stereo_match(self, right: "ORBextractor", mbf: float, mb: float, keep_on_device: bool = False) -> None:
