@@ -192,6 +192,9 @@ struct borb_extractor {
     int mt_rounds = 0;
 
     std::vector<GraphEntry> graphs;
+    int graph_miss_streak = 0;
+    bool have_last_miss = false;
+    GraphKey last_miss = {};
     int last_n = 0;          /* frames of the last call */
     int last_launches = 0;   /* kernels the last call's shape enqueues */
     bool results_on_host = false, pyramid_on_host = false;
@@ -839,9 +842,20 @@ int run_cached(borb_extractor *h, const GraphKey &key, F body)
     if (!h->use_graph) return body();
     for (GraphEntry &g : h->graphs)
         if (g.key == key) {
+            h->graph_miss_streak = 0;
             CU(cudaGraphLaunch(g.exec, h->stream));
             return BORB_OK;
         }
+    /* A caller that hands over a different buffer on every call would pay a capture + instantiation each time:
+     * after 8 misses in a row a call shape is only captured once it has been seen twice in a row, and launched
+     * directly until then */
+    if (h->graph_miss_streak >= 8 && !(h->have_last_miss && h->last_miss == key)) {
+        h->last_miss = key;
+        h->have_last_miss = true;
+        return body();
+    }
+    ++h->graph_miss_streak;
+    h->have_last_miss = false;
     cudaGraph_t graph = nullptr;
     CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     const int rc = body();

@@ -181,3 +181,25 @@ def test_device_input_with_odd_row_step_and_unaligned_base(count, oracle_built):
     for f in range(count):
         want = ora.extract(np.ascontiguousarray(big[f, y0:y0 + rows, x0:x0 + cols]))
         assert _same(got[f], want), f"frame {f}"
+
+
+def test_a_new_input_buffer_on_every_call(oracle_built):
+    """Device input at a different address on every call: the graph cache cannot hit; after a few misses the
+    calls are launched directly instead of being captured each time, and a buffer that comes back is captured
+    again.  Results stay the oracle's throughout."""
+    import torch
+    from orb_slam2_test_b200 import ORBextractor
+    shape = synth.TUM_SHAPE
+    imgs = [synth.make_frame(shape, seed=31, frame=f) for f in range(3)]
+    ora = oracle_built.Oracle(1000, 1.2, 8, 20, 7)
+    want = [ora.extract(i) for i in imgs]
+    ext = ORBextractor(1000, 1.2, 8, 20, 7)
+    keep = []
+    for k in range(24):
+        dev = torch.from_numpy(imgs[k % 3]).cuda()
+        keep.append(dev)  # keep them alive so that every address is new
+        ext.extract_device(dev.data_ptr(), 1, shape[1], shape[0])
+        assert _same(ext.fetch()[0], want[k % 3]), f"call {k}"
+    for k in range(6):  # a stable buffer again
+        ext.extract_device(keep[0].data_ptr(), 1, shape[1], shape[0])
+        assert _same(ext.fetch()[0], want[0])
