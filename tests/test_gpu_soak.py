@@ -37,3 +37,22 @@ def test_mismatch_rate_is_zero(shape, nf, oracle_built):
     assert n_kp > 90 * nf
     assert (bad_frames, bad_kp, bad_angle, bad_bits) == (0, 0, 0, 0), \
         f"{bad_frames} frames differ: {bad_kp} keypoint fields, {bad_angle} angles > 1e-3 deg, {bad_bits} descriptor bits of {n_kp * 256}"
+
+
+@pytest.mark.parametrize("shape,nf", [(synth.KITTI_SHAPE, 2000), (synth.TUM_SHAPE, 1000), (synth.TUM_SHAPE, 2000)],
+                         ids=["K2k", "T1k", "T2k"])
+def test_single_frame_shape_equals_the_batched_shape(shape, nf):
+    """The same 96 frames, one per call (single-launch level chain, 1024-thread quadtree with the candidates in
+    registers, blur on a graph branch, one-copy download) and as one batch (per-level kernels, 256-thread quadtree):
+    byte-identical records and descriptors.  The batched results are the ones held against the oracle above."""
+    from orb_slam2_test_b200 import ORBextractor
+    frames = [synth.make_frame(shape, seed=s, frame=f, eye=e) for s in (101, 102, 103) for f in range(16) for e in (0, 1)]
+    ext = ORBextractor(nf, 1.2, 8, 20, 7, max_batch=len(frames), want_pyramid=False)
+    res = ext.extract_batch(np.stack(frames))
+    one = ORBextractor(nf, 1.2, 8, 20, 7, max_batch=1, want_pyramid=False)
+    differ = 0
+    for img, (k, d) in zip(frames, res):
+        k1, d1 = one(img)
+        assert one.launches_per_call() == 5
+        differ += not (k1.tobytes() == k.tobytes() and d1.tobytes() == d.tobytes())
+    assert differ == 0, f"{differ} of {len(frames)} frames differ between the two launch shapes"
