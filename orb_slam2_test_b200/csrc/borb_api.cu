@@ -1591,7 +1591,8 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
 #undef MATCH_LAUNCH
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(cur->h_mt_match, cur->d_mt_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
+    if (!cur->results_on_host && cur->nout_frame_on_host != frame) /* else the frame's keypoint count is on the host already */
+        CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     cur->nout_frame_on_host = frame;
     const int nc = std::min(cur->h_nout[frame], (int)K);
