@@ -224,11 +224,25 @@ def cpu_reference_run(procs: int, frames_per_proc: int) -> dict:
     return json.loads(out.stdout.strip().splitlines()[-1])
 
 
+CPU_FRAMES_PER_PROC = 32
+
+
+def cpu_baseline_stable(cores: int, runs: int = 5) -> dict:
+    """All-cores reference throughput: every worker pinned to its own core (oracle/cpu_bench.py), 32 frames per
+    process, median of `runs` runs with min and max reported."""
+    rs = [cpu_reference_run(cores, CPU_FRAMES_PER_PROC) for _ in range(runs)]
+    v = sorted(r["frames_per_s"] for r in rs)
+    return {"value": v[len(v) // 2], "unit": "frames/s", "cores": cores, "kind": rs[0]["kind"],
+            "min": v[0], "max": v[-1], "spread": (v[-1] - v[0]) / v[len(v) // 2],
+            "sample": f"{rs[0]['frames']} KITTI-shape frames per run ({cores} pinned processes x {CPU_FRAMES_PER_PROC} frames, one extractor "
+                      f"each), median of {runs} runs, min {v[0]:.0f} max {v[-1]:.0f}"}
+
+
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
     cores = len(os.sched_getaffinity(0))
-    per_proc = 4
+    per_proc = CPU_FRAMES_PER_PROC
     for _ in range(min(args.warmup, 1)):
         cpu_reference_run(cores, 1)
     tot, wall, kind = 0, 0.0, "reference"
@@ -237,7 +251,7 @@ def run_reference_arm(args, rank, world):
         tot += r["frames"]
         wall += r["wall_s"]
         kind = r["kind"]
-    value = tot / wall
+    value = tot / wall  # = mean over the steps; the steps' own rates are in cpu_baseline.step_frames_per_s
     per_step = cores * per_proc
     sample = (f"bounded sample of the workload: {tot} frames ({per_step} per step), {cores} processes, "
               "one extractor per process, one frame at a time each")
@@ -678,9 +692,92 @@ def stereo_section(ORBextractor, synth, local, two, dev):
     return out
 
 
+def kseq_section(args, rank, world, local, synth, OrbStream, pinned_empty):
+    """BASELINE.json configs[4] as stated: the 4541-pair synthetic KITTI-00-shaped stereo sequence, host-fed, pair f on
+    rank f mod N, through one library feeder ring per GPU: left + right extraction, Frame::ComputeStereoMatches,
+    UndistortKeyPoints + AssignFeaturesToGrid on the device; mvKeys, mDescriptors (both eyes), mvuRight, mvDepth, mvKeysUn
+    and mGrid come back for every pair.  Timed pass: wall clock between barriers, max over ranks, generation excluded.
+    Second (untimed) pass: per-pair SHA-256 digests, re-ordered by frame index on rank 0, digest of digests compared with
+    tests/golden/kseq_digests.json = the reference's own Frame.cc over the same sequence (make_golden_kseq.py)."""
+    import torch
+    from orb_slam2_test_b200 import sequence
+    n_pairs = int(os.environ.get("BENCH_KSEQ_PAIRS", str(synth.KSEQ_PAIRS)))
+    if n_pairs <= 0:
+        return None
+    B = int(os.environ.get("BENCH_KSEQ_BATCH", "64"))
+    mine = list(sequence.shard_indices(n_pairs, rank, world))
+    t0 = time.perf_counter()
+    left, right = pinned_empty((len(mine), ROWS, COLS)), pinned_empty((len(mine), ROWS, COLS))
+    synth.kseq_fill(mine, left, right, threads=max(2, len(os.sched_getaffinity(0)) // world))
+    gen_s = time.perf_counter() - t0
+    K, BF = synth.KSEQ_K, synth.KSEQ_BF
+
+    def stream():
+        st = OrbStream(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, COLS, ROWS, batch=B, slots=3, device=local, stereo=True)
+        st.set_stereo(BF, BF / K[0])
+        st.set_camera(K, (0.0, 0.0, 0.0, 0.0))
+        return st
+
+    st = stream()
+    warm = min(len(mine), 4 * B)
+    sequence.run_stream_shard(st, mine[:warm], left, right, digest=False)  # graphs captured, buffers touched
+    barrier(world)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    timed = sequence.run_stream_shard(st, mine, left, right, digest=False)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3
+    barrier(world)
+    ms_all = all_max(ms, world)
+    up_b, down_b = st.link_bytes()
+    launches = st.launches_per_push() * ((len(mine) + B - 1) // B)
+    # second pass, untimed: digests
+    res = sequence.run_stream_shard(st, mine, left, right, digest=True)
+    st.close()
+    del left, right
+    merged = sequence.gather_items_to_rank0(res, rank, world)
+    if rank != 0:
+        return None
+    out = {"workload": "Kseq: %d synthetic KITTI-00-shaped stereo pairs (1241x376, 2000 kp per eye), pair f -> rank f mod N" % n_pairs,
+           "reference": "Examples/Stereo/stereo_kitti.cc:66-108 -> Frame::Frame src/Frame.cc:79-151",
+           "pairs": n_pairs, "pairs_per_s": n_pairs / (ms_all / 1e3), "images_per_s": 2 * n_pairs / (ms_all / 1e3),
+           "wall_ms": ms_all, "n_gpus": world, "batch_pairs": B,
+           "h2d_bytes_per_pair": up_b // B, "d2h_bytes_per_pair": down_b // B,
+           "link_GBps": (up_b + down_b) / B * n_pairs / (ms_all / 1e3) / 1e9,
+           "gpu_launches_rank0": launches, "generation_s_excluded": gen_s,
+           "keypoints_left_mean": float(np.mean([r.n_left for r in merged])),
+           "matched_mean": float(np.mean([r.n_matched for r in merged])),
+           "timed_pass_counts_equal_digest_pass": [(r.n_left, r.n_right, r.n_matched) for r in timed] ==
+                                                  [(r.n_left, r.n_right, r.n_matched) for r in res]}
+    try:
+        dig = sequence.sequence_digest(merged, n_pairs)
+        out["digest"] = dig
+        gold = json.loads((ROOT / "tests" / "golden" / "kseq_digests.json").read_text())
+        want = gold["prefix"].get(str(n_pairs))
+        out["digest_equals_reference"] = (dig == want) if want else None
+        out["digest_reference"] = "tests/golden/kseq_digests.json: the reference's own src/Frame.cc + ORBextractor.cc (oracle/_ref/libreframe.so) over the same pairs"
+    except Exception as e:  # noqa: BLE001
+        out["digest"] = f"unavailable ({type(e).__name__}: {e})"
+    return out
+
+
+def kseq_cpu_arm(cores: int) -> dict:
+    """The reference's stereo Frame constructor (libreframe.so: two extraction threads + ComputeStereoMatches + grid) on
+    all host cores, one process per two cores, over a bounded sample of the same pairs."""
+    procs = max(1, cores // 2)
+    runs = []
+    for _ in range(3):
+        out = subprocess.run([sys.executable, "-m", "oracle.cpu_bench", "--stereo", "--procs", str(procs), "--frames-per-proc", "12"],
+                             cwd=str(ROOT), capture_output=True, text=True, check=True)
+        runs.append(json.loads(out.stdout.strip().splitlines()[-1]))
+    v = sorted(r["frames_per_s"] for r in runs)
+    return {"pairs_per_s": v[1], "min": v[0], "max": v[2], "cores": cores, "kind": "reference",
+            "sample": f"{runs[0]['frames']} pairs per run ({procs} processes x 12 pairs, 2 threads each as src/Frame.cc:110-113), median of 3 runs"}
+
+
 def run_ours(args, rank, world, local):
     import torch
-    from orb_slam2_test_b200 import ORBextractor, synth
+    from orb_slam2_test_b200 import ORBextractor, OrbStream, synth
     from orb_slam2_test_b200.extractor import pinned_empty
     from orb_slam2_test_b200.sequence import shard_indices
 
@@ -755,47 +852,81 @@ def run_ours(args, rank, world, local):
         return
     ext.set_stage_timing(False)
 
-    # ---- e2e: host-facing C ABI, pinned host buffers, H2D + D2H inside the timed region ----
-    sub = min(int(os.environ.get("BENCH_E2E_SUB", "128")), F)  # frames per submit: small launches lose throughput to tails
+    # ---- e2e: the library's pipelined feeder (borb_stream_*), page-locked host buffers, H2D of every frame and
+    #      D2H of every result inside the timed region ----
+    ext.close()
+    sub = min(int(os.environ.get("BENCH_E2E_SUB", "128")), F)  # frames per push: small launches lose throughput to tails
     n_sub = max(1, F // sub)
-    depth = min(int(os.environ.get("BENCH_E2E_DEPTH", "4")), n_sub)
-    hosts = []
-    for i in range(depth):
-        h = pinned_empty((sub, ROWS, COLS))
-        h[:] = batch[(np.arange(sub) + i * sub) % F]
-        hosts.append(h)
-    exts = [ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=sub,
-                         want_pyramid=False) for _ in range(depth)]
-    kp_bytes = 0
+    n_streams = max(1, int(os.environ.get("BENCH_E2E_STREAMS", "2")))
+    slots = max(2, int(os.environ.get("BENCH_E2E_SLOTS", "3")))
+    host = pinned_empty((n_sub * sub, ROWS, COLS))
+    host[:] = batch[np.arange(n_sub * sub) % F]
 
-    def e2e_run(n_steps):
-        """n_steps x n_sub submits as ONE continuous pipeline with `depth` batches in flight (the
-        pipeline is drained only at the end, inside the timing)."""
-        nonlocal kp_bytes
-        inflight = []
-        for i in range(n_steps * n_sub):
-            j = i % depth
-            if len(inflight) == depth:
-                k = inflight.pop(0)
-                exts[k].wait()
-                kp_bytes += int(exts[k].counts().sum()) * 60
-            exts[j].submit_batch(hosts[j])
-            inflight.append(j)
-        for k in inflight:
-            exts[k].wait()
-            kp_bytes += int(exts[k].counts().sum()) * 60
+    def e2e_measure(want_pyramid: bool, steps: int, warm: int) -> dict:
+        """steps x n_sub pushes of `sub` frames as ONE continuous pipeline over n_streams rings (drained only at
+        the end, inside the timing); wall clock bracketed by barriers, max over ranks."""
+        streams = [OrbStream(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, COLS, ROWS, batch=sub, slots=slots, device=local,
+                             want_pyramid=want_pyramid) for _ in range(n_streams)]
+        fsz = ROWS * COLS
+        seen = {"kp": 0, "batches": 0}
 
-    e2e_run(W)
-    kp_bytes = 0
-    barrier(world)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    e2e_run(args.steps)
-    torch.cuda.synchronize()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
-    barrier(world)
-    e2e_ms_max = all_max(e2e_ms, world)
-    e2e_value = world * n_sub * sub * args.steps / (e2e_ms_max / 1e3)
+        def drain(st):
+            _, m = st.pop()
+            seen["kp"] += sum(st.count(j) for j in range(0, m, 16)) * 16  # every 16th item's count, cheaply
+            seen["batches"] += 1
+            st.release()
+
+        def run(n_steps):
+            seen["kp"] = seen["batches"] = 0
+            for i in range(n_steps * n_sub):
+                st = streams[i % n_streams]
+                if st.slots_free() == 0:
+                    drain(st)
+                st.push_ptr(host.ctypes.data + (i % n_sub) * sub * fsz, None, sub, tag=i)
+            for st in streams:
+                while st.in_flight():
+                    drain(st)
+
+        run(warm)
+        barrier(world)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        run(steps)
+        torch.cuda.synchronize()
+        ms_ = (time.perf_counter() - t0) * 1e3
+        barrier(world)
+        ms_all = all_max(ms_, world)
+        up_b, down_b = streams[0].link_bytes()
+        launches = streams[0].launches_per_push() * steps * n_sub
+        for st in streams:
+            st.close()
+        frames = n_sub * sub * steps
+        return {"value": world * frames / (ms_all / 1e3), "ms": ms_all, "h2d_bytes_per_step": n_sub * up_b,
+                "d2h_bytes_per_step": n_sub * down_b, "launches": launches, "batches": seen["batches"],
+                "GBps": world * frames / sub * (up_b + down_b) / (ms_all / 1e3) / 1e9}
+
+    e2e = e2e_measure(False, args.steps, W)
+    e2e_value = e2e["value"]
+    # the same loop with every frame's padded pyramid brought back too (mvImagePyramid for a host-side consumer such
+    # as the reference's own ComputeStereoMatches, src/Frame.cc:626,738,751,757): SURVEY.md 8 a11 "reported both ways"
+    e2e_pyr = e2e_measure(True, max(2, args.steps // 4), 1)
+    # raw copy ceiling of the box at this N, same sizes, no kernels (orb_slam2_test_b200/hostlink.py)
+    from orb_slam2_test_b200 import hostlink
+    link = hostlink.measure(local, sub * ROWS * COLS, e2e["d2h_bytes_per_step"] // n_sub, iters=40,
+                            barrier=(lambda: barrier(world)) if world > 1 else None)
+    link_s = all_max(link["both_s"], world)
+    link_GBps = world * (link["h2d_bytes"] + link["d2h_bytes"]) * link["iters"] / link_s / 1e9
+    link_up_s = all_max(link["h2d_alone_s"], world)
+    link_up_GBps = world * link["h2d_bytes"] * link["iters"] / link_up_s / 1e9
+    del host
+
+    kseq = None
+    if not os.environ.get("BENCH_NO_KSEQ"):
+        try:
+            kseq = kseq_section(args, rank, world, local, synth, OrbStream, pinned_empty)
+        except Exception as e:  # noqa: BLE001 -- an extra key must not take the headline line down
+            kseq = {"error": f"{type(e).__name__}: {e}"}
+            barrier(world)
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
@@ -856,11 +987,20 @@ def run_ours(args, rank, world, local):
     cores = len(os.sched_getaffinity(0))
     cpu = None
     if world == 1:
-        r = max((cpu_reference_run(cores, 8) for _ in range(2)), key=lambda q: q["frames_per_s"])  # best of 2
-        r1 = cpu_reference_run(1, 8)
-        cpu = {"value": r["frames_per_s"], "unit": "frames/s", "cores": cores, "kind": r["kind"],
-               "sample": f"{r['frames']} KITTI-shape frames, {cores} processes x 8 frames, one extractor each, best of 2 runs",
-               "single_core_frames_per_s": r1["frames_per_s"]}
+        cpu = cpu_baseline_stable(cores)
+        r1 = cpu_reference_run(1, 16)
+        cpu["single_core_frames_per_s"] = r1["frames_per_s"]
+        try:
+            out = subprocess.run([sys.executable, "-m", "oracle.cpu_bench", "--primitives"], cwd=str(ROOT), capture_output=True,
+                                 text=True, check=True)
+            cpu["primitive_ratio"] = json.loads(out.stdout.strip().splitlines()[-1])
+        except Exception as e:  # noqa: BLE001
+            cpu["primitive_ratio"] = {"unavailable": type(e).__name__}
+        if isinstance(kseq, dict) and "pairs_per_s" in kseq:
+            try:
+                kseq["cpu_baseline"] = kseq_cpu_arm(cores)
+            except Exception as e:  # noqa: BLE001
+                kseq["cpu_baseline"] = {"unavailable": type(e).__name__}
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": W, "ms_per_step": step_ms, "higher_is_better": True,
@@ -868,9 +1008,20 @@ def run_ours(args, rank, world, local):
         "config": bench_config(F),
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "frames/s",
-                "h2d_bytes_per_step": n_sub * sub * ROWS * COLS,
-                "d2h_bytes_per_step": int(kp_bytes / max(args.steps, 1)),
-                "how": f"{depth} handles x {sub}-frame batches in flight, pinned host buffers, wall clock; {numa_note}"},
+                "h2d_bytes_per_step": e2e["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": e2e["d2h_bytes_per_step"],
+                "link_GBps": e2e["GBps"],
+                "link_ceiling_GBps": link_GBps, "frac_of_link": e2e["GBps"] / link_GBps,
+                "link_ceiling_h2d_alone_GBps": link_up_GBps,
+                "frames_per_s_link_ceiling": world * sub * link["iters"] / link_s,
+                "gpu_launches": e2e["launches"],
+                "with_pyramid": {"value": e2e_pyr["value"], "unit": "frames/s", "h2d_bytes_per_step": e2e_pyr["h2d_bytes_per_step"],
+                                 "d2h_bytes_per_step": e2e_pyr["d2h_bytes_per_step"], "link_GBps": e2e_pyr["GBps"],
+                                 "what": "same loop with BORB_STREAM_PYRAMID: every frame's 8 padded levels (1.79 MB) come back too, "
+                                         "what a stock Frame.cc caller of mvImagePyramid pays"},
+                "how": f"{n_streams} library feeder rings (borb_stream_*) x {slots} slots x {sub}-frame batches: upload, kernel and "
+                       f"download streams per ring, page-locked host memory uploaded in place, wall clock between barriers, max over "
+                       f"ranks; link ceiling = plain cudaMemcpyAsync of the same sizes on every rank at once, no kernels; {numa_note}"},
         "gpu_launches": args.steps * launches_per_call,
         "roofline": {"bound": "hbm", "kernel": STAGE_KERNEL[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(STAGE_KERNEL[dom], F), "peak_source": peak_src,
@@ -883,6 +1034,7 @@ def run_ours(args, rank, world, local):
                      "path_achieved": algorithmic_bytes(n_kp) * value / world / 1e9,
                      "path_frac": algorithmic_bytes(n_kp) * value / world / 1e9 / peak},
         "cpu_baseline": cpu,
+        "kseq": kseq,
         "latency": lat,
         "stereo": stereo,
         "prestep": prestep,

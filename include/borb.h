@@ -245,6 +245,73 @@ typedef struct borb_init_frame {
 int borb_search_for_initialization(borb_extractor *cur, int frame, const borb_init_frame *f1, float *prev_matched,
                                    int window_size, float nnratio, unsigned flags, int32_t *matches12, int *nmatches);
 
+/* -- pipelined sequence feeder: replaces the drivers' frame loop around the extractor
+ *    (Examples/Stereo/stereo_kitti.cc:66-108 -> System::TrackStereo -> Frame::Frame, src/Frame.cc:79-151, whose two
+ *    ExtractORB threads :110-113 and ComputeStereoMatches :124 are the device work) for callers that have many
+ *    frames: SURVEY.md 8(e), one feeder per GPU --------------------------------------------------------------------
+ *
+ * A stream owns one extractor (two for stereo pairs) and a ring of `slots` batches.  Each slot has page-locked
+ * input and result buffers on the host and their twins on the device; uploads, kernels and downloads run on three
+ * CUDA streams chained by events, so batch k+1's upload and batch k-1's download overlap batch k's kernels on ONE
+ * stream object.  The kernels of a batch are one cached CUDA graph per (slot, eye).  Nothing is exchanged between
+ * streams (or GPUs): a sequence is sharded item-wise over one stream per GPU with no collective. */
+typedef struct borb_stream borb_stream;
+
+#define BORB_STREAM_STEREO 1u  /* an item is a stereo pair: left + right extractor, Frame::ComputeStereoMatches on
+                                  the device (needs borb_stream_set_stereo), mvuRight / mvDepth come back with it */
+#define BORB_STREAM_PYRAMID 2u /* also bring every item's padded pyramids back (mvImagePyramid for a host-side
+                                  consumer; ~4x the download) */
+
+/* batch = items (frames, or pairs) per push, slots >= 2 = ring depth.  Geometry is fixed at open. */
+int borb_stream_open(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast, int device,
+                     int cols, int rows, int batch, int slots, unsigned flags, borb_stream **out);
+void borb_stream_close(borb_stream *s);
+/* Frame::mbf and the baseline of the search range, as borb_stereo_match takes them */
+int borb_stream_set_stereo(borb_stream *s, float mbf, float mb);
+/* as borb_set_camera: undistorted positions + 64 x 48 grid come back with every item (both eyes: the right eye's
+ * are computed and not downloaded, as the reference's Frame never undistorts mvKeysRight) */
+int borb_stream_set_camera(borb_stream *s, const float *K, const float *dist, int n_dist);
+
+/* The page-locked input buffer of the slot the next push will use (eye 0 = left / mono, 1 = right): a producer
+ * that decodes or renders frames straight into it saves the staging copy.  capacity = batch * rows * cols bytes,
+ * frames densely packed.  BORB_ERR_STATE when the ring is full (pop first). */
+int borb_stream_input(borb_stream *s, int eye, uint8_t **buf, size_t *capacity);
+/* Enqueue one batch of n <= batch items and return at once.  left (and right, for pairs): n images in host
+ * memory, rows `step` bytes apart, images `frame_stride` bytes apart; page-locked dense memory is uploaded from
+ * where it lies, anything else is packed into the slot's buffer first.  left == NULL: the frames already are in
+ * the slot's input buffers (borb_stream_input).  tag travels with the batch.  BORB_ERR_STATE when the ring is full. */
+int borb_stream_push(borb_stream *s, const uint8_t *left, const uint8_t *right, int n, size_t step,
+                     size_t frame_stride, uint64_t tag);
+/* Block until the OLDEST batch in flight has its results on the host; they stay readable (and its slot stays
+ * reserved) until the next pop or borb_stream_release.  BORB_ERR_STATE when nothing is in flight. */
+int borb_stream_pop(borb_stream *s, uint64_t *tag, int *n);
+int borb_stream_release(borb_stream *s);
+int borb_stream_in_flight(const borb_stream *s); /* pushed, not yet popped */
+int borb_stream_slots_free(const borb_stream *s); /* pushes possible right now */
+/* results of the popped batch, item i, as borb_result / borb_stereo_result / borb_frame_grid / borb_pyramid */
+int borb_stream_result(const borb_stream *s, int eye, int item, const borb_keypoint **kps, const uint8_t **desc,
+                       int *n);
+int borb_stream_stereo_result(const borb_stream *s, int item, const float **u_right, const float **depth, int *n,
+                              int *n_matched);
+int borb_stream_frame_grid(const borb_stream *s, int item, const float **xy_un, const int32_t **cell_start,
+                           const int32_t **cell_idx, float *bounds);
+int borb_stream_pyramid(const borb_stream *s, int eye, int item, int level, const uint8_t **data, int *cols,
+                        int *rows, size_t *step);
+/* bytes one full batch moves over the host link: [0] host->device, [1] device->host */
+int borb_stream_link_bytes(const borb_stream *s, uint64_t *bytes);
+/* kernel launches one push enqueues (bench.py's gpu_launches) */
+int borb_stream_launches_per_push(const borb_stream *s);
+
+/* The feeder thread.  produce(user, index, left, right, max_items) writes up to max_items frames (pairs) of
+ * batch `index` (0, 1, 2 ...) into the page-locked buffers it is handed and returns how many (0 = end of the
+ * sequence, < 0 = abort); consume(user, s, tag, n) is called for every finished batch, in push order, tag = index,
+ * and reads it through the borb_stream_* result calls.  Both run on the feeder thread.  start returns at once;
+ * join waits for the end of the sequence and returns the first error (message through borb_last_error). */
+typedef int (*borb_produce_fn)(void *user, uint64_t index, uint8_t *left, uint8_t *right, int max_items);
+typedef void (*borb_consume_fn)(void *user, borb_stream *s, uint64_t tag, int n);
+int borb_stream_start(borb_stream *s, borb_produce_fn produce, borb_consume_fn consume, void *user);
+int borb_stream_join(borb_stream *s);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/borb.h"
@@ -145,7 +146,7 @@ struct borb_extractor {
      * handle (n == max_batch, the single-frame case) brings everything back with ONE copy; d_out_kp, d_out_desc,
      * d_nout, d_err and their h_ twins point into it */
     uint8_t *d_res = nullptr, *h_res = nullptr;
-    size_t res_bytes = 0;
+    size_t res_bytes = 0, res_o_desc = 0, res_o_nout = 0, res_o_err = 0;
     BorbKpRec *d_out_kp = nullptr;
     uint8_t *d_out_desc = nullptr;
     /* pinned staging */
@@ -164,7 +165,7 @@ struct borb_extractor {
     bool have_cam = false;
     BorbCamera cam;
     uint8_t *d_fr = nullptr, *h_fr = nullptr; /* one slab for K8's outputs, like d_res / h_res: [un_xy][cell_start][cell_idx][bounds] */
-    size_t fr_bytes = 0;
+    size_t fr_bytes = 0, fr_o_cs = 0, fr_o_ci = 0, fr_o_bd = 0;
     float2 *d_un_xy = nullptr, *h_un_xy = nullptr;
     int *d_cell_start = nullptr, *d_cell_idx = nullptr, *d_cell_of = nullptr, *h_cell_start = nullptr, *h_cell_idx = nullptr;
     float *d_bounds = nullptr, *h_bounds = nullptr;
@@ -177,6 +178,8 @@ struct borb_extractor {
     int st_span = 0;
     cudaEvent_t ev_peer = nullptr; /* recorded on this handle's stream for a peer handle to wait on */
     bool stereo_on_host = false;
+    unsigned long long extract_gen = 0; /* bumped by every extract call */
+    unsigned long long stereo_gen = 0;  /* extract_gen the last borb_stereo_match saw (0 = none) */
     /* frame-to-frame matcher (M1), allocated on first use: the last frame's packed arrays
      * [desc 32c][xyz 12c][angle 4c][octave 4c][flags c] for a capacity of c = mt_cap queries */
     unsigned char *d_mt_last = nullptr, *h_mt_last = nullptr;
@@ -574,6 +577,7 @@ int build_plan(borb_extractor *h, int cols, int rows)
         const size_t o_nout = o_desc + (size_t)align_up((long long)(B * (size_t)P.kp_total * 32), 256);
         const size_t o_err = o_nout + (size_t)align_up((long long)(B * 4), 16);
         h->res_bytes = o_err + 16;
+        h->res_o_desc = o_desc; h->res_o_nout = o_nout; h->res_o_err = o_err;
         CU(cudaMalloc(&h->d_res, h->res_bytes));
         CU(cudaMallocHost(&h->h_res, h->res_bytes));
         CU(cudaMemset(h->d_res, 0, h->res_bytes));
@@ -759,12 +763,14 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
          * (gridDim.x, gridDim.y); small jobs get one CTA per cell */
         int per_sm = 256; /* far more CTAs than fit at once: the hardware scheduler evens out the uneven
                              cells (measured: 12/SM 4.0 ms, 48/SM 3.5 ms, 400/SM 3.2 ms per 512 frames) */
-        if (const char *e = getenv("BORB_FAST_CTAS_PER_SM")) per_sm = std::max(1, atoi(e)); /* tuning knob */
+        static const int env_per_sm = getenv("BORB_FAST_CTAS_PER_SM") ? atoi(getenv("BORB_FAST_CTAS_PER_SM")) : 0; /* tuning knobs, read once */
+        static const int env_grid_y = getenv("BORB_FAST_GRID_Y") ? atoi(getenv("BORB_FAST_GRID_Y")) : 0;
+        if (env_per_sm > 0) per_sm = env_per_sm;
         const int ctas = h->n_sm * per_sm;
         dim3 grid(P.n_cells, n);
         if ((long long)P.n_cells * n > 2LL * ctas) {
             grid.y = std::min(n, 64);
-            if (const char *e = getenv("BORB_FAST_GRID_Y")) grid.y = std::max(1, std::min(n, atoi(e)));
+            if (env_grid_y > 0) grid.y = std::min(n, env_grid_y);
             grid.x = std::min(P.n_cells, std::max(1, ctas / (int)grid.y));
         }
 #define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->plan, h->d_cells, n, h->fast_maps, f0, \
@@ -837,7 +843,7 @@ int enqueue_fetch(borb_extractor *h, int n, unsigned flags)
 
 /* body(h) enqueues work on h->stream; run it through a cached CUDA graph when enabled */
 template <typename F>
-int run_cached(borb_extractor *h, const GraphKey &key, F body)
+int run_cached(borb_extractor *h, const GraphKey &key, F body, bool always_capture = false)
 {
     if (!h->use_graph) return body();
     for (GraphEntry &g : h->graphs)
@@ -849,7 +855,7 @@ int run_cached(borb_extractor *h, const GraphKey &key, F body)
     /* A caller that hands over a different buffer on every call would pay a capture + instantiation each time:
      * after 8 misses in a row a call shape is only captured once it has been seen twice in a row, and launched
      * directly until then */
-    if (h->graph_miss_streak >= 8 && !(h->have_last_miss && h->last_miss == key)) {
+    if (!always_capture && h->graph_miss_streak >= 8 && !(h->have_last_miss && h->last_miss == key)) {
         h->last_miss = key;
         h->have_last_miss = true;
         return body();
@@ -870,13 +876,25 @@ int run_cached(borb_extractor *h, const GraphKey &key, F body)
     e = cudaGraphInstantiate(&ge.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (e != cudaSuccess) return fail(BORB_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
-    if (h->graphs.size() >= 16) {
+    if (h->graphs.size() >= 48) {
         cudaGraphExecDestroy(h->graphs.front().exec);
         h->graphs.erase(h->graphs.begin());
     }
     h->graphs.push_back(ge);
     CU(cudaGraphLaunch(ge.exec, h->stream));
     return BORB_OK;
+}
+
+/* every extract call invalidates what the previous one left on the host -- and the stereo association, whose
+ * mvuRight / mvDepth are parallel to the PREVIOUS call's keypoints (stereo_gen != extract_gen from here on) */
+void note_new_extract(borb_extractor *h)
+{
+    ++h->extract_gen;
+    h->results_on_host = false;
+    h->nout_frame_on_host = -1;
+    h->pyramid_on_host = false;
+    h->stereo_on_host = false;
+    h->frame_on_host = false;
 }
 
 int check_device_err(borb_extractor *h)
@@ -1034,6 +1052,7 @@ static int check_call(borb_extractor *h, const void *img, int n, int cols, int r
         const size_t o_ci = o_cs + (size_t)align_up((long long)(B * (FR_CELLS + 1) * 4), 256);
         const size_t o_bd = o_ci + (size_t)align_up((long long)(B * K * 4), 256);
         h->fr_bytes = o_bd + B * 16;
+        h->fr_o_cs = o_cs; h->fr_o_ci = o_ci; h->fr_o_bd = o_bd;
         CU(cudaMalloc(&h->d_fr, h->fr_bytes));
         CU(cudaMallocHost(&h->h_fr, h->fr_bytes));
         CU(cudaMemset(h->d_fr, 0, h->fr_bytes));
@@ -1053,9 +1072,10 @@ static int check_call(borb_extractor *h, const void *img, int n, int cols, int r
 int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int rows, size_t step,
                      size_t stride, unsigned flags)
 {
+    /* before check_call: a geometry change there frees the buffers the pending call is still using */
+    if (h && h->pending) return fail(BORB_ERR_STATE, "previous submit has not been waited for");
     int rc = check_call(h, img, n, cols, rows, step, stride);
     if (rc != BORB_OK) return rc;
-    if (h->pending) return fail(BORB_ERR_STATE, "previous submit has not been waited for");
     if ((flags & BORB_WANT_PYRAMID) && (rc = ensure_pyr_host(h)) != BORB_OK) return rc;
     const size_t rowb = (size_t)cols * h->in_ch, fsz = rowb * rows;
     if ((rc = ensure_input(h, fsz)) != BORB_OK) return rc;
@@ -1091,9 +1111,7 @@ int borb_submit_host(borb_extractor *h, const uint8_t *img, int n, int cols, int
     h->last_n = n;
     h->pending = true;
     h->pending_flags = flags;
-    h->results_on_host = false;
-    h->nout_frame_on_host = -1;
-    h->pyramid_on_host = false;
+    note_new_extract(h);
     return BORB_OK;
 }
 
@@ -1161,6 +1179,7 @@ float borb_timer_ms(borb_extractor *h)
 int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n, int cols, int rows,
                      size_t step, size_t stride, float *ms)
 {
+    if (h && h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
     int rc = check_call(h, dev_img, n, cols, rows, step, stride);
     if (rc != BORB_OK) return rc;
     if (!ms) return fail(BORB_ERR_ARG, "ms is null");
@@ -1169,13 +1188,14 @@ int borb_stage_times(borb_extractor *h, const uint8_t *dev_img, int n, int cols,
     CU(cudaStreamSynchronize(h->stream));
     for (int i = 0; i < 5; ++i) CU(cudaEventElapsedTime(&ms[i], h->evs[i], h->evs[i + 1]));
     h->last_n = n;
-    h->results_on_host = h->pyramid_on_host = false;
+    note_new_extract(h);
     return BORB_OK;
 }
 
 int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int cols, int rows,
                         size_t step, size_t stride)
 {
+    if (h && h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
     int rc = check_call(h, dev_img, n, cols, rows, step, stride);
     if (rc != BORB_OK) return rc;
     GraphKey key = {1, dev_img, n, step, stride, 0, cols, rows};
@@ -1184,9 +1204,7 @@ int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int co
     if (rc != BORB_OK) return rc;
     CU(cudaEventRecord(h->ev1, h->stream));
     h->last_n = n;
-    h->results_on_host = false;
-    h->nout_frame_on_host = -1;
-    h->pyramid_on_host = false;
+    note_new_extract(h);
     return BORB_OK;
 }
 
@@ -1375,36 +1393,44 @@ int borb_set_rectify_map(borb_extractor *h, const float *map_x, const float *map
     return BORB_OK;
 }
 
-/* Frame::ComputeStereoMatches (src/Frame.cc:619-834) on the two handles' device-resident results */
-int borb_stereo_match(borb_extractor *l, borb_extractor *r, float mbf, float mb, unsigned flags)
+namespace {
+
+/* scratch of the stereo association on the left handle: SADs, per-row candidate tables (allocated on first use) */
+int ensure_stereo_scratch(borb_extractor *l)
 {
-    if (!l || !r || l == r) return fail(BORB_ERR_ARG, "two distinct handles are needed");
-    if (!l->have_plan || !r->have_plan || l->last_n < 1 || l->last_n != r->last_n)
-        return fail(BORB_ERR_STATE, "both handles need a finished extract call over the same number of frames");
+    if (l->d_st_sad) return BORB_OK;
+    const BorbPlan &P = l->plan;
+    const size_t B = (size_t)l->max_batch, K = (size_t)P.kp_total;
+    CU(cudaMalloc(&l->d_st_sad, B * K * 4));
+    l->st_span = (int)(4.f * l->scale[l->nlevels - 1]) + 3;
+    CU(cudaMalloc(&l->d_st_rows, B * (size_t)(P.rows + 1) * 4));
+    CU(cudaMalloc(&l->d_st_ent, B * K * (size_t)l->st_span * 2));
+    CU(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)((2 * (size_t)P.rows + ST_ROWS_NT) * 4)));
+    return BORB_OK;
+}
+
+int check_stereo_pair(const borb_extractor *l, const borb_extractor *r)
+{
     if (l->device != r->device) return fail(BORB_ERR_ARG, "handles live on devices %d and %d", l->device, r->device);
     if (l->plan.cols != r->plan.cols || l->plan.rows != r->plan.rows || l->nlevels != r->nlevels ||
         l->scale_factor != r->scale_factor || l->plan.kp_total != r->plan.kp_total)
         return fail(BORB_ERR_ARG, "left and right extractor differ in geometry or pyramid parameters");
-    if (!(mbf > 0.f) || !(mb > 0.f)) return fail(BORB_ERR_ARG, "mbf %g, mb %g", (double)mbf, (double)mb);
-    CU(cudaSetDevice(l->device));
+    /* S0 stores right-keypoint indices as 16-bit entries and S1 packs the index into the low 16 bits of its key */
+    if (l->plan.kp_total > 65535)
+        return fail(BORB_ERR_ARG, "the stereo association packs keypoint indices in 16 bits: %d keypoint slots per frame",
+                    l->plan.kp_total);
+    return BORB_OK;
+}
+
+/* S0 + S1 + S2 over the n frames whose results the two handles' (currently bound) result slabs hold; outputs to
+ * u / z / kept.  Runs on l's stream, ordered after r's; r's next call is ordered after it. */
+int enqueue_stereo(borb_extractor *l, borb_extractor *r, int n, float mbf, float mb, float *u, float *z, int *kept)
+{
     const BorbPlan &P = l->plan;
-    const size_t B = (size_t)l->max_batch, K = (size_t)P.kp_total;
-    if (!l->d_st_u) {
-        CU(cudaMalloc(&l->d_st_u, B * K * 4));
-        CU(cudaMalloc(&l->d_st_z, B * K * 4));
-        CU(cudaMalloc(&l->d_st_sad, B * K * 4));
-        CU(cudaMalloc(&l->d_st_kept, B * 4));
-        l->st_span = (int)(4.f * l->scale[l->nlevels - 1]) + 3;
-        CU(cudaMalloc(&l->d_st_rows, B * (size_t)(P.rows + 1) * 4));
-        CU(cudaMalloc(&l->d_st_ent, B * K * (size_t)l->st_span * 2));
-        CU(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)((2 * (size_t)P.rows + ST_ROWS_NT) * 4)));
-        CU(cudaMallocHost(&l->h_st_u, B * K * 4));
-        CU(cudaMallocHost(&l->h_st_z, B * K * 4));
-        CU(cudaMallocHost(&l->h_st_kept, B * 4));
-    }
+    const size_t K = (size_t)P.kp_total;
     if (!r->ev_peer) CU(cudaEventCreateWithFlags(&r->ev_peer, cudaEventDisableTiming));
-    const int n = l->last_n;
+    if (!l->ev_peer) CU(cudaEventCreateWithFlags(&l->ev_peer, cudaEventDisableTiming));
     /* the right extractor's kernels run on its own stream: order the match after them */
     CU(cudaEventRecord(r->ev_peer, r->stream));
     CU(cudaStreamWaitEvent(l->stream, r->ev_peer, 0));
@@ -1413,14 +1439,42 @@ int borb_stereo_match(borb_extractor *l, borb_extractor *r, float mbf, float mb,
         l->d_plan, r->d_out_kp, r->d_nout, l->st_span, l->d_st_rows, l->d_st_ent);
     k_stereo_match<<<grid, ST_NT, 0, l->stream>>>(l->d_plan, l->d_out_kp, l->d_out_desc, l->d_nout, r->d_out_kp,
                                                   r->d_out_desc, r->d_nout, l->st_span, l->d_st_rows, l->d_st_ent,
-                                                  l->d_pyr, r->d_pyr, mbf, mb, l->d_st_u, l->d_st_z, l->d_st_sad);
-    k_stereo_cut<<<n, ST_CUT_NT, 0, l->stream>>>(l->d_plan, l->d_nout, l->d_st_u, l->d_st_z, l->d_st_sad, l->d_st_kept);
+                                                  l->d_pyr, r->d_pyr, mbf, mb, u, z, l->d_st_sad);
+    k_stereo_cut<<<n, ST_CUT_NT, 0, l->stream>>>(l->d_plan, l->d_nout, u, z, l->d_st_sad, kept);
     CU(cudaGetLastError());
     /* the right handle must not start its next call before the match has read its buffers */
-    if (!l->ev_peer) CU(cudaEventCreateWithFlags(&l->ev_peer, cudaEventDisableTiming));
     CU(cudaEventRecord(l->ev_peer, l->stream));
     CU(cudaStreamWaitEvent(r->stream, l->ev_peer, 0));
+    return BORB_OK;
+}
+
+} // namespace
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:619-834) on the two handles' device-resident results */
+int borb_stereo_match(borb_extractor *l, borb_extractor *r, float mbf, float mb, unsigned flags)
+{
+    if (!l || !r || l == r) return fail(BORB_ERR_ARG, "two distinct handles are needed");
+    if (!l->have_plan || !r->have_plan || l->last_n < 1 || l->last_n != r->last_n)
+        return fail(BORB_ERR_STATE, "both handles need a finished extract call over the same number of frames");
+    int rc = check_stereo_pair(l, r);
+    if (rc != BORB_OK) return rc;
+    if (!(mbf > 0.f) || !(mb > 0.f)) return fail(BORB_ERR_ARG, "mbf %g, mb %g", (double)mbf, (double)mb);
+    CU(cudaSetDevice(l->device));
+    const BorbPlan &P = l->plan;
+    const size_t B = (size_t)l->max_batch, K = (size_t)P.kp_total;
+    if ((rc = ensure_stereo_scratch(l)) != BORB_OK) return rc;
+    if (!l->d_st_u) {
+        CU(cudaMalloc(&l->d_st_u, B * K * 4));
+        CU(cudaMalloc(&l->d_st_z, B * K * 4));
+        CU(cudaMalloc(&l->d_st_kept, B * 4));
+        CU(cudaMallocHost(&l->h_st_u, B * K * 4));
+        CU(cudaMallocHost(&l->h_st_z, B * K * 4));
+        CU(cudaMallocHost(&l->h_st_kept, B * 4));
+    }
+    const int n = l->last_n;
+    if ((rc = enqueue_stereo(l, r, n, mbf, mb, l->d_st_u, l->d_st_z, l->d_st_kept)) != BORB_OK) return rc;
     l->stereo_on_host = false;
+    l->stereo_gen = l->extract_gen; /* mvuRight / mvDepth are parallel to THIS call's keypoints */
     if (flags & BORB_STEREO_KEEP_ON_DEVICE) return BORB_OK;
     CU(cudaMemcpyAsync(l->h_st_u, l->d_st_u, (size_t)n * K * 4, cudaMemcpyDeviceToHost, l->stream));
     CU(cudaMemcpyAsync(l->h_st_z, l->d_st_z, (size_t)n * K * 4, cudaMemcpyDeviceToHost, l->stream));
@@ -1457,7 +1511,8 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     if (cur->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
     if (frame < 0 || frame >= cur->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, cur->last_n);
     if (n < 0 || (n > 0 && (!geo || !desc || !qflags || !octave))) return fail(BORB_ERR_ARG, "query arrays");
-    if (use_stereo && !cur->d_st_u) return fail(BORB_ERR_STATE, "no stereo result on this handle");
+    if (use_stereo && (!cur->d_st_u || cur->stereo_gen != cur->extract_gen))
+        return fail(BORB_ERR_STATE, "no stereo result for this handle's last extract call (run borb_stereo_match after it)");
     for (int i = 0; i < n; ++i)
         if ((qflags[i] & 1) && (octave[i] < 0 || octave[i] >= cur->nlevels))
             return fail(BORB_ERR_ARG, "octave %d of query %d", octave[i], i);
@@ -1745,3 +1800,5 @@ void borb_debug_sincos(float radians, float *s, float *c) { orb_sincosf_exact(ra
 int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_score_px(p, pitch, t_lo); }
 
 } // extern "C"
+
+#include "borb_stream.inl"

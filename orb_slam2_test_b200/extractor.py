@@ -40,6 +40,15 @@ SYMBOLS = [
     "borb_last_prestep_ms", "borb_set_camera", "borb_frame_grid",
     "borb_search_by_projection", "borb_search_local_points", "borb_search_for_initialization", "borb_match_rounds", "borb_max_keypoints",
 ]
+# the pipelined sequence feeder (bound in stream.py)
+STREAM_SYMBOLS = [
+    "borb_stream_open", "borb_stream_close", "borb_stream_set_stereo", "borb_stream_set_camera",
+    "borb_stream_input", "borb_stream_push", "borb_stream_pop", "borb_stream_release",
+    "borb_stream_in_flight", "borb_stream_slots_free", "borb_stream_result", "borb_stream_stereo_result",
+    "borb_stream_frame_grid", "borb_stream_pyramid", "borb_stream_link_bytes",
+    "borb_stream_launches_per_push", "borb_stream_start", "borb_stream_join",
+]
+SYMBOLS += STREAM_SYMBOLS
 
 
 class BorbError(RuntimeError):

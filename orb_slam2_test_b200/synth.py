@@ -101,6 +101,34 @@ def make_sequence(shape=KITTI_SHAPE, seed: int = 0, start: int = 0, count: int =
     return np.stack([make_frame(shape, seed, start + i, eye) for i in range(count)])
 
 
+# ---- BASELINE.json configs[4]: the KITTI-00-shaped stereo sequence ------------------------------
+
+KSEQ_PAIRS = 4541   # frames of KITTI odometry sequence 00 (the reference's Examples/Stereo/stereo_kitti.cc loop)
+KSEQ_SEED = 4541
+KSEQ_K = (718.856, 718.856, 607.1928, 185.2157)  # Examples/Stereo/KITTI00-02.yaml: fx, fy, cx, cy (no distortion)
+KSEQ_BF = 386.1448                               # Camera.bf
+
+
+def kseq_pair(f: int):
+    """(left, right) of pair f of the synthetic Kseq sequence: a pure function of f."""
+    return make_frame(KITTI_SHAPE, KSEQ_SEED, f, 0), make_frame(KITTI_SHAPE, KSEQ_SEED, f, 1)
+
+
+def kseq_fill(frames, left: np.ndarray, right: np.ndarray, threads: int = 0) -> None:
+    """Render pairs `frames` into left[i], right[i] (e.g. page-locked arrays), on a thread pool: the noise
+    generator and the array arithmetic release the GIL."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+    frames = list(frames)
+    _scene(KITTI_SHAPE[0], KITTI_SHAPE[1], KSEQ_SEED, 300)  # build the shared scene once, before the threads
+
+    def one(i):
+        left[i] = make_frame(KITTI_SHAPE, KSEQ_SEED, frames[i], 0)
+        right[i] = make_frame(KITTI_SHAPE, KSEQ_SEED, frames[i], 1)
+    with ThreadPoolExecutor(threads or max(1, len(os.sched_getaffinity(0)))) as ex:
+        list(ex.map(one, range(len(frames))))
+
+
 # ---- inputs for the step before the extractor (colour frames, stereo rectification maps) -------
 
 EUROC_SHAPE = (480, 752)

@@ -81,3 +81,95 @@ def test_incomplete_sequence_is_detected():
     res = _expected(5, True)
     with pytest.raises(RuntimeError):
         sequence.check_complete(res[:-1], 5, True)
+
+
+# ---- the pipelined runner (sequence.run_stream_shard) over a stand-in for OrbStream -------------------------------
+
+class _FakeStream:
+    """The ring bookkeeping of OrbStream (push / pop / release / slots_free) over the stand-in extract function;
+    no pixels are processed the way the product does -- only routing and ordering are under test here."""
+
+    def __init__(self, batch, slots, rows=8, cols=12):
+        self.batch, self.slots, self.rows, self.cols, self.eyes = batch, slots, rows, cols, 2
+        self.q, self.held = [], None
+
+    def slots_free(self):
+        return self.slots - len(self.q) - (self.held is not None)
+
+    def in_flight(self):
+        return len(self.q)
+
+    def push_ptr(self, lp, rp, n, tag=0):
+        import ctypes as C
+        assert self.slots_free() > 0
+        def arr(p):
+            buf = (C.c_uint8 * (n * self.rows * self.cols)).from_address(p)
+            return np.frombuffer(buf, np.uint8).reshape(n, self.rows, self.cols).copy()
+        self.q.append((tag, n, _fake_extract(arr(lp)), _fake_extract(arr(rp))))
+
+    def pop(self):
+        self.held = self.q.pop(0)
+        return self.held[0], self.held[1]
+
+    def release(self):
+        self.held = None
+
+    def result(self, item, eye=0, copy=True):
+        return self.held[2 + eye][item]
+
+    def count(self, item, eye=0):
+        return len(self.held[2 + eye][item][0])
+
+    def stereo_result(self, item, copy=True):
+        n = self.count(item, 0)
+        return np.full(n, 1.5, np.float32), np.full(n, 2.5, np.float32), n // 2
+
+
+def _stream_worker(rank, world, port, n_frames, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mine = list(sequence.shard_indices(n_frames, rank, world))
+        left = np.stack([_load(f, 0) for f in mine])
+        right = np.stack([_load(f, 1) for f in mine])
+        res = sequence.run_stream_shard(_FakeStream(batch=3, slots=2), mine, left, right)
+        assert [r.frame for r in res] == mine
+        merged = sequence.gather_items_to_rank0(res, rank, world)
+        if rank == 0:
+            q.put(sequence.sequence_digest(merged, n_frames))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_stream_runner_gives_the_single_rank_digest():
+    n_frames, world = 29, 2
+    left = np.stack([_load(f, 0) for f in range(n_frames)])
+    right = np.stack([_load(f, 1) for f in range(n_frames)])
+    one = sequence.run_stream_shard(_FakeStream(batch=4, slots=3), range(n_frames), left, right)
+    want = sequence.sequence_digest(sequence.gather_items_to_rank0(one, 0, 1), n_frames)
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_stream_worker, args=(r, world, port, n_frames, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got == want
+    with pytest.raises(RuntimeError):
+        sequence.sequence_digest(one[1:], n_frames)
+
+
+def test_kseq_golden_file_is_complete():
+    import json
+    from pathlib import Path
+    g = json.loads((Path(__file__).parent / "golden" / "kseq_digests.json").read_text())
+    assert g["pairs"] == 4541 and len(g["first_64"]) == 64 and set(g["prefix"]) == {"16", "64", "256", "1024", "4541"}
+    import hashlib
+    h = hashlib.sha256()
+    for d in g["first_64"]:
+        h.update(bytes.fromhex(d))
+    assert h.hexdigest() == g["prefix"]["64"]
