@@ -312,6 +312,29 @@ typedef void (*borb_consume_fn)(void *user, borb_stream *s, uint64_t tag, int n)
 int borb_stream_start(borb_stream *s, borb_produce_fn produce, borb_consume_fn consume, void *user);
 int borb_stream_join(borb_stream *s);
 
+/* -- allocation-free variant of the per-keypoint step.  NO COUNTERPART IN THE REFERENCE: added
+ *    for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ *    loops, harnesses that forbid allocation) --------------------------------------------------------------------
+ *
+ * The arithmetic of borb_set_camera + borb_frame_grid (cv::undistortPoints with P = K, the image bounds, the
+ * 64 x 48 keypoint grid; bit for bit the same results), but on buffers the CALLER owns, all in DEVICE memory of the
+ * current CUDA device, and with the kernel's scratch memory (one int per keypoint slot) in a static device array of
+ * BORB_NOALLOC_MAX_SLOTS entries (1 MiB, held by every GPU that loads the library until the process exits) instead
+ * of an allocation.  The call allocates and frees nothing (no cudaMalloc / cudaFree / cudaMallocHost, no library
+ * routine that allocates) and does not synchronise: the kernel is enqueued on `stream` (a cudaStream_t cast to
+ * void *; NULL = the default stream) and the outputs are valid when that stream reaches them.
+ *   dev_kps [n_frames][kp_stride] keypoint records, dev_counts [n_frames] keypoints per frame (<= kp_stride)
+ *   K = {fx, fy, cx, cy}, dist = {k1, k2, p1, p2[, k3]} (host memory, as borb_set_camera; k1 == 0: identity)
+ *   dev_xy_un [n_frames][kp_stride][2], dev_cell_start [n_frames][64*48 + 1], dev_cell_idx [n_frames][kp_stride],
+ *   dev_bounds [n_frames][4]: as borb_frame_grid describes them
+ * n_frames * kp_stride > BORB_NOALLOC_MAX_SLOTS is refused with BORB_ERR_CAPACITY.  Every call on a device shares
+ * the one scratch array (nothing in it needs clearing between calls: each entry a call reads it has written first),
+ * so calls that OVERLAP on the GPU -- two streams, two threads -- race: serialise them. */
+#define BORB_NOALLOC_MAX_SLOTS 262144
+int borb_undistort_grid_noalloc(const borb_keypoint *dev_kps, const int32_t *dev_counts, int n_frames, int kp_stride,
+                                int cols, int rows, const float *K, const float *dist, int n_dist, float *dev_xy_un,
+                                int32_t *dev_cell_start, int32_t *dev_cell_idx, float *dev_bounds, void *stream);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

@@ -1802,3 +1802,4 @@ int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_s
 } // extern "C"
 
 #include "borb_stream.inl"
+#include "borb_noalloc.inl"

@@ -49,6 +49,8 @@ STREAM_SYMBOLS = [
     "borb_stream_launches_per_push", "borb_stream_start", "borb_stream_join",
 ]
 SYMBOLS += STREAM_SYMBOLS
+# allocation-free variant of the per-keypoint step (no counterpart in the reference; see include/borb.h)
+SYMBOLS += ["borb_undistort_grid_noalloc"]
 
 
 class BorbError(RuntimeError):
@@ -124,6 +126,7 @@ def load_library() -> C.CDLL:
     lib.borb_max_keypoints.argtypes = [_vp]
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
                                        C.POINTER(C.c_int)]
+    lib.borb_undistort_grid_noalloc.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]
     _lib = lib
     return lib
 
