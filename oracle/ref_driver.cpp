@@ -42,7 +42,12 @@ const size_t kNodeBytes = sizeof(std::_List_node<ORB_SLAM2::ExtractorNode>);
 /* Every thread that allocates list nodes gets its own bump arena, carved from ONE address-space
  * reservation (untouched pages cost nothing), so that operator delete -- possibly running on
  * another thread, possibly after the allocating thread has exited -- recognises arena memory by a
- * range check and leaves it alone.  Arenas are never returned. */
+ * range check and leaves it alone.  A thread's arena goes back to a free list when the thread exits:
+ * the reference's Frame constructor starts two fresh threads per frame (src/Frame.cc:110-113), and
+ * without recycling a process would run out of arenas after 128 frames and silently fall back to
+ * malloc, i.e. to the raw heap-address tie-break.  Every list node an extraction allocates dies
+ * inside DistributeOctTree (lNodes is a local, src/ORBextractor.cc:682), so an exited thread's arena
+ * holds no live node. */
 const size_t kArenaBytes = size_t(64) << 20;
 const size_t kReserveBytes = size_t(16) << 30; /* 256 thread arenas per process, then plain malloc */
 thread_local char *t_arena = nullptr;
@@ -52,6 +57,22 @@ thread_local bool t_active = false;
  * Frame constructor spawns two, src/Frame.cc:110-113) */
 std::atomic<int> g_force_monotone{0};
 std::atomic<size_t> g_next_arena{0};
+std::atomic<long> g_malloc_fallbacks{0}; /* node allocations that fell through to malloc while monotone mode was on */
+/* free list of recycled arenas: fixed storage, spin lock (no allocation inside operator new) */
+char *g_free_arena[256];
+int g_n_free = 0;
+std::atomic_flag g_free_lock = ATOMIC_FLAG_INIT;
+struct ArenaReturn {
+    ~ArenaReturn()
+    {
+        if (!t_arena) return;
+        while (g_free_lock.test_and_set(std::memory_order_acquire)) {}
+        if (g_n_free < 256) g_free_arena[g_n_free++] = t_arena;
+        g_free_lock.clear(std::memory_order_release);
+        t_arena = nullptr;
+    }
+};
+thread_local ArenaReturn t_return;
 
 inline char *reservation()
 {
@@ -76,8 +97,15 @@ void *operator new(size_t n)
 {
     if ((t_active || g_force_monotone.load(std::memory_order_relaxed)) && n == kNodeBytes) {
         if (!t_arena && reservation()) {
-            const size_t off = g_next_arena.fetch_add(kArenaBytes);
-            if (off + kArenaBytes <= kReserveBytes) t_arena = reservation() + off;
+            (void)&t_return; /* odr-use: constructed here, destroyed (arena returned) at thread exit */
+            while (g_free_lock.test_and_set(std::memory_order_acquire)) {}
+            if (g_n_free > 0) t_arena = g_free_arena[--g_n_free];
+            g_free_lock.clear(std::memory_order_release);
+            if (!t_arena) {
+                const size_t off = g_next_arena.fetch_add(kArenaBytes);
+                if (off + kArenaBytes <= kReserveBytes) t_arena = reservation() + off;
+            }
+            t_used = 0;
         }
         const size_t need = (n + 15) & ~size_t(15);
         if (t_arena && t_used + need <= kArenaBytes) {
@@ -85,6 +113,7 @@ void *operator new(size_t n)
             t_used += need;
             return p;
         }
+        g_malloc_fallbacks.fetch_add(1, std::memory_order_relaxed);
     }
     void *p = std::malloc(n ? n : 1);
     if (!p) throw std::bad_alloc();
@@ -106,6 +135,16 @@ struct reforb_kp { /* == cv::KeyPoint, 28 bytes */
     float x, y, size, angle, response;
     int octave, class_id;
 };
+
+/* node allocations that missed the arena while monotone mode was on: must stay 0 for a canonical run */
+long reforb_malloc_fallbacks(void)
+{
+#ifdef REF_MONOTONE_ALLOC
+    return g_malloc_fallbacks.load();
+#else
+    return -1;
+#endif
+}
 
 void reforb_force_monotone(int on)
 {

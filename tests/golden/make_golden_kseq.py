@@ -10,8 +10,8 @@ Run in the build container (needs /root/reference built into oracle/_ref):
     python tests/golden/make_golden_kseq.py [--pairs 4541] [--procs 8]
 
 Per pair the digest is orb_slam2_test_b200.sequence.item_digest's: SHA-256 over mvKeys, mDescriptors,
-mvKeysRight, mDescriptorsRight, mvuRight, mvDepth.  The file keeps the per-pair digests of the first 64 pairs
-and the digest-of-digests of the prefixes 16, 64, 256, 1024 and 4541, so that a GPU test can check a short
+mvKeysRight, mDescriptorsRight, mvuRight, mvDepth.  The file keeps the per-pair digests of the first 64 pairs, the
+first 16 hex digits of every pair's digest (to localise a mismatch), and the digest-of-digests of the prefixes 16, 64, 256, 1024 and 4541, so that a GPU test can check a short
 prefix in seconds and bench.py the whole sequence.
 """
 import argparse
@@ -39,7 +39,10 @@ def pair_digest(f: int):
     h = hashlib.sha256()
     for k in ("kps_l", "desc_l", "kps_r", "desc_r", "u_right", "depth"):
         h.update(np.ascontiguousarray(r[k]).tobytes())
-    return f, h.hexdigest(), len(r["kps_l"]), len(r["kps_r"]), int((r["depth"] > 0).sum())
+    # canonical only while every quadtree node came from the monotone arena (oracle/ref_driver.cpp)
+    lib = RefFrame.load()
+    lib.reforb_malloc_fallbacks.restype = __import__("ctypes").c_long
+    return f, h.hexdigest(), len(r["kps_l"]), len(r["kps_r"]), int((r["depth"] > 0).sum()), int(lib.reforb_malloc_fallbacks())
 
 
 def main():
@@ -51,9 +54,14 @@ def main():
     with mp.get_context("fork").Pool(args.procs) as pool:
         res = pool.map(pair_digest, range(args.pairs), chunksize=16)
     res.sort()
+    missed = max(r[5] for r in res)
+    if missed != 0:
+        raise SystemExit(f"{missed} quadtree nodes were allocated outside the monotone arena: the run is not canonical")
     dig = [r[1] for r in res]
     out = {"what": "reference src/Frame.cc stereo constructor (oracle/_ref/libreframe.so, canonical tie-break) over synth.kseq_pair(f)",
            "seed": 4541, "pairs": args.pairs, "first_64": dig[:64],
+           # the first 16 hex digits of every pair's digest: enough to say WHICH pair differs when a prefix digest does
+           "all_short": "".join(d[:16] for d in dig),
            "keypoints_left_mean": float(np.mean([r[2] for r in res])), "keypoints_right_mean": float(np.mean([r[3] for r in res])),
            "matched_mean": float(np.mean([r[4] for r in res])), "prefix": {}}
     for p in PREFIXES:
