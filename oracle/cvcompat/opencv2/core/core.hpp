@@ -37,6 +37,8 @@
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_8UC3 16
+#define CV_8UC4 24
 #define CV_32F 5
 #define CV_32FC1 5
 #define CV_32FC2 13

@@ -30,7 +30,13 @@ using namespace ORB_SLAM2;
 
 extern "C" {
 
+#ifdef FRAME_DRIVER_NO_MONOTONE
+/* built against the B200 drop-in ORBextractor (tests/shim/Makefile: libshimframe.so): there is no host quadtree
+ * and so no allocator to switch -- the device quadtree IS the canonical tie-break */
+static void reforb_force_monotone(int) {}
+#else
 void reforb_force_monotone(int on); /* oracle/ref_driver.cpp, monotone-allocator build */
+#endif
 
 struct refframe_out {
     int n_left, n_right;

@@ -507,15 +507,23 @@ class RefFrame:
             cls._lib = lib
         return cls._lib
 
+    @staticmethod
+    def bind(lib: C.CDLL) -> C.CDLL:
+        """argtypes of the refframe_stereo entry point (oracle/frame_driver.cpp) on any library that exports it --
+        oracle/_ref/libreframe.so, or tests/shim/libshimframe.so (the same reference Frame.cc over the drop-in class)."""
+        lib.refframe_stereo.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int,
+                                        _vp, _vp, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int] + [_vp] * 10
+        return lib
+
     @classmethod
     def stereo(cls, left: np.ndarray, right: np.ndarray, K, dist, bf: float, mb: float, nfeatures=2000,
-               scale=1.2, nlevels=8, ini_th=20, min_th=7, canonical=True) -> dict:
+               scale=1.2, nlevels=8, ini_th=20, min_th=7, canonical=True, lib=None) -> dict:
         """Frame(imLeft, imRight, ...) of the reference -> its mvKeys / mDescriptors (both eyes),
         mvKeysUn positions, mvuRight, mvDepth, mGrid (as CSR) and image bounds.  `mb` is the value the
         uninitialised member holds when ComputeStereoMatches reads it (see oracle/frame_driver.cpp);
         canonical=True runs the two extraction threads with the monotone node allocator, so the
         keypoints are the canonical ones (= oracle = CUDA path)."""
-        lib = cls.load()
+        lib = lib if lib is not None else cls.load()
         left = np.ascontiguousarray(left); right = np.ascontiguousarray(right)
         rows, cols = left.shape
         cap = nfeatures + 64 * nlevels + 4096

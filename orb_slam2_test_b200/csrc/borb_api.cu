@@ -759,8 +759,8 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         K5_ON(h->stream2);
         CU(cudaEventRecord(h->ev_join, h->stream2));
     }
-    {   /* K2: persistent CTAs, a multiple of the SM count, walking (cell, frame) with strides
-         * (gridDim.x, gridDim.y); small jobs get one CTA per cell */
+    {   /* K2: persistent CTAs walking (cell, frame) items, frames first (stride gridDim.y), then cells (stride
+         * gridDim.x); small jobs get one CTA per (cell, frame) */
         int per_sm = 256; /* far more CTAs than fit at once: the hardware scheduler evens out the uneven
                              cells (measured: 12/SM 4.0 ms, 48/SM 3.5 ms, 400/SM 3.2 ms per 512 frames) */
         static const int env_per_sm = getenv("BORB_FAST_CTAS_PER_SM") ? atoi(getenv("BORB_FAST_CTAS_PER_SM")) : 0; /* tuning knobs, read once */
@@ -769,9 +769,11 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         const int ctas = h->n_sm * per_sm;
         dim3 grid(P.n_cells, n);
         if ((long long)P.n_cells * n > 2LL * ctas) {
-            grid.y = std::min(n, 64);
+            /* one CTA column per cell: a CTA keeps its cell and walks frames blockIdx.y, + gridDim.y, ... so that the
+             * per-cell lane geometry is computed once per CTA (k_fast.cuh) */
+            grid.x = std::min(P.n_cells, ctas);
+            grid.y = std::max(1, std::min(n, ctas / (int)grid.x));
             if (env_grid_y > 0) grid.y = std::min(n, env_grid_y);
-            grid.x = std::min(P.n_cells, std::max(1, ctas / (int)grid.y));
         }
 #define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->plan, h->d_cells, n, h->fast_maps, f0, \
                                                                    d_cand_xy, d_cand_score, d_ncand)

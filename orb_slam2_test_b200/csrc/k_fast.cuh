@@ -193,13 +193,19 @@ struct FastMaps { /* kernel parameter (__grid_constant__): one TMA descriptor pe
     int max_wh, max_pix, n_cells, ini_th, min_th;
 };
 
-__device__ __forceinline__ void fast_tma_window(const CUtensorMap *maps, const BorbCell &cell, int frame, uint32_t dst,
-                                                uint32_t bar, uint32_t bytes)
+/* box origin of a cell's window in its level's padded plane, packed x | y << 16 | level << 28 (x, y < 4096 + pad) */
+__device__ __forceinline__ uint32_t fast_tma_origin(const BorbCell &cell)
 {
     const int x = BORB_XPAD + ((cell.x0 - 1) & ~15), y = BORB_EDGE + cell.y0; /* BORB_XPAD is a multiple of 16 */
+    return (uint32_t)x | ((uint32_t)y << 16);
+}
+__device__ __forceinline__ void fast_tma_window(const CUtensorMap *maps, uint32_t origin, int level, int frame, uint32_t dst,
+                                                uint32_t bar, uint32_t bytes)
+{
+    const int x = (int)(origin & 0xffffu), y = (int)(origin >> 16);
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                 ::"r"(dst), "l"(maps + cell.level), "r"(x), "r"(y), "r"(frame), "r"(bar)
+                 ::"r"(dst), "l"(maps + level), "r"(x), "r"(y), "r"(frame), "r"(bar)
                  : "memory");
 }
 
@@ -237,11 +243,16 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
 
     for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(sc)[i] = 0u;
 
-    /* persistent walk over (frame, cell): cells strided by gridDim.x, frames by gridDim.y; the
-     * window of the NEXT item is copied into the other buffer while this one is processed */
+    /* persistent walk over (cell, frame) items, FRAME-MAJOR per CTA: a CTA keeps its cell and walks the frames
+     * blockIdx.y, blockIdx.y + gridDim.y, ... before it moves to cell ci + gridDim.x (the host sizes gridDim.x =
+     * n_cells whenever it can, so in the batched shape a CTA never changes cell).  Everything that depends only on
+     * the cell -- the stage-1 lane geometry, the level's candidate slab -- is computed when the cell changes, not
+     * per item (it was 12.5 % of the kernel's instructions when the walk was cell-major).  The window of the NEXT
+     * item is copied into the other buffer while this one is processed. */
     int frame = blockIdx.y, ci = blockIdx.x, buf = 0;
     bool have = frame < n_frames && ci < n_cells;
-    BorbCell cell;
+    uint32_t origin = 0; /* of the current cell's window (fast_tma_origin) */
+    int level = 0;
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0) : "memory");
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8) : "memory");
@@ -249,45 +260,65 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
     }
     __syncthreads();
     if (have) {
-        cell = cells[ci];
-        if (tid == 0) fast_tma_window(maps, cell, frame0 + frame, win0, bar0, box_bytes);
+        const BorbCell c0 = cells[ci];
+        origin = fast_tma_origin(c0);
+        level = c0.level;
+        if (tid == 0) fast_tma_window(maps, origin, level, frame0 + frame, win0, bar0, box_bytes);
     }
+    /* per-cell state (see the geometry block below) */
+    int dw = 0, dh = 0, s1_R = 1, s1_rig = 0, s1_col = 0, org_off = 0, s1_qoff = 0, cand_cap = 0, sxy3 = 0;
+    bool s1_on = false;
+    uint32_t s1_vlo = 0, s1_vhi = 0;
+    long long cand_off = 0;
+    bool new_cell = true;
     uint32_t it = 0;
     while (have) {
-        int nci = ci + gridDim.x, nframe = frame;
-        if (nci >= n_cells) { nci = blockIdx.x; nframe += gridDim.y; }
-        const bool nhave = nframe < n_frames;
+        int nci = ci, nframe = frame + gridDim.y;
+        if (nframe >= n_frames) { nci = ci + gridDim.x; nframe = blockIdx.y; }
+        const bool nhave = nci < n_cells;
         uint8_t *win = fast_raw + lay.win_off + buf * lay.win_bytes;
         fast_mbar_wait(bar0 + 8 * buf, (it >> 1) & 1u); /* this item's window has landed */
         __syncthreads(); /* and everybody is done with the other buffer and the lists of the previous item */
-        BorbCell ncell;
+        uint32_t norigin = origin;
+        int nlevel = level;
         if (nhave) {
-            ncell = cells[nci];
+            if (nci != ci) { /* never in the batched shape (gridDim.x == n_cells) */
+                const BorbCell nc = cells[nci];
+                norigin = fast_tma_origin(nc);
+                nlevel = nc.level;
+            }
             if (tid == 0)
-                fast_tma_window(maps, ncell, frame0 + nframe, win0 + (buf ^ 1) * lay.win_bytes, bar0 + 8 * (buf ^ 1), box_bytes);
+                fast_tma_window(maps, norigin, nlevel, frame0 + nframe, win0 + (buf ^ 1) * lay.win_bytes, bar0 + 8 * (buf ^ 1), box_bytes);
         }
         ++it;
-        const BorbLevel &L = plan->lv[cell.level];
-        const int dw = cell.ww - 6, dh = cell.wh - 6; /* detection domain */
-
-        /* stage-1 lane geometry: Q words cover a domain row (bytes b0 .. b0+dw-1 of the staged row),
-         * R rows per warp step; this lane: row s1_rig of the step, word s1_ql of the row */
-        const int s1_b0 = FAST_DOMAIN_BYTE(cell.x0), s1_w0 = s1_b0 >> 2;
-        const uint8_t *org = win + 3 * WP + s1_b0; /* domain pixel (0,0): staged row 3 */
-        const int s1_Q = ((s1_b0 + dw - 1) >> 2) - s1_w0 + 1;
-        const int s1_R = (int)(cell.dmagic >> 8);
-        int s1_rig = 0;
+        if (new_cell) {
+            const BorbCell cell = cells[ci];
+            const BorbLevel &L = plan->lv[cell.level];
+            dw = cell.ww - 6; dh = cell.wh - 6; /* detection domain */
+            /* stage-1 lane geometry: Q words cover a domain row (bytes b0 .. b0+dw-1 of the staged row),
+             * R rows per warp step; this lane: row s1_rig of the step, word s1_ql of the row */
+            const int s1_b0 = FAST_DOMAIN_BYTE(cell.x0), s1_w0 = s1_b0 >> 2;
+            org_off = 3 * WP + s1_b0; /* domain pixel (0,0): staged row 3 */
+            const int s1_Q = ((s1_b0 + dw - 1) >> 2) - s1_w0 + 1;
+            s1_R = (int)(cell.dmagic >> 8);
+            s1_rig = 0;
 #pragma unroll
-        for (int k = 1; k < 8; ++k) s1_rig += lane >= k * s1_Q;
-        const bool s1_on = s1_rig < s1_R;
-        const int s1_ql = lane - s1_rig * s1_Q;
-        const int s1_col = 4 * (s1_w0 + s1_ql) - s1_b0; /* domain x of this lane's first pixel (may be < 0) */
-        const uint32_t s1_vlo = ((unsigned)s1_col < (unsigned)dw ? 0x00000600u : 0u) |
-                                ((unsigned)(s1_col + 1) < (unsigned)dw ? 0x06000000u : 0u);
-        const uint32_t s1_vhi = ((unsigned)(s1_col + 2) < (unsigned)dw ? 0x00000600u : 0u) |
-                                ((unsigned)(s1_col + 3) < (unsigned)dw ? 0x06000000u : 0u);
-        const uint32_t *s1_qp = reinterpret_cast<const uint32_t *>(win + 3 * WP) + s1_w0 + s1_ql +
-                                s1_rig * (WP / 4);
+            for (int k = 1; k < 8; ++k) s1_rig += lane >= k * s1_Q;
+            s1_on = s1_rig < s1_R;
+            const int s1_ql = lane - s1_rig * s1_Q;
+            s1_col = 4 * (s1_w0 + s1_ql) - s1_b0; /* domain x of this lane's first pixel (may be < 0) */
+            s1_vlo = ((unsigned)s1_col < (unsigned)dw ? 0x00000600u : 0u) |
+                     ((unsigned)(s1_col + 1) < (unsigned)dw ? 0x06000000u : 0u);
+            s1_vhi = ((unsigned)(s1_col + 2) < (unsigned)dw ? 0x00000600u : 0u) |
+                     ((unsigned)(s1_col + 3) < (unsigned)dw ? 0x06000000u : 0u);
+            s1_qoff = 3 * (WP / 4) + s1_w0 + s1_ql + s1_rig * (WP / 4); /* this lane's word of staged row 3 + rig */
+            cand_off = L.cand_off; cand_cap = L.cand_cap;
+            /* window-relative (x+3, y+3) shifted by the cell origin: coords relative to (minBorderX, minBorderY),
+             * src/ORBextractor.cc:1087-1088 */
+            sxy3 = (3 + cell.sx) | ((3 + cell.sy) << 16);
+        }
+        const uint8_t *org = win + org_off;
+        const uint32_t *s1_qp = reinterpret_cast<const uint32_t *>(win) + s1_qoff;
         int n2 = 0, n3 = 0, cell_total = 0;
         /* The reference's two cv::FAST calls (:1069-1075) as two passes, the second only for cells
          * where the first found nothing; K(ini) needs nothing below ini: a corner's score is at
@@ -427,18 +458,15 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
         /* ---- emit this warp's survivors; one global atomicAdd per warp ---- */
         if (cell_total > 0 && n3 > 0) {
             int base = 0;
-            if (lane == 0) base = atomicAdd(ncand + frame * BORB_MAXL + cell.level, n3);
+            if (lane == 0) base = atomicAdd(ncand + frame * BORB_MAXL + level, n3);
             base = __shfl_sync(0xffffffffu, base, 0);
-            uint32_t *oxy = cand_xy + (size_t)frame * (size_t)plan->cand_total + L.cand_off;
-            uint32_t *osc = cand_score + (size_t)frame * (size_t)plan->cand_total + L.cand_off;
+            uint32_t *oxy = cand_xy + (size_t)frame * (size_t)plan->cand_total + cand_off;
+            uint32_t *osc = cand_score + (size_t)frame * (size_t)plan->cand_total + cand_off;
             for (int i = lane; i < n3; i += 32) {
                 const uint32_t rec = list3[i];
                 const int slot = base + i;
-                if (slot < L.cand_cap) {
-                    const int x = rec & 63, y = (rec >> 6) & 63;
-                    /* window-relative (x+3, y+3) shifted by the cell origin: coords relative
-                     * to (minBorderX, minBorderY), src/ORBextractor.cc:1087-1088 */
-                    oxy[slot] = (uint32_t)(x + 3 + cell.sx) | ((uint32_t)(y + 3 + cell.sy) << 16);
+                if (slot < cand_cap) {
+                    oxy[slot] = (uint32_t)sxy3 + ((rec & 63u) | ((rec << 10) & 0x3f0000u)); /* x | y << 16 */
                     osc[slot] = rec >> 12;
                 }
             }
@@ -450,7 +478,8 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
         }
         /* the next cell's first write to the score plane / wcnt comes after its top barrier */
         have = nhave;
-        if (nhave) { cell = ncell; ci = nci; frame = nframe; buf ^= 1; }
+        new_cell = nci != ci;
+        if (nhave) { origin = norigin; level = nlevel; ci = nci; frame = nframe; buf ^= 1; }
     }
 }
 
