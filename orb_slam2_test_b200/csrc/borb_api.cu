@@ -188,7 +188,7 @@ struct borb_extractor {
     uint32_t *d_mt_cache = nullptr; /* [mt_cap][MT_K] candidate keys */
     uint8_t *d_mt_more = nullptr, *d_mt_occ = nullptr, *h_mt_occ = nullptr; /* occupancy of the local-map matcher */
     int mt_rescans = 0;
-    /* monocular-initialisation matcher (M3): chooser lists [2][K][MT_CH] + counts [2][K], result [mt_cap] + F2's mvKeysUn */
+    /* monocular-initialisation matcher (M3): chooser lists: nodes [2][mt_cap] + heads [2][K], result [mt_cap] + F2's mvKeysUn */
     uint32_t *d_mt_ent = nullptr;
     int *d_mt_cnt = nullptr, *d_mt_m12 = nullptr, *h_mt_m12 = nullptr;
     float *h_mt_unxy = nullptr;
@@ -1538,6 +1538,8 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         if (cur->d_mt_cache) cudaFree(cur->d_mt_cache);
         if (cur->d_mt_more) cudaFree(cur->d_mt_more);
         if (cur->d_mt_m12) cudaFree(cur->d_mt_m12);
+        if (cur->d_mt_ent) cudaFree(cur->d_mt_ent);
+        cur->d_mt_ent = nullptr;
         if (cur->h_mt_m12) cudaFreeHost(cur->h_mt_m12);
         cur->d_mt_m12 = cur->h_mt_m12 = nullptr;
         cur->d_mt_last = cur->h_mt_last = nullptr; cur->d_mt_choice = nullptr; cur->mt_cap = 0;
@@ -1546,6 +1548,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         CU(cudaMallocHost(&cur->h_mt_last, cap * 57));
         CU(cudaMalloc(&cur->d_mt_choice, cap * 8));
         CU(cudaMalloc(&cur->d_mt_m12, cap * 4));
+        CU(cudaMalloc(&cur->d_mt_ent, 2 * cap * 4));
         CU(cudaMallocHost(&cur->h_mt_m12, cap * 4));
         CU(cudaMalloc(&cur->d_mt_cache, cap * MT_K * 4));
         CU(cudaMalloc(&cur->d_mt_more, cap));
@@ -1619,8 +1622,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     if (mode == 1) MATCH_LAUNCH(1);
     else if (mode == 2) MATCH_LAUNCH(2);
     else {
-        if (!cur->d_mt_ent) {
-            CU(cudaMalloc(&cur->d_mt_ent, 2 * K * MT_CH * 4));
+        if (!cur->d_mt_cnt) {
             CU(cudaMalloc(&cur->d_mt_cnt, 2 * K * 4));
             CU(cudaMallocHost(&cur->h_mt_unxy, K * 8));
         }
@@ -1630,7 +1632,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
                 nullptr, nullptr, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);
         k_match_resolve_init<<<1, MT_NT, 0, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci,
                                                   cur->d_bounds + (size_t)frame * 4, l_geo, l_angle, l_oct, l_desc, l_flags,
-                                                  cur->d_mt_cache, cur->d_mt_more, cur->d_mt_choice, cur->d_mt_ent, cur->d_mt_cnt,
+                                                  cur->d_mt_cache, cur->d_mt_more, cur->d_mt_choice, cur->d_mt_ent, (int)c, cur->d_mt_cnt,
                                                   (int)K, cur->d_mt_match, cur->d_mt_m12, cur->d_mt_match + K);
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(cur->h_mt_m12, cur->d_mt_m12, std::max<size_t>(un, 1) * 4, cudaMemcpyDeviceToHost, st));
@@ -1639,7 +1641,6 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         CU(cudaStreamSynchronize(st));
         cur->mt_rounds = cur->h_mt_match[K + 1];
         cur->mt_rescans = cur->h_mt_match[K + 2];
-        if (cur->h_mt_match[K + 3]) return fail(BORB_ERR_STATE, "initialisation matcher: more than %d queries chose one keypoint in a round", MT_CH);
         if (n) std::memcpy(match, cur->h_mt_m12, un * 4);
         if (nmatches) *nmatches = cur->h_mt_match[K];
         if (n_cur) *n_cur = n;

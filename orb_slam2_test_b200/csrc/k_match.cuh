@@ -401,18 +401,19 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
  * chooser lists) reach the unique sequential solution.  At the end keypoint c belongs to its LAST
  * accepted chooser, the orientation histogram counts every accepted query (also the ones taken over
  * later, :562-577), and entries of discarded bins are cleared only where they still hold (:606-613).
- * ent [2][kp_total][MT_CH] chooser records (query << 8 | distance), cnt [2][kp_total]; overflow of a list
- * is reported through nm[3] (the host turns it into an error, nothing is returned silently wrong).
+ * The choosers of a keypoint are a linked list threaded through the queries themselves: head [2][kp_total] = the
+ * query pushed last (-1 = none), node [2][n] = (next query + 1) << 8 | accepted distance.  A query holds at most
+ * one keypoint per round, so a list can have any length (on repetitive texture with a 100-px window dozens of
+ * level-0 keypoints may pick the same one; the reference never fails there) and nothing can overflow.
  */
-#define MT_CH 32
 #define MT_TH_LOW 50
 
-__device__ __forceinline__ bool mt_init_closed(const uint32_t *__restrict__ ent, const int *__restrict__ cnt, int c, int i, int d)
+__device__ __forceinline__ bool mt_init_closed(const uint32_t *__restrict__ node, const int *__restrict__ head, int c, int i, int d)
 {
-    const int n = min(cnt[c], MT_CH);
-    for (int k = 0; k < n; ++k) {
-        const uint32_t e = ent[(size_t)c * MT_CH + k];
-        if ((int)(e >> 8) < i && (int)(e & 0xffu) <= d) return true;
+    for (int k = head[c]; k >= 0;) {
+        const uint32_t e = node[k];
+        if (k < i && (int)(e & 0xffu) <= d) return true;
+        k = (int)(e >> 8) - 1;
     }
     return false;
 }
@@ -425,27 +426,27 @@ k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__
                      const float *__restrict__ l_angle, const int *__restrict__ l_octave,
                      const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
                      const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more,
-                     int *__restrict__ choice /* [n][2]: keypoint, distance */, uint32_t *__restrict__ ent,
-                     int *__restrict__ cnt, int kp_total, int *__restrict__ owner /* [kp_total] */,
+                     int *__restrict__ choice /* [n][2]: keypoint, distance */, uint32_t *__restrict__ node /* [2][node_cap] */,
+                     int node_cap, int *__restrict__ head /* [2][kp_total] */, int kp_total, int *__restrict__ owner /* [kp_total] */,
                      int *__restrict__ m12 /* [n] */, int *__restrict__ nm)
 {
-    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans, s_overflow;
+    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans;
     const int tid = threadIdx.x, n1 = mp.n_last;
     const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
     const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
-    if (tid == 0) { s_nm = 0; s_rescans = 0; s_overflow = 0; }
+    if (tid == 0) { s_nm = 0; s_rescans = 0; }
     if (tid < MT_HISTO) { s_hist[tid] = 0; s_keep[tid] = 1; }
     for (int i = tid; i < n1; i += MT_NT) { choice[2 * i] = -1; choice[2 * i + 1] = 0; }
-    for (int c = tid; c < kp_total; c += MT_NT) { cnt[c] = 0; owner[c] = -1; }
+    for (int c = tid; c < kp_total; c += MT_NT) { head[c] = -1; owner[c] = -1; }
     __syncthreads();
 
     int round = 0;
     for (;; ++round) {
-        const uint32_t *ent_prev = ent + (size_t)(round & 1) * kp_total * MT_CH;
-        uint32_t *ent_new = ent + (size_t)((round + 1) & 1) * kp_total * MT_CH;
-        const int *cnt_prev = cnt + (round & 1) * kp_total;
-        int *cnt_new = cnt + ((round + 1) & 1) * kp_total;
-        for (int c = tid; c < kp_total; c += MT_NT) cnt_new[c] = 0;
+        const uint32_t *node_prev = node + (size_t)(round & 1) * node_cap;
+        uint32_t *node_new = node + (size_t)((round + 1) & 1) * node_cap;
+        const int *head_prev = head + (round & 1) * kp_total;
+        int *head_new = head + ((round + 1) & 1) * kp_total;
+        for (int c = tid; c < kp_total; c += MT_NT) head_new[c] = -1;
         if (tid == 0) s_changed = 0;
         __syncthreads();
         for (int i = tid; i < n1; i += MT_NT) {
@@ -458,7 +459,7 @@ k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__
                 if (key == MT_NOKEY) { decided = true; continue; }
                 const int c = (int)(key & 0xffffu), d = (int)(key >> 16);
                 if (found == 0 && d > MT_TH_LOW) { decided = true; continue; } /* the best open one can only be worse */
-                if (mt_init_closed(ent_prev, cnt_prev, c, i, d)) continue;
+                if (mt_init_closed(node_prev, head_prev, c, i, d)) continue;
                 if (found == 0) { bd = d; bidx = c; found = 1; }
                 else { bd2 = d; found = 2; decided = true; }
             }
@@ -473,7 +474,7 @@ k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__
                         for (int q = q0; q < q1; ++q) {
                             const int i2 = cell_idx[q];
                             const int d = mt_candidate(Q, i2, kp, un_xy, nullptr, nullptr, desc, d0, d1);
-                            if (d < 0 || mt_init_closed(ent_prev, cnt_prev, i2, i, d)) continue;
+                            if (d < 0 || mt_init_closed(node_prev, head_prev, i2, i, d)) continue;
                             if (d < bd) { bd2 = bd; bd = d; bidx = i2; }
                             else if (d < bd2) bd2 = d;
                         }
@@ -482,11 +483,7 @@ k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__
             int ch = -1, chd = 0;
             if (bidx >= 0 && bd <= MT_TH_LOW && (float)bd < (float)bd2 * mp.nnratio) { ch = bidx; chd = bd; }
             if (ch != choice[2 * i] || chd != choice[2 * i + 1]) { choice[2 * i] = ch; choice[2 * i + 1] = chd; s_changed = 1; }
-            if (ch >= 0) {
-                const int slot = atomicAdd(&cnt_new[ch], 1);
-                if (slot < MT_CH) ent_new[(size_t)ch * MT_CH + slot] = ((uint32_t)i << 8) | (uint32_t)chd;
-                else s_overflow = 1;
-            }
+            if (ch >= 0) node_new[i] = ((uint32_t)(atomicExch(&head_new[ch], i) + 1) << 8) | (uint32_t)chd; /* push */
         }
         __syncthreads();
         const int changed = s_changed;
@@ -528,7 +525,7 @@ k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__
         m12[i] = out;
     }
     __syncthreads();
-    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; nm[3] = s_overflow; }
+    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; nm[3] = 0; }
 }
 
 #endif

@@ -175,8 +175,9 @@ def test_initialisation_matcher(kw, oracle_built):
     assert _check_init("init", oracle_built, **kw) > 800
 
 
-@pytest.mark.parametrize("copies", [2, 4])
+@pytest.mark.parametrize("copies", [2, 4, 48])
 def test_initialisation_matcher_take_overs(copies, oracle_built):
     """several initial keypoints want the same current keypoint at different distances: a later, strictly better
-    one takes it over (:552-558), an equal or worse one is skipped (:526-527)"""
+    one takes it over (:552-558), an equal or worse one is skipped (:526-527).  With 48 copies a keypoint has up to
+    48 choosers in a round (repetitive texture): the chooser lists have no length limit."""
     _check_init(f"init x{copies}", oracle_built, windows=(100, 40), seed=9, copies=copies)

@@ -77,9 +77,9 @@ def test_local_map_matcher(kw, oracle_built, ref):
 # ---- the monocular-initialisation matcher: ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:487-632 ----
 
 @pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, step=3), dict(seed=4, nf=4000, step=2), dict(seed=9, copies=2),
-                                dict(seed=9, copies=4),
+                                dict(seed=9, copies=4), dict(seed=9, copies=48),
                                 dict(seed=3, shape=synth.KITTI_SHAPE, K=matchcase.KITTI_K, dist=(0.0, 0.0, 0.0, 0.0))],
-                         ids=["tum", "tum-3-later", "tum-4000", "takeovers-x2", "takeovers-x4", "kitti"])
+                         ids=["tum", "tum-3-later", "tum-4000", "takeovers-x2", "takeovers-x4", "takeovers-x48", "kitti"])
 def test_initialisation_matcher(kw, oracle_built, ref):
     """windows 100 (the reference's), 30 and 300; ratio 0.9 / 0.7; with and without the orientation check; then the
     call chained on a later frame with the vbPrevMatched the first call updated (src/Tracking.cc:616)"""
