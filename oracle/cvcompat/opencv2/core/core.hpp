@@ -28,6 +28,9 @@
 #include <cstring>
 #include <iterator>
 #include <memory>
+#include <sstream> /* the real core.hpp pulls these in; DBoW2 relies on it */
+#include <iostream>
+#include <string>
 #include <vector>
 
 #if defined(__SSE2__)
@@ -382,6 +385,28 @@ void undistortPoints(InputArray src, OutputArray dst, InputArray K, InputArray d
 struct KeyPointsFilter {
     static void retainBest(std::vector<KeyPoint> &keypoints, int npoints);
 };
+
+/* cv::FileStorage / cv::FileNode: named by the YAML save()/load() members of DBoW2's TemplatedVocabulary
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1452-1632), which are virtual and therefore instantiated with the
+ * class.  Nothing here reads or writes YAML (the vocabulary comes from loadFromTextFile :1338): every member aborts. */
+class FileNode {
+public:
+    FileNode operator[](const std::string &) const { std::abort(); }
+    FileNode operator[](const char *) const { std::abort(); }
+    FileNode operator[](int) const { std::abort(); }
+    size_t size() const { std::abort(); }
+    operator int() const { std::abort(); }
+    operator double() const { std::abort(); }
+    operator std::string() const { std::abort(); }
+};
+class FileStorage {
+public:
+    enum { READ = 0, WRITE = 1 };
+    FileStorage(const char *, int) {}
+    bool isOpened() const { return false; }
+    FileNode operator[](const std::string &) const { std::abort(); }
+};
+template <typename T> inline FileStorage &operator<<(FileStorage &, const T &) { std::abort(); }
 
 } // namespace cv
 

@@ -1,6 +1,8 @@
 /* oracle/matchcompat -- TEST INFRASTRUCTURE.  Shadow of include/KeyFrame.h: the members
- * src/ORBmatcher.cc names in its keyframe matchers (SearchByBoW, Fuse, SearchBySim3, ...), none of
- * which the driver calls -- every method aborts.  Only there so that the translation unit compiles. */
+ * src/ORBmatcher.cc names in its keyframe matchers.  A keyframe here is a plain record of what
+ * SearchByBoW(KeyFrame*, Frame&, ...) (:195-351) and the relocalisation SearchByProjection(Frame&, KeyFrame*, ...)
+ * (:1670-1798) read -- map-point matches, feature vector, descriptors, undistorted keypoints -- which
+ * the drivers (oracle/bow_driver.cpp) fill; the methods of the matchers nobody runs here abort. */
 #ifndef KEYFRAME_H
 #define KEYFRAME_H
 #include <cstdlib>
@@ -13,7 +15,8 @@ namespace ORB_SLAM2 {
 class MapPoint;
 class KeyFrame {
 public:
-    std::vector<MapPoint *> GetMapPointMatches() { std::abort(); }
+    std::vector<MapPoint *> mvpMapPoints;
+    std::vector<MapPoint *> GetMapPointMatches() { return mvpMapPoints; }
     std::set<MapPoint *> GetMapPoints() { std::abort(); }
     MapPoint *GetMapPoint(const size_t &) { std::abort(); }
     cv::Mat GetRotation() { std::abort(); }

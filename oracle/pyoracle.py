@@ -543,3 +543,147 @@ class RefFrame:
         return {"kps_l": kl[:nl].copy(), "desc_l": dl[:nl].copy(), "kps_r": kr[:nr].copy(), "desc_r": dr[:nr].copy(),
                 "un_xy": un[:nl].copy(), "u_right": u[:nl].copy(), "depth": z[:nl].copy(), "cell_start": start,
                 "cell_idx": gi[:start[-1]].copy(), "bounds": np.array(list(out.bounds), np.float32)}
+
+
+# ---- bag of words: TemplatedVocabulary::transform / Frame::ComputeBoW / ORBmatcher::SearchByBoW(KeyFrame*, Frame&) ----
+
+def _bow_out(n: int):
+    return (np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64), np.zeros(max(n, 1), np.uint32),
+            np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.uint32), C.c_int(0), C.c_int(0))
+
+
+def _bow_pack(out):
+    wid, wv, nid, ns, fi, nw, nn = out
+    return {"word_id": wid[:nw.value].copy(), "word_val": wv[:nw.value].copy(), "node_id": nid[:nn.value].copy(),
+            "node_start": ns[:nn.value + 1].copy(), "feat_idx": fi[:ns[nn.value]].copy()}
+
+
+class BowVocabulary:
+    """Our restatement (oracle/bow_oracle.cpp in liborb_oracle.so) of DBoW2's vocabulary: loadFromTextFile,
+    transform, L1 score, and ORBmatcher::SearchByBoW(KeyFrame*, Frame&) on its feature vectors."""
+
+    def __init__(self, path: str):
+        lib = Oracle.load()
+        lib.bo_load_text.restype = _vp
+        lib.bo_load_text.argtypes = [C.c_char_p]
+        lib.bo_free.argtypes = [_vp]
+        lib.bo_info.argtypes = [_vp] + [_vp] * 6
+        lib.bo_arrays.argtypes = [_vp] * 5
+        lib.bo_descend.argtypes = [_vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp]
+        lib.bo_transform.argtypes = [_vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+        lib.bo_score_l1.restype = C.c_double
+        lib.bo_score_l1.argtypes = [_vp, _vp, C.c_int, _vp, _vp, C.c_int]
+        lib.bo_search_by_bow.restype = C.c_int
+        lib.bo_search_by_bow.argtypes = ([C.c_int] + [_vp] * 6 + [C.c_int] + [C.c_int] + [_vp] * 5 + [C.c_int] +
+                                         [C.c_float, C.c_int, _vp])
+        self.lib = lib
+        self.h = lib.bo_load_text(str(path).encode())
+        if not self.h:
+            raise ValueError(f"not a vocabulary text file: {path}")
+        v = [C.c_int() for _ in range(6)]
+        lib.bo_info(self.h, *[C.byref(x) for x in v])
+        self.k, self.L, self.n_nodes, self.n_words, self.scoring, self.weighting = [x.value for x in v]
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.bo_free(self.h)
+            self.h = None
+
+    def arrays(self):
+        """-> parent [N-1] i32, leaf [N-1] u8, desc [N-1, 32] u8, weight [N-1] f64 for nodes 1..N-1"""
+        n = self.n_nodes - 1
+        parent, leaf = np.zeros(n, np.int32), np.zeros(n, np.uint8)
+        desc, weight = np.zeros((n, 32), np.uint8), np.zeros(n, np.float64)
+        self.lib.bo_arrays(self.h, _ptr(parent), _ptr(leaf), _ptr(desc), _ptr(weight))
+        return parent, leaf, desc, weight
+
+    def descend(self, desc: np.ndarray, levelsup: int = 4):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d)
+        word, node, w = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float64)
+        self.lib.bo_descend(self.h, _ptr(d), n, levelsup, _ptr(word), _ptr(node), _ptr(w))
+        return word, node, w
+
+    def transform(self, desc: np.ndarray, levelsup: int = 4) -> dict:
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        out = _bow_out(len(d))
+        self.lib.bo_transform(self.h, _ptr(d), len(d), levelsup, _ptr(out[0]), _ptr(out[1]), C.byref(out[5]),
+                              _ptr(out[2]), _ptr(out[3]), _ptr(out[4]), C.byref(out[6]))
+        return _bow_pack(out)
+
+    def score(self, a: dict, b: dict) -> float:
+        return float(self.lib.bo_score_l1(_ptr(a["word_id"]), _ptr(a["word_val"]), len(a["word_id"]),
+                                          _ptr(b["word_id"]), _ptr(b["word_val"]), len(b["word_id"])))
+
+    def search_by_bow(self, kf_kps, kf_desc, kf_mp, f_kps, f_desc, nnratio=0.7, check_ori=True, kf_fv=None, f_fv=None):
+        """-> (match [n_f] i32: keyframe keypoint index or -1, nmatches)"""
+        kd = np.ascontiguousarray(kf_desc, np.uint8).reshape(-1, 32)
+        fd = np.ascontiguousarray(f_desc, np.uint8).reshape(-1, 32)
+        kfv = kf_fv or self.transform(kd, 4)
+        ffv = f_fv or self.transform(fd, 4)
+        ka = np.ascontiguousarray(kf_kps["angle"], np.float32)
+        fa = np.ascontiguousarray(f_kps["angle"], np.float32)
+        mp = np.ascontiguousarray(kf_mp, np.uint8)
+        out = np.full(max(len(fd), 1), -1, np.int32)
+        nm = self.lib.bo_search_by_bow(len(kd), _ptr(ka), _ptr(kd), _ptr(mp), _ptr(kfv["node_id"]), _ptr(kfv["node_start"]),
+                                       _ptr(kfv["feat_idx"]), len(kfv["node_id"]), len(fd), _ptr(fa), _ptr(fd),
+                                       _ptr(ffv["node_id"]), _ptr(ffv["node_start"]), _ptr(ffv["feat_idx"]),
+                                       len(ffv["node_id"]), nnratio, int(check_ori), _ptr(out))
+        return out[:len(fd)], int(nm)
+
+
+class RefBow:
+    """The reference's own DBoW2 + Frame::ComputeBoW + ORBmatcher::SearchByBoW (oracle/_ref/librefbow.so)."""
+
+    _lib = None
+
+    @classmethod
+    def available(cls) -> bool:
+        return (HERE / "_ref" / "librefbow.so").exists()
+
+    def __init__(self, path: str):
+        if RefBow._lib is None:
+            lib = C.CDLL(str(HERE / "_ref" / "librefbow.so"))
+            lib.refbow_load.restype = _vp
+            lib.refbow_load.argtypes = [C.c_char_p]
+            lib.refbow_free.argtypes = [_vp]
+            lib.refbow_info.argtypes = [_vp] * 6
+            lib.refbow_compute_bow.argtypes = [_vp, _vp, C.c_int, C.c_int] + [_vp] * 7
+            lib.refbow_score.restype = C.c_double
+            lib.refbow_score.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, C.c_int]
+            lib.refbow_search_by_bow.restype = C.c_int
+            lib.refbow_search_by_bow.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, _vp, C.c_float, C.c_int, _vp]
+            RefBow._lib = lib
+        self.lib = RefBow._lib
+        self.h = self.lib.refbow_load(str(path).encode())
+        if not self.h:
+            raise ValueError(f"the reference refused {path}")
+        v = [C.c_int() for _ in range(5)]
+        self.lib.refbow_info(self.h, *[C.byref(x) for x in v])
+        self.k, self.L, self.n_words, self.scoring, self.weighting = [x.value for x in v]
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.refbow_free(self.h)
+            self.h = None
+
+    def transform(self, desc: np.ndarray, levelsup: int = 4) -> dict:
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        out = _bow_out(len(d))
+        self.lib.refbow_compute_bow(self.h, _ptr(d), len(d), levelsup, _ptr(out[0]), _ptr(out[1]), C.byref(out[5]),
+                                    _ptr(out[2]), _ptr(out[3]), _ptr(out[4]), C.byref(out[6]))
+        return _bow_pack(out)
+
+    def score(self, a: dict, b: dict) -> float:
+        return float(self.lib.refbow_score(self.h, _ptr(a["word_id"]), _ptr(a["word_val"]), len(a["word_id"]),
+                                           _ptr(b["word_id"]), _ptr(b["word_val"]), len(b["word_id"])))
+
+    def search_by_bow(self, kf_kps, kf_desc, kf_mp, f_kps, f_desc, nnratio=0.7, check_ori=True):
+        kd = np.ascontiguousarray(kf_desc, np.uint8).reshape(-1, 32)
+        fd = np.ascontiguousarray(f_desc, np.uint8).reshape(-1, 32)
+        kk, fk = np.ascontiguousarray(kf_kps), np.ascontiguousarray(f_kps)
+        mp = np.ascontiguousarray(kf_mp, np.uint8)
+        out = np.full(max(len(fd), 1), -1, np.int32)
+        nm = self.lib.refbow_search_by_bow(self.h, len(kd), _ptr(kk), _ptr(kd), _ptr(mp), len(fd), _ptr(fk), _ptr(fd),
+                                           nnratio, int(check_ori), _ptr(out))
+        return out[:len(fd)], int(nm)
