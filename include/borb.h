@@ -335,6 +335,59 @@ int borb_undistort_grid_noalloc(const borb_keypoint *dev_kps, const int32_t *dev
                                 int cols, int rows, const float *K, const float *dist, int n_dist, float *dev_xy_un,
                                 int32_t *dev_cell_start, int32_t *dev_cell_idx, float *dev_bounds, void *stream);
 
+/* -- bag of words: Frame::ComputeBoW (src/Frame.cc:532-539) and the matcher that consumes it ------------------
+ *
+ * The vocabulary is DBoW2's TemplatedVocabulary<FORB::TDescriptor, FORB> (include/ORBVocabulary.h): a k-ary tree
+ * of 256-bit descriptors, words at the leaves.  borb_voc_load_text reads the text format of
+ * TemplatedVocabulary::loadFromTextFile (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1421) that
+ * System::System loads (src/System.cc); borb_voc_create takes the same tree as arrays.  The tree is uploaded once and
+ * used read-only: any number of extractor handles on that device may share it. */
+typedef struct borb_vocabulary borb_vocabulary;
+int borb_voc_load_text(const char *path, int device, borb_vocabulary **out);
+/* nodes 1 .. n_nodes in file order (node 0 = root): parent id (< own id), leaf flag (> 0: a word; word ids count the
+ * flagged nodes in order), 32-byte descriptor, weight.  scoring / weighting: DBoW2's ScoringType / WeightingType
+ * (BowVector.h:36-53; ORBvoc.txt: L1_NORM = 0, TF_IDF = 0). */
+int borb_voc_create(int k, int L, int scoring, int weighting, int n_nodes, const int32_t *parent, const uint8_t *is_leaf,
+                    const uint8_t *desc, const double *weight, int device, borb_vocabulary **out);
+void borb_voc_destroy(borb_vocabulary *v);
+int borb_voc_info(const borb_vocabulary *v, int *k, int *L, int *n_nodes /* with the root */, int *n_words,
+                  int *scoring, int *weighting);
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1127-1206) on frame `frame` of
+ * h's last extract call, from the descriptors that call left on the device; the reference calls it with
+ * levelsup = 4 (Frame::ComputeBoW, src/Frame.cc:536).  Results stay on the device for borb_search_by_bow and come
+ * back in one copy.  Up to 16384 keypoint slots per frame (BORB_ERR_CAPACITY beyond). */
+int borb_compute_bow(borb_extractor *h, int frame, const borb_vocabulary *voc, int levelsup);
+/* mBowVec as (word id ascending, value) pairs -- std::map order -- and mFeatVec in CSR form: node ids ascending, the
+ * features of node u are feat_idx[node_start[u] .. node_start[u + 1]), ascending (= push_back order).  Values are
+ * the reference's doubles bit for bit (weights added in feature order, norm summed in word order).  Pointers into
+ * page-locked memory owned by the handle, valid until its next borb_compute_bow. */
+int borb_bow_result(borb_extractor *h, int frame, const uint32_t **word_id, const double **word_val, int *n_words,
+                    const uint32_t **node_id, const int32_t **node_start, const uint32_t **feat_idx, int *n_nodes);
+/* the same transform for descriptors in host memory (KeyFrame::ComputeBoW on a keyframe no handle holds).
+ * Capacities: word_id / word_val / node_id / feat_idx [n], node_start [n + 1].  One call at a time per vocabulary. */
+int borb_voc_transform(borb_vocabulary *v, const uint8_t *desc, int n, int levelsup, uint32_t *word_id, double *word_val,
+                       int *n_words, uint32_t *node_id, int32_t *node_start, uint32_t *feat_idx, int *n_nodes);
+
+/* ORBmatcher::SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (src/ORBmatcher.cc:195-351;
+ * Tracking::TrackReferenceKeyFrame src/Tracking.cc, Tracking::Relocalization): F = frame `frame` of cur's last call
+ * after borb_compute_bow; the keyframe arrives as flat arrays. */
+typedef struct borb_keyframe {
+    int n;                   /* pKF->N */
+    const uint8_t *desc;     /* pKF->mDescriptors, n x 32 */
+    const float *angle;      /* pKF->mvKeysUn[i].angle */
+    const uint8_t *mp_flags; /* bit 0: GetMapPointMatches()[i] != NULL, bit 1: that map point isBad() */
+    int n_nodes;             /* pKF->mFeatVec, CSR as borb_bow_result returns it */
+    const uint32_t *node_id;
+    const int32_t *node_start;
+    const uint32_t *feat_idx;
+} borb_keyframe;
+/* match [borb_max_keypoints]: per keypoint of F the index of the keyframe keypoint whose map point it receives, or -1
+ * (the caller maps it to vpMapPointsKF[index]); *nmatches = the reference's return value.  nnratio = mfNNratio;
+ * flags: BORB_MATCH_NO_ORIENTATION = !mbCheckOrientation. */
+int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, float nnratio, unsigned flags,
+                       int32_t *match, int *n_cur, int *nmatches);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

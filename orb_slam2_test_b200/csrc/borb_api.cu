@@ -92,6 +92,9 @@ struct GraphEntry {
 
 } // namespace
 
+struct BowState; /* borb_bow.inl */
+static void bow_release(BowState *&b);
+
 struct borb_extractor {
     /* constructor state, reference src/ORBextractor.cc:432-521 */
     int nfeatures, nlevels, ini_th, min_th;
@@ -192,6 +195,7 @@ struct borb_extractor {
     uint32_t *d_mt_ent = nullptr;
     int *d_mt_cnt = nullptr, *d_mt_m12 = nullptr, *h_mt_m12 = nullptr;
     float *h_mt_unxy = nullptr;
+    BowState *bow = nullptr; /* bag of words of one frame + SearchByBoW staging (borb_bow.inl) */
     int mt_rounds = 0;
 
     std::vector<GraphEntry> graphs;
@@ -280,6 +284,7 @@ void free_geometry(borb_extractor *h)
                     h->h_st_u, h->h_st_z, h->h_st_kept, h->h_fr,
                     h->h_mt_last, h->h_mt_match, h->h_mt_occ, h->h_mt_m12, h->h_mt_unxy};
     for (void *p : host) if (p) cudaFreeHost(p);
+    bow_release(h->bow);
     h->d_mt_last = h->h_mt_last = nullptr;
     h->mt_cap = 0;
     h->d_mt_choice = h->d_mt_taker = h->d_mt_match = h->h_mt_match = nullptr;
@@ -1806,3 +1811,4 @@ int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_s
 
 #include "borb_stream.inl"
 #include "borb_noalloc.inl"
+#include "borb_bow.inl"

@@ -1,0 +1,467 @@
+/*
+ * borb_bow.inl -- host side of the bag-of-words entry points (include/borb.h), part of borb_api.cu:
+ *   borb_voc_load_text / borb_voc_create     TemplatedVocabulary::loadFromTextFile
+ *                                            /root/reference/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1421
+ *   borb_compute_bow / borb_voc_transform    Frame::ComputeBoW src/Frame.cc:532-539 -> transform :1127-1206
+ *   borb_search_by_bow                       ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:195-351
+ * Kernels: k_bow.cuh.  The vocabulary is uploaded once, in child-slot order (see k_bow.cuh); a frame's bow vector
+ * and feature vector are built on the device from the descriptors the extract call left there and stay there for
+ * the matcher; one slab comes back to page-locked host memory.
+ */
+#include "k_bow.cuh"
+
+struct borb_vocabulary {
+    int device = 0, k = 0, L = 0, scoring = 0, weighting = 0, n_nodes = 0, n_words = 0, max_children = 0;
+    int n_slots = 0;
+    BowVocDev dev = {};
+    void *d_blob = nullptr; /* all five slot arrays */
+    /* scratch of the stand-alone transform (borb_voc_transform), grown on demand */
+    cudaStream_t stream = nullptr;
+    int cap = 0;
+    uint8_t *d_desc = nullptr, *h_desc = nullptr;
+    int *d_word = nullptr, *d_node = nullptr;
+    double *d_weight = nullptr;
+    uint8_t *d_out = nullptr, *h_out = nullptr; /* result slab, layout bow_slab_layout */
+    int *d_bstart = nullptr;
+};
+
+struct BowSlab { /* byte offsets of one frame's results inside a slab, for a capacity of K features */
+    size_t word, val, node, start, feat, counts, bytes;
+};
+static BowSlab bow_slab_layout(size_t K)
+{
+    BowSlab s;
+    size_t b = 0;
+    s.val = b; b += K * 8;
+    s.word = b; b += K * 4;
+    s.node = b; b += K * 4;
+    s.start = b; b += (K + 1) * 4;
+    s.feat = b; b += K * 4;
+    b = (b + 15) & ~(size_t)15;
+    s.counts = b; b += 16;
+    s.bytes = b;
+    return s;
+}
+
+struct BowState { /* per extractor handle, allocated by the first borb_compute_bow */
+    size_t K = 0;
+    int *d_word = nullptr, *d_node = nullptr, *d_bstart = nullptr;
+    double *d_weight = nullptr;
+    uint8_t *d_out = nullptr, *h_out = nullptr;
+    int frame = -1;
+    unsigned long long gen = 0; /* extract_gen the results belong to */
+    bool on_host = false;
+    /* SearchByBoW: keyframe side staging [desc 32c][angle 4c][node 4c][start 4(c+1)][feat 4c][mp c], results */
+    size_t kf_cap = 0;
+    uint8_t *d_kf = nullptr, *h_kf = nullptr;
+    int *d_match = nullptr, *h_match = nullptr; /* [K + 4]: matches, then nmatches */
+    uint8_t *d_bin = nullptr;
+    int *d_hist = nullptr;
+};
+
+static void bow_release(BowState *&b)
+{
+    if (!b) return;
+    void *dev[] = {b->d_word, b->d_node, b->d_bstart, b->d_weight, b->d_out, b->d_kf, b->d_match, b->d_bin, b->d_hist};
+    for (void *p : dev) if (p) cudaFree(p);
+    void *host[] = {b->h_out, b->h_kf, b->h_match};
+    for (void *p : host) if (p) cudaFreeHost(p);
+    delete b;
+    b = nullptr;
+}
+
+namespace {
+
+unsigned bow_flags(int scoring, int weighting)
+{
+    /* TF_IDF (0), TF (1): BowVector::addWeight; IDF (2), BINARY (3): addIfNotExist (TemplatedVocabulary.h:1144-1197).
+     * L1 norm for L1 / chi-square / KL / Bhattacharyya scoring, L2 for L2, none for the dot product
+     * (ScoringObject.h:74-89); without a norm the accumulated values are divided by the number of words (:1160-1166). */
+    const bool accumulate = weighting == 0 || weighting == 1;
+    const unsigned norm = scoring == 5 ? 0u : scoring == 1 ? 2u : 1u;
+    return (accumulate ? 1u : 0u) | (norm << 1) | ((accumulate && norm == 0) ? 8u : 0u);
+}
+
+int bow_np2(int n)
+{
+    int p = BOW_ASM_NT;
+    while (p < n) p <<= 1;
+    return p;
+}
+
+/* B1 + B2 on `st`: descriptors desc (device, 32 B each), count from n_p (device) or n_val */
+int bow_enqueue(const borb_vocabulary *voc, const uint8_t *d_desc, const int *n_p, int n_val, int cap, int levelsup,
+                int *d_word, int *d_node, double *d_weight, int *d_bstart, uint8_t *d_out, cudaStream_t st)
+{
+    const BowSlab S = bow_slab_layout((size_t)cap);
+    const int G = voc->max_children <= 8 ? 8 : voc->max_children <= 16 ? 16 : 32;
+    const int per_cta = BOW_NT / G, grid = std::max(1, (cap + per_cta - 1) / per_cta);
+#define B1(G_) k_bow_descend<G_><<<grid, BOW_NT, 0, st>>>(voc->dev, reinterpret_cast<const uint4 *>(d_desc), n_p, n_val, cap, \
+                                                      levelsup, d_word, d_node, d_weight)
+    if (G == 8) B1(8); else if (G == 16) B1(16); else B1(32);
+#undef B1
+    const size_t smem = (size_t)bow_np2(cap) * 8;
+    if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_bow_assemble<<<1, BOW_ASM_NT, smem, st>>>(d_word, d_node, d_weight, n_p, n_val, cap, bow_flags(voc->scoring, voc->weighting),
+                                               reinterpret_cast<uint32_t *>(d_out + S.word), reinterpret_cast<double *>(d_out + S.val),
+                                               d_bstart, reinterpret_cast<uint32_t *>(d_out + S.node),
+                                               reinterpret_cast<int *>(d_out + S.start), reinterpret_cast<uint32_t *>(d_out + S.feat),
+                                               reinterpret_cast<int *>(d_out + S.counts));
+    CU(cudaGetLastError());
+    return BORB_OK;
+}
+
+bool bow_next_token(char *&p, char *&tok)
+{
+    while (*p == ' ' || *p == '\t' || *p == '\r' || *p == '\n') ++p;
+    if (!*p) return false;
+    tok = p;
+    while (*p && *p != ' ' && *p != '\t' && *p != '\r' && *p != '\n') ++p;
+    if (*p) *p++ = 0;
+    return true;
+}
+
+} // namespace
+
+extern "C" {
+
+/* nodes 1 .. n_nodes (node 0 is the root): parent id (< the node's own id), leaf flag (> 0: the node is a word;
+ * word ids count the flagged nodes in order), 32-byte descriptor, weight */
+int borb_voc_create(int k, int L, int scoring, int weighting, int n_nodes, const int32_t *parent, const uint8_t *is_leaf,
+                    const uint8_t *desc, const double *weight, int device, borb_vocabulary **out)
+{
+    if (!out) return fail(BORB_ERR_ARG, "out is null");
+    *out = nullptr;
+    /* the reference's own check (TemplatedVocabulary.h:1359) */
+    if (k < 0 || k > 20 || L < 1 || L > 10 || scoring < 0 || scoring > 5 || weighting < 0 || weighting > 3)
+        return fail(BORB_ERR_ARG, "not a vocabulary header: k %d, L %d, scoring %d, weighting %d", k, L, scoring, weighting);
+    if (n_nodes < 0 || (n_nodes > 0 && (!parent || !is_leaf || !desc || !weight))) return fail(BORB_ERR_ARG, "node arrays");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(BORB_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    if (device < 0) CU(cudaGetDevice(&device));
+    if (device >= ndev) return fail(BORB_ERR_ARG, "device %d of %d", device, ndev);
+    const int N = n_nodes + 1;
+    for (int i = 1; i < N; ++i)
+        if (parent[i - 1] < 0 || parent[i - 1] >= i)
+            return fail(BORB_ERR_ARG, "node %d names parent %d (the reference indexes m_nodes[parent] while it reads the file)", i, parent[i - 1]);
+    std::vector<int> cstart((size_t)N + 1, 0), child((size_t)std::max(n_nodes, 1)), word_id((size_t)N, 0);
+    for (int i = 1; i < N; ++i) ++cstart[(size_t)parent[i - 1] + 1];
+    for (int i = 0; i < N; ++i) cstart[(size_t)i + 1] += cstart[i];
+    {
+        std::vector<int> fill(cstart.begin(), cstart.end() - 1);
+        for (int i = 1; i < N; ++i) child[(size_t)fill[parent[i - 1]]++] = i; /* children in file order */
+    }
+    int n_words = 0, max_children = 0;
+    for (int i = 1; i < N; ++i) if (is_leaf[i - 1] > 0) word_id[i] = n_words++;
+    for (int i = 0; i < N; ++i) max_children = std::max(max_children, cstart[(size_t)i + 1] - cstart[i]);
+    if (max_children > 65535) return fail(BORB_ERR_ARG, "a node has %d children", max_children);
+
+    borb_vocabulary *v = new borb_vocabulary();
+    v->device = device; v->k = k; v->L = L; v->scoring = scoring; v->weighting = weighting;
+    v->n_nodes = N; v->n_words = n_words; v->max_children = max_children; v->n_slots = n_nodes;
+    const size_t S = (size_t)std::max(n_nodes, 1);
+    /* blob: [cweight 8S][cdesc 32S][cinfo 8S][cnode 4S][cword 4S], every section on a 16-byte boundary */
+    const size_t o_desc = (S * 8 + 15) & ~(size_t)15, o_info = o_desc + S * 32, o_node = (o_info + S * 8 + 15) & ~(size_t)15,
+                 o_word = (o_node + S * 4 + 15) & ~(size_t)15, bytes = o_word + S * 4;
+    std::vector<uint8_t> blob(bytes, 0);
+    double *cw = reinterpret_cast<double *>(blob.data());
+    uint8_t *cd = blob.data() + o_desc;
+    int *ci = reinterpret_cast<int *>(blob.data() + o_info), *cn = reinterpret_cast<int *>(blob.data() + o_node),
+        *cwd = reinterpret_cast<int *>(blob.data() + o_word);
+    for (int s = 0; s < n_nodes; ++s) {
+        const int id = child[s];
+        cw[s] = weight[id - 1];
+        std::memcpy(cd + (size_t)s * 32, desc + (size_t)(id - 1) * 32, 32);
+        ci[2 * s] = cstart[id];
+        ci[2 * s + 1] = cstart[(size_t)id + 1] - cstart[id];
+        cn[s] = id;
+        cwd[s] = word_id[id];
+    }
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaMalloc(&v->d_blob, bytes);
+    if (e == cudaSuccess) e = cudaMemcpy(v->d_blob, blob.data(), bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        if (v->d_blob) cudaFree(v->d_blob);
+        delete v;
+        cudaSetDevice(prev);
+        return fail(BORB_ERR_CUDA, "vocabulary upload: %s", cudaGetErrorString(e));
+    }
+    uint8_t *b = static_cast<uint8_t *>(v->d_blob);
+    v->dev.cweight = reinterpret_cast<const double *>(b);
+    v->dev.cdesc = reinterpret_cast<const uint4 *>(b + o_desc);
+    v->dev.cinfo = reinterpret_cast<const int2 *>(b + o_info);
+    v->dev.cnode = reinterpret_cast<const int *>(b + o_node);
+    v->dev.cword = reinterpret_cast<const int *>(b + o_word);
+    v->dev.root_start = cstart[0];
+    v->dev.root_count = cstart[1] - cstart[0];
+    v->dev.L = L;
+    *out = v;
+    return BORB_OK;
+}
+
+/* TemplatedVocabulary::loadFromTextFile (:1338-1421): "k L scoring weighting", then one node per line:
+ * parent isLeaf d0 .. d31 weight.  A blank line (the reference would parse it into a node with an indeterminate
+ * descriptor) is skipped; a descriptor token that is not a number leaves a 0 byte. */
+int borb_voc_load_text(const char *path, int device, borb_vocabulary **out)
+{
+    if (!path || !out) return fail(BORB_ERR_ARG, "null argument");
+    *out = nullptr;
+    FILE *f = std::fopen(path, "r");
+    if (!f) return fail(BORB_ERR_ARG, "cannot open %s", path);
+    char *line = nullptr;
+    size_t cap = 0;
+    int h[4] = {-1, -1, -1, -1};
+    if (getline(&line, &cap, f) >= 0) {
+        char *p = line, *tok;
+        for (int i = 0; i < 4 && bow_next_token(p, tok); ++i) h[i] = (int)std::strtol(tok, nullptr, 10);
+    }
+    std::vector<int32_t> parent;
+    std::vector<uint8_t> leaf, desc;
+    std::vector<double> weight;
+    while (getline(&line, &cap, f) >= 0) {
+        char *p = line, *tok;
+        if (!bow_next_token(p, tok)) continue;
+        parent.push_back((int32_t)std::strtol(tok, nullptr, 10));
+        leaf.push_back(bow_next_token(p, tok) && std::strtol(tok, nullptr, 10) > 0 ? 1 : 0);
+        uint8_t d[32] = {0};
+        for (int i = 0; i < 32; ++i) {
+            if (!bow_next_token(p, tok)) break;
+            char *end = tok;
+            const long n = std::strtol(tok, &end, 10);
+            if (end != tok) d[i] = (uint8_t)n;
+        }
+        desc.insert(desc.end(), d, d + 32);
+        weight.push_back(bow_next_token(p, tok) ? std::strtod(tok, nullptr) : 0.0);
+    }
+    std::free(line);
+    std::fclose(f);
+    return borb_voc_create(h[0], h[1], h[2], h[3], (int)parent.size(), parent.data(), leaf.data(), desc.data(), weight.data(),
+                           device, out);
+}
+
+void borb_voc_destroy(borb_vocabulary *v)
+{
+    if (!v) return;
+    cudaSetDevice(v->device);
+    if (v->stream) cudaStreamSynchronize(v->stream);
+    void *dev[] = {v->d_blob, v->d_desc, v->d_word, v->d_node, v->d_weight, v->d_out, v->d_bstart};
+    for (void *p : dev) if (p) cudaFree(p);
+    if (v->h_desc) cudaFreeHost(v->h_desc);
+    if (v->h_out) cudaFreeHost(v->h_out);
+    if (v->stream) cudaStreamDestroy(v->stream);
+    delete v;
+}
+
+int borb_voc_info(const borb_vocabulary *v, int *k, int *L, int *n_nodes, int *n_words, int *scoring, int *weighting)
+{
+    if (!v) return fail(BORB_ERR_ARG, "null vocabulary");
+    if (k) *k = v->k;
+    if (L) *L = v->L;
+    if (n_nodes) *n_nodes = v->n_nodes;
+    if (n_words) *n_words = v->n_words;
+    if (scoring) *scoring = v->scoring;
+    if (weighting) *weighting = v->weighting;
+    return BORB_OK;
+}
+
+/* transform(features, v, fv, levelsup) for descriptors in HOST memory (KeyFrame::ComputeBoW on a keyframe whose
+ * descriptors no handle holds).  Capacities: word_id / word_val / node_id / feat_idx [n], node_start [n + 1]. */
+int borb_voc_transform(borb_vocabulary *v, const uint8_t *desc, int n, int levelsup, uint32_t *word_id, double *word_val,
+                       int *n_words, uint32_t *node_id, int32_t *node_start, uint32_t *feat_idx, int *n_nodes)
+{
+    if (!v || n < 0 || (n > 0 && !desc) || !n_words || !n_nodes || !node_start) return fail(BORB_ERR_ARG, "null argument");
+    if (n > 0 && (!word_id || !word_val || !node_id || !feat_idx)) return fail(BORB_ERR_ARG, "null output array");
+    if (n > BOW_MAX_FEATURES) return fail(BORB_ERR_CAPACITY, "%d features; the bag-of-words step sorts up to %d per frame", n, BOW_MAX_FEATURES);
+    *n_words = 0; *n_nodes = 0; node_start[0] = 0;
+    if (n == 0 || v->n_words == 0) return BORB_OK; /* empty(): the reference returns empty vectors (:1136) */
+    CU(cudaSetDevice(v->device));
+    if (n > v->cap) {
+        const int cap = bow_np2(n);
+        CU(cudaStreamSynchronize(v->stream));
+        void *dev[] = {v->d_desc, v->d_word, v->d_node, v->d_weight, v->d_out, v->d_bstart};
+        for (void *p : dev) if (p) cudaFree(p);
+        if (v->h_desc) cudaFreeHost(v->h_desc);
+        if (v->h_out) cudaFreeHost(v->h_out);
+        v->d_desc = v->h_desc = v->d_out = v->h_out = nullptr; v->d_word = v->d_node = v->d_bstart = nullptr; v->d_weight = nullptr;
+        v->cap = 0;
+        const BowSlab S = bow_slab_layout((size_t)cap);
+        CU(cudaMalloc(&v->d_desc, (size_t)cap * 32));
+        CU(cudaMallocHost(&v->h_desc, (size_t)cap * 32));
+        CU(cudaMalloc(&v->d_word, (size_t)cap * 4));
+        CU(cudaMalloc(&v->d_node, (size_t)cap * 4));
+        CU(cudaMalloc(&v->d_weight, (size_t)cap * 8));
+        CU(cudaMalloc(&v->d_bstart, ((size_t)cap + 1) * 4));
+        CU(cudaMalloc(&v->d_out, S.bytes));
+        CU(cudaMallocHost(&v->h_out, S.bytes));
+        v->cap = cap;
+    }
+    const BowSlab S = bow_slab_layout((size_t)v->cap);
+    std::memcpy(v->h_desc, desc, (size_t)n * 32);
+    CU(cudaMemcpyAsync(v->d_desc, v->h_desc, (size_t)n * 32, cudaMemcpyHostToDevice, v->stream));
+    int rc = bow_enqueue(v, v->d_desc, nullptr, n, v->cap, levelsup, v->d_word, v->d_node, v->d_weight, v->d_bstart, v->d_out, v->stream);
+    if (rc != BORB_OK) return rc;
+    CU(cudaMemcpyAsync(v->h_out, v->d_out, S.bytes, cudaMemcpyDeviceToHost, v->stream));
+    CU(cudaStreamSynchronize(v->stream));
+    const int *cnt = reinterpret_cast<const int *>(v->h_out + S.counts);
+    const int nw = cnt[0], nn = cnt[1];
+    std::memcpy(word_id, v->h_out + S.word, (size_t)nw * 4);
+    std::memcpy(word_val, v->h_out + S.val, (size_t)nw * 8);
+    std::memcpy(node_id, v->h_out + S.node, (size_t)nn * 4);
+    std::memcpy(node_start, v->h_out + S.start, ((size_t)nn + 1) * 4);
+    std::memcpy(feat_idx, v->h_out + S.feat, (size_t)node_start[nn] * 4);
+    *n_words = nw; *n_nodes = nn;
+    return BORB_OK;
+}
+
+/* Frame::ComputeBoW (src/Frame.cc:532-539; the reference passes levelsup = 4) on frame `frame` of h's last call */
+int borb_compute_bow(borb_extractor *h, int frame, const borb_vocabulary *voc, int levelsup)
+{
+    if (!h || !voc) return fail(BORB_ERR_ARG, "null argument");
+    if (!h->have_plan || h->last_n < 1) return fail(BORB_ERR_STATE, "no extraction yet");
+    if (h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    if (frame < 0 || frame >= h->last_n) return fail(BORB_ERR_ARG, "frame %d of %d", frame, h->last_n);
+    if (voc->device != h->device) return fail(BORB_ERR_ARG, "vocabulary on device %d, extractor on %d", voc->device, h->device);
+    const size_t K = (size_t)h->plan.kp_total;
+    if (K > BOW_MAX_FEATURES) return fail(BORB_ERR_CAPACITY, "%zu keypoint slots per frame; the bag-of-words step sorts up to %d", K, BOW_MAX_FEATURES);
+    CU(cudaSetDevice(h->device));
+    if (h->bow && h->bow->K != K) { CU(cudaStreamSynchronize(h->stream)); bow_release(h->bow); }
+    if (!h->bow) {
+        BowState *b = new BowState();
+        h->bow = b;
+        b->K = K;
+        const BowSlab S = bow_slab_layout(K);
+        CU(cudaMalloc(&b->d_word, K * 4));
+        CU(cudaMalloc(&b->d_node, K * 4));
+        CU(cudaMalloc(&b->d_weight, K * 8));
+        CU(cudaMalloc(&b->d_bstart, (K + 1) * 4));
+        CU(cudaMalloc(&b->d_out, S.bytes));
+        CU(cudaMallocHost(&b->h_out, S.bytes));
+        CU(cudaMemset(b->d_out, 0, S.bytes));
+        std::memset(b->h_out, 0, S.bytes);
+    }
+    BowState *b = h->bow;
+    const BowSlab S = bow_slab_layout(K);
+    b->on_host = false;
+    b->frame = -1;
+    if (voc->n_words == 0) { /* empty(): empty vectors */
+        CU(cudaMemsetAsync(b->d_out + S.counts, 0, 16, h->stream));
+        CU(cudaMemsetAsync(b->d_out + S.start, 0, 4, h->stream));
+    } else {
+        int rc = bow_enqueue(voc, h->d_out_desc + (size_t)frame * K * 32, h->d_nout + frame, 0, (int)K, levelsup, b->d_word,
+                             b->d_node, b->d_weight, b->d_bstart, b->d_out, h->stream);
+        if (rc != BORB_OK) return rc;
+    }
+    CU(cudaMemcpyAsync(b->h_out, b->d_out, S.bytes, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    b->frame = frame;
+    b->gen = h->extract_gen;
+    b->on_host = true;
+    return BORB_OK;
+}
+
+/* mBowVec as (word id ascending, value) and mFeatVec in CSR form (node id ascending; the features of node u are
+ * feat_idx[node_start[u] .. node_start[u+1]), ascending).  Pointers into page-locked memory owned by the handle,
+ * valid until its next borb_compute_bow. */
+int borb_bow_result(borb_extractor *h, int frame, const uint32_t **word_id, const double **word_val, int *n_words,
+                    const uint32_t **node_id, const int32_t **node_start, const uint32_t **feat_idx, int *n_nodes)
+{
+    if (!h) return fail(BORB_ERR_ARG, "null handle");
+    BowState *b = h->bow;
+    if (!b || !b->on_host || b->frame != frame || b->gen != h->extract_gen)
+        return fail(BORB_ERR_STATE, "borb_compute_bow has not run for frame %d of the current extraction", frame);
+    const BowSlab S = bow_slab_layout(b->K);
+    const int *cnt = reinterpret_cast<const int *>(b->h_out + S.counts);
+    if (word_id) *word_id = reinterpret_cast<const uint32_t *>(b->h_out + S.word);
+    if (word_val) *word_val = reinterpret_cast<const double *>(b->h_out + S.val);
+    if (n_words) *n_words = cnt[0];
+    if (node_id) *node_id = reinterpret_cast<const uint32_t *>(b->h_out + S.node);
+    if (node_start) *node_start = reinterpret_cast<const int32_t *>(b->h_out + S.start);
+    if (feat_idx) *feat_idx = reinterpret_cast<const uint32_t *>(b->h_out + S.feat);
+    if (n_nodes) *n_nodes = cnt[1];
+    return BORB_OK;
+}
+
+/* ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches) (src/ORBmatcher.cc:195-351): F = frame `frame` of cur's last
+ * call, whose bow vectors borb_compute_bow left on the device.  match [borb_max_keypoints]: per current keypoint the
+ * index of the keyframe keypoint whose map point it takes, or -1. */
+int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, float nnratio, unsigned flags,
+                       int32_t *match, int *n_cur, int *nmatches)
+{
+    if (!cur || !kf || !match) return fail(BORB_ERR_ARG, "null argument");
+    BowState *b = cur->bow;
+    if (!b || b->frame != frame || b->gen != cur->extract_gen)
+        return fail(BORB_ERR_STATE, "borb_compute_bow has not run for frame %d of the current extraction", frame);
+    if (cur->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    const int n = kf->n, nn = kf->n_nodes;
+    if (n < 0 || nn < 0 || (n > 0 && (!kf->desc || !kf->angle || !kf->mp_flags)) || (nn > 0 && (!kf->node_id || !kf->node_start || !kf->feat_idx)))
+        return fail(BORB_ERR_ARG, "keyframe arrays");
+    const int nfeat = nn > 0 ? kf->node_start[nn] : 0;
+    if (nfeat < 0 || nfeat > n) return fail(BORB_ERR_ARG, "keyframe feature vector lists %d features of %d", nfeat, n);
+    for (int i = 0; i < nfeat; ++i)
+        if (kf->feat_idx[i] >= (uint32_t)n) return fail(BORB_ERR_ARG, "keyframe feature index %u of %d", kf->feat_idx[i], n);
+    CU(cudaSetDevice(cur->device));
+    const size_t K = b->K;
+    cudaStream_t st = cur->stream;
+    if ((size_t)n > b->kf_cap || !b->d_kf) {
+        const size_t c = (((size_t)std::max(n, 1) + 1023) / 1024) * 1024;
+        CU(cudaStreamSynchronize(st));
+        if (b->d_kf) cudaFree(b->d_kf);
+        if (b->h_kf) cudaFreeHost(b->h_kf);
+        b->d_kf = b->h_kf = nullptr; b->kf_cap = 0;
+        CU(cudaMalloc(&b->d_kf, c * 49 + 16));
+        CU(cudaMallocHost(&b->h_kf, c * 49 + 16));
+        b->kf_cap = c;
+    }
+    if (!b->d_match) {
+        CU(cudaMalloc(&b->d_match, (K + 4) * 4));
+        CU(cudaMallocHost(&b->h_match, (K + 4) * 4));
+        CU(cudaMalloc(&b->d_bin, K));
+        CU(cudaMalloc(&b->d_hist, MT_HISTO * 4));
+    }
+    const size_t c = b->kf_cap, un = (size_t)n;
+    /* [desc 32c][angle 4c][node 4c][feat 4c][start 4(c+1)][mp c] */
+    const size_t o_ang = 32 * c, o_node = 36 * c, o_feat = 40 * c, o_start = 44 * c, o_mp = 48 * c + 8;
+    uint8_t *hp = b->h_kf, *dp = b->d_kf;
+    if (n) {
+        std::memcpy(hp, kf->desc, un * 32);
+        std::memcpy(hp + o_ang, kf->angle, un * 4);
+        std::memcpy(hp + o_mp, kf->mp_flags, un);
+    }
+    if (nn) {
+        std::memcpy(hp + o_node, kf->node_id, (size_t)nn * 4);
+        std::memcpy(hp + o_start, kf->node_start, ((size_t)nn + 1) * 4);
+        std::memcpy(hp + o_feat, kf->feat_idx, (size_t)nfeat * 4);
+    }
+    CU(cudaMemcpyAsync(dp, hp, c * 49 + 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(b->d_match, 0xff, K * 4, st));
+    CU(cudaMemsetAsync(b->d_hist, 0, MT_HISTO * 4, st));
+    const BowSlab S = bow_slab_layout(K);
+    const size_t fo = (size_t)frame * K;
+    const int check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
+    if (nn > 0)
+        k_bow_search<<<(nn + BOW_SEARCH_NT / 32 - 1) / (BOW_SEARCH_NT / 32), BOW_SEARCH_NT, 0, st>>>(
+            reinterpret_cast<const uint4 *>(dp), reinterpret_cast<const float *>(dp + o_ang), dp + o_mp,
+            reinterpret_cast<const uint32_t *>(dp + o_node), reinterpret_cast<const int *>(dp + o_start),
+            reinterpret_cast<const uint32_t *>(dp + o_feat), nn, reinterpret_cast<const uint4 *>(cur->d_out_desc + fo * 32),
+            cur->d_out_kp + fo, reinterpret_cast<const uint32_t *>(b->d_out + S.node), reinterpret_cast<const int *>(b->d_out + S.start),
+            reinterpret_cast<const uint32_t *>(b->d_out + S.feat), reinterpret_cast<const int *>(b->d_out + S.counts), nnratio,
+            check_ori, b->d_match, b->d_bin, b->d_hist);
+    k_bow_finish<<<1, 1024, 0, st>>>(cur->d_nout + frame, (int)K, check_ori, b->d_hist, b->d_bin, b->d_match, b->d_match + K);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(b->h_match, b->d_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
+    if (!cur->results_on_host && cur->nout_frame_on_host != frame)
+        CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    cur->nout_frame_on_host = frame;
+    const int nc = std::min(cur->h_nout[frame], (int)K);
+    std::memcpy(match, b->h_match, (size_t)nc * 4);
+    if (n_cur) *n_cur = nc;
+    if (nmatches) *nmatches = b->h_match[K];
+    return BORB_OK;
+}
+
+} // extern "C"

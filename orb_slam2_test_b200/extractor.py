@@ -51,6 +51,9 @@ STREAM_SYMBOLS = [
 SYMBOLS += STREAM_SYMBOLS
 # allocation-free variant of the per-keypoint step (no counterpart in the reference; see include/borb.h)
 SYMBOLS += ["borb_undistort_grid_noalloc"]
+# bag of words: Frame::ComputeBoW and ORBmatcher::SearchByBoW(KeyFrame*, Frame&)
+SYMBOLS += ["borb_voc_load_text", "borb_voc_create", "borb_voc_destroy", "borb_voc_info", "borb_voc_transform",
+            "borb_compute_bow", "borb_bow_result", "borb_search_by_bow"]
 
 
 class BorbError(RuntimeError):
@@ -127,6 +130,15 @@ def load_library() -> C.CDLL:
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
                                        C.POINTER(C.c_int)]
     lib.borb_undistort_grid_noalloc.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]
+    lib.borb_voc_load_text.argtypes = [C.c_char_p, C.c_int, C.POINTER(_vp)]
+    lib.borb_voc_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(_vp)]
+    lib.borb_voc_destroy.argtypes = [_vp]
+    lib.borb_voc_info.argtypes = [_vp] + [C.POINTER(C.c_int)] * 6
+    lib.borb_voc_transform.argtypes = [_vp, _vp, C.c_int, C.c_int, _vp, _vp, C.POINTER(C.c_int), _vp, _vp, _vp, C.POINTER(C.c_int)]
+    lib.borb_compute_bow.argtypes = [_vp, C.c_int, _vp, C.c_int]
+    lib.borb_bow_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int), C.POINTER(_vp),
+                                    C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int)]
+    lib.borb_search_by_bow.argtypes = [_vp, C.c_int, _vp, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     _lib = lib
     return lib
 
@@ -154,6 +166,55 @@ class _MapPoints(C.Structure):  # == borb_map_points
 class _LastFrame(C.Structure):  # == borb_last_frame
     _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("octave", _vp), ("angle", _vp),
                 ("Tcw", _vp)]
+
+
+class _KeyFrame(C.Structure):  # == borb_keyframe
+    _fields_ = [("n", C.c_int), ("desc", _vp), ("angle", _vp), ("mp_flags", _vp), ("n_nodes", C.c_int), ("node_id", _vp),
+                ("node_start", _vp), ("feat_idx", _vp)]
+
+
+class ORBVocabulary:
+    """ORB_SLAM2::ORBVocabulary (include/ORBVocabulary.h = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) on the
+    device: loadFromTextFile's format (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1421) or the tree as arrays."""
+
+    def __init__(self, path: str | None = None, device: int = -1, arrays=None):
+        self._lib = load_library()
+        self._h = _vp()
+        if path is not None:
+            _check(self._lib, self._lib.borb_voc_load_text(str(path).encode(), device, C.byref(self._h)))
+        else:
+            k, L, scoring, weighting, parent, leaf, desc, weight = arrays
+            keep = [np.ascontiguousarray(parent, np.int32), np.ascontiguousarray(leaf, np.uint8),
+                    np.ascontiguousarray(desc, np.uint8), np.ascontiguousarray(weight, np.float64)]
+            _check(self._lib, self._lib.borb_voc_create(k, L, scoring, weighting, len(keep[0]), *[a.ctypes.data for a in keep],
+                                                        device, C.byref(self._h)))
+        v = [C.c_int() for _ in range(6)]
+        _check(self._lib, self._lib.borb_voc_info(self._h, *[C.byref(x) for x in v]))
+        self.k, self.L, self.n_nodes, self.n_words, self.scoring, self.weighting = [x.value for x in v]
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.borb_voc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform(self, desc: np.ndarray, levelsup: int = 4) -> dict:
+        """transform(features, BowVector, FeatureVector, levelsup) for descriptors in host memory
+        (KeyFrame::ComputeBoW).  -> dict word_id, word_val, node_id, node_start, feat_idx (see include/borb.h)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d)
+        wid, wv = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64)
+        nid, ns, fi = np.zeros(max(n, 1), np.uint32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.uint32)
+        nw, nn = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_voc_transform(self._h, d.ctypes.data, n, levelsup, wid.ctypes.data, wv.ctypes.data,
+                                                       C.byref(nw), nid.ctypes.data, ns.ctypes.data, fi.ctypes.data, C.byref(nn)))
+        return {"word_id": wid[:nw.value].copy(), "word_val": wv[:nw.value].copy(), "node_id": nid[:nn.value].copy(),
+                "node_start": ns[:nn.value + 1].copy(), "feat_idx": fi[:ns[nn.value]].copy()}
 
 
 class ORBextractor:
@@ -466,6 +527,38 @@ class ORBextractor:
                                                                    nnratio, 0 if check_orientation else 2, out.ctypes.data,
                                                                    C.byref(nm)))
         return out[:fr.n].copy(), pv, nm.value
+
+    def compute_bow(self, voc: ORBVocabulary, frame: int = 0, levelsup: int = 4) -> dict:
+        """Frame::ComputeBoW (src/Frame.cc:532-539) on frame `frame` of the last call: mBowVec as (word_id, word_val),
+        mFeatVec as CSR (node_id, node_start, feat_idx).  The device copies stay for search_by_bow."""
+        _check(self._lib, self._lib.borb_compute_bow(self._h, frame, voc._h, levelsup))
+        p = [_vp() for _ in range(5)]
+        nw, nn = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_bow_result(self._h, frame, C.byref(p[0]), C.byref(p[1]), C.byref(nw), C.byref(p[2]),
+                                                    C.byref(p[3]), C.byref(p[4]), C.byref(nn)))
+
+        def view(ptr, n, dt):
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_ubyte)), (n * np.dtype(dt).itemsize,)).view(dt).copy() if n else np.zeros(0, dt)
+        ns = view(p[3], nn.value + 1, np.int32)
+        return {"word_id": view(p[0], nw.value, np.uint32), "word_val": view(p[1], nw.value, np.float64),
+                "node_id": view(p[2], nn.value, np.uint32), "node_start": ns, "feat_idx": view(p[4], int(ns[-1]), np.uint32)}
+
+    def search_by_bow(self, kf: dict, nnratio: float = 0.7, frame: int = 0, check_orientation: bool = True):
+        """ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches) (src/ORBmatcher.cc:195-351) with frame `frame` of the last
+        call (after compute_bow) as F.  kf: dict desc [n,32] u8, angle [n] f32 (mvKeysUn), mp_flags [n] u8 (bit 0 map
+        point, bit 1 bad), fv = the keyframe's feature vector (dict as compute_bow / ORBVocabulary.transform return).
+        -> (match [n_cur] i32: keyframe keypoint index or -1, nmatches)."""
+        fv = kf["fv"]
+        keep = [np.ascontiguousarray(kf["desc"], np.uint8), np.ascontiguousarray(kf["angle"], np.float32),
+                np.ascontiguousarray(kf["mp_flags"], np.uint8), np.ascontiguousarray(fv["node_id"], np.uint32),
+                np.ascontiguousarray(fv["node_start"], np.int32), np.ascontiguousarray(fv["feat_idx"], np.uint32)]
+        rec = _KeyFrame(len(keep[2]), keep[0].ctypes.data, keep[1].ctypes.data, keep[2].ctypes.data, len(keep[3]),
+                        keep[3].ctypes.data, keep[4].ctypes.data, keep[5].ctypes.data)
+        out = np.full(max(self._lib.borb_max_keypoints(self._h), 1), -1, np.int32)
+        n, nm = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_search_by_bow(self._h, frame, C.addressof(rec), nnratio, 0 if check_orientation else 2,
+                                                       out.ctypes.data, C.byref(n), C.byref(nm)))
+        return out[:n.value].copy(), nm.value
 
     def match_rounds(self) -> int:
         return self._lib.borb_match_rounds(self._h) & 0xff

@@ -1,0 +1,118 @@
+"""Bag of words on the device against the CPU restatement (itself equal to the reference's own DBoW2 + Frame.cc +
+ORBmatcher.cc object code, tests/test_oracle_bow_vs_reference.py): Frame::ComputeBoW (src/Frame.cc:532-539) and
+ORBmatcher::SearchByBoW(KeyFrame*, Frame&) (src/ORBmatcher.cc:195-351), through the C ABI.  Word values are compared
+as float64 BIT PATTERNS."""
+import numpy as np
+import pytest
+
+import bowcase
+from orb_slam2_test_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def vocdir(tmp_path_factory):
+    return tmp_path_factory.mktemp("voc")
+
+
+@pytest.mark.parametrize("name", [v[0] for v in bowcase.VOCABULARIES])
+def test_transform_of_host_descriptors(name, vocdir, oracle_built):
+    from oracle import pyoracle
+    from orb_slam2_test_b200 import ORBVocabulary
+    path = bowcase.vocabulary(vocdir, name)
+    ours, want = ORBVocabulary(path), pyoracle.BowVocabulary(path)
+    assert (ours.k, ours.L, ours.n_nodes, ours.n_words, ours.scoring, ours.weighting) == \
+           (want.k, want.L, want.n_nodes, want.n_words, want.scoring, want.weighting)
+    sets = [bowcase.frame_features(synth.TUM_SHAPE, 1, 0, 1000)[1], bowcase.frame_features(synth.KITTI_SHAPE, 2, 3, 2000)[1],
+            bowcase.word_like(name, 3000, 5), bowcase.word_like(name, 500, 6, noise_bits=0), np.zeros((0, 32), np.uint8),
+            np.zeros((7, 32), np.uint8), bowcase.word_like(name, 16384, 7)]
+    for d in sets:
+        for levelsup in (4, 2, 0, 12):
+            assert bowcase.same_bow(ours.transform(d, levelsup), want.transform(d, levelsup)), f"{name} n={len(d)} levelsup={levelsup}"
+    # the vocabulary from arrays is the vocabulary from the file
+    parent, leaf, desc, weight = want.arrays()
+    again = ORBVocabulary(arrays=(want.k, want.L, want.scoring, want.weighting, parent, leaf, desc, weight))
+    assert bowcase.same_bow(again.transform(sets[2], 4), want.transform(sets[2], 4))
+
+
+@pytest.mark.parametrize("scoring", range(6))
+@pytest.mark.parametrize("weighting", range(4))
+def test_every_scoring_and_weighting_type(scoring, weighting, vocdir, oracle_built):
+    from oracle import pyoracle
+    from orb_slam2_test_b200 import ORBVocabulary
+    path = bowcase.vocabulary(vocdir, "k10L3", scoring, weighting)
+    ours, want = ORBVocabulary(path), pyoracle.BowVocabulary(path)
+    d = bowcase.word_like("k10L3", 2500, 11)
+    assert bowcase.same_bow(ours.transform(d, 4), want.transform(d, 4))
+    assert bowcase.same_bow(ours.transform(d, 1), want.transform(d, 1))
+
+
+def test_errors(vocdir, tmp_path):
+    from orb_slam2_test_b200 import BorbError, ORBVocabulary, ORBextractor
+    bad = tmp_path / "bad.txt"
+    bad.write_text("30 6 0 0\n0 1 " + " ".join(["0"] * 32) + " 1.0")
+    with pytest.raises(BorbError):
+        ORBVocabulary(str(bad))  # k > 20: the reference's own header check
+    with pytest.raises(BorbError):
+        ORBVocabulary(str(tmp_path / "missing.txt"))
+    voc = ORBVocabulary(bowcase.vocabulary(vocdir, "k10L3"))
+    ext = ORBextractor(500, 1.2, 8, 20, 7)
+    with pytest.raises(BorbError):
+        ext.compute_bow(voc)  # nothing extracted yet
+    ext(synth.make_frame(synth.TUM_SHAPE, seed=1, frame=0))
+    with pytest.raises(BorbError):
+        ext.search_by_bow({"desc": np.zeros((0, 32), np.uint8), "angle": np.zeros(0, np.float32), "mp_flags": np.zeros(0, np.uint8),
+                           "fv": {"node_id": np.zeros(0, np.uint32), "node_start": np.zeros(1, np.int32), "feat_idx": np.zeros(0, np.uint32)}})
+    ext.compute_bow(voc)
+    ext(synth.make_frame(synth.TUM_SHAPE, seed=1, frame=1))
+    with pytest.raises(BorbError):  # the bow vectors belonged to the previous extraction
+        ext.search_by_bow({"desc": np.zeros((0, 32), np.uint8), "angle": np.zeros(0, np.float32), "mp_flags": np.zeros(0, np.uint8),
+                           "fv": {"node_id": np.zeros(0, np.uint32), "node_start": np.zeros(1, np.int32), "feat_idx": np.zeros(0, np.uint32)}})
+
+
+@pytest.mark.parametrize("name,shape,nf", [("k10L4", synth.TUM_SHAPE, 1000), ("k4L6", synth.KITTI_SHAPE, 2000),
+                                           ("k9L5ragged", synth.TUM_SHAPE, 2000), ("k10L3", synth.TUM_SHAPE, 500)])
+def test_compute_bow_and_search_by_bow_on_extracted_frames(name, shape, nf, vocdir, oracle_built):
+    """the frame's descriptors never leave the device between the extraction, ComputeBoW and SearchByBoW"""
+    from oracle import pyoracle
+    from orb_slam2_test_b200 import ORBVocabulary, ORBextractor
+    path = bowcase.vocabulary(vocdir, name)
+    voc, want = ORBVocabulary(path), pyoracle.BowVocabulary(path)
+    ext = ORBextractor(nf, 1.2, 8, 20, 7)
+    total = 0
+    for t in (0, 2):
+        kk, kd = bowcase.frame_features(shape, 3, t, nf)          # keyframe: frame t (host side, as a KeyFrame is)
+        fk, fd = bowcase.frame_features(shape, 3, t + 1, nf)      # current frame: frame t + 1, extracted on the device
+        gk, gd = ext(synth.make_frame(shape, seed=3, frame=t + 1))
+        assert gk.tobytes() == fk.tobytes() and np.array_equal(gd, fd)
+        bow = ext.compute_bow(voc)
+        assert bowcase.same_bow(bow, want.transform(fd, 4)), f"{name} t={t}: ComputeBoW differs"
+        mp = bowcase.keyframe_flags(len(kk), 40 + t)
+        kf = {"desc": kd, "angle": kk["angle"], "mp_flags": mp, "fv": voc.transform(kd, 4)}
+        assert bowcase.same_bow(kf["fv"], want.transform(kd, 4))
+        for ratio, ori in ((0.7, True), (0.9, True), (0.6, False)):
+            w, wnm = want.search_by_bow(kk, kd, mp, fk, fd, ratio, ori)
+            g, nm = ext.search_by_bow(kf, ratio, check_orientation=ori)
+            bad = np.nonzero(g != w)[0]
+            assert bad.size == 0 and nm == wnm, f"{name} t={t} ratio={ratio} ori={ori}: {bad.size} differ, nm {nm} vs {wnm}, e.g. {bad[:5]}"
+            total += nm
+    assert total > 100
+    # an empty keyframe matches nothing
+    e = {"desc": np.zeros((0, 32), np.uint8), "angle": np.zeros(0, np.float32), "mp_flags": np.zeros(0, np.uint8),
+         "fv": {"node_id": np.zeros(0, np.uint32), "node_start": np.zeros(1, np.int32), "feat_idx": np.zeros(0, np.uint32)}}
+    g, nm = ext.search_by_bow(e)
+    assert nm == 0 and (g == -1).all()
+
+
+def test_batch_frames_and_replay(vocdir, oracle_built):
+    """ComputeBoW on frame 2 of a 4-frame batch, twice (same answer), then on frame 0"""
+    from oracle import pyoracle
+    from orb_slam2_test_b200 import ORBVocabulary, ORBextractor
+    path = bowcase.vocabulary(vocdir, "k10L4")
+    voc, want = ORBVocabulary(path), pyoracle.BowVocabulary(path)
+    ext = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=4)
+    imgs = np.stack([synth.make_frame(synth.TUM_SHAPE, seed=5, frame=f) for f in range(4)])
+    res = ext.extract_batch(imgs)
+    for f in (2, 2, 0, 3):
+        assert bowcase.same_bow(ext.compute_bow(voc, frame=f), want.transform(res[f][1], 4)), f"frame {f}"
