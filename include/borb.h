@@ -428,6 +428,11 @@ float borb_last_prestep_ms(borb_extractor *h);
 int borb_debug_candidates(borb_extractor *h, int frame, int level, int32_t *xs, int32_t *ys,
                           int32_t *scores, int cap, int *n);
 int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out /* cols*rows */);
+/* computeOrbDescriptor (src/ORBextractor.cc:117-157) of the pixel (x, y) of a caller-supplied (already blurred) image
+ * at a caller-supplied angle, by the device function the extract kernels use: the known-answer tap for the float
+ * form of the pattern rotation.  18 <= x < cols - 18, 18 <= y < rows - 18. */
+int borb_debug_describe(borb_extractor *h, const uint8_t *img, int cols, int rows, size_t step, int x, int y,
+                        float angle_deg, uint8_t *desc32);
 /* host evaluation of the device sin/cos routine (same inline function, host build) */
 void borb_debug_sincos(float radians, float *s, float *c);
 /* host evaluation of the per-pixel FAST score used by the cell kernel: 0 = not a FAST-9 corner at

@@ -1804,6 +1804,27 @@ int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out)
     return BORB_OK;
 }
 
+/* K6 (computeOrbDescriptor, src/ORBextractor.cc:117-157) on a caller-supplied image and angle: the device function the
+ * extract kernels use, on one warp.  (x, y) must keep the rotated pattern (|offset| <= 18) inside the image. */
+int borb_debug_describe(borb_extractor *h, const uint8_t *img, int cols, int rows, size_t step, int x, int y, float angle_deg,
+                        uint8_t *desc32)
+{
+    if (!h || !img || !desc32 || cols < 37 || rows < 37 || step < (size_t)cols || x < 18 || y < 18 || x + 18 >= cols || y + 18 >= rows)
+        return fail(BORB_ERR_ARG, "debug_describe arguments");
+    CU(cudaSetDevice(h->device));
+    uint8_t *d = nullptr;
+    CU(cudaMalloc(&d, step * (size_t)rows + 32));
+    cudaError_t e = cudaMemcpy(d, img, step * (size_t)rows, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_debug_describe<<<1, 32, 0, h->stream>>>(d, (int)step, x, y, angle_deg, h->d_pattern, d + step * (size_t)rows);
+        e = cudaStreamSynchronize(h->stream);
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(desc32, d + step * (size_t)rows, 32, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(BORB_ERR_CUDA, "debug_describe: %s", cudaGetErrorString(e));
+    return BORB_OK;
+}
+
 void borb_debug_sincos(float radians, float *s, float *c) { orb_sincosf_exact(radians, s, c); }
 int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_score_px(p, pitch, t_lo); }
 

@@ -51,6 +51,46 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
     return a;
 }
 
+/* K6, one descriptor byte: bit k compares the blurred image at the two rotated pattern points of pattern word
+ * pw[k] (xa, ya, xb, yb as int8); c = the keypoint's pixel, pitch = bytes per row (src/ORBextractor.cc:117-157).
+ * The rotation has the form the reference's -O3 -march=native object contains -- x*b + y*a contracted to
+ * fma(x, b, rn(y*a)), x*a - y*b to fma(x, a, -rn(y*b)) --, sin/cos are glibc's sincosf, cvRound is round-half-even:
+ * tests/test_gpu_edge.py holds inputs within an ulp of a rounding tie where the unfused form reads another pixel. */
+__device__ __forceinline__ int orb_desc_byte(const uint8_t *c, int pitch, float angle_deg, const uint32_t *pw)
+{
+    const float factor_pi = (float)(3.1415926535897932384626433832795 / 180.f);
+    float a, b;
+    orb_sincosf_exact(__fmul_rn(angle_deg, factor_pi), &b, &a);
+    int val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        int t[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const float px = (float)(int)(signed char)(pw[k] >> (16 * e));
+            const float py = (float)(int)(signed char)(pw[k] >> (16 * e + 8));
+            const int row = __float2int_rn(__fmaf_rn(px, b, __fmul_rn(py, a)));
+            const int col = __float2int_rn(__fmaf_rn(px, a, -__fmul_rn(py, b)));
+            t[e] = c[row * pitch + col];
+        }
+        val |= (t[0] < t[1]) << k;
+    }
+    return val;
+}
+
+/* parity tap (borb_debug_describe): K6 on a caller-supplied patch and angle, one warp */
+__global__ void k_debug_describe(const uint8_t *__restrict__ patch, int pitch, int cx, int cy, float angle_deg,
+                                 const signed char *__restrict__ pattern, uint8_t *__restrict__ desc)
+{
+    const int lane = threadIdx.x;
+    uint32_t pw[8];
+    const uint4 p0 = __ldg(reinterpret_cast<const uint4 *>(pattern) + lane * 2);
+    const uint4 p1 = __ldg(reinterpret_cast<const uint4 *>(pattern) + lane * 2 + 1);
+    pw[0] = p0.x; pw[1] = p0.y; pw[2] = p0.z; pw[3] = p0.w;
+    pw[4] = p1.x; pw[5] = p1.y; pw[6] = p1.z; pw[7] = p1.w;
+    desc[lane] = (uint8_t)orb_desc_byte(patch + (size_t)cy * pitch + cx, pitch, angle_deg, pw);
+}
+
 #ifndef DESC_NT
 #define DESC_NT 128
 #endif
@@ -223,24 +263,7 @@ k_orient_describe(const __grid_constant__ DescMaps dm, const signed char *__rest
         const float angle = fast_atan2_deg((float)m01, (float)m10);
 
         /* ---- K6 ---- */
-        const float factor_pi = (float)(3.1415926535897932384626433832795 / 180.f);
-        float a, b;
-        orb_sincosf_exact(__fmul_rn(angle, factor_pi), &b, &a);
-        const uint8_t *c = bufp + DESC_POFF + 18 * DESC_PB + ((x - 18) & 15) + 18;
-        int val = 0;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            int t[2];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const float px = (float)(int)(signed char)(pw[k] >> (16 * e));
-                const float py = (float)(int)(signed char)(pw[k] >> (16 * e + 8));
-                const int row = __float2int_rn(__fmaf_rn(px, b, __fmul_rn(py, a)));
-                const int col = __float2int_rn(__fmaf_rn(px, a, -__fmul_rn(py, b)));
-                t[e] = c[row * DESC_PB + col];
-            }
-            val |= (t[0] < t[1]) << k;
-        }
+        const int val = orb_desc_byte(bufp + DESC_POFF + 18 * DESC_PB + ((x - 18) & 15) + 18, DESC_PB, angle, pw);
         out_desc[((size_t)frame * kp_total + o) * 32 + lane] = (uint8_t)val;
         __syncwarp(); /* this buffer is refilled during the next iteration */
 
