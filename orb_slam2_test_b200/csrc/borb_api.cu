@@ -133,9 +133,6 @@ struct borb_extractor {
     uint2 *d_chain_tabs = nullptr;
     int chain_tstride = 0;
     int chain_tiles = 0, chain_off_b = 0, chain_off_t = 0, chain_smem = 0;
-    /* K1, throughput shape: a frame per thread-block cluster (k_pyr_band); band_clusters == 0: geometry not supported */
-    PyrBandPlan band = {};
-    int band_smem = 0, band_clusters = 0;
     std::vector<BorbCell> cells;
     std::vector<BorbTile> tiles;
     BorbPlan *d_plan = nullptr;
@@ -318,97 +315,6 @@ void free_geometry(borb_extractor *h)
     h->results_on_host = h->pyramid_on_host = false;
     h->nout_frame_on_host = -1;
     h->last_n = 0;
-}
-
-/* K1 throughput shape (k_pyr_band): CTA c of a cluster of C owns rows [c*h/C, (c+1)*h/C) of every level; in shared
- * memory it holds those plus the rows of the level that the NEXT level's band reads through its two y taps.  The
- * kernel's x path reads 12 bytes from the word that holds the first tap of a 4-pixel word column and expects the four
- * tap pairs within 8 bytes of that tap: true up to a scale factor of about 2; beyond that, or when two CTAs' buffers
- * do not fit an SM, the per-level kernels stay in charge (band_clusters = 0). */
-int build_band_plan(borb_extractor *h, const BorbPlan &P, const std::vector<int> &tab_i)
-{
-    h->band_clusters = 0;
-    static const bool off = getenv("BORB_PYR_BAND_OFF") != nullptr; /* A/B knob */
-    if (off) return BORB_OK;
-    const int nl = P.nlevels, C = PBD_MAXC;
-    PyrBandPlan &B = h->band;
-    std::memset(&B, 0, sizeof B);
-    B.C = C;
-    for (int l = 1; l < nl; ++l) {
-        const BorbLevel &L = P.lv[l];
-        for (int x = 0; x < L.w; x += 4) {
-            const int x3 = std::min(x + 3, L.w - 1);
-            if (tab_i[L.xofs_off + x3] - tab_i[L.xofs_off + x] > 6) return BORB_OK; /* not supported: keep the per-level kernels */
-        }
-    }
-    size_t buf[2] = {0, 0};
-    int max_rows = 1;
-    for (int l = 0; l < nl; ++l) {
-        const BorbLevel &L = P.lv[l];
-        B.spitch[l] = (int)align_up(L.w + 12, 16);
-        for (int c = 0; c < C; ++c) {
-            PyrBandRows &R = B.r[l][c];
-            R.a = (short)((long long)c * L.h / C);
-            R.b = (short)((long long)(c + 1) * L.h / C);
-            int s0 = R.a, s1 = R.b - 1;
-            if (l + 1 < nl) {
-                const BorbLevel &D = P.lv[l + 1];
-                const int da = (int)((long long)c * D.h / C), db = (int)((long long)(c + 1) * D.h / C);
-                if (db > da) {
-                    const int lo = std::min(std::max(tab_i[D.yofs_off + da], 0), L.h - 1);
-                    const int hi = std::min(std::max(tab_i[D.yofs_off + db - 1] + 1, 0), L.h - 1);
-                    s0 = std::min(s0, lo);
-                    s1 = std::max(s1, hi);
-                }
-            }
-            R.s0 = (short)s0; R.s1 = (short)s1;
-            buf[l & 1] = std::max(buf[l & 1], (size_t)std::max(s1 - s0 + 1, 0) * B.spitch[l]);
-            max_rows = std::max(max_rows, R.b - R.a);
-        }
-        /* row groups: items = column blocks x groups over 16 warps; cost of a round = rows per group + ~1.5 rows of tap set-up */
-        const int ncb = ((L.w + 3) / 4 + 31) / 32, nw = PBD_NT / 32, rows = std::max(1, (L.h + C - 1) / C);
-        double best = 1e30;
-        int bestG = 1;
-        for (int G = 1; G <= rows; ++G) {
-            const double cost = (double)((ncb * G + nw - 1) / nw) * ((rows + G - 1) / G + 1.5);
-            if (cost < best) { best = cost; bestG = G; }
-        }
-        B.groups[l] = bestG;
-    }
-    B.buf_off[0] = 0;
-    B.buf_off[1] = (int)align_up((long long)buf[0], 16);
-    B.rt_off = (int)align_up((long long)B.buf_off[1] + (long long)buf[1], 16);
-    int rt_rows = 0;
-    for (int l = 1; l < nl; ++l) {
-        B.rt_lvl[l] = rt_rows;
-        int m = 0;
-        for (int c = 0; c < C; ++c) m = std::max(m, B.r[l][c].b - B.r[l][c].a);
-        rt_rows += m;
-    }
-    const size_t total = (size_t)B.rt_off + (size_t)std::max(rt_rows, 1) * 8;
-    if (total > 200 * 1024) return BORB_OK; /* frame too large for a cluster of this size */
-    h->band_smem = (int)total;
-    CU(cudaFuncSetAttribute(k_pyr_band, cudaFuncAttributeMaxDynamicSharedMemorySize, h->band_smem));
-    /* how many clusters the device holds at once: the grid is that many, each walking frames */
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(C * 64);
-    cfg.blockDim = dim3(PBD_NT);
-    cfg.dynamicSmemBytes = (size_t)h->band_smem;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    int ncl = 0;
-    if (cudaOccupancyMaxActiveClusters(&ncl, k_pyr_band, &cfg) != cudaSuccess || ncl < 1) {
-        cudaGetLastError();
-        return BORB_OK;
-    }
-    h->band_clusters = ncl;
-    if (getenv("BORB_VERBOSE"))
-        fprintf(stderr, "[borb] k_pyr_band: %d clusters of %d CTAs resident, %d B of shared memory per CTA, row groups %d %d %d %d %d %d %d\n",
-                ncl, C, h->band_smem, B.groups[1], B.groups[2], B.groups[3], B.groups[4], B.groups[5], B.groups[6], B.groups[7]);
-    return BORB_OK;
 }
 
 /* Rectangles of k_pyr_chain: the levels are cut by one gx x gy grid (x cuts on multiples of 4 so that a tile's
@@ -694,9 +600,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
     if (!tab_i.empty()) CU(cudaMemcpy(h->d_tab_i, tab_i.data(), tab_i.size() * sizeof(int), cudaMemcpyHostToDevice));
     if (!tab_s.empty()) CU(cudaMemcpy(h->d_tab_s, tab_s.data(), tab_s.size() * sizeof(short), cudaMemcpyHostToDevice));
     {
-        int rc = build_chain(h, P, tab_i, tab_s);
+        const int rc = build_chain(h, P, tab_i, tab_s);
         if (rc != BORB_OK) return rc;
-        if ((rc = build_band_plan(h, P, tab_i)) != BORB_OK) return rc;
     }
     CU(cudaMemset(h->d_err, 0, 4));
     /* the blurred slab's frame/padding is never written; keep it defined */
@@ -828,25 +733,11 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     }
     static const bool chain_off = getenv("BORB_PYR_LEVELS") != nullptr; /* A/B knob: per-level kernels in every shape */
     const bool chain = !chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm;
-    h->last_launches = (chain || h->band_clusters > 0 ? 1 : P.nlevels) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
+    h->last_launches = (chain ? 1 : P.nlevels) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
     if (chain) {
         /* K1, latency shape: the whole chain in one launch */
         k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_chain_tabs, h->chain_tstride,
                                                                          dev_img, step, stride, d_pyr, h->chain_off_b, h->chain_off_t);
-    } else if (h->band_clusters > 0) { /* K1, throughput shape: a frame per cluster, all levels on chip */
-        cudaLaunchConfig_t cfg = {};
-        const int ncl = std::min(n, h->band_clusters);
-        cfg.gridDim = dim3(h->band.C * ncl);
-        cfg.blockDim = dim3(PBD_NT);
-        cfg.dynamicSmemBytes = (size_t)h->band_smem;
-        cfg.stream = st;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = h->band.C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.attrs = at;
-        cfg.numAttrs = 1;
-        CU(cudaLaunchKernelEx(&cfg, k_pyr_band, h->plan, h->band, (const int *)h->d_tab_i, (const short *)h->d_tab_s,
-                              (const uint8_t *)dev_img, step, stride, d_pyr, n));
     } else {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
         const int units = L0.pitch / 16;
@@ -1090,15 +981,6 @@ void borb_destroy(borb_extractor *h)
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-#ifdef PBD_PROF
-    {   /* phase cycles of cluster 0 / CTA 0 of k_pyr_band (profiling build only) */
-        unsigned long long t[8] = {};
-        if (cudaMemcpyFromSymbol(t, pbd_prof, sizeof t) == cudaSuccess && t[6])
-            fprintf(stderr, "[borb] k_pyr_band cycles per frame: level-0 load %llu, compute %llu, frame words %llu, "
-                            "cluster barrier wait %llu, halo %llu (%llu frames)\n", t[0] / t[6], t[2] / t[6], t[3] / t[6],
-                    t[4] / t[6], t[5] / t[6], t[6]);
-    }
-#endif
     free_geometry(h);
     if (h->d_pattern) cudaFree(h->d_pattern);
     if (h->d_map_xy) cudaFree(h->d_map_xy);

@@ -361,281 +361,4 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
         }
 }
 
-/* ---- the whole level chain of a frame on ONE thread-block cluster, for batches (the throughput shape) ----
- * The per-level kernels above write a level to HBM and the next launch reads it back (512-frame slabs are far larger
- * than L2): 1.85x the algorithmic traffic, and every 128 x 32 tile pays a prologue of tap loads and a staging pass.
- * Here a cluster of C CTAs owns a frame and walks the levels; CTA c owns the horizontal band
- * [c*h/C, (c+1)*h/C) of EVERY level and keeps the band of the current and of the previous level in shared memory
- * (ping-pong), so a level is read from HBM never -- each pixel is written once (1.18x the algorithmic bytes, all of
- * it the padded frame the layout asks for).  Per level:
- *   (1) compute the band from the previous level's band in shared memory: a lane = one word column (4 pixels, x taps
- *       in registers) walking down its rows; the lower source row's horizontal sums are the previous output row's
- *       upper ones five times out of six; the word goes to shared memory (source of the next level) and straight to
- *       the padded plane, and to the frame row that mirrors it (reflect-101) where there is one;
- *   (2) cluster barrier ARRIVE; the words that hold frame columns (left and right of every row) are written while the
- *       other CTAs catch up; barrier WAIT; then the one to three rows of the level that the NEXT level's band reads
- *       through its y taps from the neighbouring bands come back from the plane (L2 hits, ld.cg) into the halo rows
- *       of the shared-memory band.
- * No pixel is computed twice, so the planes are those of the kernels above bit for bit.  The host (borb_api.cu:
- * build_band_plan) fixes the bands, the halo rows, the row groups and the buffer sizes per geometry; the y-tap table
- * of every level's band is built once per CTA, not per frame. */
-#define PBD_NT 512
-#define PBD_MAXC 8
-
-struct PyrBandRows { short a, b, s0, s1; }; /* own rows [a, b); rows resident in shared memory [s0, s1] (s1 < s0: none) */
-struct PyrBandPlan {
-    PyrBandRows r[BORB_MAXL][PBD_MAXC];
-    int spitch[BORB_MAXL]; /* shared-memory row pitch of level l: a multiple of 16, >= w + 12 */
-    int buf_off[2];        /* the two band buffers (even / odd levels) */
-    int rt_off;            /* y-tap tables: int2 per band row, level l at rt_lvl[l] entries */
-    int rt_lvl[BORB_MAXL];
-    int groups[BORB_MAXL]; /* row groups the band of level l is cut into (work items = column blocks x groups) */
-    int C;
-};
-
-#ifdef PBD_PROF
-__device__ unsigned long long pbd_prof[8]; /* cycles of cluster 0 / CTA 0: level-0 load, -, compute, frame words, cluster barrier, halo, frames */
-#define PBD_T(i)                                                                              \
-    do {                                                                                      \
-        if (blockIdx.x == 0 && threadIdx.x == 0) { const long long t_ = clock64(); pbd_prof[i] += t_ - pbd_t0; pbd_t0 = t_; } \
-    } while (0)
-#else
-#define PBD_T(i) do { } while (0)
-#endif
-
-/* frame rows that mirror interior row r of a level of height h: -r for 1 <= r <= 19, 2(h-1) - r for h-20 <= r <= h-2
- * (as padded row numbers; -1 = none) */
-__device__ __forceinline__ int pbd_mirror_top(int r) { return (r >= 1 && r <= BORB_EDGE) ? BORB_EDGE - r : -1; }
-__device__ __forceinline__ int pbd_mirror_bot(int r, int h)
-{
-    return (r >= h - 1 - BORB_EDGE && r <= h - 2) ? BORB_EDGE + 2 * (h - 1) - r : -1;
-}
-
-/* the words of the band's rows (and of the frame rows that mirror them) that hold frame COLUMNS: x in [-20, 0) on the
- * left, from the word that holds column w to w + 18 on the right; byte by byte from the band in shared memory */
-__device__ __forceinline__ void pbd_frame_words(const BorbLevel &L, const PyrBandRows R, const unsigned char *buf, int pitch,
-                                                uint8_t *__restrict__ plane)
-{
-    const int nrows = R.b - R.a;
-    const int t0 = max((int)R.a, 1), nt = max(min((int)R.b, BORB_EDGE + 1) - t0, 0);
-    const int b0 = max((int)R.a, L.h - 1 - BORB_EDGE), nb = max(min((int)R.b, L.h - 1) - b0, 0);
-    const int J = nrows + nt + nb;
-    const int xr = L.w & ~3, nright = ((L.w + BORB_EDGE - 1) >> 2) - (xr >> 2) + 1; /* <= 6 */
-    for (int it = threadIdx.x; it < 16 * J; it += PBD_NT) {
-        const int j = it >> 4, e = it & 15;
-        if (e >= 5 + nright) continue;
-        int r, pr;
-        if (j < nrows) { r = R.a + j; pr = r + BORB_EDGE; }
-        else if (j < nrows + nt) { r = t0 + j - nrows; pr = BORB_EDGE - r; }
-        else { r = b0 + j - nrows - nt; pr = BORB_EDGE + 2 * (L.h - 1) - r; }
-        const int c = e < 5 ? 4 * e - 20 : xr + 4 * (e - 5);
-        const unsigned char *row = buf + (r - R.s0) * pitch;
-        uint32_t v = 0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            int x = min(max(c + q, -BORB_EDGE), L.w - 1 + BORB_EDGE); /* beyond the frame: don't care */
-            x = reflect101(x, L.w);
-            v |= (uint32_t)row[x] << (8 * q);
-        }
-        *reinterpret_cast<uint32_t *>(plane + (size_t)pr * L.pitch + BORB_XPAD + c) = v;
-    }
-}
-
-__global__ void __launch_bounds__(PBD_NT, 2)
-k_pyr_band(const __grid_constant__ BorbPlan plan_c, const __grid_constant__ PyrBandPlan bp, const int *__restrict__ tab_i,
-           const short *__restrict__ tab_s, const uint8_t *__restrict__ img, size_t step, size_t frame_stride,
-           uint8_t *__restrict__ pyr, int n_frames)
-{
-    const BorbPlan *plan = &plan_c;
-    extern __shared__ __align__(16) unsigned char pbd_smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nl = plan->nlevels;
-    int cta;
-    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
-    const int C = bp.C, ncl = gridDim.x / C;
-    int2 *const rt = reinterpret_cast<int2 *>(pbd_smem + bp.rt_off);
-    const uint32_t smem_s = (uint32_t)__cvta_generic_to_shared(pbd_smem);
-
-    /* y taps of this CTA's band of every level, once: the two source rows (relative to the resident rows of the level
-     * below) and the weight pair */
-    for (int l = 1; l < nl; ++l) {
-        const BorbLevel &L = plan->lv[l];
-        const BorbLevel &S = plan->lv[l - 1];
-        const PyrBandRows R = bp.r[l][cta], RS = bp.r[l - 1][cta];
-        for (int j = tid; j < R.b - R.a; j += PBD_NT) {
-            const int y = R.a + j, sy = tab_i[L.yofs_off + y];
-            const int sy0 = min(max(sy, 0), S.h - 1) - RS.s0, sy1 = min(max(sy + 1, 0), S.h - 1) - RS.s0;
-            rt[bp.rt_lvl[l] + j] = make_int2(sy0 | (sy1 << 16), *reinterpret_cast<const int *>(tab_s + L.yb_off + 2 * y));
-        }
-    }
-    __syncthreads();
-#ifdef PBD_PROF
-    long long pbd_t0 = clock64();
-#endif
-    for (int f = blockIdx.x / C; f < n_frames; f += ncl) {
-        uint8_t *const frame = pyr + (size_t)f * (size_t)plan->pyr_bytes;
-        {   /* level 0: the input rows of the band and of its halo, as aligned words whatever the input's row step;
-             * own rows go to the padded plane (and to the frame rows that mirror them) on the way */
-            const BorbLevel &L = plan->lv[0];
-            const PyrBandRows R = bp.r[0][cta];
-            unsigned char *const buf = pbd_smem + bp.buf_off[0];
-            const int pitch = bp.spitch[0], nw = (L.w + 3) >> 2;
-            const uint8_t *src = img + (size_t)f * frame_stride;
-            if (f + ncl < n_frames) { /* the next frame's band: on its way into L2 while this one is worked on */
-                const uint8_t *nsrc = src + (size_t)ncl * frame_stride + (size_t)R.s0 * step;
-                const size_t bytes = (size_t)(R.s1 - R.s0) * step + (size_t)L.w;
-                for (size_t o = (size_t)tid * 128; o < bytes; o += (size_t)PBD_NT * 128)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(nsrc + o));
-            }
-            uint8_t *const plane = frame + L.off;
-            for (int r = R.s0 + warp; r <= R.s1; r += PBD_NT / 32) {
-                const uint8_t *srow = src + (size_t)r * step;
-                uint32_t *drow = reinterpret_cast<uint32_t *>(buf + (r - R.s0) * pitch);
-                const uintptr_t a0 = reinterpret_cast<uintptr_t>(srow);
-                const int ph = (int)(a0 & 3);
-                const uint32_t *base = reinterpret_cast<const uint32_t *>(a0 - ph);
-                const bool own = r >= R.a && r < R.b;
-                const int mt = own ? pbd_mirror_top(r) : -1, mb = own ? pbd_mirror_bot(r, L.h) : -1;
-                uint32_t *g0 = reinterpret_cast<uint32_t *>(plane + (size_t)(r + BORB_EDGE) * L.pitch + BORB_XPAD);
-                uint32_t *g1 = reinterpret_cast<uint32_t *>(plane + (size_t)max(mt, 0) * L.pitch + BORB_XPAD);
-                uint32_t *g2 = reinterpret_cast<uint32_t *>(plane + (size_t)max(mb, 0) * L.pitch + BORB_XPAD);
-                /* eight words per lane in flight: all loads of a pass are issued before the first store */
-                for (int wb = 0; wb < nw; wb += 256) {
-                    uint32_t lo[8], hi[8];
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        const int w = wb + 32 * q + lane;
-                        lo[q] = hi[q] = 0u;
-                        if (w < nw && 4 * w + 8 <= L.w) {
-                            lo[q] = __ldg(base + w);
-                            if (ph) hi[q] = __ldg(base + w + 1);
-                        }
-                    }
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        const int w = wb + 32 * q + lane;
-                        if (w >= nw) continue;
-                        uint32_t v = __funnelshift_r(lo[q], hi[q], 8 * ph);
-                        if (4 * w + 8 > L.w) { /* the row's last words: byte loads, nothing is read past the row */
-                            v = 0;
-#pragma unroll
-                            for (int b = 0; b < 4; ++b)
-                                if (4 * w + b < L.w) v |= (uint32_t)__ldg(srow + 4 * w + b) << (8 * b);
-                        }
-                        drow[w] = v;
-                        if (own) { /* the row's last word may hold frame columns: pbd_frame_words writes it again, complete */
-                            g0[w] = v;
-                            if (mt >= 0) g1[w] = v;
-                            if (mb >= 0) g2[w] = v;
-                        }
-                    }
-                }
-            }
-            __syncthreads();
-            PBD_T(0);
-            pbd_frame_words(L, R, buf, pitch, plane);
-            PBD_T(3);
-        }
-        for (int l = 1; l < nl; ++l) {
-            const BorbLevel &L = plan->lv[l];
-            const PyrBandRows R = bp.r[l][cta];
-            const uint32_t sbuf_s = smem_s + bp.buf_off[(l - 1) & 1];
-            unsigned char *const dbuf = pbd_smem + bp.buf_off[l & 1];
-            const int spitch = bp.spitch[l - 1], dpitch = bp.spitch[l], nrows = R.b - R.a;
-            const int2 *const rtl = rt + bp.rt_lvl[l];
-            uint8_t *const plane = frame + L.off;
-            /* work items: 32 adjacent word columns (a lane each) x one of G row groups, dealt to the warps; the host
-             * picks G per level so that the rounds come out even */
-            const int nwc = (L.w + 3) >> 2, ncb = (nwc + 31) >> 5, G = bp.groups[l];
-            for (int item = warp; item < ncb * G; item += PBD_NT / 32) {
-                const int g = item / ncb, col = (item - g * ncb) * 32 + lane;
-                const int j0 = g * nrows / G, j1 = (g + 1) * nrows / G;
-                if (col >= nwc || j0 >= j1) continue;
-                /* x taps of this word column: the 8 source bytes from sx[0] on hold all four pairs (host-checked) */
-                uint32_t aw[4], sel[4];
-                int sx0 = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int x = min(4 * col + k, L.w - 1);
-                    const int sx = tab_i[L.xofs_off + x];
-                    if (k == 0) sx0 = sx;
-                    const uint32_t d = (uint32_t)(sx - sx0);
-                    sel[k] = d | ((d + 1u) << 4);
-                    aw[k] = *reinterpret_cast<const uint32_t *>(tab_s + L.xa_off + 2 * x); /* a0 | a1 << 16 */
-                }
-                const uint32_t scol_s = sbuf_s + (uint32_t)(sx0 & ~3);
-                const uint32_t sh = 8u * (uint32_t)(sx0 & 3);
-                int rowB = -1;
-                uint32_t hB[4] = {0, 0, 0, 0};
-                unsigned char *dcol = dbuf + (R.a - R.s0) * dpitch + 4 * col;
-                uint8_t *gcol = plane + BORB_XPAD + 4 * col;
-/* horizontal sums (already >> 4, as the vertical pass uses them) of the lane's four columns in staged row `row` */
-#define PBD_HSUM(n, row)                                                                                  \
-    do {                                                                                                  \
-        uint32_t w0_, w1_, w2_;                                                                           \
-        const uint32_t a_ = scol_s + (uint32_t)((row) * spitch);                                          \
-        asm("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"            \
-            : "=r"(w0_), "=r"(w1_), "=r"(w2_) : "r"(a_));                                                 \
-        const uint32_t lo_ = __funnelshift_r(w0_, w1_, sh), hi_ = __funnelshift_r(w1_, w2_, sh);           \
-        _Pragma("unroll") for (int k = 0; k < 4; ++k) n[k] = __dp2a_lo(aw[k], __byte_perm(lo_, hi_, sel[k]), 0u) >> 4; \
-    } while (0)
-                for (int j = j0; j < j1; ++j) {
-                    const int2 e = rtl[j];
-                    const int sy0 = e.x & 0xffff, sy1 = e.x >> 16;
-                    const uint32_t b0 = (uint32_t)e.y << 16, b1 = (uint32_t)e.y & 0xffff0000u;
-                    /* the upper source row is new in every iteration (it grows with the output row); the lower one is
-                     * the previous iteration's upper one unless the source skipped a row */
-                    uint32_t n0[4], n1[4];
-                    if (sy0 == rowB) {
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) n0[k] = hB[k];
-                    } else PBD_HSUM(n0, sy0);
-                    PBD_HSUM(n1, sy1);
-                    uint32_t v = 0;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint32_t d = (__umulhi(b0, n0[k]) + __umulhi(b1, n1[k]) + 2u) >> 2;
-                        v |= d << (8 * k);
-                        hB[k] = n1[k];
-                    }
-                    rowB = sy1;
-                    *reinterpret_cast<uint32_t *>(dcol + j * dpitch) = v;
-                    {   /* the row's last word may hold frame columns: pbd_frame_words writes it again, complete; its
-                         * interior bytes must be in the plane BEFORE the cluster barrier (a neighbour's halo row) */
-                        const int r = R.a + j; /* warp-uniform */
-                        *reinterpret_cast<uint32_t *>(gcol + (size_t)(r + BORB_EDGE) * L.pitch) = v;
-                        const int mt = pbd_mirror_top(r), mb = pbd_mirror_bot(r, L.h);
-                        if (mt >= 0) *reinterpret_cast<uint32_t *>(gcol + (size_t)mt * L.pitch) = v;
-                        if (mb >= 0) *reinterpret_cast<uint32_t *>(gcol + (size_t)mb * L.pitch) = v;
-                    }
-                }
-#undef PBD_HSUM
-            }
-            __syncthreads();
-            PBD_T(2);
-            if (l + 1 < nl) /* every interior word of this CTA's band of level l is on its way to the plane */
-                asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-            pbd_frame_words(L, R, dbuf, dpitch, plane);
-            PBD_T(3);
-            if (l + 1 < nl) {
-                /* every band of level l is in the plane: fetch the rows the next level's band needs from the neighbours */
-                asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-                PBD_T(4);
-                const int nu = (L.w + 15) >> 4, nh = (R.a - R.s0) + (R.s1 - R.b + 1);
-                for (int j = warp; j < nh; j += PBD_NT / 32) {
-                    const int r = j < R.a - R.s0 ? R.s0 + j : R.b + (j - (R.a - R.s0));
-                    const uint4 *s = reinterpret_cast<const uint4 *>(plane + (size_t)(r + BORB_EDGE) * L.pitch + BORB_XPAD);
-                    uint4 *d = reinterpret_cast<uint4 *>(dbuf + (r - R.s0) * dpitch);
-                    for (int u = lane; u < nu; u += 32) d[u] = __ldcg(s + u);
-                }
-                __syncthreads(); /* the halo rows are in place for the next level */
-                PBD_T(5);
-            }
-        }
-#ifdef PBD_PROF
-        if (blockIdx.x == 0 && threadIdx.x == 0) pbd_prof[6] += 1;
-#endif
-        __syncthreads(); /* the next frame's level 0 overwrites a buffer that the last pbd_frame_words may still read */
-    }
-}
-
 #endif
