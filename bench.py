@@ -293,16 +293,37 @@ def stage_algorithmic_bytes(n_kp: float, n_cand: float) -> dict:
     }
 
 
+def ncu_entry(kernel: str, frames: int):
+    """the committed ncu --set full summary of `kernel` at this launch shape (profiles/r2_traffic.json, else
+    profiles/r1_traffic.json; written by tools/ncu_traffic.py), or None"""
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            e = json.loads((ROOT / "profiles" / name).read_text())[kernel]
+            if int(e["frames_per_launch"]) == frames:
+                return dict(e, source=f"profiles/{name}")
+        except Exception:
+            continue
+    return None
+
+
 def ncu_traffic(kernel: str, frames: int):
-    """dram bytes per launch of `kernel` from the committed ncu --set full capture, if it was taken at
-    this launch shape (profiles/r1_traffic.json, written by tools/ncu_traffic.py)."""
-    p = ROOT / "profiles" / "r1_traffic.json"
-    try:
-        t = json.loads(p.read_text())
-        e = t[kernel]
-        return float(e["dram_bytes"]) if int(e["frames_per_launch"]) == frames else None
-    except Exception:
-        return None
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture, if it was taken at this launch shape"""
+    e = ncu_entry(kernel, frames)
+    return float(e["dram_bytes"]) if e and "dram_bytes" in e else None
+
+
+def issue_roofline(kernel: str, frames: int, kernel_ms: float, sm_mhz: float, n_sm: int = 148) -> dict:
+    """The path is instruction-issue bound, not HBM bound: warp instructions of one launch (ncu: sm__inst_executed.sum of
+    the committed capture -- a property of the code and the input, not of the run) over the issue slots the launch had
+    LIVE (SMs x 4 schedulers x measured SM clock x event-timed duration)."""
+    e = ncu_entry(kernel, frames)
+    if not e or "warp_instructions" not in e or not sm_mhz or not kernel_ms:
+        return {"issue_frac": None}
+    slots = n_sm * 4 * sm_mhz * 1e6 * kernel_ms / 1e3
+    return {"issue_frac": float(e["warp_instructions"]) / slots, "warp_instructions_per_launch": float(e["warp_instructions"]),
+            "issue_slots_busy_pct_under_ncu": e.get("issue_slots_busy_pct"), "issue_source": e["source"],
+            "issue_how": "warp instructions per launch (ncu capture) / (148 SMs x 4 schedulers x SM clock sampled during the "
+                         "timed region x this run's event-timed kernel duration)"}
 
 
 def prestep_section(ORBextractor, synth, local, peak):
@@ -603,6 +624,96 @@ def matcher_section(ORBextractor, synth, local):
                                  "parity_check": "identical" if (np.array_equal(m, w) and nm == wnm and np.array_equal(pv, wpv)) else "MISMATCH"}
     except Exception as ex:
         out["initialisation"] = f"unavailable ({type(ex).__name__}: {ex})"
+    return out
+
+
+def bow_section(ORBextractor, synth, local):
+    """SURVEY.md 8(f)-4: Frame::ComputeBoW (src/Frame.cc:532-539 -> DBoW2 transform, levelsup 4) and
+    ORBmatcher::SearchByBoW(KeyFrame*, Frame&) (src/ORBmatcher.cc:195-351) on the device.  The reference's vocabulary
+    blob (ORBvoc.txt, k = 10, L = 6) is not in the reference tree: a SYNTHETIC vocabulary of the same shape
+    (tests/golden/make_vocabulary.py, k = 10, L = 5: 111 110 nodes -- L = 6 is 145 MB of text) in the reference's text
+    format.  Timed: the whole host calls, on a KITTI-shape frame whose descriptors are already on the device."""
+    import tempfile
+    sys.path.insert(0, str(ROOT / "tests" / "golden"))
+    import make_vocabulary
+    from orb_slam2_test_b200 import ORBVocabulary
+    out = {"reference": "src/Frame.cc:532-539, Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1270, src/ORBmatcher.cc:195-351",
+           "vocabulary": "synthetic, k = 10, L = 5, L1 scoring, TF-IDF weighting (the real ORBvoc.txt is absent from the reference tree)"}
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "voc.txt")
+        make_vocabulary.write_vocabulary(path, 10, 5, seed=5)
+        voc = ORBVocabulary(path, device=local)
+        ext = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        kk, kd = ext(synth.make_frame((ROWS, COLS), seed=81, frame=0))
+        kk, kd = kk.copy(), kd.copy()
+        fk, fd = ext(synth.make_frame((ROWS, COLS), seed=81, frame=1))
+        for _ in range(10):
+            bow = ext.compute_bow(voc)
+        ts = []
+        for _ in range(100):
+            t1 = time.perf_counter()
+            bow = ext.compute_bow(voc)
+            ts.append((time.perf_counter() - t1) * 1e6)
+        out["compute_bow"] = {"call_p50_us": float(np.percentile(ts, 50)), "features": int(len(fd)), "words": int(len(bow["word_id"])),
+                              "nodes": int(len(bow["node_id"]))}
+        rng = np.random.default_rng(81)
+        mp = (rng.random(len(kk)) < 0.7).astype(np.uint8)
+        kf = {"desc": kd, "angle": kk["angle"], "mp_flags": mp, "fv": voc.transform(kd, 4)}
+        for _ in range(10):
+            m, nm = ext.search_by_bow(kf, 0.7)
+        ts = []
+        for _ in range(100):
+            t1 = time.perf_counter()
+            m, nm = ext.search_by_bow(kf, 0.7)
+            ts.append((time.perf_counter() - t1) * 1e6)
+        out["search_by_bow"] = {"call_p50_us": float(np.percentile(ts, 50)), "nmatches": int(nm), "keyframe_map_points": int(mp.sum()),
+                                "nodes": int(len(kf["fv"]["node_id"])),
+                                "note": "levelsup 4 on this L = 5 tree groups the features under 10 nodes (up to 480 per node); the walk "
+                                        "inside a node is sequential, as in the reference"}
+        # the granularity of the real vocabulary (L = 6, levelsup 4 -> 100 nodes): levelsup 3 on this tree
+        kf3 = dict(kf, fv=voc.transform(kd, 3))
+        ext.compute_bow(voc, levelsup=3)
+        for _ in range(10):
+            m3, nm3 = ext.search_by_bow(kf3, 0.7)
+        ts = []
+        for _ in range(100):
+            t1 = time.perf_counter()
+            m3, nm3 = ext.search_by_bow(kf3, 0.7)
+            ts.append((time.perf_counter() - t1) * 1e6)
+        out["search_by_bow_100_nodes"] = {"call_p50_us": float(np.percentile(ts, 50)), "nmatches": int(nm3),
+                                          "nodes": int(len(kf3["fv"]["node_id"])), "levelsup": 3}
+        bow = ext.compute_bow(voc)
+        try:
+            from oracle import pyoracle
+            want = pyoracle.BowVocabulary(path)
+            tc = []
+            for _ in range(10):
+                t1 = time.perf_counter()
+                wb = want.transform(fd, 4)
+                tc.append((time.perf_counter() - t1) * 1e6)
+            out["compute_bow"]["cpu_p50_us_one_core"] = float(np.percentile(tc, 50))
+            same = all(np.array_equal(np.asarray(bow[k]).view(np.uint8), np.asarray(wb[k]).view(np.uint8)) for k in wb)
+            out["compute_bow"]["parity_check"] = "bit-exact" if same else "MISMATCH"
+            kfv = want.transform(kd, 4)
+            tc = []
+            for _ in range(10):
+                t1 = time.perf_counter()
+                w, wnm = want.search_by_bow(kk, kd, mp, fk, fd, 0.7, True, kf_fv=kfv, f_fv=wb)
+                tc.append((time.perf_counter() - t1) * 1e6)
+            out["search_by_bow"]["cpu_p50_us_one_core"] = float(np.percentile(tc, 50))
+            out["search_by_bow"]["parity_check"] = "identical" if (np.array_equal(m, w) and nm == wnm) else "MISMATCH"
+            wb3, kfv3 = want.transform(fd, 3), want.transform(kd, 3)
+            tc = []
+            for _ in range(10):
+                t1 = time.perf_counter()
+                w3, wnm3 = want.search_by_bow(kk, kd, mp, fk, fd, 0.7, True, kf_fv=kfv3, f_fv=wb3)
+                tc.append((time.perf_counter() - t1) * 1e6)
+            out["search_by_bow_100_nodes"]["cpu_p50_us_one_core"] = float(np.percentile(tc, 50))
+            out["search_by_bow_100_nodes"]["parity_check"] = "identical" if (np.array_equal(m3, w3) and nm3 == wnm3) else "MISMATCH"
+        except Exception as ex:
+            out["parity_check"] = f"unavailable ({type(ex).__name__}: {ex})"
+        ext.close()
+        voc.close()
     return out
 
 
@@ -930,7 +1041,7 @@ def run_ours(args, rank, world, local):
 
     # ---- single-frame latency through the host ABI (pageable input, like a cv::Mat) ----
     lat = {}
-    stereo = prestep = poststep = matcher = tum = None
+    stereo = prestep = poststep = matcher = tum = bow = None
     if rank == 0:
         one = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1, want_pyramid=False)
         img = batch[0].copy()
@@ -973,6 +1084,10 @@ def run_ours(args, rank, world, local):
         prestep = prestep_section(ORBextractor, synth, local, measured_peak()[0])
         poststep = poststep_section(ORBextractor, synth, local)
         matcher = matcher_section(ORBextractor, synth, local)
+        try:
+            bow = bow_section(ORBextractor, synth, local)
+        except Exception as ex:  # a reported side measurement, never the headline
+            bow = {"unavailable": f"{type(ex).__name__}: {ex}"}
         tum = tum_section(ORBextractor, synth, local)
 
     if rank != 0:
@@ -1032,7 +1147,8 @@ def run_ours(args, rank, world, local):
                      "stage_ms_per_launch": st, "stage_ms_last_timed_call": last_stage,
                      "stage_GBps": {k: stage_bytes[k] * F / (st[k] / 1e3) / 1e9 for k in st},
                      "path_achieved": algorithmic_bytes(n_kp) * value / world / 1e9,
-                     "path_frac": algorithmic_bytes(n_kp) * value / world / 1e9 / peak},
+                     "path_frac": algorithmic_bytes(n_kp) * value / world / 1e9 / peak,
+                     **issue_roofline(STAGE_KERNEL[dom], F, st[dom], clocks.get("sm_mhz") if isinstance(clocks, dict) else None)},
         "cpu_baseline": cpu,
         "kseq": kseq,
         "latency": lat,
@@ -1040,6 +1156,7 @@ def run_ours(args, rank, world, local):
         "prestep": prestep,
         "poststep": poststep,
         "matcher": matcher,
+        "bow": bow,
         "tum": tum,
         "keypoints_per_frame": n_kp, "candidates_per_frame": n_cand,
         "parity_check": parity,

@@ -55,6 +55,9 @@ struct BowState { /* per extractor handle, allocated by the first borb_compute_b
     size_t kf_cap = 0;
     uint8_t *d_kf = nullptr, *h_kf = nullptr;
     int *d_match = nullptr, *h_match = nullptr; /* [K + 4]: matches, then nmatches */
+    uint32_t *d_cache = nullptr; /* [kf_cap][BOW_K] candidate keys */
+    int *d_choice = nullptr;     /* [kf_cap] accepted list position per keyframe feature */
+    uint8_t *d_more = nullptr;
     uint8_t *d_bin = nullptr;
     int *d_hist = nullptr;
 };
@@ -62,7 +65,7 @@ struct BowState { /* per extractor handle, allocated by the first borb_compute_b
 static void bow_release(BowState *&b)
 {
     if (!b) return;
-    void *dev[] = {b->d_word, b->d_node, b->d_bstart, b->d_weight, b->d_out, b->d_kf, b->d_match, b->d_bin, b->d_hist};
+    void *dev[] = {b->d_word, b->d_node, b->d_bstart, b->d_weight, b->d_out, b->d_kf, b->d_match, b->d_bin, b->d_hist, b->d_cache, b->d_more, b->d_choice};
     for (void *p : dev) if (p) cudaFree(p);
     void *host[] = {b->h_out, b->h_kf, b->h_match};
     for (void *p : host) if (p) cudaFreeHost(p);
@@ -100,13 +103,14 @@ int bow_enqueue(const borb_vocabulary *voc, const uint8_t *d_desc, const int *n_
                                                       levelsup, d_word, d_node, d_weight)
     if (G == 8) B1(8); else if (G == 16) B1(16); else B1(32);
 #undef B1
-    const size_t smem = (size_t)bow_np2(cap) * 8;
+    const int dual = bow_np2(cap) <= 8192 ? 1 : 0; /* both key arrays in shared memory: one sorting pass */
+    const size_t smem = (size_t)bow_np2(cap) * 8 * (size_t)(1 + dual);
     if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_bow_assemble<<<1, BOW_ASM_NT, smem, st>>>(d_word, d_node, d_weight, n_p, n_val, cap, bow_flags(voc->scoring, voc->weighting),
                                                reinterpret_cast<uint32_t *>(d_out + S.word), reinterpret_cast<double *>(d_out + S.val),
                                                d_bstart, reinterpret_cast<uint32_t *>(d_out + S.node),
                                                reinterpret_cast<int *>(d_out + S.start), reinterpret_cast<uint32_t *>(d_out + S.feat),
-                                               reinterpret_cast<int *>(d_out + S.counts));
+                                               reinterpret_cast<int *>(d_out + S.counts), dual);
     CU(cudaGetLastError());
     return BORB_OK;
 }
@@ -406,14 +410,21 @@ int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, 
     CU(cudaSetDevice(cur->device));
     const size_t K = b->K;
     cudaStream_t st = cur->stream;
+    if (!b->on_host) return fail(BORB_ERR_STATE, "the frame's bow vectors are not on the host");
     if ((size_t)n > b->kf_cap || !b->d_kf) {
         const size_t c = (((size_t)std::max(n, 1) + 1023) / 1024) * 1024;
         CU(cudaStreamSynchronize(st));
         if (b->d_kf) cudaFree(b->d_kf);
         if (b->h_kf) cudaFreeHost(b->h_kf);
-        b->d_kf = b->h_kf = nullptr; b->kf_cap = 0;
-        CU(cudaMalloc(&b->d_kf, c * 49 + 16));
-        CU(cudaMallocHost(&b->h_kf, c * 49 + 16));
+        if (b->d_cache) cudaFree(b->d_cache);
+        if (b->d_more) cudaFree(b->d_more);
+        if (b->d_choice) cudaFree(b->d_choice);
+        b->d_kf = b->h_kf = nullptr; b->d_cache = nullptr; b->d_more = nullptr; b->d_choice = nullptr; b->kf_cap = 0;
+        CU(cudaMalloc(&b->d_choice, c * 4));
+        CU(cudaMalloc(&b->d_cache, c * BOW_K * 4));
+        CU(cudaMalloc(&b->d_more, c));
+        CU(cudaMalloc(&b->d_kf, c * 57 + 32));
+        CU(cudaMallocHost(&b->h_kf, c * 57 + 32));
         b->kf_cap = c;
     }
     if (!b->d_match) {
@@ -423,33 +434,59 @@ int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, 
         CU(cudaMalloc(&b->d_hist, MT_HISTO * 4));
     }
     const size_t c = b->kf_cap, un = (size_t)n;
-    /* [desc 32c][angle 4c][node 4c][feat 4c][start 4(c+1)][mp c] */
-    const size_t o_ang = 32 * c, o_node = 36 * c, o_feat = 40 * c, o_start = 44 * c, o_mp = 48 * c + 8;
+    /* [desc 32c][angle 4c][feat 4c][pos_node 4c][start 4(c+1) (+4)][node_f 8c][mp c] */
+    const size_t o_ang = 32 * c, o_feat = 36 * c, o_pn = 40 * c, o_start = 44 * c, o_nf = 48 * c + 8, o_mp = 56 * c + 8;
     uint8_t *hp = b->h_kf, *dp = b->d_kf;
     if (n) {
         std::memcpy(hp, kf->desc, un * 32);
         std::memcpy(hp + o_ang, kf->angle, un * 4);
         std::memcpy(hp + o_mp, kf->mp_flags, un);
     }
+    int max_nf = 0;
+    {   /* both feature vectors are sorted by node id: walk them in step, as the reference does (:219-338) */
+        const BowSlab S = bow_slab_layout(K);
+        const int *cnt = reinterpret_cast<const int *>(b->h_out + S.counts);
+        const uint32_t *fnode = reinterpret_cast<const uint32_t *>(b->h_out + S.node);
+        const int *fstart = reinterpret_cast<const int *>(b->h_out + S.start);
+        int *pn = reinterpret_cast<int *>(hp + o_pn), *nf = reinterpret_cast<int *>(hp + o_nf);
+        int fb = 0;
+        for (int a = 0; a < nn; ++a) {
+            if (kf->node_start[a] < 0 || kf->node_start[a + 1] < kf->node_start[a] || kf->node_start[a + 1] > nfeat)
+                return fail(BORB_ERR_ARG, "keyframe feature vector: node_start is not ascending");
+            while (fb < cnt[1] && fnode[fb] < kf->node_id[a]) ++fb;
+            const bool both = fb < cnt[1] && fnode[fb] == kf->node_id[a];
+            nf[2 * a] = both ? fstart[fb] : 0;
+            nf[2 * a + 1] = both ? fstart[fb + 1] : 0;
+            max_nf = std::max(max_nf, nf[2 * a + 1] - nf[2 * a]);
+            for (int p = kf->node_start[a]; p < kf->node_start[a + 1]; ++p) pn[p] = a;
+        }
+    }
     if (nn) {
-        std::memcpy(hp + o_node, kf->node_id, (size_t)nn * 4);
         std::memcpy(hp + o_start, kf->node_start, ((size_t)nn + 1) * 4);
         std::memcpy(hp + o_feat, kf->feat_idx, (size_t)nfeat * 4);
     }
-    CU(cudaMemcpyAsync(dp, hp, c * 49 + 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(dp, hp, c * 57 + 32, cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(b->d_match, 0xff, K * 4, st));
+    CU(cudaMemsetAsync(b->d_match + K, 0, 16, st));
     CU(cudaMemsetAsync(b->d_hist, 0, MT_HISTO * 4, st));
     const BowSlab S = bow_slab_layout(K);
     const size_t fo = (size_t)frame * K;
     const int check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
-    if (nn > 0)
-        k_bow_search<<<(nn + BOW_SEARCH_NT / 32 - 1) / (BOW_SEARCH_NT / 32), BOW_SEARCH_NT, 0, st>>>(
-            reinterpret_cast<const uint4 *>(dp), reinterpret_cast<const float *>(dp + o_ang), dp + o_mp,
-            reinterpret_cast<const uint32_t *>(dp + o_node), reinterpret_cast<const int *>(dp + o_start),
-            reinterpret_cast<const uint32_t *>(dp + o_feat), nn, reinterpret_cast<const uint4 *>(cur->d_out_desc + fo * 32),
-            cur->d_out_kp + fo, reinterpret_cast<const uint32_t *>(b->d_out + S.node), reinterpret_cast<const int *>(b->d_out + S.start),
-            reinterpret_cast<const uint32_t *>(b->d_out + S.feat), reinterpret_cast<const int *>(b->d_out + S.counts), nnratio,
-            check_ori, b->d_match, b->d_bin, b->d_hist);
+    if (nn > 0 && nfeat > 0) {
+        const uint4 *f_desc = reinterpret_cast<const uint4 *>(cur->d_out_desc + fo * 32);
+        const uint32_t *f_feat = reinterpret_cast<const uint32_t *>(b->d_out + S.feat);
+        const uint32_t *k_feat = reinterpret_cast<const uint32_t *>(dp + o_feat);
+        const int2 *node_f = reinterpret_cast<const int2 *>(dp + o_nf);
+        k_bow_candidates<<<(nfeat + BOW_CAND_NT / 32 - 1) / (BOW_CAND_NT / 32), BOW_CAND_NT, 0, st>>>(
+            reinterpret_cast<const uint4 *>(dp), dp + o_mp, k_feat, reinterpret_cast<const int *>(dp + o_pn), node_f, nfeat, f_desc,
+            f_feat, b->d_cache, b->d_more);
+        const int tw = (max_nf + 31) / 32 + 1;
+        const size_t smem = (size_t)(BOW_RES_NT / 32) * ((size_t)tw + 32 * (BOW_K + 1)) * 4;
+        k_bow_resolve<<<(nn + BOW_RES_NT / 32 - 1) / (BOW_RES_NT / 32), BOW_RES_NT, smem, st>>>(
+            reinterpret_cast<const uint4 *>(dp), reinterpret_cast<const float *>(dp + o_ang), k_feat,
+            reinterpret_cast<const int *>(dp + o_start), node_f, nn, f_desc, cur->d_out_kp + fo, f_feat, b->d_cache, b->d_more,
+            nnratio, check_ori, tw, b->d_choice, b->d_match, b->d_bin, b->d_hist, b->d_match + K + 1);
+    }
     k_bow_finish<<<1, 1024, 0, st>>>(cur->d_nout + frame, (int)K, check_ori, b->d_hist, b->d_bin, b->d_match, b->d_match + K);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(b->h_match, b->d_match, (K + 4) * 4, cudaMemcpyDeviceToHost, st));
@@ -461,6 +498,8 @@ int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, 
     std::memcpy(match, b->h_match, (size_t)nc * 4);
     if (n_cur) *n_cur = nc;
     if (nmatches) *nmatches = b->h_match[K];
+    cur->mt_rounds = 1;
+    cur->mt_rescans = b->h_match[K + 1]; /* borb_match_rounds: features that scanned their node again */
     return BORB_OK;
 }
 

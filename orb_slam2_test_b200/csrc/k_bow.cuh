@@ -23,10 +23,8 @@
  *                    does (TF-IDF / TF) or once (IDF / BINARY); then BowVector::normalize: the norm is summed
  *                    SEQUENTIALLY in word order by one thread, because that order is what the reference's
  *                    double rounding follows (L2: fma(v, v, norm), as the reference object contracts it).
- * B3 k_bow_search    a warp per keyframe node: the reference's loop over a node's keyframe features is
- *                    sequential (a frame feature matched by an earlier one is skipped, :243-244) but nodes are
- *                    independent (a feature belongs to one node); inside, lanes scan the frame features of the
- *                    node 32 at a time for the best and second-best distance.
+ * B3 k_bow_candidates / k_bow_resolve   SearchByBoW: the Hamming scans of all keyframe features in parallel, then a
+ *                    warp per node walks its features in the reference's order on the cached candidates, see there.
  * B4 k_bow_finish    orientation histogram -> three maxima (:1800-1843) -> removal, nmatches.
  */
 #ifndef K_BOW_CUH
@@ -115,6 +113,23 @@ __device__ __forceinline__ void bow_bitonic(unsigned long long *k, int np2)
     __syncthreads();
 }
 
+/* the same for two arrays at once: one barrier per stage serves both (the sorts are barrier-bound at these sizes) */
+__device__ __forceinline__ void bow_bitonic2(unsigned long long *k, unsigned long long *k2, int np2)
+{
+    for (int size = 2; size <= np2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (np2 >> 1); t += BOW_ASM_NT) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const unsigned long long a = k[lo], b = k[hi], c = k2[lo], d = k2[hi];
+                if ((a > b) == up) { k[lo] = b; k[hi] = a; }
+                if ((c > d) == up) { k2[lo] = d; k2[hi] = c; }
+            }
+        }
+    __syncthreads();
+}
+
 /* exclusive scan of one int per thread over the CTA (BOW_ASM_NT threads); *total = sum.  sw: 33 ints of shared memory */
 __device__ __forceinline__ int bow_block_exscan(int v, int *sw, int *total)
 {
@@ -179,7 +194,7 @@ k_bow_assemble(const int *__restrict__ word, const int *__restrict__ node, const
                const int *__restrict__ n_p, int n_val, int cap, unsigned flags, uint32_t *__restrict__ bow_word,
                double *__restrict__ bow_val, int *__restrict__ bow_start /* scratch [cap + 1] */,
                uint32_t *__restrict__ fv_node, int *__restrict__ fv_start, uint32_t *__restrict__ fv_feat,
-               int *__restrict__ counts)
+               int *__restrict__ counts, int dual /* shared memory holds both key arrays: one sorting pass */)
 {
     extern __shared__ __align__(16) unsigned long long bow_keys[];
     __shared__ int sw[33];
@@ -189,24 +204,30 @@ k_bow_assemble(const int *__restrict__ word, const int *__restrict__ node, const
     int np2 = BOW_ASM_NT;
     while (np2 < n) np2 <<= 1;
 
-    /* ---- FeatureVector: features grouped by node, node ids ascending (std::map order), features ascending ---- */
-    for (int t = tid; t < np2; t += BOW_ASM_NT)
-        bow_keys[t] = (t < n && weight[t] > 0.0) ? (((unsigned long long)(uint32_t)node[t] << 32) | (uint32_t)t) : ~0ull;
-    bow_bitonic(bow_keys, np2);
+    /* ---- FeatureVector: features grouped by node, node ids ascending (std::map order), features ascending;
+     *      BowVector: unique words ascending; value = the word's weight once per feature (or once) ---- */
+    unsigned long long *const wkeys = dual ? bow_keys + np2 : bow_keys;
+    for (int t = tid; t < np2; t += BOW_ASM_NT) {
+        const bool on = t < n && weight[t] > 0.0;
+        bow_keys[t] = on ? (((unsigned long long)(uint32_t)node[t] << 32) | (uint32_t)t) : ~0ull;
+        if (dual) wkeys[t] = on ? (((unsigned long long)(uint32_t)word[t] << 32) | (uint32_t)t) : ~0ull;
+    }
+    if (dual) bow_bitonic2(bow_keys, wkeys, np2);
+    else bow_bitonic(bow_keys, np2);
     const int n_nodes = bow_segments(bow_keys, np2, sw, fv_node, fv_start, fv_feat);
     __syncthreads();
-
-    /* ---- BowVector: unique words ascending; value = the word's weight once per feature (or once) ---- */
-    for (int t = tid; t < np2; t += BOW_ASM_NT)
-        bow_keys[t] = (t < n && weight[t] > 0.0) ? (((unsigned long long)(uint32_t)word[t] << 32) | (uint32_t)t) : ~0ull;
-    bow_bitonic(bow_keys, np2);
-    const int n_words = bow_segments(bow_keys, np2, sw, bow_word, bow_start, nullptr);
+    if (!dual) {
+        for (int t = tid; t < np2; t += BOW_ASM_NT)
+            bow_keys[t] = (t < n && weight[t] > 0.0) ? (((unsigned long long)(uint32_t)word[t] << 32) | (uint32_t)t) : ~0ull;
+        bow_bitonic(bow_keys, np2);
+    }
+    const int n_words = bow_segments(wkeys, np2, sw, bow_word, bow_start, nullptr);
     __syncthreads(); /* bow_start is complete (global memory, this CTA only) */
     const bool accumulate = flags & 1u;
     const unsigned norm_mode = (flags >> 1) & 3u;
     for (int u = tid; u < n_words; u += BOW_ASM_NT) {
         const int s = bow_start[u], c = bow_start[u + 1] - s;
-        const double w = weight[(uint32_t)bow_keys[s]];
+        const double w = weight[(uint32_t)wkeys[s]];
         double v = w;
         if (accumulate)
             for (int j = 1; j < c; ++j) v = __dadd_rn(v, w); /* addWeight: += in feature order */
@@ -215,7 +236,7 @@ k_bow_assemble(const int *__restrict__ word, const int *__restrict__ node, const
     }
     __syncthreads();
     if (norm_mode) { /* BowVector::normalize: the sum runs in word order */
-        double *vals = reinterpret_cast<double *>(bow_keys); /* the keys are dead */
+        double *vals = reinterpret_cast<double *>(bow_keys); /* the node keys are dead; the word keys have been read */
         for (int u = tid; u < n_words; u += BOW_ASM_NT) vals[u] = bow_val[u];
         __syncthreads();
         if (tid == 0) {
@@ -235,71 +256,175 @@ k_bow_assemble(const int *__restrict__ word, const int *__restrict__ node, const
     if (tid == 0) { counts[0] = n_words; counts[1] = n_nodes; }
 }
 
-/* ---- ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches), src/ORBmatcher.cc:195-351 ---- */
-#define BOW_SEARCH_NT 128
+/* ---- ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches), src/ORBmatcher.cc:195-351 ----
+ * Inside a node the reference loop is sequential in the keyframe feature: a frame feature matched by an earlier
+ * keyframe feature is skipped by every later one (:243-244); nodes are independent (a feature belongs to one node).
+ * Two kernels, as for the projection matchers (k_match.cuh):
+ *   B3a k_bow_candidates  a warp per keyframe feature, over the whole GPU: Hamming distance to every frame feature of
+ *       the same node, the BOW_K best (distance << 16 | position in the node's list) kept in ascending order -- one key
+ *       per lane, an insertion is one shuffle, one max and one min -- plus "there were more".  Nothing here depends on
+ *       other queries.
+ *   B3b k_bow_resolve     a warp per node walks its keyframe features IN ORDER: the first two cached candidates that no
+ *       earlier feature has taken are the reference's bestDist1 / bestDist2 (its `<` / `else if <` chain keeps the
+ *       first of equal distances: the smaller list position); a taken-bit per frame feature of the node lives in
+ *       shared memory; only a feature whose cached candidates are (all but at most one) taken AND that had more
+ *       scans the node again.  A step of the walk is a shared-memory lookup and a ballot, not a Hamming scan. */
+#define BOW_K 16
+#define BOW_CAND_NT 256
+#define BOW_RES_NT 128
+#define BOW_NOKEY 0xffffffffu
 
-/* match [kp_total] preset to -1, hist [MT_HISTO] preset to 0.  kf_mp: bit 0 = map point, bit 1 = isBad(). */
-__global__ void __launch_bounds__(BOW_SEARCH_NT)
-k_bow_search(const uint4 *__restrict__ kf_desc, const float *__restrict__ kf_angle, const uint8_t *__restrict__ kf_mp,
-             const uint32_t *__restrict__ kf_node, const int *__restrict__ kf_start, const uint32_t *__restrict__ kf_feat,
-             int kf_nodes, const uint4 *__restrict__ f_desc, const BorbKpRec *__restrict__ f_kp,
-             const uint32_t *__restrict__ f_node, const int *__restrict__ f_start, const uint32_t *__restrict__ f_feat,
-             const int *__restrict__ f_counts, float nnratio, int check_ori, int *match, uint8_t *__restrict__ bin_of,
-             int *__restrict__ hist)
+/* per keyframe list position p: pos_node [p] = its node's index in the keyframe's feature vector; per node:
+ * node_f [a] = (first, end) of the same node's list in the frame's feature vector, (0, 0) if the frame has none */
+__global__ void __launch_bounds__(BOW_CAND_NT)
+k_bow_candidates(const uint4 *__restrict__ kf_desc, const uint8_t *__restrict__ kf_mp, const uint32_t *__restrict__ kf_feat,
+                 const int *__restrict__ pos_node, const int2 *__restrict__ node_f, int n_pos,
+                 const uint4 *__restrict__ f_desc, const uint32_t *__restrict__ f_feat, uint32_t *__restrict__ cache,
+                 uint8_t *__restrict__ more)
 {
     const int lane = threadIdx.x & 31;
-    const int a = blockIdx.x * (BOW_SEARCH_NT / 32) + (threadIdx.x >> 5);
-    if (a >= kf_nodes) return;
-    int b;
-    {   /* the frame's list of the same node: both lists are sorted, the reference walks them in step (:219-338) */
-        const uint32_t want = kf_node[a];
-        int lo = 0, hi = f_counts[1];
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            if (f_node[mid] < want) lo = mid + 1;
-            else hi = mid;
-        }
-        if (lo >= f_counts[1] || f_node[lo] != want) return;
-        b = lo;
-    }
-    const int fs = f_start[b], fe = f_start[b + 1];
-    for (int ik = kf_start[a]; ik < kf_start[a + 1]; ++ik) {
-        const uint32_t rk = kf_feat[ik];
-        const uint32_t fl = kf_mp[rk];
-        if (!(fl & 1u) || (fl & 2u)) continue; /* no map point, or a bad one (:230-234) */
+    const int p = blockIdx.x * (BOW_CAND_NT / 32) + (threadIdx.x >> 5);
+    if (p >= n_pos) return; /* whole warp */
+    uint32_t T = BOW_NOKEY; /* lane l < BOW_K: the l-th best key so far */
+    int cnt = 0;
+    const uint32_t rk = kf_feat[p];
+    const uint32_t fl = kf_mp[rk];
+    if ((fl & 1u) && !(fl & 2u)) { /* a map point, and not a bad one (:230-234) */
+        const int2 nf = node_f[pos_node[p]];
         const uint4 d0 = kf_desc[2 * rk], d1 = kf_desc[2 * rk + 1];
-        uint32_t B1 = (256u << 16) | 0xffffu; /* best (distance, list position); 256 = none yet */
-        int B2 = 256;
-        for (int base = fs; base < fe; base += 32) {
+        for (int base = nf.x; base < nf.y; base += 32) {
             const int jf = base + lane;
-            uint32_t key = 0xffffffffu;
-            if (jf < fe) {
-                const uint32_t rf = f_feat[jf];
-                if (*(volatile int *)(match + rf) < 0) { /* not matched by an earlier keyframe feature (:243-244) */
-                    const int d = mt_hamming(d0, d1, f_desc + 2 * (size_t)rf);
-                    if (d < 256) key = ((uint32_t)d << 16) | (uint32_t)(jf - fs);
-                }
+            uint32_t key = BOW_NOKEY;
+            if (jf < nf.y) {
+                const int d = mt_hamming(d0, d1, f_desc + 2 * (size_t)f_feat[jf]);
+                if (d < 256) key = ((uint32_t)d << 16) | (uint32_t)(jf - nf.x); /* 256 never beats bestDist = 256 */
             }
-            const uint32_t m1 = __reduce_min_sync(0xffffffffu, key);
-            if (m1 == 0xffffffffu) continue;
-            const uint32_t m2 = __reduce_min_sync(0xffffffffu, key == m1 ? 0xffffffffu : key);
-            const int m2d = m2 == 0xffffffffu ? 256 : (int)(m2 >> 16);
-            if (m1 < B1) { B2 = min((int)(B1 >> 16), m2d); B1 = m1; }
-            else B2 = min(B2, (int)(m1 >> 16));
-        }
-        const int best1 = (int)(B1 >> 16);
-        if (best1 <= BOW_TH_LOW && (float)best1 < nnratio * (float)B2) {
-            if (lane == 0) {
-                const uint32_t bi = f_feat[fs + (int)(B1 & 0xffffu)];
-                match[bi] = (int)rk;
-                if (check_ori) {
-                    const int bin = mt_bin(kf_angle[rk], f_kp[bi].angle);
-                    bin_of[bi] = (uint8_t)bin;
-                    atomicAdd(&hist[bin], 1);
-                }
+            cnt += __popc(__ballot_sync(0xffffffffu, key != BOW_NOKEY));
+            while (true) { /* move this chunk's keys that beat the cached worst into the sorted cache */
+                const uint32_t m = __reduce_min_sync(0xffffffffu, key);
+                if (m >= __shfl_sync(0xffffffffu, T, BOW_K - 1)) break;
+                if (key == m) key = BOW_NOKEY;
+                const uint32_t up = __shfl_up_sync(0xffffffffu, T, 1);
+                T = min(T, max(m, lane ? up : 0u));
             }
         }
-        __syncwarp(); /* lane 0's match[] write is visible to the warp's next scan */
+    }
+    if (lane < BOW_K) cache[(size_t)p * BOW_K + lane] = T;
+    if (lane == 0) more[p] = cnt > BOW_K;
+}
+
+/* match [kp_total] preset to -1, hist [MT_HISTO] preset to 0.  Dynamic shared memory: taken bits (tw words per warp),
+ * then a 32 x (BOW_K + 1) tile of cached keys per warp. */
+__global__ void __launch_bounds__(BOW_RES_NT)
+k_bow_resolve(const uint4 *__restrict__ kf_desc, const float *__restrict__ kf_angle, const uint32_t *__restrict__ kf_feat,
+              const int *__restrict__ kf_start, const int2 *__restrict__ node_f, int kf_nodes,
+              const uint4 *__restrict__ f_desc, const BorbKpRec *__restrict__ f_kp, const uint32_t *__restrict__ f_feat,
+              const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more, float nnratio, int check_ori, int tw,
+              int *choice /* scratch, one per keyframe list position */, int *__restrict__ match, uint8_t *__restrict__ bin_of, int *__restrict__ hist, int *__restrict__ rescans)
+{
+    extern __shared__ uint32_t bow_taken[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int a = blockIdx.x * (BOW_RES_NT / 32) + warp;
+    if (a >= kf_nodes) return; /* whole warp */
+    uint32_t *taken = bow_taken + warp * tw;
+    const int2 nf = node_f[a];
+    const int fs = nf.x, fe = nf.y;
+    if (fe <= fs) return;
+    for (int i = lane; i < ((fe - fs + 31) >> 5); i += 32) taken[i] = 0u;
+    __syncwarp();
+    const int ks = kf_start[a], ke = kf_start[a + 1];
+    /* The walk, 32 features at a time: lane j holds feature p0 + j's cached keys in registers and a mask of the ones
+     * still open, and the decision those give (first two open keys); step j broadcasts lane j's decision, an accepted
+     * position is struck from every lane's mask and only a lane that lost an open key decides again -- the serial
+     * chain of a step is one shuffle.  Taken bits also go to shared memory, for the next block's masks and for the rare full scan. */
+    uint32_t *tile = bow_taken + (BOW_RES_NT / 32) * tw + warp * (32 * (BOW_K + 1));
+    for (int p0 = ks; p0 < ke; p0 += 32) {
+        const int nsteps = min(32, ke - p0);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < BOW_K; ++i) { /* all loads of the block in flight at once; rows padded to BOW_K + 1 words */
+            const int row = 2 * i + (lane >> 4);
+            tile[row * (BOW_K + 1) + (lane & 15)] = row < nsteps ? cache[(size_t)(p0 + row) * BOW_K + (lane & 15)] : BOW_NOKEY;
+        }
+        const int mo = lane < nsteps ? more[p0 + lane] : 0;
+        __syncwarp();
+        uint32_t K[BOW_K], mask = 0u;
+#pragma unroll
+        for (int k = 0; k < BOW_K; ++k) {
+            K[k] = tile[lane * (BOW_K + 1) + k];
+            if (K[k] != BOW_NOKEY && !((taken[(K[k] & 0xffffu) >> 5] >> (K[k] & 31u)) & 1u)) mask |= 1u << k;
+        }
+        /* every lane keeps the decision its feature would take with its current mask (position, -1 none, -2 "scan the
+         * node again"): a step is then one shuffle, and only a lane that loses an open key decides again */
+#define BOW_DECIDE()                                                                                          \
+    do {                                                                                                      \
+        dec = -1;                                                                                             \
+        if (K[0] != BOW_NOKEY) { /* else: no map point, or no candidate */                                    \
+            if (__popc(mask) >= 2 || !mo) { /* the cached order is (distance, list position): first two open keys */ \
+                if (mask) {                                                                                   \
+                    const uint32_t k1 = tile[lane * (BOW_K + 1) + __ffs(mask) - 1];                            \
+                    const uint32_t m2 = mask & (mask - 1u);                                                   \
+                    const int best2 = m2 ? (int)(tile[lane * (BOW_K + 1) + __ffs(m2) - 1] >> 16) : 256;        \
+                    const int best1 = (int)(k1 >> 16);                                                        \
+                    if (best1 <= BOW_TH_LOW && (float)best1 < nnratio * (float)best2) dec = (int)(k1 & 0xffffu); \
+                }                                                                                             \
+            } else dec = -2; /* fewer than two open among the cached ones and there were more */              \
+        }                                                                                                     \
+    } while (0)
+        int mypos = -1, dec;
+        BOW_DECIDE();
+        for (int j = 0; j < nsteps; ++j) {
+            int pos = __shfl_sync(0xffffffffu, dec, j);
+            if (pos == -2) { /* scan the node again, all lanes */
+                __syncwarp(); /* this block's taken bits */
+                if (lane == 0) atomicAdd(rescans, 1);
+                const uint32_t rk = kf_feat[p0 + j];
+                const uint4 d0 = kf_desc[2 * rk], d1 = kf_desc[2 * rk + 1];
+                uint32_t B1 = (256u << 16) | 0xffffu;
+                int best2 = 256;
+                for (int base = fs; base < fe; base += 32) {
+                    const int jf = base + lane;
+                    uint32_t k = BOW_NOKEY;
+                    if (jf < fe && !((taken[(jf - fs) >> 5] >> ((jf - fs) & 31)) & 1u)) {
+                        const int d = mt_hamming(d0, d1, f_desc + 2 * (size_t)f_feat[jf]);
+                        if (d < 256) k = ((uint32_t)d << 16) | (uint32_t)(jf - fs);
+                    }
+                    const uint32_t m1 = __reduce_min_sync(0xffffffffu, k);
+                    if (m1 == BOW_NOKEY) continue;
+                    const uint32_t m2 = __reduce_min_sync(0xffffffffu, k == m1 ? BOW_NOKEY : k);
+                    const int m2d = m2 == BOW_NOKEY ? 256 : (int)(m2 >> 16);
+                    if (m1 < B1) { best2 = min((int)(B1 >> 16), m2d); B1 = m1; }
+                    else best2 = min(best2, (int)(m1 >> 16));
+                }
+                const int best1 = (int)(B1 >> 16);
+                pos = (best1 <= BOW_TH_LOW && (float)best1 < nnratio * (float)best2) ? (int)(B1 & 0xffffu) : -1;
+            }
+            if (pos >= 0) {
+                if (lane == j) {
+                    mypos = pos;
+                    taken[pos >> 5] |= 1u << (pos & 31);
+                }
+                const uint32_t before = mask;
+#pragma unroll
+                for (int k = 0; k < BOW_K; ++k)
+                    if ((K[k] & 0xffffu) == (uint32_t)pos) mask &= ~(1u << k);
+                if (mask != before && lane > j) BOW_DECIDE();
+            }
+        }
+#undef BOW_DECIDE
+        if (lane < nsteps) choice[p0 + lane] = mypos;
+    }
+    __syncwarp();
+    for (int p = ks + lane; p < ke; p += 32) {
+        const int pos = choice[p];
+        if (pos < 0) continue;
+        const uint32_t rk = kf_feat[p], bi = f_feat[fs + pos];
+        match[bi] = (int)rk;
+        if (check_ori) {
+            const int bin = mt_bin(kf_angle[rk], f_kp[bi].angle);
+            bin_of[bi] = (uint8_t)bin;
+            atomicAdd(&hist[bin], 1);
+        }
     }
 }
 
