@@ -238,4 +238,83 @@ int ORBextractor::SearchForInitialization(const std::vector<cv::KeyPoint> &F1Key
     return nmatches;
 }
 
+namespace {
+
+void fill_maps(const uint32_t *wid, const double *wval, int nw, const uint32_t *nid, const int32_t *nstart, const uint32_t *fidx,
+               int nn, std::map<unsigned int, double> &bowVec, std::map<unsigned int, std::vector<unsigned int> > &featVec)
+{
+    bowVec.clear();
+    featVec.clear();
+    for (int i = 0; i < nw; ++i) bowVec.insert(bowVec.end(), std::make_pair((unsigned int)wid[i], wval[i])); /* ascending ids */
+    for (int u = 0; u < nn; ++u)
+        featVec.insert(featVec.end(), std::make_pair((unsigned int)nid[u], std::vector<unsigned int>(fidx + nstart[u], fidx + nstart[u + 1])));
+}
+
+} // namespace
+
+DeviceVocabulary::DeviceVocabulary(const std::string &strVocFile, int device) : voc(NULL)
+{
+    check(borb_voc_load_text(strVocFile.c_str(), device, &voc), "vocabulary");
+}
+
+DeviceVocabulary::~DeviceVocabulary() { borb_voc_destroy(voc); }
+
+void DeviceVocabulary::transform(const cv::Mat &descriptors, std::map<unsigned int, double> &bowVec,
+                                 std::map<unsigned int, std::vector<unsigned int> > &featVec, int levelsup)
+{
+    const int n = descriptors.rows;
+    assert(n == 0 || descriptors.cols == 32);
+    std::vector<unsigned char> d((size_t)32 * n);
+    for (int i = 0; i < n; ++i) memcpy(&d[(size_t)32 * i], descriptors.ptr(i), 32);
+    std::vector<uint32_t> wid((size_t)n + 1), nid((size_t)n + 1), fidx((size_t)n + 1);
+    std::vector<double> wval((size_t)n + 1);
+    std::vector<int32_t> nstart((size_t)n + 2);
+    int nw = 0, nn = 0;
+    check(borb_voc_transform(voc, d.data(), n, levelsup, wid.data(), wval.data(), &nw, nid.data(), nstart.data(), fidx.data(), &nn),
+          "vocabulary transform");
+    fill_maps(wid.data(), wval.data(), nw, nid.data(), nstart.data(), fidx.data(), nn, bowVec, featVec);
+}
+
+void ORBextractor::ComputeBoW(DeviceVocabulary &voc, std::map<unsigned int, double> &mBowVec,
+                              std::map<unsigned int, std::vector<unsigned int> > &mFeatVec, int levelsup)
+{
+    check(borb_compute_bow(handle, 0, voc.get(), levelsup), "compute bow");
+    const uint32_t *wid = NULL, *nid = NULL, *fidx = NULL;
+    const double *wval = NULL;
+    const int32_t *nstart = NULL;
+    int nw = 0, nn = 0;
+    check(borb_bow_result(handle, 0, &wid, &wval, &nw, &nid, &nstart, &fidx, &nn), "bow result");
+    fill_maps(wid, wval, nw, nid, nstart, fidx, nn, mBowVec, mFeatVec);
+}
+
+int ORBextractor::SearchByBoW(const cv::Mat &kfDescriptors, const std::vector<cv::KeyPoint> &kfKeysUn,
+                              const unsigned char *kfMapPointFlags, const std::map<unsigned int, std::vector<unsigned int> > &kfFeatVec,
+                              float nnRatio, bool checkOrientation, std::vector<int> &vnMatches)
+{
+    const int n = (int)kfKeysUn.size();
+    assert(kfDescriptors.rows == n && (n == 0 || kfDescriptors.cols == 32));
+    std::vector<unsigned char> desc((size_t)32 * n);
+    std::vector<float> angle((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        memcpy(&desc[(size_t)32 * i], kfDescriptors.ptr(i), 32);
+        angle[i] = kfKeysUn[i].angle;
+    }
+    std::vector<uint32_t> nid, fidx;
+    std::vector<int32_t> nstart(1, 0);
+    for (std::map<unsigned int, std::vector<unsigned int> >::const_iterator it = kfFeatVec.begin(); it != kfFeatVec.end(); ++it) {
+        nid.push_back(it->first);
+        fidx.insert(fidx.end(), it->second.begin(), it->second.end());
+        nstart.push_back((int32_t)fidx.size());
+    }
+    borb_keyframe kf;
+    kf.n = n; kf.desc = desc.data(); kf.angle = angle.data(); kf.mp_flags = kfMapPointFlags;
+    kf.n_nodes = (int)nid.size(); kf.node_id = nid.data(); kf.node_start = nstart.data(); kf.feat_idx = fidx.data();
+    vnMatches.assign((size_t)borb_max_keypoints(handle), -1);
+    int nc = 0, nmatches = 0;
+    check(borb_search_by_bow(handle, 0, &kf, nnRatio, checkOrientation ? 0u : BORB_MATCH_NO_ORIENTATION, vnMatches.data(), &nc, &nmatches),
+          "search by bow");
+    vnMatches.resize((size_t)nc);
+    return nmatches;
+}
+
 } // namespace ORB_SLAM2

@@ -23,11 +23,14 @@
 #define ORBEXTRACTOR_H
 
 #include <list>
+#include <map>
+#include <string>
 #include <vector>
 
 #include <opencv2/core/core.hpp>
 
 struct borb_extractor;
+struct borb_vocabulary;
 
 namespace ORB_SLAM2
 {
@@ -43,6 +46,28 @@ public:
     cv::Point2i UL, UR, BL, BR;
     std::list<ExtractorNode>::iterator lit;
     bool bNoMore;
+};
+
+// Device copy of the vocabulary (extension).  The reference's ORBVocabulary (include/ORBVocabulary.h, DBoW2's
+// TemplatedVocabulary<FORB::TDescriptor, FORB>) stays what System owns and KeyFrameDatabase scores with; this class holds
+// the same tree on the GPU for the per-frame transform: construct it from the text file System::System loads with
+// mpVocabulary->loadFromTextFile(strVocFile) (reference src/System.cc), once, next to that call.
+class DeviceVocabulary
+{
+public:
+    explicit DeviceVocabulary(const std::string &strVocFile, int device = -1);
+    ~DeviceVocabulary();
+    // transform(features, BowVector, FeatureVector, levelsup) for descriptors in host memory (KeyFrame::ComputeBoW on a
+    // keyframe no extractor holds); DBoW2::BowVector IS-A std::map<unsigned int, double> and DBoW2::FeatureVector IS-A
+    // std::map<unsigned int, std::vector<unsigned int> >, so mBowVec / mFeatVec bind to these references directly
+    void transform(const cv::Mat &descriptors, std::map<unsigned int, double> &bowVec,
+                   std::map<unsigned int, std::vector<unsigned int> > &featVec, int levelsup = 4);
+    borb_vocabulary *get() const { return voc; }
+
+private:
+    DeviceVocabulary(const DeviceVocabulary &);
+    DeviceVocabulary &operator=(const DeviceVocabulary &);
+    borb_vocabulary *voc;
 };
 
 class ORBextractor
@@ -132,6 +157,20 @@ public:
     int SearchForInitialization(const std::vector<cv::KeyPoint> &F1KeysUn, const cv::Mat &F1Descriptors,
                                 std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12, int windowSize,
                                 float nnRatio, bool checkOrientation);
+
+    // Frame::ComputeBoW (reference src/Frame.cc:532-539: mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4))
+    // on the device, from the descriptors the last operator() call left there; fills the frame's mBowVec / mFeatVec
+    // with the reference's values bit for bit.
+    void ComputeBoW(DeviceVocabulary &voc, std::map<unsigned int, double> &mBowVec,
+                    std::map<unsigned int, std::vector<unsigned int> > &mFeatVec, int levelsup = 4);
+    // ORBmatcher::SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (reference
+    // src/ORBmatcher.cc:195-351) on the device, *this = F's extractor after ComputeBoW.  The keyframe arrives as
+    // pKF->mDescriptors, pKF->mvKeysUn, pKF->mFeatVec and one flag byte per keypoint (bit 0: GetMapPointMatches()[i] !=
+    // NULL, bit 1: that point isBad()).  vnMatches[iF] = index of the keyframe keypoint whose map point F's keypoint iF
+    // receives, or -1; returns nmatches.
+    int SearchByBoW(const cv::Mat &kfDescriptors, const std::vector<cv::KeyPoint> &kfKeysUn, const unsigned char *kfMapPointFlags,
+                    const std::map<unsigned int, std::vector<unsigned int> > &kfFeatVec, float nnRatio, bool checkOrientation,
+                    std::vector<int> &vnMatches);
 
 protected:
     int nfeatures;

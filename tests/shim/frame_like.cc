@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <chrono>
 #include <thread>
+#include <map>
 #include <vector>
 
 #include "ORBextractor.h"
@@ -283,8 +284,68 @@ static int init_mode(char **argv)
     return 0;
 }
 
+/* `bow` mode: Frame::ComputeBoW and ORBmatcher::SearchByBoW(KeyFrame*, Frame&) through the shim (reference
+ * src/Frame.cc:532-539, src/ORBmatcher.cc:195-351).  argv: bow image cols rows nfeatures vocabulary.txt kf.bin out.bin;
+ * kf.bin = int32 n, float nnratio, then angle[n], desc[32n], flags[n] of the keyframe.  out.bin = int32 nmatches, nF,
+ * words, nodes, entries; vnMatches[nF]; word ids [words] (u32), values [words] (f64); node ids [nodes], node sizes [nodes],
+ * feature indices [entries] of the FRAME's mBowVec / mFeatVec; then the same five arrays of the keyframe's. */
+static void dump_bow(FILE *f, const std::map<unsigned int, double> &bow, const std::map<unsigned int, std::vector<unsigned int> > &fv)
+{
+    int words = (int)bow.size(), nodes = (int)fv.size(), entries = 0;
+    for (std::map<unsigned int, std::vector<unsigned int> >::const_iterator it = fv.begin(); it != fv.end(); ++it) entries += (int)it->second.size();
+    fwrite(&words, 4, 1, f); fwrite(&nodes, 4, 1, f); fwrite(&entries, 4, 1, f);
+    for (std::map<unsigned int, double>::const_iterator it = bow.begin(); it != bow.end(); ++it) fwrite(&it->first, 4, 1, f);
+    for (std::map<unsigned int, double>::const_iterator it = bow.begin(); it != bow.end(); ++it) fwrite(&it->second, 8, 1, f);
+    for (std::map<unsigned int, std::vector<unsigned int> >::const_iterator it = fv.begin(); it != fv.end(); ++it) fwrite(&it->first, 4, 1, f);
+    for (std::map<unsigned int, std::vector<unsigned int> >::const_iterator it = fv.begin(); it != fv.end(); ++it) { int c = (int)it->second.size(); fwrite(&c, 4, 1, f); }
+    for (std::map<unsigned int, std::vector<unsigned int> >::const_iterator it = fv.begin(); it != fv.end(); ++it) fwrite(it->second.data(), 4, it->second.size(), f);
+}
+
+static int bow_mode(char **argv)
+{
+    const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[5]);
+    vector<unsigned char> im = slurp(argv[2], (size_t)cols * rows);
+    cv::Mat image(rows, cols, CV_8UC1, im.data());
+    FILE *in = fopen(argv[7], "rb");
+    if (!in) return 2;
+    int n = 0;
+    float ratio = 0.f;
+    if (fread(&n, 4, 1, in) != 1 || fread(&ratio, 4, 1, in) != 1) return 2;
+    vector<cv::KeyPoint> kfKeysUn((size_t)n);
+    vector<float> angle((size_t)n);
+    vector<unsigned char> flags((size_t)n);
+    cv::Mat kfDesc(n, 32, CV_8UC1);
+    if (fread(angle.data(), 4, (size_t)n, in) != (size_t)n) return 2;
+    for (int i = 0; i < n; ++i) { if (fread(kfDesc.ptr(i), 1, 32, in) != 32) return 2; kfKeysUn[i].angle = angle[i]; }
+    if (fread(flags.data(), 1, (size_t)n, in) != (size_t)n) return 2;
+    fclose(in);
+    DeviceVocabulary voc(argv[6]);                       /* next to System's loadFromTextFile */
+    std::map<unsigned int, double> kfBow, mBowVec;       /* DBoW2::BowVector / FeatureVector derive from these */
+    std::map<unsigned int, std::vector<unsigned int> > kfFeatVec, mFeatVec;
+    voc.transform(kfDesc, kfBow, kfFeatVec, 4);          /* KeyFrame::ComputeBoW */
+    ORBextractor ext(nFeatures, 1.2f, 8, 20, 7);
+    vector<cv::KeyPoint> keys;
+    cv::Mat desc;
+    ext(image, cv::Mat(), keys, desc);
+    ext.ComputeBoW(voc, mBowVec, mFeatVec);              /* Frame::ComputeBoW */
+    vector<int> vnMatches;
+    const int nmatches = ext.SearchByBoW(kfDesc, kfKeysUn, flags.data(), kfFeatVec, ratio, true, vnMatches);
+    FILE *f = fopen(argv[8], "wb");
+    if (!f) return 2;
+    const int nF = (int)vnMatches.size();
+    fwrite(&nmatches, 4, 1, f);
+    fwrite(&nF, 4, 1, f);
+    fwrite(vnMatches.data(), 4, vnMatches.size(), f);
+    dump_bow(f, mBowVec, mFeatVec);
+    dump_bow(f, kfBow, kfFeatVec);
+    fclose(f);
+    printf("frame_like bow ok\n");
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
+    if (argc == 9 && !strcmp(argv[1], "bow")) return bow_mode(argv);
     if (argc == 8 && !strcmp(argv[1], "init")) return init_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "match")) return match_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "pre")) return pre_mode(argv);

@@ -230,3 +230,43 @@ def test_initialisation_matcher_through_the_shim(tmp_path, oracle_built):
     want, wprev, wnm = oracle_built.search_for_initialization(f1, f2, bounds, prev, 100, np.float32(0.9), True)
     assert nn == n and np.array_equal(got, want) and nm == wnm > 150
     assert np.array_equal(gprev.view(np.uint32), wprev.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_bag_of_words_through_the_shim(tmp_path, oracle_built):
+    """DeviceVocabulary / ORBextractor::ComputeBoW / ORBextractor::SearchByBoW (shim) = Frame::ComputeBoW (src/Frame.cc:532-539)
+    and ORBmatcher::SearchByBoW(KeyFrame*, Frame&) (src/ORBmatcher.cc:195-351) restated (pinned to the reference's own
+    DBoW2 + Frame.cc + ORBmatcher.cc): std::map contents identical, word values as float64 bit patterns."""
+    import bowcase
+    from oracle import pyoracle
+    _build()
+    path = bowcase.vocabulary(tmp_path, "k10L4")
+    want = pyoracle.BowVocabulary(path)
+    kk, kd = bowcase.frame_features(synth.TUM_SHAPE, 3, 0, 1000)
+    fk, fd = bowcase.frame_features(synth.TUM_SHAPE, 3, 1, 1000)
+    mp = bowcase.keyframe_flags(len(kk), 44)
+    (tmp_path / "cur.raw").write_bytes(synth.make_frame(synth.TUM_SHAPE, seed=3, frame=1).tobytes())
+    (tmp_path / "kf.bin").write_bytes(struct.pack("<if", len(kk), 0.7) + kk["angle"].astype("<f4").tobytes() + kd.tobytes() + mp.tobytes())
+    r = subprocess.run([str(EXE), "bow", str(tmp_path / "cur.raw"), "640", "480", "1000", path, str(tmp_path / "kf.bin"),
+                        str(tmp_path / "b.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = (tmp_path / "b.bin").read_bytes()
+    nm, nf = struct.unpack_from("<ii", buf, 0)
+    got = np.frombuffer(buf, "<i4", nf, 8)
+    off = 8 + 4 * nf
+
+    def read_bow(off):
+        words, nodes, entries = struct.unpack_from("<iii", buf, off)
+        off += 12
+        wid = np.frombuffer(buf, "<u4", words, off); off += 4 * words
+        wv = np.frombuffer(buf, "<f8", words, off); off += 8 * words
+        nid = np.frombuffer(buf, "<u4", nodes, off); off += 4 * nodes
+        cnt = np.frombuffer(buf, "<i4", nodes, off); off += 4 * nodes
+        fi = np.frombuffer(buf, "<u4", entries, off); off += 4 * entries
+        return {"word_id": wid, "word_val": wv, "node_id": nid, "node_start": np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32),
+                "feat_idx": fi}, off
+    fbow, off = read_bow(off)
+    kbow, off = read_bow(off)
+    assert bowcase.same_bow(fbow, want.transform(fd, 4)) and bowcase.same_bow(kbow, want.transform(kd, 4))
+    w, wnm = want.search_by_bow(kk, kd, mp, fk, fd, np.float32(0.7), True)
+    assert nf == len(w) and np.array_equal(got, w) and nm == wnm > 50

@@ -12,7 +12,7 @@ import sys
 
 WANT = {
     "dram__bytes_read.sum": "dram_read", "dram__bytes_write.sum": "dram_write",
-    "gpu__time_duration.sum": "duration", "sm__inst_executed.sum": "warp_instructions",
+    "gpu__time_duration.sum": "duration", "sm__inst_executed.sum": "warp_instructions", "smsp__inst_executed.sum": "warp_instructions",
     "sm__throughput.avg.pct_of_peak_sustained_elapsed": "sm_throughput_pct",
     "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": "dram_throughput_pct",
     "sm__warps_active.avg.pct_of_peak_sustained_active": "achieved_occupancy_pct",
