@@ -733,16 +733,17 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     }
     static const bool chain_off = getenv("BORB_PYR_LEVELS") != nullptr; /* A/B knob: per-level kernels in every shape */
     const bool chain = !chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm;
-    h->last_launches = (chain ? 1 : P.nlevels) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
+    h->last_launches = (chain ? 1 : P.nlevels + 1) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
     if (chain) {
         /* K1, latency shape: the whole chain in one launch */
         k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_chain_tabs, h->chain_tstride,
                                                                          dev_img, step, stride, d_pyr, h->chain_off_b, h->chain_off_t);
     } else {   /* K1 */
         const BorbLevel &L0 = P.lv[0];
-        const int units = L0.pitch / 16;
-        k_pyr_level0<<<dim3((units + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->plan, dev_img, step,
-                                                                                          stride, d_pyr);
+        const int units = L0.pitch / 16, n_int = L0.w / 16;
+        if (n_int > 0)
+            k_pyr_level0<true><<<dim3((n_int + 31) / 32, (L0.prows + 3) / 4, n), dim3(32, 4), 0, st>>>(h->plan, dev_img, step, stride, d_pyr);
+        k_pyr_level0<false><<<dim3((L0.prows + 127) / 128, units - n_int, n), dim3(32, 4), 0, st>>>(h->plan, dev_img, step, stride, d_pyr);
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);
@@ -766,8 +767,9 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     }
     {   /* K2: persistent CTAs walking (cell, frame) items, frames first (stride gridDim.y), then cells (stride
          * gridDim.x); small jobs get one CTA per (cell, frame) */
-        int per_sm = 256; /* far more CTAs than fit at once: the hardware scheduler evens out the uneven
-                             cells (measured: 12/SM 4.0 ms, 48/SM 3.5 ms, 400/SM 3.2 ms per 512 frames) */
+        int per_sm = 768; /* far more CTAs than fit at once: the hardware scheduler evens out the uneven cells.
+                             K2k, 512 frames, CTA rows per cell column (frames walked per CTA = 512 / rows): 29 rows 2.025 ms,
+                             64 1.996, 96 1.994, 128 2.005, 256 2.058, 512 (one frame per CTA) 2.190 */
         static const int env_per_sm = getenv("BORB_FAST_CTAS_PER_SM") ? atoi(getenv("BORB_FAST_CTAS_PER_SM")) : 0; /* tuning knobs, read once */
         static const int env_grid_y = getenv("BORB_FAST_GRID_Y") ? atoi(getenv("BORB_FAST_GRID_Y")) : 0;
         if (env_per_sm > 0) per_sm = env_per_sm;
@@ -777,7 +779,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             /* one CTA column per cell: a CTA keeps its cell and walks frames blockIdx.y, + gridDim.y, ... so that the
              * per-cell lane geometry is computed once per CTA (k_fast.cuh) */
             grid.x = std::min(P.n_cells, ctas);
-            grid.y = std::max(1, std::min(n, ctas / (int)grid.x));
+            grid.y = std::max(1, std::min(std::min(n, 96), ctas / (int)grid.x));
             if (env_grid_y > 0) grid.y = std::min(n, env_grid_y);
         }
 #define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->plan, h->d_cells, n, h->fast_maps, f0, \

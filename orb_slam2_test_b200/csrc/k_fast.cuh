@@ -376,14 +376,13 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
                 const uint32_t any_lo = (s_lo | (s_lo >> 1)) & 0x02000200u, any_hi = (s_hi | (s_hi >> 1)) & 0x02000200u;
                 const int c = __popc(any_lo | (any_hi >> 1));
                 if (__ballot_sync(0xffffffffu, c != 0) == 0u) continue;
-                int inc = c;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int up = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += up;
-                }
-                uint16_t *dst = list1 + n1 + inc - c;
-                n1 += __shfl_sync(0xffffffffu, inc, 31);
+                /* exclusive prefix of the per-lane counts (0 .. 4) from three ballots, one per bit of the count:
+                 * independent votes instead of a chain of five dependent shuffles */
+                const uint32_t v0 = __ballot_sync(0xffffffffu, c & 1), v1 = __ballot_sync(0xffffffffu, c & 2),
+                               v2 = __ballot_sync(0xffffffffu, c & 4);
+                const int before = __popc(v0 & below) + 2 * __popc(v1 & below) + 4 * __popc(v2 & below);
+                uint16_t *dst = list1 + n1 + before;
+                n1 += __popc(v0) + 2 * __popc(v1) + 4 * __popc(v2);
                 const uint32_t pixb = (uint32_t)((y << 6) + s1_col);
                 const uint32_t sd0 = (s_lo >> 9) & 3u, sd1 = (s_lo >> 25) & 3u, sd2 = (s_hi >> 9) & 3u, sd3 = (s_hi >> 25) & 3u;
                 if (sd0) *dst++ = (uint16_t)(pixb | (sd0 << 12));

@@ -40,24 +40,42 @@ __device__ __forceinline__ int reflect101(int i, int n)
 __host__ __device__ __forceinline__ int pyr_words_per_row(int w) { return (w + BORB_EDGE + PYR_LPAD + 3) >> 2; }
 
 /* level 0: copy of the input with the frame (src/ORBextractor.cc:1436-1439).  A thread writes 16
- * bytes (one aligned uint4) of a padded row; interior units read their 16 contiguous source
- * bytes, at whatever alignment the input's row step gives them, as 5 aligned words + funnel
- * shifts.  Grid: (units of 16 columns / 32, padded rows / 4, frames), block (32, 4). */
+ * bytes (one aligned uint4) of a padded row.  Two launch shapes, so that no warp mixes the two paths (one launch for
+ * everything ran with 11 of 32 lanes active: the frame units' per-byte path diverged two of the three warps of a row):
+ *   INTERIOR  units that lie inside the image: the 16 contiguous source bytes, at whatever alignment the input's row
+ *             step gives them, as 5 aligned words + funnel shifts.  Grid (interior units / 32, padded rows / 4, frames),
+ *             block (32, 4).
+ *   FRAME     the units that hold frame columns (two on the left, the rest on the right), byte by byte at the
+ *             reflected coordinate; a warp = 32 consecutive padded ROWS of one such unit column.
+ *             Grid (padded rows / 128, frame units, frames), block (32, 4). */
+template <bool INTERIOR>
 __global__ void __launch_bounds__(PYR_NT)
 k_pyr_level0(const __grid_constant__ BorbPlan plan_c, const uint8_t *__restrict__ img, size_t step,
              size_t frame_stride, uint8_t *__restrict__ pyr)
 {
     const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     const BorbLevel &L = plan->lv[0];
-    const int r = blockIdx.y * 4 + threadIdx.y;           /* padded row */
-    const int c = (blockIdx.x * 32 + threadIdx.x) * 16 - BORB_XPAD; /* first of 16 level columns */
-    if (r >= L.prows || c + BORB_XPAD >= L.pitch) return; /* pitch is a multiple of 16: whole units */
+    const int n_int = L.w >> 4; /* units with 0 <= c and c + 15 < w */
+    int r, c;
+    if (INTERIOR) {
+        r = blockIdx.y * 4 + threadIdx.y;                  /* padded row */
+        const int u = blockIdx.x * 32 + threadIdx.x;
+        if (r >= L.prows || u >= n_int) return;
+        c = 16 * u;                                        /* first of 16 level columns */
+    } else {
+        r = (blockIdx.x * 4 + threadIdx.y) * 32 + threadIdx.x;
+        if (r >= L.prows) return;
+        const int e = blockIdx.y;                          /* frame unit: 0, 1 left of the image, then right of it */
+        c = e < 2 ? 16 * e - BORB_XPAD : 16 * (n_int + e - 2);
+    }
     const uint8_t *src = img + (size_t)blockIdx.z * frame_stride;
     uint8_t *dst = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes + L.off + (size_t)r * L.pitch + BORB_XPAD + c;
     const int y = reflect101(r - BORB_EDGE, L.h);
     const uint8_t *srow = src + (size_t)y * step;
     uint32_t v[4];
-    if (c >= 0 && c + 15 < L.w && y + 1 < L.h) {
+    /* the fifth word is read only when it holds bytes of this unit, so nothing is read past the word that holds the row's
+     * last needed byte; the image's very last row still takes the byte path (a checker would flag its last word) */
+    if (INTERIOR && (y + 1 < L.h || blockIdx.z + 1 < gridDim.z)) {
         const uintptr_t a = reinterpret_cast<uintptr_t>(srow + c);
         const uint32_t *base = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
         const uint32_t sh = (uint32_t)(a & 3) * 8u;
