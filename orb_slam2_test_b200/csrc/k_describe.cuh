@@ -255,11 +255,8 @@ k_orient_describe(const __grid_constant__ DescMaps dm, const signed char *__rest
             }
             m10 = ic_u * colsum;
         }
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) {
-            m10 += __shfl_xor_sync(0xffffffffu, m10, s);
-            m01 += __shfl_xor_sync(0xffffffffu, m01, s);
-        }
+        m10 = __reduce_add_sync(0xffffffffu, m10); /* integer sums: one REDUX each instead of a five-step butterfly */
+        m01 = __reduce_add_sync(0xffffffffu, m01);
         const float angle = fast_atan2_deg((float)m01, (float)m10);
 
         /* ---- K6 ---- */
