@@ -375,11 +375,11 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
                 /* flagged pixels of this lane (bit 9 = dark, bit 10 = bright, per field) */
                 const uint32_t any_lo = (s_lo | (s_lo >> 1)) & 0x02000200u, any_hi = (s_hi | (s_hi >> 1)) & 0x02000200u;
                 const int c = __popc(any_lo | (any_hi >> 1));
+                if (__ballot_sync(0xffffffffu, c != 0) == 0u) continue; /* (folding this vote into the three below: slower) */
                 /* exclusive prefix of the per-lane counts (0 .. 4) from three ballots, one per bit of the count:
                  * independent votes instead of a chain of five dependent shuffles */
                 const uint32_t v0 = __ballot_sync(0xffffffffu, c & 1), v1 = __ballot_sync(0xffffffffu, c & 2),
                                v2 = __ballot_sync(0xffffffffu, c & 4);
-                if ((v0 | v1 | v2) == 0u) continue;
                 const int before = __popc(v0 & below) + 2 * __popc(v1 & below) + 4 * __popc(v2 & below);
                 uint16_t *dst = list1 + n1 + before;
                 n1 += __popc(v0) + 2 * __popc(v1) + 4 * __popc(v2);
