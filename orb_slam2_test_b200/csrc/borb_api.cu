@@ -117,6 +117,7 @@ struct borb_extractor {
     bool have_plan = false;
     BorbPlan plan;
     int qt_M = 0;
+    int fast_smem4 = 0; /* K2 with four warps per cell (a frame or two per call) */
     int fast_smem = 0, n_sm = 148;
     int fast_wp = 64;                   /* staged window pitch of K2 = TMA box width */
     FastMaps fast_maps;                 /* one TMA descriptor per level, passed by value to K2 */
@@ -609,10 +610,14 @@ int build_plan(borb_extractor *h, int cols, int rows)
     CU(cudaMemset(h->d_pyr, 0, B * (size_t)P.pyr_bytes));
 
     h->fast_wp = FAST_WP_FOR(P.fast_max_ww);
-    h->fast_smem = fast_smem_layout(P.fast_max_wh, P.fast_max_pix, h->fast_wp).bytes;
-        CU(cudaFuncSetAttribute(k_fast_cells<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
-    CU(cudaFuncSetAttribute(k_fast_cells<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
-    CU(cudaFuncSetAttribute(k_fast_cells<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    h->fast_smem = fast_smem_layout(P.fast_max_wh, P.fast_max_pix, h->fast_wp, 2).bytes;
+    h->fast_smem4 = fast_smem_layout(P.fast_max_wh, P.fast_max_pix, h->fast_wp, 4).bytes;
+    CU(cudaFuncSetAttribute(k_fast_cells<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    CU(cudaFuncSetAttribute(k_fast_cells<80, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    CU(cudaFuncSetAttribute(k_fast_cells<96, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem));
+    CU(cudaFuncSetAttribute(k_fast_cells<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem4));
+    CU(cudaFuncSetAttribute(k_fast_cells<80, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem4));
+    CU(cudaFuncSetAttribute(k_fast_cells<96, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fast_smem4));
     {   /* TMA descriptors of K2's window loads: one 3-D map (column bytes, rows, frames) per padded
          * level plane; box = fast_wp bytes x fast_max_wh rows x 1 frame */
         typedef CUresult (*EncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -782,9 +787,13 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             grid.y = std::max(1, std::min(std::min(n, 96), ctas / (int)grid.x));
             if (env_grid_y > 0) grid.y = std::min(n, env_grid_y);
         }
-#define K2(WP) k_fast_cells<WP><<<grid, FAST_NT, h->fast_smem, st>>>(h->plan, h->d_cells, n, h->fast_maps, f0, \
-                                                                   d_cand_xy, d_cand_score, d_ncand)
-        if (h->fast_wp == 64) K2(64); else if (h->fast_wp == 80) K2(80); else K2(96);
+        /* a frame or two: one CTA per (cell, frame), and the time is a cell's dependent chain -> four warps per cell */
+        static const bool env_nw2 = getenv("BORB_FAST_NW2") != nullptr; /* A/B knob: two warps per cell in every shape */
+        const bool four = !env_nw2 && (long long)P.n_cells * n <= 2LL * h->n_sm * 16;
+#define K2(WP, NW) k_fast_cells<WP, NW><<<grid, 32 * NW, NW == 4 ? h->fast_smem4 : h->fast_smem, st>>>(                   \
+        h->plan, h->d_cells, n, h->fast_maps, f0, d_cand_xy, d_cand_score, d_ncand)
+        if (four) { if (h->fast_wp == 64) K2(64, 4); else if (h->fast_wp == 80) K2(80, 4); else K2(96, 4); }
+        else { if (h->fast_wp == 64) K2(64, 2); else if (h->fast_wp == 80) K2(80, 2); else K2(96, 2); }
 #undef K2
     }
     STAGE(2);

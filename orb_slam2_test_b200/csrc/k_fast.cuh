@@ -39,9 +39,7 @@
 
 #include "borb_internal.h"
 
-#ifndef FAST_NT
-#define FAST_NT 64 /* 2 warps per cell: measured best of 64/128/256 on B200 */
-#endif
+
 /* staged window row pitch WP (template parameter of the kernel) = width of the TMA box.  A box must
  * start on a 16-byte boundary of the plane row (measured: any other start coordinate faults), so the
  * detection domain begins at byte 4..19 of a staged row; WP is the smallest of 64 / 80 / 96 that
@@ -168,22 +166,21 @@ __device__ __forceinline__ uint32_t fast_arc_minmax3_x2(const uint32_t *P)
 
 /* Shared memory of one CTA, sized on the host for the largest cell of the plan (K2k: 33x40 px ->
  * 18 KB; the 60x60 worst case of the cell formula needs 44 KB).  chunk = pixels per warp. */
-#define FAST_NW (FAST_NT / 32)
 struct FastSmemLayout {
     int chunk, win_off, win_bytes, sc_off, l1_off, l2_off, l3_off, bytes;
 };
-__host__ __device__ __forceinline__ int fast_chunk(int npix) { return ((npix + FAST_NT - 1) / FAST_NT) * 32; }
-__host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix, int wp)
+__host__ __device__ __forceinline__ int fast_chunk(int npix, int nw) { return ((npix + 32 * nw - 1) / (32 * nw)) * 32; }
+__host__ __device__ __forceinline__ FastSmemLayout fast_smem_layout(int max_wh, int max_pix, int wp, int nw)
 {
     FastSmemLayout o;
-    o.chunk = fast_chunk(max_pix) + 64; /* a warp owns whole rows: up to one row (< 64 px) above its share */
+    o.chunk = fast_chunk(max_pix, nw) + 64; /* a warp owns whole rows: up to one row (< 64 px) above its share */
     int b = 128; /* per-warp counts [0,64), the two window mbarriers [64,80) */
     o.win_off = b; o.win_bytes = (max_wh * wp + 127) & ~127; b += 2 * o.win_bytes; /* double buffered, 128-B aligned (TMA) */
     o.sc_off = b;  b += ((max_wh - 4) * FAST_SPITCH + 15) & ~15;
     /* list1 (u16 pixel | side<<12) is dead once stage 2 has consumed it; list3 (u32 NMS survivors:
      * pixel | score<<12, at most half a warp's pixels + one per row) reuses its storage */
-    o.l1_off = b;  o.l3_off = b;  b += FAST_NW * (o.chunk + 64) * 2;
-    o.l2_off = b;  b += FAST_NW * o.chunk * 2;            /* u16 corners */
+    o.l1_off = b;  o.l3_off = b;  b += nw * (o.chunk + 64) * 2;
+    o.l2_off = b;  b += nw * o.chunk * 2;            /* u16 corners */
     o.bytes = b;
     return o;
 }
@@ -226,15 +223,18 @@ __device__ __forceinline__ void fast_mbar_wait(uint32_t bar, uint32_t parity)
 #ifndef FAST_MIN_CTAS
 #define FAST_MIN_CTAS 16
 #endif
-template <int WP>
-__global__ void __launch_bounds__(FAST_NT, FAST_MIN_CTAS)
+/* NW = warps per cell: 2 for batches (measured best of 2 / 4 / 8: load balance between uneven cells), 4 for a frame or
+ * two, where the grid is one CTA per cell and a cell's dependent chain (load -> pre-test -> score -> NMS) is the time */
+template <int WP, int NW>
+__global__ void __launch_bounds__(32 * NW, FAST_MIN_CTAS * 2 / NW)
 k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict__ cells, int n_frames,
              const __grid_constant__ FastMaps tmaps, int frame0, uint32_t *__restrict__ cand_xy,
              uint32_t *__restrict__ cand_score, int *__restrict__ ncand)
 {
     const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     extern __shared__ __align__(128) unsigned char fast_raw[];
-    const FastSmemLayout lay = fast_smem_layout(tmaps.max_wh, tmaps.max_pix, WP);
+    constexpr int FAST_NT = 32 * NW, FAST_NW = NW;
+    const FastSmemLayout lay = fast_smem_layout(tmaps.max_wh, tmaps.max_pix, WP, NW);
     const uint32_t bar0 = fast_smem_u32(fast_raw + 64), win0 = fast_smem_u32(fast_raw + lay.win_off);
     const uint32_t box_bytes = (uint32_t)(WP * tmaps.max_wh);
     const CUtensorMap *maps = tmaps.m;
