@@ -433,6 +433,9 @@ int borb_debug_blurred(borb_extractor *h, int frame, int level, uint8_t *out /* 
  * form of the pattern rotation.  18 <= x < cols - 18, 18 <= y < rows - 18. */
 int borb_debug_describe(borb_extractor *h, const uint8_t *img, int cols, int rows, size_t step, int x, int y,
                         float angle_deg, uint8_t *desc32);
+/* the frame-to-frame / local-map matchers run at most this many rounds of their fixed point before one thread finishes
+ * the still-open suffix in the reference's order (default 16; 0 restores it): lets a test reach the sequential finish */
+void borb_debug_set_match_rounds(int max_rounds);
 /* host evaluation of the device sin/cos routine (same inline function, host build) */
 void borb_debug_sincos(float radians, float *s, float *c);
 /* host evaluation of the per-pixel FAST score used by the cell kernel: 0 = not a FAST-9 corner at

@@ -1516,6 +1516,8 @@ int borb_stereo_result(const borb_extractor *l, int frame, const float **u_right
     return BORB_OK;
 }
 
+static int g_match_max_rounds = 0; /* 0 = MT_MAX_ROUNDS; borb_debug_set_match_rounds */
+
 namespace {
 
 /* Both matchers (k_match.cuh): upload the query side's packed arrays [desc 32c][geo 16c][angle 4c][octave 4c][flags c]
@@ -1609,6 +1611,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     }
     mp.fx = cur->cam.fx; mp.fy = cur->cam.fy; mp.cx = cur->cam.cx; mp.cy = cur->cam.cy;
     mp.n_last = n;
+    mp.max_rounds = g_match_max_rounds;
     for (int l = 0; l < BORB_MAXL; ++l) mp.scale[l] = l < cur->nlevels ? cur->scale[l] : 0.f;
     const size_t fo = (size_t)frame * K;
     const float *d_ur = use_stereo ? cur->d_st_u + fo : nullptr;
@@ -1837,6 +1840,7 @@ int borb_debug_describe(borb_extractor *h, const uint8_t *img, int cols, int row
 }
 
 void borb_debug_sincos(float radians, float *s, float *c) { orb_sincosf_exact(radians, s, c); }
+void borb_debug_set_match_rounds(int max_rounds) { g_match_max_rounds = max_rounds > 0 ? max_rounds : 0; }
 int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_score_px(p, pitch, t_lo); }
 
 } // extern "C"

@@ -51,6 +51,7 @@ struct MatchParams {
     float nnratio; /* M2: mfNNratio of the local-map matcher */
     int mono, check_ori, n_last;
     int dir; /* 1 forward, 2 backward, 0 neither: from tlc.z against mb (:1515-1526), evaluated on the host */
+    int max_rounds; /* fixed-point rounds of M1b before the open suffix is finished sequentially (MT_MAX_ROUNDS) */
     float scale[BORB_MAXL];
 };
 
@@ -88,6 +89,9 @@ __device__ __forceinline__ int mt_bin(float a_last, float a_cur)
 }
 
 #define MT_K 8            /* cached candidates per query (M1b loads them as two uint4) */
+#ifndef MT_MAX_ROUNDS
+#define MT_MAX_ROUNDS 16  /* fixed-point rounds of M1b before the open suffix is finished sequentially */
+#endif
 #define MT_CAND_NT 256    /* M1a: 8 queries per CTA */
 #define MT_NOKEY 0xffffffffu
 
@@ -252,7 +256,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
      * barriers apart instead of three global-memory round trips */
     extern __shared__ int mt_taker_s[];
     int *taker = taker_in_smem ? mt_taker_s : taker_g;
-    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans;
+    __shared__ int s_changed, s_nm, s_hist[MT_HISTO], s_keep[MT_HISTO], s_rescans, s_first;
     const int tid = threadIdx.x;
     const int n_cur = min(*n_cur_p, kp_total), n_last = mp.n_last;
     const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
@@ -264,14 +268,8 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
     for (int c = tid; c < kp_total; c += MT_NT) { taker[c] = 0x7fffffff; match[c] = -1; }
     __syncthreads();
 
-    int round = 0;
-    for (;; ++round) {
-        const int *tk_prev = taker + (round & 1) * kp_total;
-        int *tk_new = taker + ((round + 1) & 1) * kp_total;
-        for (int c = tid; c < n_cur; c += MT_NT) tk_new[c] = 0x7fffffff;
-        if (tid == 0) s_changed = 0;
-        __syncthreads();
-        for (int i = tid; i < n_last; i += MT_NT) {
+    /* what query i chooses when tk[c] = the earliest query (with observations) that holds keypoint c */
+    auto choose = [&](int i, const int *tk) -> int {
             int ch = -1;
             /* the query's cached entries and who holds each of them, loaded side by side (two 16-byte loads, then
              * MT_K independent ones) */
@@ -283,7 +281,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                 keys[0] = k0.x; keys[1] = k0.y; keys[2] = k0.z; keys[3] = k0.w;
                 keys[4] = k1.x; keys[5] = k1.y; keys[6] = k1.z; keys[7] = k1.w;
 #pragma unroll
-                for (int k = 0; k < MT_K; ++k) held_by[k] = keys[k] != MT_NOKEY ? tk_prev[keys[k] & 0xffffu] : 0x7fffffff;
+                for (int k = 0; k < MT_K; ++k) held_by[k] = keys[k] != MT_NOKEY ? tk[keys[k] & 0xffffu] : 0x7fffffff;
             }
             if (MODE == 1) {
                 bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
@@ -303,7 +301,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                         const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
                         for (int q = q0; q < q1; ++q) {
                             const int i2 = cell_idx[q];
-                            if (tk_prev[i2] < i) continue;
+                            if (tk[i2] < i) continue;
                             const int d = mt_candidate(Q, i2, kp, un_xy, u_right, occupied, desc, d0, d1);
                             if (d >= 0 && d < best) { best = d; best_idx = i2; }
                         }
@@ -335,7 +333,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                         const int q0 = cell_start[ix * MT_ROWS + Q.cy0], q1 = cell_start[ix * MT_ROWS + Q.cy1 + 1];
                         for (int q = q0; q < q1; ++q) {
                             const int i2 = cell_idx[q];
-                            if (tk_prev[i2] < i) continue;
+                            if (tk[i2] < i) continue;
                             const int d = mt_candidate(Q, i2, kp, un_xy, u_right, occupied, desc, d0, d1);
                             if (d < 0) continue;
                             if (d < bd) { bd2 = bd; bd = d; bl2 = bl; bl = kp[i2].octave; bidx = i2; }
@@ -345,13 +343,53 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                 }
                 if (bd <= MT_TH_HIGH && !(bl == bl2 && (float)bd > mp.nnratio * (float)bd2)) ch = bidx;
             }
-            if (ch != choice[i]) { choice[i] = ch; s_changed = 1; }
+            return ch;
+    };
+
+    /* Rounds of the fixed point.  After round r every query below the smallest index whose choice changed in round r
+     * is final (a choice depends on earlier queries only), so the rounds needed equal the longest chain of displaced
+     * queries: 2-10 on real frames, but up to n_last on adversarial input (many map points projecting onto the same few
+     * keypoints).  After MT_MAX_ROUNDS the still-open suffix is finished by ONE thread walking it in the reference's own
+     * order -- exact by construction, slow only where the input is pathological. */
+    int round = 0;
+    bool settled = false;
+    const int max_rounds = mp.max_rounds > 0 ? mp.max_rounds : MT_MAX_ROUNDS;
+    for (; round < max_rounds; ++round) {
+        const int *tk_prev = taker + (round & 1) * kp_total;
+        int *tk_new = taker + ((round + 1) & 1) * kp_total;
+        for (int c = tid; c < n_cur; c += MT_NT) tk_new[c] = 0x7fffffff;
+        if (tid == 0) { s_changed = 0; s_first = 0x7fffffff; }
+        __syncthreads();
+        for (int i = tid; i < n_last; i += MT_NT) {
+            const int ch = choose(i, tk_prev);
+            if (ch != choice[i]) { choice[i] = ch; s_changed = 1; atomicMin(&s_first, i); }
             if (ch >= 0 && (l_flags[i] & 2u)) atomicMin(&tk_new[ch], i);
         }
         __syncthreads();
         const int changed = s_changed;
         __syncthreads();
-        if (!changed) break;
+        if (!changed) { settled = true; break; }
+    }
+    if (!settled) {
+        /* queries below `first` are final; rebuild the takers from them alone, then walk the rest in order */
+        const int first = s_first;
+        int *tk = taker + (round & 1) * kp_total; /* the array the last round filled: overwritten here */
+        __syncthreads();
+        for (int c = tid; c < n_cur; c += MT_NT) tk[c] = 0x7fffffff;
+        __syncthreads();
+        for (int i = tid; i < first && i < n_last; i += MT_NT) {
+            const int ch = choice[i];
+            if (ch >= 0 && (l_flags[i] & 2u)) atomicMin(&tk[ch], i);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            for (int i = max(first, 0); i < n_last; ++i) {
+                const int ch = choose(i, tk);
+                choice[i] = ch;
+                if (ch >= 0 && (l_flags[i] & 2u) && tk[ch] > i) tk[ch] = i;
+            }
+        }
+        __syncthreads();
     }
 
     /* ---- assignment, orientation histogram, three maxima ---- */
@@ -387,7 +425,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
         }
         __syncthreads();
     }
-    if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; }
+    if (tid == 0) { nm[0] = s_nm; nm[1] = settled ? round + 1 : max_rounds + 1; nm[2] = s_rescans; } /* max_rounds + 1: the sequential finish ran */
 }
 
 /* ---------------------------------------------------------------------------------------------

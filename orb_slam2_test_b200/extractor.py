@@ -33,7 +33,7 @@ SYMBOLS = [
     "borb_scale_factor", "borb_table", "borb_features_per_level", "borb_umax",
     "borb_extract_host", "borb_extract_device", "borb_fetch", "borb_sync", "borb_result",
     "borb_pyramid", "borb_level_size", "borb_launches_per_call", "borb_last_device_ms",
-    "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score", "borb_debug_describe",
+    "borb_debug_candidates", "borb_debug_blurred", "borb_debug_sincos", "borb_debug_fast_score", "borb_debug_describe", "borb_debug_set_match_rounds",
     "borb_submit_host", "borb_wait", "borb_host_alloc", "borb_host_free", "borb_timer_start",
     "borb_timer_stop", "borb_timer_ms", "borb_stage_times", "borb_set_stage_timing", "borb_last_stage_ms", "borb_counts",
     "borb_stereo_match", "borb_stereo_result", "borb_set_input_format", "borb_set_rectify_map",
@@ -99,6 +99,8 @@ def load_library() -> C.CDLL:
                                           C.POINTER(C.c_int)]
     lib.borb_debug_blurred.argtypes = [_vp, C.c_int, C.c_int, _vp]
     lib.borb_debug_sincos.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.borb_debug_set_match_rounds.argtypes = [C.c_int]
+    lib.borb_debug_set_match_rounds.restype = None
     lib.borb_debug_describe.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_float, _vp]
     lib.borb_debug_fast_score.argtypes = [_vp, C.c_int, C.c_int]
     lib.borb_submit_host.argtypes = lib.borb_extract_host.argtypes

@@ -126,6 +126,42 @@ def _check_local(tag, oracle, ths=(1.0, 3.0, 5.0), ratios=(0.8, 0.6), **kw):
     return total
 
 
+def test_long_displacement_chains_are_finished_sequentially(oracle_built, capsys):
+    """Crowded queries (every map point 3 / 12 / 40 times, all with observations): the round counts of the fixed point
+    are reported, and with the round limit lowered to 2 / 4 the still-open suffix is walked in the reference's order by
+    one thread -- same answer for the frame-to-frame and the local-map matcher."""
+    from orb_slam2_test_b200.extractor import load_library
+    lib = load_library()
+    try:
+        for copies in (3, 12, 40):
+            cur, last, cam, bounds, scale = matchcase.make_case(seed=4, copies=copies, obs_rate=1.0)
+            bf, mb = float(cam[4]), float(cam[5])
+            ext, right = _gpu_frame(synth.KITTI_SHAPE, 4, 1, matchcase.KITTI_K, (0.0, 0.0, 0.0, 0.0), True, 2000, bf, mb)
+            for th in (7.0, 30.0):
+                want, wnm = oracle_built.search_by_projection(cur, last, cam, bounds, scale, th)
+                for limit in (0, 4, 2):
+                    lib.borb_debug_set_match_rounds(limit)
+                    got, nm = ext.search_by_projection(_last_for_abi(last), cur["Tcw"], bf, mb, th, use_stereo=True)
+                    assert np.array_equal(got, want) and nm == wnm, f"copies={copies} th={th} limit={limit}"
+                    if limit == 0:
+                        assert ext.match_rounds() <= 16
+                        with capsys.disabled():
+                            print(f"\n[info] frame-to-frame matcher, every map point x{copies}, th {th:.0f}: {ext.match_rounds()} rounds, "
+                                  f"{ext.match_rescans()} rescans, {nm} matches")
+                    else:
+                        assert ext.match_rounds() == limit + 1  # the sequential finish ran
+        cur, bounds, scale, mps, occ = matchcase.make_local_case(seed=3, copies=4, obs_rate=1.0)
+        ext, right = _gpu_frame(synth.KITTI_SHAPE, 3, 1, matchcase.KITTI_K, (0.0, 0.0, 0.0, 0.0), True, 2000, matchcase.KITTI_BF,
+                                matchcase.KITTI_BF / matchcase.KITTI_K[0])
+        want, wnm = oracle_built.search_local_points(cur, bounds, scale, mps, occ, 3.0, 0.8)
+        for limit in (0, 2):
+            lib.borb_debug_set_match_rounds(limit)
+            got, nm = ext.search_local_points(mps, occ, 3.0, 0.8, use_stereo=True)
+            assert np.array_equal(got, want) and nm == wnm, f"local map, limit={limit}"
+    finally:
+        lib.borb_debug_set_match_rounds(0)
+
+
 @pytest.mark.parametrize("seed,copies,obs", [(1, 2, 0.9), (2, 3, 0.5), (3, 4, 1.0)])
 def test_local_map_kitti(seed, copies, obs, oracle_built):
     assert _check_local(f"local kitti {seed}", oracle_built, seed=seed, copies=copies, obs_rate=obs) > 2000
