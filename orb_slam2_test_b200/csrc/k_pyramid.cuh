@@ -126,7 +126,7 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
         int x = min(c + k, L.w - 1 + BORB_EDGE);
         x = reflect101(x, L.w);
         sx[k] = tab_i[L.xofs_off + x];
-        aw[k] = (uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x] | ((uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x + 1] << 16);
+        aw[k] = *reinterpret_cast<const uint32_t *>(tab_s + L.xa_off + 2 * x); /* a0 | a1 << 16: the tables' offsets are even */
         sx_lo = min(sx_lo, sx[k]);
         sx_hi = max(sx_hi, min(sx[k] + 1, S.w - 1));
     }
@@ -185,11 +185,13 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     /* Both source rows' horizontal sums (already >> 4, as the vertical pass uses them) are computed for every output row:
      * keeping the previous row's sums to reuse the shared one (5 rows of 6 at 1.2) cost more instructions -- the
      * compares, branches and 8 register moves per row -- than the 4 dot products it saved (0.952 -> 0.944 ms). */
-    uint8_t *dst = frame + L.off + BORB_XPAD + c;
+    /* a running store pointer: the row's address as (size_t)r * pitch cost 14 instructions per row in SASS */
+    const int rw0 = r0 + warp * (PYR_TH / 4);
+    uint8_t *drow = frame + L.off + BORB_XPAD + c + (size_t)rw0 * L.pitch;
+    const int nrow = min(PYR_TH / 4, L.prows - rw0);
 #pragma unroll
-    for (int i = 0; i < PYR_TH / 4; ++i) {
-        const int r = r0 + warp * (PYR_TH / 4) + i;
-        if (r >= L.prows) break;
+    for (int i = 0; i < PYR_TH / 4; ++i, drow += L.pitch) {
+        if (i >= nrow) break;
         /* (b * h) >> 16 as the high word of (b << 16) * h: operands are non-negative */
         const uint32_t rw_ = __shfl_sync(0xffffffffu, my_rows, warp * (PYR_TH / 4) + i);
         const uint32_t bw_ = __shfl_sync(0xffffffffu, my_b, warp * (PYR_TH / 4) + i);
@@ -210,7 +212,7 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
             const uint32_t d = (__umulhi(b0, n0[k]) + __umulhi(b1, n1[k]) + 2u) >> 2;
             v |= d << (8 * k);
         }
-        if (col_on) *reinterpret_cast<uint32_t *>(dst + (size_t)r * L.pitch) = v;
+        if (col_on) *reinterpret_cast<uint32_t *>(drow) = v;
     }
 }
 
