@@ -24,6 +24,7 @@
 #include "MapPoint.h"
 #include "ORBVocabulary.h"
 #include "ORBmatcher.h"
+#include "matchcompat/MapPoint_impl.h"
 
 using namespace ORB_SLAM2;
 

@@ -247,14 +247,10 @@ public:
         return s;
     }
 
-    /* float (CV_32F, one channel) algebra used by the reference's Frame.cc pose code */
-    Mat t() const
-    {
-        Mat m(cols, rows, type_);
-        for (int y = 0; y < rows; ++y)
-            for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
-        return m;
-    }
+    /* float (CV_32F, one channel) algebra used by the reference's Frame.cc pose code.  t() is an EXPRESSION, as
+     * cv::MatExpr is: -A.t() * B reaches cv::gemm with GEMM_1_T and alpha = -1, a different arithmetic path from A * B
+     * (MatT below). */
+    inline class MatT t() const;
 
 private:
     std::shared_ptr<uchar> store_;
@@ -293,6 +289,40 @@ inline Mat operator-(const Mat &a, const Mat &b) { return mat_lin_(a, 1.f, &b, -
 inline Mat operator-(const Mat &a) { return mat_lin_(a, -1.f, nullptr, 0.f); }
 inline Mat operator*(float s, const Mat &a) { return mat_lin_(a, s, nullptr, 0.f); }
 inline Mat operator/(const Mat &a, float s) { return mat_lin_(a, 1.f / s, nullptr, 0.f); } /* only named by keyframe matchers nobody runs here */
+/* A.t() [scaled]: what cv::MatExpr carries for a transpose.  Used as a matrix it is the plain transpose
+ * (cv::transpose, src/Frame.cc:332); multiplied, it is cv::gemm(A, B, alpha, noArray(), 0, GEMM_1_T), which -- unlike
+ * the plain small product above -- takes OpenCV's generic path: the sum over k in DOUBLE, left to right, times alpha,
+ * one rounding to float (cv2 4.13: tests/test_oracle_match.py::test_transposed_gemm_form_is_cv2s).  This is
+ * Ow = -Rcw.t() * tcw of src/Frame.cc:334 and src/ORBmatcher.cc:366, 1146, 1516, 1676. */
+class MatT {
+public:
+    MatT(const Mat &a, double alpha) : a_(a), alpha_(alpha) {}
+    operator Mat() const
+    {
+        if (alpha_ != 1.0) std::abort(); /* a scaled transpose on its own (src/ORBmatcher.cc:1280): not pinned, nobody runs it here */
+        Mat m(a_.cols, a_.rows, CV_32F);
+        for (int y = 0; y < a_.rows; ++y)
+            for (int x = 0; x < a_.cols; ++x) m.at<float>(x, y) = a_.at<float>(y, x);
+        return m;
+    }
+    Mat a_;
+    double alpha_;
+};
+inline MatT Mat::t() const { return MatT(*this, 1.0); }
+inline MatT operator-(const MatT &e) { return MatT(e.a_, -e.alpha_); }
+inline MatT operator*(double s, const MatT &e) { return MatT(e.a_, s * e.alpha_); }
+CVCOMPAT_NOFMA inline Mat operator*(const MatT &e, const Mat &b)
+{
+    const Mat &a = e.a_; /* result = alpha * a^T * b */
+    Mat m(a.cols, b.cols, CV_32F);
+    for (int y = 0; y < a.cols; ++y)
+        for (int x = 0; x < b.cols; ++x) {
+            double s = 0.0;
+            for (int k = 0; k < a.rows; ++k) s += (double)a.at<float>(k, y) * (double)b.at<float>(k, x);
+            m.at<float>(y, x) = (float)(s * e.alpha_);
+        }
+    return m;
+}
 enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
 /* L1 norm of a - b, accumulated in double as OpenCV does for CV_32F */
 inline double norm(const Mat &a, const Mat &b, int type)

@@ -21,7 +21,9 @@
  *   radius = th * mvScaleFactors[octave]                     (:1561)
  *   ur     = fmaf(-mbf, invzc, u);  er = fabsf(ur - mvuRight[i2])   (:1593-1594)
  *   rot    = angleLast - angleCur; if (rot < 0) rot += 360.f; bin = round(rot * (1.f / 30))  (:1617-1622)
- *   tlc    = Rlw * (-Rcw^T * tcw) + tlw, same product form   (:1515-1521)
+ *   twc    = -Rcw.t() * tcw     cv::gemm with GEMM_1_T, alpha = -1: OpenCV's generic path, the sum over k in DOUBLE,
+ *                               times alpha, one rounding (cv2 4.13: test_transposed_gemm_form_is_cv2s)   (:1516)
+ *   tlc    = Rlw * twc + tlw, the small-product form of x3Dc   (:1521)
  *
  * The reference loop is sequential: a current keypoint that already holds a map point with
  * Observations() > 0 is skipped by every later query (:1583-1585), one holding a map point without
@@ -98,9 +100,9 @@ int mo_search_by_projection(const mo_frame *cur, const mo_frame *last, const flo
     /* twc = -Rcw^T * tcw; tlc = Rlw * twc + tlw */
     float twc[3], tcw[3] = {Tc[3], Tc[7], Tc[11]};
     for (int y = 0; y < 3; ++y) {
-        float s = 0.f;
-        for (int k = 0; k < 3; ++k) s += (-Tc[4 * k + y]) * tcw[k];
-        twc[y] = s;
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += (double)Tc[4 * k + y] * (double)tcw[k];
+        twc[y] = (float)(s * -1.0);
     }
     const float tlc_z = mo_dot3(Tl + 8, 1, twc) + Tl[11];
     const bool forward = tlc_z > mb && !mono, backward = -tlc_z > mb && !mono;
@@ -354,4 +356,126 @@ int mo_search_for_initialization(const mo_frame *f1, const mo_frame *f2, const f
     return nmatches;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound,
+ *                                const float th, const int ORBdist)
+ *     /root/reference/src/ORBmatcher.cc:1670-1798 -- the matcher of Tracking::Relocalization's second and third
+ *     search (src/Tracking.cc: "matcher2.SearchByProjection(mCurrentFrame, vpCandidateKFs[i], sFound, 10, 100)",
+ *     then "(…, 3, 64)").
+ * Entry i is keyframe keypoint i: kf_flags[i] bit 0 = vpMPs[i] != NULL, bit 1 = isBad(), bit 2 = the point is in
+ * sAlreadyFound; kf_xyz = GetWorldPos(), kf_desc = GetDescriptor(), kf_dist[2i] = mfMinDistance, [2i + 1] =
+ * mfMaxDistance (src/MapPoint.cc:520-530, :575-590), kf_angle[i] = pKF->mvKeysUn[i].angle.  occupied[i2] != 0 where
+ * CurrentFrame.mvpMapPoints[i2] is set on entry (every set slot is skipped, :1735-1736 -- also the ones this call sets).
+ * log_scale = CurrentFrame.mfLogScaleFactor.  Float forms as the reference object has them:
+ *   Ow      = -Rcw.t() * tcw          cv::gemm GEMM_1_T, double accumulation (see the header)            (:1676)
+ *   x3Dc, u, v                        as the frame-to-frame matcher; NO invzc < 0 test here             (:1693-1705)
+ *   dist3D  = (float)cv::norm(x3Dw - Ow)   squares summed in double left to right, double sqrt          (:1708-1709)
+ *   0.8f * mfMinDistance, 1.2f * mfMaxDistance                                                          (:1711-1716)
+ *   PredictScale: ratio = mfMaxDistance / dist3D; nScale = ceilf(logf(ratio) / mfLogScaleFactor), clamped to
+ *                 [0, mnScaleLevels - 1] (with `using namespace std` in effect both calls are the float overloads;
+ *                 logf is glibc's, which the device restates: csrc/orb_logf.cuh)
+ *   radius  = th * mvScaleFactors[nPredictedLevel], octaves nPredictedLevel - 1 .. nPredictedLevel + 1   (:1721-1723)
+ */
+int mo_search_by_projection_kf(const mo_frame *cur, const float *cam, const float *bounds, const float *scale, int nlevels,
+                               float log_scale, int n_kf, const uint8_t *kf_flags, const float *kf_xyz, const uint8_t *kf_desc,
+                               const float *kf_dist, const float *kf_angle, const uint8_t *occupied, float th, int orb_dist,
+                               int check_ori, int32_t *out_match)
+{
+    const float fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3];
+    const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
+    const float winv = (float)MO_COLS / (max_x - min_x), hinv = (float)MO_ROWS / (max_y - min_y);
+    const mo_kp *ck = reinterpret_cast<const mo_kp *>(cur->kps);
+    const float *Tc = cur->Tcw;
+    float Ow[3];
+    for (int y = 0; y < 3; ++y) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += (double)Tc[4 * k + y] * (double)Tc[4 * k + 3];
+        Ow[y] = (float)(s * -1.0);
+    }
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    if (cur->grid_count)
+        for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + cur->grid_count[c];
+    for (int i = 0; i < cur->n; ++i) out_match[i] = -1;
+    std::vector<int> hist[MO_HISTO];
+    const float factor = 1.0f / MO_HISTO;
+    int nmatches = 0;
+
+    for (int i = 0; i < n_kf; ++i) {
+        if (!(kf_flags[i] & 1) || (kf_flags[i] & 6)) continue;
+        const float *X = kf_xyz + 3 * i;
+        const float xc = mo_dot3(Tc, 1, X) + Tc[3], yc = mo_dot3(Tc + 4, 1, X) + Tc[7], zc = mo_dot3(Tc + 8, 1, X) + Tc[11];
+        const float invzc = 1.0f / zc;
+        const float u = std::fmaf(fx * xc, invzc, cx), v = std::fmaf(fy * yc, invzc, cy);
+        if (u < min_x || u > max_x) continue;
+        if (v < min_y || v > max_y) continue;
+        double s2 = 0.0;
+        for (int k = 0; k < 3; ++k) {
+            const float po = X[k] - Ow[k];
+            s2 += (double)po * (double)po;
+        }
+        const float dist3D = (float)std::sqrt(s2);
+        const float max_d = 1.2f * kf_dist[2 * i + 1], min_d = 0.8f * kf_dist[2 * i];
+        if (dist3D < min_d || dist3D > max_d) continue;
+        const float ratio = kf_dist[2 * i + 1] / dist3D;
+        int lvl = (int)std::ceil(std::log(ratio) / log_scale); /* float overloads */
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= nlevels) lvl = nlevels - 1;
+        const float radius = th * scale[lvl];
+        const int min_level = lvl - 1, max_level = lvl + 1;
+
+        const int cx0 = std::max(0, (int)std::floor((u - min_x - radius) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((u - min_x + radius) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((v - min_y - radius) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((v - min_y + radius) * hinv));
+        if (cy1 < 0) continue;
+        const bool check_levels = (min_level > 0) || (max_level >= 0);
+
+        int best = 256, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int i2 = cur->grid_idx[q];
+                    if (check_levels) {
+                        if (ck[i2].octave < min_level) continue;
+                        if (max_level >= 0 && ck[i2].octave > max_level) continue;
+                    }
+                    const float dx = cur->un_xy[2 * i2] - u, dy = cur->un_xy[2 * i2 + 1] - v;
+                    if (!(std::fabs(dx) < radius && std::fabs(dy) < radius)) continue;
+                    if ((occupied && occupied[i2]) || out_match[i2] >= 0) continue; /* :1735-1736 */
+                    const int d = mo_hamming256(kf_desc + (size_t)i * 32, cur->desc + (size_t)i2 * 32);
+                    if (d < best) { best = d; best_idx = i2; }
+                }
+            }
+        if (best <= orb_dist && best_idx >= 0) {
+            out_match[best_idx] = i;
+            ++nmatches;
+            if (check_ori) {
+                float rot = kf_angle[i] - ck[best_idx].angle;
+                if (rot < 0.0f) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == MO_HISTO) bin = 0;
+                hist[bin].push_back(best_idx);
+            }
+        }
+    }
+    if (check_ori) {
+        int sz[MO_HISTO], i1, i2, i3;
+        for (int b = 0; b < MO_HISTO; ++b) sz[b] = (int)hist[b].size();
+        mo_three_maxima(sz, MO_HISTO, &i1, &i2, &i3);
+        for (int b = 0; b < MO_HISTO; ++b) {
+            if (b == i1 || b == i2 || b == i3) continue;
+            for (size_t j = 0; j < hist[b].size(); ++j) {
+                out_match[hist[b][j]] = -1;
+                --nmatches;
+            }
+        }
+    }
+    return nmatches;
+}
+
 } // extern "C"
+

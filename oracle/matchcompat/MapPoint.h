@@ -23,9 +23,12 @@ public:
     bool isBad() { return mbBad; }
 
     cv::Mat GetNormal() { std::abort(); }
-    float GetMaxDistanceInvariance() { std::abort(); }
-    float GetMinDistanceInvariance() { std::abort(); }
-    int PredictScale(const float &, Frame *) { std::abort(); }
+    /* src/MapPoint.cc:520-530 and :575-590, restated (the reference's MapPoint.cc needs the whole map model); the body of
+     * PredictScale is in MapPoint_impl.h, which the drivers include where Frame is complete */
+    float mfMinDistance = 0, mfMaxDistance = 0;
+    float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
+    float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }
+    int PredictScale(const float &currentDist, Frame *pF);
     int PredictScale(const float &, KeyFrame *) { std::abort(); }
     bool IsInKeyFrame(KeyFrame *) { std::abort(); }
     void Replace(MapPoint *) { std::abort(); }

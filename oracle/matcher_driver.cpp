@@ -14,10 +14,12 @@
  */
 #include <cstdint>
 #include <cstring>
+#include <set>
 #include <vector>
 
 #include "Frame.h"
 #include "ORBmatcher.h"
+#include "matchcompat/MapPoint_impl.h"
 
 using namespace ORB_SLAM2;
 
@@ -218,4 +220,75 @@ int refmatch_search_for_initialization(const refmatch_frame *f1, const refmatch_
     return nm;
 }
 
+/* ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist)
+ * (src/ORBmatcher.cc:1670-1798), the relocalisation matcher.  kf_flags[i] bit 0 = vpMPs[i] != NULL, bit 1 = isBad(),
+ * bit 2 = member of sAlreadyFound; kf_dist[2i], [2i + 1] = mfMinDistance, mfMaxDistance; kf_angle[i] =
+ * pKF->mvKeysUn[i].angle; occupied[i2] != 0: CurrentFrame.mvpMapPoints[i2] is set on entry.  out_match[i2] = index of the
+ * keyframe keypoint whose map point this call put into slot i2, -1 elsewhere. */
+int refmatch_search_by_projection_kf(const refmatch_frame *cur, const float *cam, const float *bounds, const float *scale,
+                                     int nlevels, float log_scale, int n_kf, const uint8_t *kf_flags, const float *kf_xyz,
+                                     const uint8_t *kf_desc, const float *kf_dist, const float *kf_angle,
+                                     const uint8_t *occupied, float th, int orb_dist, int check_ori, int32_t *out_match)
+{
+    Frame::fx = cam[0]; Frame::fy = cam[1]; Frame::cx = cam[2]; Frame::cy = cam[3];
+    Frame::invfx = 1.0f / cam[0]; Frame::invfy = 1.0f / cam[1];
+    Frame::mnMinX = bounds[0]; Frame::mnMaxX = bounds[1]; Frame::mnMinY = bounds[2]; Frame::mnMaxY = bounds[3];
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);
+    Frame::mbInitialComputations = false;
+    Frame f;
+    const refmatch_frame &r = *cur;
+    f.N = r.n;
+    f.mvKeys.resize(r.n);
+    if (r.n) std::memcpy(f.mvKeys.data(), r.kps, (size_t)r.n * 28);
+    f.mvKeysUn = f.mvKeys;
+    for (int i = 0; i < r.n; ++i) { f.mvKeysUn[i].pt.x = r.un_xy[2 * i]; f.mvKeysUn[i].pt.y = r.un_xy[2 * i + 1]; }
+    f.mDescriptors = cv::Mat(r.n, 32, CV_8UC1);
+    for (int i = 0; i < r.n; ++i) std::memcpy(f.mDescriptors.ptr(i), r.desc + (size_t)i * 32, 32);
+    f.mvuRight.assign(r.n, -1.f);
+    f.mnScaleLevels = nlevels;
+    f.mfLogScaleFactor = log_scale;
+    f.mvScaleFactors.assign(scale, scale + nlevels);
+    int k = 0;
+    for (int i = 0; i < FRAME_GRID_COLS; ++i)
+        for (int j = 0; j < FRAME_GRID_ROWS; ++j) {
+            const int c = r.grid_count[i * FRAME_GRID_ROWS + j];
+            f.mGrid[i][j].assign(r.grid_idx + k, r.grid_idx + k + c);
+            k += c;
+        }
+    f.SetPose(pose_mat(r.Tcw));
+    MapPoint held;
+    f.mvpMapPoints.assign(r.n, static_cast<MapPoint *>(NULL));
+    if (occupied)
+        for (int i = 0; i < r.n; ++i)
+            if (occupied[i]) f.mvpMapPoints[i] = &held;
+    std::vector<MapPoint> mps(n_kf);
+    KeyFrame kf;
+    kf.mvpMapPoints.assign(n_kf, static_cast<MapPoint *>(NULL));
+    kf.mvKeysUn.resize(n_kf);
+    std::set<MapPoint *> found;
+    for (int i = 0; i < n_kf; ++i) {
+        kf.mvKeysUn[i].angle = kf_angle[i];
+        if (!(kf_flags[i] & 1)) continue;
+        MapPoint &m = mps[i];
+        m.mWorldPos = cv::Mat(3, 1, CV_32F);
+        for (int c = 0; c < 3; ++c) m.mWorldPos.at<float>(c) = kf_xyz[3 * i + c];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1);
+        std::memcpy(m.mDescriptor.ptr(0), kf_desc + (size_t)i * 32, 32);
+        m.mbBad = (kf_flags[i] & 2) != 0;
+        m.mfMinDistance = kf_dist[2 * i];
+        m.mfMaxDistance = kf_dist[2 * i + 1];
+        kf.mvpMapPoints[i] = &m;
+        if (kf_flags[i] & 4) found.insert(&m);
+    }
+    ORBmatcher matcher(0.9f, check_ori != 0);
+    const int nm = matcher.SearchByProjection(f, &kf, found, th, orb_dist);
+    for (int i2 = 0; i2 < r.n; ++i2) {
+        MapPoint *p = f.mvpMapPoints[i2];
+        out_match[i2] = (p && p != &held) ? (int32_t)(p - mps.data()) : -1;
+    }
+    return nm;
+}
+
 } // extern "C"
+

@@ -329,8 +329,56 @@ def search_for_initialization(f1, f2, bounds, prev, window=100, nnratio=0.9, che
     return _init_call(Oracle.load().mo_search_for_initialization, f1, f2, bounds, prev, window, nnratio, check_ori)
 
 
+def _reloc_call(fn, cur: dict, cam, bounds, scale, log_scale: float, kf: dict, occupied, th: float, orb_dist: int,
+                check_ori: bool):
+    """Common marshalling for mo_search_by_projection_kf / refmatch_search_by_projection_kf.  cur as _match_call's (with
+    Tcw and the grid); kf: flags [n] u8 (bit 0 map point, bit 1 bad, bit 2 already found), xyz [n,3], desc [n,32],
+    dist [n,2] f32 (mfMinDistance, mfMaxDistance), angle [n] f32; occupied [n_cur] u8 or None.
+    -> (match [n_cur] i32: keyframe keypoint whose map point this call put there or -1, nmatches)."""
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+
+    f = _MatchFrame()
+    f.n = len(cur["kps"])
+    f.kps = arr(cur["kps"], KP_DTYPE)
+    f.un_xy = arr(cur["un_xy"], np.float32)
+    f.desc = arr(cur["desc"], np.uint8)
+    f.u_right = None
+    f.grid_count = arr(np.diff(cur["cell_start"]), np.int32)
+    f.grid_idx = arr(cur["cell_idx"], np.int32)
+    f.Tcw = arr(cur["Tcw"], np.float32)
+    scale = np.ascontiguousarray(scale, np.float32)
+    out = np.full(max(f.n, 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_float, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_float, C.c_int,
+                   C.c_int, _vp]
+    nm = fn(C.addressof(f), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data, len(scale), float(log_scale),
+            len(kf["flags"]), arr(kf["flags"], np.uint8), arr(kf["xyz"], np.float32), arr(kf["desc"], np.uint8),
+            arr(kf["dist"], np.float32), arr(kf["angle"], np.float32),
+            arr(occupied, np.uint8) if occupied is not None else None, float(th), int(orb_dist), int(check_ori),
+            out.ctypes.data)
+    return out[:f.n], int(nm)
+
+
+def search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occupied, th=10.0, orb_dist=100, check_ori=True):
+    """The relocalisation matcher (src/ORBmatcher.cc:1670-1798) restated (oracle/match_oracle.cpp)."""
+    return _reloc_call(Oracle.load().mo_search_by_projection_kf, cur, cam, bounds, scale, log_scale, kf, occupied, th,
+                       orb_dist, check_ori)
+
+
 class RefMatcher:
     """The reference's own src/ORBmatcher.cc + src/Frame.cc (oracle/_ref/librefmatch.so)."""
+
+    @classmethod
+    def search_by_projection_kf(cls, cur, cam, bounds, scale, log_scale, kf, occupied, th=10.0, orb_dist=100, check_ori=True):
+        if cls._lib is None:
+            cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
+        return _reloc_call(cls._lib.refmatch_search_by_projection_kf, cur, cam, bounds, scale, log_scale, kf, occupied, th,
+                           orb_dist, check_ori)
 
     _lib = None
 

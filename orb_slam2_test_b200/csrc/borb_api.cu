@@ -1520,6 +1520,18 @@ static int g_match_max_rounds = 0; /* 0 = MT_MAX_ROUNDS; borb_debug_set_match_ro
 
 namespace {
 
+/* Ow = -Rcw.t() * tcw as cv::MatExpr evaluates it (src/ORBmatcher.cc:1516, :1676; src/Frame.cc:334): cv::gemm(Rcw, tcw,
+ * -1, noArray(), 0, GEMM_1_T) -- OpenCV's generic path, products and sum in double, left to right, times alpha, one
+ * rounding to float (pinned against cv2 4.13.0 in tests/test_oracle_match.py). */
+void camera_centre(const float *Tcw /* 3 x 4 row-major */, float *Ow)
+{
+    for (int y = 0; y < 3; ++y) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += (double)Tcw[4 * k + y] * (double)Tcw[4 * k + 3];
+        Ow[y] = (float)(s * -1.0);
+    }
+}
+
 /* Both matchers (k_match.cuh): upload the query side's packed arrays [desc 32c][geo 16c][angle 4c][octave 4c][flags c]
  * (+ the occupancy bytes of the local-map matcher), M1a over the whole GPU, M1b in one CTA, download the matches. */
 int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *geo, int geo_stride, const uint8_t *desc,
@@ -1698,15 +1710,12 @@ int borb_search_by_projection(borb_extractor *cur, int frame, const borb_last_fr
     mp.mbf = mbf; mp.mb = mb; mp.th = th;
     mp.mono = (flags & BORB_MATCH_MONO) ? 1 : 0;
     mp.check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
-    {   /* search direction (:1515-1526): twc = -Rcw^T tcw, tlc = Rlw twc + tlw, OpenCV's small float gemm
+    {   /* search direction (:1515-1526): twc = -Rcw.t() * tcw is cv::gemm with GEMM_1_T and alpha = -1 (the sum over k
+         * in double, times alpha, one rounding: camera_centre), tlc = Rlw twc + tlw OpenCV's small float product
          * (products summed left to right); this file is compiled without contraction */
         const float *Tc = mp.Tc, *Tl = mp.Tl;
         float twc[3];
-        for (int y = 0; y < 3; ++y) {
-            float sacc = 0.f;
-            for (int k = 0; k < 3; ++k) sacc += (-Tc[4 * k + y]) * Tc[4 * k + 3];
-            twc[y] = sacc;
-        }
+        camera_centre(Tc, twc);
         float sacc = 0.f;
         for (int k = 0; k < 3; ++k) sacc += Tl[8 + k] * twc[k];
         const float tlc_z = sacc + Tl[11];

@@ -171,3 +171,28 @@ def make_init_case(seed=0, shape=synth.TUM_SHAPE, K=TUM1_K, dist=TUM1_D, nf=2000
         f1["un_xy"] = np.concatenate([f1["un_xy"]] * copies)
         f1["desc"] = np.concatenate(desc)
     return f1, f2, f2["bounds"], f1["un_xy"].copy()
+
+
+def make_reloc_case(seed=0, copies=1, found_rate=0.2, bad_rate=0.05, occupied_rate=0.15, dist_jitter=0.25, **kw):
+    """Scenario for the relocalisation matcher ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)
+    (src/ORBmatcher.cc:1670-1798): the keyframe is the previous frame of make_case with its map points (copies > 1 crowds the
+    queries), some of them bad, some already found by the PnP step; the scale-invariance distances are what
+    MapPoint::UpdateNormalAndDepth (src/MapPoint.cc) would give for the keyframe's own observation, jittered so that a share
+    of the points fails the distance test and the predicted level moves; some slots of the current frame are occupied.
+    -> (cur, cam, bounds, scale, log_scale, kf, occupied); kf: flags, xyz, desc, dist [n,2] = (mfMinDistance, mfMaxDistance), angle."""
+    cur, last, cam, bounds, scale = make_case(seed=seed, copies=copies, **kw)
+    rng = np.random.default_rng(9000 + seed)
+    n = len(last["mp_flags"])
+    T = last["Tcw"].astype(np.float64)
+    Ow = -T[:, :3].T @ T[:, 3]
+    d = np.linalg.norm(last["mp_xyz"].astype(np.float64) - Ow, axis=1)
+    sc = np.asarray(scale, np.float64)
+    max_d = d * sc[last["kps"]["octave"]] * rng.uniform(1 - dist_jitter, 1 + dist_jitter, n)
+    min_d = max_d / sc[-1]
+    flags = ((last["mp_flags"] & 1) | ((rng.random(n) < bad_rate).astype(np.uint8) << 1)
+             | ((rng.random(n) < found_rate).astype(np.uint8) << 2)).astype(np.uint8)
+    kf = {"flags": flags, "xyz": last["mp_xyz"], "desc": last["mp_desc"],
+          "dist": np.stack([min_d, max_d], 1).astype(np.float32), "angle": last["kps"]["angle"].astype(np.float32)}
+    occupied = (rng.random(len(cur["kps"])) < occupied_rate).astype(np.uint8)
+    log_scale = np.float32(np.log(np.float32(1.2)))  # Frame: mfLogScaleFactor = log(mfScaleFactor), float
+    return cur, cam, bounds, scale, float(log_scale), kf, occupied

@@ -27,6 +27,45 @@ def test_small_gemm_form_is_cv2s():
         assert np.array_equal(got, want)
 
 
+def test_transposed_gemm_form_is_cv2s():
+    """Ow = -Rcw.t() * tcw (src/ORBmatcher.cc:1516, :1676; src/Frame.cc:334) is cv::gemm(R, t, -1, None, 0, GEMM_1_T): with a
+    transposed operand OpenCV 4.13 leaves the small-matrix shortcut and sums the products in DOUBLE, left to right, times
+    alpha, one rounding -- not the float form of the plain product above (which differs on ~80 % of random inputs).
+    oracle/cvcompat (MatT), the restatement and the library's camera_centre use that form."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(5)
+    n_float_form_differs = 0
+    for _ in range(4000):
+        R = rng.standard_normal((3, 3)).astype(np.float32)
+        t = (rng.standard_normal((3, 1)) * 10).astype(np.float32)
+        want = cv2.gemm(R, t, -1.0, None, 0.0, flags=cv2.GEMM_1_T)
+        got = np.zeros((3, 1), np.float32)
+        flt = np.zeros((3, 1), np.float32)
+        for i in range(3):
+            s = 0.0
+            f = np.float32(0)
+            for k in range(3):
+                s = s + float(R[k, i]) * float(t[k, 0])
+                f = np.float32(f + np.float32(np.float32(-R[k, i]) * t[k, 0]))
+            got[i, 0] = np.float32(s * -1.0)
+            flt[i, 0] = f
+        assert np.array_equal(got, want)
+        n_float_form_differs += not np.array_equal(flt, want)
+    assert n_float_form_differs > 1000
+
+
+def test_norm_form_is_cv2s():
+    """dist3D = cv::norm(PO) (src/ORBmatcher.cc:1712): squares summed in double, left to right, double sqrt"""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(6)
+    for _ in range(4000):
+        v = (rng.standard_normal((3, 1)) * 10).astype(np.float32)
+        s = 0.0
+        for k in range(3):
+            s += float(v[k, 0]) * float(v[k, 0])
+        assert np.sqrt(s) == cv2.norm(v)
+
+
 def _three_maxima(sz):
     """ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1800-1843), line by line"""
     max1 = max2 = max3 = 0

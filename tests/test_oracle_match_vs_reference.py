@@ -94,3 +94,47 @@ def test_initialisation_matcher(kw, oracle_built, ref):
     a = ref.search_for_initialization(f1, f3, bounds, pv, 100, 0.9, True)
     b = oracle_built.search_for_initialization(f1, f3, bounds, pv, 100, 0.9, True)
     assert np.array_equal(a[0], b[0]) and a[2] == b[2] and np.array_equal(a[1], b[1])
+
+
+# ---- the relocalisation matcher: ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist),
+# ---- src/ORBmatcher.cc:1670-1798 ----
+
+def _compare_reloc(py, ref, tag, settings=((10.0, 100), (3.0, 64)), **kw):
+    cur, cam, bounds, scale, log_scale, kf, occupied = matchcase.make_reloc_case(**kw)
+    total = 0
+    for th, orb_dist in settings:
+        for ori in (True, False):
+            for occ in (occupied, None):
+                want, wnm = ref.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occ, th, orb_dist, ori)
+                got, nm = py.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occ, th, orb_dist, ori)
+                assert np.array_equal(got, want), f"{tag} th={th} dist={orb_dist} ori={ori}: {(got != want).sum()} slots differ"
+                assert nm == wnm, f"{tag} th={th} dist={orb_dist} ori={ori}: nmatches {nm} vs {wnm}"
+                if occ is not None:
+                    assert not (want[occ != 0] >= 0).any()
+                total += wnm
+    return total
+
+
+@pytest.mark.parametrize("seed,dz", [(1, 0.0), (2, 2.0), (3, -2.0)])
+def test_reloc_kitti(seed, dz, oracle_built, ref):
+    """the keyframe seen again from the same place, from 2 m ahead and 2 m behind (the predicted level moves)"""
+    assert _compare_reloc(oracle_built, ref, f"reloc kitti {seed} dz {dz}", seed=seed, dz=dz) > 1000
+
+
+def test_reloc_crowded(oracle_built, ref):
+    """three copies of every keyframe point: a slot taken by an earlier query is closed to every later one (:1735-1736)"""
+    _compare_reloc(oracle_built, ref, "reloc crowded", seed=4, copies=3, found_rate=0.1)
+
+
+def test_reloc_monocular_distorted(oracle_built, ref):
+    assert _compare_reloc(oracle_built, ref, "reloc tum", seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
+                          bf=40.0, stereo=False, nf=1000, dist_jitter=0.4) > 500
+
+
+def test_reloc_pose_looking_away(oracle_built, ref):
+    """no invzc < 0 test in this matcher: points behind the camera that project inside the image are searched (:1701-1710)"""
+    cur, cam, bounds, scale, log_scale, kf, occupied = matchcase.make_reloc_case(seed=9)
+    cur["Tcw"] = matchcase.compose(matchcase.pose(ry=np.pi), cur["Tcw"])
+    want, wnm = ref.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occupied, 10.0, 100, True)
+    got, nm = oracle_built.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occupied, 10.0, 100, True)
+    assert nm == wnm and np.array_equal(got, want)
