@@ -561,6 +561,51 @@ def matcher_section(ORBextractor, synth, local):
         out["local_map"] = loc
     except Exception as ex:
         out["local_map"] = f"unavailable ({type(ex).__name__}: {ex})"
+    # the relocalisation matcher ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist): the last
+    # frame as the keyframe, its map points with the scale-invariance distances of their own observation, 20 % of them
+    # already found and 15 % of the current slots set (tests/matchcase.py: make_reloc_case builds the same on the CPU)
+    try:
+        from oracle import pyoracle
+        import ctypes
+        import ctypes.util
+        libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
+        libm.logf.restype, libm.logf.argtypes = ctypes.c_float, [ctypes.c_float]
+        rng = np.random.default_rng(73)
+        n = len(last["mp_flags"])
+        Tl = T_last.astype(np.float64)
+        Ow = -Tl[:, :3].T @ Tl[:, 3]
+        d = np.linalg.norm(last["mp_xyz"].astype(np.float64) - Ow, axis=1)
+        sc = np.asarray(scale, np.float64)
+        max_d = d * sc[last["kps"]["octave"]] * rng.uniform(0.75, 1.25, n)
+        kf = {"flags": ((last["mp_flags"] & 1) | ((rng.random(n) < 0.05).astype(np.uint8) << 1)
+                        | ((rng.random(n) < 0.2).astype(np.uint8) << 2)).astype(np.uint8),
+              "xyz": last["mp_xyz"], "desc": last["mp_desc"], "dist": np.stack([max_d / sc[-1], max_d], 1).astype(np.float32),
+              "angle": last["kps"]["angle"].astype(np.float32)}
+        occ_r = (rng.random(len(cur["kps"])) < 0.15).astype(np.uint8)
+        rel = {"reference": "src/ORBmatcher.cc:1670-1798 (Tracking::Relocalization), MapPoint::PredictScale src/MapPoint.cc:575-590",
+               "config": "%d keyframe map points, %d already found, %d current slots set" % (
+                   int((kf["flags"] & 1).sum()), int(((kf["flags"] & 5) == 5).sum()), int(occ_r.sum()))}
+        for th, od in ((10.0, 100), (3.0, 64)):
+            for _ in range(10):
+                m, nm = ext.search_by_projection_keyframe(kf, cur["Tcw"], occ_r, th, od)
+            ts = []
+            for _ in range(100):
+                t1 = time.perf_counter()
+                m, nm = ext.search_by_projection_keyframe(kf, cur["Tcw"], occ_r, th, od)
+                ts.append((time.perf_counter() - t1) * 1e6)
+            tc = []
+            for _ in range(20):
+                t1 = time.perf_counter()
+                w, wnm = pyoracle.search_by_projection_kf(cur, cam, cur["bounds"], scale, libm.logf(float(np.float32(SCALE))), kf,
+                                                          occ_r, th, od, True)
+                tc.append((time.perf_counter() - t1) * 1e6)
+            rel["th_%d_dist_%d" % (int(th), od)] = {
+                "call_p50_us": float(np.percentile(ts, 50)), "nmatches": nm, "rounds": ext.match_rounds(),
+                "rescans": ext.match_rescans(), "cpu_p50_us_one_core": float(np.percentile(tc, 50)),
+                "parity_check": "identical" if (np.array_equal(m, w) and nm == wnm) else "MISMATCH"}
+        out["relocalisation"] = rel
+    except Exception as ex:
+        out["relocalisation"] = f"unavailable ({type(ex).__name__}: {ex})"
     # the whole per-frame front end of the tracking thread for a stereo frame, as one sequence through the host ABI:
     # both eyes extracted on two threads (+ undistortion / grid), stereo association, frame-to-frame matcher,
     # local-map matcher -- the current frame's keypoints, descriptors, grid and mvuRight never leave the device

@@ -225,6 +225,36 @@ typedef struct borb_map_points {
 int borb_search_local_points(borb_extractor *cur, int frame, const borb_map_points *mps, const uint8_t *occupied,
                              float th, float nnratio, unsigned flags, int32_t *match, int *n_cur, int *nmatches);
 
+/* -- relocalisation matcher: replaces ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF,
+ *    const set<MapPoint*> &sAlreadyFound, const float th, const int ORBdist) (src/ORBmatcher.cc:1670-1798), the second and
+ *    third search of Tracking::Relocalization (src/Tracking.cc: th 10 / ORBdist 100, then 3 / 64) ------------------- */
+
+/* The keyframe's map points as the matcher reads them: entry i is keyframe keypoint i.
+ *   flags[i]   bit 0: pKF->GetMapPointMatches()[i] != NULL, bit 1: that point isBad(), bit 2: it is in sAlreadyFound
+ *   xyz[3i..]  pMP->GetWorldPos(), desc[32i..] pMP->GetDescriptor() (read only where bit 0 is set)
+ *   dist[2i]   pMP->mfMinDistance, dist[2i + 1] pMP->mfMaxDistance -- the raw members: the 0.8f / 1.2f factors of
+ *              GetMinDistanceInvariance / GetMaxDistanceInvariance and MapPoint::PredictScale(dist3D, &CurrentFrame)
+ *              (src/MapPoint.cc:520-530, :575-590, with glibc's logf) are applied on the device
+ *   angle[i]   pKF->mvKeysUn[i].angle */
+typedef struct borb_keyframe_points {
+    int n;
+    const float *xyz;
+    const uint8_t *desc;
+    const uint8_t *flags;
+    const float *dist;
+    const float *angle;
+} borb_keyframe_points;
+
+/* CurrentFrame = frame `frame` of cur's last extract call (as borb_search_by_projection; mfLogScaleFactor and
+ * mnScaleLevels are the handle's).  Tcw_cur = CurrentFrame.mTcw rows 0-2.  occupied[i2], i2 < the frame's keypoint
+ * count: non-zero where CurrentFrame.mvpMapPoints[i2] is set on entry -- every set slot is skipped (:1735-1736), NULL =
+ * none set.  orb_dist in 0..255.  flags: BORB_MATCH_NO_ORIENTATION.  match[i2] = index of the keyframe keypoint whose map
+ * point this call puts into CurrentFrame.mvpMapPoints[i2], -1 where the slot keeps what it held; *nmatches = the return
+ * value. */
+int borb_search_by_projection_keyframe(borb_extractor *cur, int frame, const borb_keyframe_points *kf, const float *Tcw_cur,
+                                       const uint8_t *occupied, float th, int orb_dist, unsigned flags, int32_t *match,
+                                       int *n_cur, int *nmatches);
+
 /* -- monocular-initialisation matcher: replaces ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2,
  *    vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12, int windowSize)
  *    (src/ORBmatcher.cc:487-632), called by Tracking::MonocularInitialization (src/Tracking.cc:570-646) --- */
@@ -438,6 +468,10 @@ int borb_debug_describe(borb_extractor *h, const uint8_t *img, int cols, int row
 void borb_debug_set_match_rounds(int max_rounds);
 /* host evaluation of the device sin/cos routine (same inline function, host build) */
 void borb_debug_sincos(float radians, float *s, float *c);
+/* glibc's logf as the relocalisation matcher's level prediction uses it (csrc/orb_logf.cuh): the host copy and the
+ * device copy (one small kernel; allocates) */
+void borb_debug_logf(const float *x, float *y, int n);
+int borb_debug_logf_device(const float *x, float *y, int n);
 /* host evaluation of the per-pixel FAST score used by the cell kernel: 0 = not a FAST-9 corner at
  * threshold t_lo, else the largest threshold at which p still is one */
 int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo);

@@ -1545,7 +1545,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     if (n < 0 || (n > 0 && (!geo || !desc || !qflags || !octave))) return fail(BORB_ERR_ARG, "query arrays");
     if (use_stereo && (!cur->d_st_u || cur->stereo_gen != cur->extract_gen))
         return fail(BORB_ERR_STATE, "no stereo result for this handle's last extract call (run borb_stereo_match after it)");
-    for (int i = 0; i < n; ++i)
+    for (int i = 0; i < n && mode != 4; ++i) /* mode 4 predicts the level; its octave column carries mfMinDistance */
         if ((qflags[i] & 1) && (octave[i] < 0 || octave[i] >= cur->nlevels))
             return fail(BORB_ERR_ARG, "octave %d of query %d", octave[i], i);
     CU(cudaSetDevice(cur->device));
@@ -1637,6 +1637,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     if (tk_smem > 48 * 1024) {
         CU(cudaFuncSetAttribute(k_match_resolve<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
         CU(cudaFuncSetAttribute(k_match_resolve<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
+        CU(cudaFuncSetAttribute(k_match_resolve<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
     }
 #define MATCH_LAUNCH(MODE)                                                                                                   \
     do {                                                                                                                     \
@@ -1652,6 +1653,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     } while (0)
     if (mode == 1) MATCH_LAUNCH(1);
     else if (mode == 2) MATCH_LAUNCH(2);
+    else if (mode == 4) MATCH_LAUNCH(4);
     else {
         if (!cur->d_mt_cnt) {
             CU(cudaMalloc(&cur->d_mt_cnt, 2 * K * 4));
@@ -1737,6 +1739,54 @@ int borb_search_local_points(borb_extractor *cur, int frame, const borb_map_poin
     mp.nnratio = nnratio;
     return run_matcher(cur, frame, 2, mps->n, mps->proj, 4, mps->desc, mps->flags, mps->level, nullptr, occupied, mp,
                        (flags & BORB_MATCH_USE_STEREO) != 0, match, n_cur, nmatches);
+}
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1670-1798), the
+ * relocalisation matcher, against the device-resident results of frame `frame` of cur's last call.  The keyframe's map
+ * points become the queries of M1a / M1b in MODE 4 (k_match.cuh): every set slot is closed to every query, so all queries
+ * carry the "holds its slot" bit and the caller's occupancy bytes close the slots set on entry. */
+int borb_search_by_projection_keyframe(borb_extractor *cur, int frame, const borb_keyframe_points *kf, const float *Tcw_cur,
+                                       const uint8_t *occupied, float th, int orb_dist, unsigned flags, int32_t *match,
+                                       int *n_cur, int *nmatches)
+{
+    if (!cur || !kf || !Tcw_cur || !match) return fail(BORB_ERR_ARG, "null argument");
+    if (orb_dist < 0 || orb_dist > 255) return fail(BORB_ERR_ARG, "ORBdist %d: a 256-bit Hamming distance is 0..256 and the reference's best starts at 256", orb_dist);
+    if (kf->n > 0 && (!kf->xyz || !kf->desc || !kf->flags || !kf->dist || !kf->angle)) return fail(BORB_ERR_ARG, "keyframe arrays");
+    MatchParams mp;
+    std::memset(&mp, 0, sizeof mp);
+    std::memcpy(mp.Tc, Tcw_cur, 48);
+    mp.th = th;
+    mp.mono = 1;
+    mp.check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
+    mp.orb_dist = orb_dist;
+    mp.nlevels = cur->nlevels;
+    mp.log_scale = orb_logf_exact((float)cur->scale_factor); /* Frame: mfLogScaleFactor = log(mfScaleFactor), the float overload */
+    camera_centre(mp.Tc, mp.Ow);
+    const size_t n = (size_t)std::max(kf->n, 0);
+    std::vector<float> geo(4 * n);
+    std::vector<int32_t> mind(n);
+    std::vector<uint8_t> qf(n), occ;
+    for (size_t i = 0; i < n; ++i) {
+        geo[4 * i] = kf->xyz[3 * i]; geo[4 * i + 1] = kf->xyz[3 * i + 1]; geo[4 * i + 2] = kf->xyz[3 * i + 2];
+        geo[4 * i + 3] = kf->dist[2 * i + 1];
+        std::memcpy(&mind[i], &kf->dist[2 * i], 4);
+        qf[i] = ((kf->flags[i] & 1) && !(kf->flags[i] & 6)) ? 3 : 0; /* a query, and it closes the slot it takes */
+    }
+    if (occupied) { /* any set slot is skipped (:1735-1736): the kernels close the slots marked 2 */
+        if (!cur->have_plan || cur->last_n < 1 || frame < 0 || frame >= cur->last_n)
+            return fail(BORB_ERR_STATE, "no finished extract call holds frame %d", frame);
+        if (!cur->results_on_host && cur->nout_frame_on_host != frame) { /* the frame's keypoint count sizes the array */
+            CU(cudaSetDevice(cur->device));
+            CU(cudaMemcpyAsync(cur->h_nout + frame, cur->d_nout + frame, 4, cudaMemcpyDeviceToHost, cur->stream));
+            CU(cudaStreamSynchronize(cur->stream));
+            cur->nout_frame_on_host = frame;
+        }
+        const int nc0 = std::min(cur->h_nout[frame], cur->plan.kp_total);
+        occ.assign((size_t)cur->plan.kp_total, 0);
+        for (int i = 0; i < nc0; ++i) occ[i] = occupied[i] ? 2 : 0;
+    }
+    return run_matcher(cur, frame, 4, kf->n, geo.data(), 4, kf->desc, qf.data(), mind.data(), kf->angle,
+                       occupied ? occ.data() : nullptr, mp, false, match, n_cur, nmatches);
 }
 
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:487-632) */
@@ -1849,6 +1899,25 @@ int borb_debug_describe(borb_extractor *h, const uint8_t *img, int cols, int row
 }
 
 void borb_debug_sincos(float radians, float *s, float *c) { orb_sincosf_exact(radians, s, c); }
+void borb_debug_logf(const float *x, float *y, int n)
+{
+    for (int i = 0; i < n; ++i) y[i] = orb_logf_exact(x[i]);
+}
+int borb_debug_logf_device(const float *x, float *y, int n)
+{
+    if (n < 1 || !x || !y) return fail(BORB_ERR_ARG, "arguments");
+    float *d = nullptr;
+    CU(cudaMalloc(&d, (size_t)n * 4));
+    cudaError_t e = cudaMemcpy(d, x, (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_debug_logf<<<(n + 255) / 256, 256>>>(d, n);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(y, d, (size_t)n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(BORB_ERR_CUDA, "%s", cudaGetErrorString(e));
+    return BORB_OK;
+}
 void borb_debug_set_match_rounds(int max_rounds) { g_match_max_rounds = max_rounds > 0 ? max_rounds : 0; }
 int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_score_px(p, pitch, t_lo); }
 

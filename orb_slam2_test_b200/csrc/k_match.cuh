@@ -38,6 +38,7 @@
 
 #include "borb_internal.h"
 #include "k_describe.cuh" /* BorbKpRec */
+#include "orb_logf.cuh"
 
 #define MT_NT 1024
 #define MT_COLS 64
@@ -53,6 +54,9 @@ struct MatchParams {
     int dir; /* 1 forward, 2 backward, 0 neither: from tlc.z against mb (:1515-1526), evaluated on the host */
     int max_rounds; /* fixed-point rounds of M1b before the open suffix is finished sequentially (MT_MAX_ROUNDS) */
     float scale[BORB_MAXL];
+    /* MODE 4 (relocalisation matcher): camera centre Ow = -Rcw.t() * tcw, CurrentFrame.mfLogScaleFactor, mnScaleLevels, ORBdist */
+    float Ow[3], log_scale;
+    int nlevels, orb_dist;
 };
 
 __device__ __forceinline__ float mt_dot3(const float *row, const float *x)
@@ -106,7 +110,14 @@ struct MtQuery { /* what the candidate scan of one query needs (:1537-1572) */
  * MODE 2: the local-map matcher, ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:59-154) of
  *         Tracking::SearchLocalPoints: geo = mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos as
  *         Frame::isInFrustum left them, lvl = mnTrackScaleLevel; r = RadiusByViewingCos (:156-162), r *= th unless
- *         th == 1, window r * scale[lvl], octaves lvl-1 .. lvl (:72-79). */
+ *         th == 1, window r * scale[lvl], octaves lvl-1 .. lvl (:72-79).
+ * MODE 4: the relocalisation matcher, ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)
+ *         (src/ORBmatcher.cc:1670-1798): geo = world position and mfMaxDistance, `oct` = the BIT PATTERN of mfMinDistance
+ *         (this mode predicts the level, so the octave column carries the second distance).  Projection as MODE 1 but with
+ *         no invzc < 0 test (:1697-1705); dist3D = (float)cv::norm(x3Dw - Ow): squares summed in double, left to right,
+ *         double square root; 0.8f * mfMinDistance <= dist3D <= 1.2f * mfMaxDistance (:1711-1716); MapPoint::PredictScale
+ *         (src/MapPoint.cc:575-590): ceilf(logf(mfMaxDistance / dist3D) / mfLogScaleFactor) clamped to the levels, logf =
+ *         glibc's (orb_logf.cuh); window th * scale[level], octaves level-1 .. level+1. */
 template <int MODE>
 __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *__restrict__ l_geo, int oct, int i,
                                             float min_x, float max_x, float min_y, float max_y, float winv, float hinv)
@@ -125,6 +136,30 @@ __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *
         else if (mp.dir == 2) { Q.min_level = 0; Q.max_level = oct; }
         else { Q.min_level = oct - 1; Q.max_level = oct + 1; }
         Q.ur = fmaf(-mp.mbf, invzc, Q.u);
+    } else if (MODE == 4) {
+        const float X[3] = {g.x, g.y, g.z};
+        const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7], zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
+        const float invzc = 1.0f / zc;
+        Q.u = fmaf(mp.fx * xc, invzc, mp.cx);
+        Q.v = fmaf(mp.fy * yc, invzc, mp.cy);
+        Q.ok = !(Q.u < min_x || Q.u > max_x) && !(Q.v < min_y || Q.v > max_y);
+        double s2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float po = X[k] - mp.Ow[k];
+            s2 = __dadd_rn(s2, __dmul_rn((double)po, (double)po));
+        }
+        const float dist3D = (float)__dsqrt_rn(s2);
+        const float max_d = 1.2f * g.w, min_d = 0.8f * __int_as_float(oct);
+        Q.ok = Q.ok && !(dist3D < min_d || dist3D > max_d);
+        const float ratio = g.w / dist3D;
+        int lvl = orb_cvtt_x86(ceilf(orb_logf_exact(ratio) / mp.log_scale));
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= mp.nlevels) lvl = mp.nlevels - 1;
+        Q.radius = mp.th * mp.scale[lvl];
+        Q.min_level = lvl - 1;
+        Q.max_level = lvl + 1;
+        Q.ur = 0.f;
     } else if (MODE == 3) { /* SearchForInitialization: window of windowSize (= mp.th) around vbPrevMatched, level 0 only (:510) */
         Q.radius = mp.th;
         Q.u = g.x;
@@ -283,18 +318,21 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
 #pragma unroll
                 for (int k = 0; k < MT_K; ++k) held_by[k] = keys[k] != MT_NOKEY ? tk[keys[k] & 0xffffu] : 0x7fffffff;
             }
-            if (MODE == 1) {
+            if (MODE == 1 || MODE == 4) {
+                /* MODE 4: every set slot is closed (:1735-1736; the host sets the "observations" bit of every query) and
+                 * the acceptance threshold is the caller's ORBdist (:1750) */
+                const uint32_t th_d = MODE == 4 ? (uint32_t)mp.orb_dist : (uint32_t)MT_TH_HIGH;
                 bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
 #pragma unroll
                 for (int k = 0; k < MT_K; ++k) {
                     if (!all_held) continue;
                     const uint32_t key = keys[k];
-                    if (key == MT_NOKEY || (key >> 16) > MT_TH_HIGH) { all_held = false; continue; }
+                    if (key == MT_NOKEY || (key >> 16) > th_d) { all_held = false; continue; }
                     if (held_by[k] >= i) { ch = (int)(key & 0xffffu); all_held = false; }
                 }
                 if (all_held && more[i]) { /* rare: walk the cells again, now with the holders known */
                     atomicAdd(&s_rescans, 1);
-                    const MtQuery Q = mt_query<1>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+                    const MtQuery Q = mt_query<MODE == 4 ? 4 : 1>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
                     const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
                     int best = 256, best_idx = -1;
                     for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
@@ -306,7 +344,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                             if (d >= 0 && d < best) { best = d; best_idx = i2; }
                         }
                     }
-                    ch = best <= MT_TH_HIGH ? best_idx : -1;
+                    ch = best <= (int)th_d ? best_idx : -1;
                 }
             } else {
                 /* best and second best among the candidates nobody earlier holds (:84-115): the first two free
@@ -398,11 +436,11 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
         if (ch >= 0) {
             atomicAdd(&s_nm, 1);
             atomicMax(&match[ch], i);
-            if (MODE == 1 && mp.check_ori) atomicAdd(&s_hist[mt_bin(l_angle[i], kp[ch].angle)], 1);
+            if ((MODE == 1 || MODE == 4) && mp.check_ori) atomicAdd(&s_hist[mt_bin(l_angle[i], kp[ch].angle)], 1);
         }
     }
     __syncthreads();
-    if (MODE == 1 && mp.check_ori) {
+    if ((MODE == 1 || MODE == 4) && mp.check_ori) {
         if (tid == 0) {
             int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
             for (int b = 0; b < MT_HISTO; ++b) {
@@ -564,6 +602,13 @@ k_match_resolve_init(const __grid_constant__ MatchParams mp, const BorbKpRec *__
     }
     __syncthreads();
     if (tid == 0) { nm[0] = s_nm; nm[1] = round + 1; nm[2] = s_rescans; nm[3] = 0; }
+}
+
+/* tap for tests/test_logf.py: the device copy of orb_logf_exact, in place */
+__global__ void k_debug_logf(float *x, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] = orb_logf_exact(x[i]);
 }
 
 #endif

@@ -54,6 +54,8 @@ SYMBOLS += ["borb_undistort_grid_noalloc"]
 # bag of words: Frame::ComputeBoW and ORBmatcher::SearchByBoW(KeyFrame*, Frame&)
 SYMBOLS += ["borb_voc_load_text", "borb_voc_create", "borb_voc_destroy", "borb_voc_info", "borb_voc_transform",
             "borb_compute_bow", "borb_bow_result", "borb_search_by_bow"]
+# the relocalisation matcher ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) and its logf taps
+SYMBOLS += ["borb_search_by_projection_keyframe", "borb_debug_logf", "borb_debug_logf_device"]
 
 
 class BorbError(RuntimeError):
@@ -128,6 +130,11 @@ def load_library() -> C.CDLL:
     lib.borb_search_local_points.argtypes = [_vp, C.c_int, _vp, _vp, C.c_float, C.c_float, C.c_uint, _vp,
                                              C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.borb_search_for_initialization.argtypes = [_vp, C.c_int, _vp, _vp, C.c_int, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
+    lib.borb_search_by_projection_keyframe.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, C.c_uint, _vp,
+                                                       C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_debug_logf.argtypes = [_vp, _vp, C.c_int]
+    lib.borb_debug_logf.restype = None
+    lib.borb_debug_logf_device.argtypes = [_vp, _vp, C.c_int]
     lib.borb_match_rounds.argtypes = [_vp]
     lib.borb_max_keypoints.argtypes = [_vp]
     lib.borb_stereo_result.argtypes = [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_int),
@@ -158,6 +165,18 @@ def debug_sincos(radians: float):
     return s.value, c.value
 
 
+def debug_logf(x: np.ndarray, device: bool = False) -> np.ndarray:
+    """csrc/orb_logf.cuh (glibc's logf restated): the host copy, or the device copy through one small kernel"""
+    lib = load_library()
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.empty_like(x)
+    if device:
+        _check(lib, lib.borb_debug_logf_device(x.ctypes.data, y.ctypes.data, len(x)))
+    else:
+        lib.borb_debug_logf(x.ctypes.data, y.ctypes.data, len(x))
+    return y
+
+
 class _InitFrame(C.Structure):  # == borb_init_frame
     _fields_ = [("n", C.c_int), ("octave", _vp), ("angle", _vp), ("desc", _vp)]
 
@@ -169,6 +188,10 @@ class _MapPoints(C.Structure):  # == borb_map_points
 class _LastFrame(C.Structure):  # == borb_last_frame
     _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("octave", _vp), ("angle", _vp),
                 ("Tcw", _vp)]
+
+
+class _KeyFramePoints(C.Structure):  # == borb_keyframe_points
+    _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("dist", _vp), ("angle", _vp)]
 
 
 class _KeyFrame(C.Structure):  # == borb_keyframe
@@ -513,6 +536,26 @@ class ORBextractor:
         _check(self._lib, self._lib.borb_search_local_points(self._h, frame, C.addressof(mp), occ.ctypes.data if occ is not None else None,
                                                              th, nnratio, 4 if use_stereo else 0, out.ctypes.data,
                                                              C.byref(n), C.byref(nm)))
+        return out[:n.value].copy(), nm.value
+
+    def search_by_projection_keyframe(self, kf: dict, Tcw_cur, occupied=None, th: float = 10.0, orb_dist: int = 100,
+                                      frame: int = 0, check_orientation: bool = True):
+        """The relocalisation matcher ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)
+        (src/ORBmatcher.cc:1670-1798) with frame `frame` of this extractor's last call as CurrentFrame, on the device.
+        kf: dict with flags [n] u8 (bit 0 map point, bit 1 bad, bit 2 already found), xyz [n,3] f32, desc [n,32] u8,
+        dist [n,2] f32 (mfMinDistance, mfMaxDistance), angle [n] f32; occupied [n_cur] u8 or None.
+        -> (match [n_cur] i32: keyframe keypoint whose map point the slot receives or -1, nmatches)."""
+        keep = [np.ascontiguousarray(kf["xyz"], np.float32), np.ascontiguousarray(kf["desc"], np.uint8),
+                np.ascontiguousarray(kf["flags"], np.uint8), np.ascontiguousarray(kf["dist"], np.float32),
+                np.ascontiguousarray(kf["angle"], np.float32)]
+        rec = _KeyFramePoints(len(keep[2]), *[a.ctypes.data for a in keep])
+        T = np.ascontiguousarray(Tcw_cur, np.float32)
+        occ = np.ascontiguousarray(occupied, np.uint8) if occupied is not None else None
+        out = np.full(max(self._lib.borb_max_keypoints(self._h), 1), -1, np.int32)
+        n, nm = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_search_by_projection_keyframe(
+            self._h, frame, C.addressof(rec), T.ctypes.data, occ.ctypes.data if occ is not None else None, th, orb_dist,
+            0 if check_orientation else 2, out.ctypes.data, C.byref(n), C.byref(nm)))
         return out[:n.value].copy(), nm.value
 
     def search_for_initialization(self, f1: dict, prev, window: int = 100, nnratio: float = 0.9, frame: int = 0,

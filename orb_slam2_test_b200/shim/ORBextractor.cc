@@ -211,6 +211,26 @@ int ORBextractor::SearchLocalPoints(int nPoints, const float *proj, const unsign
     return nmatches;
 }
 
+int ORBextractor::SearchByProjectionKF(const cv::Mat &TcwCur, int nKF, const float *worldPos, const unsigned char *mpDescriptors,
+                                       const unsigned char *flags, const float *minMaxDistance, const float *angle,
+                                       const unsigned char *occupied, float th, int ORBdist, bool checkOrientation,
+                                       std::vector<int> &vnMatches)
+{
+    assert(TcwCur.rows == 4 && TcwCur.cols == 4 && TcwCur.type() == CV_32F);
+    float tc[12];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) tc[4 * r + c] = TcwCur.at<float>(r, c);
+    borb_keyframe_points kf;
+    kf.n = nKF; kf.xyz = worldPos; kf.desc = mpDescriptors; kf.flags = flags; kf.dist = minMaxDistance; kf.angle = angle;
+    vnMatches.assign((size_t)borb_max_keypoints(handle), -1);
+    int n = 0, nmatches = 0;
+    check(borb_search_by_projection_keyframe(handle, 0, &kf, tc, occupied, th, ORBdist,
+                                             checkOrientation ? 0u : BORB_MATCH_NO_ORIENTATION, vnMatches.data(), &n, &nmatches),
+          "search by projection (keyframe)");
+    vnMatches.resize((size_t)n);
+    return nmatches;
+}
+
 int ORBextractor::SearchForInitialization(const std::vector<cv::KeyPoint> &F1KeysUn, const cv::Mat &F1Descriptors,
                                           std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12,
                                           int windowSize, float nnRatio, bool checkOrientation)

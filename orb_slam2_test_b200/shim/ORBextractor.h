@@ -150,6 +150,17 @@ public:
     int SearchLocalPoints(int nPoints, const float *proj, const unsigned char *mpDescriptors, const unsigned char *flags,
                           const int *level, const unsigned char *occupied, float th, float nnRatio, bool useStereo,
                           std::vector<int> &vnMatches);
+    // ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist)
+    // (reference src/ORBmatcher.cc:1670-1798, the second and third search of Tracking::Relocalization) on the device,
+    // *this = CurrentFrame's left extractor after its operator() call (SetCamera on).  Entry i = keyframe keypoint i:
+    // flags bit 0 = GetMapPointMatches()[i] != NULL, bit 1 = isBad(), bit 2 = member of sAlreadyFound; GetWorldPos(),
+    // GetDescriptor(), minMaxDistance[2i] = mfMinDistance, [2i + 1] = mfMaxDistance, angle[i] = pKF->mvKeysUn[i].angle;
+    // occupied[i2] != 0 where CurrentFrame.mvpMapPoints[i2] is set on entry (may be NULL).
+    // vnMatches[i2] = i put into CurrentFrame.mvpMapPoints[i2] by this call, -1 = slot unchanged; returns nmatches.
+    int SearchByProjectionKF(const cv::Mat &TcwCur, int nKF, const float *worldPos, const unsigned char *mpDescriptors,
+                             const unsigned char *flags, const float *minMaxDistance, const float *angle,
+                             const unsigned char *occupied, float th, int ORBdist, bool checkOrientation,
+                             std::vector<int> &vnMatches);
     // ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (reference
     // src/ORBmatcher.cc:487-632, Tracking::MonocularInitialization) on the device, *this = F2's extractor after its
     // operator() call (SetCamera on).  F1 arrives as its mvKeysUn (octave, angle) and descriptors (CV_8U, n x 32).

@@ -49,8 +49,28 @@ INIT_CASES = {
 }
 
 
+# name -> (make_reloc_case kwargs, (th, ORBdist) settings): the relocalisation matcher
+# ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), orientation check on and off
+RELOC_CASES = {
+    "reloc_kitti": (dict(seed=22), ((10.0, 100), (3.0, 64))),
+    "reloc_kitti_ahead": (dict(seed=23, dz=2.0), ((10.0, 100),)),
+    "reloc_kitti_crowded": (dict(seed=24, copies=3, found_rate=0.1), ((10.0, 100), (3.0, 64))),
+    "reloc_tum_mono": (dict(seed=25, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False,
+                            nf=1000, dist_jitter=0.4), ((10.0, 100),)),
+}
+
+
 def main():
     out = {}
+    for name, (kw, settings) in RELOC_CASES.items():
+        cur, cam, bounds, scale, log_scale, kf, occ = matchcase.make_reloc_case(**kw)
+        for th, od in settings:
+            for ori in (1, 0):
+                m, nm = RefMatcher.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occ, th, od, bool(ori))
+                key = f"{name}_th{int(th)}_d{od}_ori{ori}"
+                out[key + "_match"] = m
+                out[key + "_nm"] = np.array([nm, len(kf["flags"]), int((m >= 0).sum())], np.int32)
+                print(key, "nmatches", nm, "slots", int((m >= 0).sum()))
     for name, (kw, wins) in INIT_CASES.items():
         f1, f2, bounds, prev = matchcase.make_init_case(**kw)
         for win in wins:

@@ -194,5 +194,11 @@ def make_reloc_case(seed=0, copies=1, found_rate=0.2, bad_rate=0.05, occupied_ra
     kf = {"flags": flags, "xyz": last["mp_xyz"], "desc": last["mp_desc"],
           "dist": np.stack([min_d, max_d], 1).astype(np.float32), "angle": last["kps"]["angle"].astype(np.float32)}
     occupied = (rng.random(len(cur["kps"])) < occupied_rate).astype(np.uint8)
-    log_scale = np.float32(np.log(np.float32(1.2)))  # Frame: mfLogScaleFactor = log(mfScaleFactor), float
+    # Frame: mfLogScaleFactor = log(mfScaleFactor) on floats = the host libm's logf
+    import ctypes
+    import ctypes.util
+    libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
+    libm.logf.restype = ctypes.c_float
+    libm.logf.argtypes = [ctypes.c_float]
+    log_scale = libm.logf(float(np.float32(1.2)))
     return cur, cam, bounds, scale, float(log_scale), kf, occupied

@@ -232,6 +232,54 @@ static int match_mode(char **argv)
     return 0;
 }
 
+/* `reloc` mode: the relocalisation matcher through the shim (reference src/ORBmatcher.cc:1670-1798).  argv: reloc cur.raw
+ * cols rows nfeatures kf.bin out.bin; kf.bin = int32 n, n_occ, float K[4], th, int32 ORBdist, float TcwCur[16], then
+ * xyz[3n], desc[32n], flags[n], dist[2n], angle[n], occupied[n_occ] (the arrays of include/borb.h: borb_keyframe_points).
+ * out.bin = int32 nmatches, n_cur, then n_cur int32 matches. */
+static int reloc_mode(char **argv)
+{
+    const int cols = atoi(argv[3]), rows = atoi(argv[4]), nFeatures = atoi(argv[5]);
+    vector<unsigned char> im = slurp(argv[2], (size_t)cols * rows);
+    cv::Mat image(rows, cols, CV_8UC1, im.data());
+    FILE *in = fopen(argv[6], "rb");
+    if (!in) return 2;
+    int n = 0, nocc = 0, orbDist = 0;
+    float K4[4], th, tc[16];
+    if (fread(&n, 4, 1, in) != 1 || fread(&nocc, 4, 1, in) != 1 || fread(K4, 4, 4, in) != 4 || fread(&th, 4, 1, in) != 1 ||
+        fread(&orbDist, 4, 1, in) != 1 || fread(tc, 4, 16, in) != 16)
+        return 2;
+    vector<float> xyz((size_t)3 * n), dist((size_t)2 * n), angle((size_t)n);
+    vector<unsigned char> desc((size_t)32 * n), flags((size_t)n), occupied((size_t)nocc);
+    if (fread(xyz.data(), 4, xyz.size(), in) != xyz.size() || fread(desc.data(), 1, desc.size(), in) != desc.size() ||
+        fread(flags.data(), 1, flags.size(), in) != flags.size() || fread(dist.data(), 4, dist.size(), in) != dist.size() ||
+        fread(angle.data(), 4, angle.size(), in) != angle.size() || fread(occupied.data(), 1, occupied.size(), in) != occupied.size())
+        return 2;
+    fclose(in);
+    cv::Mat K(3, 3, CV_32F), DistCoef(4, 1, CV_32F), TcwCur(4, 4, CV_32F);
+    memset(K.data, 0, 36);
+    memset(DistCoef.data, 0, 16);
+    K.at<float>(0, 0) = K4[0]; K.at<float>(1, 1) = K4[1]; K.at<float>(0, 2) = K4[2]; K.at<float>(1, 2) = K4[3]; K.at<float>(2, 2) = 1.f;
+    memcpy(TcwCur.data, tc, 64);
+    ORBextractor ext(nFeatures, 1.2f, 8, 20, 7);
+    ext.SetCamera(K, DistCoef);
+    vector<cv::KeyPoint> keys;
+    cv::Mat descriptors;
+    ext(image, cv::Mat(), keys, descriptors);
+    if ((int)keys.size() != nocc) return 3;
+    vector<int> vnMatches;
+    const int nmatches = ext.SearchByProjectionKF(TcwCur, n, xyz.data(), desc.data(), flags.data(), dist.data(), angle.data(),
+                                                  occupied.data(), th, orbDist, true, vnMatches);
+    FILE *f = fopen(argv[7], "wb");
+    if (!f) return 2;
+    int nc = (int)vnMatches.size();
+    fwrite(&nmatches, 4, 1, f);
+    fwrite(&nc, 4, 1, f);
+    fwrite(vnMatches.data(), 4, vnMatches.size(), f);
+    fclose(f);
+    printf("frame_like reloc ok\n");
+    return 0;
+}
+
 /* `init` mode: ORBmatcher::SearchForInitialization through the shim (reference src/ORBmatcher.cc:487-632).  argv: init
  * image cols rows nfeatures f1.bin out.bin; f1.bin = int32 n, window, float nnratio, then octave[n] (int32), angle[n],
  * desc[32n], prev[2n].  The image is the CURRENT frame (the mpIniORBextractor instance, TUM1 camera); out.bin = int32
@@ -347,6 +395,7 @@ int main(int argc, char **argv)
 {
     if (argc == 9 && !strcmp(argv[1], "bow")) return bow_mode(argv);
     if (argc == 8 && !strcmp(argv[1], "init")) return init_mode(argv);
+    if (argc == 8 && !strcmp(argv[1], "reloc")) return reloc_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "match")) return match_mode(argv);
     if (argc == 9 && !strcmp(argv[1], "pre")) return pre_mode(argv);
     if (argc != 7) { fprintf(stderr, "usage: %s left right cols rows nfeatures out\n", argv[0]); return 2; }

@@ -11,7 +11,7 @@ import matchcase
 
 HERE = Path(__file__).resolve().parent
 sys.path.insert(0, str(HERE / "golden"))
-from make_golden_match import CASES, INIT_CASES, LOCAL_CASES  # noqa: E402
+from make_golden_match import CASES, INIT_CASES, LOCAL_CASES, RELOC_CASES  # noqa: E402
 
 
 def _golden():
@@ -120,3 +120,34 @@ def test_cuda_reproduces_the_reference_initialisation_matcher(name, oracle_built
         key = f"{name}_w{win}"
         assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
         assert np.array_equal(pv.view(np.uint32), g[key + "_prev"].view(np.uint32)), key
+
+
+@pytest.mark.parametrize("name", sorted(RELOC_CASES))
+def test_oracle_reproduces_the_reference_relocalisation_matcher(name, oracle_built):
+    g = _golden()
+    kw, settings = RELOC_CASES[name]
+    cur, cam, bounds, scale, log_scale, kf, occ = matchcase.make_reloc_case(**kw)
+    for th, od in settings:
+        for ori in (1, 0):
+            m, nm = oracle_built.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occ, th, od, bool(ori))
+            key = f"{name}_th{int(th)}_d{od}_ori{ori}"
+            assert len(kf["flags"]) == g[key + "_nm"][1], "the scenario is not the one the golden file was made from"
+            assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(RELOC_CASES))
+def test_cuda_reproduces_the_reference_relocalisation_matcher(name, oracle_built):
+    from orb_slam2_test_b200 import ORBextractor, synth
+    g = _golden()
+    kw, settings = RELOC_CASES[name]
+    cur, cam, bounds, scale, log_scale, kf, occ = matchcase.make_reloc_case(**kw)
+    shape, seed, nf = kw.get("shape", synth.KITTI_SHAPE), kw["seed"], kw.get("nf", 2000)
+    ext = ORBextractor(nf, 1.2, 8, 20, 7)
+    ext.set_camera(kw.get("K", matchcase.KITTI_K), kw.get("dist", (0.0, 0.0, 0.0, 0.0)))
+    ext(synth.make_frame(shape, seed=seed, frame=1, eye=0))
+    for th, od in settings:
+        for ori in (1, 0):
+            m, nm = ext.search_by_projection_keyframe(kf, cur["Tcw"], occ, th, od, check_orientation=bool(ori))
+            key = f"{name}_th{int(th)}_d{od}_ori{ori}"
+            assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key

@@ -217,3 +217,83 @@ def test_initialisation_matcher_take_overs(copies, oracle_built):
     one takes it over (:552-558), an equal or worse one is skipped (:526-527).  With 48 copies a keypoint has up to
     48 choosers in a round (repetitive texture): the chooser lists have no length limit."""
     _check_init(f"init x{copies}", oracle_built, windows=(100, 40), seed=9, copies=copies)
+
+
+# ---- the relocalisation matcher: ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist),
+# ---- src/ORBmatcher.cc:1670-1798 (borb_search_by_projection_keyframe) ----
+
+def _check_reloc(tag, oracle, settings=((10.0, 100), (3.0, 64)), look_away=False, **kw):
+    cur, cam, bounds, scale, log_scale, kf, occupied = matchcase.make_reloc_case(**kw)
+    if look_away:
+        cur["Tcw"] = matchcase.compose(matchcase.pose(ry=np.pi), cur["Tcw"])
+    ext, _ = _gpu_frame(kw.get("shape", synth.KITTI_SHAPE), kw.get("seed", 0), kw.get("frame", 0) + 1,
+                        kw.get("K", matchcase.KITTI_K), kw.get("dist", (0.0, 0.0, 0.0, 0.0)), False, kw.get("nf", 2000), 0.0, 0.0)
+    kps, desc = ext.result(0)
+    assert kps.tobytes() == cur["kps"].tobytes() and np.array_equal(desc, cur["desc"]), f"{tag}: current frame differs"
+    total = 0
+    for th, od in settings:
+        for ori in (True, False):
+            for occ in (occupied, None):
+                want, wnm = oracle.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occ, th, od, ori)
+                got, nm = ext.search_by_projection_keyframe(kf, cur["Tcw"], occ, th, od, check_orientation=ori)
+                assert len(got) == len(want)
+                bad = np.nonzero(got != want)[0]
+                assert bad.size == 0, f"{tag} th={th} d={od} ori={ori}: {bad.size} slots differ, e.g. {bad[:5]}: {got[bad[:5]]} vs {want[bad[:5]]}"
+                assert nm == wnm, f"{tag} th={th} d={od}: nmatches {nm} vs {wnm}"
+                total += nm
+    return total, ext
+
+
+@pytest.mark.parametrize("seed,dz", [(1, 0.0), (2, 2.0), (3, -2.0), (6, 0.7)])
+def test_relocalisation_matcher_kitti(seed, dz, oracle_built):
+    assert _check_reloc(f"reloc kitti {seed} dz {dz}", oracle_built, seed=seed, dz=dz)[0] > 1000
+
+
+def test_relocalisation_matcher_crowded_and_the_sequential_finish(oracle_built):
+    """three and twelve copies of every keyframe point (a taken slot is closed to every later query, :1735-1736); with the
+    round limit lowered the open suffix is walked by one thread in the reference's order"""
+    from orb_slam2_test_b200.extractor import load_library
+    lib = load_library()
+    _check_reloc("reloc crowded x3", oracle_built, seed=4, copies=3, found_rate=0.1)
+    try:
+        lib.borb_debug_set_match_rounds(2)
+        _, ext = _check_reloc("reloc crowded x12, 2 rounds", oracle_built, settings=((10.0, 100),), seed=5, copies=12,
+                              found_rate=0.0, bad_rate=0.0)
+        assert ext.match_rounds() == 3
+    finally:
+        lib.borb_debug_set_match_rounds(0)
+
+
+def test_relocalisation_matcher_monocular_tum_with_distortion(oracle_built):
+    assert _check_reloc("reloc tum", oracle_built, seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
+                        bf=40.0, stereo=False, nf=1000, dist_jitter=0.4)[0] > 500
+
+
+def test_relocalisation_matcher_pose_looking_away(oracle_built):
+    """this matcher has no invzc < 0 test: points behind the camera that project inside the image are searched"""
+    _check_reloc("reloc away", oracle_built, settings=((10.0, 100),), look_away=True, seed=9)
+
+
+def test_relocalisation_matcher_empty_and_argument_errors(oracle_built):
+    from orb_slam2_test_b200 import BorbError
+    cur, cam, bounds, scale, log_scale, kf, occupied = matchcase.make_reloc_case(seed=1)
+    ext, _ = _gpu_frame(synth.KITTI_SHAPE, 1, 1, matchcase.KITTI_K, (0.0, 0.0, 0.0, 0.0), False, 2000, 0.0, 0.0)
+    none = {k: v[:0] for k, v in kf.items()}
+    m, nm = ext.search_by_projection_keyframe(none, cur["Tcw"], occupied)
+    assert nm == 0 and (m == -1).all() and len(m) == len(cur["kps"])
+    nothing = dict(kf)
+    nothing["flags"] = kf["flags"] | 2  # every point bad
+    m, nm = ext.search_by_projection_keyframe(nothing, cur["Tcw"], None)
+    assert nm == 0 and (m == -1).all()
+    everything_taken = np.ones(len(cur["kps"]), np.uint8)
+    m, nm = ext.search_by_projection_keyframe(kf, cur["Tcw"], everything_taken)
+    assert nm == 0 and (m == -1).all()
+    for bad_dist in (-1, 256):
+        with pytest.raises(BorbError):
+            ext.search_by_projection_keyframe(kf, cur["Tcw"], None, 10.0, bad_dist)
+    with pytest.raises(BorbError):
+        ext.search_by_projection_keyframe(kf, cur["Tcw"], None, frame=3)
+    no_cam = __import__("orb_slam2_test_b200").ORBextractor(2000, 1.2, 8, 20, 7)
+    no_cam(synth.make_frame(synth.KITTI_SHAPE, seed=1, frame=1, eye=0))
+    with pytest.raises(BorbError):
+        no_cam.search_by_projection_keyframe(kf, cur["Tcw"], None)

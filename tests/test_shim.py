@@ -208,6 +208,32 @@ def test_frame_to_frame_matcher_through_the_shim(tmp_path, oracle_built):
 
 
 @pytest.mark.gpu
+def test_relocalisation_matcher_through_the_shim(tmp_path, oracle_built):
+    """ORBextractor::SearchByProjectionKF (shim) = ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th,
+    ORBdist) restated (oracle/match_oracle.cpp, pinned to the reference's ORBmatcher.cc): the Frame-like caller extracts the
+    current frame and matches a keyframe's map points against it."""
+    import matchcase
+    _build()
+    cur, cam, bounds, scale, log_scale, kf, occ = matchcase.make_reloc_case(seed=35, copies=2)
+    shape = synth.KITTI_SHAPE
+    (tmp_path / "cur.raw").write_bytes(synth.make_frame(shape, seed=35, frame=1, eye=0).tobytes())
+    n = len(kf["flags"])
+    T4 = np.vstack([cur["Tcw"], [0, 0, 0, 1]]).astype("<f4")
+    blob = struct.pack("<ii4ffi", n, len(occ), *matchcase.KITTI_K, 10.0, 100) + T4.tobytes()
+    blob += kf["xyz"].astype("<f4").tobytes() + kf["desc"].tobytes() + kf["flags"].tobytes()
+    blob += kf["dist"].astype("<f4").tobytes() + kf["angle"].astype("<f4").tobytes() + occ.tobytes()
+    (tmp_path / "kf.bin").write_bytes(blob)
+    r = subprocess.run([str(EXE), "reloc", str(tmp_path / "cur.raw"), str(shape[1]), str(shape[0]), "2000",
+                        str(tmp_path / "kf.bin"), str(tmp_path / "r.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    buf = (tmp_path / "r.bin").read_bytes()
+    nm, nc = struct.unpack_from("<ii", buf, 0)
+    got = np.frombuffer(buf, "<i4", nc, 8)
+    want, wnm = oracle_built.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occ, 10.0, 100, True)
+    assert nc == len(want) and np.array_equal(got, want) and nm == wnm and nm > 300
+
+
+@pytest.mark.gpu
 def test_initialisation_matcher_through_the_shim(tmp_path, oracle_built):
     """ORBextractor::SearchForInitialization (shim) = ORBmatcher::SearchForInitialization restated (pinned to the
     reference's ORBmatcher.cc): the Frame-like caller extracts the current frame with the initialisation extractor and
