@@ -1181,7 +1181,7 @@ def run_ours(args, rank, world, local):
                                          "what a stock Frame.cc caller of mvImagePyramid pays"},
                 "how": f"{n_streams} library feeder rings (borb_stream_*) x {slots} slots x {sub}-frame batches: upload, kernel and "
                        f"download streams per ring, page-locked host memory uploaded in place, wall clock between barriers, max over "
-                       f"ranks; link ceiling = plain cudaMemcpyAsync of the same sizes on every rank at once, no kernels; {numa_note}"},
+                       f"ranks; link ceiling = plain cudaMemcpyAsync of the same sizes on every rank at once on two upload + two download streams (as the two rings), best of 3 runs, no kernels; {numa_note}"},
         "gpu_launches": args.steps * launches_per_call,
         "roofline": {"bound": "hbm", "kernel": STAGE_KERNEL[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(STAGE_KERNEL[dom], F), "peak_source": peak_src,

@@ -2,7 +2,8 @@
 """Aggregate host<->device copy ceiling of the box at N = 1/2/4/8 GPUs.
 
 Every rank loops plain cudaMemcpyAsync of the host-fed extraction loop's exact sizes (one 128-frame KITTI
-batch = 59.7 MB page-locked -> device, its results = 15.6 MB device -> page-locked, two streams, no
+batch = 59.7 MB page-locked -> device, its results = 15.6 MB device -> page-locked, two upload and two download streams
+(the feeder's two rings), best of three runs, no
 kernels; orb_slam2_test_b200/hostlink.py); rank 0 prints one JSON line per N with the aggregate GB/s
 (total bytes / slowest rank's time) and what that allows in frames/s.
 
@@ -49,7 +50,7 @@ def one(args):
                 "aggregate_h2d_alone_GBps": world * args.h2d * it / up / 1e9,
                 "aggregate_d2h_alone_GBps": world * args.d2h * it / down / 1e9 if down > 0 else None,
                 "frames_per_s_ceiling": world * SUB * it / both * (args.h2d / H2D),
-                "how": "plain copies, two streams per rank, no kernels; time = slowest rank (barrier before and after)"}
+                "how": "plain copies, two upload + two download streams per rank (as the two feeder rings), best of 3 runs, no kernels; time = slowest rank (barrier before and after)"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
