@@ -418,6 +418,14 @@ typedef struct borb_keyframe {
 int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, float nnratio, unsigned flags,
                        int32_t *match, int *n_cur, int *nmatches);
 
+/* ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (src/ORBmatcher.cc:634-777;
+ * LoopClosing::ComputeSim3): both keyframes as flat arrays (their mFeatVec e.g. from borb_voc_transform), matched on the
+ * vocabulary's device with its stream and scratch -- one call at a time per vocabulary.  match12 [kf1->n]: per pKF1
+ * keypoint the index of the pKF2 keypoint whose map point vpMatches12 receives, or -1; *nmatches = the return value.
+ * Up to 65535 keypoints per keyframe. */
+int borb_voc_search_by_bow(borb_vocabulary *v, const borb_keyframe *kf1, const borb_keyframe *kf2, float nnratio,
+                           unsigned flags, int32_t *match12, int *nmatches);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

@@ -156,4 +156,44 @@ int refbow_search_by_bow(void *v, int n_kf, const uint8_t *kf_kps, const uint8_t
     return nm;
 }
 
+/* ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (src/ORBmatcher.cc:634-777, the
+ * matcher of LoopClosing::ComputeSim3).  Both keyframes as refbow_search_by_bow's keyframe side; their feature vectors are
+ * computed here with the reference transform.  out_match12[i1] = index of the pKF2 keypoint whose map point pKF1's keypoint
+ * i1 is matched with, or -1.  Returns nmatches. */
+int refbow_search_by_bow_kf(void *v, int n1, const uint8_t *kps1, const uint8_t *desc1, const uint8_t *mp1,
+                            int n2, const uint8_t *kps2, const uint8_t *desc2, const uint8_t *mp2, float nnratio,
+                            int check_ori, int32_t *out_match12)
+{
+    ORBVocabulary *voc = static_cast<ORBVocabulary *>(v);
+    KeyFrame KF[2];
+    const int n[2] = {n1, n2};
+    const uint8_t *kps[2] = {kps1, kps2}, *desc[2] = {desc1, desc2}, *mp[2] = {mp1, mp2};
+    std::vector<MapPoint> mps[2];
+    for (int s = 0; s < 2; ++s) {
+        KeyFrame &K = KF[s];
+        mps[s].resize((size_t)std::max(n[s], 1));
+        K.N = n[s];
+        K.mvKeysUn.resize(n[s]);
+        if (n[s]) std::memcpy(K.mvKeysUn.data(), kps[s], (size_t)n[s] * 28);
+        K.mvKeys = K.mvKeysUn;
+        K.mDescriptors = desc_mat(desc[s], n[s]);
+        K.mvpMapPoints.assign(n[s], static_cast<MapPoint *>(nullptr));
+        for (int i = 0; i < n[s]; ++i)
+            if (mp[s][i] & 1) {
+                mps[s][i].mbBad = (mp[s][i] & 2) != 0;
+                K.mvpMapPoints[i] = &mps[s][i];
+            }
+        std::vector<cv::Mat> vd;
+        for (int i = 0; i < n[s]; ++i) vd.push_back(K.mDescriptors.row(i));
+        DBoW2::BowVector bv;
+        voc->transform(vd, bv, K.mFeatVec, 4);
+    }
+    ORBmatcher matcher(nnratio, check_ori != 0);
+    std::vector<MapPoint *> matches;
+    const int nm = matcher.SearchByBoW(&KF[0], &KF[1], matches);
+    for (int i = 0; i < n1; ++i) out_match12[i] = matches[i] ? (int32_t)(matches[i] - mps[1].data()) : -1;
+    return nm;
+}
+
 } // extern "C"
+

@@ -299,4 +299,71 @@ int bo_search_by_bow(int n_kf, const float *kf_angle, const uint8_t *kf_desc, co
     return nmatches;
 }
 
+/* ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) :634-777 on the two feature vectors.  mp1 / mp2: bit 0 = the keypoint
+ * has a map point, bit 1 = it isBad().  A pKF2 keypoint without a usable map point or matched already is skipped
+ * (:686-690); acceptance is bestDist1 < TH_LOW -- strict here, unlike the keyframe-to-frame overload -- and the ratio
+ * test (:712-714); the orientation histogram holds pKF1 indices (:726) and a discarded bin clears vpMatches12 there.
+ * out_match12[i1] = pKF2 keypoint index or -1.  Returns nmatches. */
+int bo_search_by_bow_kf(int n1, const float *angle1, const uint8_t *desc1, const uint8_t *mp1,
+                        const uint32_t *node1, const int32_t *start1, const uint32_t *feat1, int nodes1,
+                        int n2, const float *angle2, const uint8_t *desc2, const uint8_t *mp2,
+                        const uint32_t *node2, const int32_t *start2, const uint32_t *feat2, int nodes2,
+                        float nnratio, int check_ori, int32_t *out_match12)
+{
+    const int TH_LOW = 50, HISTO = 30;
+    for (int i = 0; i < n1; ++i) out_match12[i] = -1;
+    std::vector<char> matched2((size_t)std::max(n2, 1), 0);
+    std::vector<int> hist[30];
+    const float factor = 1.0f / HISTO;
+    int nmatches = 0, a = 0, b = 0;
+    while (a < nodes1 && b < nodes2) {
+        if (node1[a] == node2[b]) {
+            for (int i1 = start1[a]; i1 < start1[a + 1]; ++i1) {
+                const uint32_t idx1 = feat1[i1];
+                if (!(mp1[idx1] & 1) || (mp1[idx1] & 2)) continue;
+                int best1 = 256, best2 = 256, best_idx = -1;
+                for (int i2 = start2[b]; i2 < start2[b + 1]; ++i2) {
+                    const uint32_t idx2 = feat2[i2];
+                    if (matched2[idx2] || !(mp2[idx2] & 1)) continue;
+                    if (mp2[idx2] & 2) continue;
+                    const int d = hamming256(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+                    if (d < best1) { best2 = best1; best1 = d; best_idx = (int)idx2; }
+                    else if (d < best2) best2 = d;
+                }
+                if (best1 < TH_LOW && (float)best1 < nnratio * (float)best2) {
+                    out_match12[idx1] = best_idx;
+                    matched2[best_idx] = 1;
+                    if (check_ori) {
+                        float rot = angle1[idx1] - angle2[best_idx];
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO) bin = 0;
+                        hist[bin].push_back((int)idx1);
+                    }
+                    ++nmatches;
+                }
+            }
+            ++a; ++b;
+        } else if (node1[a] < node2[b]) ++a;
+        else ++b;
+    }
+    if (check_ori) { /* ComputeThreeMaxima :1800-1843 */
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO; ++i) {
+            const int s = (int)hist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) ind3 = -1;
+        for (int i = 0; i < HISTO; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : hist[i]) { out_match12[idx] = -1; --nmatches; }
+        }
+    }
+    return nmatches;
+}
+
 } // extern "C"
+

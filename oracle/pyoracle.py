@@ -680,6 +680,29 @@ class BowVocabulary:
         return out[:len(fd)], int(nm)
 
 
+def _bow_kf_restated(self, kps1, desc1, mp1, kps2, desc2, mp2, nnratio=0.75, check_ori=True, fv1=None, fv2=None):
+    """ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) restated (oracle/bow_oracle.cpp)
+    -> (match12 [n1] i32: pKF2 keypoint index or -1, nmatches)"""
+    d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    f1 = fv1 or self.transform(d1, 4)
+    f2 = fv2 or self.transform(d2, 4)
+    a1 = np.ascontiguousarray(kps1["angle"], np.float32)
+    a2 = np.ascontiguousarray(kps2["angle"], np.float32)
+    m1, m2 = np.ascontiguousarray(mp1, np.uint8), np.ascontiguousarray(mp2, np.uint8)
+    out = np.full(max(len(d1), 1), -1, np.int32)
+    fn = self.lib.bo_search_by_bow_kf
+    fn.restype = C.c_int
+    fn.argtypes = ([C.c_int] + [_vp] * 6 + [C.c_int]) * 2 + [C.c_float, C.c_int, _vp]
+    nm = fn(len(d1), _ptr(a1), _ptr(d1), _ptr(m1), _ptr(f1["node_id"]), _ptr(f1["node_start"]), _ptr(f1["feat_idx"]),
+            len(f1["node_id"]), len(d2), _ptr(a2), _ptr(d2), _ptr(m2), _ptr(f2["node_id"]), _ptr(f2["node_start"]),
+            _ptr(f2["feat_idx"]), len(f2["node_id"]), nnratio, int(check_ori), _ptr(out))
+    return out[:len(d1)], int(nm)
+
+
+BowVocabulary.search_by_bow_kf = _bow_kf_restated
+
+
 class RefBow:
     """The reference's own DBoW2 + Frame::ComputeBoW + ORBmatcher::SearchByBoW (oracle/_ref/librefbow.so)."""
 
@@ -735,3 +758,17 @@ class RefBow:
         nm = self.lib.refbow_search_by_bow(self.h, len(kd), _ptr(kk), _ptr(kd), _ptr(mp), len(fd), _ptr(fk), _ptr(fd),
                                            nnratio, int(check_ori), _ptr(out))
         return out[:len(fd)], int(nm)
+
+    def search_by_bow_kf(self, kps1, desc1, mp1, kps2, desc2, mp2, nnratio=0.75, check_ori=True):
+        """ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) -> (match12 [n1] i32: pKF2 keypoint index or -1, nmatches)"""
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        k1, k2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+        m1, m2 = np.ascontiguousarray(mp1, np.uint8), np.ascontiguousarray(mp2, np.uint8)
+        out = np.full(max(len(d1), 1), -1, np.int32)
+        fn = self.lib.refbow_search_by_bow_kf
+        fn.restype = C.c_int
+        fn.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, _vp]
+        nm = fn(self.h, len(d1), _ptr(k1), _ptr(d1), _ptr(m1), len(d2), _ptr(k2), _ptr(d2), _ptr(m2), nnratio, int(check_ori),
+                _ptr(out))
+        return out[:len(d1)], int(nm)

@@ -23,6 +23,12 @@ struct borb_vocabulary {
     double *d_weight = nullptr;
     uint8_t *d_out = nullptr, *h_out = nullptr; /* result slab, layout bow_slab_layout */
     int *d_bstart = nullptr;
+    /* scratch of the keyframe-to-keyframe matcher (borb_voc_search_by_bow), grown on demand: staging blob of both
+     * sides (layout in the function), candidate cache, choices, results */
+    size_t kk_c1 = 0, kk_c2 = 0;
+    uint8_t *d_kk = nullptr, *h_kk = nullptr, *d_kk_more = nullptr, *d_kk_bin = nullptr;
+    uint32_t *d_kk_cache = nullptr;
+    int *d_kk_choice = nullptr, *d_kk_match = nullptr, *h_kk_match = nullptr, *d_kk_hist = nullptr;
 };
 
 struct BowSlab { /* byte offsets of one frame's results inside a slab, for a capacity of K features */
@@ -252,10 +258,13 @@ void borb_voc_destroy(borb_vocabulary *v)
     if (!v) return;
     cudaSetDevice(v->device);
     if (v->stream) cudaStreamSynchronize(v->stream);
-    void *dev[] = {v->d_blob, v->d_desc, v->d_word, v->d_node, v->d_weight, v->d_out, v->d_bstart};
+    void *dev[] = {v->d_blob, v->d_desc, v->d_word, v->d_node, v->d_weight, v->d_out, v->d_bstart, v->d_kk, v->d_kk_more,
+                   v->d_kk_bin, v->d_kk_cache, v->d_kk_choice, v->d_kk_match, v->d_kk_hist};
     for (void *p : dev) if (p) cudaFree(p);
     if (v->h_desc) cudaFreeHost(v->h_desc);
     if (v->h_out) cudaFreeHost(v->h_out);
+    if (v->h_kk) cudaFreeHost(v->h_kk);
+    if (v->h_kk_match) cudaFreeHost(v->h_kk_match);
     if (v->stream) cudaStreamDestroy(v->stream);
     delete v;
 }
@@ -485,7 +494,7 @@ int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, 
         k_bow_resolve<<<(nn + BOW_RES_NT / 32 - 1) / (BOW_RES_NT / 32), BOW_RES_NT, smem, st>>>(
             reinterpret_cast<const uint4 *>(dp), reinterpret_cast<const float *>(dp + o_ang), k_feat,
             reinterpret_cast<const int *>(dp + o_start), node_f, nn, f_desc, cur->d_out_kp + fo, f_feat, b->d_cache, b->d_more,
-            nnratio, check_ori, tw, b->d_choice, b->d_match, b->d_bin, b->d_hist, b->d_match + K + 1);
+            nnratio, check_ori, tw, b->d_choice, b->d_match, b->d_bin, b->d_hist, b->d_match + K + 1, BOW_TH_LOW, nullptr);
     }
     k_bow_finish<<<1, 1024, 0, st>>>(cur->d_nout + frame, (int)K, check_ori, b->d_hist, b->d_bin, b->d_match, b->d_match + K);
     CU(cudaGetLastError());
@@ -503,4 +512,129 @@ int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, 
     return BORB_OK;
 }
 
+/* ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (src/ORBmatcher.cc:634-777), the
+ * matcher of LoopClosing::ComputeSim3: both sides are keyframes no extractor handle holds, so both arrive as flat arrays
+ * and the vocabulary handle lends its device, stream and scratch.  The same kernels as borb_search_by_bow (B3a / B3b / B4,
+ * k_bow.cuh) with pKF1 as the query side: the pKF2 features that can never be chosen -- no map point, or a bad one
+ * (:686-690) -- are dropped from pKF2's node lists on the host (their order is kept, so the first-of-equals rule is
+ * untouched); the distance test is strict here (bestDist1 < TH_LOW, :712), i.e. <= TH_LOW - 1; the kernels' per-pKF2
+ * result (each pKF2 keypoint is matched at most once, vbMatched2) is turned into vpMatches12 on the host. */
+int borb_voc_search_by_bow(borb_vocabulary *v, const borb_keyframe *kf1, const borb_keyframe *kf2, float nnratio,
+                           unsigned flags, int32_t *match12, int *nmatches)
+{
+    if (!v || !kf1 || !kf2 || !match12) return fail(BORB_ERR_ARG, "null argument");
+    const borb_keyframe *kf[2] = {kf1, kf2};
+    int nfeat[2] = {0, 0};
+    for (int s = 0; s < 2; ++s) {
+        const borb_keyframe *k = kf[s];
+        if (k->n < 0 || k->n_nodes < 0 || (k->n > 0 && (!k->desc || !k->angle || !k->mp_flags)) ||
+            (k->n_nodes > 0 && (!k->node_id || !k->node_start || !k->feat_idx)))
+            return fail(BORB_ERR_ARG, "keyframe %d arrays", s + 1);
+        if (k->n > 65535) return fail(BORB_ERR_CAPACITY, "keyframe %d has %d keypoints; list positions are packed in 16 bits", s + 1, k->n);
+        nfeat[s] = k->n_nodes > 0 ? k->node_start[k->n_nodes] : 0;
+        if (nfeat[s] < 0 || nfeat[s] > k->n) return fail(BORB_ERR_ARG, "keyframe %d feature vector lists %d features of %d", s + 1, nfeat[s], k->n);
+        for (int a = 0; a < k->n_nodes; ++a)
+            if (k->node_start[a] < 0 || k->node_start[a + 1] < k->node_start[a] || k->node_start[a + 1] > nfeat[s])
+                return fail(BORB_ERR_ARG, "keyframe %d feature vector: node_start is not ascending", s + 1);
+        for (int i = 0; i < nfeat[s]; ++i)
+            if (k->feat_idx[i] >= (uint32_t)k->n) return fail(BORB_ERR_ARG, "keyframe %d feature index %u of %d", s + 1, k->feat_idx[i], k->n);
+    }
+    const int n1 = kf1->n, n2 = kf2->n, nn1 = kf1->n_nodes, nn2 = kf2->n_nodes;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    if (nmatches) *nmatches = 0;
+    if (n1 == 0 || n2 == 0 || nfeat[0] == 0 || nfeat[1] == 0) return BORB_OK;
+    CU(cudaSetDevice(v->device));
+    cudaStream_t st = v->stream;
+    const size_t c1 = (((size_t)n1 + 1023) / 1024) * 1024, c2 = (((size_t)n2 + 1023) / 1024) * 1024;
+    if (c1 > v->kk_c1 || c2 > v->kk_c2 || !v->d_kk) {
+        const size_t a1 = std::max(c1, v->kk_c1), a2 = std::max(c2, v->kk_c2);
+        CU(cudaStreamSynchronize(st));
+        void *dev[] = {v->d_kk, v->d_kk_more, v->d_kk_bin, v->d_kk_cache, v->d_kk_choice, v->d_kk_match, v->d_kk_hist};
+        for (void *p : dev) if (p) cudaFree(p);
+        if (v->h_kk) cudaFreeHost(v->h_kk);
+        if (v->h_kk_match) cudaFreeHost(v->h_kk_match);
+        v->d_kk = v->h_kk = v->d_kk_more = v->d_kk_bin = nullptr; v->d_kk_cache = nullptr;
+        v->d_kk_choice = v->d_kk_match = v->h_kk_match = v->d_kk_hist = nullptr; v->kk_c1 = v->kk_c2 = 0;
+        const size_t blob = a1 * 57 + 32 + a2 * 40 + 16;
+        CU(cudaMalloc(&v->d_kk, blob));
+        CU(cudaMallocHost(&v->h_kk, blob));
+        CU(cudaMalloc(&v->d_kk_more, a1));
+        CU(cudaMalloc(&v->d_kk_bin, a2));
+        CU(cudaMalloc(&v->d_kk_cache, a1 * BOW_K * 4));
+        CU(cudaMalloc(&v->d_kk_choice, a1 * 4));
+        CU(cudaMalloc(&v->d_kk_match, (a2 + 4) * 4));
+        CU(cudaMallocHost(&v->h_kk_match, (a2 + 4) * 4));
+        CU(cudaMalloc(&v->d_kk_hist, MT_HISTO * 4));
+        v->kk_c1 = a1; v->kk_c2 = a2;
+    }
+    const size_t A1 = v->kk_c1, A2 = v->kk_c2, K2 = A2;
+    /* side 1: [desc 32][angle 4][feat 4][pos_node 4][start 4 (+8)][node_f 8 (+8)][mp 1] per A1; side 2 after it, 16-byte
+     * aligned: [desc 32][angle 4][feat 4] per A2, then the keypoint count */
+    const size_t o_ang = 32 * A1, o_feat = 36 * A1, o_pn = 40 * A1, o_start = 44 * A1, o_nf = 48 * A1 + 8, o_mp = 56 * A1 + 8;
+    const size_t o2 = (57 * A1 + 8 + 15) & ~(size_t)15, o2_ang = o2 + 32 * A2, o2_feat = o2 + 36 * A2, o2_cnt = o2 + 40 * A2;
+    uint8_t *hp = v->h_kk, *dp = v->d_kk;
+    std::memcpy(hp, kf1->desc, (size_t)n1 * 32);
+    std::memcpy(hp + o_ang, kf1->angle, (size_t)n1 * 4);
+    std::memcpy(hp + o_mp, kf1->mp_flags, (size_t)n1);
+    std::memcpy(hp + o_start, kf1->node_start, ((size_t)nn1 + 1) * 4);
+    std::memcpy(hp + o_feat, kf1->feat_idx, (size_t)nfeat[0] * 4);
+    std::memcpy(hp + o2, kf2->desc, (size_t)n2 * 32);
+    std::memcpy(hp + o2_ang, kf2->angle, (size_t)n2 * 4);
+    *reinterpret_cast<int *>(hp + o2_cnt) = n2;
+    int max_nf = 0;
+    {   /* pKF2's lists without the features that are never candidates; both vectors are sorted by node id: walked in
+         * step, as the reference does (:658-745) */
+        uint32_t *f2 = reinterpret_cast<uint32_t *>(hp + o2_feat);
+        int *pn = reinterpret_cast<int *>(hp + o_pn), *nf = reinterpret_cast<int *>(hp + o_nf);
+        int b = 0, w = 0;
+        for (int a = 0; a < nn1; ++a) {
+            while (b < nn2 && kf2->node_id[b] < kf1->node_id[a]) ++b;
+            const bool both = b < nn2 && kf2->node_id[b] == kf1->node_id[a];
+            nf[2 * a] = w;
+            if (both)
+                for (int p = kf2->node_start[b]; p < kf2->node_start[b + 1]; ++p) {
+                    const uint32_t i2 = kf2->feat_idx[p];
+                    if ((kf2->mp_flags[i2] & 1) && !(kf2->mp_flags[i2] & 2)) f2[w++] = i2;
+                }
+            nf[2 * a + 1] = w;
+            max_nf = std::max(max_nf, nf[2 * a + 1] - nf[2 * a]);
+            for (int p = kf1->node_start[a]; p < kf1->node_start[a + 1]; ++p) pn[p] = a;
+        }
+    }
+    CU(cudaMemcpyAsync(dp, hp, o2_cnt + 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(v->d_kk_match, 0xff, K2 * 4, st));
+    CU(cudaMemsetAsync(v->d_kk_match + K2, 0, 16, st));
+    CU(cudaMemsetAsync(v->d_kk_hist, 0, MT_HISTO * 4, st));
+    const int check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
+    {
+        const uint4 *f_desc = reinterpret_cast<const uint4 *>(dp + o2);
+        const uint32_t *f_feat = reinterpret_cast<const uint32_t *>(dp + o2_feat);
+        const uint32_t *k_feat = reinterpret_cast<const uint32_t *>(dp + o_feat);
+        const int2 *node_f = reinterpret_cast<const int2 *>(dp + o_nf);
+        k_bow_candidates<<<(nfeat[0] + BOW_CAND_NT / 32 - 1) / (BOW_CAND_NT / 32), BOW_CAND_NT, 0, st>>>(
+            reinterpret_cast<const uint4 *>(dp), dp + o_mp, k_feat, reinterpret_cast<const int *>(dp + o_pn), node_f, nfeat[0], f_desc,
+            f_feat, v->d_kk_cache, v->d_kk_more);
+        const int tw = (max_nf + 31) / 32 + 1;
+        const size_t smem = (size_t)(BOW_RES_NT / 32) * ((size_t)tw + 32 * (BOW_K + 1)) * 4;
+        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k_bow_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_bow_resolve<<<(nn1 + BOW_RES_NT / 32 - 1) / (BOW_RES_NT / 32), BOW_RES_NT, smem, st>>>(
+            reinterpret_cast<const uint4 *>(dp), reinterpret_cast<const float *>(dp + o_ang), k_feat,
+            reinterpret_cast<const int *>(dp + o_start), node_f, nn1, f_desc, nullptr, f_feat, v->d_kk_cache, v->d_kk_more,
+            nnratio, check_ori, tw, v->d_kk_choice, v->d_kk_match, v->d_kk_bin, v->d_kk_hist, v->d_kk_match + K2 + 1,
+            BOW_TH_LOW - 1, reinterpret_cast<const float *>(dp + o2_ang));
+    }
+    k_bow_finish<<<1, 1024, 0, st>>>(reinterpret_cast<const int *>(dp + o2_cnt), (int)K2, check_ori, v->d_kk_hist, v->d_kk_bin,
+                                     v->d_kk_match, v->d_kk_match + K2);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(v->h_kk_match, v->d_kk_match, (K2 + 4) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (int i2 = 0; i2 < n2; ++i2) {
+        const int i1 = v->h_kk_match[i2];
+        if (i1 >= 0 && i1 < n1) match12[i1] = i2;
+    }
+    if (nmatches) *nmatches = v->h_kk_match[K2];
+    return BORB_OK;
+}
+
 } // extern "C"
+

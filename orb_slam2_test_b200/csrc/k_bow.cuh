@@ -320,7 +320,9 @@ k_bow_resolve(const uint4 *__restrict__ kf_desc, const float *__restrict__ kf_an
               const int *__restrict__ kf_start, const int2 *__restrict__ node_f, int kf_nodes,
               const uint4 *__restrict__ f_desc, const BorbKpRec *__restrict__ f_kp, const uint32_t *__restrict__ f_feat,
               const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more, float nnratio, int check_ori, int tw,
-              int *choice /* scratch, one per keyframe list position */, int *__restrict__ match, uint8_t *__restrict__ bin_of, int *__restrict__ hist, int *__restrict__ rescans)
+              int *choice /* scratch, one per keyframe list position */, int *__restrict__ match, uint8_t *__restrict__ bin_of, int *__restrict__ hist, int *__restrict__ rescans,
+              int th_low /* accept best <= th_low: TH_LOW for (KeyFrame, Frame) :273, TH_LOW - 1 for (KeyFrame, KeyFrame) whose test is strict :712 */,
+              const float *__restrict__ f_angle /* the second side's angles when it is a keyframe (no cv::KeyPoint records on the device), else NULL */)
 {
     extern __shared__ uint32_t bow_taken[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -366,7 +368,7 @@ k_bow_resolve(const uint4 *__restrict__ kf_desc, const float *__restrict__ kf_an
                     const uint32_t m2 = mask & (mask - 1u);                                                   \
                     const int best2 = m2 ? (int)(tile[lane * (BOW_K + 1) + __ffs(m2) - 1] >> 16) : 256;        \
                     const int best1 = (int)(k1 >> 16);                                                        \
-                    if (best1 <= BOW_TH_LOW && (float)best1 < nnratio * (float)best2) dec = (int)(k1 & 0xffffu); \
+                    if (best1 <= th_low && (float)best1 < nnratio * (float)best2) dec = (int)(k1 & 0xffffu);     \
                 }                                                                                             \
             } else dec = -2; /* fewer than two open among the cached ones and there were more */              \
         }                                                                                                     \
@@ -397,7 +399,7 @@ k_bow_resolve(const uint4 *__restrict__ kf_desc, const float *__restrict__ kf_an
                     else best2 = min(best2, (int)(m1 >> 16));
                 }
                 const int best1 = (int)(B1 >> 16);
-                pos = (best1 <= BOW_TH_LOW && (float)best1 < nnratio * (float)best2) ? (int)(B1 & 0xffffu) : -1;
+                pos = (best1 <= th_low && (float)best1 < nnratio * (float)best2) ? (int)(B1 & 0xffffu) : -1;
             }
             if (pos >= 0) {
                 if (lane == j) {
@@ -421,7 +423,7 @@ k_bow_resolve(const uint4 *__restrict__ kf_desc, const float *__restrict__ kf_an
         const uint32_t rk = kf_feat[p], bi = f_feat[fs + pos];
         match[bi] = (int)rk;
         if (check_ori) {
-            const int bin = mt_bin(kf_angle[rk], f_kp[bi].angle);
+            const int bin = mt_bin(kf_angle[rk], f_angle ? f_angle[bi] : f_kp[bi].angle);
             bin_of[bi] = (uint8_t)bin;
             atomicAdd(&hist[bin], 1);
         }

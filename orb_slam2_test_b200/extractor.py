@@ -56,6 +56,8 @@ SYMBOLS += ["borb_voc_load_text", "borb_voc_create", "borb_voc_destroy", "borb_v
             "borb_compute_bow", "borb_bow_result", "borb_search_by_bow"]
 # the relocalisation matcher ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) and its logf taps
 SYMBOLS += ["borb_search_by_projection_keyframe", "borb_debug_logf", "borb_debug_logf_device"]
+# ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)
+SYMBOLS += ["borb_voc_search_by_bow"]
 
 
 class BorbError(RuntimeError):
@@ -132,6 +134,7 @@ def load_library() -> C.CDLL:
     lib.borb_search_for_initialization.argtypes = [_vp, C.c_int, _vp, _vp, C.c_int, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_search_by_projection_keyframe.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, C.c_uint, _vp,
                                                        C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_voc_search_by_bow.argtypes = [_vp, _vp, _vp, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_debug_logf.argtypes = [_vp, _vp, C.c_int]
     lib.borb_debug_logf.restype = None
     lib.borb_debug_logf_device.argtypes = [_vp, _vp, C.c_int]
@@ -241,6 +244,26 @@ class ORBVocabulary:
                                                        C.byref(nw), nid.ctypes.data, ns.ctypes.data, fi.ctypes.data, C.byref(nn)))
         return {"word_id": wid[:nw.value].copy(), "word_val": wv[:nw.value].copy(), "node_id": nid[:nn.value].copy(),
                 "node_start": ns[:nn.value + 1].copy(), "feat_idx": fi[:ns[nn.value]].copy()}
+
+
+    def search_by_bow(self, kf1: dict, kf2: dict, nnratio: float = 0.75, check_orientation: bool = True):
+        """ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (src/ORBmatcher.cc:634-777) on the device.  kf1 / kf2: dicts
+        as ORBextractor.search_by_bow takes (desc, angle, mp_flags, fv).
+        -> (match12 [n1] i32: pKF2 keypoint index or -1, nmatches)."""
+        keep, recs = [], []
+        for kf in (kf1, kf2):
+            fv = kf["fv"]
+            a = [np.ascontiguousarray(kf["desc"], np.uint8), np.ascontiguousarray(kf["angle"], np.float32),
+                 np.ascontiguousarray(kf["mp_flags"], np.uint8), np.ascontiguousarray(fv["node_id"], np.uint32),
+                 np.ascontiguousarray(fv["node_start"], np.int32), np.ascontiguousarray(fv["feat_idx"], np.uint32)]
+            keep.append(a)
+            recs.append(_KeyFrame(len(a[2]), a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data, len(a[3]),
+                                  a[3].ctypes.data, a[4].ctypes.data, a[5].ctypes.data))
+        out = np.full(max(recs[0].n, 1), -1, np.int32)
+        nm = C.c_int()
+        _check(self._lib, self._lib.borb_voc_search_by_bow(self._h, C.addressof(recs[0]), C.addressof(recs[1]), nnratio,
+                                                           0 if check_orientation else 2, out.ctypes.data, C.byref(nm)))
+        return out[:recs[0].n].copy(), nm.value
 
 
 class ORBextractor:

@@ -307,6 +307,51 @@ void ORBextractor::ComputeBoW(DeviceVocabulary &voc, std::map<unsigned int, doub
     fill_maps(wid, wval, nw, nid, nstart, fidx, nn, mBowVec, mFeatVec);
 }
 
+namespace {
+struct FlatKeyFrame { /* a keyframe as include/borb.h's borb_keyframe wants it */
+    std::vector<unsigned char> desc;
+    std::vector<float> angle;
+    std::vector<uint32_t> nid, fidx;
+    std::vector<int32_t> nstart;
+    borb_keyframe rec;
+    FlatKeyFrame(const cv::Mat &descriptors, const std::vector<cv::KeyPoint> &keysUn, const unsigned char *flags,
+                 const std::map<unsigned int, std::vector<unsigned int> > &featVec)
+        : nstart(1, 0)
+    {
+        const int n = (int)keysUn.size();
+        assert(descriptors.rows == n && (n == 0 || descriptors.cols == 32));
+        desc.resize((size_t)32 * n);
+        angle.resize((size_t)n);
+        for (int i = 0; i < n; ++i) {
+            memcpy(&desc[(size_t)32 * i], descriptors.ptr(i), 32);
+            angle[i] = keysUn[i].angle;
+        }
+        for (std::map<unsigned int, std::vector<unsigned int> >::const_iterator it = featVec.begin(); it != featVec.end(); ++it) {
+            nid.push_back(it->first);
+            fidx.insert(fidx.end(), it->second.begin(), it->second.end());
+            nstart.push_back((int32_t)fidx.size());
+        }
+        rec.n = n; rec.desc = desc.data(); rec.angle = angle.data(); rec.mp_flags = flags;
+        rec.n_nodes = (int)nid.size(); rec.node_id = nid.data(); rec.node_start = nstart.data(); rec.feat_idx = fidx.data();
+    }
+};
+} // namespace
+
+int DeviceVocabulary::SearchByBoW(const cv::Mat &descriptors1, const std::vector<cv::KeyPoint> &keysUn1,
+                                  const unsigned char *mapPointFlags1, const std::map<unsigned int, std::vector<unsigned int> > &featVec1,
+                                  const cv::Mat &descriptors2, const std::vector<cv::KeyPoint> &keysUn2,
+                                  const unsigned char *mapPointFlags2, const std::map<unsigned int, std::vector<unsigned int> > &featVec2,
+                                  float nnRatio, bool checkOrientation, std::vector<int> &vnMatches12)
+{
+    FlatKeyFrame a(descriptors1, keysUn1, mapPointFlags1, featVec1), b(descriptors2, keysUn2, mapPointFlags2, featVec2);
+    vnMatches12.assign(keysUn1.size(), -1);
+    int nmatches = 0;
+    check(borb_voc_search_by_bow(voc, &a.rec, &b.rec, nnRatio, checkOrientation ? 0u : BORB_MATCH_NO_ORIENTATION,
+                                 vnMatches12.data(), &nmatches),
+          "search by bow (keyframes)");
+    return nmatches;
+}
+
 int ORBextractor::SearchByBoW(const cv::Mat &kfDescriptors, const std::vector<cv::KeyPoint> &kfKeysUn,
                               const unsigned char *kfMapPointFlags, const std::map<unsigned int, std::vector<unsigned int> > &kfFeatVec,
                               float nnRatio, bool checkOrientation, std::vector<int> &vnMatches)

@@ -62,6 +62,15 @@ public:
     // std::map<unsigned int, std::vector<unsigned int> >, so mBowVec / mFeatVec bind to these references directly
     void transform(const cv::Mat &descriptors, std::map<unsigned int, double> &bowVec,
                    std::map<unsigned int, std::vector<unsigned int> > &featVec, int levelsup = 4);
+    // ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12) (reference
+    // src/ORBmatcher.cc:634-777, LoopClosing::ComputeSim3) on the device.  Each keyframe arrives as its mDescriptors,
+    // mvKeysUn, mFeatVec and one flag byte per keypoint (bit 0: GetMapPointMatches()[i] != NULL, bit 1: that point
+    // isBad()).  vnMatches12[i1] = index of the pKF2 keypoint whose map point vpMatches12[i1] receives, or -1; returns nmatches.
+    int SearchByBoW(const cv::Mat &descriptors1, const std::vector<cv::KeyPoint> &keysUn1, const unsigned char *mapPointFlags1,
+                    const std::map<unsigned int, std::vector<unsigned int> > &featVec1, const cv::Mat &descriptors2,
+                    const std::vector<cv::KeyPoint> &keysUn2, const unsigned char *mapPointFlags2,
+                    const std::map<unsigned int, std::vector<unsigned int> > &featVec2, float nnRatio, bool checkOrientation,
+                    std::vector<int> &vnMatches12);
     borb_vocabulary *get() const { return voc; }
 
 private:

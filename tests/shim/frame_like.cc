@@ -386,6 +386,19 @@ static int bow_mode(char **argv)
     fwrite(vnMatches.data(), 4, vnMatches.size(), f);
     dump_bow(f, mBowVec, mFeatVec);
     dump_bow(f, kfBow, kfFeatVec);
+    /* ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (reference src/ORBmatcher.cc:634-777): the keyframe against the
+     * current frame promoted to a keyframe -- every keypoint but each fourth carries a map point, each 16th a bad one */
+    {
+        vector<unsigned char> flags2(keys.size());
+        for (size_t i = 0; i < keys.size(); ++i) flags2[i] = (unsigned char)((i % 4 ? 1 : 0) | (i % 16 == 5 ? 2 : 0));
+        vector<int> vnMatches12;
+        const int nm12 = voc.SearchByBoW(kfDesc, kfKeysUn, flags.data(), kfFeatVec, desc, keys, flags2.data(), mFeatVec, 0.75f, true,
+                                         vnMatches12);
+        const int n1 = (int)vnMatches12.size();
+        fwrite(&nm12, 4, 1, f);
+        fwrite(&n1, 4, 1, f);
+        fwrite(vnMatches12.data(), 4, vnMatches12.size(), f);
+    }
     fclose(f);
     printf("frame_like bow ok\n");
     return 0;

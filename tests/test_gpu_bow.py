@@ -116,3 +116,50 @@ def test_batch_frames_and_replay(vocdir, oracle_built):
     res = ext.extract_batch(imgs)
     for f in (2, 2, 0, 3):
         assert bowcase.same_bow(ext.compute_bow(voc, frame=f), want.transform(res[f][1], 4)), f"frame {f}"
+
+
+@pytest.mark.parametrize("name,shape,nf", [("k10L4", synth.TUM_SHAPE, 1000), ("k4L6", synth.KITTI_SHAPE, 2000),
+                                           ("k9L5ragged", synth.TUM_SHAPE, 2000), ("k10L3", synth.TUM_SHAPE, 500)])
+def test_search_by_bow_between_keyframes(name, shape, nf, vocdir, oracle_built):
+    """ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (src/ORBmatcher.cc:634-777) through borb_voc_search_by_bow: both
+    keyframes as flat arrays, their feature vectors from borb_voc_transform"""
+    from oracle import pyoracle
+    from orb_slam2_test_b200 import BorbError, ORBVocabulary
+    path = bowcase.vocabulary(vocdir, name)
+    voc, want = ORBVocabulary(path), pyoracle.BowVocabulary(path)
+    total = 0
+    kfs = None
+    for t in (0, 2):
+        k1, d1 = bowcase.frame_features(shape, 3, t, nf)
+        k2, d2 = bowcase.frame_features(shape, 3, t + 1, nf)
+        m1, m2 = bowcase.keyframe_flags(len(k1), 40 + t), bowcase.keyframe_flags(len(k2), 60 + t)
+        kf1 = {"desc": d1, "angle": k1["angle"], "mp_flags": m1, "fv": voc.transform(d1, 4)}
+        kf2 = {"desc": d2, "angle": k2["angle"], "mp_flags": m2, "fv": voc.transform(d2, 4)}
+        kfs = (kf1, kf2)
+        for ratio, ori in ((0.75, True), (0.9, True), (0.6, False)):
+            w, wnm = want.search_by_bow_kf(k1, d1, m1, k2, d2, m2, ratio, ori)
+            for rep in range(2):  # the second call reuses the scratch
+                g, nm = voc.search_by_bow(kf1, kf2, ratio, check_orientation=ori)
+                bad = np.nonzero(g != w)[0]
+                assert bad.size == 0 and nm == wnm, f"{name} t={t} ratio={ratio} ori={ori}: {bad.size} differ, nm {nm} vs {wnm}, e.g. {bad[:5]}"
+            total += nm
+        # the sides swapped (another pair of sizes through the same scratch)
+        w, wnm = want.search_by_bow_kf(k2, d2, m2, k1, d1, m1, 0.75, True)
+        g, nm = voc.search_by_bow(kf2, kf1, 0.75)
+        assert np.array_equal(g, w) and nm == wnm
+    assert total > 100
+    e = {"desc": np.zeros((0, 32), np.uint8), "angle": np.zeros(0, np.float32), "mp_flags": np.zeros(0, np.uint8),
+         "fv": {"node_id": np.zeros(0, np.uint32), "node_start": np.zeros(1, np.int32), "feat_idx": np.zeros(0, np.uint32)}}
+    g, nm = voc.search_by_bow(e, kfs[1])
+    assert nm == 0 and len(g) == 0
+    g, nm = voc.search_by_bow(kfs[0], e)
+    assert nm == 0 and (g == -1).all() and len(g) == len(kfs[0]["desc"])
+    nobody = dict(kfs[1])
+    nobody["mp_flags"] = np.zeros_like(kfs[1]["mp_flags"])  # no pKF2 keypoint has a map point
+    g, nm = voc.search_by_bow(kfs[0], nobody)
+    assert nm == 0 and (g == -1).all()
+    broken = dict(kfs[0])
+    broken["fv"] = dict(kfs[0]["fv"])
+    broken["fv"]["feat_idx"] = kfs[0]["fv"]["feat_idx"] + np.uint32(100000)
+    with pytest.raises(BorbError):
+        voc.search_by_bow(broken, kfs[1])

@@ -83,3 +83,32 @@ def test_search_by_bow_equals_the_reference(name, shape, nf, vocdir, oracle_buil
     ek = np.zeros(0, kk.dtype)
     assert ref.search_by_bow(ek, e, np.zeros(0, np.uint8), fk, fd)[1] == ours.search_by_bow(ek, e, np.zeros(0, np.uint8), fk, fd)[1] == 0
     assert ref.search_by_bow(kk, kd, mp, ek, e)[1] == ours.search_by_bow(kk, kd, mp, ek, e)[1] == 0
+
+
+@pytest.mark.parametrize("name,shape,nf", [("k10L4", synth.TUM_SHAPE, 1000), ("k4L6", synth.KITTI_SHAPE, 2000),
+                                           ("k9L5ragged", synth.TUM_SHAPE, 2000), ("k10L3", synth.TUM_SHAPE, 500)])
+def test_search_by_bow_between_keyframes_equals_the_reference(name, shape, nf, vocdir, oracle_built):
+    """ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (src/ORBmatcher.cc:634-777, LoopClosing::ComputeSim3): keyframe 1 =
+    frame t, keyframe 2 = frame t + 1 of the synthetic sequence, 70 % of the keypoints of either carry a map point, 5 % of
+    those are bad -- the pKF2 side skips them too (:686-690) and the distance test is strict (:712)."""
+    path = bowcase.vocabulary(vocdir, name)
+    ref, ours = pyoracle.RefBow(path), pyoracle.BowVocabulary(path)
+    total = 0
+    for t in (0, 2):
+        k1, d1 = bowcase.frame_features(shape, 3, t, nf)
+        k2, d2 = bowcase.frame_features(shape, 3, t + 1, nf)
+        m1, m2 = bowcase.keyframe_flags(len(k1), 40 + t), bowcase.keyframe_flags(len(k2), 60 + t)
+        for ratio, ori in ((0.75, True), (0.9, True), (0.6, False)):
+            want, wnm = ref.search_by_bow_kf(k1, d1, m1, k2, d2, m2, ratio, ori)
+            got, nm = ours.search_by_bow_kf(k1, d1, m1, k2, d2, m2, ratio, ori)
+            assert np.array_equal(got, want) and nm == wnm, f"{name} t={t} ratio={ratio} ori={ori}"
+            hit = got >= 0
+            assert nm == int(hit.sum()) and (m1[hit] == 1).all() and (m2[got[hit]] == 1).all()
+            assert len(np.unique(got[hit])) == nm  # a pKF2 keypoint is matched once
+            total += nm
+    assert total > 100
+    e = np.zeros((0, 32), np.uint8)
+    ek = np.zeros(0, k1.dtype)
+    z = np.zeros(0, np.uint8)
+    assert ref.search_by_bow_kf(ek, e, z, k2, d2, m2)[1] == ours.search_by_bow_kf(ek, e, z, k2, d2, m2)[1] == 0
+    assert ref.search_by_bow_kf(k1, d1, m1, ek, e, z)[1] == ours.search_by_bow_kf(k1, d1, m1, ek, e, z)[1] == 0

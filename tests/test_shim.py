@@ -296,3 +296,10 @@ def test_bag_of_words_through_the_shim(tmp_path, oracle_built):
     assert bowcase.same_bow(fbow, want.transform(fd, 4)) and bowcase.same_bow(kbow, want.transform(kd, 4))
     w, wnm = want.search_by_bow(kk, kd, mp, fk, fd, np.float32(0.7), True)
     assert nf == len(w) and np.array_equal(got, w) and nm == wnm > 50
+    # DeviceVocabulary::SearchByBoW(keyframe, keyframe) = ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) (:634-777)
+    nm12, n1 = struct.unpack_from("<ii", buf, off)
+    got12 = np.frombuffer(buf, "<i4", n1, off + 8)
+    i = np.arange(len(fk))
+    mp2 = ((i % 4 != 0).astype(np.uint8) | ((i % 16 == 5).astype(np.uint8) << 1)).astype(np.uint8)
+    w12, wnm12 = want.search_by_bow_kf(kk, kd, mp, fk, fd, mp2, np.float32(0.75), True)
+    assert n1 == len(w12) and np.array_equal(got12, w12) and nm12 == wnm12 > 30
