@@ -426,6 +426,28 @@ int borb_search_by_bow(borb_extractor *cur, int frame, const borb_keyframe *kf, 
 int borb_voc_search_by_bow(borb_vocabulary *v, const borb_keyframe *kf1, const borb_keyframe *kf2, float nnratio,
                            unsigned flags, int32_t *match12, int *nmatches);
 
+/* ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vector<pair<size_t, size_t> >
+ * &vMatchedPairs, const bool bOnlyStereo) (src/ORBmatcher.cc:779-966, with CheckDistEpipolarLine :165-182;
+ * LocalMapping::CreateNewMapPoints): the keyframes as borb_keyframe records (only bit 0 of mp_flags is read here: the
+ * keypoint has a map point) and what the epipolar test reads beside them. */
+typedef struct borb_triangulation {
+    const float *F12;            /* 3 x 3 row-major, as LocalMapping::ComputeF12 returns it */
+    const float *Ow1;            /* pKF1->GetCameraCenter(), 3 floats */
+    const float *Tcw2;           /* pKF2's pose rows 0-2 (GetRotation / GetTranslation), 3 x 4 row-major */
+    float fx2, fy2, cx2, cy2;    /* pKF2->fx, fy, cx, cy */
+    const float *xy1, *xy2;      /* mvKeysUn[i].pt of either keyframe, 2 floats per keypoint */
+    const int32_t *octave2;      /* pKF2->mvKeysUn[i].octave */
+    const float *u_right1, *u_right2; /* mvuRight; NULL = a monocular keyframe (all -1) */
+    int nlevels;
+    const float *scale_factors2, *level_sigma2_2; /* pKF2->mvScaleFactors, mvLevelSigma2 */
+} borb_triangulation;
+#define BORB_MATCH_ONLY_STEREO 8u /* bOnlyStereo */
+/* match12 [kf1->n]: per pKF1 keypoint the pKF2 keypoint it is paired with, or -1 -- vMatchedPairs is the list of
+ * (i1, match12[i1]) for match12[i1] >= 0 in ascending i1 (:950-956); *nmatches = the return value.  flags:
+ * BORB_MATCH_NO_ORIENTATION, BORB_MATCH_ONLY_STEREO.  One call at a time per vocabulary. */
+int borb_voc_search_for_triangulation(borb_vocabulary *v, const borb_keyframe *kf1, const borb_keyframe *kf2,
+                                      const borb_triangulation *g, unsigned flags, int32_t *match12, int *nmatches);
+
 /* capacity of a frame's result arrays (keypoints per frame can never exceed it; valid after any extract call) */
 int borb_max_keypoints(const borb_extractor *h);
 /* low 8 bits: rounds the last call's fixed-point iteration took (>= 1); the rest: cell rescans

@@ -195,5 +195,72 @@ int refbow_search_by_bow_kf(void *v, int n1, const uint8_t *kps1, const uint8_t 
     return nm;
 }
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:779-966, with
+ * CheckDistEpipolarLine :165-182), the matcher of LocalMapping::CreateNewMapPoints.  Keyframes as in
+ * refbow_search_by_bow_kf (only bit 0 of mp is read: the keypoint has a map point), plus mvKeysUn positions / octaves
+ * inside the 28-B records, mvuRight (may be null: all -1), the poses (3 x 4 row-major), pKF2's intrinsics cam2 = fx, fy,
+ * cx, cy and its level tables.  out_match12[i1] = pKF2 keypoint paired with pKF1 keypoint i1 or -1 (vMatchedPairs is that
+ * list in i1 order).  Returns nmatches. */
+int refbow_search_for_triangulation(void *v, int n1, const uint8_t *kps1, const uint8_t *desc1, const uint8_t *mp1,
+                                    const float *ur1, const float *Tcw1, int n2, const uint8_t *kps2, const uint8_t *desc2,
+                                    const uint8_t *mp2, const float *ur2, const float *Tcw2, const float *cam2, int nlevels,
+                                    const float *scale2, const float *sigma2_2, const float *F12, int only_stereo,
+                                    int check_ori, int32_t *out_match12)
+{
+    ORBVocabulary *voc = static_cast<ORBVocabulary *>(v);
+    KeyFrame KF[2];
+    const int n[2] = {n1, n2};
+    const uint8_t *kps[2] = {kps1, kps2}, *desc[2] = {desc1, desc2}, *mp[2] = {mp1, mp2};
+    const float *ur[2] = {ur1, ur2}, *Tcw[2] = {Tcw1, Tcw2};
+    std::vector<MapPoint> mps[2];
+    for (int s = 0; s < 2; ++s) {
+        KeyFrame &K = KF[s];
+        mps[s].resize((size_t)std::max(n[s], 1));
+        K.N = n[s];
+        K.mvKeysUn.resize(n[s]);
+        if (n[s]) std::memcpy(K.mvKeysUn.data(), kps[s], (size_t)n[s] * 28);
+        K.mvKeys = K.mvKeysUn;
+        K.mDescriptors = desc_mat(desc[s], n[s]);
+        K.mvpMapPoints.assign(n[s], static_cast<MapPoint *>(nullptr));
+        K.mvuRight.assign(n[s], -1.f);
+        if (ur[s]) K.mvuRight.assign(ur[s], ur[s] + n[s]);
+        for (int i = 0; i < n[s]; ++i)
+            if (mp[s][i] & 1) K.mvpMapPoints[i] = &mps[s][i];
+        K.Tcw_ = cv::Mat(4, 4, CV_32F);
+        for (int c = 0; c < 4; ++c) K.Tcw_.at<float>(3, c) = c == 3 ? 1.f : 0.f;
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 4; ++c) K.Tcw_.at<float>(r, c) = Tcw[s][4 * r + c];
+        {   /* KeyFrame::SetPose (src/KeyFrame.cc): Ow = -Rcw.t() * tcw */
+            cv::Mat Rcw = K.Tcw_.rowRange(0, 3).colRange(0, 3);
+            cv::Mat tcw = K.Tcw_.rowRange(0, 3).col(3);
+            K.Ow_ = -Rcw.t() * tcw;
+        }
+        K.fx = cam2[0]; K.fy = cam2[1]; K.cx = cam2[2]; K.cy = cam2[3];
+        K.mnScaleLevels = nlevels;
+        K.mvScaleFactors.assign(scale2, scale2 + nlevels);
+        K.mvLevelSigma2.assign(sigma2_2, sigma2_2 + nlevels);
+        std::vector<cv::Mat> vd;
+        for (int i = 0; i < n[s]; ++i) vd.push_back(K.mDescriptors.row(i));
+        DBoW2::BowVector bv;
+        voc->transform(vd, bv, K.mFeatVec, 4);
+    }
+    cv::Mat F(3, 3, CV_32F);
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) F.at<float>(r, c) = F12[3 * r + c];
+    ORBmatcher matcher(0.6f, check_ori != 0);
+    std::vector<std::pair<size_t, size_t> > pairs;
+    const int nm = matcher.SearchForTriangulation(&KF[0], &KF[1], F, pairs, only_stereo != 0);
+    for (int i = 0; i < n1; ++i) out_match12[i] = -1;
+    size_t prev = 0;
+    for (size_t k = 0; k < pairs.size(); ++k) {
+        if (k && pairs[k].first <= prev) std::abort(); /* the list is in i1 order */
+        prev = pairs[k].first;
+        out_match12[pairs[k].first] = (int32_t)pairs[k].second;
+    }
+    if ((int)pairs.size() != nm) std::abort();
+    return nm;
+}
+
 } // extern "C"
+
 

@@ -365,5 +365,107 @@ int bo_search_by_bow_kf(int n1, const float *angle1, const uint8_t *desc1, const
     return nmatches;
 }
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) :779-966 on the two feature vectors.
+ * Only bit 0 of mp1 / mp2 is read (a keypoint that has ANY map point is left out on either side, :823-824, :850-851);
+ * vbMatched2 is never set by the reference, so a pKF2 keypoint may be paired with several pKF1 keypoints and the
+ * keypoints of pKF1 are independent of each other.  Inside a node the running best starts at TH_LOW and a candidate with
+ * dist <= best that passes the geometry takes over (:867-888): the LAST of the smallest distances wins.
+ * Float forms as the reference object has them (objdump of _ref/ORBmatcher.o):
+ *   C2 = R2w * Cw + t2w       the small float product; invz = 1.0f / C2z
+ *   ex = fmaf(fx * C2x, invz, cx), ey likewise                                            (:791-793)
+ *   fmaf(distex, distex, distey * distey) < 100 * mvScaleFactors[octave2]  -> skipped      (:874-879)
+ *   CheckDistEpipolarLine (:165-182): a = fmaf(x1, F00, y1 * F10) + F20, b = fmaf(x1, F01, y1 * F11) + F21,
+ *   c = fmaf(y1, F12, x1 * F02) + F22, den = fmaf(a, a, b * b), num = c + fmaf(b, y2, a * x2),
+ *   (double)(num * num / den) < 3.84 * (double)mvLevelSigma2[octave2]
+ * xy / octave / angle come from the 28-B cv::KeyPoint records (mvKeysUn).  out_match12[i1] = pKF2 index or -1. */
+struct bo_kp { float x, y, size, angle, response; int octave, class_id; };
+int bo_search_for_triangulation(int n1, const uint8_t *kps1, const uint8_t *desc1, const uint8_t *mp1, const float *ur1,
+                                const float *Ow1, const uint32_t *node1, const int32_t *start1, const uint32_t *feat1, int nodes1,
+                                int n2, const uint8_t *kps2, const uint8_t *desc2, const uint8_t *mp2, const float *ur2,
+                                const float *Tcw2, const uint32_t *node2, const int32_t *start2, const uint32_t *feat2, int nodes2,
+                                const float *cam2, const float *scale2, const float *sigma2_2, const float *F, int only_stereo,
+                                int check_ori, int32_t *out_match12)
+{
+    (void)n2;
+    const int TH_LOW = 50, HISTO = 30;
+    const bo_kp *k1 = reinterpret_cast<const bo_kp *>(kps1), *k2 = reinterpret_cast<const bo_kp *>(kps2);
+    float C2[3];
+    for (int r = 0; r < 3; ++r) {
+        float s = 0.f;
+        for (int k = 0; k < 3; ++k) s += Tcw2[4 * r + k] * Ow1[k];
+        C2[r] = s + Tcw2[4 * r + 3];
+    }
+    const float invz = 1.0f / C2[2];
+    const float ex = std::fmaf(cam2[0] * C2[0], invz, cam2[2]), ey = std::fmaf(cam2[1] * C2[1], invz, cam2[3]);
+    for (int i = 0; i < n1; ++i) out_match12[i] = -1;
+    std::vector<int> hist[30];
+    const float factor = 1.0f / HISTO;
+    int nmatches = 0, a = 0, b = 0;
+    while (a < nodes1 && b < nodes2) {
+        if (node1[a] == node2[b]) {
+            for (int i1 = start1[a]; i1 < start1[a + 1]; ++i1) {
+                const uint32_t idx1 = feat1[i1];
+                if (mp1[idx1] & 1) continue;
+                const bool stereo1 = ur1 && ur1[idx1] >= 0;
+                if (only_stereo && !stereo1) continue;
+                const float x1 = k1[idx1].x, y1 = k1[idx1].y;
+                int best = TH_LOW, best_idx = -1;
+                for (int i2 = start2[b]; i2 < start2[b + 1]; ++i2) {
+                    const uint32_t idx2 = feat2[i2];
+                    if (mp2[idx2] & 1) continue;
+                    const bool stereo2 = ur2 && ur2[idx2] >= 0;
+                    if (only_stereo && !stereo2) continue;
+                    const int d = hamming256(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+                    if (d > TH_LOW || d > best) continue;
+                    const float x2 = k2[idx2].x, y2 = k2[idx2].y;
+                    const int o2 = k2[idx2].octave;
+                    if (!stereo1 && !stereo2) {
+                        const float dx = ex - x2, dy = ey - y2;
+                        if (std::fmaf(dx, dx, dy * dy) < 100 * scale2[o2]) continue;
+                    }
+                    const float la = std::fmaf(x1, F[0], y1 * F[3]) + F[6];
+                    const float lb = std::fmaf(x1, F[1], y1 * F[4]) + F[7];
+                    const float lc = std::fmaf(y1, F[5], x1 * F[2]) + F[8];
+                    const float den = std::fmaf(la, la, lb * lb);
+                    if (den == 0) continue;
+                    const float num = lc + std::fmaf(lb, y2, la * x2);
+                    const float dsqr = num * num / den;
+                    if ((double)dsqr < 3.84 * (double)sigma2_2[o2]) { best_idx = (int)idx2; best = d; }
+                }
+                if (best_idx >= 0) {
+                    out_match12[idx1] = best_idx;
+                    ++nmatches;
+                    if (check_ori) {
+                        float rot = k1[idx1].angle - k2[best_idx].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO) bin = 0;
+                        hist[bin].push_back((int)idx1);
+                    }
+                }
+            }
+            ++a; ++b;
+        } else if (node1[a] < node2[b]) ++a;
+        else ++b;
+    }
+    if (check_ori) { /* ComputeThreeMaxima :1800-1843 */
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO; ++i) {
+            const int s = (int)hist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) ind3 = -1;
+        for (int i = 0; i < HISTO; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : hist[i]) { out_match12[idx] = -1; --nmatches; }
+        }
+    }
+    return nmatches;
+}
+
 } // extern "C"
+
 

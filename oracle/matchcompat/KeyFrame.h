@@ -18,11 +18,14 @@ public:
     std::vector<MapPoint *> mvpMapPoints;
     std::vector<MapPoint *> GetMapPointMatches() { return mvpMapPoints; }
     std::set<MapPoint *> GetMapPoints() { std::abort(); }
-    MapPoint *GetMapPoint(const size_t &) { std::abort(); }
-    cv::Mat GetRotation() { std::abort(); }
-    cv::Mat GetTranslation() { std::abort(); }
-    cv::Mat GetCameraCenter() { std::abort(); }
-    cv::Mat GetPose() { std::abort(); }
+    MapPoint *GetMapPoint(const size_t &idx) { return mvpMapPoints[idx]; }
+    /* pose accessors as src/KeyFrame.cc has them (clones of Tcw's blocks and of Ow, which KeyFrame::SetPose computes as
+     * -Rcw.t() * tcw): the drivers fill Tcw_ and Ow_ */
+    cv::Mat Tcw_, Ow_;
+    cv::Mat GetRotation() { return Tcw_.rowRange(0, 3).colRange(0, 3).clone(); }
+    cv::Mat GetTranslation() { return Tcw_.rowRange(0, 3).col(3).clone(); }
+    cv::Mat GetCameraCenter() { return Ow_.clone(); }
+    cv::Mat GetPose() { return Tcw_.clone(); }
     std::vector<size_t> GetFeaturesInArea(const float &, const float &, const float &) const { std::abort(); }
     bool IsInImage(const float &, const float &) const { std::abort(); }
     void AddMapPoint(MapPoint *, const size_t &) { std::abort(); }

@@ -703,6 +703,49 @@ def _bow_kf_restated(self, kps1, desc1, mp1, kps2, desc2, mp2, nnratio=0.75, che
 BowVocabulary.search_by_bow_kf = _bow_kf_restated
 
 
+def camera_centre(Tcw) -> np.ndarray:
+    """Ow = -Rcw.t() * tcw as cv::MatExpr evaluates it (cv::gemm GEMM_1_T: double accumulation, one rounding)"""
+    T = np.asarray(Tcw, np.float32)
+    out = np.zeros(3, np.float32)
+    for y in range(3):
+        s = 0.0
+        for k in range(3):
+            s += float(T[k, y]) * float(T[k, 3])
+        out[y] = np.float32(s * -1.0)
+    return out
+
+
+def _bow_triangulation_restated(self, kf1: dict, kf2: dict, geo: dict, only_stereo=False, check_ori=True, fv1=None, fv2=None):
+    """ORBmatcher::SearchForTriangulation restated (oracle/bow_oracle.cpp); arguments as RefBow.search_for_triangulation"""
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+    d1 = np.ascontiguousarray(kf1["desc"], np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(kf2["desc"], np.uint8).reshape(-1, 32)
+    f1 = fv1 or self.transform(d1, 4)
+    f2 = fv2 or self.transform(d2, 4)
+    fn = self.lib.bo_search_for_triangulation
+    fn.restype = C.c_int
+    fn.argtypes = ([C.c_int] + [_vp] * 8 + [C.c_int]) * 2 + [_vp] * 4 + [C.c_int, C.c_int, _vp]
+    n1 = len(d1)
+    out = np.full(max(n1, 1), -1, np.int32)
+
+    def side(k, d, f, pose):
+        return [len(d), arr(k["kps"], KP_DTYPE), arr(d, np.uint8), arr(k["mp"], np.uint8),
+                arr(k["u_right"], np.float32) if k.get("u_right") is not None else None, pose,
+                arr(f["node_id"], np.uint32), arr(f["node_start"], np.int32), arr(f["feat_idx"], np.uint32), len(f["node_id"])]
+    nm = fn(*side(kf1, d1, f1, arr(camera_centre(kf1["Tcw"]), np.float32)), *side(kf2, d2, f2, arr(kf2["Tcw"], np.float32)),
+            arr(geo["cam2"], np.float32), arr(geo["scale2"], np.float32), arr(geo["sigma2_2"], np.float32),
+            arr(geo["F12"], np.float32), int(only_stereo), int(check_ori), _ptr(out))
+    return out[:n1], int(nm)
+
+
+BowVocabulary.search_for_triangulation = _bow_triangulation_restated
+
+
 class RefBow:
     """The reference's own DBoW2 + Frame::ComputeBoW + ORBmatcher::SearchByBoW (oracle/_ref/librefbow.so)."""
 
@@ -772,3 +815,25 @@ class RefBow:
         nm = fn(self.h, len(d1), _ptr(k1), _ptr(d1), _ptr(m1), len(d2), _ptr(k2), _ptr(d2), _ptr(m2), nnratio, int(check_ori),
                 _ptr(out))
         return out[:len(d1)], int(nm)
+
+    def search_for_triangulation(self, kf1: dict, kf2: dict, geo: dict, only_stereo=False, check_ori=True):
+        """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:779-966).  kf: kps (KP_DTYPE, mvKeysUn), desc, mp [n] u8,
+        u_right [n] f32 or None, Tcw [3,4]; geo: cam2 (fx, fy, cx, cy), scale2, sigma2_2, F12 [3,3].
+        -> (match12 [n1] i32, nmatches)"""
+        keep = []
+
+        def arr(a, dt):
+            a = np.ascontiguousarray(a, dt)
+            keep.append(a)
+            return a.ctypes.data
+        fn = self.lib.refbow_search_for_triangulation
+        fn.restype = C.c_int
+        fn.argtypes = [_vp] + [C.c_int, _vp, _vp, _vp, _vp, _vp] * 2 + [_vp, C.c_int, _vp, _vp, _vp, C.c_int, C.c_int, _vp]
+        n1, n2 = len(kf1["kps"]), len(kf2["kps"])
+        out = np.full(max(n1, 1), -1, np.int32)
+        side = lambda k: [len(k["kps"]), arr(k["kps"], KP_DTYPE), arr(np.asarray(k["desc"]).reshape(-1, 32), np.uint8),
+                          arr(k["mp"], np.uint8), arr(k["u_right"], np.float32) if k.get("u_right") is not None else None,
+                          arr(k["Tcw"], np.float32)]
+        nm = fn(self.h, *side(kf1), *side(kf2), arr(geo["cam2"], np.float32), len(geo["scale2"]), arr(geo["scale2"], np.float32),
+                arr(geo["sigma2_2"], np.float32), arr(geo["F12"], np.float32), int(only_stereo), int(check_ori), _ptr(out))
+        return out[:n1], int(nm)

@@ -25,7 +25,7 @@ struct borb_vocabulary {
     int *d_bstart = nullptr;
     /* scratch of the keyframe-to-keyframe matcher (borb_voc_search_by_bow), grown on demand: staging blob of both
      * sides (layout in the function), candidate cache, choices, results */
-    size_t kk_c1 = 0, kk_c2 = 0;
+    size_t kk_c1 = 0, kk_c2 = 0, kk_blob = 0;
     uint8_t *d_kk = nullptr, *h_kk = nullptr, *d_kk_more = nullptr, *d_kk_bin = nullptr;
     uint32_t *d_kk_cache = nullptr;
     int *d_kk_choice = nullptr, *d_kk_match = nullptr, *h_kk_match = nullptr, *d_kk_hist = nullptr;
@@ -118,6 +118,33 @@ int bow_enqueue(const borb_vocabulary *voc, const uint8_t *d_desc, const int *n_
                                                reinterpret_cast<int *>(d_out + S.start), reinterpret_cast<uint32_t *>(d_out + S.feat),
                                                reinterpret_cast<int *>(d_out + S.counts), dual);
     CU(cudaGetLastError());
+    return BORB_OK;
+}
+
+/* scratch of the keyframe-to-keyframe matchers on the vocabulary handle: a staging blob of `blob` bytes on both sides of
+ * the link, per-pKF1 arrays for c1 keypoints, per-keypoint result arrays for max(c1, c2) */
+int kk_reserve(borb_vocabulary *v, size_t c1, size_t c2, size_t blob)
+{
+    if (c1 <= v->kk_c1 && c2 <= v->kk_c2 && blob <= v->kk_blob && v->d_kk) return BORB_OK;
+    c1 = std::max(c1, v->kk_c1); c2 = std::max(c2, v->kk_c2); blob = std::max(blob, v->kk_blob);
+    CU(cudaStreamSynchronize(v->stream));
+    void *dev[] = {v->d_kk, v->d_kk_more, v->d_kk_bin, v->d_kk_cache, v->d_kk_choice, v->d_kk_match, v->d_kk_hist};
+    for (void *p : dev) if (p) cudaFree(p);
+    if (v->h_kk) cudaFreeHost(v->h_kk);
+    if (v->h_kk_match) cudaFreeHost(v->h_kk_match);
+    v->d_kk = v->h_kk = v->d_kk_more = v->d_kk_bin = nullptr; v->d_kk_cache = nullptr;
+    v->d_kk_choice = v->d_kk_match = v->h_kk_match = v->d_kk_hist = nullptr; v->kk_c1 = v->kk_c2 = v->kk_blob = 0;
+    const size_t cm = std::max(c1, c2);
+    CU(cudaMalloc(&v->d_kk, blob));
+    CU(cudaMallocHost(&v->h_kk, blob));
+    CU(cudaMalloc(&v->d_kk_more, c1));
+    CU(cudaMalloc(&v->d_kk_bin, cm));
+    CU(cudaMalloc(&v->d_kk_cache, c1 * BOW_K * 4));
+    CU(cudaMalloc(&v->d_kk_choice, c1 * 4));
+    CU(cudaMalloc(&v->d_kk_match, (cm + 4) * 4));
+    CU(cudaMallocHost(&v->h_kk_match, (cm + 4) * 4));
+    CU(cudaMalloc(&v->d_kk_hist, MT_HISTO * 4));
+    v->kk_c1 = c1; v->kk_c2 = c2; v->kk_blob = blob;
     return BORB_OK;
 }
 
@@ -546,26 +573,10 @@ int borb_voc_search_by_bow(borb_vocabulary *v, const borb_keyframe *kf1, const b
     CU(cudaSetDevice(v->device));
     cudaStream_t st = v->stream;
     const size_t c1 = (((size_t)n1 + 1023) / 1024) * 1024, c2 = (((size_t)n2 + 1023) / 1024) * 1024;
-    if (c1 > v->kk_c1 || c2 > v->kk_c2 || !v->d_kk) {
+    {
         const size_t a1 = std::max(c1, v->kk_c1), a2 = std::max(c2, v->kk_c2);
-        CU(cudaStreamSynchronize(st));
-        void *dev[] = {v->d_kk, v->d_kk_more, v->d_kk_bin, v->d_kk_cache, v->d_kk_choice, v->d_kk_match, v->d_kk_hist};
-        for (void *p : dev) if (p) cudaFree(p);
-        if (v->h_kk) cudaFreeHost(v->h_kk);
-        if (v->h_kk_match) cudaFreeHost(v->h_kk_match);
-        v->d_kk = v->h_kk = v->d_kk_more = v->d_kk_bin = nullptr; v->d_kk_cache = nullptr;
-        v->d_kk_choice = v->d_kk_match = v->h_kk_match = v->d_kk_hist = nullptr; v->kk_c1 = v->kk_c2 = 0;
-        const size_t blob = a1 * 57 + 32 + a2 * 40 + 16;
-        CU(cudaMalloc(&v->d_kk, blob));
-        CU(cudaMallocHost(&v->h_kk, blob));
-        CU(cudaMalloc(&v->d_kk_more, a1));
-        CU(cudaMalloc(&v->d_kk_bin, a2));
-        CU(cudaMalloc(&v->d_kk_cache, a1 * BOW_K * 4));
-        CU(cudaMalloc(&v->d_kk_choice, a1 * 4));
-        CU(cudaMalloc(&v->d_kk_match, (a2 + 4) * 4));
-        CU(cudaMallocHost(&v->h_kk_match, (a2 + 4) * 4));
-        CU(cudaMalloc(&v->d_kk_hist, MT_HISTO * 4));
-        v->kk_c1 = a1; v->kk_c2 = a2;
+        const int rc = kk_reserve(v, a1, a2, a1 * 57 + 32 + a2 * 40 + 16);
+        if (rc != BORB_OK) return rc;
     }
     const size_t A1 = v->kk_c1, A2 = v->kk_c2, K2 = A2;
     /* side 1: [desc 32][angle 4][feat 4][pos_node 4][start 4 (+8)][node_f 8 (+8)][mp 1] per A1; side 2 after it, 16-byte
@@ -636,5 +647,126 @@ int borb_voc_search_by_bow(borb_vocabulary *v, const borb_keyframe *kf1, const b
     return BORB_OK;
 }
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:779-966), the matcher
+ * of LocalMapping::CreateNewMapPoints: one kernel (k_bow_triangulate, a warp per pKF1 keypoint) + B4 for the orientation
+ * histogram, on the vocabulary's device, stream and scratch. */
+int borb_voc_search_for_triangulation(borb_vocabulary *v, const borb_keyframe *kf1, const borb_keyframe *kf2,
+                                      const borb_triangulation *g, unsigned flags, int32_t *match12, int *nmatches)
+{
+    if (!v || !kf1 || !kf2 || !g || !match12) return fail(BORB_ERR_ARG, "null argument");
+    if (!g->F12 || !g->Ow1 || !g->Tcw2 || !g->scale_factors2 || !g->level_sigma2_2) return fail(BORB_ERR_ARG, "geometry arrays");
+    if (g->nlevels < 1 || g->nlevels > BORB_MAXL) return fail(BORB_ERR_ARG, "nlevels %d", g->nlevels);
+    const borb_keyframe *kf[2] = {kf1, kf2};
+    int nfeat[2] = {0, 0};
+    for (int s = 0; s < 2; ++s) {
+        const borb_keyframe *k = kf[s];
+        if (k->n < 0 || k->n_nodes < 0 || (k->n > 0 && (!k->desc || !k->angle || !k->mp_flags)) ||
+            (k->n_nodes > 0 && (!k->node_id || !k->node_start || !k->feat_idx)))
+            return fail(BORB_ERR_ARG, "keyframe %d arrays", s + 1);
+        if (k->n > 65535) return fail(BORB_ERR_CAPACITY, "keyframe %d has %d keypoints; list positions are packed in 16 bits", s + 1, k->n);
+        nfeat[s] = k->n_nodes > 0 ? k->node_start[k->n_nodes] : 0;
+        if (nfeat[s] < 0 || nfeat[s] > k->n) return fail(BORB_ERR_ARG, "keyframe %d feature vector lists %d features of %d", s + 1, nfeat[s], k->n);
+        for (int a = 0; a < k->n_nodes; ++a)
+            if (k->node_start[a] < 0 || k->node_start[a + 1] < k->node_start[a] || k->node_start[a + 1] > nfeat[s])
+                return fail(BORB_ERR_ARG, "keyframe %d feature vector: node_start is not ascending", s + 1);
+        for (int i = 0; i < nfeat[s]; ++i)
+            if (k->feat_idx[i] >= (uint32_t)k->n) return fail(BORB_ERR_ARG, "keyframe %d feature index %u of %d", s + 1, k->feat_idx[i], k->n);
+    }
+    const int n1 = kf1->n, n2 = kf2->n, nn1 = kf1->n_nodes, nn2 = kf2->n_nodes;
+    if ((n1 > 0 && !g->xy1) || (n2 > 0 && (!g->xy2 || !g->octave2))) return fail(BORB_ERR_ARG, "keypoint positions");
+    for (int i = 0; i < n2; ++i)
+        if (g->octave2[i] < 0 || g->octave2[i] >= g->nlevels) return fail(BORB_ERR_ARG, "octave %d of pKF2 keypoint %d", g->octave2[i], i);
+    const bool only_stereo = (flags & BORB_MATCH_ONLY_STEREO) != 0;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    if (nmatches) *nmatches = 0;
+    if (n1 == 0 || n2 == 0 || nfeat[0] == 0 || nfeat[1] == 0) return BORB_OK;
+    CU(cudaSetDevice(v->device));
+    cudaStream_t st = v->stream;
+    const size_t c1 = (((size_t)n1 + 1023) / 1024) * 1024, c2 = (((size_t)n2 + 1023) / 1024) * 1024;
+    {
+        const size_t a1 = std::max(c1, v->kk_c1), a2 = std::max(c2, v->kk_c2);
+        const int rc = kk_reserve(v, a1, a2, a1 * 69 + 32 + a2 * 56 + 32);
+        if (rc != BORB_OK) return rc;
+    }
+    const size_t A1 = v->kk_c1, A2 = v->kk_c2;
+    /* side 1, per A1: [desc 32][angle 4][feat 4][pos_node 4][node_f 8][xy 8][u_right 4][mp 1], then the keypoint count;
+     * side 2, per A2, 16-byte aligned: [desc 32][angle 4][feat 4][xy 8][octave 4][u_right 4] */
+    const size_t o_ang = 32 * A1, o_feat = 36 * A1, o_pn = 40 * A1, o_nf = 44 * A1, o_xy = 52 * A1, o_ur = 60 * A1, o_mp = 64 * A1,
+                 o_cnt = 65 * A1;
+    const size_t o2 = (65 * A1 + 16 + 15) & ~(size_t)15, o2_ang = o2 + 32 * A2, o2_feat = o2 + 36 * A2, o2_xy = o2 + 40 * A2,
+                 o2_oct = o2 + 48 * A2, o2_ur = o2 + 52 * A2, o_end = o2 + 56 * A2;
+    uint8_t *hp = v->h_kk, *dp = v->d_kk;
+    std::memcpy(hp, kf1->desc, (size_t)n1 * 32);
+    std::memcpy(hp + o_ang, kf1->angle, (size_t)n1 * 4);
+    std::memcpy(hp + o_feat, kf1->feat_idx, (size_t)nfeat[0] * 4);
+    std::memcpy(hp + o_xy, g->xy1, (size_t)n1 * 8);
+    if (g->u_right1) std::memcpy(hp + o_ur, g->u_right1, (size_t)n1 * 4);
+    std::memcpy(hp + o_mp, kf1->mp_flags, (size_t)n1);
+    *reinterpret_cast<int *>(hp + o_cnt) = n1;
+    std::memcpy(hp + o2, kf2->desc, (size_t)n2 * 32);
+    std::memcpy(hp + o2_ang, kf2->angle, (size_t)n2 * 4);
+    std::memcpy(hp + o2_xy, g->xy2, (size_t)n2 * 8);
+    std::memcpy(hp + o2_oct, g->octave2, (size_t)n2 * 4);
+    if (g->u_right2) std::memcpy(hp + o2_ur, g->u_right2, (size_t)n2 * 4);
+    {   /* pKF2's lists without what can never be a candidate; the two vectors walked in step (:809-919) */
+        uint32_t *f2 = reinterpret_cast<uint32_t *>(hp + o2_feat);
+        int *pn = reinterpret_cast<int *>(hp + o_pn), *nf = reinterpret_cast<int *>(hp + o_nf);
+        int b = 0, w = 0;
+        for (int a = 0; a < nn1; ++a) {
+            while (b < nn2 && kf2->node_id[b] < kf1->node_id[a]) ++b;
+            const bool both = b < nn2 && kf2->node_id[b] == kf1->node_id[a];
+            nf[2 * a] = w;
+            if (both)
+                for (int p = kf2->node_start[b]; p < kf2->node_start[b + 1]; ++p) {
+                    const uint32_t i2 = kf2->feat_idx[p];
+                    if (kf2->mp_flags[i2] & 1) continue;
+                    if (only_stereo && !(g->u_right2 && g->u_right2[i2] >= 0.f)) continue;
+                    f2[w++] = i2;
+                }
+            nf[2 * a + 1] = w;
+            for (int p = kf1->node_start[a]; p < kf1->node_start[a + 1]; ++p) pn[p] = a;
+        }
+    }
+    TriParams tp;
+    std::memset(&tp, 0, sizeof tp);
+    std::memcpy(tp.F, g->F12, 36);
+    {   /* C2 = R2w * Cw + t2w (the small float product), the epipole (:785-793) */
+        float C2[3];
+        for (int r = 0; r < 3; ++r) {
+            float acc = 0.f;
+            for (int k = 0; k < 3; ++k) acc += g->Tcw2[4 * r + k] * g->Ow1[k];
+            C2[r] = acc + g->Tcw2[4 * r + 3];
+        }
+        const float invz = 1.0f / C2[2];
+        tp.ex = fmaf(g->fx2 * C2[0], invz, g->cx2);
+        tp.ey = fmaf(g->fy2 * C2[1], invz, g->cy2);
+    }
+    tp.only_stereo = only_stereo ? 1 : 0;
+    for (int l = 0; l < g->nlevels; ++l) { tp.scale2[l] = g->scale_factors2[l]; tp.sigma2[l] = g->level_sigma2_2[l]; }
+    const size_t cm = std::max(A1, A2);
+    CU(cudaMemcpyAsync(dp, hp, o_end, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(v->d_kk_match, 0xff, cm * 4, st));
+    CU(cudaMemsetAsync(v->d_kk_match + cm, 0, 16, st));
+    CU(cudaMemsetAsync(v->d_kk_hist, 0, MT_HISTO * 4, st));
+    const int check_ori = (flags & BORB_MATCH_NO_ORIENTATION) ? 0 : 1;
+    k_bow_triangulate<<<(nfeat[0] + BOW_CAND_NT / 32 - 1) / (BOW_CAND_NT / 32), BOW_CAND_NT, 0, st>>>(
+        tp, reinterpret_cast<const uint4 *>(dp), dp + o_mp, reinterpret_cast<const float2 *>(dp + o_xy),
+        reinterpret_cast<const float *>(dp + o_ang), g->u_right1 ? reinterpret_cast<const float *>(dp + o_ur) : nullptr,
+        reinterpret_cast<const uint32_t *>(dp + o_feat), reinterpret_cast<const int *>(dp + o_pn),
+        reinterpret_cast<const int2 *>(dp + o_nf), nfeat[0], reinterpret_cast<const uint4 *>(dp + o2),
+        reinterpret_cast<const float2 *>(dp + o2_xy), reinterpret_cast<const int *>(dp + o2_oct),
+        reinterpret_cast<const float *>(dp + o2_ang), g->u_right2 ? reinterpret_cast<const float *>(dp + o2_ur) : nullptr,
+        reinterpret_cast<const uint32_t *>(dp + o2_feat), check_ori, v->d_kk_match, v->d_kk_bin, v->d_kk_hist);
+    k_bow_finish<<<1, 1024, 0, st>>>(reinterpret_cast<const int *>(dp + o_cnt), (int)cm, check_ori, v->d_kk_hist, v->d_kk_bin,
+                                     v->d_kk_match, v->d_kk_match + cm);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(v->h_kk_match, v->d_kk_match, (cm + 4) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    std::memcpy(match12, v->h_kk_match, (size_t)n1 * 4);
+    if (nmatches) *nmatches = v->h_kk_match[cm];
+    return BORB_OK;
+}
+
 } // extern "C"
+
 

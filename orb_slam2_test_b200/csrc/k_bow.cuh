@@ -464,4 +464,76 @@ k_bow_finish(const int *__restrict__ n_p, int cap, int check_ori, const int *__r
     if (tid == 0) nm[0] = s_nm;
 }
 
+/* ---- ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo), src/ORBmatcher.cc:779-966, with
+ * CheckDistEpipolarLine :165-182 (LocalMapping::CreateNewMapPoints) ----
+ * The reference never sets vbMatched2, so the keypoints of pKF1 are independent: a warp per pKF1 list position, the node's
+ * pKF2 list 32 at a time.  The running best of the reference starts at TH_LOW and a candidate with dist <= best that
+ * passes the geometry takes over (:867-888), i.e. the LAST of the smallest distances among the candidates that pass wins:
+ * the minimum of (distance << 16 | 0xffff - list position).  The host has dropped from pKF2's lists what can never be a
+ * candidate (a keypoint with a map point, :850-851; a monocular one under bOnlyStereo, :855-857).
+ * Float forms as the reference object has them (oracle/bow_oracle.cpp); the library is built with --fmad=false, so only
+ * the fmaf() written here fuses. */
+struct TriParams {
+    float F[9];   /* F12, row-major */
+    float ex, ey; /* the epipole of pKF1's centre in pKF2 (:785-793), evaluated on the host */
+    int only_stereo;
+    float scale2[BORB_MAXL], sigma2[BORB_MAXL]; /* pKF2->mvScaleFactors, mvLevelSigma2 */
+};
+#define BOW_TH_LOW_TRI 50
+
+__global__ void __launch_bounds__(BOW_CAND_NT)
+k_bow_triangulate(const __grid_constant__ TriParams tp, const uint4 *__restrict__ desc1, const uint8_t *__restrict__ mp1,
+                  const float2 *__restrict__ xy1, const float *__restrict__ ang1, const float *__restrict__ ur1,
+                  const uint32_t *__restrict__ feat1, const int *__restrict__ pos_node, const int2 *__restrict__ node_f, int n_pos,
+                  const uint4 *__restrict__ desc2, const float2 *__restrict__ xy2, const int *__restrict__ oct2,
+                  const float *__restrict__ ang2, const float *__restrict__ ur2, const uint32_t *__restrict__ feat2,
+                  int check_ori, int *__restrict__ match12, uint8_t *__restrict__ bin_of, int *__restrict__ hist)
+{
+    const int lane = threadIdx.x & 31;
+    const int p = blockIdx.x * (BOW_CAND_NT / 32) + (threadIdx.x >> 5);
+    if (p >= n_pos) return; /* whole warp */
+    const uint32_t i1 = feat1[p];
+    if (mp1[i1] & 1u) return; /* has a map point already (:823-824) */
+    const bool stereo1 = ur1 && ur1[i1] >= 0.f;
+    if (tp.only_stereo && !stereo1) return;
+    const float2 P1 = xy1[i1];
+    /* the epipolar line of keypoint 1 in image 2 (:168-170) */
+    const float la = __fadd_rn(fmaf(P1.x, tp.F[0], __fmul_rn(P1.y, tp.F[3])), tp.F[6]);
+    const float lb = __fadd_rn(fmaf(P1.x, tp.F[1], __fmul_rn(P1.y, tp.F[4])), tp.F[7]);
+    const float lc = __fadd_rn(fmaf(P1.y, tp.F[5], __fmul_rn(P1.x, tp.F[2])), tp.F[8]);
+    const float den = fmaf(la, la, __fmul_rn(lb, lb));
+    const int2 nf = node_f[pos_node[p]];
+    const uint4 d0 = desc1[2 * i1], d1 = desc1[2 * i1 + 1];
+    uint32_t best = BOW_NOKEY;
+    for (int base = nf.x; base < nf.y; base += 32) {
+        const int jf = base + lane;
+        if (jf >= nf.y) continue;
+        const uint32_t i2 = feat2[jf];
+        const int d = mt_hamming(d0, d1, desc2 + 2 * (size_t)i2);
+        if (d > BOW_TH_LOW_TRI) continue;
+        const float2 P2 = xy2[i2];
+        const int o2 = oct2[i2];
+        const bool stereo2 = ur2 && ur2[i2] >= 0.f;
+        if (!stereo1 && !stereo2) { /* too close to the epipole (:872-879) */
+            const float dx = __fsub_rn(tp.ex, P2.x), dy = __fsub_rn(tp.ey, P2.y);
+            if (fmaf(dx, dx, __fmul_rn(dy, dy)) < __fmul_rn(100.f, tp.scale2[o2])) continue;
+        }
+        if (den == 0.f) continue;
+        const float num = __fadd_rn(lc, fmaf(lb, P2.y, __fmul_rn(la, P2.x)));
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if (!((double)dsqr < __dmul_rn(3.84, (double)tp.sigma2[o2]))) continue;
+        best = min(best, ((uint32_t)d << 16) | (0xffffu - (uint32_t)(jf - nf.x)));
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (lane == 0 && best != BOW_NOKEY) {
+        const uint32_t i2 = feat2[nf.x + (int)(0xffffu - (best & 0xffffu))];
+        match12[i1] = (int)i2;
+        if (check_ori) {
+            const int bin = mt_bin(ang1[i1], ang2[i2]);
+            bin_of[i1] = (uint8_t)bin;
+            atomicAdd(&hist[bin], 1);
+        }
+    }
+}
+
 #endif

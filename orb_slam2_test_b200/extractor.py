@@ -58,6 +58,8 @@ SYMBOLS += ["borb_voc_load_text", "borb_voc_create", "borb_voc_destroy", "borb_v
 SYMBOLS += ["borb_search_by_projection_keyframe", "borb_debug_logf", "borb_debug_logf_device"]
 # ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)
 SYMBOLS += ["borb_voc_search_by_bow"]
+# ORBmatcher::SearchForTriangulation
+SYMBOLS += ["borb_voc_search_for_triangulation"]
 
 
 class BorbError(RuntimeError):
@@ -135,6 +137,7 @@ def load_library() -> C.CDLL:
     lib.borb_search_by_projection_keyframe.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_int, C.c_uint, _vp,
                                                        C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.borb_voc_search_by_bow.argtypes = [_vp, _vp, _vp, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
+    lib.borb_voc_search_for_triangulation.argtypes = [_vp, _vp, _vp, _vp, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_debug_logf.argtypes = [_vp, _vp, C.c_int]
     lib.borb_debug_logf.restype = None
     lib.borb_debug_logf_device.argtypes = [_vp, _vp, C.c_int]
@@ -202,6 +205,12 @@ class _KeyFrame(C.Structure):  # == borb_keyframe
                 ("node_start", _vp), ("feat_idx", _vp)]
 
 
+class _Triangulation(C.Structure):  # == borb_triangulation
+    _fields_ = [("F12", _vp), ("Ow1", _vp), ("Tcw2", _vp), ("fx2", C.c_float), ("fy2", C.c_float), ("cx2", C.c_float),
+                ("cy2", C.c_float), ("xy1", _vp), ("xy2", _vp), ("octave2", _vp), ("u_right1", _vp), ("u_right2", _vp),
+                ("nlevels", C.c_int), ("scale_factors2", _vp), ("level_sigma2_2", _vp)]
+
+
 class ORBVocabulary:
     """ORB_SLAM2::ORBVocabulary (include/ORBVocabulary.h = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) on the
     device: loadFromTextFile's format (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1421) or the tree as arrays."""
@@ -263,6 +272,37 @@ class ORBVocabulary:
         nm = C.c_int()
         _check(self._lib, self._lib.borb_voc_search_by_bow(self._h, C.addressof(recs[0]), C.addressof(recs[1]), nnratio,
                                                            0 if check_orientation else 2, out.ctypes.data, C.byref(nm)))
+        return out[:recs[0].n].copy(), nm.value
+
+
+    def search_for_triangulation(self, kf1: dict, kf2: dict, geo: dict, only_stereo: bool = False,
+                                 check_orientation: bool = True):
+        """ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:779-966) on the
+        device.  kf1 / kf2: dicts with desc, angle, mp_flags, fv (as search_by_bow) and xy [n,2] f32 (mvKeysUn positions),
+        u_right [n] f32 or None; kf2 also octave [n] i32.  geo: F12 [3,3], Ow1 [3], Tcw2 [3,4], cam2 (fx, fy, cx, cy),
+        scale2, sigma2_2.  -> (match12 [n1] i32: pKF2 keypoint or -1, nmatches); vMatchedPairs = the (i1, match12[i1]) >= 0."""
+        keep, recs = [], []
+
+        def arr(a, dt):
+            a = np.ascontiguousarray(a, dt)
+            keep.append(a)
+            return a.ctypes.data
+        for kf in (kf1, kf2):
+            fv = kf["fv"]
+            recs.append(_KeyFrame(len(kf["mp_flags"]), arr(kf["desc"], np.uint8), arr(kf["angle"], np.float32),
+                                  arr(kf["mp_flags"], np.uint8), len(fv["node_id"]), arr(fv["node_id"], np.uint32),
+                                  arr(fv["node_start"], np.int32), arr(fv["feat_idx"], np.uint32)))
+        cam = [float(x) for x in geo["cam2"]]
+        g = _Triangulation(arr(geo["F12"], np.float32), arr(geo["Ow1"], np.float32), arr(geo["Tcw2"], np.float32), cam[0], cam[1],
+                           cam[2], cam[3], arr(kf1["xy"], np.float32), arr(kf2["xy"], np.float32), arr(kf2["octave"], np.int32),
+                           arr(kf1["u_right"], np.float32) if kf1.get("u_right") is not None else None,
+                           arr(kf2["u_right"], np.float32) if kf2.get("u_right") is not None else None,
+                           len(geo["scale2"]), arr(geo["scale2"], np.float32), arr(geo["sigma2_2"], np.float32))
+        out = np.full(max(recs[0].n, 1), -1, np.int32)
+        nm = C.c_int()
+        _check(self._lib, self._lib.borb_voc_search_for_triangulation(
+            self._h, C.addressof(recs[0]), C.addressof(recs[1]), C.addressof(g),
+            (0 if check_orientation else 2) | (8 if only_stereo else 0), out.ctypes.data, C.byref(nm)))
         return out[:recs[0].n].copy(), nm.value
 
 

@@ -352,6 +352,50 @@ int DeviceVocabulary::SearchByBoW(const cv::Mat &descriptors1, const std::vector
     return nmatches;
 }
 
+int DeviceVocabulary::SearchForTriangulation(const cv::Mat &descriptors1, const std::vector<cv::KeyPoint> &keysUn1,
+                                             const unsigned char *mapPointFlags1, const std::map<unsigned int, std::vector<unsigned int> > &featVec1,
+                                             const std::vector<float> &uRight1, const cv::Mat &Ow1, const cv::Mat &descriptors2,
+                                             const std::vector<cv::KeyPoint> &keysUn2, const unsigned char *mapPointFlags2,
+                                             const std::map<unsigned int, std::vector<unsigned int> > &featVec2,
+                                             const std::vector<float> &uRight2, const cv::Mat &Tcw2, float fx2, float fy2, float cx2,
+                                             float cy2, const std::vector<float> &scaleFactors2, const std::vector<float> &levelSigma2_2,
+                                             const cv::Mat &F12, std::vector<std::pair<size_t, size_t> > &vMatchedPairs,
+                                             bool bOnlyStereo, bool checkOrientation)
+{
+    FlatKeyFrame a(descriptors1, keysUn1, mapPointFlags1, featVec1), b(descriptors2, keysUn2, mapPointFlags2, featVec2);
+    assert(F12.rows == 3 && F12.cols == 3 && F12.type() == CV_32F && Tcw2.rows == 4 && Tcw2.cols == 4 && Tcw2.type() == CV_32F);
+    assert(Ow1.rows == 3 && Ow1.cols == 1 && Ow1.type() == CV_32F && scaleFactors2.size() == levelSigma2_2.size());
+    assert(uRight1.empty() || uRight1.size() == keysUn1.size());
+    assert(uRight2.empty() || uRight2.size() == keysUn2.size());
+    float F[9], ow[3], tc[12];
+    for (int r = 0; r < 3; ++r) {
+        ow[r] = Ow1.at<float>(r, 0);
+        for (int c = 0; c < 3; ++c) F[3 * r + c] = F12.at<float>(r, c);
+        for (int c = 0; c < 4; ++c) tc[4 * r + c] = Tcw2.at<float>(r, c);
+    }
+    std::vector<float> xy1(2 * keysUn1.size()), xy2(2 * keysUn2.size());
+    std::vector<int32_t> oct2(keysUn2.size());
+    for (size_t i = 0; i < keysUn1.size(); ++i) { xy1[2 * i] = keysUn1[i].pt.x; xy1[2 * i + 1] = keysUn1[i].pt.y; }
+    for (size_t i = 0; i < keysUn2.size(); ++i) { xy2[2 * i] = keysUn2[i].pt.x; xy2[2 * i + 1] = keysUn2[i].pt.y; oct2[i] = keysUn2[i].octave; }
+    borb_triangulation g;
+    g.F12 = F; g.Ow1 = ow; g.Tcw2 = tc; g.fx2 = fx2; g.fy2 = fy2; g.cx2 = cx2; g.cy2 = cy2;
+    g.xy1 = xy1.data(); g.xy2 = xy2.data(); g.octave2 = oct2.data();
+    g.u_right1 = uRight1.empty() ? NULL : uRight1.data();
+    g.u_right2 = uRight2.empty() ? NULL : uRight2.data();
+    g.nlevels = (int)scaleFactors2.size(); g.scale_factors2 = scaleFactors2.data(); g.level_sigma2_2 = levelSigma2_2.data();
+    std::vector<int> vMatches12(keysUn1.size(), -1);
+    int nmatches = 0;
+    check(borb_voc_search_for_triangulation(voc, &a.rec, &b.rec, &g,
+                                            (checkOrientation ? 0u : BORB_MATCH_NO_ORIENTATION) | (bOnlyStereo ? BORB_MATCH_ONLY_STEREO : 0u),
+                                            vMatches12.data(), &nmatches),
+          "search for triangulation");
+    vMatchedPairs.clear();
+    vMatchedPairs.reserve((size_t)std::max(nmatches, 0));
+    for (size_t i = 0; i < vMatches12.size(); ++i) /* :950-956 */
+        if (vMatches12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)vMatches12[i]));
+    return nmatches;
+}
+
 int ORBextractor::SearchByBoW(const cv::Mat &kfDescriptors, const std::vector<cv::KeyPoint> &kfKeysUn,
                               const unsigned char *kfMapPointFlags, const std::map<unsigned int, std::vector<unsigned int> > &kfFeatVec,
                               float nnRatio, bool checkOrientation, std::vector<int> &vnMatches)

@@ -71,6 +71,18 @@ public:
                     const std::vector<cv::KeyPoint> &keysUn2, const unsigned char *mapPointFlags2,
                     const std::map<unsigned int, std::vector<unsigned int> > &featVec2, float nnRatio, bool checkOrientation,
                     std::vector<int> &vnMatches12);
+    // ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vector<pair<size_t, size_t> >
+    // &vMatchedPairs, const bool bOnlyStereo) (reference src/ORBmatcher.cc:779-966, LocalMapping::CreateNewMapPoints) on the
+    // device.  Keyframes as for SearchByBoW (bit 0 of the flag byte: the keypoint has a map point) plus mvuRight (empty =
+    // monocular); Ow1 = pKF1->GetCameraCenter() (3x1 CV_32F), Tcw2 = pKF2->GetPose() (4x4 CV_32F), pKF2's intrinsics and
+    // level tables.  Returns nmatches; vMatchedPairs as the reference fills it.
+    int SearchForTriangulation(const cv::Mat &descriptors1, const std::vector<cv::KeyPoint> &keysUn1, const unsigned char *mapPointFlags1,
+                               const std::map<unsigned int, std::vector<unsigned int> > &featVec1, const std::vector<float> &uRight1,
+                               const cv::Mat &Ow1, const cv::Mat &descriptors2, const std::vector<cv::KeyPoint> &keysUn2,
+                               const unsigned char *mapPointFlags2, const std::map<unsigned int, std::vector<unsigned int> > &featVec2,
+                               const std::vector<float> &uRight2, const cv::Mat &Tcw2, float fx2, float fy2, float cx2, float cy2,
+                               const std::vector<float> &scaleFactors2, const std::vector<float> &levelSigma2_2, const cv::Mat &F12,
+                               std::vector<std::pair<size_t, size_t> > &vMatchedPairs, bool bOnlyStereo, bool checkOrientation = true);
     borb_vocabulary *get() const { return voc; }
 
 private:

@@ -69,3 +69,40 @@ def same_bow(a: dict, b: dict) -> bool:
             np.array_equal(a["word_val"].view(np.uint64), b["word_val"].view(np.uint64)) and
             np.array_equal(a["node_id"], b["node_id"]) and np.array_equal(a["node_start"], b["node_start"]) and
             np.array_equal(a["feat_idx"], b["feat_idx"]))
+
+
+def triangulation_case(shape=synth.TUM_SHAPE, seed=3, t=0, nf=1000, baseline=(0.08, 0.0, 0.02), stereo_rate=0.0, has=0.5,
+                       K=(517.306408, 516.469215, 318.643040, 255.313989)):
+    """Scenario for ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:779-966): keyframe 1 = frame t, keyframe 2 =
+    frame t + 1 of the synthetic sequence (shifted by (3, 1) px: a small yaw / pitch of the camera), plus a translation
+    `baseline` that gives the pair an epipolar geometry; F12 as LocalMapping::ComputeF12 builds it (computed in double
+    here: the matcher takes it as an argument).  `has` of the keypoints of either side already carry a map point (left
+    out by the matcher), `stereo_rate` of them have mvuRight >= 0.
+    -> (kf1, kf2, geo) as oracle.pyoracle.RefBow.search_for_triangulation takes them"""
+    import matchcase
+    k1, d1 = frame_features(shape, seed, t, nf)
+    k2, d2 = frame_features(shape, seed, t + 1, nf)
+    rng = np.random.default_rng(8000 + seed + 17 * t)
+    T1 = matchcase.pose(0.01, -0.02, 0.005, (0.3, -0.1, 0.2))
+    rel = matchcase.pose(rx=1.0 / K[1], ry=-3.0 / K[0], t=baseline)
+    T2 = matchcase.compose(rel, T1)
+    Km = np.array([[K[0], 0, K[2]], [0, K[1], K[3]], [0, 0, 1]], np.float64)
+    R1, t1 = T1[:, :3].astype(np.float64), T1[:, 3].astype(np.float64)
+    R2, t2 = T2[:, :3].astype(np.float64), T2[:, 3].astype(np.float64)
+    R12 = R1 @ R2.T
+    t12 = -R1 @ R2.T @ t2 + t1
+    tx = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    F12 = np.linalg.inv(Km.T) @ tx @ R12 @ np.linalg.inv(Km)
+    F12 = (F12 / np.abs(F12).max()).astype(np.float32)
+
+    def side(k, d, T, s):
+        n = len(k)
+        ur = np.where(rng.random(n) < stereo_rate, k["x"] - rng.uniform(2, 40, n).astype(np.float32), -1.0).astype(np.float32)
+        return {"kps": k, "desc": d, "mp": (rng.random(n) < has).astype(np.uint8), "u_right": ur if stereo_rate > 0 else None,
+                "Tcw": T}
+    sc = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+    scale = np.ones(8, np.float32)
+    for i in range(1, 8):
+        scale[i] = np.float32(np.float64(scale[i - 1]) * 1.2)  # mvScaleFactor[i] = mvScaleFactor[i-1] * scaleFactor (double member)
+    geo = {"cam2": np.array(K, np.float32), "scale2": scale, "sigma2_2": (scale * scale).astype(np.float32), "F12": F12}
+    return side(k1, d1, T1, 0), side(k2, d2, T2, 1), geo

@@ -163,3 +163,49 @@ def test_search_by_bow_between_keyframes(name, shape, nf, vocdir, oracle_built):
     broken["fv"]["feat_idx"] = kfs[0]["fv"]["feat_idx"] + np.uint32(100000)
     with pytest.raises(BorbError):
         voc.search_by_bow(broken, kfs[1])
+
+
+def _tri_abi(kf, voc):
+    """a keyframe of bowcase.triangulation_case as ORBVocabulary.search_for_triangulation takes it"""
+    k = kf["kps"]
+    return {"desc": kf["desc"], "angle": k["angle"], "mp_flags": kf["mp"], "fv": voc.transform(kf["desc"], 4),
+            "xy": np.stack([k["x"], k["y"]], 1).astype(np.float32), "octave": k["octave"].astype(np.int32),
+            "u_right": kf.get("u_right")}
+
+
+@pytest.mark.parametrize("name,shape,nf,kw", [
+    ("k10L4", synth.TUM_SHAPE, 1000, dict()),
+    ("k4L6", synth.KITTI_SHAPE, 2000, dict(baseline=(0.02, 0.01, 0.25), K=(718.856, 718.856, 607.1928, 185.2157))),
+    ("k9L5ragged", synth.TUM_SHAPE, 2000, dict(stereo_rate=0.5)),
+    ("k10L3", synth.TUM_SHAPE, 500, dict(baseline=(0.0, 0.0, 0.3), has=0.2)),
+])
+def test_search_for_triangulation(name, shape, nf, kw, vocdir, oracle_built):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:779-966) through borb_voc_search_for_triangulation against the
+    restatement (equal to the reference's object code, tests/test_oracle_bow_vs_reference.py)"""
+    from oracle import pyoracle
+    from orb_slam2_test_b200 import BorbError, ORBVocabulary
+    path = bowcase.vocabulary(vocdir, name)
+    voc, want = ORBVocabulary(path), pyoracle.BowVocabulary(path)
+    total = 0
+    for t in (0, 2):
+        kf1, kf2, geo = bowcase.triangulation_case(shape=shape, t=t, nf=nf, **kw)
+        a, b = _tri_abi(kf1, voc), _tri_abi(kf2, voc)
+        g = dict(geo)
+        g["Ow1"], g["Tcw2"] = pyoracle.camera_centre(kf1["Tcw"]), kf2["Tcw"]
+        for only_stereo, ori in ((False, True), (False, False), (True, True)):
+            w, wnm = want.search_for_triangulation(kf1, kf2, geo, only_stereo, ori)
+            for rep in range(2):
+                got, nm = voc.search_for_triangulation(a, b, g, only_stereo, ori)
+                bad = np.nonzero(got != w)[0]
+                assert bad.size == 0 and nm == wnm, f"{name} t={t} stereo={only_stereo} ori={ori}: {bad.size} differ, nm {nm} vs {wnm}, e.g. {bad[:5]}"
+            total += nm
+        # interleaved with the keyframe-to-keyframe BoW matcher on the same scratch
+        voc.search_by_bow(a, b, 0.75)
+        got, nm = voc.search_for_triangulation(a, b, g)
+        w, wnm = want.search_for_triangulation(kf1, kf2, geo)
+        assert np.array_equal(got, w) and nm == wnm
+    assert total > 60
+    bad_oct = dict(b)
+    bad_oct["octave"] = b["octave"] + 8
+    with pytest.raises(BorbError):
+        voc.search_for_triangulation(a, bad_oct, g)

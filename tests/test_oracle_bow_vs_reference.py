@@ -112,3 +112,28 @@ def test_search_by_bow_between_keyframes_equals_the_reference(name, shape, nf, v
     z = np.zeros(0, np.uint8)
     assert ref.search_by_bow_kf(ek, e, z, k2, d2, m2)[1] == ours.search_by_bow_kf(ek, e, z, k2, d2, m2)[1] == 0
     assert ref.search_by_bow_kf(k1, d1, m1, ek, e, z)[1] == ours.search_by_bow_kf(k1, d1, m1, ek, e, z)[1] == 0
+
+
+@pytest.mark.parametrize("name,shape,nf,kw", [
+    ("k10L4", synth.TUM_SHAPE, 1000, dict()),
+    ("k4L6", synth.KITTI_SHAPE, 2000, dict(baseline=(0.02, 0.01, 0.25), K=(718.856, 718.856, 607.1928, 185.2157))),
+    ("k9L5ragged", synth.TUM_SHAPE, 2000, dict(stereo_rate=0.5)),
+    ("k10L3", synth.TUM_SHAPE, 500, dict(baseline=(0.0, 0.0, 0.3), has=0.2)),
+])
+def test_search_for_triangulation_equals_the_reference(name, shape, nf, kw, vocdir, oracle_built):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:779-966) + CheckDistEpipolarLine (:165-182): sideways and
+    forward baselines (the epipole inside the image: the 100 * scale exclusion zone, :874-879), half of the keypoints
+    stereo, bOnlyStereo, orientation check on and off"""
+    path = bowcase.vocabulary(vocdir, name)
+    ref, ours = pyoracle.RefBow(path), pyoracle.BowVocabulary(path)
+    total = 0
+    for t in (0, 2):
+        kf1, kf2, geo = bowcase.triangulation_case(shape=shape, t=t, nf=nf, **kw)
+        for only_stereo, ori in ((False, True), (False, False), (True, True)):
+            want, wnm = ref.search_for_triangulation(kf1, kf2, geo, only_stereo, ori)
+            got, nm = ours.search_for_triangulation(kf1, kf2, geo, only_stereo, ori)
+            assert np.array_equal(got, want) and nm == wnm, f"{name} t={t} stereo={only_stereo} ori={ori}: {(got != want).sum()} differ"
+            hit = got >= 0
+            assert nm == int(hit.sum()) and not (kf1["mp"][hit] & 1).any() and not (kf2["mp"][got[hit]] & 1).any()
+            total += nm
+    assert total > 60
