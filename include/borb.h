@@ -116,6 +116,14 @@ void borb_host_free(void *p);
 int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n_frames, int cols,
                         int rows, size_t step, size_t frame_stride);
 int borb_fetch(borb_extractor *h, unsigned flags);
+/* Put a frame extracted earlier -- a KeyFrame, which carries its Frame's mvKeys and mDescriptors (src/KeyFrame.cc) -- back
+ * into the handle as if an extract call had just produced it (frame 0 of a one-frame call): with a camera set, mvKeysUn,
+ * mGrid and the bounds are rebuilt on the device from the records, and every matcher below takes the handle as that
+ * frame.  cols, rows = the image size the frame came from.  No counterpart in the reference (its keyframes live in host
+ * memory); this is how the keyframe matchers reach a keyframe on the device.
+ * u_right = the keyframe's mvuRight (what BORB_MATCH_USE_STEREO then reads) or NULL for a monocular one. */
+int borb_load_frame(borb_extractor *h, const borb_keypoint *kps, const uint8_t *desc, const float *u_right, int n, int cols,
+                    int rows);
 /* blocks until everything enqueued on the handle's stream has finished */
 int borb_sync(borb_extractor *h);
 
@@ -254,6 +262,32 @@ typedef struct borb_keyframe_points {
 int borb_search_by_projection_keyframe(borb_extractor *cur, int frame, const borb_keyframe_points *kf, const float *Tcw_cur,
                                        const uint8_t *occupied, float th, int orb_dist, unsigned flags, int32_t *match,
                                        int *n_cur, int *nmatches);
+
+/* -- the fuse matcher: replaces the search inside ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints,
+ *    const float th) (src/ORBmatcher.cc:968-1131, LocalMapping::SearchInNeighbors) ---------------------------------- */
+
+/* The map points as the matcher reads them: entry i is vpMapPoints[i].
+ *   flags[i]    bit 0: vpMapPoints[i] != NULL, bit 1: isBad(), bit 2: IsInKeyFrame(pKF)
+ *   xyz, desc   GetWorldPos(), GetDescriptor();  dist[2i], [2i + 1] = mfMinDistance, mfMaxDistance (raw members, as
+ *               borb_keyframe_points);  normal[3i..] = GetNormal() */
+typedef struct borb_fuse_points {
+    int n;
+    const float *xyz;
+    const uint8_t *desc;
+    const uint8_t *flags;
+    const float *dist;
+    const float *normal;
+} borb_fuse_points;
+
+/* pKF = frame `frame` of kf's last call: a keyframe put into the handle by borb_load_frame (camera set; its mvScaleFactors,
+ * mvInvLevelSigma2, mfLogScaleFactor are the handle's).  Tcw = pKF's pose rows 0-2 (GetRotation / GetTranslation), Ow =
+ * pKF->GetCameraCenter(), bf = pKF->mbf, th as the caller passes it (3.0 by default).  flags: BORB_MATCH_USE_STEREO = the
+ * keyframe's mvuRight was loaded (its stereo keypoints take the 3-dof chi-square test :1063-1070).
+ * best_idx[i] = the keypoint bestIdx of pKF that map point i is fused into (bestDist <= TH_LOW, :1103) or -1; *nfused = the
+ * function's return value.  What follows in the reference (:1103-1127: Replace / AddObservation / AddMapPoint, in the order
+ * of i) mutates the map and stays with the caller: it reads nothing the choice depends on. */
+int borb_fuse_search(borb_extractor *kf, int frame, const borb_fuse_points *mps, const float *Tcw, const float *Ow, float bf,
+                     float th, unsigned flags, int32_t *best_idx, int *nfused);
 
 /* -- monocular-initialisation matcher: replaces ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2,
  *    vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12, int windowSize)

@@ -477,5 +477,102 @@ int mo_search_by_projection_kf(const mo_frame *cur, const float *cam, const floa
     return nmatches;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, const float th)
+ *     /root/reference/src/ORBmatcher.cc:968-1131 -- LocalMapping::SearchInNeighbors.  The CHOICE of a keypoint per map
+ *     point (what the function does to the map afterwards, :1103-1127, stays with the caller).  kf = the keyframe as a frame
+ *     record (kps with octaves, un_xy, desc, u_right, grid, Tcw); bounds = the Frame's FLOAT mnMinX, mnMaxX, mnMinY, mnMaxY:
+ *     the keyframe's own are these truncated to int (include/KeyFrame.h: const int), its grid factors the Frame's floats.
+ * Float forms as the reference object has them:
+ *   p3Dc = Rcw * p3Dw + tcw (small float product); skipped when z < 0; invz = 1.0f / z; x = xc * invz;
+ *   u = fmaf(x, fx, cx), v likewise; IsInImage on the int bounds; ur = fmaf(-bf, invz, u)                       (:993-1011)
+ *   dist3D = (float)cv::norm(p3Dw - Ow) with Ow = pKF->GetCameraCenter(); 0.8f * min, 1.2f * max                (:1013-1021)
+ *   PO.dot(Pn) summed in double, < 0.5 * (double)dist3D -> skipped                                              (:1024-1027)
+ *   PredictScale(dist3D, pKF); radius = th * mvScaleFactors[level]; keypoint levels level-1 .. level             (:1029-1054)
+ *   t = fmaf(ex, ex, ey * ey); stereo keypoint: (double)(fmaf(er, er, t) * invSigma2) > 7.8, else
+ *   (double)(invSigma2 * t) > 5.99 -> skipped                                                                    (:1056-1083)
+ *   first smallest Hamming distance in GetFeaturesInArea order; chosen when <= TH_LOW                            (:1085-1101)
+ */
+int mo_fuse(const mo_frame *kf, const float *cam, const float *bounds, const float *scale, const float *inv_sigma2, int nlevels,
+            float log_scale, int n_mp, const uint8_t *mp_flags, const float *mp_xyz, const uint8_t *mp_desc, const float *mp_dist,
+            const float *mp_normal, float th, int32_t *out_best)
+{
+    const float fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3], bf = cam[4];
+    const int min_x = (int)bounds[0], max_x = (int)bounds[1], min_y = (int)bounds[2], max_y = (int)bounds[3];
+    const float winv = (float)MO_COLS / (bounds[1] - bounds[0]), hinv = (float)MO_ROWS / (bounds[3] - bounds[2]);
+    const mo_kp *kk = reinterpret_cast<const mo_kp *>(kf->kps);
+    const float *Tc = kf->Tcw;
+    float Ow[3];
+    for (int y = 0; y < 3; ++y) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += (double)Tc[4 * k + y] * (double)Tc[4 * k + 3];
+        Ow[y] = (float)(s * -1.0);
+    }
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + kf->grid_count[c];
+    int nfused = 0;
+    for (int i = 0; i < n_mp; ++i) {
+        out_best[i] = -1;
+        if (!(mp_flags[i] & 1) || (mp_flags[i] & 6)) continue;
+        const float *X = mp_xyz + 3 * i;
+        const float xc = mo_dot3(Tc, 1, X) + Tc[3], yc = mo_dot3(Tc + 4, 1, X) + Tc[7], zc = mo_dot3(Tc + 8, 1, X) + Tc[11];
+        if (zc < 0.0f) continue;
+        const float invz = 1.0f / zc;
+        const float x = xc * invz, y = yc * invz;
+        const float u = std::fmaf(x, fx, cx), v = std::fmaf(y, fy, cy);
+        if (!(u >= min_x && u < max_x && v >= min_y && v < max_y)) continue;
+        const float ur = std::fmaf(-bf, invz, u);
+        double s2 = 0.0, dotn = 0.0;
+        float PO[3];
+        for (int k = 0; k < 3; ++k) {
+            PO[k] = X[k] - Ow[k];
+            s2 += (double)PO[k] * (double)PO[k];
+        }
+        const float dist3D = (float)std::sqrt(s2);
+        if (dist3D < 0.8f * mp_dist[2 * i] || dist3D > 1.2f * mp_dist[2 * i + 1]) continue;
+        for (int k = 0; k < 3; ++k) dotn += (double)PO[k] * (double)mp_normal[3 * i + k];
+        if (dotn < 0.5 * (double)dist3D) continue;
+        const float ratio = mp_dist[2 * i + 1] / dist3D;
+        int lvl = (int)std::ceil(std::log(ratio) / log_scale);
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= nlevels) lvl = nlevels - 1;
+        const float radius = th * scale[lvl];
+        /* KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:750-789) fused with the candidate loop */
+        const int cx0 = std::max(0, (int)std::floor((u - min_x - radius) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((u - min_x + radius) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((v - min_y - radius) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((v - min_y + radius) * hinv));
+        if (cy1 < 0) continue;
+        int best = 256, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int idx = kf->grid_idx[q];
+                    const float kx = kf->un_xy[2 * idx], ky = kf->un_xy[2 * idx + 1];
+                    if (!(std::fabs(kx - u) < radius && std::fabs(ky - v) < radius)) continue;
+                    const int lv = kk[idx].octave;
+                    if (lv < lvl - 1 || lv > lvl) continue;
+                    const float ex = u - kx, ey = v - ky;
+                    const float t = std::fmaf(ex, ex, ey * ey);
+                    const float kr = kf->u_right ? kf->u_right[idx] : -1.f;
+                    if (kr >= 0) {
+                        const float er = ur - kr;
+                        const float e2 = std::fmaf(er, er, t);
+                        if ((double)(e2 * inv_sigma2[lv]) > 7.8) continue;
+                    } else if ((double)(inv_sigma2[lv] * t) > 5.99) continue;
+                    const int d = mo_hamming256(mp_desc + (size_t)i * 32, kf->desc + (size_t)idx * 32);
+                    if (d < best) { best = d; best_idx = idx; }
+                }
+            }
+        if (best <= 50) { out_best[i] = best_idx; ++nfused; }
+    }
+    return nfused;
+}
+
 } // extern "C"
+
 

@@ -22,18 +22,24 @@ public:
     int Observations() { return nObs; }
     bool isBad() { return mbBad; }
 
-    cv::Mat GetNormal() { std::abort(); }
+    cv::Mat mNormalVector; /* 3x1 CV_32F */
+    cv::Mat GetNormal() { return mNormalVector.clone(); }
     /* src/MapPoint.cc:520-530 and :575-590, restated (the reference's MapPoint.cc needs the whole map model); the body of
      * PredictScale is in MapPoint_impl.h, which the drivers include where Frame is complete */
     float mfMinDistance = 0, mfMaxDistance = 0;
     float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
     float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }
     int PredictScale(const float &currentDist, Frame *pF);
-    int PredictScale(const float &, KeyFrame *) { std::abort(); }
-    bool IsInKeyFrame(KeyFrame *) { std::abort(); }
-    void Replace(MapPoint *) { std::abort(); }
-    void AddObservation(KeyFrame *, size_t) { std::abort(); }
-    int GetIndexInKeyFrame(KeyFrame *) { std::abort(); }
+    int PredictScale(const float &currentDist, KeyFrame *pKF); /* src/MapPoint.cc:557-572, body in MapPoint_impl.h */
+    /* the observation graph reduced to the one keyframe a matcher call works on (src/MapPoint.cc: IsInKeyFrame,
+     * AddObservation, Replace, GetIndexInKeyFrame); what the keyframe matchers do with the map AFTER choosing a keypoint is
+     * recorded, not modelled: the drivers read the choice out of KeyFrame::GetMapPoint's log */
+    bool mbInKF = false;
+    int mnIdxInKF = -1;
+    bool IsInKeyFrame(KeyFrame *) { return mbInKF; }
+    void Replace(MapPoint *) { mbBad = true; }
+    void AddObservation(KeyFrame *, size_t idx) { mbInKF = true; mnIdxInKF = (int)idx; ++nObs; }
+    int GetIndexInKeyFrame(KeyFrame *) { return mbInKF ? mnIdxInKF : -1; }
 
     float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 0;
     bool mbTrackInView = false;

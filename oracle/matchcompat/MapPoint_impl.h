@@ -21,5 +21,16 @@ int MapPoint::PredictScale(const float &currentDist, Frame *pF)
         nScale = pF->mnScaleLevels - 1;
     return nScale;
 }
+int MapPoint::PredictScale(const float &currentDist, KeyFrame *pKF) /* src/MapPoint.cc:557-572 */
+{
+    float ratio;
+    ratio = mfMaxDistance / currentDist;
+    int nScale = ceil(log(ratio) / pKF->mfLogScaleFactor);
+    if (nScale < 0)
+        nScale = 0;
+    else if (nScale >= pKF->mnScaleLevels)
+        nScale = pKF->mnScaleLevels - 1;
+    return nScale;
+}
 } // namespace ORB_SLAM2
 #endif

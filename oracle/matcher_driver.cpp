@@ -290,5 +290,94 @@ int refmatch_search_by_projection_kf(const refmatch_frame *cur, const float *cam
     return nm;
 }
 
+namespace {
+/* a keyframe stand-in (oracle/matchcompat/KeyFrame.h) filled the way KeyFrame::KeyFrame(Frame &F, ...) copies a Frame
+ * (src/KeyFrame.cc): keypoints, descriptors, grid, the Frame's float grid factors and its bounds TRUNCATED to int */
+void fill_keyframe(KeyFrame &kf, const refmatch_frame &r, const float *cam, const float *bounds, const float *scale,
+                   const float *inv_sigma2, int nlevels, float log_scale)
+{
+    kf.N = r.n;
+    kf.mvKeys.resize(r.n);
+    if (r.n) std::memcpy(kf.mvKeys.data(), r.kps, (size_t)r.n * 28);
+    kf.mvKeysUn = kf.mvKeys;
+    for (int i = 0; i < r.n; ++i) { kf.mvKeysUn[i].pt.x = r.un_xy[2 * i]; kf.mvKeysUn[i].pt.y = r.un_xy[2 * i + 1]; }
+    kf.mDescriptors = cv::Mat(r.n, 32, CV_8UC1);
+    for (int i = 0; i < r.n; ++i) std::memcpy(kf.mDescriptors.ptr(i), r.desc + (size_t)i * 32, 32);
+    kf.mvuRight.assign(r.n, -1.f);
+    if (r.u_right) kf.mvuRight.assign(r.u_right, r.u_right + r.n);
+    kf.mvpMapPoints.assign(r.n, static_cast<MapPoint *>(NULL));
+    kf.fx = cam[0]; kf.fy = cam[1]; kf.cx = cam[2]; kf.cy = cam[3]; kf.mbf = cam[4]; kf.mb = cam[5];
+    kf.invfx = 1.0f / cam[0]; kf.invfy = 1.0f / cam[1];
+    kf.mnMinX = bounds[0]; kf.mnMaxX = bounds[1]; kf.mnMinY = bounds[2]; kf.mnMaxY = bounds[3]; /* float -> int, as the const int members */
+    kf.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(bounds[1] - bounds[0]);  /* the Frame's, src/Frame.cc:135-136 */
+    kf.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(bounds[3] - bounds[2]);
+    kf.mnScaleLevels = nlevels;
+    kf.mfLogScaleFactor = log_scale;
+    kf.mvScaleFactors.assign(scale, scale + nlevels);
+    kf.mvInvLevelSigma2.assign(inv_sigma2, inv_sigma2 + nlevels);
+    kf.mGrid.assign(FRAME_GRID_COLS, std::vector<std::vector<size_t> >(FRAME_GRID_ROWS));
+    int k = 0;
+    for (int i = 0; i < FRAME_GRID_COLS; ++i)
+        for (int j = 0; j < FRAME_GRID_ROWS; ++j) {
+            const int c = r.grid_count[i * FRAME_GRID_ROWS + j];
+            kf.mGrid[i][j].assign(r.grid_idx + k, r.grid_idx + k + c);
+            k += c;
+        }
+    kf.Tcw_ = pose_mat(r.Tcw);
+    cv::Mat Rcw = kf.Tcw_.rowRange(0, 3).colRange(0, 3);
+    cv::Mat tcw = kf.Tcw_.rowRange(0, 3).col(3);
+    kf.Ow_ = -Rcw.t() * tcw; /* KeyFrame::SetPose */
+}
+} // namespace
+
+/* ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, const float th) (src/ORBmatcher.cc:968-1131), the
+ * matcher of LocalMapping::SearchInNeighbors.  What it does to the map after choosing a keypoint (Replace / AddObservation /
+ * AddMapPoint, :1103-1127) is the map model's business; what is pinned here is the CHOICE: the reference's function is run
+ * on one map point at a time -- its loop carries no state from one point to the next besides the map it mutates, and the
+ * choice reads none of that -- and the keypoint it hands to pKF->GetMapPoint (:1105) is recorded.  A second run over the
+ * whole vector must fuse the same number.  mp_flags[i] bit 0 = vpMapPoints[i] != NULL, bit 1 = isBad(), bit 2 =
+ * IsInKeyFrame(pKF); mp_dist[2i], [2i + 1] = mfMinDistance, mfMaxDistance; mp_normal[3i..] = GetNormal().
+ * out_best[i] = the chosen keypoint of pKF or -1.  Returns nFused of the whole-vector run. */
+int refmatch_fuse(const refmatch_frame *kfr, const float *cam, const float *bounds, const float *scale, const float *inv_sigma2,
+                  int nlevels, float log_scale, int n_mp, const uint8_t *mp_flags, const float *mp_xyz, const uint8_t *mp_desc,
+                  const float *mp_dist, const float *mp_normal, float th, int32_t *out_best)
+{
+    int total = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        KeyFrame kf;
+        fill_keyframe(kf, *kfr, cam, bounds, scale, inv_sigma2, nlevels, log_scale);
+        std::vector<MapPoint> mps(n_mp);
+        std::vector<MapPoint *> vp(n_mp, static_cast<MapPoint *>(NULL));
+        for (int i = 0; i < n_mp; ++i) {
+            if (!(mp_flags[i] & 1)) continue;
+            MapPoint &m = mps[i];
+            m.mWorldPos = cv::Mat(3, 1, CV_32F);
+            m.mNormalVector = cv::Mat(3, 1, CV_32F);
+            for (int c = 0; c < 3; ++c) { m.mWorldPos.at<float>(c) = mp_xyz[3 * i + c]; m.mNormalVector.at<float>(c) = mp_normal[3 * i + c]; }
+            m.mDescriptor = cv::Mat(1, 32, CV_8UC1);
+            std::memcpy(m.mDescriptor.ptr(0), mp_desc + (size_t)i * 32, 32);
+            m.mbBad = (mp_flags[i] & 2) != 0;
+            m.mbInKF = (mp_flags[i] & 4) != 0;
+            m.mfMinDistance = mp_dist[2 * i];
+            m.mfMaxDistance = mp_dist[2 * i + 1];
+            m.nObs = 1;
+            vp[i] = &m;
+        }
+        ORBmatcher matcher(0.6f, true);
+        if (pass == 0) {
+            for (int i = 0; i < n_mp; ++i) {
+                kf.mnLastGetMapPoint = -1;
+                std::vector<MapPoint *> one(1, vp[i]);
+                const int nf = matcher.Fuse(&kf, one, th);
+                out_best[i] = nf ? (int32_t)kf.mnLastGetMapPoint : -1;
+                total += nf;
+            }
+        } else if (matcher.Fuse(&kf, vp, th) != total)
+            std::abort();
+    }
+    return total;
+}
+
 } // extern "C"
+
 

@@ -370,8 +370,50 @@ def search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occupied, th
                        orb_dist, check_ori)
 
 
+def _fuse_call(fn, kf: dict, cam, bounds, scale, inv_sigma2, log_scale: float, mps: dict, th: float):
+    """Common marshalling for mo_fuse / refmatch_fuse.  kf as _match_call's current frame (kps, un_xy, desc, u_right, grid,
+    Tcw); mps: flags [n] u8 (bit 0 map point, bit 1 bad, bit 2 already in the keyframe), xyz [n,3], desc [n,32], dist [n,2]
+    (mfMinDistance, mfMaxDistance), normal [n,3].  -> (best [n] i32: the keyframe keypoint chosen per map point or -1, nFused)."""
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+
+    f = _MatchFrame()
+    f.n = len(kf["kps"])
+    f.kps = arr(kf["kps"], KP_DTYPE)
+    f.un_xy = arr(kf["un_xy"], np.float32)
+    f.desc = arr(kf["desc"], np.uint8)
+    f.u_right = arr(kf["u_right"], np.float32) if kf.get("u_right") is not None else None
+    f.grid_count = arr(np.diff(kf["cell_start"]), np.int32)
+    f.grid_idx = arr(kf["cell_idx"], np.int32)
+    f.Tcw = arr(kf["Tcw"], np.float32)
+    scale = np.ascontiguousarray(scale, np.float32)
+    n = len(mps["flags"])
+    out = np.full(max(n, 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int, C.c_float, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_float, _vp]
+    nf = fn(C.addressof(f), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data, arr(inv_sigma2, np.float32),
+            len(scale), float(log_scale), n, arr(mps["flags"], np.uint8), arr(mps["xyz"], np.float32), arr(mps["desc"], np.uint8),
+            arr(mps["dist"], np.float32), arr(mps["normal"], np.float32), float(th), out.ctypes.data)
+    return out[:n], int(nf)
+
+
+def fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th=3.0):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:968-1131): the choice per map point, restated"""
+    return _fuse_call(Oracle.load().mo_fuse, kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
+
+
 class RefMatcher:
     """The reference's own src/ORBmatcher.cc + src/Frame.cc (oracle/_ref/librefmatch.so)."""
+
+    @classmethod
+    def fuse(cls, kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th=3.0):
+        if cls._lib is None:
+            cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
+        return _fuse_call(cls._lib.refmatch_fuse, kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
 
     @classmethod
     def search_by_projection_kf(cls, cur, cam, bounds, scale, log_scale, kf, occupied, th=10.0, orb_dist=100, check_ori=True):

@@ -1052,18 +1052,9 @@ static int ensure_input(borb_extractor *h, size_t bytes)
 
 /* cols x rows: the SOURCE image (in_ch interleaved channels); the extractor's geometry is the
  * rectification map's when one is set */
-static int check_call(borb_extractor *h, const void *img, int n, int cols, int rows, size_t step,
-                      size_t stride)
+/* K8's outputs (undistorted positions, grid, bounds): one slab on either side of the link, once a camera is set */
+static int ensure_frame_buffers(borb_extractor *h)
 {
-    if (!h || !img) return fail(BORB_ERR_ARG, "null handle or image");
-    const size_t row_bytes = (size_t)cols * h->in_ch;
-    if (n < 1 || cols < 1 || rows < 1 || step < row_bytes || (n > 1 && stride < step * (size_t)(rows - 1) + row_bytes))
-        return fail(BORB_ERR_ARG, "bad image geometry");
-    if (n > h->max_batch) return fail(BORB_ERR_CAPACITY, "%d frames > max_batch %d", n, h->max_batch);
-    CU(cudaSetDevice(h->device));
-    const int ocols = h->d_map_xy ? h->map_cols : cols, orows = h->d_map_xy ? h->map_rows : rows;
-    int rc = build_plan(h, ocols, orows);
-    if (rc != BORB_OK) return rc;
     if (h->have_cam && !h->d_un_xy) {
         const size_t B = (size_t)h->max_batch, K = (size_t)h->plan.kp_total;
         const size_t o_cs = (size_t)align_up((long long)(B * K * 8), 256);
@@ -1080,6 +1071,22 @@ static int check_call(borb_extractor *h, const void *img, int n, int cols, int r
         h->d_cell_idx = reinterpret_cast<int *>(h->d_fr + o_ci); h->h_cell_idx = reinterpret_cast<int *>(h->h_fr + o_ci);
         h->d_bounds = reinterpret_cast<float *>(h->d_fr + o_bd); h->h_bounds = reinterpret_cast<float *>(h->h_fr + o_bd);
     }
+    return BORB_OK;
+}
+
+static int check_call(borb_extractor *h, const void *img, int n, int cols, int rows, size_t step,
+                      size_t stride)
+{
+    if (!h || !img) return fail(BORB_ERR_ARG, "null handle or image");
+    const size_t row_bytes = (size_t)cols * h->in_ch;
+    if (n < 1 || cols < 1 || rows < 1 || step < row_bytes || (n > 1 && stride < step * (size_t)(rows - 1) + row_bytes))
+        return fail(BORB_ERR_ARG, "bad image geometry");
+    if (n > h->max_batch) return fail(BORB_ERR_CAPACITY, "%d frames > max_batch %d", n, h->max_batch);
+    CU(cudaSetDevice(h->device));
+    const int ocols = h->d_map_xy ? h->map_cols : cols, orows = h->d_map_xy ? h->map_rows : rows;
+    int rc = build_plan(h, ocols, orows);
+    if (rc != BORB_OK) return rc;
+    if ((rc = ensure_frame_buffers(h)) != BORB_OK) return rc;
     if (pre_active(h) && !h->d_gray) {
         h->gray_pitch = (ocols + 3) & ~3;
         CU(cudaMalloc(&h->d_gray, (size_t)h->max_batch * h->gray_pitch * orows));
@@ -1223,6 +1230,56 @@ int borb_extract_device(borb_extractor *h, const uint8_t *dev_img, int n, int co
     CU(cudaEventRecord(h->ev1, h->stream));
     h->last_n = n;
     note_new_extract(h);
+    return BORB_OK;
+}
+
+/* A frame that was extracted earlier (a KeyFrame: src/KeyFrame.cc copies mvKeys, mDescriptors and the grid from the Frame it
+ * was made from) put back into the handle as if an extract call had just produced it: records and descriptors are uploaded
+ * into slot 0 of the result arrays and, with a camera set, K8 rebuilds mvKeysUn, mGrid and the bounds from them (the same
+ * arithmetic that filled the Frame's).  Every matcher then takes the handle as that frame. */
+int borb_load_frame(borb_extractor *h, const borb_keypoint *kps, const uint8_t *desc, const float *u_right, int n, int cols,
+                    int rows)
+{
+    if (!h || n < 0 || (n > 0 && (!kps || !desc)) || cols < 1 || rows < 1) return fail(BORB_ERR_ARG, "arguments");
+    if (h->pending) return fail(BORB_ERR_STATE, "a submitted call has not been waited for");
+    CU(cudaSetDevice(h->device));
+    int rc = build_plan(h, cols, rows);
+    if (rc != BORB_OK) return rc;
+    if ((rc = ensure_frame_buffers(h)) != BORB_OK) return rc;
+    const BorbPlan &P = h->plan;
+    if (n > P.kp_total) return fail(BORB_ERR_CAPACITY, "%d keypoints; a frame of this extractor holds at most %d", n, P.kp_total);
+    cudaStream_t st = h->stream;
+    CU(cudaStreamSynchronize(st)); /* the page-locked twins are about to be overwritten */
+    if (n) {
+        std::memcpy(h->h_out_kp, kps, (size_t)n * sizeof(BorbKpRec));
+        std::memcpy(h->h_out_desc, desc, (size_t)n * 32);
+        CU(cudaMemcpyAsync(h->d_out_kp, h->h_out_kp, (size_t)n * sizeof(BorbKpRec), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->d_out_desc, h->h_out_desc, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    }
+    h->h_nout[0] = n;
+    h->h_err[0] = 0;
+    CU(cudaMemcpyAsync(h->d_nout, h->h_nout, 4, cudaMemcpyHostToDevice, st));
+    if (h->have_cam)
+        k_frame_undistort_grid<FR_NT_LATENCY><<<1, FR_NT_LATENCY, 0, st>>>(h->d_plan, h->cam, h->d_out_kp, h->d_nout, h->d_un_xy,
+                                                                          h->d_cell_start, h->d_cell_idx, h->d_cell_of, h->d_bounds);
+    CU(cudaGetLastError());
+    h->last_n = 1;
+    note_new_extract(h);
+    h->nout_frame_on_host = 0;
+    if (u_right) { /* the keyframe's mvuRight, where borb_stereo_match would have left it (BORB_MATCH_USE_STEREO reads it) */
+        const size_t B = (size_t)h->max_batch, K = (size_t)P.kp_total;
+        if (!h->d_st_u) {
+            CU(cudaMalloc(&h->d_st_u, B * K * 4));
+            CU(cudaMalloc(&h->d_st_z, B * K * 4));
+            CU(cudaMalloc(&h->d_st_kept, B * 4));
+            CU(cudaMallocHost(&h->h_st_u, B * K * 4));
+            CU(cudaMallocHost(&h->h_st_z, B * K * 4));
+            CU(cudaMallocHost(&h->h_st_kept, B * 4));
+        }
+        for (size_t i = 0; i < K; ++i) h->h_st_u[i] = i < (size_t)n ? u_right[i] : -1.f;
+        CU(cudaMemcpyAsync(h->d_st_u, h->h_st_u, K * 4, cudaMemcpyHostToDevice, st));
+        h->stereo_gen = h->extract_gen;
+    }
     return BORB_OK;
 }
 
@@ -1536,7 +1593,7 @@ void camera_centre(const float *Tcw /* 3 x 4 row-major */, float *Ow)
  * (+ the occupancy bytes of the local-map matcher), M1a over the whole GPU, M1b in one CTA, download the matches. */
 int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *geo, int geo_stride, const uint8_t *desc,
                 const uint8_t *qflags, const int32_t *octave, const float *angle, const uint8_t *occupied, MatchParams &mp,
-                bool use_stereo, int32_t *match, int *n_cur, int *nmatches)
+                bool use_stereo, int32_t *match, int *n_cur, int *nmatches, const float *extra = nullptr /* 4 floats per query */)
 {
     if (!cur->have_plan || cur->last_n < 1) return fail(BORB_ERR_STATE, "no finished extract call");
     if (!cur->have_cam || !cur->d_un_xy) return fail(BORB_ERR_STATE, "borb_set_camera must be on: the matcher reads mvKeysUn, mGrid and K");
@@ -1545,7 +1602,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     if (n < 0 || (n > 0 && (!geo || !desc || !qflags || !octave))) return fail(BORB_ERR_ARG, "query arrays");
     if (use_stereo && (!cur->d_st_u || cur->stereo_gen != cur->extract_gen))
         return fail(BORB_ERR_STATE, "no stereo result for this handle's last extract call (run borb_stereo_match after it)");
-    for (int i = 0; i < n && mode != 4; ++i) /* mode 4 predicts the level; its octave column carries mfMinDistance */
+    for (int i = 0; i < n && mode < 4; ++i) /* modes >= 4 predict the level; their octave column carries mfMinDistance */
         if ((qflags[i] & 1) && (octave[i] < 0 || octave[i] >= cur->nlevels))
             return fail(BORB_ERR_ARG, "octave %d of query %d", octave[i], i);
     CU(cudaSetDevice(cur->device));
@@ -1574,8 +1631,8 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         cur->d_mt_m12 = cur->h_mt_m12 = nullptr;
         cur->d_mt_last = cur->h_mt_last = nullptr; cur->d_mt_choice = nullptr; cur->mt_cap = 0;
         cur->d_mt_cache = nullptr; cur->d_mt_more = nullptr;
-        CU(cudaMalloc(&cur->d_mt_last, cap * 57));
-        CU(cudaMallocHost(&cur->h_mt_last, cap * 57));
+        CU(cudaMalloc(&cur->d_mt_last, cap * 73));
+        CU(cudaMallocHost(&cur->h_mt_last, cap * 73));
         CU(cudaMalloc(&cur->d_mt_choice, cap * 8));
         CU(cudaMalloc(&cur->d_mt_m12, cap * 4));
         CU(cudaMalloc(&cur->d_mt_ent, 2 * cap * 4));
@@ -1597,11 +1654,13 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         if (angle) std::memcpy(hp + 48 * c, angle, un * 4);
         std::memcpy(hp + 52 * c, octave, un * 4);
         std::memcpy(hp + 56 * c, qflags, un);
+        if (extra) std::memcpy(hp + 57 * c, extra, un * 16);
     }
     cudaStream_t st = cur->stream;
     /* one contiguous upload when the arrays are nearly full, else one per array */
-    if (un * 2 >= c) CU(cudaMemcpyAsync(dp, hp, 57 * c, cudaMemcpyHostToDevice, st));
+    if (un * 2 >= c) CU(cudaMemcpyAsync(dp, hp, (extra ? 73 : 57) * c, cudaMemcpyHostToDevice, st));
     else if (n) {
+        if (extra) CU(cudaMemcpyAsync(dp + 57 * c, hp + 57 * c, un * 16, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(dp, hp, un * 32, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(dp + 32 * c, hp + 32 * c, un * 16, cudaMemcpyHostToDevice, st));
         if (angle) CU(cudaMemcpyAsync(dp + 48 * c, hp + 48 * c, un * 4, cudaMemcpyHostToDevice, st));
@@ -1631,6 +1690,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     const int *l_oct = reinterpret_cast<const int *>(dp + 52 * c);
     const uint4 *l_desc = reinterpret_cast<const uint4 *>(dp);
     const uint8_t *l_flags = dp + 56 * c;
+    const float4 *l_extra = reinterpret_cast<const float4 *>(dp + 57 * c);
     const int *cs = cur->d_cell_start + (size_t)frame * (FR_CELLS + 1), *ci = cur->d_cell_idx + fo;
     const int cand_grid = (n + MT_CAND_NT / 32 - 1) / (MT_CAND_NT / 32);
     const size_t tk_smem = 2 * K * 4 <= 96 * 1024 ? 2 * K * 4 : 0; /* takers in shared memory when they fit */
@@ -1651,6 +1711,29 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
                                                    cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,                 \
                                                    cur->d_mt_match + K, tk_smem ? 1 : 0);                                    \
     } while (0)
+    if (mode == 5) {
+        /* the matchers whose queries are independent (Fuse: the choice per map point): M1a alone; the best cached entry of a
+         * query IS its choice -- first smallest distance in GetFeaturesInArea order */
+        if (n > 0)
+            k_match_candidates<5><<<cand_grid, MT_CAND_NT, 0, st>>>(
+                mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4,
+                d_ur, nullptr, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more, l_extra);
+        CU(cudaGetLastError());
+        CU(cudaMemcpy2DAsync(cur->h_mt_m12, 4, cur->d_mt_cache, MT_K * 4, 4, std::max<size_t>(un, 1), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        int nm = 0;
+        for (size_t i = 0; i < un; ++i) {
+            const uint32_t key = (uint32_t)cur->h_mt_m12[i];
+            const bool ok = key != MT_NOKEY && (int)(key >> 16) <= mp.orb_dist;
+            match[i] = ok ? (int32_t)(key & 0xffffu) : -1;
+            nm += ok;
+        }
+        if (nmatches) *nmatches = nm;
+        if (n_cur) *n_cur = n;
+        cur->mt_rounds = 1;
+        cur->mt_rescans = 0;
+        return BORB_OK;
+    }
     if (mode == 1) MATCH_LAUNCH(1);
     else if (mode == 2) MATCH_LAUNCH(2);
     else if (mode == 4) MATCH_LAUNCH(4);
@@ -1787,6 +1870,40 @@ int borb_search_by_projection_keyframe(borb_extractor *cur, int frame, const bor
     }
     return run_matcher(cur, frame, 4, kf->n, geo.data(), 4, kf->desc, qf.data(), mind.data(), kf->angle,
                        occupied ? occ.data() : nullptr, mp, false, match, n_cur, nmatches);
+}
+
+/* ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, const float th) (src/ORBmatcher.cc:968-1131): the
+ * keypoint of pKF each map point is to be fused into.  pKF = frame `frame` of kf's last call -- a keyframe put there by
+ * borb_load_frame.  One kernel (M1a in MODE 5, k_match.cuh); the queries are independent. */
+int borb_fuse_search(borb_extractor *kf, int frame, const borb_fuse_points *mps, const float *Tcw, const float *Ow, float bf,
+                     float th, unsigned flags, int32_t *best_idx, int *nfused)
+{
+    if (!kf || !mps || !Tcw || !Ow || !best_idx) return fail(BORB_ERR_ARG, "null argument");
+    if (mps->n > 0 && (!mps->xyz || !mps->desc || !mps->flags || !mps->dist || !mps->normal)) return fail(BORB_ERR_ARG, "map point arrays");
+    MatchParams mp;
+    std::memset(&mp, 0, sizeof mp);
+    std::memcpy(mp.Tc, Tcw, 48);
+    std::memcpy(mp.Ow, Ow, 12);
+    mp.th = th;
+    mp.mbf = bf;
+    mp.orb_dist = MT_TH_LOW;
+    mp.nlevels = kf->nlevels;
+    mp.log_scale = orb_logf_exact((float)kf->scale_factor);
+    for (int l = 0; l < BORB_MAXL; ++l) mp.inv_sigma2[l] = l < kf->nlevels ? kf->inv_sigma2[l] : 0.f;
+    const size_t n = (size_t)std::max(mps->n, 0);
+    std::vector<float> geo(4 * n), extra(4 * n);
+    std::vector<int32_t> mind(n);
+    std::vector<uint8_t> qf(n);
+    for (size_t i = 0; i < n; ++i) {
+        geo[4 * i] = mps->xyz[3 * i]; geo[4 * i + 1] = mps->xyz[3 * i + 1]; geo[4 * i + 2] = mps->xyz[3 * i + 2];
+        geo[4 * i + 3] = mps->dist[2 * i + 1];
+        std::memcpy(&mind[i], &mps->dist[2 * i], 4);
+        extra[4 * i] = mps->normal[3 * i]; extra[4 * i + 1] = mps->normal[3 * i + 1]; extra[4 * i + 2] = mps->normal[3 * i + 2];
+        extra[4 * i + 3] = 0.f;
+        qf[i] = ((mps->flags[i] & 1) && !(mps->flags[i] & 6)) ? 1 : 0;
+    }
+    return run_matcher(kf, frame, 5, mps->n, geo.data(), 4, mps->desc, qf.data(), mind.data(), nullptr, nullptr, mp,
+                       (flags & BORB_MATCH_USE_STEREO) != 0, best_idx, nullptr, nfused, extra.data());
 }
 
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:487-632) */

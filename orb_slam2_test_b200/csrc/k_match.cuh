@@ -45,6 +45,7 @@
 #define MT_ROWS 48
 #define MT_HISTO 30
 #define MT_TH_HIGH 100
+#define MT_TH_LOW 50
 
 struct MatchParams {
     float Tc[12], Tl[12]; /* Tcw of the current and the last frame, 3 x 4 row-major */
@@ -57,6 +58,7 @@ struct MatchParams {
     /* MODE 4 (relocalisation matcher): camera centre Ow = -Rcw.t() * tcw, CurrentFrame.mfLogScaleFactor, mnScaleLevels, ORBdist */
     float Ow[3], log_scale;
     int nlevels, orb_dist;
+    float inv_sigma2[BORB_MAXL]; /* MODE 5: pKF->mvInvLevelSigma2 for Fuse's chi-square tests */
 };
 
 __device__ __forceinline__ float mt_dot3(const float *row, const float *x)
@@ -103,6 +105,9 @@ struct MtQuery { /* what the candidate scan of one query needs (:1537-1572) */
     bool ok, check_levels;
     float u, v, radius, ur;
     int min_level, max_level, cx0, cx1, cy0, cy1;
+    float inv_s2[2]; /* kind 1: mvInvLevelSigma2 of the two admitted levels */
+    int kind; /* the per-candidate test beside level and window: 0 = mvuRight within the radius (:1587-1595, :96-102),
+                 1 = Fuse's chi-square test on the pixel error (:1056-1083), 2 = none */
 };
 
 /* MODE 1: the frame-to-frame matcher (geo = world position; src/ORBmatcher.cc:1537-1572).
@@ -120,10 +125,15 @@ struct MtQuery { /* what the candidate scan of one query needs (:1537-1572) */
  *         glibc's (orb_logf.cuh); window th * scale[level], octaves level-1 .. level+1. */
 template <int MODE>
 __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *__restrict__ l_geo, int oct, int i,
-                                            float min_x, float max_x, float min_y, float max_y, float winv, float hinv)
+                                            float min_x, float max_x, float min_y, float max_y, float winv, float hinv,
+                                            const float4 *__restrict__ l_extra = nullptr)
 {
     MtQuery Q;
+    Q.kind = MODE >= 5 ? 2 : 0;
     const float4 g = reinterpret_cast<const float4 *>(l_geo)[i];
+    if (MODE >= 5) { /* a KeyFrame's bounds are its Frame's float bounds truncated to int (include/KeyFrame.h: const int mnMinX ...) */
+        min_x = truncf(min_x); max_x = truncf(max_x); min_y = truncf(min_y); max_y = truncf(max_y);
+    }
     if (MODE == 1) {
         const float X[3] = {g.x, g.y, g.z};
         const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7], zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
@@ -160,6 +170,40 @@ __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *
         Q.min_level = lvl - 1;
         Q.max_level = lvl + 1;
         Q.ur = 0.f;
+    } else if (MODE == 5) {
+        /* ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:968-1131): geo = world position and mfMaxDistance, `oct`
+         * = the bit pattern of mfMinDistance, extra = GetNormal().  Float forms as the reference object has them
+         * (oracle/match_oracle.cpp: mo_fuse). */
+        const float X[3] = {g.x, g.y, g.z};
+        const float xc = mt_dot3(mp.Tc, X) + mp.Tc[3], yc = mt_dot3(mp.Tc + 4, X) + mp.Tc[7], zc = mt_dot3(mp.Tc + 8, X) + mp.Tc[11];
+        const float invz = 1.0f / zc;
+        const float x = xc * invz, y = yc * invz;
+        Q.u = fmaf(x, mp.fx, mp.cx);
+        Q.v = fmaf(y, mp.fy, mp.cy);
+        Q.ok = !(zc < 0.0f) && Q.u >= min_x && Q.u < max_x && Q.v >= min_y && Q.v < max_y; /* KeyFrame::IsInImage */
+        Q.ur = fmaf(-mp.mbf, invz, Q.u);
+        const float4 nv = l_extra[i];
+        const float N[3] = {nv.x, nv.y, nv.z};
+        double s2 = 0.0, dotn = 0.0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float po = X[k] - mp.Ow[k];
+            s2 = __dadd_rn(s2, __dmul_rn((double)po, (double)po));
+            dotn = __dadd_rn(dotn, __dmul_rn((double)po, (double)N[k]));
+        }
+        const float dist3D = (float)__dsqrt_rn(s2);
+        Q.ok = Q.ok && !(dist3D < 0.8f * __int_as_float(oct) || dist3D > 1.2f * g.w);
+        Q.ok = Q.ok && !(dotn < __dmul_rn(0.5, (double)dist3D));
+        const float ratio = g.w / dist3D;
+        int lvl = orb_cvtt_x86(ceilf(orb_logf_exact(ratio) / mp.log_scale));
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= mp.nlevels) lvl = mp.nlevels - 1;
+        Q.radius = mp.th * mp.scale[lvl];
+        Q.min_level = lvl - 1;
+        Q.max_level = lvl;
+        Q.kind = 1;
+        Q.inv_s2[0] = lvl > 0 ? mp.inv_sigma2[lvl - 1] : 0.f;
+        Q.inv_s2[1] = mp.inv_sigma2[lvl];
     } else if (MODE == 3) { /* SearchForInitialization: window of windowSize (= mp.th) around vbPrevMatched, level 0 only (:510) */
         Q.radius = mp.th;
         Q.u = g.x;
@@ -201,9 +245,20 @@ __device__ __forceinline__ int mt_candidate(const MtQuery &Q, int i2, const Borb
     if (Q.check_levels && (o2 < Q.min_level || (Q.max_level >= 0 && o2 > Q.max_level))) return -1;
     const float2 p = un_xy[i2];
     if (!(fabsf(p.x - Q.u) < Q.radius && fabsf(p.y - Q.v) < Q.radius)) return -1;
-    if (u_right) {
-        const float ur2 = u_right[i2];
-        if (ur2 > 0 && fabsf(Q.ur - ur2) > Q.radius) return -1;
+    if (Q.kind == 0) {
+        if (u_right) {
+            const float ur2 = u_right[i2];
+            if (ur2 > 0 && fabsf(Q.ur - ur2) > Q.radius) return -1;
+        }
+    } else if (Q.kind == 1) { /* Fuse: chi-square test of the pixel error, 3 dof for a stereo keypoint (:1056-1083) */
+        const float ex = Q.u - p.x, ey = Q.v - p.y;
+        const float t = fmaf(ex, ex, ey * ey);
+        const float kr = u_right ? u_right[i2] : -1.f;
+        const float inv = Q.inv_s2[o2 - Q.min_level];
+        if (kr >= 0.f) {
+            const float er = Q.ur - kr;
+            if ((double)(fmaf(er, er, t) * inv) > 7.8) return -1;
+        } else if ((double)(inv * t) > 5.99) return -1;
     }
     return mt_hamming(d0, d1, reinterpret_cast<const uint4 *>(desc) + 2 * i2);
 }
@@ -219,7 +274,7 @@ k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__re
                    const float *__restrict__ bounds, const float *__restrict__ u_right,
                    const uint8_t *__restrict__ occupied, const float *__restrict__ l_geo, const int *__restrict__ l_octave,
                    const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
-                   uint32_t *__restrict__ cache, uint8_t *__restrict__ more)
+                   uint32_t *__restrict__ cache, uint8_t *__restrict__ more, const float4 *__restrict__ l_extra = nullptr)
 {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * (MT_CAND_NT / 32) + (threadIdx.x >> 5);
@@ -232,7 +287,7 @@ k_match_candidates(const __grid_constant__ MatchParams mp, const BorbKpRec *__re
     if ((fl & 1u) && !(fl & 4u)) {
         const float min_x = bounds[0], max_x = bounds[1], min_y = bounds[2], max_y = bounds[3];
         const float winv = (float)MT_COLS / (max_x - min_x), hinv = (float)MT_ROWS / (max_y - min_y);
-        const MtQuery Q = mt_query<MODE>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+        const MtQuery Q = mt_query<MODE>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv, l_extra);
         if (Q.ok) {
             const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
             for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {
@@ -482,8 +537,6 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
  * one keypoint per round, so a list can have any length (on repetitive texture with a 100-px window dozens of
  * level-0 keypoints may pick the same one; the reference never fails there) and nothing can overflow.
  */
-#define MT_TH_LOW 50
-
 __device__ __forceinline__ bool mt_init_closed(const uint32_t *__restrict__ node, const int *__restrict__ head, int c, int i, int d)
 {
     for (int k = head[c]; k >= 0;) {

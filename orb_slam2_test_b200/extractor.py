@@ -60,6 +60,8 @@ SYMBOLS += ["borb_search_by_projection_keyframe", "borb_debug_logf", "borb_debug
 SYMBOLS += ["borb_voc_search_by_bow"]
 # ORBmatcher::SearchForTriangulation
 SYMBOLS += ["borb_voc_search_for_triangulation"]
+# keyframes on the device and the matchers that take one: ORBmatcher::Fuse(pKF, vpMapPoints, th)
+SYMBOLS += ["borb_load_frame", "borb_fuse_search"]
 
 
 class BorbError(RuntimeError):
@@ -138,6 +140,8 @@ def load_library() -> C.CDLL:
                                                        C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.borb_voc_search_by_bow.argtypes = [_vp, _vp, _vp, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_voc_search_for_triangulation.argtypes = [_vp, _vp, _vp, _vp, C.c_uint, _vp, C.POINTER(C.c_int)]
+    lib.borb_load_frame.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int]
+    lib.borb_fuse_search.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_debug_logf.argtypes = [_vp, _vp, C.c_int]
     lib.borb_debug_logf.restype = None
     lib.borb_debug_logf_device.argtypes = [_vp, _vp, C.c_int]
@@ -194,6 +198,10 @@ class _MapPoints(C.Structure):  # == borb_map_points
 class _LastFrame(C.Structure):  # == borb_last_frame
     _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("octave", _vp), ("angle", _vp),
                 ("Tcw", _vp)]
+
+
+class _FusePoints(C.Structure):  # == borb_fuse_points
+    _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("dist", _vp), ("normal", _vp)]
 
 
 class _KeyFramePoints(C.Structure):  # == borb_keyframe_points
@@ -600,6 +608,32 @@ class ORBextractor:
                                                              th, nnratio, 4 if use_stereo else 0, out.ctypes.data,
                                                              C.byref(n), C.byref(nm)))
         return out[:n.value].copy(), nm.value
+
+    def load_frame(self, kps: np.ndarray, desc: np.ndarray, cols: int, rows: int, u_right=None) -> None:
+        """Put a frame extracted earlier (a KeyFrame's mvKeys + mDescriptors, optionally its mvuRight) back into the handle as
+        if an extract call had produced it: mvKeysUn, mGrid and the bounds are rebuilt on the device (set_camera first)."""
+        k = np.ascontiguousarray(kps, KP_DTYPE)
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        ur = np.ascontiguousarray(u_right, np.float32) if u_right is not None else None
+        _check(self._lib, self._lib.borb_load_frame(self._h, k.ctypes.data, d.ctypes.data, ur.ctypes.data if ur is not None else None,
+                                                    len(k), cols, rows))
+        self._n = 1
+
+    def fuse_search(self, mps: dict, Tcw, Ow, bf: float, th: float = 3.0, frame: int = 0, use_stereo: bool = False):
+        """The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:968-1131) with frame `frame` of this handle
+        (a keyframe put there by load_frame) as pKF.  mps: flags [n] u8 (bit 0 map point, bit 1 bad, bit 2 already in the
+        keyframe), xyz [n,3], desc [n,32], dist [n,2] (mfMinDistance, mfMaxDistance), normal [n,3].
+        -> (best [n] i32: keypoint of pKF per map point or -1, nFused)."""
+        keep = [np.ascontiguousarray(mps["xyz"], np.float32), np.ascontiguousarray(mps["desc"], np.uint8),
+                np.ascontiguousarray(mps["flags"], np.uint8), np.ascontiguousarray(mps["dist"], np.float32),
+                np.ascontiguousarray(mps["normal"], np.float32)]
+        rec = _FusePoints(len(keep[2]), *[a.ctypes.data for a in keep])
+        T, O = np.ascontiguousarray(Tcw, np.float32), np.ascontiguousarray(Ow, np.float32)
+        out = np.full(max(rec.n, 1), -1, np.int32)
+        nf = C.c_int()
+        _check(self._lib, self._lib.borb_fuse_search(self._h, frame, C.addressof(rec), T.ctypes.data, O.ctypes.data, bf, th,
+                                                     4 if use_stereo else 0, out.ctypes.data, C.byref(nf)))
+        return out[:rec.n].copy(), nf.value
 
     def search_by_projection_keyframe(self, kf: dict, Tcw_cur, occupied=None, th: float = 10.0, orb_dist: int = 100,
                                       frame: int = 0, check_orientation: bool = True):

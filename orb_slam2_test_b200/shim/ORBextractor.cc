@@ -231,6 +231,38 @@ int ORBextractor::SearchByProjectionKF(const cv::Mat &TcwCur, int nKF, const flo
     return nmatches;
 }
 
+void ORBextractor::LoadKeyFrame(const std::vector<cv::KeyPoint> &keys, const cv::Mat &descriptors, const std::vector<float> &uRight,
+                                int cols, int rows)
+{
+    const int n = (int)keys.size();
+    assert(descriptors.rows == n && (n == 0 || descriptors.cols == 32) && (uRight.empty() || (int)uRight.size() == n));
+    static_assert(sizeof(cv::KeyPoint) == sizeof(borb_keypoint), "cv::KeyPoint is the 28-byte record of include/borb.h");
+    std::vector<unsigned char> desc((size_t)32 * n);
+    for (int i = 0; i < n; ++i) memcpy(&desc[(size_t)32 * i], descriptors.ptr(i), 32);
+    check(borb_load_frame(handle, reinterpret_cast<const borb_keypoint *>(keys.data()), desc.data(),
+                          uRight.empty() ? NULL : uRight.data(), n, cols, rows),
+          "load keyframe");
+}
+
+int ORBextractor::FuseSearch(const cv::Mat &Tcw, const cv::Mat &Ow, float bf, int nPoints, const float *worldPos,
+                             const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
+                             const float *normals, float th, bool useStereo, std::vector<int> &vnBestIdx)
+{
+    assert(Tcw.rows == 4 && Tcw.cols == 4 && Tcw.type() == CV_32F && Ow.rows == 3 && Ow.cols == 1 && Ow.type() == CV_32F);
+    float tc[12], ow[3];
+    for (int r = 0; r < 3; ++r) {
+        ow[r] = Ow.at<float>(r, 0);
+        for (int c = 0; c < 4; ++c) tc[4 * r + c] = Tcw.at<float>(r, c);
+    }
+    borb_fuse_points mps;
+    mps.n = nPoints; mps.xyz = worldPos; mps.desc = mpDescriptors; mps.flags = flags; mps.dist = minMaxDistance; mps.normal = normals;
+    vnBestIdx.assign((size_t)std::max(nPoints, 0), -1);
+    int nfused = 0;
+    check(borb_fuse_search(handle, 0, &mps, tc, ow, bf, th, useStereo ? BORB_MATCH_USE_STEREO : 0u, vnBestIdx.data(), &nfused),
+          "fuse search");
+    return nfused;
+}
+
 int ORBextractor::SearchForInitialization(const std::vector<cv::KeyPoint> &F1KeysUn, const cv::Mat &F1Descriptors,
                                           std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12,
                                           int windowSize, float nnRatio, bool checkOrientation)

@@ -182,6 +182,20 @@ public:
                              const unsigned char *flags, const float *minMaxDistance, const float *angle,
                              const unsigned char *occupied, float th, int ORBdist, bool checkOrientation,
                              std::vector<int> &vnMatches);
+    // A KeyFrame on the device: the keyframe's mvKeys, mDescriptors (and mvuRight, empty = monocular) put back into this
+    // instance as if operator() had just produced them; mvKeysUn, mGrid and the bounds are rebuilt on the device (SetCamera
+    // on).  The keyframe matchers below then take *this as that keyframe.  cols, rows = the image size.
+    void LoadKeyFrame(const std::vector<cv::KeyPoint> &keys, const cv::Mat &descriptors, const std::vector<float> &uRight,
+                      int cols, int rows);
+    // The search inside ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, const float th) (reference
+    // src/ORBmatcher.cc:968-1131, LocalMapping::SearchInNeighbors), *this = pKF after LoadKeyFrame.  Entry i =
+    // vpMapPoints[i]: flags bit 0 = non-NULL, bit 1 = isBad(), bit 2 = IsInKeyFrame(pKF); GetWorldPos(), GetDescriptor(),
+    // minMaxDistance[2i] = mfMinDistance, [2i + 1] = mfMaxDistance, normals[3i..] = GetNormal().  Tcw = pKF->GetPose() (4x4
+    // CV_32F), Ow = pKF->GetCameraCenter() (3x1).  vnBestIdx[i] = the keypoint of pKF the reference hands to
+    // pKF->GetMapPoint(bestIdx) (:1105) or -1; returns nFused.  The caller then runs the reference's own :1103-1127 per i.
+    int FuseSearch(const cv::Mat &Tcw, const cv::Mat &Ow, float bf, int nPoints, const float *worldPos,
+                   const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
+                   const float *normals, float th, bool useStereo, std::vector<int> &vnBestIdx);
     // ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (reference
     // src/ORBmatcher.cc:487-632, Tracking::MonocularInitialization) on the device, *this = F2's extractor after its
     // operator() call (SetCamera on).  F1 arrives as its mvKeysUn (octave, angle) and descriptors (CV_8U, n x 32).

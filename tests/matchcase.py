@@ -202,3 +202,39 @@ def make_reloc_case(seed=0, copies=1, found_rate=0.2, bad_rate=0.05, occupied_ra
     libm.logf.argtypes = [ctypes.c_float]
     log_scale = libm.logf(float(np.float32(1.2)))
     return cur, cam, bounds, scale, float(log_scale), kf, occupied
+
+
+def host_logf(x: float) -> float:
+    import ctypes
+    import ctypes.util
+    libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
+    libm.logf.restype = ctypes.c_float
+    libm.logf.argtypes = [ctypes.c_float]
+    return float(libm.logf(float(np.float32(x))))
+
+
+def make_fuse_case(seed=0, copies=1, bad_rate=0.05, in_kf_rate=0.1, dist_jitter=0.25, normal_tilt=0.6, **kw):
+    """Scenario for ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:968-1131): the keyframe is the current frame of
+    make_case (stereo keypoints where the scenario is stereo), the map points are the previous frame's (a neighbour
+    keyframe's), with scale-invariance distances as in make_reloc_case and viewing normals = the direction they were seen
+    from, tilted at random so that some fail the 60 degree test.
+    -> (kf, cam, bounds, scale, inv_sigma2, log_scale, mps)"""
+    cur, last, cam, bounds, scale = make_case(seed=seed, copies=copies, **kw)
+    rng = np.random.default_rng(11000 + seed)
+    n = len(last["mp_flags"])
+    T = last["Tcw"].astype(np.float64)
+    Ow = -T[:, :3].T @ T[:, 3]
+    PO = last["mp_xyz"].astype(np.float64) - Ow
+    d = np.linalg.norm(PO, axis=1)
+    sc = np.asarray(scale, np.float64)
+    max_d = d * sc[last["kps"]["octave"]] * rng.uniform(1 - dist_jitter, 1 + dist_jitter, n)
+    nrm = PO / np.maximum(d, 1e-9)[:, None] + rng.normal(0, normal_tilt, (n, 3))
+    nrm /= np.maximum(np.linalg.norm(nrm, axis=1), 1e-9)[:, None]
+    flags = ((last["mp_flags"] & 1) | ((rng.random(n) < bad_rate).astype(np.uint8) << 1)
+             | ((rng.random(n) < in_kf_rate).astype(np.uint8) << 2)).astype(np.uint8)
+    mps = {"flags": flags, "xyz": last["mp_xyz"], "desc": last["mp_desc"],
+           "dist": np.stack([max_d / sc[-1], max_d], 1).astype(np.float32), "normal": nrm.astype(np.float32)}
+    sc32 = np.asarray(scale, np.float32)
+    sigma2 = (sc32 * sc32).astype(np.float32)            # mvLevelSigma2[i] = mvScaleFactor[i] * mvScaleFactor[i]
+    inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)   # mvInvLevelSigma2[i] = 1.0f / mvLevelSigma2[i]
+    return cur, cam, bounds, scale, inv_sigma2, host_logf(1.2), mps

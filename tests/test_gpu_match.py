@@ -297,3 +297,66 @@ def test_relocalisation_matcher_empty_and_argument_errors(oracle_built):
     no_cam(synth.make_frame(synth.KITTI_SHAPE, seed=1, frame=1, eye=0))
     with pytest.raises(BorbError):
         no_cam.search_by_projection_keyframe(kf, cur["Tcw"], None)
+
+
+# ---- keyframes on the device (borb_load_frame) and ORBmatcher::Fuse(pKF, vpMapPoints, th), src/ORBmatcher.cc:968-1131 ----
+
+def test_a_loaded_keyframe_is_the_extracted_frame(oracle_built):
+    """borb_load_frame: the records and descriptors of a frame extracted earlier, put back into a handle, give the same
+    mvKeysUn / mGrid / bounds and the same matcher results as the frame the extract call left there"""
+    from orb_slam2_test_b200 import ORBextractor
+    cur, last, cam, bounds, scale = matchcase.make_case(seed=6, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
+                                                        bf=40.0, stereo=False, nf=1000)
+    ext, _ = _gpu_frame(synth.TUM_SHAPE, 6, 1, matchcase.TUM1_K, matchcase.TUM1_D, False, 1000, 0.0, 0.0)
+    kps, desc = ext.result(0)
+    want = ext.search_by_projection(_last_for_abi(last), cur["Tcw"], 40.0, float(cam[5]), 15.0, mono=True)
+    grid = ext.frame_grid(0)
+    kf = ORBextractor(1000, 1.2, 8, 20, 7)
+    kf.set_camera(matchcase.TUM1_K, matchcase.TUM1_D)
+    kf.load_frame(kps, desc, 640, 480)
+    got = kf.search_by_projection(_last_for_abi(last), cur["Tcw"], 40.0, float(cam[5]), 15.0, mono=True)
+    assert np.array_equal(got[0], want[0]) and got[1] == want[1] and got[1] > 200
+    kf.fetch()
+    k2, d2 = kf.result(0)
+    assert k2.tobytes() == kps.tobytes() and np.array_equal(d2, desc)
+    g2 = kf.frame_grid(0)
+    for a, b in zip(grid, g2):
+        assert np.asarray(a).tobytes() == np.asarray(b).tobytes()
+    ext(synth.make_frame(synth.TUM_SHAPE, seed=6, frame=3))  # the handle takes extract calls again afterwards, and loads again
+    kf.load_frame(kps[:10], desc[:10], 640, 480)
+    kf.fetch()
+    assert kf.count(0) == 10
+
+
+def _check_fuse(tag, oracle, ths=(3.0, 6.0), **kw):
+    from orb_slam2_test_b200 import ORBextractor
+    kf, cam, bounds, scale, inv_sigma2, log_scale, mps = matchcase.make_fuse_case(**kw)
+    stereo = kw.get("stereo", True)
+    h = ORBextractor(kw.get("nf", 2000), 1.2, 8, 20, 7)
+    h.set_camera(kw.get("K", matchcase.KITTI_K), kw.get("dist", (0.0, 0.0, 0.0, 0.0)))
+    shape = kw.get("shape", synth.KITTI_SHAPE)
+    h.load_frame(kf["kps"], kf["desc"], shape[1], shape[0], kf["u_right"] if stereo else None)
+    Ow = oracle.camera_centre(kf["Tcw"])
+    total = 0
+    for th in ths:
+        want, wnf = oracle.fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
+        got, nf = h.fuse_search(mps, kf["Tcw"], Ow, float(cam[4]), th, use_stereo=stereo)
+        bad = np.nonzero(got != want)[0]
+        assert bad.size == 0 and nf == wnf, f"{tag} th={th}: {bad.size} map points differ, e.g. {bad[:5]}: {got[bad[:5]]} vs {want[bad[:5]]}"
+        total += nf
+    return total
+
+
+@pytest.mark.parametrize("seed,dz", [(1, 0.0), (2, 0.3), (3, -0.3)])
+def test_fuse_search_kitti_stereo_keyframe(seed, dz, oracle_built):
+    assert _check_fuse(f"fuse kitti {seed} dz {dz}", oracle_built, seed=seed, dz=dz) > 400
+
+
+def test_fuse_search_crowded(oracle_built):
+    assert _check_fuse("fuse crowded", oracle_built, seed=4, copies=3) > 2000
+
+
+def test_fuse_search_monocular_distorted_keyframe(oracle_built):
+    """the keyframe's bounds are the frame's float bounds truncated to int"""
+    assert _check_fuse("fuse tum", oracle_built, seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
+                       bf=40.0, stereo=False, nf=1000, dist_jitter=0.4) > 300

@@ -138,3 +138,34 @@ def test_reloc_pose_looking_away(oracle_built, ref):
     want, wnm = ref.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occupied, 10.0, 100, True)
     got, nm = oracle_built.search_by_projection_kf(cur, cam, bounds, scale, log_scale, kf, occupied, 10.0, 100, True)
     assert nm == wnm and np.array_equal(got, want)
+
+
+# ---- ORBmatcher::Fuse(pKF, vpMapPoints, th), src/ORBmatcher.cc:968-1131 (LocalMapping::SearchInNeighbors) ----
+
+def _compare_fuse(py, ref, tag, ths=(3.0, 6.0), **kw):
+    kf, cam, bounds, scale, inv_sigma2, log_scale, mps = matchcase.make_fuse_case(**kw)
+    total = 0
+    for th in ths:
+        want, wnf = ref.fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
+        got, nf = py.fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
+        assert np.array_equal(got, want), f"{tag} th={th}: {(got != want).sum()} map points differ"
+        assert nf == wnf == int((got >= 0).sum())
+        assert not (got[(mps["flags"] & 6) != 0] >= 0).any()
+        total += nf
+    return total
+
+
+@pytest.mark.parametrize("seed,dz", [(1, 0.0), (2, 0.3), (3, -0.3)])
+def test_fuse_kitti_stereo_keyframe(seed, dz, oracle_built, ref):
+    """stereo keypoints take the 3-dof chi-square test (7.8), the others the 2-dof one (5.99)"""
+    assert _compare_fuse(oracle_built, ref, f"fuse kitti {seed} dz {dz}", seed=seed, dz=dz) > 400
+
+
+def test_fuse_crowded(oracle_built, ref):
+    _compare_fuse(oracle_built, ref, "fuse crowded", seed=4, copies=3)
+
+
+def test_fuse_monocular_distorted_keyframe(oracle_built, ref):
+    """a distorted camera: the keyframe's bounds are the Frame's float bounds truncated to int"""
+    assert _compare_fuse(oracle_built, ref, "fuse tum", seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
+                         bf=40.0, stereo=False, nf=1000, dist_jitter=0.4) > 150
