@@ -294,15 +294,18 @@ inline Mat operator/(const Mat &a, float s) { return mat_lin_(a, 1.f / s, nullpt
  * the plain small product above -- takes OpenCV's generic path: the sum over k in DOUBLE, left to right, times alpha,
  * one rounding to float (cv2 4.13: tests/test_oracle_match.py::test_transposed_gemm_form_is_cv2s).  This is
  * Ow = -Rcw.t() * tcw of src/Frame.cc:334 and src/ORBmatcher.cc:366, 1146, 1516, 1676. */
+CVCOMPAT_NOFMA inline float mul_nofma_(float a, float b) { return a * b; }
 class MatT {
 public:
     MatT(const Mat &a, double alpha) : a_(a), alpha_(alpha) {}
     operator Mat() const
     {
-        if (alpha_ != 1.0) std::abort(); /* a scaled transpose on its own (src/ORBmatcher.cc:1280): not pinned, nobody runs it here */
+        /* MatOp_T::assign (OpenCV modules/core/src/matop.cpp): cv::transpose, then convertTo(m, -1, alpha) when alpha != 1,
+         * which for CV_32F is a float multiply by (float)alpha (src/ORBmatcher.cc:1280: (1.0 / s12) * R12.t()) */
         Mat m(a_.cols, a_.rows, CV_32F);
+        const float fa = (float)alpha_;
         for (int y = 0; y < a_.rows; ++y)
-            for (int x = 0; x < a_.cols; ++x) m.at<float>(x, y) = a_.at<float>(y, x);
+            for (int x = 0; x < a_.cols; ++x) m.at<float>(x, y) = alpha_ != 1.0 ? mul_nofma_(a_.at<float>(y, x), fa) : a_.at<float>(y, x);
         return m;
     }
     Mat a_;

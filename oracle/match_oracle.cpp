@@ -573,6 +573,223 @@ int mo_fuse(const mo_frame *kf, const float *cam, const float *bounds, const flo
     return nfused;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * The keyframe matchers that project points with a given transform and take, per point, the first smallest Hamming
+ * distance among the keypoints of the predicted level and the one below inside a window of th * scale[level]:
+ *   ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)                 src/ORBmatcher.cc:1133-1260
+ *   ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)        :353-485
+ *   ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th)     :1262-1501  (both directions)
+ * Shared float forms (the reference object): p3Dc = R * p3Dw + t (small float product; SearchBySim3 applies a second one,
+ * p3Dc2 = sR21 * p3Dc1 + t21); skipped when z < 0; invz = 1.0f / z; x = xc * invz; u = fmaf(x, fx, cx); KeyFrame::IsInImage
+ * on the int bounds; dist3D = (float)cv::norm(p3Dw - Ow) -- or, SearchBySim3, of the camera-frame point -- in double;
+ * 0.8f * mfMinDistance <= dist3D <= 1.2f * mfMaxDistance; the two Scw functions also PO.dot(Pn) < 0.5 * dist3D in double;
+ * MapPoint::PredictScale; radius = th * mvScaleFactors[level].
+ * T1 / T2: 3 x 4 row-major [R | t]; T2 = NULL for one step; Ow = NULL: dist3D of the camera-frame point; normal = NULL: no
+ * viewing-angle test.  A point is a query when bit 0 of its flag is set and bits 1, 2 are clear.
+ * out_best[i] = keypoint or -1 (distance <= max_dist).  Returns the number chosen.
+ */
+int mo_project_search(const mo_frame *kf, const float *cam, const float *bounds, const float *scale, int nlevels, float log_scale,
+                      const float *T1, const float *T2, const float *Ow, int n, const uint8_t *flags, const float *xyz,
+                      const uint8_t *desc, const float *dist, const float *normal, float th, int max_dist, int32_t *out_best)
+{
+    const float fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3];
+    const int min_x = (int)bounds[0], max_x = (int)bounds[1], min_y = (int)bounds[2], max_y = (int)bounds[3];
+    const float winv = (float)MO_COLS / (bounds[1] - bounds[0]), hinv = (float)MO_ROWS / (bounds[3] - bounds[2]);
+    const mo_kp *kk = reinterpret_cast<const mo_kp *>(kf->kps);
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + kf->grid_count[c];
+    int nfound = 0;
+    for (int i = 0; i < n; ++i) {
+        out_best[i] = -1;
+        if (!(flags[i] & 1) || (flags[i] & 6)) continue;
+        const float *X = xyz + 3 * i;
+        float P[3] = {mo_dot3(T1, 1, X) + T1[3], mo_dot3(T1 + 4, 1, X) + T1[7], mo_dot3(T1 + 8, 1, X) + T1[11]};
+        if (T2) {
+            const float Q[3] = {mo_dot3(T2, 1, P) + T2[3], mo_dot3(T2 + 4, 1, P) + T2[7], mo_dot3(T2 + 8, 1, P) + T2[11]};
+            P[0] = Q[0]; P[1] = Q[1]; P[2] = Q[2];
+        }
+        if (P[2] < 0.0f) continue;
+        const float invz = 1.0f / P[2];
+        const float x = P[0] * invz, y = P[1] * invz;
+        const float u = std::fmaf(x, fx, cx), v = std::fmaf(y, fy, cy);
+        if (!(u >= min_x && u < max_x && v >= min_y && v < max_y)) continue;
+        double s2 = 0.0, dotn = 0.0;
+        float PO[3];
+        for (int k = 0; k < 3; ++k) {
+            PO[k] = Ow ? X[k] - Ow[k] : P[k];
+            s2 += (double)PO[k] * (double)PO[k];
+        }
+        const float dist3D = (float)std::sqrt(s2);
+        if (dist3D < 0.8f * dist[2 * i] || dist3D > 1.2f * dist[2 * i + 1]) continue;
+        if (normal) {
+            for (int k = 0; k < 3; ++k) dotn += (double)PO[k] * (double)normal[3 * i + k];
+            if (dotn < 0.5 * (double)dist3D) continue;
+        }
+        const float ratio = dist[2 * i + 1] / dist3D;
+        int lvl = (int)std::ceil(std::log(ratio) / log_scale);
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= nlevels) lvl = nlevels - 1;
+        const float radius = th * scale[lvl];
+        const int cx0 = std::max(0, (int)std::floor((u - min_x - radius) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((u - min_x + radius) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((v - min_y - radius) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((v - min_y + radius) * hinv));
+        if (cy1 < 0) continue;
+        int best = INT_MAX, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int idx = kf->grid_idx[q];
+                    if (!(std::fabs(kf->un_xy[2 * idx] - u) < radius && std::fabs(kf->un_xy[2 * idx + 1] - v) < radius)) continue;
+                    const int lv = kk[idx].octave;
+                    if (lv < lvl - 1 || lv > lvl) continue;
+                    const int d = mo_hamming256(desc + (size_t)i * 32, kf->desc + (size_t)idx * 32);
+                    if (d < best) { best = d; best_idx = idx; }
+                }
+            }
+        if (best <= max_dist) { out_best[i] = best_idx; ++nfound; }
+    }
+    return nfound;
+}
+
+/* Scw -> Rcw, tcw, Ow as :360-365 / :1140-1146 compute them: scw = (float)sqrt(row0 . row0) with the dot product in double;
+ * A / scw is A * (float)(1.0 / scw) (cv::MatExpr: convertTo with alpha = 1. / s); Ow = -Rcw.t() * tcw through cv::gemm's
+ * GEMM_1_T path.  T = [Rcw | tcw], 3 x 4. */
+void mo_sim3_decompose(const float *Scw /* 4 x 4 row-major */, float *T, float *Ow)
+{
+    double d = 0.0;
+    for (int k = 0; k < 3; ++k) d += (double)Scw[k] * (double)Scw[k];
+    const float scw = (float)std::sqrt(d);
+    const float inv = 1.0f / scw;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) T[4 * r + c] = inv * Scw[4 * r + c];
+    for (int y = 0; y < 3; ++y) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += (double)T[4 * k + y] * (double)T[4 * k + 3];
+        Ow[y] = (float)(s * -1.0);
+    }
+}
+
+/* sR12 = s12 * R12; sR21 = (1.0 / s12) * R12.t(); t21 = -sR21 * t12 (:1279-1281): T12 = [sR12 | t12], T21 = [sR21 | t21] */
+void mo_sim3_relative(float s12, const float *R12, const float *t12, float *T12, float *T21)
+{
+    const float is = (float)(1.0 / (double)s12);
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) {
+            T12[4 * r + c] = s12 * R12[3 * r + c];
+            T21[4 * r + c] = R12[3 * c + r] * is;
+        }
+        T12[4 * r + 3] = t12[r];
+    }
+    for (int r = 0; r < 3; ++r) {
+        float s = 0.f;
+        for (int k = 0; k < 3; ++k) s += (-T21[4 * r + k]) * t12[k];
+        T21[4 * r + 3] = s;
+    }
+}
+
+/* ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) :353-485: sequential in the points -- a keypoint whose
+ * vpMatched entry is set (on entry, or by an earlier point of this call) is skipped (:437-438).  T = [Rcw | tcw], Ow from
+ * mo_sim3_decompose.  out_match[idx] = the point put into vpMatched[idx] by this call or -1.  Returns nmatches. */
+int mo_search_by_projection_kf_sim3(const mo_frame *kf, const float *cam, const float *bounds, const float *scale, int nlevels,
+                                    float log_scale, const float *T, const float *Ow, int n, const uint8_t *flags, const float *xyz,
+                                    const uint8_t *desc, const float *dist, const float *normal, const uint8_t *occupied, int th,
+                                    int32_t *out_match)
+{
+    const float fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3];
+    const int min_x = (int)bounds[0], max_x = (int)bounds[1], min_y = (int)bounds[2], max_y = (int)bounds[3];
+    const float winv = (float)MO_COLS / (bounds[1] - bounds[0]), hinv = (float)MO_ROWS / (bounds[3] - bounds[2]);
+    const mo_kp *kk = reinterpret_cast<const mo_kp *>(kf->kps);
+    std::vector<int> cell_start(MO_COLS * MO_ROWS + 1, 0);
+    for (int c = 0; c < MO_COLS * MO_ROWS; ++c) cell_start[c + 1] = cell_start[c] + kf->grid_count[c];
+    for (int i = 0; i < kf->n; ++i) out_match[i] = -1;
+    int nmatches = 0;
+    for (int i = 0; i < n; ++i) {
+        if (!(flags[i] & 1) || (flags[i] & 6)) continue;
+        const float *X = xyz + 3 * i;
+        const float P[3] = {mo_dot3(T, 1, X) + T[3], mo_dot3(T + 4, 1, X) + T[7], mo_dot3(T + 8, 1, X) + T[11]};
+        if (P[2] < 0.0f) continue;
+        const float invz = 1.0f / P[2];
+        const float x = P[0] * invz, y = P[1] * invz;
+        const float u = std::fmaf(x, fx, cx), v = std::fmaf(y, fy, cy);
+        if (!(u >= min_x && u < max_x && v >= min_y && v < max_y)) continue;
+        double s2 = 0.0, dotn = 0.0;
+        float PO[3];
+        for (int k = 0; k < 3; ++k) {
+            PO[k] = X[k] - Ow[k];
+            s2 += (double)PO[k] * (double)PO[k];
+        }
+        const float dist3D = (float)std::sqrt(s2);
+        if (dist3D < 0.8f * dist[2 * i] || dist3D > 1.2f * dist[2 * i + 1]) continue;
+        for (int k = 0; k < 3; ++k) dotn += (double)PO[k] * (double)normal[3 * i + k];
+        if (dotn < 0.5 * (double)dist3D) continue;
+        const float ratio = dist[2 * i + 1] / dist3D;
+        int lvl = (int)std::ceil(std::log(ratio) / log_scale);
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= nlevels) lvl = nlevels - 1;
+        const float radius = (float)th * scale[lvl];
+        const int cx0 = std::max(0, (int)std::floor((u - min_x - radius) * winv));
+        if (cx0 >= MO_COLS) continue;
+        const int cx1 = std::min((int)MO_COLS - 1, (int)std::ceil((u - min_x + radius) * winv));
+        if (cx1 < 0) continue;
+        const int cy0 = std::max(0, (int)std::floor((v - min_y - radius) * hinv));
+        if (cy0 >= MO_ROWS) continue;
+        const int cy1 = std::min((int)MO_ROWS - 1, (int)std::ceil((v - min_y + radius) * hinv));
+        if (cy1 < 0) continue;
+        int best = 256, best_idx = -1;
+        for (int ix = cx0; ix <= cx1; ++ix)
+            for (int iy = cy0; iy <= cy1; ++iy) {
+                const int c = ix * MO_ROWS + iy;
+                for (int q = cell_start[c]; q < cell_start[c + 1]; ++q) {
+                    const int idx = kf->grid_idx[q];
+                    if (!(std::fabs(kf->un_xy[2 * idx] - u) < radius && std::fabs(kf->un_xy[2 * idx + 1] - v) < radius)) continue;
+                    if ((occupied && occupied[idx]) || out_match[idx] >= 0) continue;
+                    const int lv = kk[idx].octave;
+                    if (lv < lvl - 1 || lv > lvl) continue;
+                    const int d = mo_hamming256(desc + (size_t)i * 32, kf->desc + (size_t)idx * 32);
+                    if (d < best) { best = d; best_idx = idx; }
+                }
+            }
+        if (best <= 50) { out_match[best_idx] = i; ++nmatches; }
+    }
+    return nmatches;
+}
+
+/* ORBmatcher::SearchBySim3 :1262-1501: both directions through mo_project_search, then the agreement check (:1484-1498).
+ * T1w / T2w = the keyframes' poses; flags bit 0 = the keypoint has a map point, bit 1 = bad; pre12 as the driver's. */
+int mo_search_by_sim3(const mo_frame *k1, const mo_frame *k2, const float *cam, const float *bounds, const float *scale, int nlevels,
+                      float log_scale, const uint8_t *flags1, const float *xyz1, const uint8_t *desc1, const float *dist1,
+                      const uint8_t *flags2, const float *xyz2, const uint8_t *desc2, const float *dist2, const int32_t *pre12,
+                      float s12, const float *R12, const float *t12, float th, int32_t *out12)
+{
+    float T12[12], T21[12];
+    mo_sim3_relative(s12, R12, t12, T12, T21);
+    const int n1 = k1->n, n2 = k2->n;
+    std::vector<uint8_t> f1(flags1, flags1 + n1), f2(flags2, flags2 + n2);
+    for (int i = 0; i < n1; ++i)
+        if (pre12[i] >= 0) { /* vbAlreadyMatched1 / 2 (:1291-1302) */
+            f1[i] |= 4;
+            if (pre12[i] < n2) f2[pre12[i]] |= 4;
+        }
+    std::vector<int32_t> m1((size_t)std::max(n1, 1)), m2((size_t)std::max(n2, 1));
+    mo_project_search(k2, cam, bounds, scale, nlevels, log_scale, k1->Tcw, T21, nullptr, n1, f1.data(), xyz1, desc1, dist1, nullptr,
+                      th, MO_TH_HIGH, m1.data());
+    mo_project_search(k1, cam, bounds, scale, nlevels, log_scale, k2->Tcw, T12, nullptr, n2, f2.data(), xyz2, desc2, dist2, nullptr,
+                      th, MO_TH_HIGH, m2.data());
+    int nfound = 0;
+    for (int i = 0; i < n1; ++i) {
+        out12[i] = pre12[i];
+        const int idx2 = m1[i];
+        if (idx2 >= 0 && m2[idx2] == i) { out12[i] = idx2; ++nfound; }
+    }
+    return nfound;
+}
+
 } // extern "C"
+
 
 

@@ -19,7 +19,14 @@ class KeyFrame {
 public:
     std::vector<MapPoint *> mvpMapPoints;
     std::vector<MapPoint *> GetMapPointMatches() { return mvpMapPoints; }
-    std::set<MapPoint *> GetMapPoints() { std::abort(); }
+    std::set<MapPoint *> GetMapPoints() /* src/KeyFrame.cc: the non-NULL entries of mvpMapPoints that are not bad */
+    {
+        std::set<MapPoint *> s;
+        for (size_t i = 0; i < mvpMapPoints.size(); ++i)
+            if (mvpMapPoints[i] && !mp_is_bad_(mvpMapPoints[i])) s.insert(mvpMapPoints[i]);
+        return s;
+    }
+    static bool mp_is_bad_(MapPoint *p); /* MapPoint is incomplete here; defined in MapPoint_impl.h */
     mutable long mnLastGetMapPoint = -1; /* the drivers read a matcher's choice out of this */
     MapPoint *GetMapPoint(const size_t &idx) { mnLastGetMapPoint = (long)idx; return mvpMapPoints[idx]; }
     /* pose accessors as src/KeyFrame.cc has them (clones of Tcw's blocks and of Ow, which KeyFrame::SetPose computes as

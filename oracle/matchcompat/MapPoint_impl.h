@@ -32,5 +32,6 @@ int MapPoint::PredictScale(const float &currentDist, KeyFrame *pKF) /* src/MapPo
         nScale = pKF->mnScaleLevels - 1;
     return nScale;
 }
+bool KeyFrame::mp_is_bad_(MapPoint *p) { return p->isBad(); }
 } // namespace ORB_SLAM2
 #endif

@@ -378,6 +378,139 @@ int refmatch_fuse(const refmatch_frame *kfr, const float *cam, const float *boun
     return total;
 }
 
+namespace {
+cv::Mat mat44(const float *m16)
+{
+    cv::Mat T(4, 4, CV_32F);
+    for (int r = 0; r < 4; ++r)
+        for (int c = 0; c < 4; ++c) T.at<float>(r, c) = m16[4 * r + c];
+    return T;
+}
+void fill_points(std::vector<MapPoint> &mps, int n, const uint8_t *flags, const float *xyz, const uint8_t *desc, const float *dist,
+                 const float *normal)
+{
+    mps.assign((size_t)std::max(n, 1), MapPoint());
+    for (int i = 0; i < n; ++i) {
+        MapPoint &m = mps[i];
+        m.mWorldPos = cv::Mat(3, 1, CV_32F);
+        m.mNormalVector = cv::Mat(3, 1, CV_32F);
+        for (int c = 0; c < 3; ++c) { m.mWorldPos.at<float>(c) = xyz[3 * i + c]; m.mNormalVector.at<float>(c) = normal ? normal[3 * i + c] : 0.f; }
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1);
+        std::memcpy(m.mDescriptor.ptr(0), desc + (size_t)i * 32, 32);
+        m.mbBad = (flags[i] & 2) != 0;
+        m.mfMinDistance = dist[2 * i];
+        m.mfMaxDistance = dist[2 * i + 1];
+        m.nObs = 1;
+    }
+}
+} // namespace
+
+/* ORBmatcher::Fuse(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, float th, vector<MapPoint*>
+ * &vpReplacePoint) (src/ORBmatcher.cc:1133-1260, LoopClosing::SearchAndFuse): the CHOICE per point, pinned as in
+ * refmatch_fuse (one point per call of the reference's function, the keypoint handed to pKF->GetMapPoint recorded; a run
+ * over the whole vector must fuse as many).  Scw = the 4x4 similarity, row-major.  mp_flags[i] bit 1 = isBad(), bit 2 = the
+ * point is one of pKF->GetMapPoints() (spAlreadyFound, :1147). */
+int refmatch_fuse_sim3(const refmatch_frame *kfr, const float *cam, const float *bounds, const float *scale, const float *inv_sigma2,
+                       int nlevels, float log_scale, const float *Scw, int n_mp, const uint8_t *mp_flags, const float *mp_xyz,
+                       const uint8_t *mp_desc, const float *mp_dist, const float *mp_normal, float th, int32_t *out_best)
+{
+    int total = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        KeyFrame kf;
+        fill_keyframe(kf, *kfr, cam, bounds, scale, inv_sigma2, nlevels, log_scale);
+        std::vector<MapPoint> mps;
+        fill_points(mps, n_mp, mp_flags, mp_xyz, mp_desc, mp_dist, mp_normal);
+        std::vector<MapPoint *> vp(n_mp);
+        for (int i = 0; i < n_mp; ++i) {
+            vp[i] = &mps[i];
+            if (mp_flags[i] & 4) kf.mvpMapPoints.push_back(&mps[i]); /* beyond N: only GetMapPoints() sees them */
+        }
+        ORBmatcher matcher(0.6f, true);
+        cv::Mat S = mat44(Scw);
+        if (pass == 0) {
+            for (int i = 0; i < n_mp; ++i) {
+                kf.mnLastGetMapPoint = -1;
+                std::vector<MapPoint *> one(1, vp[i]), rep(1, static_cast<MapPoint *>(NULL));
+                const int nf = matcher.Fuse(&kf, S, one, th, rep);
+                out_best[i] = nf ? (int32_t)kf.mnLastGetMapPoint : -1;
+                total += nf;
+            }
+        } else {
+            std::vector<MapPoint *> rep(n_mp, static_cast<MapPoint *>(NULL));
+            if (matcher.Fuse(&kf, S, vp, th, rep) != total) std::abort();
+        }
+    }
+    return total;
+}
+
+/* ORBmatcher::SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, vector<MapPoint*>
+ * &vpMatched, int th) (src/ORBmatcher.cc:353-485, LoopClosing::ComputeSim3).  occupied[idx] != 0: vpMatched[idx] is set on
+ * entry; mp_flags[i] bit 1 = isBad(), bit 2 = the point is in vpMatched already (spAlreadyFound, :367-368) -- such points
+ * are what the occupied slots hold here.  out_match[idx] = the point this call put into vpMatched[idx], -1 elsewhere. */
+int refmatch_search_by_projection_kf_sim3(const refmatch_frame *kfr, const float *cam, const float *bounds, const float *scale,
+                                          const float *inv_sigma2, int nlevels, float log_scale, const float *Scw, int n_mp,
+                                          const uint8_t *mp_flags, const float *mp_xyz, const uint8_t *mp_desc, const float *mp_dist,
+                                          const float *mp_normal, const uint8_t *occupied, int th, int32_t *out_match)
+{
+    KeyFrame kf;
+    fill_keyframe(kf, *kfr, cam, bounds, scale, inv_sigma2, nlevels, log_scale);
+    std::vector<MapPoint> mps;
+    fill_points(mps, n_mp, mp_flags, mp_xyz, mp_desc, mp_dist, mp_normal);
+    std::vector<MapPoint *> vp(n_mp), found;
+    for (int i = 0; i < n_mp; ++i) {
+        vp[i] = &mps[i];
+        if (mp_flags[i] & 4) found.push_back(&mps[i]);
+    }
+    MapPoint held;
+    std::vector<MapPoint *> matched(kfr->n, static_cast<MapPoint *>(NULL));
+    size_t k = 0;
+    for (int idx = 0; idx < kfr->n; ++idx)
+        if (occupied && occupied[idx]) matched[idx] = k < found.size() ? found[k++] : &held;
+    if (k < found.size()) std::abort(); /* the scenario must offer a slot per already-found point */
+    std::vector<MapPoint *> before = matched;
+    ORBmatcher matcher(0.75f, true);
+    const int nm = matcher.SearchByProjection(&kf, mat44(Scw), vp, matched, th);
+    for (int idx = 0; idx < kfr->n; ++idx)
+        out_match[idx] = (matched[idx] && matched[idx] != before[idx]) ? (int32_t)(matched[idx] - mps.data()) : -1;
+    return nm;
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1262-1501, LoopClosing::ComputeSim3).
+ * Each keyframe: frame record with its pose in Tcw, map points per keypoint (flags bit 0 = GetMapPointMatches()[i] != NULL,
+ * bit 1 = isBad()).  pre12[i1] = the pKF2 keypoint whose map point vpMatches12[i1] holds on entry, or -1.
+ * out12[i1] = the pKF2 keypoint whose map point vpMatches12[i1] holds on return, -1 = NULL.  Returns nFound. */
+int refmatch_search_by_sim3(const refmatch_frame *k1, const refmatch_frame *k2, const float *cam, const float *bounds,
+                            const float *scale, const float *inv_sigma2, int nlevels, float log_scale, const uint8_t *flags1,
+                            const float *xyz1, const uint8_t *desc1, const float *dist1, const uint8_t *flags2, const float *xyz2,
+                            const uint8_t *desc2, const float *dist2, const int32_t *pre12, float s12, const float *R12,
+                            const float *t12, float th, int32_t *out12)
+{
+    KeyFrame kf1, kf2;
+    fill_keyframe(kf1, *k1, cam, bounds, scale, inv_sigma2, nlevels, log_scale);
+    fill_keyframe(kf2, *k2, cam, bounds, scale, inv_sigma2, nlevels, log_scale);
+    std::vector<MapPoint> m1, m2;
+    fill_points(m1, k1->n, flags1, xyz1, desc1, dist1, NULL);
+    fill_points(m2, k2->n, flags2, xyz2, desc2, dist2, NULL);
+    for (int i = 0; i < k1->n; ++i) if (flags1[i] & 1) kf1.mvpMapPoints[i] = &m1[i];
+    for (int i = 0; i < k2->n; ++i) {
+        if (flags2[i] & 1) kf2.mvpMapPoints[i] = &m2[i];
+        m2[i].mbInKF = true; /* GetIndexInKeyFrame(pKF2) of a pKF2 point: its own index (:1297) */
+        m2[i].mnIdxInKF = i;
+    }
+    std::vector<MapPoint *> v12(k1->n, static_cast<MapPoint *>(NULL));
+    for (int i = 0; i < k1->n; ++i) if (pre12[i] >= 0) v12[i] = &m2[pre12[i]];
+    cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
+    for (int r = 0; r < 3; ++r) {
+        t.at<float>(r) = t12[r];
+        for (int c = 0; c < 3; ++c) R.at<float>(r, c) = R12[3 * r + c];
+    }
+    ORBmatcher matcher(0.75f, true);
+    const int nf = matcher.SearchBySim3(&kf1, &kf2, v12, s12, R, t, th);
+    for (int i = 0; i < k1->n; ++i) out12[i] = v12[i] ? (int32_t)(v12[i] - m2.data()) : -1;
+    return nf;
+}
+
 } // extern "C"
+
 
 

@@ -401,6 +401,110 @@ def _fuse_call(fn, kf: dict, cam, bounds, scale, inv_sigma2, log_scale: float, m
     return out[:n], int(nf)
 
 
+def _kf_frame(kf: dict, keep: list):
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data
+    f = _MatchFrame()
+    f.n = len(kf["kps"])
+    f.kps = arr(kf["kps"], KP_DTYPE)
+    f.un_xy = arr(kf["un_xy"], np.float32)
+    f.desc = arr(kf["desc"], np.uint8)
+    f.u_right = arr(kf["u_right"], np.float32) if kf.get("u_right") is not None else None
+    f.grid_count = arr(np.diff(kf["cell_start"]), np.int32)
+    f.grid_idx = arr(kf["cell_idx"], np.int32)
+    f.Tcw = arr(kf["Tcw"], np.float32)
+    keep.append(f)
+    return f, arr
+
+
+def sim3_decompose(Scw) -> tuple:
+    """Scw [4,4] -> (T [3,4] = [Rcw | tcw], Ow [3]) as src/ORBmatcher.cc:360-365 / :1140-1146 compute them"""
+    S = np.ascontiguousarray(Scw, np.float32)
+    T, Ow = np.zeros((3, 4), np.float32), np.zeros(3, np.float32)
+    Oracle.load().mo_sim3_decompose(_ptr(S), _ptr(T), _ptr(Ow))
+    return T, Ow
+
+
+def sim3_relative(s12: float, R12, t12) -> tuple:
+    """-> (T12 = [s12 R12 | t12], T21 = [sR21 | t21]) as src/ORBmatcher.cc:1279-1281"""
+    R, t = np.ascontiguousarray(R12, np.float32), np.ascontiguousarray(t12, np.float32)
+    T12, T21 = np.zeros((3, 4), np.float32), np.zeros((3, 4), np.float32)
+    fn = Oracle.load().mo_sim3_relative
+    fn.argtypes = [C.c_float, _vp, _vp, _vp, _vp]
+    fn(float(s12), _ptr(R), _ptr(t), _ptr(T12), _ptr(T21))
+    return T12, T21
+
+
+def project_search(kf, cam, bounds, scale, log_scale, T1, T2, Ow, pts, th, max_dist):
+    """mo_project_search (oracle/match_oracle.cpp): the choice per point of Fuse(pKF, Scw, ...) / one direction of SearchBySim3.
+    pts: flags, xyz, desc, dist, normal (or None)"""
+    keep = []
+    f, arr = _kf_frame(kf, keep)
+    scale = np.ascontiguousarray(scale, np.float32)
+    n = len(pts["flags"])
+    out = np.full(max(n, 1), -1, np.int32)
+    fn = Oracle.load().mo_project_search
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_float, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp]
+    nf = fn(C.addressof(f), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data, len(scale), float(log_scale),
+            arr(T1, np.float32), arr(T2, np.float32) if T2 is not None else None, arr(Ow, np.float32) if Ow is not None else None,
+            n, arr(pts["flags"], np.uint8), arr(pts["xyz"], np.float32), arr(pts["desc"], np.uint8), arr(pts["dist"], np.float32),
+            arr(pts["normal"], np.float32) if pts.get("normal") is not None else None, float(th), int(max_dist), out.ctypes.data)
+    return out[:n], int(nf)
+
+
+def fuse_sim3(kf, cam, bounds, scale, log_scale, Scw, pts, th=4.0):
+    """ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1133-1260): the choice per point, restated"""
+    T, Ow = sim3_decompose(Scw)
+    return project_search(kf, cam, bounds, scale, log_scale, T, None, Ow, pts, th, 50)
+
+
+def search_by_projection_kf_sim3(kf, cam, bounds, scale, log_scale, Scw, pts, occupied, th=10):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:353-485), restated"""
+    keep = []
+    f, arr = _kf_frame(kf, keep)
+    T, Ow = sim3_decompose(Scw)
+    scale = np.ascontiguousarray(scale, np.float32)
+    out = np.full(max(f.n, 1), -1, np.int32)
+    fn = Oracle.load().mo_search_by_projection_kf_sim3
+    fn.restype = C.c_int
+    fn.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_float, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]
+    nm = fn(C.addressof(f), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data, len(scale), float(log_scale),
+            arr(T, np.float32), arr(Ow, np.float32), len(pts["flags"]), arr(pts["flags"], np.uint8), arr(pts["xyz"], np.float32),
+            arr(pts["desc"], np.uint8), arr(pts["dist"], np.float32), arr(pts["normal"], np.float32),
+            arr(occupied, np.uint8) if occupied is not None else None, int(th), out.ctypes.data)
+    return out[:f.n], int(nm)
+
+
+def _sim3_args(k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12, th, keep, with_sigma):
+    f1, arr = _kf_frame(k1, keep)
+    f2, _ = _kf_frame(k2, keep)
+    scale = np.ascontiguousarray(scale, np.float32)
+    keep.append(scale)
+    a = [C.addressof(f1), C.addressof(f2), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data]
+    if with_sigma:
+        a.append(arr(inv_sigma2, np.float32))
+    a += [len(scale), float(log_scale)]
+    for p in (p1, p2):
+        a += [arr(p["flags"], np.uint8), arr(p["xyz"], np.float32), arr(p["desc"], np.uint8), arr(p["dist"], np.float32)]
+    a += [arr(pre12, np.int32), float(s12), arr(R12, np.float32), arr(t12, np.float32), float(th)]
+    return a, f1.n
+
+
+def search_by_sim3(k1, k2, cam, bounds, scale, log_scale, p1, p2, pre12, s12, R12, t12, th=7.5):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1262-1501), restated -> (vpMatches12 as pKF2 keypoint indices, nFound)"""
+    keep = []
+    a, n1 = _sim3_args(k1, k2, cam, bounds, scale, None, log_scale, p1, p2, pre12, s12, R12, t12, th, keep, False)
+    out = np.full(max(n1, 1), -1, np.int32)
+    fn = Oracle.load().mo_search_by_sim3
+    fn.restype = C.c_int
+    fn.argtypes = [_vp] * 5 + [C.c_int, C.c_float] + [_vp] * 9 + [C.c_float, _vp, _vp, C.c_float, _vp]
+    nf = fn(*a, out.ctypes.data)
+    return out[:n1], int(nf)
+
+
 def fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th=3.0):
     """ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:968-1131): the choice per map point, restated"""
     return _fuse_call(Oracle.load().mo_fuse, kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
@@ -408,6 +512,53 @@ def fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th=3.0):
 
 class RefMatcher:
     """The reference's own src/ORBmatcher.cc + src/Frame.cc (oracle/_ref/librefmatch.so)."""
+
+    @classmethod
+    def _load(cls):
+        if cls._lib is None:
+            cls._lib = C.CDLL(str(HERE / "_ref" / "librefmatch.so"))
+        return cls._lib
+
+    @classmethod
+    def fuse_sim3(cls, kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, th=4.0):
+        keep = []
+        f, arr = _kf_frame(kf, keep)
+        scale = np.ascontiguousarray(scale, np.float32)
+        n = len(pts["flags"])
+        out = np.full(max(n, 1), -1, np.int32)
+        fn = cls._load().refmatch_fuse_sim3
+        fn.restype = C.c_int
+        fn.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int, C.c_float, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_float, _vp]
+        nf = fn(C.addressof(f), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data, arr(inv_sigma2, np.float32),
+                len(scale), float(log_scale), arr(Scw, np.float32), n, arr(pts["flags"], np.uint8), arr(pts["xyz"], np.float32),
+                arr(pts["desc"], np.uint8), arr(pts["dist"], np.float32), arr(pts["normal"], np.float32), float(th), out.ctypes.data)
+        return out[:n], int(nf)
+
+    @classmethod
+    def search_by_projection_kf_sim3(cls, kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occupied, th=10):
+        keep = []
+        f, arr = _kf_frame(kf, keep)
+        scale = np.ascontiguousarray(scale, np.float32)
+        out = np.full(max(f.n, 1), -1, np.int32)
+        fn = cls._load().refmatch_search_by_projection_kf_sim3
+        fn.restype = C.c_int
+        fn.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int, C.c_float, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]
+        nm = fn(C.addressof(f), arr(cam, np.float32), arr(bounds, np.float32), scale.ctypes.data, arr(inv_sigma2, np.float32),
+                len(scale), float(log_scale), arr(Scw, np.float32), len(pts["flags"]), arr(pts["flags"], np.uint8),
+                arr(pts["xyz"], np.float32), arr(pts["desc"], np.uint8), arr(pts["dist"], np.float32), arr(pts["normal"], np.float32),
+                arr(occupied, np.uint8) if occupied is not None else None, int(th), out.ctypes.data)
+        return out[:f.n], int(nm)
+
+    @classmethod
+    def search_by_sim3(cls, k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12, th=7.5):
+        keep = []
+        a, n1 = _sim3_args(k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12, th, keep, True)
+        out = np.full(max(n1, 1), -1, np.int32)
+        fn = cls._load().refmatch_search_by_sim3
+        fn.restype = C.c_int
+        fn.argtypes = [_vp] * 6 + [C.c_int, C.c_float] + [_vp] * 9 + [C.c_float, _vp, _vp, C.c_float, _vp]
+        nf = fn(*a, out.ctypes.data)
+        return out[:n1], int(nf)
 
     @classmethod
     def fuse(cls, kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th=3.0):

@@ -238,3 +238,66 @@ def make_fuse_case(seed=0, copies=1, bad_rate=0.05, in_kf_rate=0.1, dist_jitter=
     sigma2 = (sc32 * sc32).astype(np.float32)            # mvLevelSigma2[i] = mvScaleFactor[i] * mvScaleFactor[i]
     inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)   # mvInvLevelSigma2[i] = 1.0f / mvLevelSigma2[i]
     return cur, cam, bounds, scale, inv_sigma2, host_logf(1.2), mps
+
+
+def sim3_of(Tcw: np.ndarray, s: float) -> np.ndarray:
+    """the 4x4 similarity [s R | s t; 0 0 0 1] of a pose (what Converter::toCvMat(g2o::Sim3) hands LoopClosing's matchers)"""
+    S = np.eye(4, dtype=np.float32)
+    S[:3, :3] = (np.float32(s) * Tcw[:, :3].astype(np.float32)).astype(np.float32)
+    S[:3, 3] = (np.float32(s) * Tcw[:, 3].astype(np.float32)).astype(np.float32)
+    return S
+
+
+def make_sim3_points_case(seed=0, s=1.03, found_rate=0.1, occupied_rate=0.2, **kw):
+    """Scenario for the two Scw matchers of LoopClosing -- Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+    (src/ORBmatcher.cc:1133-1260) and SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:353-485): make_fuse_case's
+    keyframe and points, the keyframe's pose given as a similarity of scale s; bit 2 of the point flags = already found
+    (in pKF->GetMapPoints() / in vpMatched), and enough occupied vpMatched slots to hold those.
+    -> (kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occupied)"""
+    kf, cam, bounds, scale, inv_sigma2, log_scale, mps = make_fuse_case(seed=seed, in_kf_rate=found_rate, **kw)
+    rng = np.random.default_rng(12000 + seed)
+    Scw = sim3_of(kf["Tcw"], s)
+    occupied = (rng.random(len(kf["kps"])) < occupied_rate).astype(np.uint8)
+    pts = dict(mps)
+    pts["flags"] = (mps["flags"] | 1).astype(np.uint8)  # vpPoints holds no NULL entries
+    found = np.nonzero(pts["flags"] & 4)[0]
+    pts["flags"][found[int(occupied.sum()):]] &= np.uint8(3)  # vpMatched can only hold as many points as it has set slots
+    return kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occupied
+
+
+def make_sim3_pair_case(seed=0, s12=1.02, pre_rate=0.1, bad_rate=0.05, dist_jitter=0.25, **kw):
+    """Scenario for ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1262-1501): keyframe 1 = the previous frame of make_case,
+    keyframe 2 = the current one; each keypoint with a depth carries a map point (un-projected with its own keyframe's
+    pose, as map_points does for the previous frame); the relative similarity is the true relative pose scaled by s12;
+    pre_rate of pKF1's points are matched already (vpMatches12 on entry).
+    -> (k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12)"""
+    K = kw.get("K", KITTI_K)
+    cur, last, cam, bounds, scale = make_case(seed=seed, **kw)
+    rng = np.random.default_rng(13000 + seed)
+    k1 = {k: last[k] for k in ("kps", "desc", "un_xy", "cell_start", "cell_idx", "u_right", "Tcw")}
+    cur_mp = map_points(cur, cur["Tcw"], K, rng, synth_depth=None if kw.get("stereo", True) else (4.0, 60.0))
+    k2 = {k: cur[k] for k in ("kps", "desc", "un_xy", "cell_start", "cell_idx", "u_right", "Tcw")}
+    sc = np.asarray(scale, np.float64)
+
+    def pts(fr, mp):
+        n = len(mp["mp_flags"])
+        T = fr["Tcw"].astype(np.float64)
+        Ow = -T[:, :3].T @ T[:, 3]
+        d = np.linalg.norm(mp["mp_xyz"].astype(np.float64) - Ow, axis=1)
+        max_d = d * sc[fr["kps"]["octave"]] * rng.uniform(1 - dist_jitter, 1 + dist_jitter, n)
+        flags = ((mp["mp_flags"] & 1) | ((rng.random(n) < bad_rate).astype(np.uint8) << 1)).astype(np.uint8)
+        return {"flags": flags, "xyz": mp["mp_xyz"], "desc": mp["mp_desc"], "dist": np.stack([max_d / sc[-1], max_d], 1).astype(np.float32)}
+    p1, p2 = pts(k1, last), pts(k2, cur_mp)
+    T1 = np.vstack([k1["Tcw"].astype(np.float64), [0, 0, 0, 1]])
+    T2 = np.vstack([k2["Tcw"].astype(np.float64), [0, 0, 0, 1]])
+    T12 = T1 @ np.linalg.inv(T2)  # camera 2 -> camera 1
+    R12 = T12[:3, :3].astype(np.float32)
+    t12 = (T12[:3, 3] * s12).astype(np.float32)
+    n1, n2 = len(p1["flags"]), len(p2["flags"])
+    pre12 = np.full(n1, -1, np.int32)
+    have2 = np.nonzero(p2["flags"] & 1)[0]
+    pick = np.nonzero((rng.random(n1) < pre_rate) & ((p1["flags"] & 1) != 0))[0]
+    pre12[pick] = rng.choice(have2, len(pick), replace=False) if len(pick) <= len(have2) else -1
+    sc32 = np.asarray(scale, np.float32)
+    inv_sigma2 = (np.float32(1.0) / (sc32 * sc32)).astype(np.float32)
+    return k1, k2, cam, bounds, scale, inv_sigma2, host_logf(1.2), p1, p2, pre12, float(np.float32(s12)), R12, t12

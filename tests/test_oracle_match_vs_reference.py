@@ -169,3 +169,43 @@ def test_fuse_monocular_distorted_keyframe(oracle_built, ref):
     """a distorted camera: the keyframe's bounds are the Frame's float bounds truncated to int"""
     assert _compare_fuse(oracle_built, ref, "fuse tum", seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
                          bf=40.0, stereo=False, nf=1000, dist_jitter=0.4) > 150
+
+
+# ---- LoopClosing's matchers: Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) :1133-1260, SearchByProjection(pKF, Scw, vpPoints,
+# ---- vpMatched, th) :353-485, SearchBySim3 :1262-1501 ----
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, s=0.97, dz=0.3), dict(seed=4, copies=3),
+                                dict(seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0,
+                                     stereo=False, nf=1000, dist_jitter=0.4)])
+def test_fuse_sim3_and_projection_sim3(kw, oracle_built, ref):
+    kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occupied = matchcase.make_sim3_points_case(**kw)
+    total = 0
+    for th in (4.0, 10.0):
+        want, wnf = ref.fuse_sim3(kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, th)
+        got, nf = oracle_built.fuse_sim3(kf, cam, bounds, scale, log_scale, Scw, pts, th)
+        assert np.array_equal(got, want) and nf == wnf == int((got >= 0).sum()), f"fuse sim3 th={th}: {(got != want).sum()} differ"
+        total += nf
+        for occ in (occupied, None):
+            p = pts if occ is not None else dict(pts, flags=(pts["flags"] & 3).astype(np.uint8))
+            want, wnm = ref.search_by_projection_kf_sim3(kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, p, occ, int(th))
+            got, nm = oracle_built.search_by_projection_kf_sim3(kf, cam, bounds, scale, log_scale, Scw, p, occ, int(th))
+            assert np.array_equal(got, want) and nm == wnm == int((got >= 0).sum()), f"projection sim3 th={th}: {(got != want).sum()} differ"
+            if occ is not None:
+                assert not (got[occ != 0] >= 0).any()
+            total += nm
+    assert total > 300
+
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, s12=0.96, dz=0.3), dict(seed=3, dz=-0.3, pre_rate=0.3),
+                                dict(seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0,
+                                     stereo=False, nf=1000, dist_jitter=0.4)])
+def test_search_by_sim3(kw, oracle_built, ref):
+    k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12 = matchcase.make_sim3_pair_case(**kw)
+    total = 0
+    for th in (7.5, 3.0):
+        want, wnf = ref.search_by_sim3(k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12, th)
+        got, nf = oracle_built.search_by_sim3(k1, k2, cam, bounds, scale, log_scale, p1, p2, pre12, s12, R12, t12, th)
+        assert np.array_equal(got, want) and nf == wnf, f"sim3 th={th}: {(got != want).sum()} differ, nFound {nf} vs {wnf}"
+        assert np.array_equal(got[pre12 >= 0], pre12[pre12 >= 0])
+        total += nf
+    assert total > 100
