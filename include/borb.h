@@ -289,6 +289,41 @@ typedef struct borb_fuse_points {
 int borb_fuse_search(borb_extractor *kf, int frame, const borb_fuse_points *mps, const float *Tcw, const float *Ow, float bf,
                      float th, unsigned flags, int32_t *best_idx, int *nfused);
 
+/* -- the loop-closing matchers: the searches of ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+ *    (src/ORBmatcher.cc:1133-1260, LoopClosing::SearchAndFuse), ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched,
+ *    th) (:353-485) and ORBmatcher::SearchBySim3 (:1262-1501), both LoopClosing::ComputeSim3 ------------------------- */
+
+/* How the points reach the keyframe's image.  T1 = the first transform, 3 x 4 row-major [R | t]: [Rcw | tcw] of the
+ * similarity as :360-364 / :1140-1145 derive them (Rcw = sRcw / scw, tcw = Scw.col(3) / scw), or a keyframe's pose
+ * (SearchBySim3: R1w, t1w).  T2 = a second transform applied to the camera-frame point ([sR21 | t21] resp. [sR12 | t12],
+ * :1279-1281) or NULL.  Ow = the camera centre -Rcw.t() * tcw for dist3D = |p3Dw - Ow| and the viewing-angle test, or NULL:
+ * dist3D of the camera-frame point itself (SearchBySim3, :1330 / :1418).  The matrices are the CALLER's cv::Mat results,
+ * so their arithmetic is OpenCV's own. */
+typedef struct borb_projection {
+    const float *T1;
+    const float *T2;
+    const float *Ow;
+} borb_projection;
+
+/* pKF = frame `frame` of kf's last call (borb_load_frame).  pts as borb_fuse_points: bit 0 of a flag = the entry is a point,
+ * bit 1 = isBad(), bit 2 = already found (in pKF->GetMapPoints(), :1147; in vpMatched, :367); normal = NULL switches the
+ * viewing-angle test off (SearchBySim3 has none).  best_idx[i] = the keypoint with the first smallest distance among the
+ * admitted ones when that distance is <= max_dist (TH_LOW = 50 for Fuse, :1240), else -1.  What Fuse then does with the
+ * map (:1240-1256) stays with the caller. */
+int borb_project_search(borb_extractor *kf, int frame, const borb_fuse_points *pts, const borb_projection *pr, float th,
+                        int max_dist, int32_t *best_idx, int *nfound);
+/* occupied[idx] != 0 where vpMatched[idx] is set on entry (NULL = none).  match[idx], idx < *n_kf, = the point this call puts
+ * into vpMatched[idx] or -1; *nmatches = the return value. */
+int borb_search_by_projection_sim3(borb_extractor *kf, int frame, const borb_fuse_points *pts, const borb_projection *pr,
+                                   const uint8_t *occupied, int th, int32_t *match, int *n_kf, int *nmatches);
+/* kf1 / kf2 = handles holding pKF1 / pKF2 (frame 0); pts1[i1] = pKF1->GetMapPointMatches()[i1] (bit 0 non-NULL, bit 1 bad),
+ * pts2 likewise; T1w / T2w = the keyframes' poses; T12 = [s12 R12 | t12], T21 = [sR21 | t21] (:1279-1281); pre12[i1] = the
+ * pKF2 keypoint whose map point vpMatches12[i1] holds on entry or -1 (NULL = none).  match12[i1] = the same on return;
+ * *nfound = the return value. */
+int borb_search_by_sim3(borb_extractor *kf1, borb_extractor *kf2, const borb_fuse_points *pts1, const borb_fuse_points *pts2,
+                        const float *T1w, const float *T2w, const float *T12, const float *T21, float th, const int32_t *pre12,
+                        int32_t *match12, int *nfound);
+
 /* -- monocular-initialisation matcher: replaces ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2,
  *    vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12, int windowSize)
  *    (src/ORBmatcher.cc:487-632), called by Tracking::MonocularInitialization (src/Tracking.cc:570-646) --- */

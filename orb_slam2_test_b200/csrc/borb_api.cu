@@ -1698,26 +1698,31 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
         CU(cudaFuncSetAttribute(k_match_resolve<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
         CU(cudaFuncSetAttribute(k_match_resolve<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
         CU(cudaFuncSetAttribute(k_match_resolve<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
+        CU(cudaFuncSetAttribute(k_match_resolve<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk_smem));
     }
 #define MATCH_LAUNCH(MODE)                                                                                                   \
     do {                                                                                                                     \
         if (n > 0)                                                                                                           \
             k_match_candidates<MODE><<<cand_grid, MT_CAND_NT, 0, st>>>(                                                       \
                 mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4, \
-                d_ur, d_occ, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more);                                 \
+                d_ur, d_occ, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more, l_extra);                        \
         k_match_resolve<MODE><<<1, MT_NT, tk_smem, st>>>(mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, \
                                                    cur->d_bounds + (size_t)frame * 4, cur->d_nout + frame, d_ur, d_occ, l_geo,  \
                                                    l_angle, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more,           \
                                                    cur->d_mt_choice, cur->d_mt_taker, (int)K, cur->d_mt_match,                 \
-                                                   cur->d_mt_match + K, tk_smem ? 1 : 0);                                    \
+                                                   cur->d_mt_match + K, tk_smem ? 1 : 0, l_extra);                           \
     } while (0)
-    if (mode == 5) {
-        /* the matchers whose queries are independent (Fuse: the choice per map point): M1a alone; the best cached entry of a
-         * query IS its choice -- first smallest distance in GetFeaturesInArea order */
-        if (n > 0)
+    if (mode == 5 || mode == 6) {
+        /* the matchers whose queries are independent (Fuse: the choice per map point; a direction of SearchBySim3): M1a
+         * alone; the best cached entry of a query IS its choice -- first smallest distance in GetFeaturesInArea order */
+        if (n > 0 && mode == 5)
             k_match_candidates<5><<<cand_grid, MT_CAND_NT, 0, st>>>(
                 mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4,
                 d_ur, nullptr, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more, l_extra);
+        else if (n > 0)
+            k_match_candidates<6><<<cand_grid, MT_CAND_NT, 0, st>>>(
+                mp, cur->d_out_kp + fo, cur->d_out_desc + fo * 32, cur->d_un_xy + fo, cs, ci, cur->d_bounds + (size_t)frame * 4,
+                nullptr, nullptr, l_geo, l_oct, l_desc, l_flags, cur->d_mt_cache, cur->d_mt_more, l_extra);
         CU(cudaGetLastError());
         CU(cudaMemcpy2DAsync(cur->h_mt_m12, 4, cur->d_mt_cache, MT_K * 4, 4, std::max<size_t>(un, 1), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
@@ -1737,6 +1742,7 @@ int run_matcher(borb_extractor *cur, int frame, int mode, int n, const float *ge
     if (mode == 1) MATCH_LAUNCH(1);
     else if (mode == 2) MATCH_LAUNCH(2);
     else if (mode == 4) MATCH_LAUNCH(4);
+    else if (mode == 7) MATCH_LAUNCH(6); /* MODE 6 queries with the sequential rule: SearchByProjection(pKF, Scw, ...) */
     else {
         if (!cur->d_mt_cnt) {
             CU(cudaMalloc(&cur->d_mt_cnt, 2 * K * 4));
@@ -1904,6 +1910,125 @@ int borb_fuse_search(borb_extractor *kf, int frame, const borb_fuse_points *mps,
     }
     return run_matcher(kf, frame, 5, mps->n, geo.data(), 4, mps->desc, qf.data(), mind.data(), nullptr, nullptr, mp,
                        (flags & BORB_MATCH_USE_STEREO) != 0, best_idx, nullptr, nfused, extra.data());
+}
+
+namespace {
+/* the point arrays of the loop-closing matchers as run_matcher's query columns */
+struct ProjQueries {
+    std::vector<float> geo, extra;
+    std::vector<int32_t> mind;
+    std::vector<uint8_t> qf;
+    ProjQueries(const borb_fuse_points *p, uint8_t usable)
+    {
+        const size_t n = (size_t)std::max(p->n, 0);
+        geo.resize(4 * n); mind.resize(n); qf.resize(n);
+        if (p->normal) extra.resize(4 * n);
+        for (size_t i = 0; i < n; ++i) {
+            geo[4 * i] = p->xyz[3 * i]; geo[4 * i + 1] = p->xyz[3 * i + 1]; geo[4 * i + 2] = p->xyz[3 * i + 2];
+            geo[4 * i + 3] = p->dist[2 * i + 1];
+            std::memcpy(&mind[i], &p->dist[2 * i], 4);
+            if (p->normal) { extra[4 * i] = p->normal[3 * i]; extra[4 * i + 1] = p->normal[3 * i + 1]; extra[4 * i + 2] = p->normal[3 * i + 2]; extra[4 * i + 3] = 0.f; }
+            qf[i] = ((p->flags[i] & 1) && !(p->flags[i] & 6)) ? usable : 0;
+        }
+    }
+};
+
+int proj_params(borb_extractor *kf, const borb_fuse_points *pts, const borb_projection *pr, float th, int max_dist, MatchParams &mp)
+{
+    if (!kf || !pts || !pr || !pr->T1) return fail(BORB_ERR_ARG, "null argument");
+    if (pts->n > 0 && (!pts->xyz || !pts->desc || !pts->flags || !pts->dist)) return fail(BORB_ERR_ARG, "point arrays");
+    if (max_dist < 0 || max_dist > 255) return fail(BORB_ERR_ARG, "distance threshold %d", max_dist);
+    std::memset(&mp, 0, sizeof mp);
+    std::memcpy(mp.Tc, pr->T1, 48);
+    if (pr->T2) { std::memcpy(mp.Tl, pr->T2, 48); mp.two_step = 1; }
+    if (pr->Ow) std::memcpy(mp.Ow, pr->Ow, 12); else mp.cam_norm = 1;
+    mp.use_normal = pts->normal ? 1 : 0;
+    if (mp.use_normal && mp.cam_norm) return fail(BORB_ERR_ARG, "the viewing-angle test needs the camera centre");
+    mp.th = th;
+    mp.orb_dist = max_dist;
+    mp.nlevels = kf->nlevels;
+    mp.log_scale = orb_logf_exact((float)kf->scale_factor);
+    return BORB_OK;
+}
+} // namespace
+
+/* The search inside ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1133-1260) and one direction
+ * of ORBmatcher::SearchBySim3 (:1305-1390 / :1393-1481): per point the first smallest Hamming distance among pKF's keypoints
+ * of the predicted level and the one below inside the window, when <= max_dist.  M1a in MODE 6; independent queries. */
+int borb_project_search(borb_extractor *kf, int frame, const borb_fuse_points *pts, const borb_projection *pr, float th,
+                        int max_dist, int32_t *best_idx, int *nfound)
+{
+    MatchParams mp;
+    int rc = proj_params(kf, pts, pr, th, max_dist, mp);
+    if (rc != BORB_OK) return rc;
+    if (!best_idx) return fail(BORB_ERR_ARG, "null output");
+    ProjQueries q(pts, 1);
+    return run_matcher(kf, frame, 6, pts->n, q.geo.data(), 4, pts->desc, q.qf.data(), q.mind.data(), nullptr, nullptr, mp, false,
+                       best_idx, nullptr, nfound, pts->normal ? q.extra.data() : nullptr);
+}
+
+/* ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:353-485): sequential in the points (a
+ * keypoint whose vpMatched entry is set is closed, :437-438) -- M1a in MODE 6, M1b with the rule of the relocalisation
+ * matcher and TH_LOW. */
+int borb_search_by_projection_sim3(borb_extractor *kf, int frame, const borb_fuse_points *pts, const borb_projection *pr,
+                                   const uint8_t *occupied, int th, int32_t *match, int *n_kf, int *nmatches)
+{
+    MatchParams mp;
+    int rc = proj_params(kf, pts, pr, (float)th, MT_TH_LOW, mp);
+    if (rc != BORB_OK) return rc;
+    if (!match) return fail(BORB_ERR_ARG, "null output");
+    if (!pr->Ow || !pts->normal) return fail(BORB_ERR_ARG, "this matcher tests the viewing angle: camera centre and normals");
+    ProjQueries q(pts, 3); /* a query, and it closes the slot it takes */
+    std::vector<uint8_t> occ;
+    if (occupied) {
+        if (!kf->have_plan || kf->last_n < 1 || frame < 0 || frame >= kf->last_n)
+            return fail(BORB_ERR_STATE, "no finished extract call holds frame %d", frame);
+        if (!kf->results_on_host && kf->nout_frame_on_host != frame) {
+            CU(cudaSetDevice(kf->device));
+            CU(cudaMemcpyAsync(kf->h_nout + frame, kf->d_nout + frame, 4, cudaMemcpyDeviceToHost, kf->stream));
+            CU(cudaStreamSynchronize(kf->stream));
+            kf->nout_frame_on_host = frame;
+        }
+        const int nc0 = std::min(kf->h_nout[frame], kf->plan.kp_total);
+        occ.assign((size_t)kf->plan.kp_total, 0);
+        for (int i = 0; i < nc0; ++i) occ[i] = occupied[i] ? 2 : 0;
+    }
+    return run_matcher(kf, frame, 7, pts->n, q.geo.data(), 4, pts->desc, q.qf.data(), q.mind.data(), nullptr,
+                       occupied ? occ.data() : nullptr, mp, false, match, n_kf, nmatches, q.extra.data());
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1262-1501): pKF1's points searched
+ * in pKF2 and pKF2's in pKF1 (two borb_project_search calls, TH_HIGH), then the agreement check (:1484-1498). */
+int borb_search_by_sim3(borb_extractor *kf1, borb_extractor *kf2, const borb_fuse_points *pts1, const borb_fuse_points *pts2,
+                        const float *T1w, const float *T2w, const float *T12, const float *T21, float th, const int32_t *pre12,
+                        int32_t *match12, int *nfound)
+{
+    if (!kf1 || !kf2 || !pts1 || !pts2 || !T1w || !T2w || !T12 || !T21 || !match12) return fail(BORB_ERR_ARG, "null argument");
+    const int n1 = pts1->n, n2 = pts2->n;
+    if (n1 < 0 || n2 < 0) return fail(BORB_ERR_ARG, "point counts");
+    std::vector<uint8_t> f1(pts1->flags, pts1->flags + n1), f2(pts2->flags, pts2->flags + n2);
+    for (int i = 0; i < n1 && pre12; ++i)
+        if (pre12[i] >= 0) { /* vbAlreadyMatched1 / 2 (:1291-1302) */
+            f1[i] |= 4;
+            if (pre12[i] < n2) f2[pre12[i]] |= 4;
+        }
+    borb_fuse_points a = *pts1, b = *pts2;
+    a.flags = f1.data(); a.normal = nullptr;
+    b.flags = f2.data(); b.normal = nullptr;
+    std::vector<int32_t> m1((size_t)std::max(n1, 1)), m2((size_t)std::max(n2, 1));
+    borb_projection p12 = {T1w, T21, nullptr}, p21 = {T2w, T12, nullptr};
+    int rc = borb_project_search(kf2, 0, &a, &p12, th, MT_TH_HIGH, m1.data(), nullptr);
+    if (rc != BORB_OK) return rc;
+    rc = borb_project_search(kf1, 0, &b, &p21, th, MT_TH_HIGH, m2.data(), nullptr);
+    if (rc != BORB_OK) return rc;
+    int nf = 0;
+    for (int i = 0; i < n1; ++i) {
+        match12[i] = pre12 ? pre12[i] : -1;
+        const int idx2 = m1[i];
+        if (idx2 >= 0 && idx2 < n2 && m2[idx2] == i) { match12[i] = idx2; ++nf; }
+    }
+    if (nfound) *nfound = nf;
+    return BORB_OK;
 }
 
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:487-632) */

@@ -59,6 +59,9 @@ struct MatchParams {
     float Ow[3], log_scale;
     int nlevels, orb_dist;
     float inv_sigma2[BORB_MAXL]; /* MODE 5: pKF->mvInvLevelSigma2 for Fuse's chi-square tests */
+    /* MODE 6 (the loop-closing matchers): a second transform applied to the camera-frame point (SearchBySim3), dist3D taken
+     * of the camera-frame point instead of p3Dw - Ow (SearchBySim3), the viewing-angle test on / off */
+    int two_step, cam_norm, use_normal;
 };
 
 __device__ __forceinline__ float mt_dot3(const float *row, const float *x)
@@ -204,6 +207,41 @@ __device__ __forceinline__ MtQuery mt_query(const MatchParams &mp, const float *
         Q.kind = 1;
         Q.inv_s2[0] = lvl > 0 ? mp.inv_sigma2[lvl - 1] : 0.f;
         Q.inv_s2[1] = mp.inv_sigma2[lvl];
+    } else if (MODE == 6) {
+        /* Fuse(pKF, Scw, ...) :1133-1260, SearchByProjection(pKF, Scw, ...) :353-485, one direction of SearchBySim3
+         * :1262-1501 (oracle/match_oracle.cpp: mo_project_search).  Tc = the first transform, Tl the second one. */
+        const float X[3] = {g.x, g.y, g.z};
+        float P[3] = {mt_dot3(mp.Tc, X) + mp.Tc[3], mt_dot3(mp.Tc + 4, X) + mp.Tc[7], mt_dot3(mp.Tc + 8, X) + mp.Tc[11]};
+        if (mp.two_step) {
+            const float P2[3] = {mt_dot3(mp.Tl, P) + mp.Tl[3], mt_dot3(mp.Tl + 4, P) + mp.Tl[7], mt_dot3(mp.Tl + 8, P) + mp.Tl[11]};
+            P[0] = P2[0]; P[1] = P2[1]; P[2] = P2[2];
+        }
+        const float invz = 1.0f / P[2];
+        const float x = P[0] * invz, y = P[1] * invz;
+        Q.u = fmaf(x, mp.fx, mp.cx);
+        Q.v = fmaf(y, mp.fy, mp.cy);
+        Q.ok = !(P[2] < 0.0f) && Q.u >= min_x && Q.u < max_x && Q.v >= min_y && Q.v < max_y;
+        Q.ur = 0.f;
+        double s2 = 0.0, dotn = 0.0;
+        float N[3] = {0.f, 0.f, 0.f};
+        if (mp.use_normal) { const float4 nv = l_extra[i]; N[0] = nv.x; N[1] = nv.y; N[2] = nv.z; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float po = mp.cam_norm ? P[k] : X[k] - mp.Ow[k];
+            s2 = __dadd_rn(s2, __dmul_rn((double)po, (double)po));
+            dotn = __dadd_rn(dotn, __dmul_rn((double)po, (double)N[k]));
+        }
+        const float dist3D = (float)__dsqrt_rn(s2);
+        Q.ok = Q.ok && !(dist3D < 0.8f * __int_as_float(oct) || dist3D > 1.2f * g.w);
+        if (mp.use_normal) Q.ok = Q.ok && !(dotn < __dmul_rn(0.5, (double)dist3D));
+        const float ratio = g.w / dist3D;
+        int lvl = orb_cvtt_x86(ceilf(orb_logf_exact(ratio) / mp.log_scale));
+        if (lvl < 0) lvl = 0;
+        else if (lvl >= mp.nlevels) lvl = mp.nlevels - 1;
+        Q.radius = mp.th * mp.scale[lvl];
+        Q.min_level = lvl - 1;
+        Q.max_level = lvl;
+        Q.kind = 2;
     } else if (MODE == 3) { /* SearchForInitialization: window of windowSize (= mp.th) around vbPrevMatched, level 0 only (:510) */
         Q.radius = mp.th;
         Q.u = g.x;
@@ -340,7 +378,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                 const uint4 *__restrict__ l_desc, const uint8_t *__restrict__ l_flags,
                 const uint32_t *__restrict__ cache, const uint8_t *__restrict__ more,
                 int *__restrict__ choice, int *__restrict__ taker_g, int kp_total, int *__restrict__ match,
-                int *__restrict__ nm, int taker_in_smem)
+                int *__restrict__ nm, int taker_in_smem, const float4 *__restrict__ l_extra = nullptr)
 {
     /* the two taker arrays live in shared memory when they fit (2 x kp_total ints): a round is then three
      * barriers apart instead of three global-memory round trips */
@@ -373,10 +411,11 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
 #pragma unroll
                 for (int k = 0; k < MT_K; ++k) held_by[k] = keys[k] != MT_NOKEY ? tk[keys[k] & 0xffffu] : 0x7fffffff;
             }
-            if (MODE == 1 || MODE == 4) {
-                /* MODE 4: every set slot is closed (:1735-1736; the host sets the "observations" bit of every query) and
+            if (MODE == 1 || MODE == 4 || MODE == 6) {
+                /* MODE 6: SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) -- the rule of MODE 4 with TH_LOW (:437-438, :454).
+                 * MODE 4: every set slot is closed (:1735-1736; the host sets the "observations" bit of every query) and
                  * the acceptance threshold is the caller's ORBdist (:1750) */
-                const uint32_t th_d = MODE == 4 ? (uint32_t)mp.orb_dist : (uint32_t)MT_TH_HIGH;
+                const uint32_t th_d = MODE >= 4 ? (uint32_t)mp.orb_dist : (uint32_t)MT_TH_HIGH;
                 bool all_held = true; /* every cached candidate is held by an earlier query with observations (:1583-1585) */
 #pragma unroll
                 for (int k = 0; k < MT_K; ++k) {
@@ -387,7 +426,7 @@ k_match_resolve(const __grid_constant__ MatchParams mp, const BorbKpRec *__restr
                 }
                 if (all_held && more[i]) { /* rare: walk the cells again, now with the holders known */
                     atomicAdd(&s_rescans, 1);
-                    const MtQuery Q = mt_query<MODE == 4 ? 4 : 1>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv);
+                    const MtQuery Q = mt_query<MODE == 2 ? 1 : MODE>(mp, l_geo, l_octave[i], i, min_x, max_x, min_y, max_y, winv, hinv, l_extra);
                     const uint4 d0 = l_desc[2 * i], d1 = l_desc[2 * i + 1];
                     int best = 256, best_idx = -1;
                     for (int ix = Q.cx0; ix <= Q.cx1; ++ix) {

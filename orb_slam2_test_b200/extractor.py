@@ -62,6 +62,8 @@ SYMBOLS += ["borb_voc_search_by_bow"]
 SYMBOLS += ["borb_voc_search_for_triangulation"]
 # keyframes on the device and the matchers that take one: ORBmatcher::Fuse(pKF, vpMapPoints, th)
 SYMBOLS += ["borb_load_frame", "borb_fuse_search"]
+# the loop-closing matchers: Fuse(pKF, Scw, ...), SearchByProjection(pKF, Scw, ...), SearchBySim3
+SYMBOLS += ["borb_project_search", "borb_search_by_projection_sim3", "borb_search_by_sim3"]
 
 
 class BorbError(RuntimeError):
@@ -142,6 +144,9 @@ def load_library() -> C.CDLL:
     lib.borb_voc_search_for_triangulation.argtypes = [_vp, _vp, _vp, _vp, C.c_uint, _vp, C.POINTER(C.c_int)]
     lib.borb_load_frame.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int]
     lib.borb_fuse_search.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_float, C.c_float, C.c_uint, _vp, C.POINTER(C.c_int)]
+    lib.borb_project_search.argtypes = [_vp, C.c_int, _vp, _vp, C.c_float, C.c_int, _vp, C.POINTER(C.c_int)]
+    lib.borb_search_by_projection_sim3.argtypes = [_vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.borb_search_by_sim3.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_float, _vp, _vp, C.POINTER(C.c_int)]
     lib.borb_debug_logf.argtypes = [_vp, _vp, C.c_int]
     lib.borb_debug_logf.restype = None
     lib.borb_debug_logf_device.argtypes = [_vp, _vp, C.c_int]
@@ -198,6 +203,25 @@ class _MapPoints(C.Structure):  # == borb_map_points
 class _LastFrame(C.Structure):  # == borb_last_frame
     _fields_ = [("n", C.c_int), ("xyz", _vp), ("desc", _vp), ("flags", _vp), ("octave", _vp), ("angle", _vp),
                 ("Tcw", _vp)]
+
+
+class _Projection(C.Structure):  # == borb_projection
+    _fields_ = [("T1", _vp), ("T2", _vp), ("Ow", _vp)]
+
+
+def _fuse_points(pts: dict, keep: list) -> "_FusePoints":
+    a = [np.ascontiguousarray(pts["xyz"], np.float32), np.ascontiguousarray(pts["desc"], np.uint8),
+         np.ascontiguousarray(pts["flags"], np.uint8), np.ascontiguousarray(pts["dist"], np.float32)]
+    nrm = np.ascontiguousarray(pts["normal"], np.float32) if pts.get("normal") is not None else None
+    keep += a + [nrm]
+    return _FusePoints(len(a[2]), a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data, a[3].ctypes.data,
+                       nrm.ctypes.data if nrm is not None else None)
+
+
+def _projection(T1, T2, Ow, keep: list) -> "_Projection":
+    a = [np.ascontiguousarray(x, np.float32) if x is not None else None for x in (T1, T2, Ow)]
+    keep += a
+    return _Projection(*[x.ctypes.data if x is not None else None for x in a])
 
 
 class _FusePoints(C.Structure):  # == borb_fuse_points
@@ -634,6 +658,46 @@ class ORBextractor:
         _check(self._lib, self._lib.borb_fuse_search(self._h, frame, C.addressof(rec), T.ctypes.data, O.ctypes.data, bf, th,
                                                      4 if use_stereo else 0, out.ctypes.data, C.byref(nf)))
         return out[:rec.n].copy(), nf.value
+
+    def project_search(self, pts: dict, T1, T2=None, Ow=None, th: float = 4.0, max_dist: int = 50, frame: int = 0):
+        """The search of ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1133-1260) or one direction
+        of SearchBySim3 (:1262-1501) with this handle's frame (load_frame) as the keyframe.  pts: flags, xyz, desc, dist,
+        normal (None = no viewing-angle test); T1 / T2 / Ow as include/borb.h: borb_projection.
+        -> (best [n] i32: keypoint per point or -1, number found)."""
+        keep = []
+        rec, pr = _fuse_points(pts, keep), _projection(T1, T2, Ow, keep)
+        out = np.full(max(rec.n, 1), -1, np.int32)
+        nf = C.c_int()
+        _check(self._lib, self._lib.borb_project_search(self._h, frame, C.addressof(rec), C.addressof(pr), th, max_dist,
+                                                        out.ctypes.data, C.byref(nf)))
+        return out[:rec.n].copy(), nf.value
+
+    def search_by_projection_sim3(self, pts: dict, T, Ow, occupied=None, th: int = 10, frame: int = 0):
+        """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:353-485), this handle's frame as
+        pKF.  T = [Rcw | tcw], Ow as the reference derives them from Scw.  -> (match [n_kf] i32: point put into vpMatched[idx]
+        or -1, nmatches)."""
+        keep = []
+        rec, pr = _fuse_points(pts, keep), _projection(T, None, Ow, keep)
+        occ = np.ascontiguousarray(occupied, np.uint8) if occupied is not None else None
+        out = np.full(max(self._lib.borb_max_keypoints(self._h), 1), -1, np.int32)
+        n, nm = C.c_int(), C.c_int()
+        _check(self._lib, self._lib.borb_search_by_projection_sim3(self._h, frame, C.addressof(rec), C.addressof(pr),
+                                                                   occ.ctypes.data if occ is not None else None, int(th),
+                                                                   out.ctypes.data, C.byref(n), C.byref(nm)))
+        return out[:n.value].copy(), nm.value
+
+    def search_by_sim3(self, other: "ORBextractor", pts1: dict, pts2: dict, T1w, T2w, T12, T21, th: float = 7.5, pre12=None):
+        """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1262-1501): self holds pKF1, other pKF2 (load_frame).
+        -> (vpMatches12 as pKF2 keypoint indices [n1] i32, nFound)."""
+        keep = []
+        a, b = _fuse_points(dict(pts1, normal=None), keep), _fuse_points(dict(pts2, normal=None), keep)
+        mats = [np.ascontiguousarray(x, np.float32) for x in (T1w, T2w, T12, T21)]
+        pre = np.ascontiguousarray(pre12, np.int32) if pre12 is not None else None
+        out = np.full(max(a.n, 1), -1, np.int32)
+        nf = C.c_int()
+        _check(self._lib, self._lib.borb_search_by_sim3(self._h, other._h, C.addressof(a), C.addressof(b), *[m.ctypes.data for m in mats],
+                                                        th, pre.ctypes.data if pre is not None else None, out.ctypes.data, C.byref(nf)))
+        return out[:a.n].copy(), nf.value
 
     def search_by_projection_keyframe(self, kf: dict, Tcw_cur, occupied=None, th: float = 10.0, orb_dist: int = 100,
                                       frame: int = 0, check_orientation: bool = True):

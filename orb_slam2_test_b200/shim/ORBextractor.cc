@@ -263,6 +263,78 @@ int ORBextractor::FuseSearch(const cv::Mat &Tcw, const cv::Mat &Ow, float bf, in
     return nfused;
 }
 
+namespace {
+void rt34(const cv::Mat &R, const cv::Mat &t, float *T) /* [R | t], 3 x 4 row-major */
+{
+    assert(R.rows == 3 && R.cols == 3 && R.type() == CV_32F && t.rows == 3 && t.cols == 1 && t.type() == CV_32F);
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) T[4 * r + c] = R.at<float>(r, c);
+        T[4 * r + 3] = t.at<float>(r, 0);
+    }
+}
+void pose34(const cv::Mat &Tcw, float *T)
+{
+    assert(Tcw.rows == 4 && Tcw.cols == 4 && Tcw.type() == CV_32F);
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) T[4 * r + c] = Tcw.at<float>(r, c);
+}
+} // namespace
+
+int ORBextractor::FuseSim3Search(const cv::Mat &Rcw, const cv::Mat &tcw, const cv::Mat &Ow, int nPoints, const float *worldPos,
+                                 const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
+                                 const float *normals, float th, std::vector<int> &vnBestIdx)
+{
+    float T[12], ow[3] = {Ow.at<float>(0, 0), Ow.at<float>(1, 0), Ow.at<float>(2, 0)};
+    rt34(Rcw, tcw, T);
+    borb_fuse_points pts;
+    pts.n = nPoints; pts.xyz = worldPos; pts.desc = mpDescriptors; pts.flags = flags; pts.dist = minMaxDistance; pts.normal = normals;
+    borb_projection pr;
+    pr.T1 = T; pr.T2 = NULL; pr.Ow = ow;
+    vnBestIdx.assign((size_t)std::max(nPoints, 0), -1);
+    int nf = 0;
+    check(borb_project_search(handle, 0, &pts, &pr, th, 50 /* TH_LOW */, vnBestIdx.data(), &nf), "fuse (Sim3) search");
+    return nf;
+}
+
+int ORBextractor::SearchByProjectionSim3(const cv::Mat &Rcw, const cv::Mat &tcw, const cv::Mat &Ow, int nPoints, const float *worldPos,
+                                         const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
+                                         const float *normals, const unsigned char *occupied, int th, std::vector<int> &vnMatches)
+{
+    float T[12], ow[3] = {Ow.at<float>(0, 0), Ow.at<float>(1, 0), Ow.at<float>(2, 0)};
+    rt34(Rcw, tcw, T);
+    borb_fuse_points pts;
+    pts.n = nPoints; pts.xyz = worldPos; pts.desc = mpDescriptors; pts.flags = flags; pts.dist = minMaxDistance; pts.normal = normals;
+    borb_projection pr;
+    pr.T1 = T; pr.T2 = NULL; pr.Ow = ow;
+    vnMatches.assign((size_t)borb_max_keypoints(handle), -1);
+    int n = 0, nm = 0;
+    check(borb_search_by_projection_sim3(handle, 0, &pts, &pr, occupied, th, vnMatches.data(), &n, &nm), "search by projection (Sim3)");
+    vnMatches.resize((size_t)n);
+    return nm;
+}
+
+int ORBextractor::SearchBySim3(ORBextractor &kf2, const cv::Mat &T1w, const cv::Mat &T2w, const cv::Mat &sR12, const cv::Mat &t12,
+                               const cv::Mat &sR21, const cv::Mat &t21, int n1, const float *worldPos1, const unsigned char *desc1,
+                               const unsigned char *flags1, const float *minMaxDistance1, int n2, const float *worldPos2,
+                               const unsigned char *desc2, const unsigned char *flags2, const float *minMaxDistance2, float th,
+                               std::vector<int> &vnMatches12)
+{
+    float a[12], b[12], t12m[12], t21m[12];
+    pose34(T1w, a);
+    pose34(T2w, b);
+    rt34(sR12, t12, t12m);
+    rt34(sR21, t21, t21m);
+    borb_fuse_points p1, p2;
+    p1.n = n1; p1.xyz = worldPos1; p1.desc = desc1; p1.flags = flags1; p1.dist = minMaxDistance1; p1.normal = NULL;
+    p2.n = n2; p2.xyz = worldPos2; p2.desc = desc2; p2.flags = flags2; p2.dist = minMaxDistance2; p2.normal = NULL;
+    std::vector<int> pre(vnMatches12);
+    pre.resize((size_t)std::max(n1, 0), -1);
+    vnMatches12.assign((size_t)std::max(n1, 0), -1);
+    int nf = 0;
+    check(borb_search_by_sim3(handle, kf2.handle, &p1, &p2, a, b, t12m, t21m, th, pre.data(), vnMatches12.data(), &nf), "search by Sim3");
+    return nf;
+}
+
 int ORBextractor::SearchForInitialization(const std::vector<cv::KeyPoint> &F1KeysUn, const cv::Mat &F1Descriptors,
                                           std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12,
                                           int windowSize, float nnRatio, bool checkOrientation)

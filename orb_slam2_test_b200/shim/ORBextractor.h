@@ -196,6 +196,28 @@ public:
     int FuseSearch(const cv::Mat &Tcw, const cv::Mat &Ow, float bf, int nPoints, const float *worldPos,
                    const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
                    const float *normals, float th, bool useStereo, std::vector<int> &vnBestIdx);
+    // The loop-closing matchers (reference src/ORBmatcher.cc; LoopClosing::ComputeSim3 / SearchAndFuse), *this = the keyframe
+    // after LoadKeyFrame.  Points as FuseSearch's (flags bit 0 = an entry, bit 1 = isBad(), bit 2 = already found); the
+    // matrices are the caller's cv::Mat results, exactly as the reference derives them: Rcw = sRcw / scw, tcw = Scw.col(3) /
+    // scw, Ow = -Rcw.t() * tcw (:360-365, :1140-1146); sR12, sR21, t21 (:1279-1281).
+    //   FuseSim3Search: the search of Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1133-1260): vnBestIdx[i] = the keypoint
+    //   handed to pKF->GetMapPoint (:1242) or -1; the caller runs :1240-1256 per i.
+    int FuseSim3Search(const cv::Mat &Rcw, const cv::Mat &tcw, const cv::Mat &Ow, int nPoints, const float *worldPos,
+                       const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
+                       const float *normals, float th, std::vector<int> &vnBestIdx);
+    //   SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:353-485): occupied[idx] != 0 where vpMatched[idx] is set on
+    //   entry (may be NULL); vnMatches[idx] = the point put into vpMatched[idx] by this call or -1; returns nmatches.
+    int SearchByProjectionSim3(const cv::Mat &Rcw, const cv::Mat &tcw, const cv::Mat &Ow, int nPoints, const float *worldPos,
+                               const unsigned char *mpDescriptors, const unsigned char *flags, const float *minMaxDistance,
+                               const float *normals, const unsigned char *occupied, int th, std::vector<int> &vnMatches);
+    //   SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (:1262-1501): *this = pKF1, kf2 = pKF2 (both loaded);
+    //   points i = GetMapPointMatches()[i] of either keyframe; T1w / T2w = the poses (4x4); sR12, t12, sR21, t21 as :1279-1281;
+    //   vnMatches12 in/out = vpMatches12 as pKF2 keypoint indices (-1 = NULL); returns nFound.
+    int SearchBySim3(ORBextractor &kf2, const cv::Mat &T1w, const cv::Mat &T2w, const cv::Mat &sR12, const cv::Mat &t12,
+                     const cv::Mat &sR21, const cv::Mat &t21, int n1, const float *worldPos1, const unsigned char *desc1,
+                     const unsigned char *flags1, const float *minMaxDistance1, int n2, const float *worldPos2,
+                     const unsigned char *desc2, const unsigned char *flags2, const float *minMaxDistance2, float th,
+                     std::vector<int> &vnMatches12);
     // ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (reference
     // src/ORBmatcher.cc:487-632, Tracking::MonocularInitialization) on the device, *this = F2's extractor after its
     // operator() call (SetCamera on).  F1 arrives as its mvKeysUn (octave, angle) and descriptors (CV_8U, n x 32).

@@ -360,3 +360,57 @@ def test_fuse_search_monocular_distorted_keyframe(oracle_built):
     """the keyframe's bounds are the frame's float bounds truncated to int"""
     assert _check_fuse("fuse tum", oracle_built, seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D,
                        bf=40.0, stereo=False, nf=1000, dist_jitter=0.4) > 300
+
+
+# ---- LoopClosing's matchers on the device: Fuse(pKF, Scw, ...) :1133-1260, SearchByProjection(pKF, Scw, ...) :353-485,
+# ---- SearchBySim3 :1262-1501 ----
+
+def _loaded(kf, shape, K, dist, nf):
+    from orb_slam2_test_b200 import ORBextractor
+    h = ORBextractor(nf, 1.2, 8, 20, 7)
+    h.set_camera(K, dist)
+    h.load_frame(kf["kps"], kf["desc"], shape[1], shape[0])
+    return h
+
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, s=0.97, dz=0.3), dict(seed=4, copies=3),
+                                dict(seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0,
+                                     stereo=False, nf=1000, dist_jitter=0.4)])
+def test_fuse_sim3_and_projection_sim3_on_the_device(kw, oracle_built):
+    kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occupied = matchcase.make_sim3_points_case(**kw)
+    h = _loaded(kf, kw.get("shape", synth.KITTI_SHAPE), kw.get("K", matchcase.KITTI_K), kw.get("dist", (0.0, 0.0, 0.0, 0.0)),
+                kw.get("nf", 2000))
+    T, Ow = oracle_built.sim3_decompose(Scw)
+    total = 0
+    for th in (4.0, 10.0):
+        want, wnf = oracle_built.fuse_sim3(kf, cam, bounds, scale, log_scale, Scw, pts, th)
+        got, nf = h.project_search(pts, T, None, Ow, th, 50)
+        bad = np.nonzero(got != want)[0]
+        assert bad.size == 0 and nf == wnf, f"fuse sim3 th={th}: {bad.size} differ, e.g. {bad[:5]}: {got[bad[:5]]} vs {want[bad[:5]]}"
+        total += nf
+        for occ in (occupied, None):
+            p = pts if occ is not None else dict(pts, flags=(pts["flags"] & 3).astype(np.uint8))
+            want, wnm = oracle_built.search_by_projection_kf_sim3(kf, cam, bounds, scale, log_scale, Scw, p, occ, int(th))
+            got, nm = h.search_by_projection_sim3(p, T, Ow, occ, int(th))
+            bad = np.nonzero(got != want)[0]
+            assert bad.size == 0 and nm == wnm, f"projection sim3 th={th}: {bad.size} differ, nm {nm} vs {wnm}"
+            total += nm
+    assert total > 300
+
+
+@pytest.mark.parametrize("kw", [dict(seed=1), dict(seed=2, s12=0.96, dz=0.3), dict(seed=3, dz=-0.3, pre_rate=0.3),
+                                dict(seed=5, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0,
+                                     stereo=False, nf=1000, dist_jitter=0.4)])
+def test_search_by_sim3_on_the_device(kw, oracle_built):
+    k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12 = matchcase.make_sim3_pair_case(**kw)
+    args = (kw.get("shape", synth.KITTI_SHAPE), kw.get("K", matchcase.KITTI_K), kw.get("dist", (0.0, 0.0, 0.0, 0.0)), kw.get("nf", 2000))
+    h1, h2 = _loaded(k1, *args), _loaded(k2, *args)
+    T12, T21 = oracle_built.sim3_relative(s12, R12, t12)
+    total = 0
+    for th in (7.5, 3.0):
+        want, wnf = oracle_built.search_by_sim3(k1, k2, cam, bounds, scale, log_scale, p1, p2, pre12, s12, R12, t12, th)
+        got, nf = h1.search_by_sim3(h2, p1, p2, k1["Tcw"], k2["Tcw"], T12, T21, th, pre12)
+        bad = np.nonzero(got != want)[0]
+        assert bad.size == 0 and nf == wnf, f"sim3 th={th}: {bad.size} differ, nFound {nf} vs {wnf}"
+        total += nf
+    assert total > 100
