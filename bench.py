@@ -606,6 +606,47 @@ def matcher_section(ORBextractor, synth, local):
         out["relocalisation"] = rel
     except Exception as ex:
         out["relocalisation"] = f"unavailable ({type(ex).__name__}: {ex})"
+    # the matchers of the back-end threads that project map points into a KEYFRAME (loaded into a handle with
+    # borb_load_frame): Fuse(pKF, vpMapPoints, th) of LocalMapping::SearchInNeighbors and SearchBySim3 of LoopClosing
+    try:
+        from oracle import pyoracle
+
+        def timed(fn, reps):
+            for _ in range(max(2, reps // 10)):
+                r = fn()
+            ts = []
+            for _ in range(reps):
+                t1 = time.perf_counter()
+                r = fn()
+                ts.append((time.perf_counter() - t1) * 1e6)
+            return r, float(np.percentile(ts, 50))
+        kf_, cam_, bounds_, scale_, inv_s2, log_s, mps_ = matchcase.make_fuse_case(seed=74)
+        hk = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        hk.set_camera(K, (0.0, 0.0, 0.0, 0.0))
+        _, t_load = timed(lambda: hk.load_frame(kf_["kps"], kf_["desc"], COLS, ROWS, kf_["u_right"]), 50)
+        Ow_ = pyoracle.camera_centre(kf_["Tcw"])
+        (b_, nf_), t_gpu = timed(lambda: hk.fuse_search(mps_, kf_["Tcw"], Ow_, float(cam_[4]), 3.0, use_stereo=True), 100)
+        (w_, wnf_), t_cpu = timed(lambda: pyoracle.fuse(kf_, cam_, bounds_, scale_, inv_s2, log_s, mps_, 3.0), 10)
+        out["fuse"] = {"reference": "src/ORBmatcher.cc:968-1131 (LocalMapping::SearchInNeighbors): the search; the map update stays with the caller",
+                       "config": "%d map points into a stereo keyframe of %d keypoints" % (int((mps_["flags"] & 1).sum()), len(kf_["kps"])),
+                       "load_keyframe_p50_us": t_load, "call_p50_us": t_gpu, "nfused": int(nf_), "cpu_p50_us_one_core": t_cpu,
+                       "parity_check": "identical" if (np.array_equal(b_, w_) and nf_ == wnf_) else "MISMATCH"}
+        k1_, k2_, cam_, bounds_, scale_, inv_s2, log_s, p1_, p2_, pre_, s12_, R12_, t12_ = matchcase.make_sim3_pair_case(seed=75)
+        h1_ = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        h2_ = ORBextractor(NFEATURES, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+        for h_, k_ in ((h1_, k1_), (h2_, k2_)):
+            h_.set_camera(K, (0.0, 0.0, 0.0, 0.0))
+            h_.load_frame(k_["kps"], k_["desc"], COLS, ROWS)
+        T12_, T21_ = pyoracle.sim3_relative(s12_, R12_, t12_)
+        (m_, nf_), t_gpu = timed(lambda: h1_.search_by_sim3(h2_, p1_, p2_, k1_["Tcw"], k2_["Tcw"], T12_, T21_, 7.5, pre_), 100)
+        (w_, wnf_), t_cpu = timed(lambda: pyoracle.search_by_sim3(k1_, k2_, cam_, bounds_, scale_, log_s, p1_, p2_, pre_, s12_, R12_, t12_, 7.5), 10)
+        out["search_by_sim3"] = {"reference": "src/ORBmatcher.cc:1262-1501 (LoopClosing::ComputeSim3)", "call_p50_us": t_gpu,
+                                 "nfound": int(nf_), "cpu_p50_us_one_core": t_cpu,
+                                 "parity_check": "identical" if (np.array_equal(m_, w_) and nf_ == wnf_) else "MISMATCH"}
+        for h_ in (hk, h1_, h2_):
+            h_.close()
+    except Exception as ex:
+        out["keyframe_matchers"] = f"unavailable ({type(ex).__name__}: {ex})"
     # the whole per-frame front end of the tracking thread for a stereo frame, as one sequence through the host ABI:
     # both eyes extracted on two threads (+ undistortion / grid), stereo association, frame-to-frame matcher,
     # local-map matcher -- the current frame's keypoints, descriptors, grid and mvuRight never leave the device
@@ -757,6 +798,47 @@ def bow_section(ORBextractor, synth, local):
             out["search_by_bow_100_nodes"]["parity_check"] = "identical" if (np.array_equal(m3, w3) and nm3 == wnm3) else "MISMATCH"
         except Exception as ex:
             out["parity_check"] = f"unavailable ({type(ex).__name__}: {ex})"
+        # the back-end threads' bag-of-words matchers between two keyframes (both sides uploaded): SearchByBoW(pKF1, pKF2)
+        # of LoopClosing::ComputeSim3 and SearchForTriangulation of LocalMapping::CreateNewMapPoints
+        try:
+            from oracle import pyoracle
+            sys.path.insert(0, str(ROOT / "tests"))
+            import bowcase
+            want = pyoracle.BowVocabulary(path)
+            mp2 = (rng.random(len(fk)) < 0.7).astype(np.uint8)
+            kf1 = {"desc": kd, "angle": kk["angle"], "mp_flags": mp, "fv": voc.transform(kd, 3)}
+            kf2 = {"desc": fd, "angle": fk["angle"], "mp_flags": mp2, "fv": voc.transform(fd, 3)}
+            fv1, fv2 = want.transform(kd, 3), want.transform(fd, 3)
+
+            def timed(fn, reps):
+                for _ in range(max(2, reps // 10)):
+                    r = fn()
+                ts = []
+                for _ in range(reps):
+                    t1 = time.perf_counter()
+                    r = fn()
+                    ts.append((time.perf_counter() - t1) * 1e6)
+                return r, float(np.percentile(ts, 50))
+            (m, nm), t_gpu = timed(lambda: voc.search_by_bow(kf1, kf2, 0.75), 100)
+            (w, wnm), t_cpu = timed(lambda: want.search_by_bow_kf(kk, kd, mp, fk, fd, mp2, 0.75, True, fv1=fv1, fv2=fv2), 10)
+            out["search_by_bow_keyframes"] = {"reference": "src/ORBmatcher.cc:634-777", "call_p50_us": t_gpu, "nmatches": int(nm),
+                                              "cpu_p50_us_one_core": t_cpu, "nodes": int(len(fv1["node_id"])),
+                                              "parity_check": "identical" if (np.array_equal(m, w) and nm == wnm) else "MISMATCH"}
+            a, b, geo = bowcase.triangulation_case(shape=(ROWS, COLS), seed=81, t=0, nf=NFEATURES, baseline=(0.3, 0.0, 0.05),
+                                                   K=(718.856, 718.856, 607.1928, 185.2157), has=0.6)
+            t1_ = {"desc": a["desc"], "angle": a["kps"]["angle"], "mp_flags": a["mp"], "fv": voc.transform(a["desc"], 3),
+                   "xy": np.stack([a["kps"]["x"], a["kps"]["y"]], 1).astype(np.float32), "octave": a["kps"]["octave"].astype(np.int32)}
+            t2_ = {"desc": b["desc"], "angle": b["kps"]["angle"], "mp_flags": b["mp"], "fv": voc.transform(b["desc"], 3),
+                   "xy": np.stack([b["kps"]["x"], b["kps"]["y"]], 1).astype(np.float32), "octave": b["kps"]["octave"].astype(np.int32)}
+            g = dict(geo, Ow1=pyoracle.camera_centre(a["Tcw"]), Tcw2=b["Tcw"])
+            f1_, f2_ = want.transform(a["desc"], 3), want.transform(b["desc"], 3)
+            (m, nm), t_gpu = timed(lambda: voc.search_for_triangulation(t1_, t2_, g), 100)
+            (w, wnm), t_cpu = timed(lambda: want.search_for_triangulation(a, b, geo, False, True, fv1=f1_, fv2=f2_), 10)
+            out["search_for_triangulation"] = {"reference": "src/ORBmatcher.cc:779-966 (+ CheckDistEpipolarLine :165-182)",
+                                               "call_p50_us": t_gpu, "nmatches": int(nm), "cpu_p50_us_one_core": t_cpu,
+                                               "parity_check": "identical" if (np.array_equal(m, w) and nm == wnm) else "MISMATCH"}
+        except Exception as ex:
+            out["keyframe_matchers"] = f"unavailable ({type(ex).__name__}: {ex})"
         ext.close()
         voc.close()
     return out

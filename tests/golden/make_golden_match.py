@@ -60,8 +60,50 @@ RELOC_CASES = {
 }
 
 
+# name -> make_fuse_case kwargs: ORBmatcher::Fuse(pKF, vpMapPoints, th), th 3 and 6
+FUSE_CASES = {
+    "fuse_kitti": dict(seed=26),
+    "fuse_kitti_crowded": dict(seed=27, copies=3),
+    "fuse_tum_mono": dict(seed=28, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False, nf=1000,
+                          dist_jitter=0.4),
+}
+# name -> make_sim3_points_case kwargs: Fuse(pKF, Scw, ...) and SearchByProjection(pKF, Scw, ...), th 4 and 10
+SIM3_POINT_CASES = {
+    "sim3pts_kitti": dict(seed=29),
+    "sim3pts_tum_mono": dict(seed=30, s=0.97, shape=synth.TUM_SHAPE, K=matchcase.TUM1_K, dist=matchcase.TUM1_D, bf=40.0, stereo=False,
+                             nf=1000, dist_jitter=0.4),
+}
+# name -> make_sim3_pair_case kwargs: SearchBySim3, th 7.5
+SIM3_PAIR_CASES = {
+    "sim3pair_kitti": dict(seed=31),
+    "sim3pair_kitti_prematched": dict(seed=32, s12=0.96, dz=0.3, pre_rate=0.3),
+}
+
+
 def main():
     out = {}
+    for name, kw in FUSE_CASES.items():
+        kf, cam, bounds, scale, inv_sigma2, log_scale, mps = matchcase.make_fuse_case(**kw)
+        for th in (3.0, 6.0):
+            b, nf = RefMatcher.fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
+            out[f"{name}_th{int(th)}_best"] = b
+            out[f"{name}_th{int(th)}_nm"] = np.array([nf, len(mps["flags"])], np.int32)
+            print(name, th, "nFused", nf)
+    for name, kw in SIM3_POINT_CASES.items():
+        kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occ = matchcase.make_sim3_points_case(**kw)
+        for th in (4, 10):
+            b, nf = RefMatcher.fuse_sim3(kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, float(th))
+            m, nm = RefMatcher.search_by_projection_kf_sim3(kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occ, th)
+            out[f"{name}_th{th}_best"] = b
+            out[f"{name}_th{th}_match"] = m
+            out[f"{name}_th{th}_nm"] = np.array([nf, nm, len(pts["flags"])], np.int32)
+            print(name, th, "nFused", nf, "nmatches", nm)
+    for name, kw in SIM3_PAIR_CASES.items():
+        k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12 = matchcase.make_sim3_pair_case(**kw)
+        m, nf = RefMatcher.search_by_sim3(k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12, 7.5)
+        out[f"{name}_match"] = m
+        out[f"{name}_nm"] = np.array([nf, len(p1["flags"])], np.int32)
+        print(name, "nFound", nf)
     for name, (kw, settings) in RELOC_CASES.items():
         cur, cam, bounds, scale, log_scale, kf, occ = matchcase.make_reloc_case(**kw)
         for th, od in settings:

@@ -11,7 +11,8 @@ import matchcase
 
 HERE = Path(__file__).resolve().parent
 sys.path.insert(0, str(HERE / "golden"))
-from make_golden_match import CASES, INIT_CASES, LOCAL_CASES, RELOC_CASES  # noqa: E402
+from make_golden_match import (CASES, FUSE_CASES, INIT_CASES, LOCAL_CASES, RELOC_CASES, SIM3_PAIR_CASES,  # noqa: E402
+                               SIM3_POINT_CASES)
 
 
 def _golden():
@@ -151,3 +152,68 @@ def test_cuda_reproduces_the_reference_relocalisation_matcher(name, oracle_built
             m, nm = ext.search_by_projection_keyframe(kf, cur["Tcw"], occ, th, od, check_orientation=bool(ori))
             key = f"{name}_th{int(th)}_d{od}_ori{ori}"
             assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][0], key
+
+
+def _loaded_keyframe(kf, kw):
+    from orb_slam2_test_b200 import ORBextractor, synth
+    shape = kw.get("shape", synth.KITTI_SHAPE)
+    h = ORBextractor(kw.get("nf", 2000), 1.2, 8, 20, 7)
+    h.set_camera(kw.get("K", matchcase.KITTI_K), kw.get("dist", (0.0, 0.0, 0.0, 0.0)))
+    h.load_frame(kf["kps"], kf["desc"], shape[1], shape[0], kf["u_right"] if kw.get("stereo", True) else None)
+    return h
+
+
+@pytest.mark.parametrize("name", sorted(FUSE_CASES))
+@pytest.mark.parametrize("cuda", [False, pytest.param(True, marks=pytest.mark.gpu)])
+def test_the_reference_fuse_search_is_reproduced(name, cuda, oracle_built):
+    g = _golden()
+    kw = FUSE_CASES[name]
+    kf, cam, bounds, scale, inv_sigma2, log_scale, mps = matchcase.make_fuse_case(**kw)
+    h = _loaded_keyframe(kf, kw) if cuda else None
+    for th in (3.0, 6.0):
+        key = f"{name}_th{int(th)}"
+        assert len(mps["flags"]) == g[key + "_nm"][1], "the scenario is not the one the golden file was made from"
+        if cuda:
+            b, nf = h.fuse_search(mps, kf["Tcw"], oracle_built.camera_centre(kf["Tcw"]), float(cam[4]), th,
+                                  use_stereo=kw.get("stereo", True))
+        else:
+            b, nf = oracle_built.fuse(kf, cam, bounds, scale, inv_sigma2, log_scale, mps, th)
+        assert np.array_equal(b, g[key + "_best"]) and nf == g[key + "_nm"][0], key
+
+
+@pytest.mark.parametrize("name", sorted(SIM3_POINT_CASES))
+@pytest.mark.parametrize("cuda", [False, pytest.param(True, marks=pytest.mark.gpu)])
+def test_the_reference_sim3_point_matchers_are_reproduced(name, cuda, oracle_built):
+    g = _golden()
+    kw = SIM3_POINT_CASES[name]
+    kf, cam, bounds, scale, inv_sigma2, log_scale, Scw, pts, occ = matchcase.make_sim3_points_case(**kw)
+    h = _loaded_keyframe(dict(kf, u_right=None), dict(kw, stereo=False)) if cuda else None
+    T, Ow = oracle_built.sim3_decompose(Scw)
+    for th in (4, 10):
+        key = f"{name}_th{th}"
+        assert len(pts["flags"]) == g[key + "_nm"][2], "the scenario is not the one the golden file was made from"
+        if cuda:
+            b, nf = h.project_search(pts, T, None, Ow, float(th), 50)
+            m, nm = h.search_by_projection_sim3(pts, T, Ow, occ, th)
+        else:
+            b, nf = oracle_built.fuse_sim3(kf, cam, bounds, scale, log_scale, Scw, pts, float(th))
+            m, nm = oracle_built.search_by_projection_kf_sim3(kf, cam, bounds, scale, log_scale, Scw, pts, occ, th)
+        assert np.array_equal(b, g[key + "_best"]) and nf == g[key + "_nm"][0], key
+        assert np.array_equal(m, g[key + "_match"]) and nm == g[key + "_nm"][1], key
+
+
+@pytest.mark.parametrize("name", sorted(SIM3_PAIR_CASES))
+@pytest.mark.parametrize("cuda", [False, pytest.param(True, marks=pytest.mark.gpu)])
+def test_the_reference_search_by_sim3_is_reproduced(name, cuda, oracle_built):
+    g = _golden()
+    kw = SIM3_PAIR_CASES[name]
+    k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12 = matchcase.make_sim3_pair_case(**kw)
+    assert len(p1["flags"]) == g[name + "_nm"][1], "the scenario is not the one the golden file was made from"
+    if cuda:
+        h1 = _loaded_keyframe(dict(k1, u_right=None), dict(kw, stereo=False))
+        h2 = _loaded_keyframe(dict(k2, u_right=None), dict(kw, stereo=False))
+        T12, T21 = oracle_built.sim3_relative(s12, R12, t12)
+        m, nf = h1.search_by_sim3(h2, p1, p2, k1["Tcw"], k2["Tcw"], T12, T21, 7.5, pre12)
+    else:
+        m, nf = oracle_built.search_by_sim3(k1, k2, cam, bounds, scale, log_scale, p1, p2, pre12, s12, R12, t12, 7.5)
+    assert np.array_equal(m, g[name + "_match"]) and nf == g[name + "_nm"][0], name
