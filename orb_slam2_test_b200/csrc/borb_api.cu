@@ -129,6 +129,8 @@ struct borb_extractor {
     cudaStream_t stream2 = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int pyr_sp[BORB_MAXL] = {}, pyr_srows[BORB_MAXL] = {}; /* staged source tile of K1: pitch, rows */
+    int pyr_yinv_off[BORB_MAXL] = {};  /* k_pyr_stream: per source row the output row that ends there (uint2 pairs inside tab_i) */
+    bool pyr_stream[BORB_MAXL] = {};   /* the level meets k_pyr_stream's preconditions */
     /* single-launch level chain of the latency shape (k_pyr_chain): per (tile, level) rectangles, shared-memory layout */
     PyrChainTile *d_chain = nullptr;
     uint2 *d_chain_tabs = nullptr;
@@ -484,6 +486,26 @@ int build_plan(borb_extractor *h, int cols, int rows)
             }
             h->pyr_sp[l] = (int)align_up(span_x + 16, 16);
             h->pyr_srows[l] = span_y + 1;
+            {   /* k_pyr_stream (source-row driven): an output row d must blend source rows yofs[d], yofs[d] + 1 with yofs
+                 * strictly increasing and inside the source (true for every level scale > 1), and the staged window must
+                 * fit the kernel's fixed pitch; else the level keeps k_pyr_resize */
+                bool ok = h->pyr_sp[l] <= PYR_SP_MAX && L.h >= 2 && S.h >= 2;
+                for (int d = 0; d < L.h && ok; ++d) {
+                    const int sy = tab_i[L.yofs_off + d];
+                    ok = sy >= 0 && sy + 1 <= S.h - 1 && (d == 0 || sy > tab_i[L.yofs_off + d - 1]);
+                }
+                h->pyr_stream[l] = ok;
+                if (tab_i.size() & 1) tab_i.push_back(0); /* uint2 alignment */
+                h->pyr_yinv_off[l] = (int)tab_i.size();
+                tab_i.resize(tab_i.size() + 2 * (size_t)S.h, -1);
+                if (ok)
+                    for (int d = 0; d < L.h; ++d) {
+                        const int s1 = tab_i[L.yofs_off + d] + 1;
+                        tab_i[h->pyr_yinv_off[l] + 2 * s1] = d;
+                        tab_i[h->pyr_yinv_off[l] + 2 * s1 + 1] = (int)((uint32_t)(uint16_t)tab_s[L.yb_off + 2 * d] |
+                                                                       ((uint32_t)(uint16_t)tab_s[L.yb_off + 2 * d + 1] << 16));
+                    }
+            }
             if ((long long)2 * h->pyr_sp[l] * h->pyr_srows[l] > 48 * 1024)
                 return fail(BORB_ERR_GEOMETRY, "scale factor too large for the pyramid tile at level %d", l);
         }
@@ -737,6 +759,7 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         STAGE(6); /* K0 = evs[0] .. evs[6]; the pyramid stage time includes it */
     }
     static const bool chain_off = getenv("BORB_PYR_LEVELS") != nullptr; /* A/B knob: per-level kernels in every shape */
+    static const bool pyr_stream_off = getenv("BORB_PYR_RESIZE_V3") != nullptr; /* A/B knob: k_pyr_resize instead of k_pyr_stream */
     const bool chain = !chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm;
     h->last_launches = (chain ? 1 : P.nlevels + 1) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
     if (chain) {
@@ -751,6 +774,12 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         k_pyr_level0<false><<<dim3((L0.prows + 127) / 128, units - n_int, n), dim3(32, 4), 0, st>>>(h->plan, dev_img, step, stride, d_pyr);
         for (int l = 1; l < P.nlevels; ++l) {
             const BorbLevel &L = P.lv[l];
+            if (h->pyr_stream[l] && !pyr_stream_off) {
+                const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (P.lv[l - 1].h - 1 + 4 * PST_NSW - 1) / (4 * PST_NSW), n);
+                k_pyr_stream<<<g, PYR_NT, PST_SMEM, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s,
+                                                         reinterpret_cast<const uint2 *>(h->d_tab_i + h->pyr_yinv_off[l]), d_pyr);
+                continue;
+            }
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);
             k_pyr_resize<<<g, PYR_NT, (size_t)2 * h->pyr_sp[l] * h->pyr_srows[l], st>>>(h->plan, l, h->d_tab_i, h->d_tab_s,
                                                                                    d_pyr, h->pyr_sp[l], h->pyr_srows[l]);

@@ -216,6 +216,145 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     }
 }
 
+/* level l > 0 from level l-1, SOURCE-row driven (the batch shape).  k_pyr_resize above computes, for every output row, the
+ * horizontal sums of BOTH source rows it blends: 2 h-sums per output row, although consecutive output rows share a source
+ * row or skip one (the level scale is >= 1: an output row d blends source rows yofs[d], yofs[d] + 1, and yofs is strictly
+ * increasing).  Here a warp walks SOURCE rows: one h-sum per source row (1.2 per output row at scale 1.2, + 1 to seed the
+ * stream), kept in registers under static names (the walk is fully unrolled, rows alternate between two register sets), and
+ * the output row that ends at this source row -- at most one, yinv[s] -- is blended and stored.  The staged pitch is a
+ * compile-time constant, so a source row's offset is an LDS immediate and the row loop carries no address arithmetic.
+ * The reflect-101 frame ROWS are copies of interior rows: the warp that computes interior row d stores it a second time
+ * at its mirror (frame columns are still computed through mirrored taps, as in k_pyr_resize).
+ * The host falls back to k_pyr_resize for a level where the preconditions fail (borb_api.cu: pyr_stream_ok).
+ * Grid: (ceil(4 * wpr / PYR_TW), ceil((S.h - 1) / (4 * PST_NSW)), frames), PYR_NT threads. */
+#ifndef PST_NSW
+#define PST_NSW 10                  /* source rows a warp walks (besides the one that seeds its stream) */
+#endif
+#define PST_SP2 (2 * PYR_SP_MAX)    /* staged row pitch in bytes (pairs) */
+#define PST_ROWS (4 * PST_NSW + 1)
+#define PST_SMEM (PST_ROWS * PST_SP2)
+
+__global__ void __launch_bounds__(PYR_NT)
+k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restrict__ tab_i, const short *__restrict__ tab_s,
+             const uint2 *__restrict__ yinv /* per source row: output row or ~0u, b0 | b1 << 16 */, uint8_t *__restrict__ pyr)
+{
+    const BorbPlan *plan = &plan_c;
+    extern __shared__ __align__(16) unsigned char pyr_tile[];
+    const BorbLevel &L = plan->lv[l];
+    const BorbLevel &S = plan->lv[l - 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * PYR_TW + 4 * lane - PYR_LPAD;
+    uint8_t *frame = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes;
+    const uint8_t *sbase = frame + S.off + (size_t)BORB_EDGE * S.pitch + BORB_XPAD;
+
+    int sx[4];
+    uint32_t aw[4];
+    int sx_lo = 0x7fffffff, sx_hi = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int x = min(c + k, L.w - 1 + BORB_EDGE);
+        x = reflect101(x, L.w);
+        sx[k] = tab_i[L.xofs_off + x];
+        aw[k] = *reinterpret_cast<const uint32_t *>(tab_s + L.xa_off + 2 * x);
+        sx_lo = min(sx_lo, sx[k]);
+        sx_hi = max(sx_hi, min(sx[k] + 1, S.w - 1));
+    }
+    sx_lo = __reduce_min_sync(0xffffffffu, sx_lo) & ~15;
+    sx_hi = __reduce_max_sync(0xffffffffu, sx_hi);
+    const int s_tile = blockIdx.y * (4 * PST_NSW);
+    const int s_last = min(s_tile + 4 * PST_NSW, S.h - 1);
+    {   /* stage source rows s_tile .. s_last of the window as byte pairs (see k_pyr_resize) */
+        const int vpr = (sx_hi - sx_lo) / 16 + 1; /* host guarantees vpr * 32 <= PST_SP2 */
+        const int nv = vpr * (s_last - s_tile + 1);
+        const uint8_t *g = sbase + (size_t)s_tile * S.pitch + sx_lo;
+        const uint32_t vmagic = 65536u / (uint32_t)vpr + 1u;
+        for (int i = threadIdx.x; i < nv; i += PYR_NT) {
+            const int rr = (int)(((uint32_t)i * vmagic) >> 16), cc = i - rr * vpr;
+            const uint32_t *gw = reinterpret_cast<const uint32_t *>(g + (size_t)rr * S.pitch) + 4 * cc;
+            const uint4 q = __ldg(reinterpret_cast<const uint4 *>(gw));
+            const uint32_t w[5] = {q.x, q.y, q.z, q.w, __ldg(gw + 4)};
+            uint32_t o[8];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                o[2 * m] = __byte_perm(w[m], 0u, 0x2110);
+                o[2 * m + 1] = __byte_perm(w[m], w[m + 1], 0x4332);
+            }
+            uint4 *dstv = reinterpret_cast<uint4 *>(pyr_tile + rr * PST_SP2 + cc * 32);
+            dstv[0] = make_uint4(o[0], o[1], o[2], o[3]);
+            dstv[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+    }
+    const int s0 = s_tile + warp * PST_NSW; /* the row that seeds this warp's stream */
+    /* lane j in 1 .. PST_NSW holds the output row that ends at source row s0 + j */
+    uint2 g = make_uint2(0xffffffffu, 0u);
+    if (lane >= 1 && lane <= PST_NSW && s0 + lane <= S.h - 1) g = __ldg(yinv + s0 + lane);
+    __syncthreads();
+    if (s0 >= S.h - 1) return;
+    const bool col_on = c < L.w + BORB_EDGE;
+    const unsigned char *A[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) A[k] = pyr_tile + (warp * PST_NSW) * PST_SP2 + 2 * (sx[k] - sx_lo);
+    /* Output addressing.  The output rows a warp produces are CONSECUTIVE (yofs is strictly increasing), so the store
+     * pointer runs: one 64-bit add per row.  Only the first and the last tiles of a level hold rows with a mirror in the
+     * reflect-101 frame; they take the variant of the walk that carries the two mirror pointers. */
+    const uint32_t ends = __ballot_sync(0xffffffffu, g.x != 0xffffffffu); /* bit j: an output row ends at source row s0 + j */
+    if (!ends) return;
+    const int nrow = min(PST_NSW, S.h - 1 - s0);
+    const uint32_t d_first = __shfl_sync(0xffffffffu, g.x, __ffs(ends) - 1);
+    const uint32_t d_last = d_first + (uint32_t)__popc(ends) - 1u;
+    const size_t pitch = (size_t)L.pitch;
+    uint8_t *drow = frame + L.off + BORB_XPAD + c + (size_t)(d_first + BORB_EDGE) * pitch;
+    const bool mirrors = d_first <= (uint32_t)BORB_EDGE || (int)d_last >= L.h - 1 - BORB_EDGE;
+    uint32_t H[2][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) H[0][k] = __dp2a_lo(aw[k], (uint32_t) * reinterpret_cast<const uint16_t *>(A[k]), 0u) >> 4;
+#define PST_HSUM(j)                                                                                                     \
+    _Pragma("unroll") for (int k = 0; k < 4; ++k)                                                                       \
+        H[(j) & 1][k] = __dp2a_lo(aw[k], (uint32_t) * reinterpret_cast<const uint16_t *>(A[k] + (j) * PST_SP2), 0u) >> 4
+#define PST_BLEND(j)                                                                                                    \
+    const uint32_t bw_ = __shfl_sync(0xffffffffu, g.y, (j));                                                            \
+    const uint32_t b0 = bw_ << 16, b1 = bw_ & 0xffff0000u;                                                              \
+    uint32_t v = 0;                                                                                                     \
+    _Pragma("unroll") for (int k = 0; k < 4; ++k) {                                                                     \
+        const uint32_t t = (__umulhi(b0, H[((j) - 1) & 1][k]) + __umulhi(b1, H[(j) & 1][k]) + 2u) >> 2;                 \
+        v |= t << (8 * k);                                                                                              \
+    }
+    if (!mirrors && nrow == PST_NSW) { /* the common walk: a full one, no frame rows */
+#pragma unroll
+        for (int j = 1; j <= PST_NSW; ++j) {
+            PST_HSUM(j);
+            if (ends & (1u << j)) { /* warp-uniform */
+                PST_BLEND(j)
+                if (col_on) *reinterpret_cast<uint32_t *>(drow) = v;
+                drow += pitch;
+            }
+        }
+    } else {
+        /* frame rows are copies of interior rows 1 .. 19 (padded row 19 - d) and h-20 .. h-2 (padded row 2h + 17 - d) */
+        uint32_t d = d_first;
+        const uint32_t bot0 = (uint32_t)(L.h - 1 - BORB_EDGE);
+        uint8_t *const row19 = frame + L.off + BORB_XPAD + c + (size_t)BORB_EDGE * pitch;
+        const long long mir2 = 2LL * (L.h - 1);
+#pragma unroll
+        for (int j = 1; j <= PST_NSW; ++j) {
+            if (j > nrow) break;
+            PST_HSUM(j);
+            if (ends & (1u << j)) {
+                PST_BLEND(j)
+                if (col_on) {
+                    *reinterpret_cast<uint32_t *>(drow) = v;
+                    if (d - 1u < (uint32_t)BORB_EDGE) *reinterpret_cast<uint32_t *>(row19 - (size_t)d * pitch) = v;
+                    if (d - bot0 < (uint32_t)BORB_EDGE) *reinterpret_cast<uint32_t *>(row19 + (size_t)(mir2 - (long long)d) * pitch) = v;
+                }
+                drow += pitch;
+                ++d;
+            }
+        }
+    }
+#undef PST_HSUM
+#undef PST_BLEND
+}
+
 /* ---- the whole level chain in ONE launch, for a frame or two (the latency shape) ----
  * Eight dependent launches of a few microseconds each are mostly launch gaps when the grid is a single frame.
  * Here a CTA owns one tile of every level (the levels are partitioned by the same gx x gy grid) and walks the
