@@ -776,8 +776,11 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             const BorbLevel &L = P.lv[l];
             if (h->pyr_stream[l] && !pyr_stream_off) {
                 const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (P.lv[l - 1].h - 1 + 4 * PST_NSW - 1) / (4 * PST_NSW), n);
-                k_pyr_stream<<<g, PYR_NT, PST_SMEM, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s,
-                                                         reinterpret_cast<const uint2 *>(h->d_tab_i + h->pyr_yinv_off[l]), d_pyr);
+                const uint2 *yinv = reinterpret_cast<const uint2 *>(h->d_tab_i + h->pyr_yinv_off[l]);
+                if (h->pyr_sp[l] <= 192)
+                    k_pyr_stream<384><<<g, PYR_NT, PST_ROWS * 384, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s, yinv, d_pyr);
+                else
+                    k_pyr_stream<2 * PYR_SP_MAX><<<g, PYR_NT, PST_ROWS * 2 * PYR_SP_MAX, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s, yinv, d_pyr);
                 continue;
             }
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);

@@ -228,13 +228,16 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
  * The host falls back to k_pyr_resize for a level where the preconditions fail (borb_api.cu: pyr_stream_ok).
  * Grid: (ceil(4 * wpr / PYR_TW), ceil((S.h - 1) / (4 * PST_NSW)), frames), PYR_NT threads. */
 #ifndef PST_NSW
-#define PST_NSW 10                  /* source rows a warp walks (besides the one that seeds its stream) */
+#define PST_NSW 12                  /* source rows a warp walks (besides the one that seeds its stream) */
 #endif
-#define PST_SP2 (2 * PYR_SP_MAX)    /* staged row pitch in bytes (pairs) */
 #define PST_ROWS (4 * PST_NSW + 1)
-#define PST_SMEM (PST_ROWS * PST_SP2)
-
-__global__ void __launch_bounds__(PYR_NT)
+/* PST_SP2 = staged row pitch in bytes (pairs), a template parameter: 2 * PYR_SP_MAX holds any window the host admits, 384
+ * the window of the usual scale factors (<= 192 source columns for 128 output columns: 1.5) at 60 % of the shared memory */
+#ifndef PST_MINB
+#define PST_MINB 9
+#endif
+template <int PST_SP2>
+__global__ void __launch_bounds__(PYR_NT, PST_MINB)
 k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restrict__ tab_i, const short *__restrict__ tab_s,
              const uint2 *__restrict__ yinv /* per source row: output row or ~0u, b0 | b1 << 16 */, uint8_t *__restrict__ pyr)
 {
@@ -243,6 +246,9 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     const BorbLevel &L = plan->lv[l];
     const BorbLevel &S = plan->lv[l - 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    /* a lane owns four adjacent columns = one aligned word of the padded row.  (Two column pairs 64 apart per lane halve the
+     * shared-memory bank conflicts of the tap loads -- 2.4 wavefronts per load here -- but cost a second, 16-bit store per
+     * row: measured 129.0 against 129.6 k frames/s, not kept.) */
     const int c = blockIdx.x * PYR_TW + 4 * lane - PYR_LPAD;
     uint8_t *frame = pyr + (size_t)blockIdx.z * (size_t)plan->pyr_bytes;
     const uint8_t *sbase = frame + S.off + (size_t)BORB_EDGE * S.pitch + BORB_XPAD;
@@ -255,7 +261,7 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
         int x = min(c + k, L.w - 1 + BORB_EDGE);
         x = reflect101(x, L.w);
         sx[k] = tab_i[L.xofs_off + x];
-        aw[k] = *reinterpret_cast<const uint32_t *>(tab_s + L.xa_off + 2 * x);
+        aw[k] = *reinterpret_cast<const uint32_t *>(tab_s + L.xa_off + 2 * x); /* a0 | a1 << 16: the tables' offsets are even */
         sx_lo = min(sx_lo, sx[k]);
         sx_hi = max(sx_hi, min(sx[k] + 1, S.w - 1));
     }
@@ -263,25 +269,40 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     sx_hi = __reduce_max_sync(0xffffffffu, sx_hi);
     const int s_tile = blockIdx.y * (4 * PST_NSW);
     const int s_last = min(s_tile + 4 * PST_NSW, S.h - 1);
-    {   /* stage source rows s_tile .. s_last of the window as byte pairs (see k_pyr_resize) */
+    {   /* stage source rows s_tile .. s_last of the window as byte pairs (see k_pyr_resize); the loads of four vectors
+         * are issued before the first of them is converted and stored (a thread stages 6-7 vectors: one at a time, the
+         * CTA waited out a DRAM latency per vector -- long-scoreboard stall 4.4 per issue in the first capture) */
         const int vpr = (sx_hi - sx_lo) / 16 + 1; /* host guarantees vpr * 32 <= PST_SP2 */
         const int nv = vpr * (s_last - s_tile + 1);
         const uint8_t *g = sbase + (size_t)s_tile * S.pitch + sx_lo;
         const uint32_t vmagic = 65536u / (uint32_t)vpr + 1u;
-        for (int i = threadIdx.x; i < nv; i += PYR_NT) {
-            const int rr = (int)(((uint32_t)i * vmagic) >> 16), cc = i - rr * vpr;
-            const uint32_t *gw = reinterpret_cast<const uint32_t *>(g + (size_t)rr * S.pitch) + 4 * cc;
-            const uint4 q = __ldg(reinterpret_cast<const uint4 *>(gw));
-            const uint32_t w[5] = {q.x, q.y, q.z, q.w, __ldg(gw + 4)};
-            uint32_t o[8];
+        for (int i0 = threadIdx.x; i0 < nv; i0 += 4 * PYR_NT) {
+            uint4 q[4];
+            uint32_t w4[4];
+            int off[4];
 #pragma unroll
-            for (int m = 0; m < 4; ++m) {
-                o[2 * m] = __byte_perm(w[m], 0u, 0x2110);
-                o[2 * m + 1] = __byte_perm(w[m], w[m + 1], 0x4332);
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * PYR_NT;
+                const int rr = (int)(((uint32_t)min(i, nv - 1) * vmagic) >> 16), cc = min(i, nv - 1) - rr * vpr;
+                const uint32_t *gw = reinterpret_cast<const uint32_t *>(g + (size_t)rr * S.pitch) + 4 * cc;
+                q[u] = __ldg(reinterpret_cast<const uint4 *>(gw));
+                w4[u] = __ldg(gw + 4);
+                off[u] = i < nv ? rr * PST_SP2 + cc * 32 : -1;
             }
-            uint4 *dstv = reinterpret_cast<uint4 *>(pyr_tile + rr * PST_SP2 + cc * 32);
-            dstv[0] = make_uint4(o[0], o[1], o[2], o[3]);
-            dstv[1] = make_uint4(o[4], o[5], o[6], o[7]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (off[u] < 0) continue;
+                const uint32_t w[5] = {q[u].x, q[u].y, q[u].z, q[u].w, w4[u]};
+                uint32_t o[8];
+#pragma unroll
+                for (int m = 0; m < 4; ++m) {
+                    o[2 * m] = __byte_perm(w[m], 0u, 0x2110);
+                    o[2 * m + 1] = __byte_perm(w[m], w[m + 1], 0x4332);
+                }
+                uint4 *dstv = reinterpret_cast<uint4 *>(pyr_tile + off[u]);
+                dstv[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                dstv[1] = make_uint4(o[4], o[5], o[6], o[7]);
+            }
         }
     }
     const int s0 = s_tile + warp * PST_NSW; /* the row that seeds this warp's stream */
