@@ -109,6 +109,28 @@ def test_pyramid_planes_in_both_launch_shapes(shape, oracle_built):
             assert np.array_equal(ext.pyramid_level(0, l, border=19), want[f][l]), f"chain kernel, frame {f} L{l}"
 
 
+@pytest.mark.parametrize("shape,scale,nlevels", [((263, 401), 1.1, 12), ((300, 400), 1.5, 4), ((376, 1241), 2.0, 3),
+                                                 ((211, 333), 1.3, 5), ((480, 640), 1.05, 8)])
+def test_batch_shape_pyramid_with_other_scale_factors(shape, scale, nlevels, oracle_built):
+    """The per-level pyramid kernels of the batch shape (k_pyr_stream: source-row driven, staged pitch 384 B or, from a
+    scale factor of about 1.5, 640 B) on other scale factors and level counts: every plane, frame included, and the
+    results of the whole path against the oracle."""
+    from oracle.pyoracle import Oracle
+    from orb_slam2_test_b200 import ORBextractor
+    nb = 48
+    ext = ORBextractor(500, scale, nlevels, 20, 7, max_batch=nb)
+    ora = Oracle(500, scale, nlevels, 20, 7)
+    imgs = np.stack([synth.make_noise_frame(shape, seed=21 + f) if f % 3 == 1 else synth.make_frame(shape, seed=21, frame=f)
+                     for f in range(nb)])
+    res = ext.extract_batch(imgs, want_pyramid=True)
+    assert ext.launches_per_call() != 5, "expected the batch launch shape"
+    for f in (0, 1, nb - 1):
+        want = ora.extract(imgs[f])
+        for l in range(nlevels):
+            assert np.array_equal(ext.pyramid_level(f, l, border=19), ora.pyramid(l, 19)), f"scale {scale}, frame {f} L{l}"
+        _assert_same(res[f], want, f"scale {scale} frame {f}")
+
+
 @pytest.mark.parametrize("cfg,count", [("K2k", 2), ("T1k", 3)])
 def test_chain_shape_with_several_frames(cfg, count, oracle_built):
     """The single-launch level chain also serves calls of two or three frames (grid.y > 1): every frame's planes and
