@@ -179,7 +179,7 @@ struct QtPts {
  * children with more than one point (written to the other expandable buffer, creation order).
  * One packed scan gives the positions of the non-empty children (field 0), of the expandable ones
  * (field 1) and of the nodes that stay (field 2). */
-template <int QT_NT, bool REG>
+template <int QT_NT, bool REG, bool BREADTH>
 __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, QtPts<QT_NT, REG> &pts, int *n_exp, bool packed)
 {
     const int nc = 4 * n_proc;
@@ -193,8 +193,10 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
                 g = (qt_u64)(n > 0) | ((qt_u64)(n > 1) << QT_F);
             }
             if (i < S) {
-                const int r = s.rank[i];
-                g |= (qt_u64)!(r >= 0 && r < n_proc) << (2 * QT_F);
+                bool stays;
+                if (BREADTH) stays = s.cnt(cur)[i] <= 1; /* rank[] is only valid where the count is > 1 */
+                else { const int r = s.rank[i]; stays = !(r >= 0 && r < n_proc); }
+                g |= (qt_u64)stays << (2 * QT_F);
             }
             return g;
         },
@@ -222,7 +224,7 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
     pts.each([&](int, uint32_t v, uint32_t &nd) {
         const int j = (int)nd;
         const int k = s.rank[j];
-        if (k >= 0 && k < n_proc)
+        if (BREADTH ? s.cnt(cur)[j] > 1 : (k >= 0 && k < n_proc))
             nd = (uint32_t)s.cf[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])];
         else
             nd = (uint32_t)s.uf[j];
@@ -233,13 +235,13 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
 }
 
 /* count the quarters of every ranked node; ccnt[0 .. 4 * ranked) must be zero on entry */
-template <int QT_NT, bool REG>
+template <int QT_NT, bool REG, bool BREADTH>
 __device__ __forceinline__ void qt_count(const QtSmem &s, int cur, QtPts<QT_NT, REG> &pts)
 {
     pts.each([&](int, uint32_t v, uint32_t &nd) {
         const int j = (int)nd;
         const int k = s.rank[j];
-        if (k >= 0)
+        if (BREADTH ? s.cnt(cur)[j] > 1 : k >= 0)
             atomicAdd(&s.ccnt[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])], 1);
     });
     __syncthreads();
@@ -293,17 +295,29 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     });
     __syncthreads();
     int cur = 0;
-    int S = (int)qt_scan_emit<QT_NT>(
-        n_ini, s.wtmp, [&](int j) -> qt_u64 { return (qt_u64)(s.ccnt[j] > 0); },
+    /* The breadth passes rank the multi-point nodes in list order.  No scan is needed for that: among the roots the
+     * rank is a second field of the scan that drops the empty ones, and after a breadth pass every multi-point node is
+     * a child born in it (whatever stayed had one point), the children stand at the head of the new list in REVERSE
+     * creation order, and the split has numbered the multi-point ones e = 0 .. E-1 in creation order: rank = E-1-e. */
+    const qt_u64 tot0 = qt_scan_emit<QT_NT>(
+        n_ini, s.wtmp, [&](int j) -> qt_u64 { const int c = s.ccnt[j]; return (qt_u64)(c > 0) | ((qt_u64)(c > 1) << QT_F); },
         [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
-            if (g) {
-                const int p = (int)before;
+            if (g & 1) {
+                const int p = (int)(before & QT_FMASK);
                 s.box(0)[p] = make_int4((int)__fmul_rn(hx, (float)j), 0, (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
                 s.cnt(0)[p] = s.ccnt[j];
                 s.cf[j] = p;
+                if (g >> QT_F) {
+                    const int k = (int)(before >> QT_F);
+                    s.rank[p] = k;
+                    s.par[k] = p;
+                }
             }
         });
+    int S = (int)(tot0 & QT_FMASK);
+    int n_exp = (int)(tot0 >> QT_F); /* multi-point nodes of the current list */
     pts.each([&](int, uint32_t, uint32_t &nd) { nd = (uint32_t)s.cf[nd]; });
+    for (int c = tid; c < 4 * n_exp; c += QT_NT) s.ccnt[c] = 0;
     __syncthreads();
 
     /* ---- split passes (:741-927) ---- */
@@ -311,25 +325,24 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     const bool packed = n < (1 << (31 - QT_EBITS)); /* (size << 11 | creation index) fits a positive int */
     bool done = (S == 0);
     while (!done) {
-        /* breadth pass: rank the multi-point nodes in list order (and clear their quarter counters) */
+        /* breadth pass: every multi-point node splits (rank, par and zeroed quarter counters are in place) */
         const int prev = S;
-        const int n_split = (int)qt_scan_emit<QT_NT>(
-            S, s.wtmp, [&](int j) -> qt_u64 { return (qt_u64)(s.cnt(cur)[j] > 1); },
-            [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
-                const int k = (int)before;
-                s.rank[j] = g ? k : -1;
-                if (g) {
-                    s.par[k] = j;
-                    *reinterpret_cast<int4 *>(&s.ccnt[4 * k]) = make_int4(0, 0, 0, 0);
-                }
-            });
+        const int n_split = n_exp;
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
-        qt_count<QT_NT, REG>(s, cur, pts);
-        int n_exp;
-        S = qt_split<QT_NT, REG>(s, cur, S, n_split, pts, &n_exp, packed);
+        qt_count<QT_NT, REG, true>(s, cur, pts);
+        S = qt_split<QT_NT, REG, true>(s, cur, S, n_split, pts, &n_exp, packed);
         cur = 1 - cur;
         if (S >= N || S == prev) break;
-        if (S + 3 * n_exp <= N) continue;
+        if (S + 3 * n_exp <= N) {
+            for (int e = tid; e < n_exp; e += QT_NT) {
+                const int pos = s.exp_pos(cur)[e], k = n_exp - 1 - e;
+                s.rank[pos] = k;
+                s.par[k] = pos;
+                *reinterpret_cast<int4 *>(&s.ccnt[4 * k]) = make_int4(0, 0, 0, 0);
+            }
+            __syncthreads();
+            continue;
+        }
 
         /* ordered passes (:853-924) */
         while (true) {
@@ -366,7 +379,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                 }
             }
             __syncthreads();
-            qt_count<QT_NT, REG>(s, cur, pts);
+            qt_count<QT_NT, REG, false>(s, cur, pts);
             /* size after processing ranks 0..k; stop at the first k reaching N */
             qt_scan_emit<QT_NT>(
                 E, s.wtmp,
@@ -378,7 +391,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                     if (S + (int)before + (int)g >= N) atomicMin(&sh_proc, k + 1);
                 });
             const int n_proc = sh_proc;
-            S = qt_split<QT_NT, REG>(s, cur, S, n_proc, pts, &n_exp, packed);
+            S = qt_split<QT_NT, REG, false>(s, cur, S, n_proc, pts, &n_exp, packed);
             cur = 1 - cur;
             if (S >= N || S == prev2) { done = true; break; }
         }
