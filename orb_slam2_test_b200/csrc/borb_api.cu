@@ -682,7 +682,8 @@ int build_plan(borb_extractor *h, int cols, int rows)
         }
         h->desc_maps.nlevels = P.nlevels; h->desc_maps.kp_total = P.kp_total;
         std::memcpy(h->desc_maps.umax, P.umax, sizeof P.umax);
-        CU(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES));
+        CU(cudaFuncSetAttribute(k_orient_describe<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES));
+        CU(cudaFuncSetAttribute(k_orient_describe<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES));
         CU(cudaFuncSetAttribute(k_blur_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, BLUR_SMEM_BYTES));
     }
     h->qt_M = M;
@@ -701,6 +702,27 @@ int build_plan(borb_extractor *h, int cols, int rows)
 namespace {
 
 bool pre_active(const borb_extractor *h) { return h->in_ch > 1 || h->d_map_xy != nullptr; }
+
+/* A kernel launch with the programmatic-serialization attribute (pdl): the kernel may be scheduled while its
+ * predecessor in the stream still runs and meets it at borb_pdl_wait() (borb_cta.cuh).  Captured into a graph the edge
+ * becomes a programmatic dependency.  Used for the single-frame shape only, where the ~1.5 us between two dependent
+ * kernels is a visible part of the call. */
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1u : 0u;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 
 /* Enqueue the whole per-call chain for n frames whose pixels are at dev_img on the device. */
 int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t step, size_t stride,
@@ -762,6 +784,9 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     static const bool pyr_stream_off = getenv("BORB_PYR_RESIZE_V3") != nullptr; /* A/B knob: k_pyr_resize instead of k_pyr_stream */
     const bool chain = !chain_off && h->chain_tiles > 0 && (long long)n * h->chain_tiles <= 2 * h->n_sm;
     h->last_launches = (chain ? 1 : P.nlevels + 1) + 4 + (pre_active(h) ? 1 : 0) + (h->have_cam ? 1 : 0);
+    static const bool pdl_off = getenv("BORB_NO_PDL") != nullptr; /* A/B knob */
+    const bool pdl = chain && !stage_events && !pdl_off; /* K2, K3 and K6 launched programmatically behind their predecessors */
+    const bool pdl2 = pdl, pdl3 = pdl, pdl6 = pdl;
     if (chain) {
         /* K1, latency shape: the whole chain in one launch */
         k_pyr_chain<<<dim3(h->chain_tiles, n), PCH_NT, h->chain_smem, st>>>(h->plan, h->d_chain, h->d_chain_tabs, h->chain_tstride,
@@ -822,30 +847,31 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         /* a frame or two: one CTA per (cell, frame), and the time is a cell's dependent chain -> four warps per cell */
         static const bool env_nw2 = getenv("BORB_FAST_NW2") != nullptr; /* A/B knob: two warps per cell in every shape */
         const bool four = !env_nw2 && (long long)P.n_cells * n <= 2LL * h->n_sm * 16;
-#define K2(WP, NW) k_fast_cells<WP, NW><<<grid, 32 * NW, NW == 4 ? h->fast_smem4 : h->fast_smem, st>>>(                   \
-        h->plan, h->d_cells, n, h->fast_maps, f0, d_cand_xy, d_cand_score, d_ncand)
+#define K2(WP, NW) CU(launch_k(k_fast_cells<WP, NW>, grid, dim3(32 * NW), (size_t)(NW == 4 ? h->fast_smem4 : h->fast_smem), st, pdl2, \
+        h->plan, (const BorbCell *)h->d_cells, n, h->fast_maps, f0, d_cand_xy, d_cand_score, d_ncand))
         if (four) { if (h->fast_wp == 64) K2(64, 4); else if (h->fast_wp == 80) K2(80, 4); else K2(96, 4); }
         else { if (h->fast_wp == 64) K2(64, 2); else if (h->fast_wp == 80) K2(80, 2); else K2(96, 2); }
 #undef K2
     }
     STAGE(2);
     if (n * P.nlevels <= 2 * h->n_sm) /* few CTAs: give each one a whole SM's worth of threads */
-        k_quadtree<QT_NT_LATENCY><<<dim3(P.nlevels, n), QT_NT_LATENCY, qt_smem_bytes(h->qt_M), st>>>(
-            h->plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
+        CU(launch_k(k_quadtree<QT_NT_LATENCY>, dim3(P.nlevels, n), dim3(QT_NT_LATENCY), qt_smem_bytes(h->qt_M), st, pdl3,
+                    h->plan, h->qt_M, (const uint32_t *)d_cand_xy, (const uint32_t *)d_cand_score, d_cand_node, (const int *)d_ncand,
+                    d_lkp_xy, d_lkp_score, d_nlkp, h->d_err));
     else
         k_quadtree<QT_NT_THROUGHPUT><<<dim3(P.nlevels, n), QT_NT_THROUGHPUT, qt_smem_bytes(h->qt_M), st>>>(
             h->plan, h->qt_M, d_cand_xy, d_cand_score, d_cand_node, d_ncand, d_lkp_xy, d_lkp_score, d_nlkp, h->d_err);
     STAGE(3);
     /* the descriptors address the whole slab: frame index = f0 + blockIdx.y */
-    if (blur_beside) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
+    if (blur_beside) CU(cudaStreamWaitEvent(st, h->ev_join, 0)); /* (joining before K3 instead: 61 us against 55 -- the blur ends after K2) */
     else K5_ON(st);
 #undef K5_ON
     STAGE(4);
     /* keypoint slots per warp: 16 when there are plenty of frames, 1 for a single frame */
     const int kpw = std::max(1, std::min(DESC_KPW, n / 4));
-    k_orient_describe<<<dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), DESC_NT, DESC_SMEM_BYTES, st>>>(
-        h->desc_maps, h->d_pattern, f0, d_lkp_xy, d_lkp_score, d_nlkp,
-        d_out_kp, d_out_desc, d_nout);
+    CU(launch_k(pdl6 ? k_orient_describe<true> : k_orient_describe<false>, dim3((P.kp_total + DESC_NW * kpw - 1) / (DESC_NW * kpw), n), dim3(DESC_NT), (size_t)DESC_SMEM_BYTES, st, pdl6,
+                h->desc_maps, (const signed char *)h->d_pattern, f0, (const uint32_t *)d_lkp_xy, (const uint32_t *)d_lkp_score,
+                (const int *)d_nlkp, d_out_kp, d_out_desc, d_nout));
     if (h->have_cam) { /* K8: rides in the describe stage's time slot */
 #define K8(NT) k_frame_undistort_grid<NT><<<n, NT, 0, st>>>(h->d_plan, h->cam, d_out_kp, d_nout, \
         h->d_un_xy + (size_t)f0 * P.kp_total, h->d_cell_start + (size_t)f0 * (FR_CELLS + 1), \
@@ -2200,3 +2226,12 @@ int borb_debug_fast_score(const uint8_t *p, int pitch, int t_lo) { return fast_s
 #include "borb_stream.inl"
 #include "borb_noalloc.inl"
 #include "borb_bow.inl"
+
+#ifdef BORB_FAST_PROBE
+/* development only (tools/probe_fast.py): the probe words of the last k_fast_cells launch */
+extern "C" int borb_debug_fast_probe(unsigned long long *out, int n_words)
+{
+    if (cudaDeviceSynchronize() != cudaSuccess) return BORB_ERR_CUDA;
+    return cudaMemcpyFromSymbol(out, g_fast_probe, (size_t)n_words * 8) == cudaSuccess ? BORB_OK : BORB_ERR_CUDA;
+}
+#endif

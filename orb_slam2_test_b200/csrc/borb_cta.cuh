@@ -4,6 +4,28 @@
 #ifndef BORB_CTA_CUH
 #define BORB_CTA_CUH
 
+/* Programmatic dependent launch (the single-frame shape, borb_api.cu enqueue_chain): a kernel launched with the
+ * programmatic-serialization attribute may start while the kernel before it in the stream still runs; it does what
+ * needs none of that kernel's results (shared-memory set-up, barrier init, constant tables), then waits here.  The wait
+ * returns when the preceding grid has COMPLETED and its writes are visible, so it is also what makes the chain
+ * transitive: every kernel of the chain calls it, before its first read of anything a predecessor wrote.  In a
+ * kernel launched the ordinary way both instructions do nothing. */
+__device__ __forceinline__ void borb_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+/* A pointer to data the preceding grid wrote, to be read only after borb_pdl_wait(): loads through a
+ * `const T *__restrict__` kernel parameter are invariant loads to the compiler, which moves them freely -- also above the
+ * wait's asm statement (seen in the SASS of k_orient_describe: the counts were loaded at the top of the kernel).  The
+ * value that comes out of this asm is opaque and volatile asm statements keep their order, so no load through the
+ * returned pointer can be scheduled before the wait. */
+template <typename T>
+__device__ __forceinline__ T *borb_pdl_after_wait(T *p)
+{
+    asm volatile("" : "+l"(p) : : "memory");
+    __builtin_assume(__isGlobal(p)); /* the asm hides the address space too: without this the loads are generic LD */
+    return p;
+}
+/* lets the NEXT kernel of the stream be scheduled once every CTA of this grid has got here (or exited) */
+__device__ __forceinline__ void borb_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 /* exclusive prefix sum of one int per thread over a CTA of NT threads (NT a multiple of 32, <= 1024):
  * shuffle scan inside each warp, then over the warp totals.  wsum: 32 ints of shared memory.
  * Returns the exclusive prefix; *total = sum over the CTA. */

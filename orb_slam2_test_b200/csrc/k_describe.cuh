@@ -22,6 +22,7 @@
 #include <cuda.h>
 
 #include "borb_internal.h"
+#include "borb_cta.cuh"
 #include "orb_sincos.cuh"
 
 struct BorbKpRec { /* == cv::KeyPoint == borb_keypoint */
@@ -122,10 +123,11 @@ struct DescMaps { /* kernel parameter (__grid_constant__): TMA descriptors of th
     float scale[BORB_MAXL], patch_size[BORB_MAXL];
 };
 
+template <bool PDL>
 __global__ void __launch_bounds__(DESC_NT, DESC_MINB)
 k_orient_describe(const __grid_constant__ DescMaps dm, const signed char *__restrict__ pattern, const int frame0,
-                  const uint32_t *__restrict__ lkp_xy, const uint32_t *__restrict__ lkp_score,
-                  const int *__restrict__ nlkp, BorbKpRec *__restrict__ out_kp,
+                  const uint32_t *__restrict__ lkp_xy_p, const uint32_t *__restrict__ lkp_score_p,
+                  const int *__restrict__ nlkp_p, BorbKpRec *__restrict__ out_kp,
                   uint8_t *__restrict__ out_desc, int *__restrict__ nout)
 {
     /* [0,64): mbarriers [warp][buffer]; per warp two buffers, each the blurred 37-row patch and the
@@ -153,6 +155,17 @@ k_orient_describe(const __grid_constant__ DescMaps dm, const signed char *__rest
         const uint4 p1 = __ldg(reinterpret_cast<const uint4 *>(pattern) + lane * 2 + 1);
         pw[0] = p0.x; pw[1] = p0.y; pw[2] = p0.z; pw[3] = p0.w;
         pw[4] = p1.x; pw[5] = p1.y; pw[6] = p1.z; pw[7] = p1.w;
+    }
+    /* PDL: launched programmatically behind K3 (the single-frame shape).  What K3 wrote is then read with ordinary
+     * loads through pointers that exist only after the wait (borb_cta.cuh); the other instantiation keeps the read-only
+     * loads the compiler derives from `const __restrict__` (they are what it would hoist above the wait). */
+    const uint32_t *lkp_xy = lkp_xy_p, *lkp_score = lkp_score_p;
+    const int *nlkp = nlkp_p;
+    if (PDL) {
+        borb_pdl_wait(); /* K3 is complete: the survivors and their counts (the blurred planes come over a full dependency) */
+        lkp_xy = borb_pdl_after_wait(lkp_xy_p);
+        lkp_score = borb_pdl_after_wait(lkp_score_p);
+        nlkp = borb_pdl_after_wait(nlkp_p);
     }
     /* lane l < nl: survivors of level l, slot offset of level l, output offset of level l */
     const int my_cnt = lane < nl ? nlkp[frame * BORB_MAXL + lane] : 0;
@@ -192,7 +205,7 @@ k_orient_describe(const __grid_constant__ DescMaps dm, const signed char *__rest
             if (idx_ < __shfl_sync(0xffffffffu, my_cnt, lv_)) {                              \
                 I.ok = true; I.level = lv_; I.slot = s_;                                     \
                 I.o = __shfl_sync(0xffffffffu, my_base, lv_) + idx_;                         \
-                I.v = lkp_xy[fkp + s_];                                                      \
+                I.v = lkp_xy[fkp + s_];                                                             \
                 break;                                                                       \
             }                                                                                \
         }                                                                                    \

@@ -38,6 +38,7 @@
 #include <cuda.h> /* CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint) */
 
 #include "borb_internal.h"
+#include "borb_cta.cuh"
 
 
 /* staged window row pitch WP (template parameter of the kernel) = width of the TMA box.  A box must
@@ -225,6 +226,22 @@ __device__ __forceinline__ void fast_mbar_wait(uint32_t bar, uint32_t parity)
 #endif
 /* NW = warps per cell: 2 for batches (measured best of 2 / 4 / 8: load balance between uneven cells), 4 for a frame or
  * two, where the grid is one CTA per cell and a cell's dependent chain (load -> pre-test -> score -> NMS) is the time */
+/* -DBORB_FAST_PROBE (tools/probe_fast.py, never in the shipped library): %globaltimer of thread 0 at eight points of
+ * a CTA's first item, for the phase split of the single-frame shape */
+#ifdef BORB_FAST_PROBE
+__device__ unsigned long long g_fast_probe[2048 * 8];
+#define FAST_PROBE(k)                                                                      \
+    do {                                                                                   \
+        if (threadIdx.x == 0 && blockIdx.y == 0 && blockIdx.x < 2048) {                    \
+            unsigned long long t_;                                                         \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                         \
+            g_fast_probe[blockIdx.x * 8 + (k)] = t_;                                       \
+        }                                                                                  \
+    } while (0)
+#else
+#define FAST_PROBE(k) do { } while (0)
+#endif
+
 template <int WP, int NW>
 __global__ void __launch_bounds__(32 * NW, FAST_MIN_CTAS * 2 / NW)
 k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict__ cells, int n_frames,
@@ -247,6 +264,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
     uint32_t *list3 = reinterpret_cast<uint32_t *>(list1);
     const int n_cells = tmaps.n_cells;
     const int ini = tmaps.ini_th, mn = tmaps.min_th;
+    FAST_PROBE(0);
 
     for (int i = tid; i < (lay.l1_off - lay.sc_off) / 4; i += FAST_NT) reinterpret_cast<uint32_t *>(sc)[i] = 0u;
 
@@ -270,8 +288,11 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
         const BorbCell c0 = cells[ci];
         origin = fast_tma_origin(c0);
         level = c0.level;
-        if (tid == 0) fast_tma_window(maps, origin, level, frame0 + frame, win0, bar0, box_bytes);
     }
+    borb_pdl_wait(); /* the pyramid is complete from here on (nothing above reads it) */
+    borb_pdl_launch_dependents();
+    if (have && tid == 0) fast_tma_window(maps, origin, level, frame0 + frame, win0, bar0, box_bytes);
+    FAST_PROBE(1);
     /* per-cell state (see the geometry block below) */
     int dw = 0, dh = 0, s1_R = 1, s1_rig = 0, s1_col = 0, org_off = 0, s1_qoff = 0, cand_cap = 0, sxy3 = 0;
     bool s1_on = false;
@@ -286,6 +307,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
         uint8_t *win = fast_raw + lay.win_off + buf * lay.win_bytes;
         fast_mbar_wait(bar0 + 8 * buf, (it >> 1) & 1u); /* this item's window has landed */
         __syncthreads(); /* and everybody is done with the other buffer and the lists of the previous item */
+        FAST_PROBE(2);
         uint32_t norigin = origin;
         int nlevel = level;
         if (nhave) {
@@ -324,6 +346,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
              * src/ORBextractor.cc:1087-1088 */
             sxy3 = (3 + cell.sx) | ((3 + cell.sy) << 16);
         }
+        FAST_PROBE(3);
         const uint8_t *org = win + org_off;
         const uint32_t *s1_qp = reinterpret_cast<const uint32_t *>(win) + s1_qoff;
         int n2 = 0, n3 = 0, cell_total = 0;
@@ -391,6 +414,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
                 if (sd3) *dst++ = (uint16_t)((pixb + 3) | (sd3 << 12));
             }
             __syncwarp();
+            FAST_PROBE(4);
 
             /* ---- stage 2: full test + score of the listed pixels ---- */
             n2 = 0;
@@ -437,6 +461,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
                 n2 += __popc(bal);
             }
             __syncthreads();
+            FAST_PROBE(5);
 
             /* ---- stage 3: strict 3x3 NMS inside the domain ---- */
             n3 = 0;
@@ -459,6 +484,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
             }
             if (lane == 0) wcnt[pass * FAST_NW + warp] = n3;
             __syncthreads();
+            FAST_PROBE(6);
             cell_total = 0;
 #pragma unroll
             for (int w = 0; w < FAST_NW; ++w) cell_total += wcnt[pass * FAST_NW + w];
@@ -487,6 +513,7 @@ k_fast_cells(const __grid_constant__ BorbPlan plan_c, const BorbCell *__restrict
             sc[(((ent >> 6) & 63) + 1) * FAST_SPITCH + (ent & 63) + 1] = 0;
         }
         /* the next cell's first write to the score plane / wcnt comes after its top barrier */
+        FAST_PROBE(7);
         have = nhave;
         new_cell = nci != ci;
         if (nhave) { origin = norigin; level = nlevel; ci = nci; frame = nframe; buf ^= 1; }

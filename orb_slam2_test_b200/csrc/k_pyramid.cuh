@@ -19,6 +19,7 @@
 #define K_PYRAMID_CUH
 
 #include "borb_internal.h"
+#include "borb_cta.cuh"
 
 #define PYR_NT 128
 #ifndef PYR_TH
@@ -415,6 +416,7 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
 {
     const BorbPlan *plan = &plan_c;
     extern __shared__ __align__(16) unsigned char pch_smem[];
+    borb_pdl_launch_dependents(); /* K2's CTAs may take their places and set up while the chain runs */
     const int tid = threadIdx.x, nl = plan->nlevels;
     const PyrChainTile *const gT = tiles + blockIdx.x;
     uint2 *const tabs = reinterpret_cast<uint2 *>(pch_smem + off_t);

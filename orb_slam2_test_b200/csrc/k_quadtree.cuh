@@ -22,6 +22,7 @@
 #define K_QUADTREE_CUH
 
 #include "borb_internal.h"
+#include "borb_cta.cuh"
 
 /* threads per CTA is a template parameter: 256 for throughput (many (level, frame) CTAs in flight;
  * measured on B200 per 512 frames: 1024 -> 0.80 ms, 512 -> 0.51 ms, 256 -> 0.48 ms), 1024 for the
@@ -428,15 +429,27 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
 
 template <int QT_NT>
 __global__ void __launch_bounds__(QT_NT, 1024 / QT_NT)
-k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__restrict__ cand_xy,
-           const uint32_t *__restrict__ cand_score, uint32_t *__restrict__ cand_node,
-           const int *__restrict__ ncand, uint32_t *__restrict__ lkp_xy,
+k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__restrict__ cand_xy_p,
+           const uint32_t *__restrict__ cand_score_p, uint32_t *__restrict__ cand_node,
+           const int *__restrict__ ncand_p, uint32_t *__restrict__ lkp_xy,
            uint32_t *__restrict__ lkp_score, int *__restrict__ nlkp, int *__restrict__ err)
 {
     const BorbPlan *plan = &plan_c; /* the plan rides in the parameter block: constant-bank reads, no global loads */
     extern __shared__ __align__(16) unsigned char qt_raw[];
     __shared__ int sh_proc;
     const BorbLevel &L = plan->lv[blockIdx.x];
+    /* The 1024-thread shape is the one launched programmatically behind K2 (a frame or two per call): what K2 wrote is
+     * read with ordinary loads through pointers that exist only after the wait (borb_cta.cuh); the throughput shape
+     * keeps the read-only loads the compiler derives from `const __restrict__`. */
+    const uint32_t *cand_xy = cand_xy_p, *cand_score = cand_score_p;
+    const int *ncand = ncand_p;
+    if (QT_NT == QT_NT_LATENCY) {
+        borb_pdl_wait(); /* K2 is complete: the candidates and their counts */
+        borb_pdl_launch_dependents();
+        cand_xy = borb_pdl_after_wait(cand_xy_p);
+        cand_score = borb_pdl_after_wait(cand_score_p);
+        ncand = borb_pdl_after_wait(ncand_p);
+    }
     int n = ncand[blockIdx.y * BORB_MAXL + blockIdx.x];
     if (n > L.cand_cap) { /* cannot happen (capacity is the NMS bound); never truncate silently */
         if (threadIdx.x == 0) atomicExch(err, 1);
