@@ -82,16 +82,19 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
 
 struct QtSmem { /* the double-buffered arrays are base + buffer * M: no pointer table indexed at run time (local memory) */
     int4 *box_;
-    int *cnt_, *exp_pos_, *exp_size_;
-    int *rank, *par, *uf, *ccnt, *cf;
-    unsigned long long *best;
+    int *cnt_, *exp_size_, *ccnt_, *cf;
+    uint16_t *rank, *uf, *par_, *exp_pos_; /* list positions and ranks are < BORB_QT_MAXNODES = 2048 */
+    unsigned long long *best; /* on top of ccnt_ (dead by then) */
     qt_u64 *wtmp;
     int M;
     __device__ __forceinline__ int4 *box(int b) const { return box_ + b * M; }
     __device__ __forceinline__ int *cnt(int b) const { return cnt_ + b * M; }
-    __device__ __forceinline__ int *exp_pos(int b) const { return exp_pos_ + b * M; }
+    __device__ __forceinline__ int *ccnt(int b) const { return ccnt_ + b * 4 * M; }
+    __device__ __forceinline__ uint16_t *par(int b) const { return par_ + b * M; }
+    __device__ __forceinline__ uint16_t *exp_pos(int b) const { return exp_pos_ + b * M; }
     __device__ __forceinline__ int *exp_size(int b) const { return exp_size_ + b * M; }
 };
+#define QT_NONE 0xffffu /* rank[] of a node that is not ranked */
 
 __device__ __forceinline__ int qt_quadrant(int x, int y, const int4 b)
 {
@@ -115,7 +118,9 @@ __device__ __forceinline__ int4 qt_child_box(const int4 b, int q)
 /* bytes of dynamic shared memory for a list capacity of M nodes */
 static inline size_t qt_smem_bytes(int M)
 {
-    return (size_t)M * (2 * 16 + 8 + 2 * 4 + 3 * 4 + 2 * 16 + 4 * 4) + 40 * 8 + 16; /* + 16: zero padding of the rank keys */
+    /* box 2x16, quarter counters 2x16, child positions 16, counts 2x4, rank keys 2x4, then the 16-bit arrays: par 2x2,
+     * exp_pos 2x2, rank 2, uf 2 */
+    return (size_t)M * (32 + 32 + 16 + 8 + 8 + 4 + 4 + 2 + 2) + 40 * 8 + 16; /* + 16: zero padding of the rank keys */
 }
 
 /* The candidates of a (level, frame): in the latency shape (1024 threads, a CTA alone on its SM) a thread keeps
@@ -174,29 +179,37 @@ struct QtPts {
 };
 
 /* One split pass over the current list (cur) into (1-cur).
- * On entry: rank[j] = processing rank of list node j (or -1), par[k] = node of rank k,
- * ccnt[4k+q] = points of rank k's q-th quarter, for all ranked nodes.
- * Only ranks < n_proc are actually split.  Returns the new list size; *n_exp = number of
- * children with more than one point (written to the other expandable buffer, creation order).
- * One packed scan gives the positions of the non-empty children (field 0), of the expandable ones
- * (field 1) and of the nodes that stay (field 2). */
+ * On entry: par(cur)[k] = list node of processing rank k, ccnt(cur)[4k+q] = points of rank k's q-th quarter, for all
+ * ranked nodes.  Only ranks < n_proc are actually split.  Returns the new list size; *n_exp = number of children
+ * with more than one point (written to the other expandable buffer, creation order).  One packed scan gives the
+ * positions of the non-empty children (field 0), of the expandable ones (field 1) and of the nodes that stay (field 2).
+ *
+ * BREADTH (every multi-point node splits): a candidate's node word is  position | (rank + 1) << 16  (0 in the upper
+ * half: a single-point node, which stays), so no rank table is read; and the pass prepares the NEXT breadth pass as it
+ * goes: after it every multi-point node is a child born in it, the children stand at the head of the new list in
+ * reverse creation order and the scan has numbered the multi-point ones e = 0 .. E-1 in creation order, so a child's
+ * next rank is E-1-e -- written into its node word, par(1-cur) and the zeroed counters ccnt(1-cur) by the scan's emit
+ * step, and the relabelling step counts each candidate into its new node's quarter right away.  A breadth pass is the
+ * scan (three barriers) and the relabel-and-count step (one).
+ * Ordered pass (!BREADTH): ranks come from rank[] (QT_NONE = not ranked), node words are plain positions. */
 template <int QT_NT, bool REG, bool BREADTH>
 __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_proc, QtPts<QT_NT, REG> &pts, int *n_exp, bool packed)
 {
     const int nc = 4 * n_proc;
     const int nxt = 1 - cur;
+    const int *const ccnt = s.ccnt(cur);
     const qt_u64 tot = qt_scan_emit<QT_NT>(
         max(nc, S), s.wtmp,
         [&](int i) -> qt_u64 {
             qt_u64 g = 0;
             if (i < nc) {
-                const int n = s.ccnt[i];
+                const int n = ccnt[i];
                 g = (qt_u64)(n > 0) | ((qt_u64)(n > 1) << QT_F);
             }
             if (i < S) {
                 bool stays;
-                if (BREADTH) stays = s.cnt(cur)[i] <= 1; /* rank[] is only valid where the count is > 1 */
-                else { const int r = s.rank[i]; stays = !(r >= 0 && r < n_proc); }
+                if (BREADTH) stays = s.cnt(cur)[i] <= 1;
+                else stays = (int)s.rank[i] >= n_proc; /* QT_NONE is larger than any rank */
                 g |= (qt_u64)stays << (2 * QT_F);
             }
             return g;
@@ -204,46 +217,63 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
         [&](int i, qt_u64 g, qt_u64 before, qt_u64 total) {
             const int C = (int)(total & QT_FMASK);
             if (g & 1) {
-                const int n = s.ccnt[i];
+                const int n = ccnt[i];
                 const int p = C - 1 - (int)(before & QT_FMASK);
-                s.box(nxt)[p] = qt_child_box(s.box(cur)[s.par[i >> 2]], i & 3);
+                s.box(nxt)[p] = qt_child_box(s.box(cur)[s.par(cur)[i >> 2]], i & 3);
                 s.cnt(nxt)[p] = n;
-                s.cf[i] = p;
+                int word = p;
                 if (n > 1) {
                     const int e = (int)((before >> QT_F) & QT_FMASK);
-                    s.exp_pos(nxt)[e] = p;
+                    s.exp_pos(nxt)[e] = (uint16_t)p;
                     s.exp_size(nxt)[e] = packed ? (n << QT_EBITS) | e : n; /* the ordered phase ranks by (size, creation order) */
+                    if (BREADTH) {
+                        const int kk = (int)((total >> QT_F) & QT_FMASK) - 1 - e;
+                        s.par(nxt)[kk] = (uint16_t)p;
+                        *reinterpret_cast<int4 *>(&s.ccnt(nxt)[4 * kk]) = make_int4(0, 0, 0, 0);
+                        word |= (kk + 1) << 16;
+                    }
                 }
+                s.cf[i] = word;
             }
             if ((g >> (2 * QT_F)) & 1) {
                 const int p = C + (int)(before >> (2 * QT_F));
                 s.box(nxt)[p] = s.box(cur)[i];
                 s.cnt(nxt)[p] = s.cnt(cur)[i];
-                s.uf[i] = p;
+                s.uf[i] = (uint16_t)p;
             }
         });
     pts.each([&](int, uint32_t v, uint32_t &nd) {
-        const int j = (int)nd;
-        const int k = s.rank[j];
-        if (BREADTH ? s.cnt(cur)[j] > 1 : (k >= 0 && k < n_proc))
-            nd = (uint32_t)s.cf[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])];
-        else
-            nd = (uint32_t)s.uf[j];
+        const int j = (int)(nd & 0xffffu);
+        const int x = (int)(v & 0xffff), y = (int)(v >> 16);
+        if (BREADTH) {
+            const int k1 = (int)(nd >> 16);
+            if (k1) {
+                const uint32_t w = (uint32_t)s.cf[4 * (k1 - 1) + qt_quadrant(x, y, s.box(cur)[j])];
+                nd = w;
+                if (w >> 16) atomicAdd(&s.ccnt(nxt)[4 * ((int)(w >> 16) - 1) + qt_quadrant(x, y, s.box(nxt)[w & 0xffffu])], 1);
+            } else {
+                nd = (uint32_t)s.uf[j];
+            }
+        } else {
+            const int k = (int)s.rank[j];
+            if (k < n_proc) nd = (uint32_t)s.cf[4 * k + qt_quadrant(x, y, s.box(cur)[j])];
+            else nd = (uint32_t)s.uf[j];
+        }
     });
     __syncthreads();
     *n_exp = (int)((tot >> QT_F) & QT_FMASK);
     return (int)(tot & QT_FMASK) + (int)(tot >> (2 * QT_F));
 }
 
-/* count the quarters of every ranked node; ccnt[0 .. 4 * ranked) must be zero on entry */
-template <int QT_NT, bool REG, bool BREADTH>
+/* ordered pass: count the quarters of every ranked node; ccnt(cur)[0 .. 4 * ranked) must be zero on entry */
+template <int QT_NT, bool REG>
 __device__ __forceinline__ void qt_count(const QtSmem &s, int cur, QtPts<QT_NT, REG> &pts)
 {
     pts.each([&](int, uint32_t v, uint32_t &nd) {
-        const int j = (int)nd;
-        const int k = s.rank[j];
-        if (BREADTH ? s.cnt(cur)[j] > 1 : k >= 0)
-            atomicAdd(&s.ccnt[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])], 1);
+        const int j = (int)(nd & 0xffffu);
+        const unsigned k = s.rank[j];
+        if (k != QT_NONE)
+            atomicAdd(&s.ccnt(cur)[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])], 1);
     });
     __syncthreads();
 }
@@ -259,16 +289,15 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         unsigned char *p = qt_raw;
         s.M = M;
         s.box_ = (int4 *)p; p += (size_t)M * 32;
-        s.best = (unsigned long long *)p; p += (size_t)M * 8;
+        s.ccnt_ = (int *)p; s.best = (unsigned long long *)p; p += (size_t)M * 32;
+        s.cf = (int *)p; p += (size_t)M * 16;
         s.wtmp = (qt_u64 *)p; p += 40 * 8;
         s.cnt_ = (int *)p; p += (size_t)M * 8;
-        s.rank = (int *)p; p += (size_t)M * 4;
-        s.par = (int *)p; p += (size_t)M * 4;
-        s.uf = (int *)p; p += (size_t)M * 4;
-        s.ccnt = (int *)p; p += (size_t)M * 16;
-        s.cf = (int *)p; p += (size_t)M * 16;
-        s.exp_pos_ = (int *)p; p += (size_t)M * 8;
-        s.exp_size_ = (int *)p;
+        s.exp_size_ = (int *)p; p += (size_t)M * 8 + 16;
+        s.par_ = (uint16_t *)p; p += (size_t)M * 4;
+        s.exp_pos_ = (uint16_t *)p; p += (size_t)M * 4;
+        s.rank = (uint16_t *)p; p += (size_t)M * 2;
+        s.uf = (uint16_t *)p;
     }
     const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
     const BorbLevel &L = plan->lv[level];
@@ -286,72 +315,69 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     /* ---- roots (:674-739): point -> root by FLOAT division, empty roots dropped ---- */
     const int n_ini = L.n_ini;
     const float hx = L.hx;
-    for (int j = tid; j < n_ini; j += QT_NT) s.ccnt[j] = 0;
+    int *const rootc = s.ccnt(1); /* the first breadth pass counts into ccnt(0) */
+    for (int j = tid; j < n_ini; j += QT_NT) rootc[j] = 0;
     __syncthreads();
     pts.init([&](uint32_t v) -> uint32_t {
         int r = (int)__fdiv_rn((float)(v & 0xffff), hx);
         r = min(max(r, 0), n_ini - 1);
-        atomicAdd(&s.ccnt[r], 1);
+        atomicAdd(&rootc[r], 1);
         return (uint32_t)r;
     });
     __syncthreads();
     int cur = 0;
-    /* The breadth passes rank the multi-point nodes in list order.  No scan is needed for that: among the roots the
-     * rank is a second field of the scan that drops the empty ones, and after a breadth pass every multi-point node is
-     * a child born in it (whatever stayed had one point), the children stand at the head of the new list in REVERSE
-     * creation order, and the split has numbered the multi-point ones e = 0 .. E-1 in creation order: rank = E-1-e. */
+    /* the scan that drops the empty roots also ranks the multi-point ones (list order) for the first breadth pass, and
+     * the relabelling step counts their quarters: from here on every breadth pass finds its ranks and counts ready */
     const qt_u64 tot0 = qt_scan_emit<QT_NT>(
-        n_ini, s.wtmp, [&](int j) -> qt_u64 { const int c = s.ccnt[j]; return (qt_u64)(c > 0) | ((qt_u64)(c > 1) << QT_F); },
+        n_ini, s.wtmp, [&](int j) -> qt_u64 { const int c = rootc[j]; return (qt_u64)(c > 0) | ((qt_u64)(c > 1) << QT_F); },
         [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
             if (g & 1) {
                 const int p = (int)(before & QT_FMASK);
                 s.box(0)[p] = make_int4((int)__fmul_rn(hx, (float)j), 0, (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
-                s.cnt(0)[p] = s.ccnt[j];
-                s.cf[j] = p;
+                s.cnt(0)[p] = rootc[j];
+                int word = p;
                 if (g >> QT_F) {
                     const int k = (int)(before >> QT_F);
-                    s.rank[p] = k;
-                    s.par[k] = p;
+                    s.par(0)[k] = (uint16_t)p;
+                    *reinterpret_cast<int4 *>(&s.ccnt(0)[4 * k]) = make_int4(0, 0, 0, 0);
+                    word |= (k + 1) << 16;
                 }
+                s.cf[j] = word;
             }
         });
     int S = (int)(tot0 & QT_FMASK);
     int n_exp = (int)(tot0 >> QT_F); /* multi-point nodes of the current list */
-    pts.each([&](int, uint32_t, uint32_t &nd) { nd = (uint32_t)s.cf[nd]; });
-    for (int c = tid; c < 4 * n_exp; c += QT_NT) s.ccnt[c] = 0;
+    pts.each([&](int, uint32_t v, uint32_t &nd) {
+        const uint32_t w = (uint32_t)s.cf[nd];
+        nd = w;
+        if (w >> 16)
+            atomicAdd(&s.ccnt(0)[4 * ((int)(w >> 16) - 1) + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(0)[w & 0xffffu])], 1);
+    });
     __syncthreads();
 
     /* ---- split passes (:741-927) ---- */
     static_assert(BORB_QT_MAXNODES <= (1 << QT_EBITS), "rank key");
+    static_assert(BORB_QT_MAXNODES < 0xffff, "16-bit positions and ranks");
     const bool packed = n < (1 << (31 - QT_EBITS)); /* (size << 11 | creation index) fits a positive int */
     bool done = (S == 0);
     while (!done) {
-        /* breadth pass: every multi-point node splits (rank, par and zeroed quarter counters are in place) */
+        /* breadth pass: every multi-point node splits */
         const int prev = S;
         const int n_split = n_exp;
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
-        qt_count<QT_NT, REG, true>(s, cur, pts);
         S = qt_split<QT_NT, REG, true>(s, cur, S, n_split, pts, &n_exp, packed);
         cur = 1 - cur;
         if (S >= N || S == prev) break;
-        if (S + 3 * n_exp <= N) {
-            for (int e = tid; e < n_exp; e += QT_NT) {
-                const int pos = s.exp_pos(cur)[e], k = n_exp - 1 - e;
-                s.rank[pos] = k;
-                s.par[k] = pos;
-                *reinterpret_cast<int4 *>(&s.ccnt[4 * k]) = make_int4(0, 0, 0, 0);
-            }
-            __syncthreads();
-            continue;
-        }
+        if (S + 3 * n_exp <= N) continue;
 
         /* ordered passes (:853-924) */
         while (true) {
             const int prev2 = S;
             const int E = n_exp;
             if (E == 0) { done = true; break; }
-            for (int j = tid; j < S; j += QT_NT) s.rank[j] = -1;
-            for (int c = tid; c < 4 * E; c += QT_NT) s.ccnt[c] = 0;
+            int *const ccnt = s.ccnt(cur);
+            for (int j = tid; j < S; j += QT_NT) s.rank[j] = (uint16_t)QT_NONE;
+            for (int c = tid; c < 4 * E; c += QT_NT) ccnt[c] = 0;
             if (tid == 0) sh_proc = E;
             if (tid < 4) s.exp_size(cur)[E + tid] = 0; /* padding of the rank keys (the array has 4 spare entries) */
             __syncthreads();
@@ -364,8 +390,8 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                         const int4 k = keys[f];
                         r += (k.x > key) + (k.y > key) + (k.z > key) + (k.w > key);
                     }
-                    s.rank[s.exp_pos(cur)[e]] = r;
-                    s.par[r] = s.exp_pos(cur)[e];
+                    s.rank[s.exp_pos(cur)[e]] = (uint16_t)r;
+                    s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
             } else {
                 for (int e = tid; e < E; e += QT_NT) {
@@ -375,17 +401,17 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                         const int sf = s.exp_size(cur)[f];
                         r += (sf > sz) || (sf == sz && f > e);
                     }
-                    s.rank[s.exp_pos(cur)[e]] = r;
-                    s.par[r] = s.exp_pos(cur)[e];
+                    s.rank[s.exp_pos(cur)[e]] = (uint16_t)r;
+                    s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
             }
             __syncthreads();
-            qt_count<QT_NT, REG, false>(s, cur, pts);
+            qt_count<QT_NT, REG>(s, cur, pts);
             /* size after processing ranks 0..k; stop at the first k reaching N */
             qt_scan_emit<QT_NT>(
                 E, s.wtmp,
                 [&](int k) -> qt_u64 {
-                    const int4 c = *reinterpret_cast<const int4 *>(&s.ccnt[4 * k]);
+                    const int4 c = *reinterpret_cast<const int4 *>(&ccnt[4 * k]);
                     return (qt_u64)((c.x > 0) + (c.y > 0) + (c.z > 0) + (c.w > 0) - 1);
                 },
                 [&](int k, qt_u64 g, qt_u64 before, qt_u64) {
@@ -411,7 +437,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                                        ((unsigned long long)(4095u - cc) << 32) |
                                        ((unsigned long long)(65535u - y) << 16) |
                                        (unsigned long long)(65535u - x);
-        atomicMax(&s.best[nd], key);
+        atomicMax(&s.best[nd & 0xffffu], key);
     });
     __syncthreads();
     uint32_t *oxy = lkp_xy + (size_t)frame * plan->kp_total + L.kp_off;

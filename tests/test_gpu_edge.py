@@ -203,3 +203,27 @@ def test_a_new_input_buffer_on_every_call(oracle_built):
     for k in range(6):  # a stable buffer again
         ext.extract_device(keep[0].data_ptr(), 1, shape[1], shape[0])
         assert _same(ext.fetch()[0], want[0])
+
+
+def test_alternating_frames_in_the_single_frame_shape(oracle_built):
+    """The single-frame shape launches FAST, the quadtree and the describe stage programmatically behind their
+    predecessors (griddepcontrol, borb_cta.cuh): a kernel that read its input before the predecessor had finished
+    would see the PREVIOUS call's candidates / survivors, which a repeated image cannot show.  Three very different
+    images in rotation (textured, noise, nearly flat), one and two frames per call, every result against the oracle's."""
+    from orb_slam2_test_b200 import ORBextractor
+    shape = synth.KITTI_SHAPE
+    flat = np.full(shape, 90, np.uint8)
+    flat[100:140, 300:360] = 160
+    imgs = [synth.make_frame(shape, seed=21, frame=0), synth.make_noise_frame(shape, seed=4), flat,
+            synth.make_frame(shape, seed=22, frame=5)]
+    ora = oracle_built.Oracle(2000, 1.2, 8, 20, 7)
+    want = [ora.extract(im) for im in imgs]
+    assert len({len(w[0]) for w in want}) >= 3 # the counts differ, so a stale count shows
+    one = ORBextractor(2000, 1.2, 8, 20, 7, max_batch=2, want_pyramid=False)
+    for it in range(120):
+        i = (it * 7 + it // 5) % len(imgs)
+        assert _same(one(imgs[i]), want[i]), f"call {it}, image {i}"
+        if it % 4 == 3:
+            j = (i + 1 + it % 3) % len(imgs)
+            res = one.extract_batch(np.stack([imgs[i], imgs[j]]))
+            assert _same(res[0], want[i]) and _same(res[1], want[j]), f"pair call {it}"
