@@ -2235,3 +2235,13 @@ extern "C" int borb_debug_fast_probe(unsigned long long *out, int n_words)
     return cudaMemcpyFromSymbol(out, g_fast_probe, (size_t)n_words * 8) == cudaSuccess ? BORB_OK : BORB_ERR_CUDA;
 }
 #endif
+
+#ifdef BORB_QT_PROBE
+/* development only (tools/probe_qt.py): the probe log of the last k_quadtree launch */
+extern "C" int borb_debug_qt_probe(unsigned long long *out, int *n_out)
+{
+    if (cudaDeviceSynchronize() != cudaSuccess) return BORB_ERR_CUDA;
+    if (cudaMemcpyFromSymbol(out, g_qt_probe, sizeof(unsigned long long) * 8 * 128 * 2) != cudaSuccess) return BORB_ERR_CUDA;
+    return cudaMemcpyFromSymbol(n_out, g_qt_probe_n, sizeof(int) * 8) == cudaSuccess ? BORB_OK : BORB_ERR_CUDA;
+}
+#endif

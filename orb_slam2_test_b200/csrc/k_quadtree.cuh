@@ -24,6 +24,29 @@
 #include "borb_internal.h"
 #include "borb_cta.cuh"
 
+/* -DBORB_QT_PROBE (tools/probe_qt.py, never in the shipped library): (tag, %globaltimer) log of thread 0 per level */
+#ifdef BORB_QT_PROBE
+__device__ unsigned long long g_qt_probe[8 * 128 * 2];
+__device__ int g_qt_probe_n[8];
+#define QT_PROBE(tag)                                                                          \
+    do {                                                                                       \
+        if (threadIdx.x == 0 && blockIdx.y == 0 && blockIdx.x < 8) {                           \
+            unsigned long long t_;                                                             \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                             \
+            const int k_ = g_qt_probe_n[blockIdx.x];                                           \
+            if (k_ < 128) {                                                                     \
+                g_qt_probe[(blockIdx.x * 128 + k_) * 2] = (unsigned long long)(tag);            \
+                g_qt_probe[(blockIdx.x * 128 + k_) * 2 + 1] = t_;                               \
+                g_qt_probe_n[blockIdx.x] = k_ + 1;                                             \
+            }                                                                                  \
+        }                                                                                      \
+    } while (0)
+#define QT_PROBE_RESET() do { if (threadIdx.x == 0 && blockIdx.y == 0 && blockIdx.x < 8) g_qt_probe_n[blockIdx.x] = 0; } while (0)
+#else
+#define QT_PROBE(tag) do { } while (0)
+#define QT_PROBE_RESET() do { } while (0)
+#endif
+
 /* threads per CTA is a template parameter: 256 for throughput (many (level, frame) CTAs in flight;
  * measured on B200 per 512 frames: 1024 -> 0.80 ms, 512 -> 0.51 ms, 256 -> 0.48 ms), 1024 for the
  * latency of a single frame (8 CTAs in total: 45 us vs 78 us) */
@@ -56,7 +79,9 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
         if (lane >= o) v += t;
     }
     if (lane == 31) wtmp[w] = v;
+    QT_PROBE(10);
     __syncthreads();
+    QT_PROBE(11);
     if (w == 0) {
         const qt_u64 t = lane < QT_NT / 32 ? wtmp[lane] : 0ull;
         qt_u64 u = t;
@@ -68,7 +93,9 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
         wtmp[lane] = u - t;
         if (lane == 31) wtmp[32] = u;
     }
+    QT_PROBE(12);
     __syncthreads();
+    QT_PROBE(13);
     qt_u64 run = wtmp[w] + v - s;
     const qt_u64 total = wtmp[32];
     for (int i = b; i < e; ++i) {
@@ -76,18 +103,25 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
         emit(i, g, run, total);
         run += g;
     }
+    QT_PROBE(14);
     __syncthreads();
+    QT_PROBE(15);
     return total;
 }
 
 struct QtSmem { /* the double-buffered arrays are base + buffer * M: no pointer table indexed at run time (local memory) */
-    int4 *box_;
+    ushort4 *box_; /* x0, y0, x1, y1 (candidate coordinates are 16-bit) */
+    uint32_t *mid_; /* the node's split point mx | my << 16: all the relabelling needs of a box, in one word */
     int *cnt_, *exp_size_, *ccnt_, *cf;
-    uint16_t *rank, *uf, *par_, *exp_pos_; /* list positions and ranks are < BORB_QT_MAXNODES = 2048 */
-    unsigned long long *best; /* on top of ccnt_ (dead by then) */
+    uint16_t *par_, *exp_pos_; /* list positions and ranks are < BORB_QT_MAXNODES = 2048 */
+    uint32_t *ru; /* per node: rank (low half, QT_NONE = not ranked) | new position if it stays (high half) */
+    unsigned long long *best;
     qt_u64 *wtmp;
     int M;
-    __device__ __forceinline__ int4 *box(int b) const { return box_ + b * M; }
+    __device__ __forceinline__ ushort4 *box(int b) const { return box_ + b * M; }
+    __device__ __forceinline__ uint32_t *mid(int b) const { return mid_ + b * M; }
+    __device__ __forceinline__ uint16_t &rank(int j) const { return reinterpret_cast<uint16_t *>(ru)[2 * j]; }
+    __device__ __forceinline__ uint16_t &uf(int j) const { return reinterpret_cast<uint16_t *>(ru)[2 * j + 1]; }
     __device__ __forceinline__ int *cnt(int b) const { return cnt_ + b * M; }
     __device__ __forceinline__ int *ccnt(int b) const { return ccnt_ + b * 4 * M; }
     __device__ __forceinline__ uint16_t *par(int b) const { return par_ + b * M; }
@@ -96,18 +130,24 @@ struct QtSmem { /* the double-buffered arrays are base + buffer * M: no pointer 
 };
 #define QT_NONE 0xffffu /* rank[] of a node that is not ranked */
 
-__device__ __forceinline__ int qt_quadrant(int x, int y, const int4 b)
+__device__ __forceinline__ uint32_t qt_mid(const ushort4 b)
 {
-    const int mx = b.x + ((b.z - b.x + 1) >> 1); /* x0 + ceil((x1-x0)/2) */
-    const int my = b.y + ((b.w - b.y + 1) >> 1);
-    return (y >= my) * 2 + (x >= mx);
+    const uint32_t mx = b.x + ((b.z - b.x + 1u) >> 1); /* x0 + ceil((x1-x0)/2) */
+    const uint32_t my = b.y + ((b.w - b.y + 1u) >> 1);
+    return mx | (my << 16);
 }
 
-__device__ __forceinline__ int4 qt_child_box(const int4 b, int q)
+/* quarter of candidate v = x | y << 16 in a node with split point m = mx | my << 16 */
+__device__ __forceinline__ int qt_quadrant(uint32_t v, uint32_t m)
 {
-    const int mx = b.x + ((b.z - b.x + 1) >> 1);
-    const int my = b.y + ((b.w - b.y + 1) >> 1);
-    int4 c;
+    return ((v >> 16) >= (m >> 16)) * 2 + ((v & 0xffffu) >= (m & 0xffffu));
+}
+
+__device__ __forceinline__ ushort4 qt_child_box(const ushort4 b, int q)
+{
+    const uint32_t m = qt_mid(b);
+    const unsigned short mx = (unsigned short)(m & 0xffffu), my = (unsigned short)(m >> 16);
+    ushort4 c;
     c.x = (q & 1) ? mx : b.x;
     c.z = (q & 1) ? b.z : mx;
     c.y = (q & 2) ? my : b.y;
@@ -118,9 +158,9 @@ __device__ __forceinline__ int4 qt_child_box(const int4 b, int q)
 /* bytes of dynamic shared memory for a list capacity of M nodes */
 static inline size_t qt_smem_bytes(int M)
 {
-    /* box 2x16, quarter counters 2x16, child positions 16, counts 2x4, rank keys 2x4, then the 16-bit arrays: par 2x2,
-     * exp_pos 2x2, rank 2, uf 2 */
-    return (size_t)M * (32 + 32 + 16 + 8 + 8 + 4 + 4 + 2 + 2) + 40 * 8 + 16; /* + 16: zero padding of the rank keys */
+    /* quarter counters 2x16, child positions 16, box 2x8, winner keys 8, split point 2x4, counts 2x4, rank keys 2x4, rank | stay
+     * position 4, then the 16-bit arrays: par 2x2, exp_pos 2x2 */
+    return (size_t)M * (32 + 16 + 16 + 8 + 8 + 8 + 8 + 4 + 4 + 4) + 40 * 8 + 16; /* + 16: zero padding of the rank keys */
 }
 
 /* The candidates of a (level, frame): in the latency shape (1024 threads, a CTA alone on its SM) a thread keeps
@@ -151,28 +191,59 @@ struct QtPts {
 #pragma unroll
             for (int u = 0; u < QT_RPT; ++u) {
                 const int i = threadIdx.x + u * QT_NT;
-                if (i < n) rnode[u] = body(rxy[u]);
+                rnode[u] = i < n ? body(rxy[u]) : 0u; /* unused slots: node word 0, a valid index for staged() */
             }
         } else {
             for (int i = threadIdx.x; i < n; i += QT_NT) node[i] = body(xy[i]);
         }
     }
-    /* body(i, xy, node&) for each of this thread's candidates */
-    template <typename F>
-    __device__ __forceinline__ void each(F body)
+    /* The per-candidate steps of a pass are chains of dependent shared-memory loads (node box -> child slot -> child
+     * box -> counter).  Run candidate by candidate, with a branch around each, the register-resident shape paid
+     * the whole chain once per candidate (1.2 us of a 2.1 us breadth pass, tools/probe_qt.py).  staged() runs the chain
+     * stage by stage over four candidates at a time: the stages take a Slot by reference and must be safe to run on an
+     * unused slot (ok == false, v == 0, nd == 0: every index they form has to stay inside its array; they must not
+     * store or count), so their loads carry no branch and four of them are in flight together. */
+    struct Slot {
+        int i;       /* candidate index */
+        uint32_t v;  /* x | y << 16 */
+        uint32_t nd; /* node word (written back after the last stage) */
+        bool ok;
+        uint32_t m, w, t; /* scratch of the stages */
+    };
+    template <typename A, typename B, typename C, typename D>
+    __device__ __forceinline__ void staged(A a, B b, C c, D d)
     {
         if (REG) {
 #pragma unroll
-            for (int u = 0; u < QT_RPT; ++u) {
-                const int i = threadIdx.x + u * QT_NT;
-                if (i < n) body(i, rxy[u], rnode[u]);
+            for (int h = 0; h < QT_RPT; h += 4) {
+                if (h * QT_NT >= n) break; /* the same for the whole CTA */
+                Slot sl[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    sl[u].i = threadIdx.x + (h + u) * QT_NT;
+                    sl[u].ok = sl[u].i < n;
+                    sl[u].v = rxy[h + u];
+                    sl[u].nd = rnode[h + u];
+                    sl[u].w = 0; sl[u].t = 0;
+                    a(sl[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) b(sl[u]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) c(sl[u]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    d(sl[u]);
+                    rnode[h + u] = sl[u].nd;
+                }
             }
         } else {
             for (int i = threadIdx.x; i < n; i += QT_NT) {
-                uint32_t nd = node[i];
-                const uint32_t before = nd;
-                body(i, xy[i], nd);
-                if (nd != before) node[i] = nd;
+                Slot sl;
+                sl.i = i; sl.ok = true; sl.v = xy[i]; sl.nd = node[i]; sl.w = 0; sl.t = 0;
+                const uint32_t before = sl.nd;
+                a(sl); b(sl); c(sl); d(sl);
+                if (sl.nd != before) node[i] = sl.nd;
             }
         }
     }
@@ -209,7 +280,7 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
             if (i < S) {
                 bool stays;
                 if (BREADTH) stays = s.cnt(cur)[i] <= 1;
-                else stays = (int)s.rank[i] >= n_proc; /* QT_NONE is larger than any rank */
+                else stays = (int)s.rank(i) >= n_proc; /* QT_NONE is larger than any rank */
                 g |= (qt_u64)stays << (2 * QT_F);
             }
             return g;
@@ -219,7 +290,9 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
             if (g & 1) {
                 const int n = ccnt[i];
                 const int p = C - 1 - (int)(before & QT_FMASK);
-                s.box(nxt)[p] = qt_child_box(s.box(cur)[s.par(cur)[i >> 2]], i & 3);
+                const ushort4 cb = qt_child_box(s.box(cur)[s.par(cur)[i >> 2]], i & 3);
+                s.box(nxt)[p] = cb;
+                s.mid(nxt)[p] = qt_mid(cb);
                 s.cnt(nxt)[p] = n;
                 int word = p;
                 if (n > 1) {
@@ -238,28 +311,44 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
             if ((g >> (2 * QT_F)) & 1) {
                 const int p = C + (int)(before >> (2 * QT_F));
                 s.box(nxt)[p] = s.box(cur)[i];
+                s.mid(nxt)[p] = s.mid(cur)[i];
                 s.cnt(nxt)[p] = s.cnt(cur)[i];
-                s.uf[i] = (uint16_t)p;
+                s.uf(i) = (uint16_t)p;
             }
         });
-    pts.each([&](int, uint32_t v, uint32_t &nd) {
-        const int j = (int)(nd & 0xffffu);
-        const int x = (int)(v & 0xffff), y = (int)(v >> 16);
-        if (BREADTH) {
-            const int k1 = (int)(nd >> 16);
-            if (k1) {
-                const uint32_t w = (uint32_t)s.cf[4 * (k1 - 1) + qt_quadrant(x, y, s.box(cur)[j])];
-                nd = w;
-                if (w >> 16) atomicAdd(&s.ccnt(nxt)[4 * ((int)(w >> 16) - 1) + qt_quadrant(x, y, s.box(nxt)[w & 0xffffu])], 1);
-            } else {
-                nd = (uint32_t)s.uf[j];
-            }
-        } else {
-            const int k = (int)s.rank[j];
-            if (k < n_proc) nd = (uint32_t)s.cf[4 * k + qt_quadrant(x, y, s.box(cur)[j])];
-            else nd = (uint32_t)s.uf[j];
-        }
-    });
+    typedef typename QtPts<QT_NT, REG>::Slot Slot;
+    if (BREADTH) {
+        pts.staged(
+            [&](Slot &p) { p.m = s.mid(cur)[p.nd & 0xffffu]; },
+            [&](Slot &p) { /* ONE load: the child slot of a node that splits, or the word whose high half is the new
+                              position of a node that stays */
+                const int k1 = (int)(p.nd >> 16);
+                const uint32_t *src = k1 ? reinterpret_cast<const uint32_t *>(s.cf) + 4 * (k1 - 1) + qt_quadrant(p.v, p.m)
+                                         : s.ru + (p.nd & 0xffffu);
+                const uint32_t w = *src;
+                p.w = p.ok ? (k1 ? w : w >> 16) : 0u;
+            },
+            [&](Slot &p) { p.m = s.mid(nxt)[p.w & 0xffffu]; },
+            [&](Slot &p) {
+                if (p.ok) p.nd = p.w;
+                if (p.w >> 16) atomicAdd(&s.ccnt(nxt)[4 * ((int)(p.w >> 16) - 1) + qt_quadrant(p.v, p.m)], 1);
+            });
+    } else {
+        pts.staged(
+            [&](Slot &p) {
+                p.m = s.mid(cur)[p.nd & 0xffffu];
+                p.t = s.ru[p.nd & 0xffffu]; /* rank | stay position << 16 */
+            },
+            [&](Slot &p) {
+                const int k = (int)(p.t & 0xffffu);
+                const bool split = k < n_proc;
+                const uint32_t ws = (uint32_t)s.cf[split ? 4 * k + qt_quadrant(p.v, p.m) : 0];
+                p.w = split ? ws : p.t >> 16;
+            },
+            [&](Slot &) {},
+            [&](Slot &p) { if (p.ok) p.nd = p.w; });
+    }
+    QT_PROBE(16);
     __syncthreads();
     *n_exp = (int)((tot >> QT_F) & QT_FMASK);
     return (int)(tot & QT_FMASK) + (int)(tot >> (2 * QT_F));
@@ -269,12 +358,16 @@ __device__ __forceinline__ int qt_split(const QtSmem &s, int cur, int S, int n_p
 template <int QT_NT, bool REG>
 __device__ __forceinline__ void qt_count(const QtSmem &s, int cur, QtPts<QT_NT, REG> &pts)
 {
-    pts.each([&](int, uint32_t v, uint32_t &nd) {
-        const int j = (int)(nd & 0xffffu);
-        const unsigned k = s.rank[j];
-        if (k != QT_NONE)
-            atomicAdd(&s.ccnt(cur)[4 * k + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(cur)[j])], 1);
-    });
+    typedef typename QtPts<QT_NT, REG>::Slot Slot;
+    pts.staged(
+        [&](Slot &p) {
+            p.m = s.mid(cur)[p.nd & 0xffffu];
+            p.t = s.rank(p.nd & 0xffffu);
+        },
+        [&](Slot &) {}, [&](Slot &) {},
+        [&](Slot &p) {
+            if (p.ok && p.t != QT_NONE) atomicAdd(&s.ccnt(cur)[4 * p.t + qt_quadrant(p.v, p.m)], 1);
+        });
     __syncthreads();
 }
 
@@ -288,16 +381,17 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     {
         unsigned char *p = qt_raw;
         s.M = M;
-        s.box_ = (int4 *)p; p += (size_t)M * 32;
-        s.ccnt_ = (int *)p; s.best = (unsigned long long *)p; p += (size_t)M * 32;
+        s.ccnt_ = (int *)p; p += (size_t)M * 32;
         s.cf = (int *)p; p += (size_t)M * 16;
+        s.box_ = (ushort4 *)p; p += (size_t)M * 16;
+        s.best = (unsigned long long *)p; p += (size_t)M * 8;
         s.wtmp = (qt_u64 *)p; p += 40 * 8;
+        s.mid_ = (uint32_t *)p; p += (size_t)M * 8;
         s.cnt_ = (int *)p; p += (size_t)M * 8;
         s.exp_size_ = (int *)p; p += (size_t)M * 8 + 16;
+        s.ru = (uint32_t *)p; p += (size_t)M * 4;
         s.par_ = (uint16_t *)p; p += (size_t)M * 4;
-        s.exp_pos_ = (uint16_t *)p; p += (size_t)M * 4;
-        s.rank = (uint16_t *)p; p += (size_t)M * 2;
-        s.uf = (uint16_t *)p;
+        s.exp_pos_ = (uint16_t *)p;
     }
     const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
     const BorbLevel &L = plan->lv[level];
@@ -307,6 +401,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     pts.xy = cand_xy + cbase;
     pts.node = cand_node + cbase;
     pts.n = n;
+    QT_PROBE(1 | (n << 8));
     pts.load();
     for (int i = tid * 8; i < n; i += QT_NT * 8) /* the scores are read once, at the very end: have them in L1 by then */
         asm volatile("prefetch.global.L1 [%0];" ::"l"(score + i));
@@ -317,6 +412,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     const float hx = L.hx;
     int *const rootc = s.ccnt(1); /* the first breadth pass counts into ccnt(0) */
     for (int j = tid; j < n_ini; j += QT_NT) rootc[j] = 0;
+    for (int j = tid; j < M; j += QT_NT) s.best[j] = 0ull; /* the winner keys of the last step: no barrier of their own */
     __syncthreads();
     pts.init([&](uint32_t v) -> uint32_t {
         int r = (int)__fdiv_rn((float)(v & 0xffff), hx);
@@ -325,6 +421,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         return (uint32_t)r;
     });
     __syncthreads();
+    QT_PROBE(2);
     int cur = 0;
     /* the scan that drops the empty roots also ranks the multi-point ones (list order) for the first breadth pass, and
      * the relabelling step counts their quarters: from here on every breadth pass finds its ranks and counts ready */
@@ -333,7 +430,10 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         [&](int j, qt_u64 g, qt_u64 before, qt_u64) {
             if (g & 1) {
                 const int p = (int)(before & QT_FMASK);
-                s.box(0)[p] = make_int4((int)__fmul_rn(hx, (float)j), 0, (int)__fmul_rn(hx, (float)(j + 1)), L.qt_h);
+                const ushort4 rb = make_ushort4((unsigned short)(int)__fmul_rn(hx, (float)j), 0,
+                                                (unsigned short)(int)__fmul_rn(hx, (float)(j + 1)), (unsigned short)L.qt_h);
+                s.box(0)[p] = rb;
+                s.mid(0)[p] = qt_mid(rb);
                 s.cnt(0)[p] = rootc[j];
                 int word = p;
                 if (g >> QT_F) {
@@ -347,14 +447,18 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         });
     int S = (int)(tot0 & QT_FMASK);
     int n_exp = (int)(tot0 >> QT_F); /* multi-point nodes of the current list */
-    pts.each([&](int, uint32_t v, uint32_t &nd) {
-        const uint32_t w = (uint32_t)s.cf[nd];
-        nd = w;
-        if (w >> 16)
-            atomicAdd(&s.ccnt(0)[4 * ((int)(w >> 16) - 1) + qt_quadrant((int)(v & 0xffff), (int)(v >> 16), s.box(0)[w & 0xffffu])], 1);
-    });
+    typedef typename QtPts<QT_NT, REG>::Slot Slot;
+    pts.staged(
+        [&](Slot &p) { p.w = p.ok ? (uint32_t)s.cf[p.nd] : 0u; },
+        [&](Slot &p) { p.m = s.mid(0)[p.w & 0xffffu]; },
+        [&](Slot &) {},
+        [&](Slot &p) {
+            if (p.ok) p.nd = p.w;
+            if (p.w >> 16) atomicAdd(&s.ccnt(0)[4 * ((int)(p.w >> 16) - 1) + qt_quadrant(p.v, p.m)], 1);
+        });
     __syncthreads();
 
+    QT_PROBE(3 | (S << 8));
     /* ---- split passes (:741-927) ---- */
     static_assert(BORB_QT_MAXNODES <= (1 << QT_EBITS), "rank key");
     static_assert(BORB_QT_MAXNODES < 0xffff, "16-bit positions and ranks");
@@ -367,6 +471,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         if (n_split == 0) break; /* list cannot grow: lNodes.size()==prevSize */
         S = qt_split<QT_NT, REG, true>(s, cur, S, n_split, pts, &n_exp, packed);
         cur = 1 - cur;
+        QT_PROBE(4 | (S << 8));
         if (S >= N || S == prev) break;
         if (S + 3 * n_exp <= N) continue;
 
@@ -376,12 +481,14 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
             const int E = n_exp;
             if (E == 0) { done = true; break; }
             int *const ccnt = s.ccnt(cur);
-            for (int j = tid; j < S; j += QT_NT) s.rank[j] = (uint16_t)QT_NONE;
+            for (int j = tid; j < S; j += QT_NT) s.rank(j) = (uint16_t)QT_NONE;
             for (int c = tid; c < 4 * E; c += QT_NT) ccnt[c] = 0;
             if (tid == 0) sh_proc = E;
             if (tid < 4) s.exp_size(cur)[E + tid] = 0; /* padding of the rank keys (the array has 4 spare entries) */
             __syncthreads();
-            if (packed) { /* rank = number of larger keys; four keys per shared-memory load (zero padding never counts) */
+            if (packed) { /* rank = number of larger keys; four keys per shared-memory load (zero padding never counts).
+                             (Four lanes per key, so that all 1024 threads of the single-frame shape compare: no change --
+                             the 2.2 us this step takes there, tools/probe_qt.py, are not the comparisons.) */
                 const int4 *keys = reinterpret_cast<const int4 *>(s.exp_size(cur));
                 for (int e = tid; e < E; e += QT_NT) {
                     const int key = s.exp_size(cur)[e];
@@ -390,7 +497,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                         const int4 k = keys[f];
                         r += (k.x > key) + (k.y > key) + (k.z > key) + (k.w > key);
                     }
-                    s.rank[s.exp_pos(cur)[e]] = (uint16_t)r;
+                    s.rank(s.exp_pos(cur)[e]) = (uint16_t)r;
                     s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
             } else {
@@ -401,12 +508,14 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                         const int sf = s.exp_size(cur)[f];
                         r += (sf > sz) || (sf == sz && f > e);
                     }
-                    s.rank[s.exp_pos(cur)[e]] = (uint16_t)r;
+                    s.rank(s.exp_pos(cur)[e]) = (uint16_t)r;
                     s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
             }
             __syncthreads();
+            QT_PROBE(5 | (E << 8));
             qt_count<QT_NT, REG>(s, cur, pts);
+            QT_PROBE(6);
             /* size after processing ranks 0..k; stop at the first k reaching N */
             qt_scan_emit<QT_NT>(
                 E, s.wtmp,
@@ -418,8 +527,10 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                     if (S + (int)before + (int)g >= N) atomicMin(&sh_proc, k + 1);
                 });
             const int n_proc = sh_proc;
+            QT_PROBE(7 | (n_proc << 8));
             S = qt_split<QT_NT, REG, false>(s, cur, S, n_proc, pts, &n_exp, packed);
             cur = 1 - cur;
+            QT_PROBE(8 | (S << 8));
             if (S >= N || S == prev2) { done = true; break; }
         }
     }
@@ -427,18 +538,20 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     /* ---- one survivor per node (:930-948) ---- */
     const uint32_t mh = 0xffffffffu / (uint32_t)L.h_cell + 1u, mw = 0xffffffffu / (uint32_t)L.w_cell + 1u; /* exact for 16-bit dividends */
     if (S > M) { if (tid == 0) atomicExch(err, 2); S = M; }
-    for (int j = tid; j < S; j += QT_NT) s.best[j] = 0ull;
-    __syncthreads();
-    pts.each([&](int i, uint32_t v, uint32_t &nd) {
-        const unsigned x = v & 0xffff, y = v >> 16;
-        const unsigned cr = L.h_cell > 1 ? __umulhi(y - 3, mh) : y - 3, cc = L.w_cell > 1 ? __umulhi(x - 3, mw) : x - 3;
-        const unsigned long long key = ((unsigned long long)score[i] << 56) |
-                                       ((unsigned long long)(4095u - cr) << 44) |
-                                       ((unsigned long long)(4095u - cc) << 32) |
-                                       ((unsigned long long)(65535u - y) << 16) |
-                                       (unsigned long long)(65535u - x);
-        atomicMax(&s.best[nd & 0xffffu], key);
-    });
+    pts.staged(
+        [&](Slot &p) { p.t = p.ok ? score[p.i] : 0u; },
+        [&](Slot &) {}, [&](Slot &) {},
+        [&](Slot &p) {
+            if (!p.ok) return;
+            const unsigned x = p.v & 0xffff, y = p.v >> 16;
+            const unsigned cr = L.h_cell > 1 ? __umulhi(y - 3, mh) : y - 3, cc = L.w_cell > 1 ? __umulhi(x - 3, mw) : x - 3;
+            const unsigned long long key = ((unsigned long long)p.t << 56) |
+                                           ((unsigned long long)(4095u - cr) << 44) |
+                                           ((unsigned long long)(4095u - cc) << 32) |
+                                           ((unsigned long long)(65535u - y) << 16) |
+                                           (unsigned long long)(65535u - x);
+            atomicMax(&s.best[p.nd & 0xffffu], key);
+        });
     __syncthreads();
     uint32_t *oxy = lkp_xy + (size_t)frame * plan->kp_total + L.kp_off;
     uint32_t *osc = lkp_score + (size_t)frame * plan->kp_total + L.kp_off;
@@ -450,6 +563,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
         osc[j] = (uint32_t)(b >> 56);
     }
     if (tid == 0) nlkp[frame * BORB_MAXL + level] = S;
+    QT_PROBE(9);
 }
 
 
@@ -464,6 +578,8 @@ k_quadtree(const __grid_constant__ BorbPlan plan_c, int M, const uint32_t *__res
     extern __shared__ __align__(16) unsigned char qt_raw[];
     __shared__ int sh_proc;
     const BorbLevel &L = plan->lv[blockIdx.x];
+    QT_PROBE_RESET();
+    QT_PROBE(0);
     /* The 1024-thread shape is the one launched programmatically behind K2 (a frame or two per call): what K2 wrote is
      * read with ordinary loads through pointers that exist only after the wait (borb_cta.cuh); the throughput shape
      * keeps the read-only loads the compiler derives from `const __restrict__`. */
