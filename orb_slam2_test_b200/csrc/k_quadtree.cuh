@@ -71,6 +71,7 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
     const int per = (len + QT_NT - 1) / QT_NT;
     const int b = min(tid * per, len), e = min(b + per, len);
     qt_u64 s = 0;
+#pragma unroll 1
     for (int i = b; i < e; ++i) s += gen(i);
     qt_u64 v = s;
 #pragma unroll
@@ -98,6 +99,7 @@ __device__ __forceinline__ qt_u64 qt_scan_emit(int len, qt_u64 *wtmp /* 33 words
     QT_PROBE(13);
     qt_u64 run = wtmp[w] + v - s;
     const qt_u64 total = wtmp[32];
+#pragma unroll 1
     for (int i = b; i < e; ++i) {
         const qt_u64 g = gen(i);
         emit(i, g, run, total);
@@ -411,7 +413,9 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     const int n_ini = L.n_ini;
     const float hx = L.hx;
     int *const rootc = s.ccnt(1); /* the first breadth pass counts into ccnt(0) */
+#pragma unroll 1
     for (int j = tid; j < n_ini; j += QT_NT) rootc[j] = 0;
+#pragma unroll 1
     for (int j = tid; j < M; j += QT_NT) s.best[j] = 0ull; /* the winner keys of the last step: no barrier of their own */
     __syncthreads();
     pts.init([&](uint32_t v) -> uint32_t {
@@ -481,7 +485,9 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
             const int E = n_exp;
             if (E == 0) { done = true; break; }
             int *const ccnt = s.ccnt(cur);
+#pragma unroll 1
             for (int j = tid; j < S; j += QT_NT) s.rank(j) = (uint16_t)QT_NONE;
+#pragma unroll 1
             for (int c = tid; c < 4 * E; c += QT_NT) ccnt[c] = 0;
             if (tid == 0) sh_proc = E;
             if (tid < 4) s.exp_size(cur)[E + tid] = 0; /* padding of the rank keys (the array has 4 spare entries) */
@@ -490,6 +496,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                              (Four lanes per key, so that all 1024 threads of the single-frame shape compare: no change --
                              the 2.2 us this step takes there, tools/probe_qt.py, are not the comparisons.) */
                 const int4 *keys = reinterpret_cast<const int4 *>(s.exp_size(cur));
+#pragma unroll 1
                 for (int e = tid; e < E; e += QT_NT) {
                     const int key = s.exp_size(cur)[e];
                     int r = 0;
@@ -501,9 +508,11 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                     s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
             } else {
+#pragma unroll 1
                 for (int e = tid; e < E; e += QT_NT) {
                     const int sz = s.exp_size(cur)[e];
                     int r = 0;
+#pragma unroll 1
                     for (int f = 0; f < E; ++f) {
                         const int sf = s.exp_size(cur)[f];
                         r += (sf > sz) || (sf == sz && f > e);
@@ -555,6 +564,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     __syncthreads();
     uint32_t *oxy = lkp_xy + (size_t)frame * plan->kp_total + L.kp_off;
     uint32_t *osc = lkp_score + (size_t)frame * plan->kp_total + L.kp_off;
+#pragma unroll 1
     for (int j = tid; j < S; j += QT_NT) {
         const unsigned long long b = s.best[j];
         const unsigned x = 65535u - (unsigned)(b & 0xffff), y = 65535u - (unsigned)((b >> 16) & 0xffff);
