@@ -333,6 +333,16 @@ int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &ta
     const int gx = std::max(1, Z.w / tw), gy = std::max(1, Z.h / th);
     std::vector<PyrChainTile> tiles((size_t)gx * gy);
     std::memset(tiles.data(), 0, tiles.size() * sizeof(PyrChainTile));
+    /* The cuts are not uniform: a tile on the image edge also writes its part of the reflect-101 frame at every level
+     * (19 rows / 19 + alignment columns whatever the level's size: 57 % more pixels than a middle tile at 1241 x 376), and
+     * the launch takes as long as its slowest tile (tools/probe_chain.py: 13.0 us against a median tile's 9.0), so the
+     * edge rows and columns of tiles are cut narrower by these weights. */
+    const char *ewx = getenv("BORB_PCH_WX"), *ewy = getenv("BORB_PCH_WY"); /* tuning knobs */
+    const double wx = ewx ? atof(ewx) : PCH_EDGE_WX, wy = ewy ? atof(ewy) : PCH_EDGE_WY;
+    std::vector<double> fx(gx + 1, 0.0), fy(gy + 1, 0.0);
+    for (int i = 0; i < gx; ++i) fx[i + 1] = fx[i] + ((i == 0 || i == gx - 1) && gx > 2 ? wx : 1.0);
+    for (int i = 0; i < gy; ++i) fy[i + 1] = fy[i] + ((i == 0 || i == gy - 1) && gy > 2 ? wy : 1.0);
+    auto cut = [](const std::vector<double> &f, int i, int n) { return (int)((double)n * f[i] / f.back()); };
     long long max_a = 0, max_b = 0, max_t = 0;
     for (int ty = 0; ty < gy; ++ty)
         for (int tx = 0; tx < gx; ++tx) {
@@ -341,9 +351,9 @@ int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &ta
             long long t = 0;
             for (int l = nl - 1; l >= 0; --l) {
                 const BorbLevel &L = P.lv[l];
-                const int ox0 = tx == 0 ? 0 : (int)((long long)tx * L.w / gx) & ~3;
-                const int ox1 = tx == gx - 1 ? L.w : (int)((long long)(tx + 1) * L.w / gx) & ~3;
-                const int oy0 = (int)((long long)ty * L.h / gy), oy1 = (int)((long long)(ty + 1) * L.h / gy);
+                const int ox0 = tx == 0 ? 0 : cut(fx, tx, L.w) & ~3;
+                const int ox1 = tx == gx - 1 ? L.w : cut(fx, tx + 1, L.w) & ~3;
+                const int oy0 = ty == 0 ? 0 : cut(fy, ty, L.h), oy1 = ty == gy - 1 ? L.h : cut(fy, ty + 1, L.h);
                 int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1; /* need(l), exclusive upper bounds */
                 const bool own = ox1 > ox0 && oy1 > oy0;
                 if (own) {
@@ -2243,5 +2253,14 @@ extern "C" int borb_debug_qt_probe(unsigned long long *out, int *n_out)
     if (cudaDeviceSynchronize() != cudaSuccess) return BORB_ERR_CUDA;
     if (cudaMemcpyFromSymbol(out, g_qt_probe, sizeof(unsigned long long) * 8 * 128 * 2) != cudaSuccess) return BORB_ERR_CUDA;
     return cudaMemcpyFromSymbol(n_out, g_qt_probe_n, sizeof(int) * 8) == cudaSuccess ? BORB_OK : BORB_ERR_CUDA;
+}
+#endif
+
+#ifdef BORB_PCH_PROBE
+/* development only (tools/probe_chain.py): the probe words of the last k_pyr_chain launch */
+extern "C" int borb_debug_chain_probe(unsigned long long *out, int n_words)
+{
+    if (cudaDeviceSynchronize() != cudaSuccess) return BORB_ERR_CUDA;
+    return cudaMemcpyFromSymbol(out, g_pch_probe, (size_t)n_words * 8) == cudaSuccess ? BORB_OK : BORB_ERR_CUDA;
 }
 #endif

@@ -390,6 +390,8 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
 #endif
 #define PCH_TW 20 /* tile size aimed at on the LAST level (measured, single KITTI frame: 24x16 -> 62.0, 20x16 -> 61.3, 20x12 -> 60.0 us per call) */
 #define PCH_TH 12
+#define PCH_EDGE_WX 0.5 /* relative width / height of the tiles on the image edge (borb_api.cu build_chain; measured, single KITTI frame, kernels p50: 1.0 x 1.0 51.3 us, 0.8 x 0.8 49.8, 0.6 x 0.5 49.2, 0.5 x 0.4 49.1, 0.4 x 0.3 48.8) */
+#define PCH_EDGE_WY 0.4
 
 struct PyrChainRect {
     short nx0, ny0, nw, nh;   /* rectangle of the level this CTA computes (level pixels) */
@@ -409,6 +411,22 @@ __host__ __device__ __forceinline__ int pch_pitch(int nw) { return (nw + 3) & ~3
 __device__ __forceinline__ uint32_t pch_magic(int w) { return w > 1 ? 0xffffffffu / (uint32_t)w + 1u : 0u; }
 __device__ __forceinline__ int pch_div(int i, uint32_t m, int w) { return w > 1 ? (int)__umulhi((uint32_t)i, m) : i; }
 
+/* -DBORB_PCH_PROBE (tools/probe_chain.py, never in the shipped library): %globaltimer of thread 0 per tile: entry, level 0
+ * staged, then per level: computed, written */
+#ifdef BORB_PCH_PROBE
+__device__ unsigned long long g_pch_probe[256 * 20];
+#define PCH_PROBE(k)                                                                       \
+    do {                                                                                   \
+        if (threadIdx.x == 0 && blockIdx.y == 0 && blockIdx.x < 256) {                     \
+            unsigned long long t_;                                                         \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                         \
+            g_pch_probe[blockIdx.x * 20 + (k)] = t_;                                       \
+        }                                                                                  \
+    } while (0)
+#else
+#define PCH_PROBE(k) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(PCH_NT)
 k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restrict__ tiles,
             const uint2 *__restrict__ gtabs, int tstride, const uint8_t *__restrict__ img, size_t step,
@@ -417,6 +435,7 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
     const BorbPlan *plan = &plan_c;
     extern __shared__ __align__(16) unsigned char pch_smem[];
     borb_pdl_launch_dependents(); /* K2's CTAs may take their places and set up while the chain runs */
+    PCH_PROBE(0);
     const int tid = threadIdx.x, nl = plan->nlevels;
     const PyrChainTile *const gT = tiles + blockIdx.x;
     uint2 *const tabs = reinterpret_cast<uint2 *>(pch_smem + off_t);
@@ -462,6 +481,7 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
         }
     }
     __syncthreads();
+    PCH_PROBE(1);
     const PyrChainRect *const sR = sT_.r;
     const int *const sToff = sT_.toff;
 
@@ -494,6 +514,7 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
             }
             __syncthreads();
         }
+        PCH_PROBE(2 + 2 * l);
             /* write the tile out, with the frame where it touches the image edge */
         if (r.ox1 > r.ox0 && r.oy1 > r.oy0) {
             const int ex0 = r.ox0 == 0 ? -BORB_XPAD : r.ox0, ex1 = r.ox1 == L.w ? L.pitch - BORB_XPAD : r.ox1;
@@ -518,6 +539,7 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
                 *reinterpret_cast<uint32_t *>(dst + (long long)py * L.pitch + px) = v;
             }
         }
+        PCH_PROBE(3 + 2 * l);
         }
 }
 
