@@ -152,6 +152,7 @@ struct borb_extractor {
      * handle (n == max_batch, the single-frame case) brings everything back with ONE copy; d_out_kp, d_out_desc,
      * d_nout, d_err and their h_ twins point into it */
     uint8_t *d_res = nullptr, *h_res = nullptr;
+    uint8_t *h_res_dev = nullptr; /* device alias of h_res (k_results_to_host), null if the platform has none */
     size_t res_bytes = 0, res_o_desc = 0, res_o_nout = 0, res_o_err = 0;
     BorbKpRec *d_out_kp = nullptr;
     uint8_t *d_out_desc = nullptr;
@@ -313,7 +314,7 @@ void free_geometry(borb_extractor *h)
     h->d_lkp_xy = h->d_lkp_score = nullptr; h->d_out_kp = nullptr; h->d_out_desc = nullptr;
     h->h_in = h->h_pyr = h->h_out_desc = nullptr; h->h_out_kp = nullptr;
     h->h_nout = h->h_err = nullptr;
-    h->d_res = h->h_res = nullptr; h->res_bytes = 0;
+    h->d_res = h->h_res = nullptr; h->h_res_dev = nullptr; h->res_bytes = 0;
     h->have_plan = false;
     h->results_on_host = h->pyramid_on_host = false;
     h->nout_frame_on_host = -1;
@@ -620,6 +621,11 @@ int build_plan(borb_extractor *h, int cols, int rows)
         CU(cudaMallocHost(&h->h_res, h->res_bytes));
         CU(cudaMemset(h->d_res, 0, h->res_bytes));
         std::memset(h->h_res, 0, h->res_bytes);
+        {
+            void *alias = nullptr;
+            if (cudaHostGetDevicePointer(&alias, h->h_res, 0) != cudaSuccess) { cudaGetLastError(); alias = nullptr; }
+            h->h_res_dev = (h->res_bytes % 16 == 0) ? static_cast<uint8_t *>(alias) : nullptr;
+        }
         h->d_out_kp = reinterpret_cast<BorbKpRec *>(h->d_res); h->h_out_kp = reinterpret_cast<BorbKpRec *>(h->h_res);
         h->d_out_desc = h->d_res + o_desc; h->h_out_desc = h->h_res + o_desc;
         h->d_nout = reinterpret_cast<int *>(h->d_res + o_nout); h->h_nout = reinterpret_cast<int *>(h->h_res + o_nout);
@@ -897,11 +903,28 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
     return BORB_OK;
 }
 
+/* The result slab of a frame or two goes to the host by a KERNEL (16-byte loads from the device slab, 16-byte stores
+ * through the device alias of the page-locked host slab) instead of a copy node: the copy engine's fixed cost -- about
+ * 9 of the 11 us the download of 122 KB added to a single-frame call -- is most of that call's download time.  Launched
+ * programmatically behind the last kernel of the chain. */
+__global__ void __launch_bounds__(256)
+k_results_to_host(const uint4 *src_p, uint4 *__restrict__ dst, int n16)
+{
+    borb_pdl_wait();
+    const uint4 *src = borb_pdl_after_wait(src_p);
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n16; i += gridDim.x * 256) dst[i] = src[i];
+}
+
 int enqueue_fetch(borb_extractor *h, int n, unsigned flags)
 {
     const BorbPlan &P = h->plan;
     cudaStream_t st = h->stream;
-    if (n == h->max_batch) { /* the whole result slab in one copy */
+    static const bool fetch_copy = getenv("BORB_FETCH_COPY") != nullptr; /* A/B knob: always the copy engine */
+    if (n == h->max_batch && n <= 2 && h->h_res_dev && !fetch_copy) {
+        const int n16 = (int)(h->res_bytes / 16);
+        CU(launch_k(k_results_to_host, dim3((unsigned)std::min(h->n_sm, (n16 + 255) / 256)), dim3(256), (size_t)0, st, true,
+                    (const uint4 *)h->d_res, (uint4 *)h->h_res_dev, n16));
+    } else if (n == h->max_batch) { /* the whole result slab in one copy */
         CU(cudaMemcpyAsync(h->h_res, h->d_res, h->res_bytes, cudaMemcpyDeviceToHost, st));
     } else {
         CU(cudaMemcpyAsync(h->h_nout, h->d_nout, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
