@@ -280,8 +280,8 @@ int borb_stream_push(borb_stream *s, const uint8_t *left, const uint8_t *right, 
                 for (int f = 0; f < n; ++f) {
                     const uint8_t *p = img[e] + (size_t)f * stride;
                     uint8_t *d = sl.h_in[e] + (size_t)f * fsz;
-                    if (step == rowb) std::memcpy(d, p, fsz);
-                    else for (int y = 0; y < s->rows; ++y) std::memcpy(d + (size_t)y * rowb, p + (size_t)y * step, rowb);
+                    if (step == rowb) pack_copy(d, p, fsz); /* streaming stores: borb_api.cu */
+                    else for (int y = 0; y < s->rows; ++y) pack_copy(d + (size_t)y * rowb, p + (size_t)y * step, rowb);
                 }
         }
         CU(cudaMemcpyAsync(sl.d_in[e], src, (size_t)n * fsz, cudaMemcpyHostToDevice, s->up));
