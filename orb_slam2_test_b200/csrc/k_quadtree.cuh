@@ -49,8 +49,11 @@ __device__ int g_qt_probe_n[8];
 
 /* threads per CTA is a template parameter: 256 for throughput (many (level, frame) CTAs in flight;
  * measured on B200 per 512 frames: 1024 -> 0.80 ms, 512 -> 0.51 ms, 256 -> 0.48 ms), 1024 for the
- * latency of a single frame (8 CTAs in total: 45 us vs 78 us) */
+ * latency of a single frame (8 CTAs in total: 45 us vs 78 us); re-measured with the round-2 kernel: 128 -> 0.32 ms,
+ * 256 -> 0.216, 512 -> 0.246 */
+#ifndef QT_NT_THROUGHPUT
 #define QT_NT_THROUGHPUT 256
+#endif
 #define QT_NT_LATENCY 1024
 
 /* Block-wide exclusive scan of up to three 21-bit fields packed in a 64-bit word.  gen(i) is the
