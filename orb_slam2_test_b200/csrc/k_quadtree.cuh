@@ -494,10 +494,12 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
             for (int c = tid; c < 4 * E; c += QT_NT) ccnt[c] = 0;
             if (tid == 0) sh_proc = E;
             if (tid < 4) s.exp_size(cur)[E + tid] = 0; /* padding of the rank keys (the array has 4 spare entries) */
+            QT_PROBE(17);
             __syncthreads();
+            QT_PROBE(18);
             if (packed) { /* rank = number of larger keys; four keys per shared-memory load (zero padding never counts).
-                             (Four lanes per key, so that all 1024 threads of the single-frame shape compare: no change --
-                             the 2.2 us this step takes there, tools/probe_qt.py, are not the comparisons.) */
+                             (Four or eight lanes per key, so that all 1024 threads of the single-frame shape compare:
+                             no faster, with eight 2.9 us against 1.5 for this step, tools/probe_qt.py.) */
                 const int4 *keys = reinterpret_cast<const int4 *>(s.exp_size(cur));
 #pragma unroll 1
                 for (int e = tid; e < E; e += QT_NT) {
@@ -524,6 +526,7 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
                     s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
             }
+            QT_PROBE(19);
             __syncthreads();
             QT_PROBE(5 | (E << 8));
             qt_count<QT_NT, REG>(s, cur, pts);

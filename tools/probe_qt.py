@@ -12,7 +12,7 @@ lib = one._lib
 names = {0: "entry", 1: "after wait (n)", 2: "roots counted", 3: "roots listed (S)", 4: "breadth pass (S)", 5: "ordered: ranked (E)",
          6: "ordered: counted", 7: "ordered: prefix (n_proc)", 8: "ordered pass (S)", 9: "end",
          10: "  scan: own sums + warp scan", 11: "  scan: barrier 1", 12: "  scan: warp 0", 13: "  scan: barrier 2", 14: "  scan: emit", 15: "  scan: barrier 3",
-         16: "  relabel (+count)"}
+         16: "  relabel (+count)", 17: "  ordered: reset issued", 18: "  ordered: reset barrier", 19: "  ordered: ranks computed"}
 for rep in range(5):
     one.extract_device(dev.data_ptr(), 1, 1241, 376); one.sync()
     if rep < 4: continue
