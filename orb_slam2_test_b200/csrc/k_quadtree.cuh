@@ -499,16 +499,20 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
             QT_PROBE(18);
             if (packed) { /* rank = number of larger keys; four keys per shared-memory load (zero padding never counts).
                              (Four or eight lanes per key, so that all 1024 threads of the single-frame shape compare:
-                             no faster, with eight 2.9 us against 1.5 for this step, tools/probe_qt.py.) */
+                             no faster, with eight 2.9 us against 1.5 for this step, tools/probe_qt.py.  The step is its instruction
+                             count: E * E / 32 warp-level compares at three instructions each (compare, add, select) on the
+                             E / 32 warps that have keys.) */
                 const int4 *keys = reinterpret_cast<const int4 *>(s.exp_size(cur));
 #pragma unroll 1
                 for (int e = tid; e < E; e += QT_NT) {
                     const int key = s.exp_size(cur)[e];
-                    int r = 0;
+                    int r0 = 0, r1 = 0, r2 = 0, r3 = 0; /* four chains, not one of 4 * E / 4 dependent adds */
+#pragma unroll 4
                     for (int f = 0; f < (E + 3) >> 2; ++f) {
                         const int4 k = keys[f];
-                        r += (k.x > key) + (k.y > key) + (k.z > key) + (k.w > key);
+                        r0 += k.x > key; r1 += k.y > key; r2 += k.z > key; r3 += k.w > key;
                     }
+                    const int r = (r0 + r1) + (r2 + r3);
                     s.rank(s.exp_pos(cur)[e]) = (uint16_t)r;
                     s.par(cur)[r] = s.exp_pos(cur)[e];
                 }
