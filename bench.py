@@ -1182,6 +1182,18 @@ def run_ours(args, rank, world, local):
                 ts.append((time.perf_counter() - t1) * 1e6)
             lat[name] = float(np.percentile(ts, 50))
             lat[name.replace("p50", "p99")] = float(np.percentile(ts, 99))
+        # the same call with the frame in page-locked memory (borb_host_alloc): uploaded from where it lies, no pack
+        from orb_slam2_test_b200.extractor import pinned_empty
+        pimg = pinned_empty(img.shape)
+        pimg[...] = img
+        for _ in range(20):
+            one._lib.borb_extract_host(one._h, pimg.ctypes.data, 1, COLS, ROWS, COLS, 0, 0)
+        ts = []
+        for _ in range(300):
+            t1 = time.perf_counter()
+            one._lib.borb_extract_host(one._h, pimg.ctypes.data, 1, COLS, ROWS, COLS, 0, 0)
+            ts.append((time.perf_counter() - t1) * 1e6)
+        lat["p50_us_page_locked_input"] = float(np.percentile(ts, 50))
         dptr = dev.data_ptr()
         ks = []
         for _ in range(200):
