@@ -414,3 +414,21 @@ def test_search_by_sim3_on_the_device(kw, oracle_built):
         assert bad.size == 0 and nf == wnf, f"sim3 th={th}: {bad.size} differ, nFound {nf} vs {wnf}"
         total += nf
     assert total > 100
+
+
+@pytest.mark.parametrize("seed", [11, 12, 13, 14, 15, 16])
+def test_back_end_matchers_over_more_scenes(seed, oracle_built):
+    """Relocalisation, Fuse and SearchBySim3 once more, on scenes and pose offsets the cases above do not use (the
+    offsets sit between theirs, so scale prediction lands on other sides of the octave boundaries): still identical."""
+    dz = (-1.3, -0.45, 0.15, 0.55, 1.2, 1.7)[seed - 11]
+    assert _check_reloc(f"reloc sweep {seed}", oracle_built, settings=((10.0, 100),), seed=seed, dz=dz)[0] > 300
+    assert _check_fuse(f"fuse sweep {seed}", oracle_built, ths=(3.0,), seed=seed, dz=0.25 * dz) > 50
+    k1, k2, cam, bounds, scale, inv_sigma2, log_scale, p1, p2, pre12, s12, R12, t12 = matchcase.make_sim3_pair_case(
+        seed=seed, s12=1.0 + 0.02 * dz, dz=0.2 * dz)
+    args = (synth.KITTI_SHAPE, matchcase.KITTI_K, (0.0, 0.0, 0.0, 0.0), 2000)
+    h1, h2 = _loaded(k1, *args), _loaded(k2, *args)
+    T12, T21 = oracle_built.sim3_relative(s12, R12, t12)
+    want, wnf = oracle_built.search_by_sim3(k1, k2, cam, bounds, scale, log_scale, p1, p2, pre12, s12, R12, t12, 7.5)
+    got, nf = h1.search_by_sim3(h2, p1, p2, k1["Tcw"], k2["Tcw"], T12, T21, 7.5, pre12)
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0 and nf == wnf, f"sim3 sweep {seed}: {bad.size} differ, nFound {nf} vs {wnf}"
