@@ -557,30 +557,59 @@ __device__ __forceinline__ void qt_run(const BorbPlan *plan, int M, const uint32
     /* ---- one survivor per node (:930-948) ---- */
     const uint32_t mh = 0xffffffffu / (uint32_t)L.h_cell + 1u, mw = 0xffffffffu / (uint32_t)L.w_cell + 1u; /* exact for 16-bit dividends */
     if (S > M) { if (tid == 0) atomicExch(err, 2); S = M; }
-    pts.staged(
-        [&](Slot &p) { p.t = p.ok ? score[p.i] : 0u; },
-        [&](Slot &) {}, [&](Slot &) {},
-        [&](Slot &p) {
-            if (!p.ok) return;
-            const unsigned x = p.v & 0xffff, y = p.v >> 16;
-            const unsigned cr = L.h_cell > 1 ? __umulhi(y - 3, mh) : y - 3, cc = L.w_cell > 1 ? __umulhi(x - 3, mw) : x - 3;
-            const unsigned long long key = ((unsigned long long)p.t << 56) |
-                                           ((unsigned long long)(4095u - cr) << 44) |
-                                           ((unsigned long long)(4095u - cc) << 32) |
-                                           ((unsigned long long)(65535u - y) << 16) |
-                                           (unsigned long long)(65535u - x);
-            atomicMax(&s.best[p.nd & 0xffffu], key);
-        });
-    __syncthreads();
     uint32_t *oxy = lkp_xy + (size_t)frame * plan->kp_total + L.kp_off;
     uint32_t *osc = lkp_score + (size_t)frame * plan->kp_total + L.kp_off;
+    /* The winner of a node is its maximum under (score, then the reference's input order: cell row, cell column, y, x).
+     * When a level has fewer than 64 x 64 cells of at most 64 x 64 pixels -- every level of an image up to ~1900 pixels
+     * a side -- that order fits 32 bits (score 8 | cell row 6 | cell column 6 | y in cell 6 | x in cell 6, the last four
+     * complemented) and shared memory has a native 32-bit atomic max; the 64-bit key needs a compare-and-swap loop per
+     * candidate (ATOMS.CAST.SPIN). */
+    const bool k32 = L.h_cell <= 64 && L.w_cell <= 64 && L.n_rows <= 64 && L.n_cols <= 64;
+    if (k32) {
+        uint32_t *const b32 = reinterpret_cast<uint32_t *>(s.best); /* zeroed with the 64-bit entries */
+        pts.staged(
+            [&](Slot &p) { p.t = p.ok ? score[p.i] : 0u; },
+            [&](Slot &) {}, [&](Slot &) {},
+            [&](Slot &p) {
+                if (!p.ok) return;
+                const unsigned x3 = (p.v & 0xffff) - 3u, y3 = (p.v >> 16) - 3u;
+                const unsigned cr = L.h_cell > 1 ? __umulhi(y3, mh) : y3, cc = L.w_cell > 1 ? __umulhi(x3, mw) : x3;
+                const unsigned yin = y3 - cr * (unsigned)L.h_cell, xin = x3 - cc * (unsigned)L.w_cell;
+                atomicMax(&b32[p.nd & 0xffffu], (p.t << 24) | ((63u - cr) << 18) | ((63u - cc) << 12) | ((63u - yin) << 6) | (63u - xin));
+            });
+        __syncthreads();
 #pragma unroll 1
-    for (int j = tid; j < S; j += QT_NT) {
-        const unsigned long long b = s.best[j];
-        const unsigned x = 65535u - (unsigned)(b & 0xffff), y = 65535u - (unsigned)((b >> 16) & 0xffff);
-        /* back to level pixel coordinates (:1116-1117) */
-        oxy[j] = (x + BORB_FAST_MARGIN) | ((y + BORB_FAST_MARGIN) << 16);
-        osc[j] = (uint32_t)(b >> 56);
+        for (int j = tid; j < S; j += QT_NT) {
+            const uint32_t b = b32[j];
+            const unsigned cr = 63u - ((b >> 18) & 63u), cc = 63u - ((b >> 12) & 63u), yin = 63u - ((b >> 6) & 63u), xin = 63u - (b & 63u);
+            const unsigned x = 3u + cc * (unsigned)L.w_cell + xin, y = 3u + cr * (unsigned)L.h_cell + yin;
+            oxy[j] = (x + BORB_FAST_MARGIN) | ((y + BORB_FAST_MARGIN) << 16); /* back to level pixel coordinates (:1116-1117) */
+            osc[j] = b >> 24;
+        }
+    } else {
+        pts.staged(
+            [&](Slot &p) { p.t = p.ok ? score[p.i] : 0u; },
+            [&](Slot &) {}, [&](Slot &) {},
+            [&](Slot &p) {
+                if (!p.ok) return;
+                const unsigned x = p.v & 0xffff, y = p.v >> 16;
+                const unsigned cr = L.h_cell > 1 ? __umulhi(y - 3, mh) : y - 3, cc = L.w_cell > 1 ? __umulhi(x - 3, mw) : x - 3;
+                const unsigned long long key = ((unsigned long long)p.t << 56) |
+                                               ((unsigned long long)(4095u - cr) << 44) |
+                                               ((unsigned long long)(4095u - cc) << 32) |
+                                               ((unsigned long long)(65535u - y) << 16) |
+                                               (unsigned long long)(65535u - x);
+                atomicMax(&s.best[p.nd & 0xffffu], key);
+            });
+        __syncthreads();
+#pragma unroll 1
+        for (int j = tid; j < S; j += QT_NT) {
+            const unsigned long long b = s.best[j];
+            const unsigned x = 65535u - (unsigned)(b & 0xffff), y = 65535u - (unsigned)((b >> 16) & 0xffff);
+            /* back to level pixel coordinates (:1116-1117) */
+            oxy[j] = (x + BORB_FAST_MARGIN) | ((y + BORB_FAST_MARGIN) << 16);
+            osc[j] = (uint32_t)(b >> 56);
+        }
     }
     if (tid == 0) nlkp[frame * BORB_MAXL + level] = S;
     QT_PROBE(9);

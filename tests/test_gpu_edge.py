@@ -227,3 +227,20 @@ def test_alternating_frames_in_the_single_frame_shape(oracle_built):
             j = (i + 1 + it % 3) % len(imgs)
             res = one.extract_batch(np.stack([imgs[i], imgs[j]]))
             assert _same(res[0], want[i]) and _same(res[1], want[j]), f"pair call {it}"
+
+
+def test_very_wide_image_uses_the_64_bit_winner_keys(oracle_built):
+    """More than 64 cell columns on level 0 (2200 px / 30): the quadtree's winner keys no longer fit 32 bits on that
+    level (k_quadtree.cuh) while the smaller levels still take the 32-bit path; textured and noise frame, one frame per
+    call and as a batch, against the oracle."""
+    from orb_slam2_test_b200 import ORBextractor
+    shape = (300, 2200)
+    ora = oracle_built.Oracle(1500, 1.2, 8, 20, 7)
+    imgs = [synth.make_frame(shape, seed=41, frame=0), synth.make_noise_frame(shape, seed=6), synth.make_frame(shape, seed=42, frame=3)]
+    want = [ora.extract(im) for im in imgs]
+    one = ORBextractor(1500, 1.2, 8, 20, 7, max_batch=1, want_pyramid=False)
+    for im, w in zip(imgs, want):
+        assert _same(one(im), w)
+    big = ORBextractor(1500, 1.2, 8, 20, 7, max_batch=3, want_pyramid=False)
+    for r, w in zip(big.extract_batch(np.stack(imgs)), want):
+        assert _same(r, w)
