@@ -392,12 +392,17 @@ int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &ta
     max_t = align_up(max_t, 16);
     const long long off_b = align_up(max_a, 16), off_t = align_up(off_b + max_b, 16), total = off_t + max_t;
     if (total > 160 * 1024) return BORB_OK; /* tiles of this geometry do not fit: the per-level kernels serve every shape */
-    /* per tile: table offsets, loop divisors, and the tap tables themselves relative to the source rectangles --
-     * x entries {sx | sx1 << 16, a0 | a1 << 16} (padded to a multiple of 4 with copies of the last), then y entries
-     * {sy0 | sy1 << 16, b0 | b1 << 16} -- so that the kernel's prologue is plain copies with no dependent loads */
+    /* per tile: table offsets, loop divisors, and the tap tables themselves relative to the source rectangles, so that
+     * the kernel's prologue is plain copies with no dependent loads.  x part, three entries per OUTPUT WORD (four pixels,
+     * the row padded to a multiple of 4 with copies of the last pixel): the four taps of pixels 0, 1 lie within two
+     * aligned words of the staged source row and so do those of pixels 2, 3 (scale factors up to 3), so an entry holds
+     * {word A | word B << 16, PRMT selector A | selector B << 16} -- a selector gathers x0, x1 of one pixel into bytes
+     * 0, 1 and of the next into bytes 2, 3 -- then {a0 | a1 << 16} of pixels 0, 1 and of pixels 2, 3 (dp2a operands).
+     * Then the y entries {sy0 | sy1 << 16, b0 | b1 << 16}. */
     const size_t tstride = (size_t)max_t / 8;
     std::vector<uint2> tabs(tiles.size() * tstride, make_uint2(0u, 0u));
     auto magic = [](int w) { return w > 1 ? 0xffffffffu / (uint32_t)w + 1u : 0u; };
+    bool chain_ok = true;
     for (size_t t = 0; t < tiles.size(); ++t) {
         PyrChainTile &T = tiles[t];
         uint2 *tab = &tabs[t * tstride];
@@ -412,22 +417,42 @@ int build_chain(borb_extractor *h, const BorbPlan &P, const std::vector<int> &ta
             if (l == 0 || r.nw == 0) continue;
             const BorbLevel &S = P.lv[l - 1];
             const PyrChainRect &q = T.r[l - 1];
-            const int nx = pch_pitch(r.nw);
-            for (int j = 0; j < nx; ++j) {
-                const int x = r.nx0 + std::min(j, r.nw - 1), sx = tab_i[L.xofs_off + x];
-                tab[off + j].x = (uint32_t)(sx - q.nx0) | ((uint32_t)(std::min(sx + 1, S.w - 1) - q.nx0) << 16);
-                tab[off + j].y = (uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x] | ((uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x + 1] << 16);
+            const int nx = pch_pitch(r.nw), nxe = 3 * (nx / 4);
+            for (int w = 0; w < nx / 4; ++w) {
+                int x0[4], x1[4];
+                uint32_t wgt[4];
+                for (int k = 0; k < 4; ++k) {
+                    const int x = r.nx0 + std::min(4 * w + k, r.nw - 1), sx = tab_i[L.xofs_off + x];
+                    x0[k] = sx - q.nx0;
+                    x1[k] = std::min(sx + 1, S.w - 1) - q.nx0;
+                    wgt[k] = (uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x] | ((uint32_t)(uint16_t)tab_s[L.xa_off + 2 * x + 1] << 16);
+                }
+                uint32_t base[2], sel[2];
+                for (int pr = 0; pr < 2; ++pr) {
+                    const int k = 2 * pr, lo = std::min(std::min(x0[k], x1[k]), std::min(x0[k + 1], x1[k + 1]));
+                    const int hi = std::max(std::max(x0[k], x1[k]), std::max(x0[k + 1], x1[k + 1]));
+                    const int b = lo >> 2;
+                    if (lo < 0 || hi - 4 * b > 7) chain_ok = false; /* a scale factor above 3: the per-level kernels serve it */
+                    base[pr] = (uint32_t)b;
+                    sel[pr] = (uint32_t)(x0[k] - 4 * b) | ((uint32_t)(x1[k] - 4 * b) << 4) | ((uint32_t)(x0[k + 1] - 4 * b) << 8) |
+                              ((uint32_t)(x1[k + 1] - 4 * b) << 12);
+                }
+                tab[off + 3 * w].x = base[0] | (base[1] << 16);
+                tab[off + 3 * w].y = (sel[0] & 0xffffu) | ((sel[1] & 0xffffu) << 16);
+                tab[off + 3 * w + 1].x = wgt[0]; tab[off + 3 * w + 1].y = wgt[1];
+                tab[off + 3 * w + 2].x = wgt[2]; tab[off + 3 * w + 2].y = wgt[3];
             }
             for (int j = 0; j < r.nh; ++j) {
                 const int y = r.ny0 + j, sy = tab_i[L.yofs_off + y];
                 const int sy0 = std::min(std::max(sy, 0), S.h - 1), sy1 = std::min(std::max(sy + 1, 0), S.h - 1);
-                tab[off + nx + j].x = (uint32_t)(sy0 - q.ny0) | ((uint32_t)(sy1 - q.ny0) << 16);
-                tab[off + nx + j].y = (uint32_t)(uint16_t)tab_s[L.yb_off + 2 * y] | ((uint32_t)(uint16_t)tab_s[L.yb_off + 2 * y + 1] << 16);
+                tab[off + nxe + j].x = (uint32_t)(sy0 - q.ny0) | ((uint32_t)(sy1 - q.ny0) << 16);
+                tab[off + nxe + j].y = (uint32_t)(uint16_t)tab_s[L.yb_off + 2 * y] | ((uint32_t)(uint16_t)tab_s[L.yb_off + 2 * y + 1] << 16);
             }
-            off += nx + r.nh;
+            off += nxe + r.nh;
         }
         T.toff[nl] = off;
     }
+    if (!chain_ok) return BORB_OK; /* chain_tiles stays 0 */
     CU(cudaMalloc(&h->d_chain, tiles.size() * sizeof(PyrChainTile)));
     CU(cudaMemcpy(h->d_chain, tiles.data(), tiles.size() * sizeof(PyrChainTile), cudaMemcpyHostToDevice));
     CU(cudaMalloc(&h->d_chain_tabs, tabs.size() * sizeof(uint2)));

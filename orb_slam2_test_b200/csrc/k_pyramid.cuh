@@ -493,23 +493,30 @@ k_pyr_chain(const __grid_constant__ BorbPlan plan_c, const PyrChainTile *__restr
         if (l > 0) {
             const uint8_t *const sbuf = pch_smem + ((l & 1) ? 0 : off_b);
             const int spitch = pch_pitch(sR[l - 1].nw);
-            const uint2 *const xt = tabs + sToff[l], *const yt = xt + pitch;
             const int wpr = pitch >> 2;
+            const uint2 *const xt = tabs + sToff[l], *const yt = xt + 3 * wpr;
             const uint32_t wm = sT_.magic[l][0];
             for (int i = tid; i < wpr * r.nh; i += PCH_NT) {
                 const int y = pch_div(i, wm, wpr), xw = i - y * wpr;
                 const uint2 ey = yt[y];
-                const uint8_t *row0 = sbuf + (ey.x & 0xffffu) * spitch, *row1 = sbuf + (ey.x >> 16) * spitch;
+                const uint32_t *row0 = reinterpret_cast<const uint32_t *>(sbuf + (ey.x & 0xffffu) * spitch);
+                const uint32_t *row1 = reinterpret_cast<const uint32_t *>(sbuf + (ey.x >> 16) * spitch);
                 const uint32_t b0 = ey.y << 16, b1 = ey.y & 0xffff0000u;
+                /* four pixels: two aligned words of each source row per pixel pair, one PRMT gathers the pair's four taps
+                 * (x0, x1 of the first pixel in bytes 0, 1, of the second in bytes 2, 3), one dp2a per pixel and row is
+                 * the horizontal blend (build_chain in borb_api.cu lays the table out) */
+                const uint2 e0 = xt[3 * xw], e1 = xt[3 * xw + 1], e2 = xt[3 * xw + 2];
+                const uint32_t wa = e0.x & 0xffffu, wb = e0.x >> 16, sa = e0.y & 0xffffu, sb = e0.y >> 16;
+                const uint32_t ta0 = __byte_perm(row0[wa], row0[wa + 1], sa), tb0 = __byte_perm(row0[wb], row0[wb + 1], sb);
+                const uint32_t ta1 = __byte_perm(row1[wa], row1[wa + 1], sa), tb1 = __byte_perm(row1[wb], row1[wb + 1], sb);
+                uint32_t n0[4], n1[4];
+                n0[0] = __dp2a_lo(e1.x, ta0, 0u) >> 4; n0[1] = __dp2a_hi(e1.y, ta0, 0u) >> 4;
+                n0[2] = __dp2a_lo(e2.x, tb0, 0u) >> 4; n0[3] = __dp2a_hi(e2.y, tb0, 0u) >> 4;
+                n1[0] = __dp2a_lo(e1.x, ta1, 0u) >> 4; n1[1] = __dp2a_hi(e1.y, ta1, 0u) >> 4;
+                n1[2] = __dp2a_lo(e2.x, tb1, 0u) >> 4; n1[3] = __dp2a_hi(e2.y, tb1, 0u) >> 4;
                 uint32_t v = 0;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint2 ex = xt[4 * xw + k];
-                    const uint32_t x0 = ex.x & 0xffffu, x1 = ex.x >> 16, a0 = ex.y & 0xffffu, a1 = ex.y >> 16;
-                    const uint32_t n0 = (row0[x0] * a0 + row0[x1] * a1) >> 4;
-                    const uint32_t n1 = (row1[x0] * a0 + row1[x1] * a1) >> 4;
-                    v |= ((__umulhi(b0, n0) + __umulhi(b1, n1) + 2u) >> 2) << (8 * k);
-                }
+                for (int k = 0; k < 4; ++k) v |= ((__umulhi(b0, n0[k]) + __umulhi(b1, n1[k]) + 2u) >> 2) << (8 * k);
                 *reinterpret_cast<uint32_t *>(buf + y * pitch + 4 * xw) = v;
             }
             __syncthreads();
