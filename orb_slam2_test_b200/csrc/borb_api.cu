@@ -888,6 +888,11 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
         /* a frame or two: one CTA per (cell, frame), and the time is a cell's dependent chain -> four warps per cell */
         static const bool env_nw2 = getenv("BORB_FAST_NW2") != nullptr; /* A/B knob: two warps per cell in every shape */
         const bool four = !env_nw2 && (long long)P.n_cells * n <= 2LL * h->n_sm * 16;
+        /* a single frame: no more CTAs than are resident at once (8 of 128 threads per SM by registers) -- the few cells
+         * beyond are walked by CTAs that already hold their places, with the next window's TMA in flight, instead of
+         * waiting for a place and paying a prologue (1220 cells on 1184 places: 46.8 -> 46.3 us per call; fewer CTAs
+         * than that: 47.3 us at 7 per SM, 48.8 at 6) */
+        if (four && n == 1) grid.x = std::min(P.n_cells, h->n_sm * 8);
 #define K2(WP, NW) CU(launch_k(k_fast_cells<WP, NW>, grid, dim3(32 * NW), (size_t)(NW == 4 ? h->fast_smem4 : h->fast_smem), st, pdl2, \
         h->plan, (const BorbCell *)h->d_cells, n, h->fast_maps, f0, d_cand_xy, d_cand_score, d_ncand))
         if (four) { if (h->fast_wp == 64) K2(64, 4); else if (h->fast_wp == 80) K2(80, 4); else K2(96, 4); }
