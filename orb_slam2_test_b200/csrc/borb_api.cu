@@ -526,6 +526,14 @@ int build_plan(borb_extractor *h, int cols, int rows)
                  * strictly increasing and inside the source (true for every level scale > 1), and the staged window must
                  * fit the kernel's fixed pitch; else the level keeps k_pyr_resize */
                 bool ok = h->pyr_sp[l] <= PYR_SP_MAX && L.h >= 2 && S.h >= 2;
+                /* ... and the taps x0, x0 + 1 of the two pixels of every lane's pixel pair (an aligned group of four padded
+                 * columns from -PYR_LPAD on, reflected into the image) must lie within two aligned words */
+                auto refl = [&](int i) { if (i < 0) i = -i; if (i >= L.w) i = 2 * (L.w - 1) - i; return i; };
+                for (int c = -PYR_LPAD; c < L.w + BORB_EDGE && ok; c += 2) {
+                    const int ta = tab_i[L.xofs_off + refl(std::min(c, L.w - 1 + BORB_EDGE))];
+                    const int tb = tab_i[L.xofs_off + refl(std::min(c + 1, L.w - 1 + BORB_EDGE))];
+                    ok = std::max(ta, tb) + 1 - (std::min(ta, tb) & ~3) <= 7;
+                }
                 for (int d = 0; d < L.h && ok; ++d) {
                     const int sy = tab_i[L.yofs_off + d];
                     ok = sy >= 0 && sy + 1 <= S.h - 1 && (d == 0 || sy > tab_i[L.yofs_off + d - 1]);
@@ -843,10 +851,10 @@ int enqueue_kernels(borb_extractor *h, const uint8_t *dev_img, int n, size_t ste
             if (h->pyr_stream[l] && !pyr_stream_off) {
                 const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (P.lv[l - 1].h - 1 + 4 * PST_NSW - 1) / (4 * PST_NSW), n);
                 const uint2 *yinv = reinterpret_cast<const uint2 *>(h->d_tab_i + h->pyr_yinv_off[l]);
-                if (h->pyr_sp[l] <= 192)
-                    k_pyr_stream<384><<<g, PYR_NT, PST_ROWS * 384, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s, yinv, d_pyr);
+                if (h->pyr_sp[l] <= 192) /* + 16: the second word of the last pixel pair of the last staged row */
+                    k_pyr_stream<192><<<g, PYR_NT, PST_ROWS * 192 + 16, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s, yinv, d_pyr);
                 else
-                    k_pyr_stream<2 * PYR_SP_MAX><<<g, PYR_NT, PST_ROWS * 2 * PYR_SP_MAX, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s, yinv, d_pyr);
+                    k_pyr_stream<PYR_SP_MAX><<<g, PYR_NT, PST_ROWS * PYR_SP_MAX + 16, st>>>(h->plan, l, h->d_tab_i, h->d_tab_s, yinv, d_pyr);
                 continue;
             }
             const dim3 g((4 * pyr_words_per_row(L.w) + PYR_TW - 1) / PYR_TW, (L.prows + PYR_TH - 1) / PYR_TH, n);

@@ -232,12 +232,18 @@ k_pyr_resize(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
 #define PST_NSW 12                  /* source rows a warp walks (besides the one that seeds its stream) */
 #endif
 #define PST_ROWS (4 * PST_NSW + 1)
-/* PST_SP2 = staged row pitch in bytes (pairs), a template parameter: 2 * PYR_SP_MAX holds any window the host admits, 384
- * the window of the usual scale factors (<= 192 source columns for 128 output columns: 1.5) at 60 % of the shared memory */
+/* PST_SP = staged row pitch in bytes, a template parameter: PYR_SP_MAX holds any window the host admits, 192 the window of
+ * the usual scale factors (<= 192 source columns for 128 output columns: 1.5).
+ * Taps (second version): the staged rows are plain copies of the source rows; the four taps of a lane's pixels 0, 1 (x0,
+ * x0 + 1 of each) lie within two aligned words of a staged row and so do those of pixels 2, 3 (the host checks it per
+ * level: scale factors up to ~3), so a row's horizontal sums are 4 LDS.32 + 2 PRMT (a selector gathers a pair's taps:
+ * first pixel in bytes 0, 1, second in bytes 2, 3) + 4 dp2a.  The first version staged every row as byte PAIRS (element i =
+ * (s[i], s[i+1]), one LDS.U16 per tap pair): twice the shared-memory stores, 8 PRMT per staged vector, and lanes 9.6 bytes
+ * apart on the tap loads (half of the kernel's shared-memory wavefronts were their bank conflicts). */
 #ifndef PST_MINB
 #define PST_MINB 9
 #endif
-template <int PST_SP2>
+template <int PST_SP>
 __global__ void __launch_bounds__(PYR_NT, PST_MINB)
 k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restrict__ tab_i, const short *__restrict__ tab_s,
              const uint2 *__restrict__ yinv /* per source row: output row or ~0u, b0 | b1 << 16 */, uint8_t *__restrict__ pyr)
@@ -270,40 +276,25 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     sx_hi = __reduce_max_sync(0xffffffffu, sx_hi);
     const int s_tile = blockIdx.y * (4 * PST_NSW);
     const int s_last = min(s_tile + 4 * PST_NSW, S.h - 1);
-    {   /* stage source rows s_tile .. s_last of the window as byte pairs (see k_pyr_resize); the loads of four vectors
-         * are issued before the first of them is converted and stored (a thread stages 6-7 vectors: one at a time, the
-         * CTA waited out a DRAM latency per vector -- long-scoreboard stall 4.4 per issue in the first capture) */
-        const int vpr = (sx_hi - sx_lo) / 16 + 1; /* host guarantees vpr * 32 <= PST_SP2 */
+    {   /* stage source rows s_tile .. s_last of the window; the loads of four vectors are issued before the first of
+         * them is stored (a thread stages 6-7 vectors: one at a time, the CTA waited out a DRAM latency per vector) */
+        const int vpr = (sx_hi - sx_lo) / 16 + 1; /* host guarantees vpr * 16 <= PST_SP */
         const int nv = vpr * (s_last - s_tile + 1);
         const uint8_t *g = sbase + (size_t)s_tile * S.pitch + sx_lo;
         const uint32_t vmagic = 65536u / (uint32_t)vpr + 1u;
         for (int i0 = threadIdx.x; i0 < nv; i0 += 4 * PYR_NT) {
             uint4 q[4];
-            uint32_t w4[4];
             int off[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int i = i0 + u * PYR_NT;
                 const int rr = (int)(((uint32_t)min(i, nv - 1) * vmagic) >> 16), cc = min(i, nv - 1) - rr * vpr;
-                const uint32_t *gw = reinterpret_cast<const uint32_t *>(g + (size_t)rr * S.pitch) + 4 * cc;
-                q[u] = __ldg(reinterpret_cast<const uint4 *>(gw));
-                w4[u] = __ldg(gw + 4);
-                off[u] = i < nv ? rr * PST_SP2 + cc * 32 : -1;
+                q[u] = __ldg(reinterpret_cast<const uint4 *>(g + (size_t)rr * S.pitch) + cc);
+                off[u] = i < nv ? rr * PST_SP + cc * 16 : -1;
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (off[u] < 0) continue;
-                const uint32_t w[5] = {q[u].x, q[u].y, q[u].z, q[u].w, w4[u]};
-                uint32_t o[8];
-#pragma unroll
-                for (int m = 0; m < 4; ++m) {
-                    o[2 * m] = __byte_perm(w[m], 0u, 0x2110);
-                    o[2 * m + 1] = __byte_perm(w[m], w[m + 1], 0x4332);
-                }
-                uint4 *dstv = reinterpret_cast<uint4 *>(pyr_tile + off[u]);
-                dstv[0] = make_uint4(o[0], o[1], o[2], o[3]);
-                dstv[1] = make_uint4(o[4], o[5], o[6], o[7]);
-            }
+            for (int u = 0; u < 4; ++u)
+                if (off[u] >= 0) *reinterpret_cast<uint4 *>(pyr_tile + off[u]) = q[u];
         }
     }
     const int s0 = s_tile + warp * PST_NSW; /* the row that seeds this warp's stream */
@@ -313,9 +304,15 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     __syncthreads();
     if (s0 >= S.h - 1) return;
     const bool col_on = c < L.w + BORB_EDGE;
-    const unsigned char *A[4];
+    /* per pixel pair: the aligned word its taps start in (a pointer into the seed row) and the PRMT selector */
+    const uint32_t *A[2];
+    uint32_t sel[2];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) A[k] = pyr_tile + (warp * PST_NSW) * PST_SP2 + 2 * (sx[k] - sx_lo);
+    for (int pr = 0; pr < 2; ++pr) {
+        const int xa = sx[2 * pr] - sx_lo, xb = sx[2 * pr + 1] - sx_lo, base = min(xa, xb) & ~3;
+        A[pr] = reinterpret_cast<const uint32_t *>(pyr_tile + (warp * PST_NSW) * PST_SP + base);
+        sel[pr] = (uint32_t)(xa - base) | ((uint32_t)(xa + 1 - base) << 4) | ((uint32_t)(xb - base) << 8) | ((uint32_t)(xb + 1 - base) << 12);
+    }
     /* Output addressing.  The output rows a warp produces are CONSECUTIVE (yofs is strictly increasing), so the store
      * pointer runs: one 64-bit add per row.  Only the first and the last tiles of a level hold rows with a mirror in the
      * reflect-101 frame; they take the variant of the walk that carries the two mirror pointers. */
@@ -328,11 +325,16 @@ k_pyr_stream(const __grid_constant__ BorbPlan plan_c, int l, const int *__restri
     uint8_t *drow = frame + L.off + BORB_XPAD + c + (size_t)(d_first + BORB_EDGE) * pitch;
     const bool mirrors = d_first <= (uint32_t)BORB_EDGE || (int)d_last >= L.h - 1 - BORB_EDGE;
     uint32_t H[2][4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) H[0][k] = __dp2a_lo(aw[k], (uint32_t) * reinterpret_cast<const uint16_t *>(A[k]), 0u) >> 4;
 #define PST_HSUM(j)                                                                                                     \
-    _Pragma("unroll") for (int k = 0; k < 4; ++k)                                                                       \
-        H[(j) & 1][k] = __dp2a_lo(aw[k], (uint32_t) * reinterpret_cast<const uint16_t *>(A[k] + (j) * PST_SP2), 0u) >> 4
+    do {                                                                                                                \
+        const uint32_t ta_ = __byte_perm(A[0][(j) * (PST_SP / 4)], A[0][(j) * (PST_SP / 4) + 1], sel[0]);               \
+        const uint32_t tb_ = __byte_perm(A[1][(j) * (PST_SP / 4)], A[1][(j) * (PST_SP / 4) + 1], sel[1]);               \
+        H[(j) & 1][0] = __dp2a_lo(aw[0], ta_, 0u) >> 4;                                                                 \
+        H[(j) & 1][1] = __dp2a_hi(aw[1], ta_, 0u) >> 4;                                                                 \
+        H[(j) & 1][2] = __dp2a_lo(aw[2], tb_, 0u) >> 4;                                                                 \
+        H[(j) & 1][3] = __dp2a_hi(aw[3], tb_, 0u) >> 4;                                                                 \
+    } while (0)
+    PST_HSUM(0);
 #define PST_BLEND(j)                                                                                                    \
     const uint32_t bw_ = __shfl_sync(0xffffffffu, g.y, (j));                                                            \
     const uint32_t b0 = bw_ << 16, b1 = bw_ & 0xffff0000u;                                                              \
